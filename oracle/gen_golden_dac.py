@@ -1,0 +1,78 @@
+"""Golden vectors for the DAC decode path: run the REFERENCE classes
+(`fish_speech/models/dac/{modded_dac,rvq}.py`, imported unmodified through
+oracle/refshim for the absent descript packages) on CPU fp32, assert the oracle
+restatement (oracle/dac_ref.py) is bit-identical, and save small fixtures.
+TEST INFRASTRUCTURE.
+"""
+from __future__ import annotations
+
+from functools import partial
+
+import torch
+
+from oracle import dac_ref as D
+from oracle.gen_golden import GOLD, import_reference
+
+
+def build_reference_dac(c: D.DACConfig):
+    """Hand-instantiate what configs/modded_dac_vq.yaml describes (hydra is absent)."""
+    import_reference()
+    from fish_speech.models.dac import modded_dac as M
+    from fish_speech.models.dac import rvq
+
+    tf_cfg = M.ModelArgs(block_size=2048, n_layer=c.tf_layers, n_head=c.tf_heads, dim=c.tf_dim,
+                         intermediate_size=c.tf_ffn, n_local_heads=-1, head_dim=c.tf_head_dim,
+                         rope_base=c.tf_rope_base, norm_eps=c.tf_norm_eps, dropout_rate=0.1,
+                         attn_dropout_rate=0.1, channels_first=True)
+    post = M.WindowLimitedTransformer(causal=True, window_size=c.tf_window, input_dim=c.latent_dim, config=tf_cfg)
+    q = rvq.DownsampleResidualVectorQuantize(
+        input_dim=c.latent_dim, n_codebooks=c.n_codebooks, codebook_size=c.codebook_size,
+        codebook_dim=c.codebook_dim, quantizer_dropout=0.5, downsample_factor=list(c.upsample_factors),
+        post_module=post, pre_module=None, semantic_codebook_size=c.semantic_codebook_size)
+    general = partial(M.ModelArgs, block_size=8192, n_local_heads=-1, head_dim=64, rope_base=10000,
+                      norm_eps=1e-5, dropout_rate=0.1, attn_dropout_rate=0.1, channels_first=True)
+    # encoder side kept minimal (unused on decode): no transformer layers there
+    dac = M.DAC(sample_rate=c.sample_rate, encoder_dim=c.latent_dim // 16, encoder_rates=[2, 4, 8, 8],
+                decoder_dim=c.decoder_dim, decoder_rates=list(c.decoder_rates),
+                encoder_transformer_layers=[0, 0, 0, 0], decoder_transformer_layers=[0, 0, 0, 0],
+                transformer_general_config=general, quantizer=q)
+    return dac.eval()
+
+
+def golden(name: str, c: D.DACConfig, B: int, T: int, seed: int = 0, oob_codes: bool = False):
+    sd = D.make_state_dict(c, seed=seed)
+    codes = D.make_codes(c, B, T, seed=2)
+    if oob_codes:  # the fast AR emits ids in [0,4096) for every codebook; the codec clamps (rvq.py:354-359)
+        g = torch.Generator().manual_seed(5)
+        codes[:, 1:] = torch.randint(0, 4096, codes[:, 1:].shape, generator=g)
+    ref = build_reference_dac(c)
+    missing, unexpected = ref.load_state_dict(sd, strict=False)
+    assert not unexpected, unexpected
+    assert all(not k.startswith(("decoder.", "quantizer.upsample", "quantizer.post_module.layers",
+                                 "quantizer.post_module.norm")) for k in missing), missing
+    with torch.inference_mode():
+        y_ref = ref.from_indices(codes.clone())
+    stages = []
+    # nn.Parameters carry requires_grad=True; torch's CPU F.linear picks a different fp32 GEMM
+    # path for a non-contiguous input when the weight requires grad (measured: 2e-6 abs), so the
+    # restatement is compared with the same flag set to be bit-identical.
+    sd_rg = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    y = D.from_indices(c, sd_rg, codes.clone(), stages)
+    y_plain = D.from_indices(c, sd, codes.clone())
+    print(f"[golden] {name}: oracle(plain tensors) vs reference max abs {float((y_plain - y_ref).abs().max()):.2e}")
+    assert torch.equal(y, y_ref), f"{name}: oracle differs from reference, max {float((y - y_ref).abs().max())}"
+    print(f"[golden] {name}: oracle == reference (+shim) bit-exact, wav {tuple(y.shape)}, rms {float(y.pow(2).mean().sqrt()):.4f}")
+    torch.save({"cfg": c.__dict__, "seed": seed, "codes": codes, "wav": y_ref.clone(),
+                "z_std": float(stages[0].std()),
+                "weights_checksum": float(sum(v.double().abs().sum() for v in sd.values()))},
+               GOLD / f"{name}.pt")
+
+
+def main():
+    torch.manual_seed(0)
+    golden("dac_small", D.small_config(), B=2, T=24)
+    golden("dac_full_T12", D.DACConfig(), B=2, T=12, oob_codes=True)
+
+
+if __name__ == "__main__":
+    main()
