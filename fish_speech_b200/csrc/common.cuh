@@ -1,0 +1,103 @@
+// Shared device helpers for the fish-speech hot-path kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifndef __CUDA_ARCH__
+#define FSB_ARCH_OK 1
+#elif __CUDA_ARCH__ >= 1000
+#define FSB_ARCH_OK 1
+#else
+#error "fish_speech_b200 kernels are written for sm_100a only"
+#endif
+
+typedef __nv_bfloat16 bf16;
+
+#define FSB_WARP 32
+
+// ----------------------------------------------------------------------------- bf16 <-> fp32
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+__device__ __forceinline__ float bf16_bits_to_f(uint16_t b) { return __uint_as_float(((uint32_t)b) << 16); }
+__device__ __forceinline__ uint16_t f_to_bf16_bits(float f) {
+    return __bfloat16_as_ushort(__float2bfloat16_rn(f));
+}
+// round-trip through bf16 (one RNE rounding), the reference's per-op rounding point
+__device__ __forceinline__ float rbf(float f) { return __bfloat162float(__float2bfloat16_rn(f)); }
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+    f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x);
+    f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+    f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z);
+    f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+    return (uint32_t)f_to_bf16_bits(a) | ((uint32_t)f_to_bf16_bits(b) << 16);
+}
+
+// ----------------------------------------------------------------------------- memory
+// streaming 128-bit load: read-only path, do not allocate in L1 (weights are touched once per step)
+__device__ __forceinline__ uint4 ld_stream(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// bulk L2 prefetch of a contiguous byte range (16 B aligned, size multiple of 16)
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+}
+// spread a prefetch of [base, base+bytes) over the CTAs of the grid; called by one thread per CTA
+__device__ __forceinline__ void l2_prefetch_share(const void* base, size_t bytes, int cta, int n_cta) {
+    if (base == nullptr || bytes == 0) return;
+    size_t per = ((bytes / n_cta) + 15) & ~(size_t)15;
+    size_t off = (size_t)cta * per;
+    if (off >= bytes) return;
+    size_t n = bytes - off < per ? bytes - off : per;
+    n &= ~(size_t)15;
+    const char* p = (const char*)base + off;
+    while (n > 0) {
+        uint32_t c = n > 65536 ? 65536u : (uint32_t)n;
+        l2_prefetch_bulk(p, c);
+        p += c; n -= c;
+    }
+}
+
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// Everything before pdl_wait() may only touch immutable data (weights); all writes come after it.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// ----------------------------------------------------------------------------- reductions
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+// block-wide sum; `red` is >= 32 floats of shared memory; result broadcast to every thread
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    float t = (lane < nw) ? red[lane] : 0.f;
+    t = warp_sum(t);
+    return t;
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_max(v);
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    float t = (lane < nw) ? red[lane] : -INFINITY;
+    t = warp_max(t);
+    return t;
+}

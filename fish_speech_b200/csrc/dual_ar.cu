@@ -1,0 +1,637 @@
+// Dual-AR decode engine: handle, launch plumbing (PDL-chained kernels, CUDA-graph replay) and the C ABI.
+// See include/fish_b200.h for the boundary and DESIGN.md for the kernel inventory.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/fish_b200.h"
+#include "attn.cuh"
+#include "gemv.cuh"
+#include "sample.cuh"
+
+namespace {
+
+struct LayerW {
+    const bf16 *attn_norm = nullptr, *wqkv = nullptr, *q_norm = nullptr, *k_norm = nullptr, *wo = nullptr,
+               *ffn_norm = nullptr, *w1 = nullptr, *w3 = nullptr, *w2 = nullptr;
+    bf16 *kc = nullptr, *vc = nullptr;
+};
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+struct fsb_dual_ar {
+    fsb_dual_ar_desc d;
+    int max_seq_len = 0;
+    std::vector<LayerW> slow, fast;
+    const bf16 *emb = nullptr, *cb_emb = nullptr, *norm = nullptr, *fast_emb = nullptr, *fast_norm = nullptr,
+               *fast_out = nullptr, *out_w = nullptr;
+    const bf16 *rope = nullptr, *fast_rope = nullptr;
+    int rope_n = 0, fast_rope_n = 0;
+    int kv_max_batch = 0, kv_max_seq = 0, fkv_max_batch = 0, fkv_max_seq = 0;
+    // workspace carve-up
+    bf16 *x = nullptr, *x2 = nullptr, *qkv = nullptr, *y = nullptr, *ff = nullptr, *hidden = nullptr,
+         *xfast = nullptr, *xf = nullptr, *xf2 = nullptr, *slow_logits = nullptr, *fast_logits = nullptr;
+    float *ws_acc = nullptr, *ws_ml = nullptr;
+    int32_t *counters = nullptr, *pf_pos = nullptr, *pf_slot = nullptr;
+    int max_splits = 32;
+    // options
+    int use_pdl = 1, use_graph = 1, attn_splits = 0;
+    size_t self_pf_bytes = 512 * 1024;
+    int n_sm = 148;
+    // graph cache
+    cudaGraphExec_t exec = nullptr;
+    cudaStream_t cap_stream = nullptr;  // capture happens here: the caller's stream may be the legacy default stream
+    size_t R = 8;                       // rows the workspace is sized for
+    fsb_frame_args cached{};
+    bool cached_valid = false;
+    std::string err;
+};
+
+namespace {
+
+int fail(fsb_dual_ar* h, const std::string& m) {
+    if (h) h->err = m;
+    return 1;
+}
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(h, std::string(#call) + ": " + cudaGetErrorString(e_) + " @" + std::to_string(__LINE__)); \
+    } while (0)
+
+template <typename Args>
+cudaError_t launch(void (*k)(Args), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl, const Args& a) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, k, a);
+}
+
+// ------------------------------------------------------------------------------------------- GEMV dispatch
+typedef void (*gemv_fn)(GemvArgs);
+template <int PRO, int EPI>
+gemv_fn pick_gemv(int M) {
+    constexpr bool SW = (EPI == EPI_SWIGLU);
+    if (M <= 1) return gemv_kernel<1, SW ? 4 : 8, PRO, EPI>;
+    if (M <= 2) return gemv_kernel<2, SW ? 2 : 4, PRO, EPI>;
+    if (M <= 4) return gemv_kernel<4, SW ? 2 : 4, PRO, EPI>;
+    return gemv_kernel<8, SW ? 1 : 2, PRO, EPI>;
+}
+gemv_fn pick_gemv(int M, int pro, int epi) {
+    if (pro == PRO_RMSNORM) {
+        if (epi == EPI_STORE) return pick_gemv<PRO_RMSNORM, EPI_STORE>(M);
+        if (epi == EPI_RESIDUAL) return pick_gemv<PRO_RMSNORM, EPI_RESIDUAL>(M);
+        return pick_gemv<PRO_RMSNORM, EPI_SWIGLU>(M);
+    }
+    if (epi == EPI_STORE) return pick_gemv<PRO_NONE, EPI_STORE>(M);
+    if (epi == EPI_RESIDUAL) return pick_gemv<PRO_NONE, EPI_RESIDUAL>(M);
+    return pick_gemv<PRO_NONE, EPI_SWIGLU>(M);
+}
+int m_bucket(int M) { return M <= 1 ? 1 : M <= 2 ? 2 : M <= 4 ? 4 : 8; }
+
+cudaError_t set_gemv_attrs() {
+    static bool done = false;
+    if (done) return cudaSuccess;
+    const int ms[4] = {1, 2, 4, 8};
+    for (int pro = 0; pro < 2; ++pro)
+        for (int epi = 0; epi < 3; ++epi)
+            for (int i = 0; i < 4; ++i) {
+                cudaError_t e = cudaFuncSetAttribute((const void*)pick_gemv(ms[i], pro, epi),
+                                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+                if (e != cudaSuccess) return e;
+            }
+    done = true;
+    return cudaSuccess;
+}
+
+// rows M are processed in passes of <= 8; x rows have stride K, out/res rows stride N
+cudaError_t run_gemv(int n_sm, size_t self_pf, bool pdl, cudaStream_t s, int M, int N, int K, int pro, int epi,
+                     const bf16* W, const bf16* W2, const bf16* x, const bf16* norm_w, const bf16* res, bf16* out,
+                     bf16* xnorm_out, float eps, const void* pf_ptr, size_t pf_bytes) {
+    for (int m0 = 0; m0 < M; m0 += 8) {
+        const int mv = std::min(8, M - m0);
+        const int mb = m_bucket(mv);
+        GemvArgs a{};
+        a.W = W; a.W2 = W2; a.x = x + (size_t)m0 * K; a.norm_w = norm_w;
+        a.res = res ? res + (size_t)m0 * N : nullptr;
+        a.out = out + (size_t)m0 * N;
+        a.xnorm_out = xnorm_out ? xnorm_out + (size_t)m0 * K : nullptr;
+        a.N = N; a.K = K; a.M_valid = mv; a.eps = eps;
+        a.pf_ptr = (m0 == 0) ? pf_ptr : nullptr; a.pf_bytes = pf_bytes; a.self_pf_bytes = self_pf;
+        int nb = std::min(2 * n_sm, std::max(1, N / 4));
+        size_t smem = (size_t)mb * K * sizeof(bf16);
+        cudaError_t e = launch(pick_gemv(mv, pro, epi), dim3(nb), dim3(GEMV_THREADS), smem, s, pdl, a);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+// ------------------------------------------------------------------------------------------- attention dispatch
+typedef void (*attn_fn)(AttnArgs);
+struct AttnKernels { attn_fn decode, append, fast; int threads_fast; };
+bool pick_attn(int hd, int gq, AttnKernels* k) {
+#define CASE(HD, GQ)                                                               \
+    if (hd == HD && gq == GQ) {                                                    \
+        k->decode = attn_decode_kernel<HD, GQ>;                                    \
+        k->append = rope_append_kernel<HD>;                                        \
+        k->fast = fast_attn_kernel<HD, GQ>;                                        \
+        k->threads_fast = 32 * GQ;                                                 \
+        return true;                                                               \
+    }
+    CASE(128, 4) CASE(64, 4) CASE(128, 1) CASE(64, 1) CASE(128, 2) CASE(64, 2) CASE(128, 8) CASE(64, 8)
+#undef CASE
+    return false;
+}
+
+int splits_for(const fsb_dual_ar* h, int M) {
+    if (h->attn_splits > 0) return std::min(h->attn_splits, h->max_splits);
+    // enough CTAs to cover the chip at small M, tiles of >= 128 keys at the longest context
+    int by_len = std::max(1, (h->max_seq_len + 255) / 256);
+    int by_sm = std::max(1, (2 * h->n_sm) / std::max(1, M * h->d.n_kv_head));
+    return std::max(1, std::min(std::min(by_len, by_sm), h->max_splits));
+}
+
+// ------------------------------------------------------------------------------------------- the passes
+// transformer layers over M rows. x_in: [M][D] input (not modified); result in h->x (slow) / h->xf (fast)
+int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_in, const int32_t* pos,
+               const int32_t* slots, bool fused_append, int pos_fixed) {
+    const fsb_dual_ar_desc& d = h->d;
+    const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn;
+    const int QKV = (H + 2 * KV) * HD;
+    AttnKernels ak;
+    if (!pick_attn(HD, H / KV, &ak)) return fail(h, "unsupported head_dim / GQA ratio");
+    const std::vector<LayerW>& L = fast ? h->fast : h->slow;
+    bf16* xa = fast ? h->xf : h->x;
+    bf16* xb = fast ? h->xf2 : h->x2;
+    const bool pdl = h->use_pdl;
+    const bf16* cur = x_in;
+    const int splits = splits_for(h, M);
+    for (size_t l = 0; l < L.size(); ++l) {
+        const LayerW& w = L[l];
+        if (!w.wqkv || !w.wo || !w.w1 || !w.w2 || !w.w3 || !w.attn_norm || !w.ffn_norm || !w.kc || !w.vc)
+            return fail(h, "unbound weights / kv cache in layer " + std::to_string(l));
+        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, QKV, D, PRO_RMSNORM, EPI_STORE, w.wqkv, nullptr, cur,
+                    w.attn_norm, nullptr, h->qkv, nullptr, d.norm_eps, nullptr, 0));
+        AttnArgs a{};
+        a.qkv = h->qkv; a.kcache = w.kc; a.vcache = w.vc; a.q_norm = w.q_norm; a.k_norm = w.k_norm;
+        a.rope = fast ? h->fast_rope : h->rope;
+        a.pos = pos; a.slots = slots; a.y = h->y; a.ws_acc = h->ws_acc; a.ws_ml = h->ws_ml;
+        a.counters = h->counters; a.H = H; a.KV = KV;
+        a.S = fast ? h->fkv_max_seq : h->kv_max_seq;
+        a.qk_norm = d.qk_norm; a.eps = d.norm_eps; a.scale = (float)(1.0 / std::sqrt((double)HD));
+        a.pos_fixed = pos_fixed;
+        a.pf_ptr = w.wo; a.pf_bytes = (size_t)D * H * HD * sizeof(bf16);
+        if (fast) {
+            CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
+        } else {
+            a.splits = splits;
+            a.fused_append = fused_append ? 1 : 0;
+            if (!fused_append) {
+                AttnArgs ap = a;
+                ap.pf_ptr = nullptr; ap.pf_bytes = 0;
+                CK(launch(ak.append, dim3(KV, M), dim3(64), 0, s, pdl, ap));
+            }
+            CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, pdl, a));
+        }
+        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, D, H * HD, PRO_NONE, EPI_RESIDUAL, w.wo, nullptr, h->y,
+                    nullptr, cur, xb, nullptr, d.norm_eps, nullptr, 0));
+        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, F, D, PRO_RMSNORM, EPI_SWIGLU, w.w1, w.w3, xb, w.ffn_norm,
+                    nullptr, h->ff, nullptr, d.norm_eps, nullptr, 0));
+        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, D, F, PRO_NONE, EPI_RESIDUAL, w.w2, nullptr, h->ff, nullptr,
+                    xb, xa, nullptr, d.norm_eps, nullptr, 0));
+        cur = xa;
+    }
+    return 0;
+}
+
+int run_embed(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens) {
+    const fsb_dual_ar_desc& d = h->d;
+    if (!h->emb || !h->cb_emb) return fail(h, "embeddings not bound");
+    EmbedArgs e{};
+    e.tokens = tokens; e.emb = h->emb; e.cb_emb = h->cb_emb; e.x = h->x2;  // x2: layer 0 reads it as x_in
+    e.D = d.dim; e.C = d.num_codebooks; e.cb = d.codebook_size;
+    e.sem_begin = d.semantic_begin_id; e.sem_end = d.semantic_end_id; e.scale = d.scale_codebook_embeddings;
+    e.inv_div = (float)std::sqrt((double)(d.num_codebooks + 1));
+    e.pf_ptr = nullptr; e.pf_bytes = 0;
+    CK(launch(embed_kernel, dim3(M), dim3(256), 0, s, h->use_pdl != 0, e));
+    return 0;
+}
+
+// slow stack + final norm + LM head for M decode rows
+int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, const int32_t* pos,
+                  const int32_t* slots) {
+    const fsb_dual_ar_desc& d = h->d;
+    if (int r = run_embed(h, s, M, tokens)) return r;
+    // embed wrote x2; layer 0 uses it as input and as the wo residual, writes xb = x2?  -> use a distinct buffer
+    // (run_layers writes xb = h->x2 in layer 0 while `cur` == h->x2 is still the residual source of the same
+    //  kernel: same element read-then-written by the same thread only, which is safe for EPI_RESIDUAL.)
+    if (int r = run_layers(h, s, false, M, h->x2, pos, slots, true, -1)) return r;
+    const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
+    if (!head || !h->norm) return fail(h, "LM head / final norm not bound");
+    CK(run_gemv(h->n_sm, h->self_pf_bytes, h->use_pdl != 0, s, M, d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head,
+                nullptr, h->x, h->norm, nullptr, h->slow_logits, h->hidden, d.norm_eps, nullptr, 0));
+    return 0;
+}
+
+int run_fast_step(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* x_in, int cb_idx, bool want_logits) {
+    const fsb_dual_ar_desc& d = h->d;
+    if (cb_idx < 0 || cb_idx >= d.num_codebooks) return fail(h, "codebook_idx out of range");
+    if (int r = run_layers(h, s, true, M, x_in, nullptr, nullptr, true, cb_idx)) return r;
+    if (want_logits) {
+        if (!h->fast_out || !h->fast_norm) return fail(h, "fast head not bound");
+        bf16* lg = h->fast_logits + (size_t)cb_idx * h->R * d.codebook_size;
+        CK(run_gemv(h->n_sm, h->self_pf_bytes, h->use_pdl != 0, s, M, d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE,
+                    h->fast_out, nullptr, h->xf, h->fast_norm, nullptr, lg, nullptr, d.norm_eps, nullptr, 0));
+    }
+    return 0;
+}
+
+int enqueue_frame(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
+    const fsb_dual_ar_desc& d = h->d;
+    const int B = fa.batch, C = d.num_codebooks, V = d.vocab, cb = d.codebook_size;
+    const bool pdl = h->use_pdl != 0;
+    if (int r = run_slow_step(h, s, B, fa.cur_tokens, fa.pos, fa.slots)) return r;
+
+    SampleArgs sa{};
+    sa.logits = h->slow_logits; sa.ld_logits = V; sa.V = V;
+    sa.bias = (const bf16*)fa.logit_bias;
+    if (fa.restrict_scan && fa.logit_bias) {
+        // finite support of semantic_logit_bias (inference.py:308-320), ascending
+        int lo0 = d.im_end_id, hi0 = d.im_end_id + 1, lo1 = d.semantic_begin_id, hi1 = d.semantic_end_id + 1;
+        if (lo0 >= lo1 && lo0 < hi1) { lo0 = hi0 = 0; }
+        else if (lo0 > lo1) { std::swap(lo0, lo1); std::swap(hi0, hi1); }
+        sa.seg_lo[0] = lo0; sa.seg_hi[0] = hi0; sa.seg_lo[1] = lo1; sa.seg_hi[1] = hi1;
+    } else {
+        sa.seg_lo[0] = 0; sa.seg_hi[0] = V; sa.seg_lo[1] = sa.seg_hi[1] = 0;
+    }
+    sa.top_k = fa.top_k;
+    sa.n_variants = 2;
+    sa.temp[0] = fa.temperature; sa.top_p[0] = fa.top_p;
+    sa.temp[1] = 1.0f;       // RAS_HIGH_TEMP  (inference.py:50)
+    sa.top_p[1] = 0.8984375f;  // RAS_HIGH_TOP_P 0.9 as bf16 (inference.py:51, tensor built in the model dtype)
+    sa.uniforms = (const bf16*)fa.uniforms;
+    sa.u_stride = 2LL * V + (long long)(C - 1) * cb;
+    sa.u_offset = 0;
+    sa.seed = fa.seed; sa.frame_counter = fa.frame_counter; sa.draw_id = 0;
+    sa.mode = 1; sa.tokens = fa.cur_tokens; sa.out_col = 0; sa.n_cols = C + 1;
+    sa.ras_window = fa.ras_window;
+    sa.sem_begin = d.semantic_begin_id; sa.sem_end = d.semantic_end_id; sa.im_end = d.im_end_id;
+    sa.codebook_size = cb; sa.done = fa.done;
+    sa.fast_emb = h->fast_emb; sa.xfast = h->xfast; sa.D = d.dim;
+    CK(launch(sample_kernel, dim3(B), dim3(SAMPLE_THREADS), 0, s, pdl, sa));
+
+    // fast AR: pass 0 on the slow hidden state (output discarded, inference.py:148-149), then C-1 sampled passes
+    const bf16* fin = d.norm_fastlayer_input ? h->hidden : h->x;
+    if (int r = run_fast_step(h, s, B, fin, 0, false)) return r;
+    for (int i = 1; i < C; ++i) {
+        if (int r = run_fast_step(h, s, B, h->xfast, i, true)) return r;
+        SampleArgs fs{};
+        fs.logits = h->fast_logits + (size_t)i * h->R * cb; fs.ld_logits = cb; fs.V = cb;
+        fs.bias = nullptr;
+        fs.seg_lo[0] = 0; fs.seg_hi[0] = cb; fs.seg_lo[1] = fs.seg_hi[1] = 0;
+        fs.top_k = fa.top_k; fs.n_variants = 1;
+        fs.temp[0] = fa.temperature; fs.top_p[0] = fa.top_p; fs.temp[1] = 1.f; fs.top_p[1] = 1.f;
+        fs.uniforms = (const bf16*)fa.uniforms;
+        fs.u_stride = sa.u_stride; fs.u_offset = 2LL * V + (long long)(i - 1) * cb;
+        fs.seed = fa.seed; fs.frame_counter = fa.frame_counter; fs.draw_id = i;
+        fs.mode = 0; fs.tokens = fa.cur_tokens; fs.out_col = i + 1; fs.n_cols = C + 1;
+        fs.ras_window = nullptr;
+        fs.sem_begin = d.semantic_begin_id; fs.sem_end = d.semantic_end_id; fs.im_end = d.im_end_id;
+        fs.codebook_size = cb; fs.done = nullptr;
+        fs.fast_emb = (i + 1 < C) ? h->fast_emb : nullptr; fs.xfast = h->xfast; fs.D = d.dim;
+        CK(launch(sample_kernel, dim3(B), dim3(SAMPLE_THREADS), 0, s, pdl, fs));
+    }
+    FrameEndArgs fe{};
+    fe.tokens = fa.cur_tokens; fe.pos = fa.pos; fe.ras_window = fa.ras_window; fe.out_tokens = fa.out_tokens;
+    fe.frame_counter = fa.frame_counter; fe.B = B; fe.n_cols = C + 1; fe.max_frames = fa.max_frames;
+    CK(launch(frame_end_kernel, dim3(1), dim3(64), 0, s, pdl, fe));
+    return 0;
+}
+
+__global__ void fill_prefill_kernel(int32_t* pos, int32_t* slot, int n, int pos0, int slot_v) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { pos[i] = pos0 + i; slot[i] = slot_v; }
+}
+
+}  // namespace
+
+// =============================================================================================== C ABI
+extern "C" {
+
+int fsb_abi_version(void) { return FSB_ABI_VERSION; }
+
+static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, char* base, fsb_dual_ar* h, size_t* total) {
+    size_t off = 0;
+    const size_t R = (size_t)std::max(d.max_rows, 8);
+    const int QKV = (d.n_head + 2 * d.n_kv_head) * d.head_dim;
+    auto take = [&](size_t bytes) {
+        char* p = base ? base + off : nullptr;
+        off = align_up(off + bytes, 256);
+        return p;
+    };
+#define T(field, type, count) { char* p_ = take((size_t)(count) * sizeof(type)); if (h) h->field = (type*)p_; }
+    T(x, bf16, R * d.dim) T(x2, bf16, R * d.dim) T(qkv, bf16, R * QKV) T(y, bf16, R * d.n_head * d.head_dim)
+    T(ff, bf16, R * d.ffn) T(hidden, bf16, R * d.dim) T(xfast, bf16, R * d.dim) T(xf, bf16, R * d.dim)
+    T(xf2, bf16, R * d.dim) T(slow_logits, bf16, R * d.vocab)
+    T(fast_logits, bf16, (size_t)d.num_codebooks * R * d.codebook_size)
+    const int gq = d.n_head / std::max(1, d.n_kv_head);
+    T(ws_acc, float, R * d.n_kv_head * max_splits * gq * d.head_dim)
+    T(ws_ml, float, R * d.n_kv_head * max_splits * gq * 2)
+    T(counters, int32_t, R * d.n_kv_head)
+    T(pf_pos, int32_t, (size_t)max_seq_len + 8) T(pf_slot, int32_t, (size_t)max_seq_len + 8)
+#undef T
+    *total = off;
+}
+
+size_t fsb_dual_ar_workspace_bytes(const fsb_dual_ar_desc* desc, int32_t max_seq_len) {
+    size_t total = 0;
+    carve(*desc, max_seq_len, 32, nullptr, nullptr, &total);
+    return total;
+}
+
+int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* workspace, size_t workspace_bytes,
+                       fsb_dual_ar** out) {
+    if (!desc || !out || !workspace) return 1;
+    fsb_dual_ar* h = new fsb_dual_ar();
+    h->d = *desc;
+    h->max_seq_len = max_seq_len;
+    h->R = (size_t)std::max(desc->max_rows, 8);
+    *out = h;
+    const fsb_dual_ar_desc& d = h->d;
+    if (d.dim % 8 || d.ffn % 8 || d.head_dim % 32 || d.n_head % d.n_kv_head || d.num_codebooks > FAST_MAX_CTX ||
+        d.num_codebooks < 1 || d.max_rows < 1)
+        return fail(h, "unsupported model shape (dim/ffn % 8, head_dim % 32, num_codebooks <= 16 required)");
+    AttnKernels ak;
+    if (!pick_attn(d.head_dim, d.n_head / d.n_kv_head, &ak)) return fail(h, "unsupported head_dim / GQA ratio");
+    size_t need = 0;
+    carve(d, max_seq_len, h->max_splits, (char*)workspace, h, &need);
+    if (need > workspace_bytes) return fail(h, "workspace too small");
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) return fail(h, "fish_speech_b200 requires an sm_100a device (B200)");
+    h->n_sm = prop.multiProcessorCount;
+    CK(set_gemv_attrs());
+    CK(cudaMemset(h->counters, 0, (size_t)std::max(d.max_rows, 8) * d.n_kv_head * sizeof(int32_t)));
+    h->slow.resize(d.n_layer);
+    h->fast.resize(d.n_fast_layer);
+    if (const char* e = getenv("FSB_PDL")) h->use_pdl = atoi(e);
+    if (const char* e = getenv("FSB_GRAPH")) h->use_graph = atoi(e);
+    if (const char* e = getenv("FSB_SELF_PF_KB")) h->self_pf_bytes = (size_t)atol(e) * 1024;
+    return 0;
+}
+
+int fsb_dual_ar_destroy(fsb_dual_ar* h) {
+    if (!h) return 0;
+    if (h->exec) cudaGraphExecDestroy(h->exec);
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
+    delete h;
+    return 0;
+}
+
+const char* fsb_dual_ar_last_error(const fsb_dual_ar* h) { return h ? h->err.c_str() : "null handle"; }
+
+int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
+    if (!h || !name) return 1;
+    std::string n(name);
+    if (n == "pdl") h->use_pdl = (int)value;
+    else if (n == "graph") h->use_graph = (int)value;
+    else if (n == "self_prefetch_kb") h->self_pf_bytes = (size_t)value * 1024;
+    else if (n == "attn_splits") h->attn_splits = (int)value;
+    else return fail(h, "unknown option " + n);
+    h->cached_valid = false;
+    return 0;
+}
+
+int fsb_dual_ar_bind_weight(fsb_dual_ar* h, const char* name, const void* dptr, int64_t rows, int64_t cols) {
+    if (!h || !name || !dptr) return 1;
+    const fsb_dual_ar_desc& d = h->d;
+    const bf16* p = (const bf16*)dptr;
+    std::string n(name);
+    if (((uintptr_t)dptr) & 15) return fail(h, n + ": pointer must be 16-byte aligned");
+    auto expect = [&](int64_t r, int64_t c) {
+        if (rows != r || cols != c) {
+            fail(h, n + ": expected [" + std::to_string(r) + "," + std::to_string(c) + "] got [" +
+                        std::to_string(rows) + "," + std::to_string(cols) + "]");
+            return false;
+        }
+        return true;
+    };
+    const int64_t D = d.dim, HD = d.head_dim, QKV = (int64_t)(d.n_head + 2 * d.n_kv_head) * HD;
+    h->cached_valid = false;
+    if (n == "embeddings.weight") { if (!expect(d.vocab, D)) return 1; h->emb = p; return 0; }
+    if (n == "output.weight") { if (!expect(d.vocab, D)) return 1; h->out_w = p; return 0; }
+    if (n == "codebook_embeddings.weight") { if (!expect((int64_t)d.codebook_size * d.num_codebooks, D)) return 1; h->cb_emb = p; return 0; }
+    if (n == "norm.weight") { if (!expect(D, 1)) return 1; h->norm = p; return 0; }
+    if (n == "fast_embeddings.weight") { if (!expect(d.codebook_size, D)) return 1; h->fast_emb = p; return 0; }
+    if (n == "fast_norm.weight") { if (!expect(D, 1)) return 1; h->fast_norm = p; return 0; }
+    if (n == "fast_output.weight") { if (!expect(d.codebook_size, D)) return 1; h->fast_out = p; return 0; }
+    bool fast = false;
+    size_t pos = 0;
+    if (n.rfind("fast_layers.", 0) == 0) { fast = true; pos = 12; }
+    else if (n.rfind("layers.", 0) == 0) { pos = 7; }
+    else return fail(h, "unknown weight name " + n);
+    size_t dot = n.find('.', pos);
+    if (dot == std::string::npos) return fail(h, "bad weight name " + n);
+    int li = atoi(n.substr(pos, dot - pos).c_str());
+    std::vector<LayerW>& L = fast ? h->fast : h->slow;
+    if (li < 0 || li >= (int)L.size()) return fail(h, "layer index out of range in " + n);
+    LayerW& w = L[li];
+    std::string k = n.substr(dot + 1);
+    if (k == "attention.wqkv.weight") { if (!expect(QKV, D)) return 1; w.wqkv = p; }
+    else if (k == "attention.wo.weight") { if (!expect(D, (int64_t)d.n_head * HD)) return 1; w.wo = p; }
+    else if (k == "attention.q_norm.weight") { if (!expect(HD, 1)) return 1; w.q_norm = p; }
+    else if (k == "attention.k_norm.weight") { if (!expect(HD, 1)) return 1; w.k_norm = p; }
+    else if (k == "feed_forward.w1.weight") { if (!expect(d.ffn, D)) return 1; w.w1 = p; }
+    else if (k == "feed_forward.w3.weight") { if (!expect(d.ffn, D)) return 1; w.w3 = p; }
+    else if (k == "feed_forward.w2.weight") { if (!expect(D, d.ffn)) return 1; w.w2 = p; }
+    else if (k == "ffn_norm.weight") { if (!expect(D, 1)) return 1; w.ffn_norm = p; }
+    else if (k == "attention_norm.weight") { if (!expect(D, 1)) return 1; w.attn_norm = p; }
+    else return fail(h, "unknown weight name " + n);
+    return 0;
+}
+
+int fsb_dual_ar_bind_rope(fsb_dual_ar* h, int32_t is_fast, const void* table, int32_t n_pos) {
+    if (!h || !table) return 1;
+    if (is_fast) { h->fast_rope = (const bf16*)table; h->fast_rope_n = n_pos; }
+    else { h->rope = (const bf16*)table; h->rope_n = n_pos; }
+    h->cached_valid = false;
+    return 0;
+}
+
+int fsb_dual_ar_bind_kv(fsb_dual_ar* h, int32_t is_fast, int32_t layer, void* k, void* v, int32_t max_batch,
+                        int32_t max_seq) {
+    if (!h || !k || !v) return 1;
+    std::vector<LayerW>& L = is_fast ? h->fast : h->slow;
+    if (layer < 0 || layer >= (int)L.size()) return fail(h, "kv layer out of range");
+    if ((((uintptr_t)k) | ((uintptr_t)v)) & 15) return fail(h, "kv pointers must be 16-byte aligned");
+    L[layer].kc = (bf16*)k; L[layer].vc = (bf16*)v;
+    if (is_fast) {
+        if (max_seq < h->d.num_codebooks) return fail(h, "fast kv cache shorter than num_codebooks");
+        h->fkv_max_batch = max_batch; h->fkv_max_seq = max_seq;
+    } else {
+        if (max_seq > h->max_seq_len) return fail(h, "kv max_seq exceeds the handle's max_seq_len");
+        h->kv_max_batch = max_batch; h->kv_max_seq = max_seq;
+    }
+    h->cached_valid = false;
+    return 0;
+}
+
+static int check_ready(fsb_dual_ar* h, int B) {
+    if (!h) return 1;
+    if (B < 1 || B > h->d.max_rows) return fail(h, "batch out of range (max_rows)");
+    if (!h->rope || !h->fast_rope) return fail(h, "RoPE tables not bound");
+    if (B > h->kv_max_batch || B > h->fkv_max_batch) return fail(h, "batch exceeds the bound KV caches");
+    return 0;
+}
+
+int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_t slot, int32_t pos0, void* stream) {
+    if (int r = check_ready(h, 1)) return r;
+    if (T <= 0) return 0;
+    if (pos0 < 0 || pos0 + T > h->kv_max_seq || pos0 + T > h->rope_n) return fail(h, "prefill exceeds max_seq_len");
+    if (slot < 0 || slot >= h->kv_max_batch) return fail(h, "slot out of range");
+    cudaStream_t s = (cudaStream_t)stream;
+    fill_prefill_kernel<<<(T + 255) / 256, 256, 0, s>>>(h->pf_pos, h->pf_slot, T, pos0, slot);
+    CK(cudaGetLastError());
+    const int C1 = h->d.num_codebooks + 1;
+    const int chunk = 8;
+    for (int t0 = 0; t0 < T; t0 += chunk) {
+        const int M = std::min(chunk, T - t0);
+        if (int r = run_embed(h, s, M, tokens + (size_t)t0 * C1)) return r;
+        if (int r = run_layers(h, s, false, M, h->x2, h->pf_pos + t0, h->pf_slot + t0, false, -1)) return r;
+    }
+    return 0;
+}
+
+int fsb_dual_ar_slow_step(fsb_dual_ar* h, int32_t B, const int32_t* tokens, const int32_t* pos, const int32_t* slots,
+                          void* stream) {
+    if (int r = check_ready(h, B)) return r;
+    return run_slow_step(h, (cudaStream_t)stream, B, tokens, pos, slots);
+}
+
+int fsb_dual_ar_fast_step(fsb_dual_ar* h, int32_t B, const void* x, int32_t codebook_idx, int32_t want_logits,
+                          void* stream) {
+    if (int r = check_ready(h, B)) return r;
+    const bf16* xin = x ? (const bf16*)x : (h->d.norm_fastlayer_input ? h->hidden : h->x);
+    return run_fast_step(h, (cudaStream_t)stream, B, xin, codebook_idx, want_logits != 0);
+}
+
+int fsb_dual_ar_buffer(fsb_dual_ar* h, const char* name, void** dptr, size_t* bytes) {
+    if (!h || !name || !dptr || !bytes) return 1;
+    const fsb_dual_ar_desc& d = h->d;
+    const size_t R = (size_t)std::max(d.max_rows, 8);
+    std::string n(name);
+    if (n == "slow_logits") { *dptr = h->slow_logits; *bytes = R * d.vocab * 2; }
+    else if (n == "hidden") { *dptr = h->hidden; *bytes = R * d.dim * 2; }
+    else if (n == "fast_logits") { *dptr = h->fast_logits; *bytes = (size_t)d.num_codebooks * R * d.codebook_size * 2; }
+    else if (n == "x") { *dptr = h->x; *bytes = R * d.dim * 2; }
+    else if (n == "xfast") { *dptr = h->xfast; *bytes = R * d.dim * 2; }
+    else return fail(h, "unknown buffer " + n);
+    return 0;
+}
+
+int fsb_dual_ar_decode_frames(fsb_dual_ar* h, const fsb_frame_args* args, int32_t n_frames, void* stream) {
+    if (!args) return 1;
+    if (int r = check_ready(h, args->batch)) return r;
+    if (!args->cur_tokens || !args->pos || !args->frame_counter) return fail(h, "cur_tokens/pos/frame_counter required");
+    if (args->top_k < 1 || args->top_k > SAMPLE_MAXK) return fail(h, "top_k must be in [1, 64]");
+    if (!h->fast_emb) return fail(h, "fast_embeddings not bound");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!h->use_graph) {
+        for (int i = 0; i < n_frames; ++i)
+            if (int r = enqueue_frame(h, s, *args)) return r;
+        return 0;
+    }
+    if (!h->cached_valid || memcmp(&h->cached, args, sizeof(fsb_frame_args)) != 0) {
+        if (h->exec) { cudaGraphExecDestroy(h->exec); h->exec = nullptr; }
+        cudaGraph_t g = nullptr;
+        if (!h->cap_stream) CK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+        CK(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+        int r = enqueue_frame(h, h->cap_stream, *args);
+        cudaError_t e = cudaStreamEndCapture(h->cap_stream, &g);
+        if (r) { if (g) cudaGraphDestroy(g); return r; }
+        if (e != cudaSuccess) return fail(h, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
+        e = cudaGraphInstantiate(&h->exec, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) { h->exec = nullptr; return fail(h, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
+        memcpy(&h->cached, args, sizeof(fsb_frame_args));
+        h->cached_valid = true;
+    }
+    for (int i = 0; i < n_frames; ++i) CK(cudaGraphLaunch(h->exec, s));
+    return 0;
+}
+
+double fsb_dual_ar_frame_bytes(const fsb_dual_ar* h, int32_t batch, int64_t ctx_sum, int32_t masked_head) {
+    if (!h) return 0;
+    const fsb_dual_ar_desc& d = h->d;
+    const double D = d.dim, HD = d.head_dim, H = d.n_head, KV = d.n_kv_head, F = d.ffn, C = d.num_codebooks;
+    const double p_layer = D * (H + 2 * KV) * HD + H * HD * D + 3 * D * F;
+    const double v_eff = masked_head ? (d.semantic_end_id - d.semantic_begin_id + 2) : d.vocab;
+    double bytes = 2.0 * (d.n_layer * p_layer + v_eff * D) + 2.0 * (C * d.n_fast_layer * p_layer + (C - 1) * d.codebook_size * D);
+    bytes += (double)ctx_sum * 2.0 * d.n_layer * 2.0 * KV * HD;
+    (void)batch;
+    return bytes;
+}
+
+int32_t fsb_dual_ar_launches_per_frame(const fsb_dual_ar* h, int32_t batch) {
+    if (!h) return 0;
+    const fsb_dual_ar_desc& d = h->d;
+    const int passes = (batch + 7) / 8;  // GEMV passes of <= 8 rows
+    const int per_layer = 4 * passes + 1;
+    const int C = d.num_codebooks;
+    return 1 + d.n_layer * per_layer + passes /*head*/ + 1 /*slow sample*/ + C * d.n_fast_layer * per_layer +
+           (C - 1) * (passes + 1) + 1 /*frame end*/;
+}
+
+int fsb_gemv(const void* W, const void* W2, const void* x, const void* norm_w, const void* res, void* out, int32_t M,
+             int32_t N, int32_t K, int32_t pro, int32_t epi, float eps, void* stream) {
+    fsb_dual_ar* h = nullptr;
+    if (!W || !x || !out || M < 1 || K % 8 || pro < 0 || pro > 1 || epi < 0 || epi > 2) return 1;
+    if (epi == EPI_SWIGLU && !W2) return 1;
+    if (epi == EPI_RESIDUAL && !res) return 1;
+    if (pro == PRO_RMSNORM && !norm_w) return 1;
+    if (set_gemv_attrs() != cudaSuccess) return 2;
+    int dev = 0, n_sm = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = run_gemv(n_sm, 512 * 1024, false, (cudaStream_t)stream, M, N, K, pro, epi, (const bf16*)W,
+                             (const bf16*)W2, (const bf16*)x, (const bf16*)norm_w, (const bf16*)res, (bf16*)out, nullptr,
+                             eps, nullptr, 0);
+    (void)h;
+    return e == cudaSuccess ? 0 : 3;
+}
+
+int fsb_sample(const void* logits, const void* bias, int32_t B, int32_t V, int32_t top_k, float temperature, float top_p,
+               int32_t n_variants, float temp2, float top_p2, const void* uniforms, uint64_t seed, int32_t seg0_lo,
+               int32_t seg0_hi, int32_t seg1_lo, int32_t seg1_hi, int32_t* out, void* stream) {
+    if (!logits || !out || B < 1 || V < 1 || top_k < 1 || top_k > SAMPLE_MAXK || n_variants < 1 || n_variants > 2) return 1;
+    SampleArgs sa{};
+    sa.logits = (const bf16*)logits; sa.bias = (const bf16*)bias; sa.V = V; sa.ld_logits = V;
+    if (seg0_hi <= seg0_lo && seg1_hi <= seg1_lo) { seg0_lo = 0; seg0_hi = V; }
+    sa.seg_lo[0] = seg0_lo; sa.seg_hi[0] = seg0_hi; sa.seg_lo[1] = seg1_lo; sa.seg_hi[1] = seg1_hi;
+    sa.top_k = top_k; sa.n_variants = n_variants;
+    sa.temp[0] = temperature; sa.top_p[0] = top_p; sa.temp[1] = temp2; sa.top_p[1] = top_p2;
+    sa.uniforms = (const bf16*)uniforms; sa.u_stride = (long long)n_variants * V; sa.u_offset = 0;
+    sa.seed = seed; sa.frame_counter = nullptr; sa.draw_id = 0;
+    sa.mode = 2; sa.tokens = out; sa.out_col = 0; sa.n_cols = 2;
+    cudaError_t e = launch(sample_kernel, dim3(B), dim3(SAMPLE_THREADS), 0, (cudaStream_t)stream, false, sa);
+    return e == cudaSuccess ? 0 : 3;
+}
+
+}  // extern "C"
