@@ -15,26 +15,29 @@ ROOT = Path(__file__).resolve().parent.parent
 
 
 def test_oracle_greedy_matches_reference_golden():
+    """top_k=1 is NOT RNG-free: a bf16 uniform is 0 with probability 1/256, which zeroes the winner's score and
+    makes argmax return index 0 (inference.py:43-46), so the recorded draws are replayed here as well."""
     g = load_golden("dual_ar_tiny_greedy")
     cfg = cfg_from_golden(g)
     sd = R.make_state_dict(cfg, seed=g["wseed"])
     assert abs(float(sum(v.float().abs().sum() for v in sd.values())) - g["weights_checksum"]) < 1e-3 * g["weights_checksum"]
     m = R.DualARRef(cfg, sd)
     tr = []
-    seq = R.generate(model=m, prompt=g["prompt"].clone(), max_new_tokens=24, temperature=1.0, top_p=0.9,
-                     top_k=1, traces=tr)
+    seq = R.generate(model=m, prompt=g["prompt"].clone(), max_new_tokens=40, temperature=1.0, top_p=0.9,
+                     top_k=1, traces=tr, rand_like=UniformFeeder(g["useed"]))
     matched, n = compare_free_run(seq, g)
-    assert matched >= 1, (matched, n)
-    # logits: bit-exact on the machine that made the fixture; within bf16 noise on any other CPU
-    assert float((tr[0]["slow_logits"].float() - g["slow_logits"][0].float()).abs().max()) < 0.05
-    # teacher-forced: the golden sequence up to frame 16 as a prompt reproduces the golden logits of frame 16
+    assert matched == n == 40, (matched, n)
+    for k in (0, 16, 32):
+        assert float((tr[k]["slow_logits"].float() - g["slow_logits"][k].float()).abs().max()) < 0.03
+    # teacher-forced through the prompt route: golden sequence up to frame 16 reproduces frame 16's logits within
+    # the oracle's own route-to-route noise (measured 0.016-0.023 max-abs, ~1 % of max |logit|)
     T = g["prompt"].shape[1]
     m2 = R.DualARRef(cfg, sd)
     m2.setup_caches(1, cfg.max_seq_len)
     pr = g["seq"][:, : T + 16]
     logits, _ = m2.forward_generate(pr[None], torch.arange(pr.shape[1]))
     d = (logits[0, -1].float() - g["slow_logits"][16].float()).abs().max()
-    assert float(d) < 0.06, float(d)
+    assert float(d) < 0.05, float(d)
 
 
 def test_oracle_sampled_matches_reference_golden():
@@ -42,11 +45,13 @@ def test_oracle_sampled_matches_reference_golden():
     cfg = cfg_from_golden(g)
     m = R.DualARRef(cfg, R.make_state_dict(cfg, seed=g["wseed"]))
     s = g["sampling"]
-    seq = R.generate(model=m, prompt=g["prompt"].clone(), max_new_tokens=4, temperature=s["temperature"],
+    seq = R.generate(model=m, prompt=g["prompt"].clone(), max_new_tokens=16, temperature=s["temperature"],
                      top_p=s["top_p"], top_k=s["top_k"], rand_like=UniformFeeder(g["useed"]))
-    # the first frame comes from the (bit-reproducible) prompt pass; later frames may drift on another CPU
     T = g["prompt"].shape[1]
     assert torch.equal(seq[:, : T + 1], g["seq"][:, : T + 1])
+    # later frames are bit-identical on the machine that made the fixture; elsewhere they may drift at near-ties
+    same = (seq == g["seq"][:, : seq.shape[1]]).all(0).float().mean()
+    assert float(same) > 0.5
 
 
 def test_oracle_sampling_cases():

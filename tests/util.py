@@ -38,7 +38,7 @@ class UniformFeeder:
         return u
 
 
-def compare_free_run(seq: torch.Tensor, g, thr: float = 0.1):
+def compare_free_run(seq: torch.Tensor, g, thr: float = 0.06):
     """Compare a free-running greedy sequence with the golden one, decision by decision.
 
     The reference's own CPU result is machine-dependent at near-ties (bf16 GEMM summation order differs between
