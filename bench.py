@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""bench.py — audio-seconds per second of the S2-Pro-shape Dual-AR decode on B200 (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--frames F]
+
+A "step" = one F-frame (default 1024) batch-1 decode job after a 512-token prompt, S2-Pro shape, random-init bf16,
+synthetic prompt.  N > 1 (torchrun): one independent utterance per GPU, no collective on the data path (weak scaling).
+Prints ONE JSON line (contract in the task statement; extra keys: roofline, roofline_frame, cpu_baseline, p50_ms_per_frame).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+FRAME_SEC = 2048.0 / 44100.0  # one Dual-AR frame = 2048 samples @ 44.1 kHz
+PROMPT_T = 512
+METRIC = "audio_sec_per_sec_dual_ar_decode_bs1"
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu: int):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self._stop_evt = gpu, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([x.strip() for x in o.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def synth_state_dict(cfg, device, seed=0):
+    """Random-init S2-Pro-shape weights straight on the device: N(0, 0.02) for Linear/Embedding (llama.py:468-477),
+    norm weights 1."""
+    import torch
+    from fish_speech_b200.dual_ar import state_dict_shapes
+    g = torch.Generator(device=device).manual_seed(seed)
+    sd = {}
+    for name, shape in state_dict_shapes(cfg).items():
+        if len(shape) == 1:
+            sd[name] = torch.ones(shape, dtype=torch.bfloat16, device=device)
+        else:
+            w = torch.empty(shape, dtype=torch.bfloat16, device=device)
+            w.normal_(0.0, cfg.initializer_range, generator=g)
+            sd[name] = w
+    return sd
+
+
+def synth_prompt(cfg, T, seed=1):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    p = torch.zeros((cfg.num_codebooks + 1, T), dtype=torch.long)
+    p[0] = torch.randint(0, cfg.semantic_begin_id, (T,), generator=g)
+    return p
+
+
+# ----------------------------------------------------------------------------------------------- CPU reference leg
+def cpu_reference_leg(frames: int, steps: int = 1, warmup: int = 0):
+    """The reference's CPU path for this workload: oracle/dual_ar_ref.py (a torch-CPU restatement pinned bit-exact
+    to the reference's own generate(); the Python reference itself cannot travel to the GPU box), S2-Pro shape,
+    bf16, all host threads, `frames` decode frames after a 16-token prompt with max_seq_len 2048 (the reference
+    attends over the whole allocated cache each step, llama.py:441,909-933, so step cost does not depend on the
+    position).  Weights are a tiled random block (values do not affect timing; building 4.5 B fresh normals would
+    dominate the run).  Returns (audio-sec/sec, cores, sample description, seconds per frame)."""
+    import torch
+    from oracle import dual_ar_ref as R
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = R.s2_config(max_seq_len=2048)
+    g = torch.Generator().manual_seed(0)
+    block = (torch.randn(1 << 20, generator=g) * cfg.initializer_range).to(torch.bfloat16)
+    sd = {}
+    for name, shape in R.state_dict_keys(cfg).items():
+        n = 1
+        for s in shape:
+            n *= s
+        if len(shape) == 1:
+            sd[name] = torch.ones(shape, dtype=torch.bfloat16)
+        else:
+            sd[name] = block.repeat((n + block.numel() - 1) // block.numel())[:n].view(shape)
+    m = R.DualARRef(cfg, sd)
+    m.setup_caches(1, cfg.max_seq_len)
+    prompt = R.make_prompt(cfg, 16, seed=1)
+    T = torch.tensor(0.8, dtype=torch.bfloat16)
+    P = torch.tensor(0.8, dtype=torch.bfloat16)
+    bias = R.make_semantic_logit_bias(cfg)
+    bias[0, 0, cfg.im_end_id] = float("-inf")  # fixed frame count
+    with torch.inference_mode():
+        first = R.decode_one_token_ar(m, prompt[None], torch.arange(16), T, P, 30, bias)
+        times = []
+        pos = 16
+        cur = first.view(1, cfg.num_codebooks + 1, -1)
+        for it in range(warmup + steps):
+            t0 = time.perf_counter()
+            out = R.decode_n_tokens(m, cur, torch.tensor([pos], dtype=torch.int), frames, T, P, 30, bias)
+            dt = time.perf_counter() - t0
+            pos += out.shape[1]
+            cur = out[:, -1:].reshape(1, cfg.num_codebooks + 1, 1)
+            if it >= warmup:
+                times.append(dt / max(1, out.shape[1]))
+    spf = statistics.mean(times)
+    sample = f"{frames} decode frames/step x {steps} step(s), S2-Pro shape bf16, bs1, max_seq_len 2048, 16-token prompt, oracle port of generate()"
+    return FRAME_SEC / spf, cores, sample, spf
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    frames = max(1, args.ref_frames)
+    v, cores, sample, spf = cpu_reference_leg(frames, steps=max(1, args.steps), warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": spf * 1e3 * frames, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "S2-Pro-shape Dual-AR decode, batch 1, CPU", "frames_per_step": frames},
+        "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------------- GPU arm
+def time_dominant_kernel(model, iters=4):
+    """Dominant kernel = the fused RMSNorm + gate/up GEMV + SiLU*mul (gemv_kernel<1,4,RMSNORM,SWIGLU>): 2 x ffn x dim
+    bf16 weights per launch.  Timed ALONE with CUDA events on the launch stream, cycling over all slow layers so
+    every launch streams weights that are not in L2 (36 x 99.6 MB >> 126 MB)."""
+    import torch
+    c = model.config
+    lib = model.lib
+    x = torch.randn(1, c.dim, device=model.device).bfloat16()
+    out = torch.empty(1, c.intermediate_size, dtype=torch.bfloat16, device=model.device)
+    st = torch.cuda.current_stream().cuda_stream
+    layers = [(model.weights[f"layers.{i}.feed_forward.w1.weight"], model.weights[f"layers.{i}.feed_forward.w3.weight"],
+               model.weights[f"layers.{i}.ffn_norm.weight"]) for i in range(c.n_layer)]
+
+    def sweep():
+        for w1, w3, nw in layers:
+            rc = lib.fsb_gemv(w1.data_ptr(), w3.data_ptr(), x.data_ptr(), nw.data_ptr(), None, out.data_ptr(), 1,
+                              c.intermediate_size, c.dim, 1, 2, c.norm_eps, st)
+            assert rc == 0
+    sweep()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        sweep()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / (iters * len(layers))
+    nbytes = 2.0 * c.intermediate_size * c.dim * 2 + 2.0 * c.dim * 2 + c.intermediate_size * 2 + c.dim * 2
+    return nbytes, ms
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from fish_speech_b200 import DualARTransformerB200, generate, s2_pro_config
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    F = args.frames
+    cfg = s2_pro_config(max_seq_len=2048)
+    sd = synth_state_dict(cfg, dev, seed=0)
+    model = DualARTransformerB200(cfg, sd, device=dev, max_rows=1)
+    del sd
+    model.setup_caches(1, cfg.max_seq_len)
+    prompt = synth_prompt(cfg, PROMPT_T, seed=1 + rank)  # a different utterance per rank
+    C1 = cfg.num_codebooks + 1
+
+    # ---- device-resident leg (`value`): prompt pass once, then K timed steps of F frames from position 512
+    model.prefill(prompt[:, :-1].to(dev), 0, 0)
+    sess = model.session(1, F + 1)
+    bias = torch.full((cfg.vocab_size,), float("-inf"), dtype=torch.bfloat16, device=dev)
+    bias[cfg.semantic_begin_id: cfg.semantic_end_id + 1] = 0.0  # <|im_end|> masked: fixed frame count
+    sess.bias, sess.restrict_scan, sess.seed = bias, True, 1234 + rank
+    last_col = prompt[:, -1].to(torch.int32).view(1, C1).to(dev)
+
+    def reset():
+        sess.cur_tokens.copy_(last_col)
+        sess.pos.fill_(PROMPT_T - 1)
+        sess.frame_counter.zero_()
+        sess.ras_window.zero_()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        reset()
+        sess.run(min(F, 64), 0.8008, 0.8008, 30, True)
+    torch.cuda.synchronize()
+    # p50 ms/frame: per-frame CUDA events over one step
+    reset()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(min(F, 256) + 1)]
+    evs[0].record()
+    for i in range(1, len(evs)):
+        sess.run(1, 0.8008, 0.8008, 30, True)
+        evs[i].record()
+    torch.cuda.synchronize()
+    p50 = statistics.median(evs[i].elapsed_time(evs[i + 1]) for i in range(len(evs) - 1))
+
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        reset()
+        sess.run(F, 0.8008, 0.8008, 30, True)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    codes_ok = bool((sess.out_tokens[:F, 0, 1:] >= 0).all()) and bool((sess.out_tokens[:F, 0, 1:] < cfg.codebook_size).all())
+
+    # ---- end-to-end leg (`e2e`): public generate() with a HOST prompt (pinned), result read back to the host
+    hp = prompt.pin_memory()
+    e2e_frames, e2e_t = 0, 0.0
+    for it in range(1 + args.e2e_steps):
+        barrier()
+        t0 = time.perf_counter()
+        seq = generate(model=model, prompt=hp.to(dev, non_blocking=True), max_new_tokens=F, temperature=0.8, top_p=0.8,
+                       top_k=30)
+        host = seq.cpu()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if it > 0:
+            e2e_frames += host.shape[1] - PROMPT_T
+            e2e_t += dt
+    tms = torch.tensor([ms, e2e_t], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([float(args.steps * F), float(e2e_frames)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms_max, e2e_t_max = float(tms[0]), float(tms[1])
+    total_frames, total_e2e_frames = float(cnt[0]), float(cnt[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = measured_peaks()
+    value = total_frames * FRAME_SEC / (ms_max / 1e3)
+    ms_per_frame = ms_max / (args.steps * F)
+    ctx_avg = PROMPT_T + (F - 1) / 2.0
+    fbytes = model.frame_bytes(1, int(ctx_avg), masked_head=False)
+    kb, kms = time_dominant_kernel(model)
+    line = {
+        "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "S2-Pro-shape Dual-AR decode, batch 1, 512-token prompt, %d-frame decode (BASELINE configs[1])" % F,
+                   "frames_per_step": F, "prompt_tokens": PROMPT_T, "utterances": world, "parallelism": f"replica x{world}, request-partitioned, no collective",
+                   "l2_policy": "inputs larger than L2: 16.3 GB of weights streamed per frame vs 126 MB L2",
+                   "sampling": "T=0.8 top_p=0.8 top_k=30, RAS on, <|im_end|> masked for a fixed frame count"},
+        "p50_ms_per_frame": p50, "mean_ms_per_frame": ms_per_frame, "codes_in_range": codes_ok,
+        "clocks": clocks,
+        "e2e": {"value": (total_e2e_frames * FRAME_SEC / e2e_t_max) if e2e_t_max > 0 else None, "unit": "audio-s/s",
+                "h2d_bytes_per_step": int(prompt.numel() * 8), "d2h_bytes_per_step": int(C1 * (PROMPT_T + F) * 8),
+                "frames": total_e2e_frames, "includes": "pinned-host prompt H2D, 512-token prompt pass, decode loop, D2H of codes"},
+        "gpu_launches": int(model.launches_per_frame(1) * F * args.steps),
+        "roofline": {"bound": "hbm", "kernel": "gemv_kernel<M=1,G=4,RMSNORM,SWIGLU> (w1/w3 gate-up, timed alone over 36 layers)",
+                     "achieved": kb / (kms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": kb / (kms * 1e-3) / 1e9 / peak,
+                     "traffic": None, "bytes_per_launch": kb, "ms_per_launch": kms, "peak_source": peak_src},
+        "roofline_frame": {"bound": "hbm", "achieved": fbytes / (ms_per_frame * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                           "frac": fbytes / (ms_per_frame * 1e-3) / 1e9 / peak, "bytes_per_frame": fbytes,
+                           "note": "algorithmic weight+KV bytes per frame (SURVEY §8d) / mean frame time, full LM head counted"},
+    }
+    if not args.no_cpu and world >= 1:
+        try:
+            v, cores, sample, _ = cpu_reference_leg(args.ref_frames)
+            line["cpu_baseline"] = {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample}
+        except Exception as e:  # the GPU numbers stand on their own
+            line["cpu_baseline"] = {"value": None, "unit": "audio-s/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=1024)
+    ap.add_argument("--ref-frames", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=1)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -71,6 +71,37 @@ def s2_pro_config(max_seq_len: int = 2048, vocab_size: int = 155776) -> DualARCo
                         semantic_end_id=vocab_size - 1, n_fast_layer=4, im_end_id=151645)
 
 
+def state_dict_shapes(c: "DualARConfig") -> Dict[str, tuple]:
+    """name -> shape of every tensor the engine binds, named as the reference nn.Module registers them
+    (llama.py:254-271 BaseTransformer, :659-705 DualARTransformer, :846-881 Attention, :978-986 FeedForward)."""
+    d, hd = c.dim, c.head_dim
+    qkv = (c.n_head + 2 * c.n_local_heads) * hd
+    out: Dict[str, tuple] = {
+        "embeddings.weight": (c.vocab_size, d),
+        "codebook_embeddings.weight": (c.codebook_size * c.num_codebooks, d),
+        "norm.weight": (d,),
+        "fast_embeddings.weight": (c.codebook_size, d),
+        "fast_norm.weight": (d,),
+        "fast_output.weight": (c.codebook_size, d),
+    }
+    if not c.tie_word_embeddings:
+        out["output.weight"] = (c.vocab_size, d)
+    for pre, n in (("layers", c.n_layer), ("fast_layers", c.n_fast_layer)):
+        for i in range(n):
+            p = f"{pre}.{i}."
+            out[p + "attention.wqkv.weight"] = (qkv, d)
+            out[p + "attention.wo.weight"] = (d, c.n_head * hd)
+            if c.attention_qk_norm:
+                out[p + "attention.q_norm.weight"] = (hd,)
+                out[p + "attention.k_norm.weight"] = (hd,)
+            out[p + "feed_forward.w1.weight"] = (c.intermediate_size, d)
+            out[p + "feed_forward.w3.weight"] = (c.intermediate_size, d)
+            out[p + "feed_forward.w2.weight"] = (d, c.intermediate_size)
+            out[p + "ffn_norm.weight"] = (d,)
+            out[p + "attention_norm.weight"] = (d,)
+    return out
+
+
 def precompute_freqs_cis(seq_len: int, n_elem: int, base: float) -> Tensor:
     """RoPE table exactly as the reference stores it (llama.py:1003-1022): bf16 [seq, n_elem/2, 2]."""
     freqs = 1.0 / (base ** (torch.arange(0, n_elem, 2)[: (n_elem // 2)].float() / n_elem))
