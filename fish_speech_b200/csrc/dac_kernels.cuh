@@ -1,0 +1,292 @@
+// DAC codec decode kernels (round-1 correctness path: fp32 activations, channels-last [B][T][C]).
+//
+// Every conv / transposed conv / linear of the decode path is ONE implicit-GEMM shape
+//     out[b][t][n] = epi( bias[n % bias_mod] + sum_j sum_k pro(A[b][t - shift_j][k]) * W[j][k][n] )
+// with shift_j = (taps-1-j)*dil (causal left padding = rows t < 0 read as zero):
+//   * CausalConvNet            (modded_dac.py:521-552, rvq.py:58-89)   taps = k, N = Cout
+//   * CausalTransConvNet k=2s  (modded_dac.py:563-580)                 taps = 2, K = Cin, N = s*Cout: output row q holds
+//                               the s phases of samples q*s..q*s+s-1, which IS channels-last [T*s][Cout]
+//   * CausalTransConvNet k=s   (rvq.py:100-117)                        taps = 1, N = s*Cout
+//   * nn.Linear                                                          taps = 1
+// Prologue: Snake1d (descript-audio-codec 1.0.0: x + sin^2(alpha x)/(alpha + 1e-9)) on the A operand.
+// Epilogue: bias, exact GELU (rvq.py:180), LayerScale / ConvNeXt gamma, residual add, tanh (modded_dac.py:795).
+// This file is the SIMT fp32 tile version used as the parity anchor; the tcgen05 version keeps the same tap/shift plan.
+#pragma once
+#include "common.cuh"
+
+enum { DEPI_NONE = 0, DEPI_TANH = 1, DEPI_GELU = 2 };
+
+struct ConvArgs {
+    const float* A;      // [B][T][Cin]
+    const float* W;      // [taps][Cin][N]
+    const float* bias;   // [bias_mod] or nullptr
+    const float* alpha;  // [Cin] snake prologue or nullptr
+    const float* res;    // [B][T][N] or nullptr
+    const float* gamma;  // [N] or nullptr
+    float* out;          // [B][T][N]
+    int B, T, Cin, N, taps, dil, bias_mod, epi;
+};
+
+__device__ __forceinline__ float snake_f(float x, float a, float inv) {
+    const float s = sinf(a * x);
+    return x + inv * s * s;
+}
+
+#define CG_BM 64
+#define CG_BN 64
+#define CG_BK 16
+
+__global__ void __launch_bounds__(256) conv_gemm_kernel(ConvArgs a) {
+    __shared__ float As[CG_BK][CG_BM + 4];
+    __shared__ float Bs[CG_BK][CG_BN];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int t0 = blockIdx.x * CG_BM, n0 = blockIdx.y * CG_BN, b = blockIdx.z;
+    const float* Ab = a.A + (size_t)b * a.T * a.Cin;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    const int am = tid >> 2, ak = (tid & 3) * 4;   // A tile: row am, 4 consecutive k
+    const int bk = tid >> 4, bn = (tid & 15) * 4;  // B tile: row bk, 4 consecutive n
+    for (int j = 0; j < a.taps; ++j) {
+        const int shift = (a.taps - 1 - j) * a.dil;
+        const float* Wj = a.W + (size_t)j * a.Cin * a.N;
+        for (int k0 = 0; k0 < a.Cin; k0 += CG_BK) {
+            float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int t = t0 + am - shift, k = k0 + ak;
+            if (t >= 0 && t < a.T && (t0 + am) < a.T && k < a.Cin) {
+                av = *reinterpret_cast<const float4*>(Ab + (size_t)t * a.Cin + k);
+                if (a.alpha) {
+                    const float4 al = *reinterpret_cast<const float4*>(a.alpha + k);
+                    av.x = snake_f(av.x, al.x, 1.f / (al.x + 1e-9f));
+                    av.y = snake_f(av.y, al.y, 1.f / (al.y + 1e-9f));
+                    av.z = snake_f(av.z, al.z, 1.f / (al.z + 1e-9f));
+                    av.w = snake_f(av.w, al.w, 1.f / (al.w + 1e-9f));
+                }
+            }
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k0 + bk < a.Cin && n0 + bn < a.N)
+                bv = *reinterpret_cast<const float4*>(Wj + (size_t)(k0 + bk) * a.N + n0 + bn);
+            __syncthreads();
+            As[ak + 0][am] = av.x; As[ak + 1][am] = av.y; As[ak + 2][am] = av.z; As[ak + 3][am] = av.w;
+            *reinterpret_cast<float4*>(&Bs[bk][bn]) = bv;
+            __syncthreads();
+#pragma unroll
+            for (int kk = 0; kk < CG_BK; ++kk) {
+                const float4 x = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+                const float4 w = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+                const float xs[4] = {x.x, x.y, x.z, x.w}, ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) acc[i][jj] = fmaf(xs[i], ws[jj], acc[i][jj]);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int t = t0 + ty * 4 + i;
+        if (t >= a.T) continue;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+            const int n = n0 + tx * 4 + jj;
+            if (n >= a.N) continue;
+            float v = acc[i][jj];
+            if (a.bias) v += a.bias[n % a.bias_mod];
+            if (a.epi == DEPI_GELU) v = 0.5f * v * (1.f + erff(v * 0.70710678118654752f));
+            if (a.gamma) v *= a.gamma[n];
+            const size_t o = ((size_t)b * a.T + t) * a.N + n;
+            if (a.res) v += a.res[o];
+            if (a.epi == DEPI_TANH) v = tanhf(v);
+            a.out[o] = v;
+        }
+    }
+}
+
+// Final conv (Cout = 1) + tanh: one warp per output sample (modded_dac.py:793-795)
+__global__ void __launch_bounds__(256) conv_out1_kernel(ConvArgs a) {
+    const int lane = threadIdx.x & 31;
+    const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= (long long)a.B * a.T) return;
+    const int b = (int)(gw / a.T), t = (int)(gw % a.T);
+    float s = 0.f;
+    for (int j = 0; j < a.taps; ++j) {
+        const int tt = t - (a.taps - 1 - j) * a.dil;
+        if (tt < 0) continue;
+        const float* row = a.A + ((size_t)b * a.T + tt) * a.Cin;
+        for (int k = lane; k < a.Cin; k += 32) {
+            float x = row[k];
+            if (a.alpha) { const float al = a.alpha[k]; x = snake_f(x, al, 1.f / (al + 1e-9f)); }
+            s = fmaf(x, a.W[(size_t)j * a.Cin + k], s);
+        }
+    }
+    s = warp_sum(s);
+    if (lane == 0) {
+        s += a.bias ? a.bias[0] : 0.f;
+        a.out[(size_t)b * a.T + t] = (a.epi == DEPI_TANH) ? tanhf(s) : s;
+    }
+}
+
+// ----------------------------------------------------------------------------- RVQ dequantisation (K11)
+// rvq.py:352-363 + descript ResidualVectorQuantize.from_codes: clamp (in place, like the reference), per codebook
+// gather the 8-d code vector, weight-normed 1x1 out_proj (+bias), sum over the codebooks.
+struct RvqArgs {
+    long long* codes;        // [B][NQ][T] int64, clamped in place
+    const float* codebooks;  // concatenated [sum sizes][CD]
+    const float* proj_w;     // [NQ][D][CD] (weight norm folded)
+    const float* proj_b;     // [NQ][D]
+    float* z;                // [B][T][D]
+    int B, T, NQ, D, CD, size0, size_rest;
+};
+__global__ void __launch_bounds__(256) rvq_dequant_kernel(RvqArgs a) {
+    __shared__ float e[16][16];  // [NQ<=16][CD<=16]
+    const int t = blockIdx.x, b = blockIdx.y;
+    if (threadIdx.x < a.NQ) {
+        const int q = threadIdx.x;
+        long long* cp = a.codes + ((size_t)b * a.NQ + q) * a.T + t;
+        long long c = *cp;
+        const long long mx = (q == 0 ? a.size0 : a.size_rest) - 1;
+        if (c > mx) { c = mx; *cp = c; }  // torch.clamp(max=...) only (rvq.py:354-359)
+        const size_t row = (q == 0) ? (size_t)c : (size_t)a.size0 + (size_t)(q - 1) * a.size_rest + (size_t)c;
+        for (int i = 0; i < a.CD; ++i) e[q][i] = a.codebooks[row * a.CD + i];
+    }
+    __syncthreads();
+    for (int d = threadIdx.x; d < a.D; d += blockDim.x) {
+        float s = 0.f;
+        for (int q = 0; q < a.NQ; ++q) {
+            const float* w = a.proj_w + ((size_t)q * a.D + d) * a.CD;
+            float p = 0.f;
+            for (int i = 0; i < a.CD; ++i) p = fmaf(w[i], e[q][i], p);
+            s += p + a.proj_b[(size_t)q * a.D + d];
+        }
+        a.z[((size_t)b * a.T + t) * a.D + d] = s;
+    }
+}
+
+// ----------------------------------------------------------------------------- row-wise norms
+// RMSNorm (modded_dac.py:320-331), one warp per row
+__global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const float* x, const float* w, float* y, long long rows, int C,
+                                                          float eps) {
+    const int lane = threadIdx.x & 31;
+    const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (r >= rows) return;
+    const float* xr = x + r * C;
+    float ss = 0.f;
+    for (int c = lane; c < C; c += 32) ss += xr[c] * xr[c];
+    ss = warp_sum(ss);
+    const float rs = rsqrtf(ss / C + eps);
+    for (int c = lane; c < C; c += 32) y[r * C + c] = xr[c] * rs * w[c];
+}
+
+// ConvNeXt front half (rvq.py:173-179): depthwise causal conv k=7 (+bias) then LayerNorm(eps 1e-6) over channels.
+// One CTA per (b, t) row.
+__global__ void __launch_bounds__(256) dwconv_ln_kernel(const float* x, const float* dw_w, const float* dw_b,
+                                                       const float* ln_w, const float* ln_b, float* y, int T, int C) {
+    extern __shared__ float v[];  // [C]
+    __shared__ float red[32];
+    const int t = blockIdx.x, b = blockIdx.y;
+    float s = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float acc = dw_b[c];
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+            const int tt = t - 6 + j;
+            if (tt >= 0) acc = fmaf(x[((size_t)b * T + tt) * C + c], dw_w[c * 7 + j], acc);
+        }
+        v[c] = acc;
+        s += acc;
+    }
+    const float mean = block_sum(s, red) / C;
+    float q = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) { const float d = v[c] - mean; q += d * d; }
+    const float var = block_sum(q, red) / C;
+    const float rs = rsqrtf(var + 1e-6f);
+    for (int c = threadIdx.x; c < C; c += blockDim.x)
+        y[((size_t)b * T + t) * C + c] = (v[c] - mean) * rs * ln_w[c] + ln_b[c];
+}
+
+// SwiGLU on a fused [rows][2F] gate|up GEMM output (modded_dac.py FeedForward: w2(silu(w1 x) * w3 x))
+__global__ void swiglu_kernel(const float* gu, float* out, long long rows, int F) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * F) return;
+    const long long r = i / F;
+    const int f = (int)(i % F);
+    const float g = gu[r * 2 * F + f], u = gu[r * 2 * F + F + f];
+    out[i] = g / (1.f + expf(-g)) * u;
+}
+
+// ----------------------------------------------------------------------------- window attention (K12)
+// RoPE in place on the q and k thirds of qkv [B][T][3][H][HD] (modded_dac.py:455-467, table bf16-rounded)
+__global__ void rope_qk_kernel(float* qkv, const float* table, int B, int T, int H, int HD) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int half = HD / 2;
+    const long long total = (long long)B * T * 2 * H * half;
+    if (i >= total) return;
+    const int p = (int)(i % half);
+    const int h = (int)((i / half) % H);
+    const int which = (int)((i / ((long long)half * H)) % 2);
+    const long long bt = i / ((long long)half * H * 2);
+    const int t = (int)(bt % T);
+    float* v = qkv + (bt * 3 + which) * H * HD + (size_t)h * HD + 2 * p;
+    const float c = table[((size_t)t * half + p) * 2], s = table[((size_t)t * half + p) * 2 + 1];
+    const float x0 = v[0], x1 = v[1];
+    v[0] = x0 * c - x1 * s;
+    v[1] = x1 * c + x0 * s;
+}
+
+// causal attention limited to the last `window` keys (WindowLimitedTransformer mask, modded_dac.py:380-398);
+// one warp per (b, h, t); lane scores keys start+lane+32i, then owns output dims lane*EPL..
+template <int HD>
+__global__ void __launch_bounds__(128) window_attn_kernel(const float* qkv, float* y, int B, int T, int H, int window,
+                                                         float scale) {
+    constexpr int EPL = HD / 32;
+    constexpr int MAXI = 4;  // window <= 128
+    __shared__ float qs[4][HD];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int t = blockIdx.x * 4 + w, h = blockIdx.y, b = blockIdx.z;
+    if (t >= T) return;
+    const size_t rs = (size_t)3 * H * HD;
+    const float* base = qkv + (size_t)b * T * rs;
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) qs[w][lane * EPL + i] = base[(size_t)t * rs + (size_t)h * HD + lane * EPL + i];
+    __syncwarp();
+    const int start = max(0, t - window + 1), n = t - start + 1;
+    float sc[MAXI], mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+        const int j = lane + 32 * i;
+        sc[i] = -INFINITY;
+        if (j < n) {
+            const float* k = base + (size_t)(start + j) * rs + (size_t)(H + h) * HD;
+            float d = 0.f;
+#pragma unroll 8
+            for (int e = 0; e < HD; ++e) d = fmaf(qs[w][e], k[e], d);
+            sc[i] = d * scale;
+            mx = fmaxf(mx, sc[i]);
+        }
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) { sc[i] = (sc[i] == -INFINITY) ? 0.f : expf(sc[i] - mx); sum += sc[i]; }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    float o[EPL];
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) o[i] = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+        for (int src = 0; src < 32; ++src) {
+            const int j = src + 32 * i;
+            if (j >= n) break;  // uniform across the warp
+            const float p = __shfl_sync(0xffffffffu, sc[i], src);
+            const float* v = base + (size_t)(start + j) * rs + (size_t)(2 * H + h) * HD + lane * EPL;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) o[e] = fmaf(p, v[e], o[e]);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) y[((size_t)b * T + t) * H * HD + (size_t)h * HD + lane * EPL + e] = o[e] * inv;
+}

@@ -12,6 +12,7 @@
 #include "../../include/fish_b200.h"
 #include "attn.cuh"
 #include "gemv.cuh"
+#include "gemv_tma.cuh"
 #include "sample.cuh"
 
 namespace {
@@ -23,6 +24,15 @@ struct LayerW {
 };
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct GemvCfg {
+    int n_sm = 148;
+    size_t self_pf = 512 * 1024;
+    int tma = 1;          // 1: bulk-async-copy staged kernel (gemv_tma.cuh), 0: direct-load kernel (gemv.cuh)
+    int nst = 4;          // ring depth of the staged kernel
+    int ctas_per_sm = 1;  // grid = ctas_per_sm * n_sm
+    int stage_kb = 20;    // target stage size
+};
 
 }  // namespace
 
@@ -43,7 +53,7 @@ struct fsb_dual_ar {
     int max_splits = 32;
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
-    size_t self_pf_bytes = 512 * 1024;
+    GemvCfg gc;
     int n_sm = 148;
     // graph cache
     cudaGraphExec_t exec = nullptr;
@@ -119,8 +129,48 @@ cudaError_t set_gemv_attrs() {
     return cudaSuccess;
 }
 
+typedef void (*gemv_tma_fn)(GemvArgs, GemvTmaGeom);
+template <int PRO, int EPI>
+gemv_tma_fn pick_gemv_tma(int M) {
+    if (M <= 1) return gemv_tma_kernel<1, PRO, EPI>;
+    if (M <= 2) return gemv_tma_kernel<2, PRO, EPI>;
+    if (M <= 4) return gemv_tma_kernel<4, PRO, EPI>;
+    return gemv_tma_kernel<8, PRO, EPI>;
+}
+gemv_tma_fn pick_gemv_tma(int M, int pro, int epi) {
+    if (pro == PRO_RMSNORM) {
+        if (epi == EPI_STORE) return pick_gemv_tma<PRO_RMSNORM, EPI_STORE>(M);
+        if (epi == EPI_RESIDUAL) return pick_gemv_tma<PRO_RMSNORM, EPI_RESIDUAL>(M);
+        return pick_gemv_tma<PRO_RMSNORM, EPI_SWIGLU>(M);
+    }
+    if (epi == EPI_STORE) return pick_gemv_tma<PRO_NONE, EPI_STORE>(M);
+    if (epi == EPI_RESIDUAL) return pick_gemv_tma<PRO_NONE, EPI_RESIDUAL>(M);
+    return pick_gemv_tma<PRO_NONE, EPI_SWIGLU>(M);
+}
+cudaError_t set_gemv_tma_attrs() {
+    static bool done = false;
+    if (done) return cudaSuccess;
+    const int ms[4] = {1, 2, 4, 8};
+    for (int pro = 0; pro < 2; ++pro)
+        for (int epi = 0; epi < 3; ++epi)
+            for (int i = 0; i < 4; ++i) {
+                cudaError_t e = cudaFuncSetAttribute((const void*)pick_gemv_tma(ms[i], pro, epi),
+                                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+                if (e != cudaSuccess) return e;
+            }
+    done = true;
+    return cudaSuccess;
+}
+// largest KC <= limit that divides K and is a multiple of 8 (0 if none)
+int pick_kc(int K, int limit) {
+    if (K <= limit) return K;
+    for (int kc = limit - (limit % 8); kc >= 64; kc -= 8)
+        if (K % kc == 0) return kc;
+    return 0;
+}
+
 // rows M are processed in passes of <= 8; x rows have stride K, out/res rows stride N
-cudaError_t run_gemv(int n_sm, size_t self_pf, bool pdl, cudaStream_t s, int M, int N, int K, int pro, int epi,
+cudaError_t run_gemv(const GemvCfg& gc, bool pdl, cudaStream_t s, int M, int N, int K, int pro, int epi,
                      const bf16* W, const bf16* W2, const bf16* x, const bf16* norm_w, const bf16* res, bf16* out,
                      bf16* xnorm_out, float eps, const void* pf_ptr, size_t pf_bytes) {
     for (int m0 = 0; m0 < M; m0 += 8) {
@@ -132,10 +182,29 @@ cudaError_t run_gemv(int n_sm, size_t self_pf, bool pdl, cudaStream_t s, int M, 
         a.out = out + (size_t)m0 * N;
         a.xnorm_out = xnorm_out ? xnorm_out + (size_t)m0 * K : nullptr;
         a.N = N; a.K = K; a.M_valid = mv; a.eps = eps;
-        a.pf_ptr = (m0 == 0) ? pf_ptr : nullptr; a.pf_bytes = pf_bytes; a.self_pf_bytes = self_pf;
-        int nb = std::min(2 * n_sm, std::max(1, N / 4));
-        size_t smem = (size_t)mb * K * sizeof(bf16);
-        cudaError_t e = launch(pick_gemv(mv, pro, epi), dim3(nb), dim3(GEMV_THREADS), smem, s, pdl, a);
+        a.pf_ptr = (m0 == 0) ? pf_ptr : nullptr; a.pf_bytes = pf_bytes; a.self_pf_bytes = gc.self_pf;
+        const size_t xsmem = (size_t)mb * K * sizeof(bf16);
+        if (gc.tma) {
+            const int nacc = (epi == EPI_SWIGLU) ? 2 : 1;
+            const int kc = pick_kc(K, gc.stage_kb * 1024 / (GT_ROWS * 2 * nacc));
+            const int nst = std::max(2, std::min(gc.nst, GT_MAX_STAGES));
+            const size_t smem = (size_t)nst * GT_ROWS * kc * 2 * nacc + xsmem;
+            if (kc > 0 && smem <= 200 * 1024) {
+                GemvTmaGeom g{kc, nst};
+                const int nb = std::min(gc.ctas_per_sm * gc.n_sm, std::max(1, N / GT_ROWS));
+                cudaLaunchConfig_t cfg{};
+                cfg.gridDim = dim3(nb); cfg.blockDim = dim3(GT_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+                at[0].val.programmaticStreamSerializationAllowed = 1;
+                cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+                cudaError_t e = cudaLaunchKernelEx(&cfg, pick_gemv_tma(mv, pro, epi), a, g);
+                if (e != cudaSuccess) return e;
+                continue;
+            }
+        }
+        int nb = std::min(2 * gc.n_sm, std::max(1, N / 4));
+        cudaError_t e = launch(pick_gemv(mv, pro, epi), dim3(nb), dim3(GEMV_THREADS), xsmem, s, pdl, a);
         if (e != cudaSuccess) return e;
     }
     return cudaSuccess;
@@ -185,7 +254,7 @@ int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_i
         const LayerW& w = L[l];
         if (!w.wqkv || !w.wo || !w.w1 || !w.w2 || !w.w3 || !w.attn_norm || !w.ffn_norm || !w.kc || !w.vc)
             return fail(h, "unbound weights / kv cache in layer " + std::to_string(l));
-        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, QKV, D, PRO_RMSNORM, EPI_STORE, w.wqkv, nullptr, cur,
+        CK(run_gemv(h->gc, pdl, s, M, QKV, D, PRO_RMSNORM, EPI_STORE, w.wqkv, nullptr, cur,
                     w.attn_norm, nullptr, h->qkv, nullptr, d.norm_eps, nullptr, 0));
         AttnArgs a{};
         a.qkv = h->qkv; a.kcache = w.kc; a.vcache = w.vc; a.q_norm = w.q_norm; a.k_norm = w.k_norm;
@@ -208,11 +277,11 @@ int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_i
             }
             CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, pdl, a));
         }
-        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, D, H * HD, PRO_NONE, EPI_RESIDUAL, w.wo, nullptr, h->y,
+        CK(run_gemv(h->gc, pdl, s, M, D, H * HD, PRO_NONE, EPI_RESIDUAL, w.wo, nullptr, h->y,
                     nullptr, cur, xb, nullptr, d.norm_eps, nullptr, 0));
-        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, F, D, PRO_RMSNORM, EPI_SWIGLU, w.w1, w.w3, xb, w.ffn_norm,
+        CK(run_gemv(h->gc, pdl, s, M, F, D, PRO_RMSNORM, EPI_SWIGLU, w.w1, w.w3, xb, w.ffn_norm,
                     nullptr, h->ff, nullptr, d.norm_eps, nullptr, 0));
-        CK(run_gemv(h->n_sm, h->self_pf_bytes, pdl, s, M, D, F, PRO_NONE, EPI_RESIDUAL, w.w2, nullptr, h->ff, nullptr,
+        CK(run_gemv(h->gc, pdl, s, M, D, F, PRO_NONE, EPI_RESIDUAL, w.w2, nullptr, h->ff, nullptr,
                     xb, xa, nullptr, d.norm_eps, nullptr, 0));
         cur = xa;
     }
@@ -243,7 +312,7 @@ int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, 
     if (int r = run_layers(h, s, false, M, h->x2, pos, slots, true, -1)) return r;
     const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
     if (!head || !h->norm) return fail(h, "LM head / final norm not bound");
-    CK(run_gemv(h->n_sm, h->self_pf_bytes, h->use_pdl != 0, s, M, d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head,
+    CK(run_gemv(h->gc, h->use_pdl != 0, s, M, d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head,
                 nullptr, h->x, h->norm, nullptr, h->slow_logits, h->hidden, d.norm_eps, nullptr, 0));
     return 0;
 }
@@ -255,7 +324,7 @@ int run_fast_step(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* x_in, int c
     if (want_logits) {
         if (!h->fast_out || !h->fast_norm) return fail(h, "fast head not bound");
         bf16* lg = h->fast_logits + (size_t)cb_idx * h->R * d.codebook_size;
-        CK(run_gemv(h->n_sm, h->self_pf_bytes, h->use_pdl != 0, s, M, d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE,
+        CK(run_gemv(h->gc, h->use_pdl != 0, s, M, d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE,
                     h->fast_out, nullptr, h->xf, h->fast_norm, nullptr, lg, nullptr, d.norm_eps, nullptr, 0));
     }
     return 0;
@@ -387,13 +456,19 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
     CK(cudaGetDeviceProperties(&prop, dev));
     if (prop.major < 10) return fail(h, "fish_speech_b200 requires an sm_100a device (B200)");
     h->n_sm = prop.multiProcessorCount;
+    h->gc.n_sm = h->n_sm;
     CK(set_gemv_attrs());
+    CK(set_gemv_tma_attrs());
     CK(cudaMemset(h->counters, 0, (size_t)std::max(d.max_rows, 8) * d.n_kv_head * sizeof(int32_t)));
     h->slow.resize(d.n_layer);
     h->fast.resize(d.n_fast_layer);
     if (const char* e = getenv("FSB_PDL")) h->use_pdl = atoi(e);
     if (const char* e = getenv("FSB_GRAPH")) h->use_graph = atoi(e);
-    if (const char* e = getenv("FSB_SELF_PF_KB")) h->self_pf_bytes = (size_t)atol(e) * 1024;
+    if (const char* e = getenv("FSB_SELF_PF_KB")) h->gc.self_pf = (size_t)atol(e) * 1024;
+    if (const char* e = getenv("FSB_GEMV_TMA")) h->gc.tma = atoi(e);
+    if (const char* e = getenv("FSB_GEMV_NST")) h->gc.nst = atoi(e);
+    if (const char* e = getenv("FSB_GEMV_CPS")) h->gc.ctas_per_sm = atoi(e);
+    if (const char* e = getenv("FSB_GEMV_STAGE_KB")) h->gc.stage_kb = atoi(e);
     return 0;
 }
 
@@ -412,7 +487,11 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     std::string n(name);
     if (n == "pdl") h->use_pdl = (int)value;
     else if (n == "graph") h->use_graph = (int)value;
-    else if (n == "self_prefetch_kb") h->self_pf_bytes = (size_t)value * 1024;
+    else if (n == "self_prefetch_kb") h->gc.self_pf = (size_t)value * 1024;
+    else if (n == "gemv_tma") h->gc.tma = (int)value;
+    else if (n == "gemv_stages") h->gc.nst = (int)value;
+    else if (n == "gemv_ctas_per_sm") h->gc.ctas_per_sm = (int)value;
+    else if (n == "gemv_stage_kb") h->gc.stage_kb = (int)value;
     else if (n == "attn_splits") h->attn_splits = (int)value;
     else return fail(h, "unknown option " + n);
     h->cached_valid = false;
@@ -606,11 +685,17 @@ int fsb_gemv(const void* W, const void* W2, const void* x, const void* norm_w, c
     if (epi == EPI_SWIGLU && !W2) return 1;
     if (epi == EPI_RESIDUAL && !res) return 1;
     if (pro == PRO_RMSNORM && !norm_w) return 1;
-    if (set_gemv_attrs() != cudaSuccess) return 2;
+    if (set_gemv_attrs() != cudaSuccess || set_gemv_tma_attrs() != cudaSuccess) return 2;
     int dev = 0, n_sm = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    cudaError_t e = run_gemv(n_sm, 512 * 1024, false, (cudaStream_t)stream, M, N, K, pro, epi, (const bf16*)W,
+    GemvCfg gc;
+    gc.n_sm = n_sm;
+    if (const char* e = getenv("FSB_GEMV_TMA")) gc.tma = atoi(e);
+    if (const char* e = getenv("FSB_GEMV_NST")) gc.nst = atoi(e);
+    if (const char* e = getenv("FSB_GEMV_CPS")) gc.ctas_per_sm = atoi(e);
+    if (const char* e = getenv("FSB_GEMV_STAGE_KB")) gc.stage_kb = atoi(e);
+    cudaError_t e = run_gemv(gc, false, (cudaStream_t)stream, M, N, K, pro, epi, (const bf16*)W,
                              (const bf16*)W2, (const bf16*)x, (const bf16*)norm_w, (const bf16*)res, (bf16*)out, nullptr,
                              eps, nullptr, 0);
     (void)h;
