@@ -1,0 +1,247 @@
+// DAC codec decode engine: DAC.from_indices (modded_dac.py:925-927) = quantizer.decode (rvq.py:352-366) + Decoder
+// (modded_dac.py:760-801) behind the C ABI of include/fish_b200.h.  Weights arrive folded (weight norm applied) and
+// packed [taps][Cin][N] by the host mirror (fish_speech_b200/dac.py); activations are fp32 channels-last.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/fish_b200.h"
+#include "dac_kernels.cuh"
+
+struct fsb_dac {
+    fsb_dac_desc d;
+    std::map<std::string, const float*> w;
+    std::map<std::string, long long> wn;
+    float* buf[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t buf_elems = 0;
+    std::string err;
+};
+
+namespace {
+
+int dfail(fsb_dac* h, const std::string& m) {
+    if (h) h->err = m;
+    return 1;
+}
+#define DCK(call)                                                                                           \
+    do {                                                                                                    \
+        cudaError_t e_ = (call);                                                                            \
+        if (e_ != cudaSuccess) return dfail(h, std::string(#call) + ": " + cudaGetErrorString(e_) + " @" + std::to_string(__LINE__)); \
+    } while (0)
+
+int rates(const fsb_dac_desc& d, int i) { const int r[4] = {d.rate0, d.rate1, d.rate2, d.rate3}; return r[i]; }
+int ups(const fsb_dac_desc& d, int i) { return i == 0 ? d.up0 : d.up1; }
+
+// largest activation (floats) per batch item and frame over the whole plan
+size_t per_frame_elems(const fsb_dac_desc& d) {
+    size_t m = std::max<size_t>({(size_t)3 * d.tf_dim, (size_t)2 * d.tf_ffn, (size_t)d.latent_dim});
+    size_t len = 1;
+    for (int i = 0; i < d.n_up; ++i) {
+        len *= ups(d, i);
+        m = std::max(m, len * (size_t)d.convnext_ratio * d.latent_dim);
+    }
+    m = std::max(m, len * (size_t)d.decoder_dim);
+    size_t ch = d.decoder_dim;
+    for (int i = 0; i < d.n_rates; ++i) {
+        len *= rates(d, i);
+        ch /= 2;
+        m = std::max(m, len * ch);
+    }
+    return m;
+}
+
+struct Runner {
+    fsb_dac* h;
+    cudaStream_t s;
+    int B;
+    int rc = 0;
+    const float* W(const std::string& n) {
+        auto it = h->w.find(n);
+        if (it == h->w.end()) { if (!rc) rc = dfail(h, "weight not bound: " + n); return nullptr; }
+        return it->second;
+    }
+    void conv(const float* A, float* out, int T, int Cin, int N, int taps, int dil, const std::string& wn,
+              const std::string& bn, int bias_mod, const float* alpha, const float* res, const float* gamma, int epi) {
+        ConvArgs a{};
+        a.A = A; a.out = out; a.W = W(wn); a.bias = bn.empty() ? nullptr : W(bn);
+        a.alpha = alpha; a.res = res; a.gamma = gamma;
+        a.B = B; a.T = T; a.Cin = Cin; a.N = N; a.taps = taps; a.dil = dil; a.bias_mod = bias_mod > 0 ? bias_mod : N; a.epi = epi;
+        if (rc) return;
+        dim3 grid((T + CG_BM - 1) / CG_BM, (N + CG_BN - 1) / CG_BN, B);
+        conv_gemm_kernel<<<grid, 256, 0, s>>>(a);
+    }
+};
+
+}  // namespace
+
+extern "C" {
+
+size_t fsb_dac_workspace_bytes(const fsb_dac_desc* d) {
+    return 4 * ((size_t)d->max_batch * d->max_frames * per_frame_elems(*d) * sizeof(float) + 256);
+}
+
+int fsb_dac_create(const fsb_dac_desc* desc, void* workspace, size_t workspace_bytes, fsb_dac** out) {
+    if (!desc || !workspace || !out) return 1;
+    fsb_dac* h = new fsb_dac();
+    h->d = *desc;
+    *out = h;
+    const fsb_dac_desc& d = h->d;
+    if (d.n_rates < 1 || d.n_rates > 4 || d.n_up < 0 || d.n_up > 2 || d.n_codebooks + 1 > 16 || d.codebook_dim > 16 ||
+        d.tf_window > 128 || (d.tf_head_dim != 64 && d.tf_head_dim != 32) || d.latent_dim % 4 || d.decoder_dim % 64)
+        return dfail(h, "unsupported DAC shape");
+    if (workspace_bytes < fsb_dac_workspace_bytes(desc)) return dfail(h, "workspace too small");
+    h->buf_elems = (size_t)d.max_batch * d.max_frames * per_frame_elems(d);
+    char* p = (char*)workspace;
+    for (int i = 0; i < 4; ++i) {
+        h->buf[i] = (float*)p;
+        p += (h->buf_elems * sizeof(float) + 255) / 256 * 256;
+    }
+    return 0;
+}
+
+int fsb_dac_destroy(fsb_dac* h) { delete h; return 0; }
+const char* fsb_dac_last_error(const fsb_dac* h) { return h ? h->err.c_str() : "null handle"; }
+
+int fsb_dac_bind_weight(fsb_dac* h, const char* name, const void* dptr, int64_t numel) {
+    if (!h || !name || !dptr) return 1;
+    if (((uintptr_t)dptr) & 15) return dfail(h, std::string(name) + ": pointer must be 16-byte aligned");
+    h->w[name] = (const float*)dptr;
+    h->wn[name] = numel;
+    return 0;
+}
+
+double fsb_dac_flops(const fsb_dac* h, int32_t B, int32_t T) {
+    if (!h) return 0;
+    const fsb_dac_desc& d = h->d;
+    double f = 0, len = T;
+    const double D = d.latent_dim;
+    f += len * d.tf_layers * 2.0 * (D * 3 * D + D * D + 3.0 * D * d.tf_ffn);  // transformer GEMMs
+    for (int i = 0; i < d.n_up; ++i) {
+        f += len * 2.0 * D * ups(d, i) * D;  // transposed conv
+        len *= ups(d, i);
+        f += len * 2.0 * (2.0 * D * d.convnext_ratio * D + 7 * D);
+    }
+    double ch = d.decoder_dim;
+    f += len * 2.0 * 7 * D * ch;
+    for (int i = 0; i < d.n_rates; ++i) {
+        const int s = rates(d, i);
+        f += len * 2.0 * 2 * ch * s * (ch / 2);
+        len *= s; ch /= 2;
+        f += len * 3 * 2.0 * (7 * ch * ch + ch * ch);
+    }
+    f += len * 2.0 * 7 * ch;
+    return f * B;
+}
+
+int fsb_dac_stage(fsb_dac* h, const char* name, void** dptr, size_t* bytes) {
+    if (!h || !name || !dptr || !bytes) return 1;
+    std::string n(name);
+    if (n.size() == 4 && n.compare(0, 3, "buf") == 0 && n[3] >= '0' && n[3] <= '3') {
+        *dptr = h->buf[n[3] - '0'];
+        *bytes = h->buf_elems * sizeof(float);
+        return 0;
+    }
+    return dfail(h, "unknown stage buffer " + n);
+}
+
+// codes: device int64 [B][1+n_codebooks][T] (clamped in place like rvq.py:354-359); wav: device fp32 [B][hop*T]
+int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, void* stream) {
+    if (!h || !codes || !wav) return 1;
+    const fsb_dac_desc& d = h->d;
+    if (B < 1 || B > d.max_batch || T < 1 || T > d.max_frames) return dfail(h, "B/T exceed the workspace (max_batch/max_frames)");
+    cudaStream_t s = (cudaStream_t)stream;
+    Runner r{h, s, B};
+    const int D = d.latent_dim, NQ = d.n_codebooks + 1;
+    float *b0 = h->buf[0], *b1 = h->buf[1], *b2 = h->buf[2], *b3 = h->buf[3];
+
+    // ---- K11: RVQ dequant -> b0 [B][T][D]
+    {
+        RvqArgs a{};
+        a.codes = (long long*)codes; a.codebooks = r.W("rvq.codebooks"); a.proj_w = r.W("rvq.proj_w");
+        a.proj_b = r.W("rvq.proj_b"); a.z = b0;
+        a.B = B; a.T = T; a.NQ = NQ; a.D = D; a.CD = d.codebook_dim; a.size0 = d.semantic_codebook_size;
+        a.size_rest = d.codebook_size;
+        if (r.rc) return r.rc;
+        rvq_dequant_kernel<<<dim3(T, B), 256, 0, s>>>(a);
+    }
+    // ---- K12: post_module window transformer (modded_dac.py:418-439,145-171)
+    const int H = d.tf_heads, HD = d.tf_head_dim, F = d.tf_ffn;
+    const long long rows = (long long)B * T;
+    const int nwb = (int)((rows * 32 + 255) / 256);
+    const float* rope = r.W("tf.rope");
+    for (int l = 0; l < d.tf_layers; ++l) {
+        const std::string p = "tf." + std::to_string(l) + ".";
+        const float *an = r.W(p + "attn_norm"), *fn = r.W(p + "ffn_norm"), *g1 = r.W(p + "gamma1"), *g2 = r.W(p + "gamma2");
+        if (r.rc) return r.rc;
+        rmsnorm_rows_kernel<<<nwb, 256, 0, s>>>(b0, an, b1, rows, D, d.tf_norm_eps);
+        r.conv(b1, b2, T, D, 3 * H * HD, 1, 1, p + "wqkv", "", 0, nullptr, nullptr, nullptr, DEPI_NONE);
+        {
+            const long long n = rows * 2 * H * (HD / 2);
+            rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(b2, rope, B, T, H, HD);
+            dim3 grid((T + 3) / 4, H, B);
+            const float scale = 1.f / sqrtf((float)HD);
+            if (HD == 64) window_attn_kernel<64><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
+            else window_attn_kernel<32><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
+        }
+        r.conv(b1, b3, T, H * HD, D, 1, 1, p + "wo", "", 0, nullptr, b0, g1, DEPI_NONE);      // h = x + gamma1 * wo(y)
+        rmsnorm_rows_kernel<<<nwb, 256, 0, s>>>(b3, fn, b1, rows, D, d.tf_norm_eps);
+        r.conv(b1, b2, T, D, 2 * F, 1, 1, p + "w13", "", 0, nullptr, nullptr, nullptr, DEPI_NONE);
+        swiglu_kernel<<<(int)((rows * F + 255) / 256), 256, 0, s>>>(b2, b1, rows, F);
+        r.conv(b1, b0, T, F, D, 1, 1, p + "w2", "", 0, nullptr, b3, g2, DEPI_NONE);           // x = h + gamma2 * w2(..)
+    }
+    {
+        const float* nw = r.W("tf.norm");
+        if (r.rc) return r.rc;
+        rmsnorm_rows_kernel<<<nwb, 256, 0, s>>>(b0, nw, b1, rows, D, d.tf_norm_eps);
+    }
+    // ---- K13: upsample stages (rvq.py:263-276): transposed conv k=s=f, ConvNeXt block.  in b1 -> out b1
+    int len = T;
+    for (int i = 0; i < d.n_up; ++i) {
+        const int f = ups(d, i);
+        const std::string p = "up." + std::to_string(i) + ".";
+        r.conv(b1, b0, len, D, f * D, 1, 1, p + "ct_w", p + "ct_b", D, nullptr, nullptr, nullptr, DEPI_NONE);
+        len *= f;
+        const float *dww = r.W(p + "dw_w"), *dwb = r.W(p + "dw_b"), *lw = r.W(p + "ln_w"), *lb = r.W(p + "ln_b");
+        const float* gm = r.W(p + "gamma");
+        if (r.rc) return r.rc;
+        dwconv_ln_kernel<<<dim3(len, B), 256, D * sizeof(float), s>>>(b0, dww, dwb, lw, lb, b2, len, D);
+        r.conv(b2, b3, len, D, d.convnext_ratio * D, 1, 1, p + "pw1_w", p + "pw1_b", 0, nullptr, nullptr, nullptr, DEPI_GELU);
+        r.conv(b3, b1, len, d.convnext_ratio * D, D, 1, 1, p + "pw2_w", p + "pw2_b", 0, nullptr, b0, gm, DEPI_NONE);
+    }
+    // ---- K14: conv decoder (modded_dac.py:760-801)
+    int ch = d.decoder_dim;
+    r.conv(b1, b0, len, D, ch, 7, 1, "dec.in_w", "dec.in_b", 0, nullptr, nullptr, nullptr, DEPI_NONE);
+    float *cur = b0, *t1 = b1, *t2 = b2, *t3 = b3;
+    for (int i = 0; i < d.n_rates; ++i) {
+        const int st = rates(d, i), co = ch / 2;
+        const std::string p = "dec." + std::to_string(i) + ".";
+        r.conv(cur, t1, len, ch, st * co, 2, 1, p + "ct_w", p + "ct_b", co, r.W(p + "alpha"), nullptr, nullptr, DEPI_NONE);
+        len *= st; ch = co;
+        float *x = t1, *y = t2, *o = t3, *spare = cur;
+        const int dil[3] = {1, 3, 9};
+        for (int j = 0; j < 3; ++j) {
+            const std::string q = p + "r" + std::to_string(j) + ".";
+            r.conv(x, y, len, ch, ch, 7, dil[j], q + "w1", q + "b1", 0, r.W(q + "a1"), nullptr, nullptr, DEPI_NONE);
+            r.conv(y, o, len, ch, ch, 1, 1, q + "w2", q + "b2", 0, r.W(q + "a2"), x, nullptr, DEPI_NONE);
+            float* tmp = x; x = o; o = spare; spare = tmp;
+        }
+        cur = x; t1 = y; t2 = o; t3 = spare;
+        if (r.rc) return r.rc;
+    }
+    {
+        ConvArgs a{};
+        a.A = cur; a.W = r.W("dec.out_w"); a.bias = r.W("dec.out_b"); a.alpha = r.W("dec.out_alpha"); a.out = (float*)wav;
+        a.B = B; a.T = len; a.Cin = ch; a.N = 1; a.taps = 7; a.dil = 1; a.bias_mod = 1; a.epi = DEPI_TANH;
+        if (r.rc) return r.rc;
+        const long long warps = (long long)B * len;
+        conv_out1_kernel<<<(int)((warps * 32 + 255) / 256), 256, 0, s>>>(a);
+    }
+    DCK(cudaGetLastError());
+    return r.rc;
+}
+
+}  // extern "C"

@@ -30,7 +30,7 @@ struct GemvCfg {
     size_t self_pf = 512 * 1024;
     int tma = 1;          // 1: bulk-async-copy staged kernel (gemv_tma.cuh), 0: direct-load kernel (gemv.cuh)
     int nst = 4;          // ring depth of the staged kernel
-    int ctas_per_sm = 1;  // grid = ctas_per_sm * n_sm
+    int ctas_per_sm = 2;  // grid = ctas_per_sm * n_sm
     int stage_kb = 20;    // target stage size
 };
 

@@ -1,0 +1,206 @@
+"""Host-side mirror of the reference's DAC codec decode interface over the CUDA engine.
+
+Drop-in surface: an object with `from_indices(LongTensor[B, 10, T]) -> Tensor[B, 1, 2048*T]`,
+`sample_rate`, `device`, `quantizer.decode`-free (the whole of DAC.from_indices, modded_dac.py:925-927, runs in
+libfish_b200.so).  Host work done here, once, at construction: fold weight norm (g * v / ||v||, recomputed on every
+forward by the reference, modded_dac.py:553-556) and repack each conv / transposed conv / linear weight into the
+engine's implicit-GEMM layout [taps][Cin][N] (csrc/dac_kernels.cuh).  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass, fields
+from typing import Dict, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+
+
+@dataclass
+class DACConfig:
+    """fish_speech/configs/modded_dac_vq.yaml values the decode path uses."""
+
+    sample_rate: int = 44100
+    latent_dim: int = 1024
+    decoder_dim: int = 1536
+    decoder_rates: Tuple[int, ...] = (8, 8, 4, 2)
+    n_codebooks: int = 9
+    codebook_size: int = 1024
+    semantic_codebook_size: int = 4096
+    codebook_dim: int = 8
+    upsample_factors: Tuple[int, ...] = (2, 2)
+    tf_layers: int = 8
+    tf_heads: int = 16
+    tf_dim: int = 1024
+    tf_ffn: int = 3072
+    tf_head_dim: int = 64
+    tf_rope_base: float = 10000.0
+    tf_norm_eps: float = 1e-5
+    tf_window: int = 128
+    convnext_ratio: int = 4
+
+    @property
+    def hop(self) -> int:
+        return int(math.prod(self.upsample_factors) * math.prod(self.decoder_rates))
+
+    @classmethod
+    def from_any(cls, cfg) -> "DACConfig":
+        if isinstance(cfg, cls):
+            return cfg
+        names = [f.name for f in fields(cls)]
+        get = (lambda k: cfg.get(k)) if isinstance(cfg, dict) else (lambda k: getattr(cfg, k, None))
+        kw = {k: get(k) for k in names if get(k) is not None}
+        for k in ("decoder_rates", "upsample_factors"):
+            if k in kw:
+                kw[k] = tuple(kw[k])
+        return cls(**kw)
+
+
+def _weight_norm(v: Tensor, g: Tensor) -> Tensor:
+    """torch weight_norm(dim=0): g * v / ||v|| with the norm over every dim but 0."""
+    n = v.flatten(1).norm(dim=1).view(-1, *([1] * (v.dim() - 1)))
+    return v * (g / n)
+
+
+def _rope_table(seq_len: int, n_elem: int, base: float) -> Tensor:
+    """modded_dac.py:442-452: table rounded to bf16 even when the codec runs fp32; stored as fp32 for the engine."""
+    freqs = 1.0 / (base ** (torch.arange(0, n_elem, 2)[: (n_elem // 2)].float() / n_elem))
+    t = torch.arange(seq_len)
+    freqs = torch.outer(t, freqs)
+    cis = torch.polar(torch.ones_like(freqs), freqs)
+    return torch.stack([cis.real, cis.imag], dim=-1).to(torch.bfloat16).float()
+
+
+def pack_weights(c: DACConfig, sd: Dict[str, Tensor], max_frames: int) -> Dict[str, Tensor]:
+    """Reference state dict (names of modded_dac.DAC / rvq.DownsampleResidualVectorQuantize) -> engine tensors."""
+    f32 = lambda t: t.detach().float()
+    out: Dict[str, Tensor] = {}
+
+    def wn_new(p):  # parametrizations.weight_norm (modded convs)
+        return _weight_norm(f32(sd[p + "conv.parametrizations.weight.original1"]),
+                            f32(sd[p + "conv.parametrizations.weight.original0"]))
+
+    conv_pack = lambda w: w.permute(2, 1, 0).contiguous()           # [Cout,Cin,k] -> [k][Cin][Cout]
+
+    def convt_pack(w, s):                                           # [Cin,Cout,k] -> [k/s][Cin][s*Cout]
+        cin, cout, k = w.shape
+        # kernel tap j reads x[q - (taps-1-j)]: x[q] pairs with w[..., r], x[q-1] with w[..., r+s] -> flip the tap axis
+        return w.view(cin, cout, k // s, s).permute(2, 0, 3, 1).reshape(k // s, cin, s * cout).flip(0).contiguous()
+
+    # ---- RVQ (descript from_codes): codebooks + weight-normed 1x1 out_proj
+    prefixes = ["quantizer.semantic_quantizer.quantizers.0."] + [f"quantizer.quantizer.quantizers.{i}." for i in range(c.n_codebooks)]
+    out["rvq.codebooks"] = torch.cat([f32(sd[p + "codebook.weight"]) for p in prefixes], 0).contiguous()
+    out["rvq.proj_w"] = torch.stack([_weight_norm(f32(sd[p + "out_proj.weight_v"]), f32(sd[p + "out_proj.weight_g"]))[:, :, 0]
+                                     for p in prefixes]).contiguous()
+    out["rvq.proj_b"] = torch.stack([f32(sd[p + "out_proj.bias"]) for p in prefixes]).contiguous()
+    # ---- post_module transformer
+    out["tf.rope"] = _rope_table(max_frames, c.tf_head_dim, c.tf_rope_base).contiguous()
+    for i in range(c.tf_layers):
+        p, q = f"quantizer.post_module.layers.{i}.", f"tf.{i}."
+        out[q + "attn_norm"] = f32(sd[p + "attention_norm.weight"])
+        out[q + "ffn_norm"] = f32(sd[p + "ffn_norm.weight"])
+        out[q + "gamma1"] = f32(sd[p + "attention_layer_scale.gamma"])
+        out[q + "gamma2"] = f32(sd[p + "ffn_layer_scale.gamma"])
+        out[q + "wqkv"] = f32(sd[p + "attention.wqkv.weight"]).t().contiguous()
+        out[q + "wo"] = f32(sd[p + "attention.wo.weight"]).t().contiguous()
+        out[q + "w13"] = torch.cat([f32(sd[p + "feed_forward.w1.weight"]), f32(sd[p + "feed_forward.w3.weight"])], 0).t().contiguous()
+        out[q + "w2"] = f32(sd[p + "feed_forward.w2.weight"]).t().contiguous()
+    out["tf.norm"] = f32(sd["quantizer.post_module.norm.weight"])
+    # ---- upsample stages
+    for i, f in enumerate(c.upsample_factors):
+        p, q = f"quantizer.upsample.{i}.", f"up.{i}."
+        out[q + "ct_w"] = convt_pack(f32(sd[p + "0.conv.weight"]), f)
+        out[q + "ct_b"] = f32(sd[p + "0.conv.bias"])
+        out[q + "dw_w"] = f32(sd[p + "1.dwconv.conv.weight"])[:, 0, :].contiguous()
+        out[q + "dw_b"] = f32(sd[p + "1.dwconv.conv.bias"])
+        out[q + "ln_w"], out[q + "ln_b"] = f32(sd[p + "1.norm.weight"]), f32(sd[p + "1.norm.bias"])
+        out[q + "pw1_w"], out[q + "pw1_b"] = f32(sd[p + "1.pwconv1.weight"]).t().contiguous(), f32(sd[p + "1.pwconv1.bias"])
+        out[q + "pw2_w"], out[q + "pw2_b"] = f32(sd[p + "1.pwconv2.weight"]).t().contiguous(), f32(sd[p + "1.pwconv2.bias"])
+        out[q + "gamma"] = f32(sd[p + "1.gamma"])
+    # ---- conv decoder
+    out["dec.in_w"], out["dec.in_b"] = conv_pack(wn_new("decoder.model.0.")), f32(sd["decoder.model.0.conv.bias"])
+    for i, s in enumerate(c.decoder_rates):
+        p, q = f"decoder.model.{i + 1}.block.", f"dec.{i}."
+        out[q + "alpha"] = f32(sd[p + "0.alpha"]).flatten()
+        out[q + "ct_w"], out[q + "ct_b"] = convt_pack(wn_new(p + "1."), s), f32(sd[p + "1.conv.bias"])
+        for j in range(3):
+            u, v = p + f"{2 + j}.block.", q + f"r{j}."
+            out[v + "a1"], out[v + "a2"] = f32(sd[u + "0.alpha"]).flatten(), f32(sd[u + "2.alpha"]).flatten()
+            out[v + "w1"], out[v + "b1"] = conv_pack(wn_new(u + "1.")), f32(sd[u + "1.conv.bias"])
+            out[v + "w2"], out[v + "b2"] = conv_pack(wn_new(u + "3.")), f32(sd[u + "3.conv.bias"])
+    n = len(c.decoder_rates)
+    out["dec.out_alpha"] = f32(sd[f"decoder.model.{n + 1}.alpha"]).flatten()
+    out["dec.out_w"], out["dec.out_b"] = conv_pack(wn_new(f"decoder.model.{n + 2}.")), f32(sd[f"decoder.model.{n + 2}.conv.bias"])
+    return out
+
+
+class DACB200:
+    """Engine-backed stand-in for modded_dac.DAC on the decode side."""
+
+    def __init__(self, config, state_dict: Dict[str, Tensor], device="cuda:0", max_batch: int = 4, max_frames: int = 1024):
+        _lib.require_cuda()
+        self.lib = _lib.load()
+        self.config = c = DACConfig.from_any(config)
+        self.device = torch.device(device)
+        self.sample_rate = c.sample_rate
+        self.hop_length = c.hop
+        self.frame_length = c.hop
+        self.max_batch, self.max_frames = int(max_batch), int(max_frames)
+        rates = list(c.decoder_rates) + [1] * (4 - len(c.decoder_rates))
+        ups = list(c.upsample_factors) + [1] * (2 - len(c.upsample_factors))
+        self._desc = d = _lib.DACDesc(
+            latent_dim=c.latent_dim, decoder_dim=c.decoder_dim, n_rates=len(c.decoder_rates), rate0=rates[0], rate1=rates[1],
+            rate2=rates[2], rate3=rates[3], n_codebooks=c.n_codebooks, codebook_size=c.codebook_size,
+            semantic_codebook_size=c.semantic_codebook_size, codebook_dim=c.codebook_dim, n_up=len(c.upsample_factors),
+            up0=ups[0], up1=ups[1], tf_layers=c.tf_layers, tf_heads=c.tf_heads, tf_dim=c.tf_dim, tf_ffn=c.tf_ffn,
+            tf_head_dim=c.tf_head_dim, tf_window=c.tf_window, convnext_ratio=c.convnext_ratio, max_batch=self.max_batch,
+            max_frames=self.max_frames, tf_norm_eps=c.tf_norm_eps)
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            nbytes = self.lib.fsb_dac_workspace_bytes(C.byref(d))
+            self._workspace = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            rc = self.lib.fsb_dac_create(C.byref(d), self._workspace.data_ptr(), nbytes, C.byref(self._h))
+            self._ck(rc)
+            dev_sd = {k: v.to(self.device) for k, v in state_dict.items()}
+            self.weights = {k: v.contiguous() for k, v in pack_weights(c, dev_sd, self.max_frames).items()}
+            for k, v in self.weights.items():
+                self._ck(self.lib.fsb_dac_bind_weight(self._h, k.encode(), v.data_ptr(), v.numel()))
+
+    def _ck(self, rc: int):
+        if rc != 0:
+            raise RuntimeError("fish_b200 dac: " + (self.lib.fsb_dac_last_error(self._h) or b"").decode())
+
+    def __del__(self):
+        try:
+            if self._h:
+                self.lib.fsb_dac_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def flops(self, B: int, T: int) -> float:
+        return float(self.lib.fsb_dac_flops(self._h, B, T))
+
+    @torch.inference_mode()
+    def from_indices(self, indices: Tensor) -> Tensor:
+        """DAC.from_indices (modded_dac.py:925-927): [B, 1+n_codebooks, T] int64 -> [B, 1, hop*T] fp32.
+        Like the reference (rvq.py:354-359) the caller's `indices` tensor is clamped in place when it is already a
+        contiguous int64 CUDA tensor."""
+        if indices.dim() != 3 or indices.shape[1] != self.config.n_codebooks + 1:
+            raise ValueError(f"expected [B, {self.config.n_codebooks + 1}, T] indices, got {tuple(indices.shape)}")
+        B, _, T = indices.shape
+        if T > self.max_frames:
+            raise ValueError(f"T={T} exceeds the engine's max_frames={self.max_frames}")
+        idx = indices
+        if idx.device != self.device or idx.dtype != torch.int64 or not idx.is_contiguous():
+            idx = indices.to(device=self.device, dtype=torch.int64).contiguous()
+        wav = torch.empty((B, 1, self.hop_length * T), dtype=torch.float32, device=self.device)
+        st = torch.cuda.current_stream().cuda_stream
+        for b0 in range(0, B, self.max_batch):
+            nb = min(self.max_batch, B - b0)
+            self._ck(self.lib.fsb_dac_decode(self._h, idx[b0: b0 + nb].data_ptr(), nb, T, wav[b0: b0 + nb].data_ptr(), st))
+        return wav
+

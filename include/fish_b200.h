@@ -117,6 +117,35 @@ int fsb_sample(const void* logits, const void* bias, int32_t B, int32_t V, int32
                float top_p, int32_t n_variants, float temp2, float top_p2, const void* uniforms, uint64_t seed,
                int32_t seg0_lo, int32_t seg0_hi, int32_t seg1_lo, int32_t seg1_hi, int32_t* out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * DAC codec decode (fish_speech/models/dac/modded_dac.py: DAC.from_indices:925 ; rvq.py decode:352)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fsb_dac fsb_dac;
+
+/* fish_speech/configs/modded_dac_vq.yaml values the decode path uses. */
+typedef struct {
+    int32_t latent_dim, decoder_dim, n_rates, rate0, rate1, rate2, rate3;
+    int32_t n_codebooks /* residual */, codebook_size, semantic_codebook_size, codebook_dim;
+    int32_t n_up, up0, up1;
+    int32_t tf_layers, tf_heads, tf_dim, tf_ffn, tf_head_dim, tf_window, convnext_ratio;
+    int32_t max_batch, max_frames; /* workspace sizing: clips per call, code frames per clip */
+    float tf_norm_eps;
+} fsb_dac_desc;
+
+size_t fsb_dac_workspace_bytes(const fsb_dac_desc* desc);
+int fsb_dac_create(const fsb_dac_desc* desc, void* workspace, size_t workspace_bytes, fsb_dac** out);
+int fsb_dac_destroy(fsb_dac* h);
+const char* fsb_dac_last_error(const fsb_dac* h);
+/* fp32 device tensors, weight norm folded, packed [taps][Cin][N] by the host mirror (fish_speech_b200/dac.py lists
+ * the name of every tensor and the reference state-dict keys it is built from). */
+int fsb_dac_bind_weight(fsb_dac* h, const char* name, const void* dptr, int64_t numel);
+/* DAC.from_indices: codes int64 [B][1+n_codebooks][T] (clamped IN PLACE like rvq.py:354-359) -> wav fp32 [B][hop*T]. */
+int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, void* stream);
+/* internal activation buffers "buf0".."buf3" (tests / profiling) */
+int fsb_dac_stage(fsb_dac* h, const char* name, void** dptr, size_t* bytes);
+/* algorithmic FLOPs of one decode call (GEMM-shaped work only) */
+double fsb_dac_flops(const fsb_dac* h, int32_t B, int32_t T);
+
 #ifdef __cplusplus
 }
 #endif
