@@ -29,9 +29,9 @@ struct GemvCfg {
     int n_sm = 148;
     size_t self_pf = 512 * 1024;
     int tma = 1;          // 1: bulk-async-copy staged kernel (gemv_tma.cuh), 0: direct-load kernel (gemv.cuh)
-    int nst = 4;          // ring depth of the staged kernel
-    int ctas_per_sm = 2;  // grid = ctas_per_sm * n_sm
-    int stage_kb = 20;    // target stage size
+    int nst = 4;          // ring depth of the staged kernel (4 x 40 KB = 160 KB in flight per SM)
+    int ctas_per_sm = 1;  // grid = ctas_per_sm * n_sm
+    int stage_kb = 40;    // target stage size: 8 row slices of 5 KB (bulk copies below ~4 KB are issue-bound)
 };
 
 }  // namespace
@@ -186,10 +186,13 @@ cudaError_t run_gemv(const GemvCfg& gc, bool pdl, cudaStream_t s, int M, int N, 
         const size_t xsmem = (size_t)mb * K * sizeof(bf16);
         if (gc.tma) {
             const int nacc = (epi == EPI_SWIGLU) ? 2 : 1;
-            const int kc = pick_kc(K, gc.stage_kb * 1024 / (GT_ROWS * 2 * nacc));
-            const int nst = std::max(2, std::min(gc.nst, GT_MAX_STAGES));
-            const size_t smem = (size_t)nst * GT_ROWS * kc * 2 * nacc + xsmem;
-            if (kc > 0 && smem <= 200 * 1024) {
+            const int kc = pick_kc(K, std::min(gc.stage_kb * 1024 / (GT_ROWS * 2), 32 * 8 * GT_CPL));
+            (void)nacc;
+            int nst = std::max(2, std::min(gc.nst, GT_MAX_STAGES));
+            if (kc > 0 && xsmem < 200 * 1024)
+                nst = std::min<int>(nst, (int)((200 * 1024 - xsmem) / ((size_t)GT_ROWS * kc * 2)));
+            const size_t smem = (size_t)nst * GT_ROWS * kc * 2 + xsmem;
+            if (kc > 0 && nst >= 2 && smem <= 200 * 1024) {
                 GemvTmaGeom g{kc, nst};
                 const int nb = std::min(gc.ctas_per_sm * gc.n_sm, std::max(1, N / GT_ROWS));
                 cudaLaunchConfig_t cfg{};

@@ -6,17 +6,25 @@
 // depend on what the math warps are doing, and the producer starts streaming BEFORE griddepcontrol.wait
 // (weights are immutable), which keeps HBM busy across the PDL kernel boundary.
 //
-//   stage  = 8 rows x KC columns (x2 matrices for SwiGLU): one bulk copy per row slice (KC*2 bytes, contiguous)
-//   warp w = row w of the current 8-row group; accumulates over the K/KC stages of the group, then finalises
-//   full[s]/empty[s] mbarriers: producer arrives with expect_tx, 8 consumer warps arrive to release a stage
+//   CTA    = 1 producer warp + 2 teams of 8 consumer warps; grid = one CTA per SM, <= ~100 KB of shared memory and
+//            <= 60 registers per thread, so the NEXT kernel's CTA fits on the SM beside it and fills its ring while this
+//            one drains (the weights never depend on the previous kernel)
+//   stage  = 8 rows x KC columns of ONE matrix: one bulk copy per row slice (KC*2 bytes, contiguous, >= 2 KB)
+//   team t = row groups 2p+t; warp w of the team = row w of the group; accumulates over the K/KC stages
+//            (x2 matrices for SwiGLU), then finalises.  Stage order interleaves the two teams so both stay busy.
+//   full[s]/empty[s] mbarriers: producer arrives with expect_tx; ALL 16 consumer warps wait on and release every stage
+//            (only the owning team computes on it), so nobody can run a phase ahead of or behind a barrier
 #pragma once
 #include "common.cuh"
 #include "gemv.cuh"
 
 #define GT_ROWS 8
-#define GT_CONSUMERS 256
+#define GT_TEAM_WARPS 8
+#define GT_TEAMS 2
+#define GT_CONSUMERS (32 * GT_TEAM_WARPS * GT_TEAMS)
 #define GT_THREADS (GT_CONSUMERS + 32)
-#define GT_MAX_STAGES 6
+#define GT_MAX_STAGES 10
+#define GT_CPL 10  // 128-bit chunks per lane per row slice: KC <= 1280 columns
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
@@ -29,7 +37,8 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* b) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
-    uint32_t ok;
+    uint32_t ok, spins = 0;
+    long long t0 = 0;
     do {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
@@ -38,6 +47,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
             : "=r"(ok)
             : "r"(smem_u32(b)), "r"(parity)
             : "memory");
+        if (!ok && (++spins & 0xfffu) == 0) {  // watchdog: a protocol bug must fault, not hang the GPU
+            if (t0 == 0) t0 = clock64();
+            else if (clock64() - t0 > 4000000000LL) __trap();
+        }
     } while (!ok);
 }
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
@@ -60,9 +73,22 @@ __device__ __forceinline__ float consumer_sum(float v, float* red) {
 }
 
 struct GemvTmaGeom {
-    int KC;       // columns per stage (divides K, multiple of 8)
-    int NST;      // ring depth
+    int KC;   // columns per stage (divides K, multiple of 8)
+    int NST;  // ring depth
 };
+
+// stage iteration space shared by producer and consumers: it -> (team, matrix q, k-chunk, row group)
+struct GtStage { int team, q, kc, gi; };
+template <int NACC>
+__device__ __forceinline__ GtStage gt_decode(int it, int NK) {
+    GtStage s;
+    s.team = it % GT_TEAMS;
+    int r = it / GT_TEAMS;
+    s.q = r % NACC; r /= NACC;
+    s.kc = r % NK;
+    s.gi = (r / NK) * GT_TEAMS + s.team;
+    return s;
+}
 
 template <int M, int PRO, int EPI>
 __global__ void __launch_bounds__(GT_THREADS, 1) gemv_tma_kernel(GemvArgs a, GemvTmaGeom g) {
@@ -80,10 +106,10 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemv_tma_kernel(GemvArgs a, Gem
     const int nrows = r1 - r0;
     const int ngroups = (nrows + GT_ROWS - 1) / GT_ROWS;
     const int NK = K / g.KC;
-    const int total = ngroups * NK;
+    const int total = ((ngroups + GT_TEAMS - 1) / GT_TEAMS) * NK * NACC * GT_TEAMS;
     const uint32_t slice_bytes = (uint32_t)g.KC * 2u;
-    const uint32_t stage_bytes = (uint32_t)GT_ROWS * slice_bytes * NACC;
-    unsigned char* stages = smem_raw;                                         // [NST][NACC][8][KC] bf16
+    const uint32_t stage_bytes = (uint32_t)GT_ROWS * slice_bytes;
+    unsigned char* stages = smem_raw;                                              // [NST][8][KC] bf16
     uint4* xs = reinterpret_cast<uint4*>(smem_raw + (size_t)g.NST * stage_bytes);  // [M][K/8]
 
     if (tid == 0) {
@@ -94,23 +120,23 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemv_tma_kernel(GemvArgs a, Gem
 
     if (warp == GT_CONSUMERS / 32) {
         // ================= producer warp: weights only, never waits on the previous kernel =================
+        int n = 0;
         for (int it = 0; it < total; ++it) {
-            const int slot = it % g.NST, ph = (it / g.NST) & 1;
-            const int gi = it / NK, kc = it % NK;
-            const int g0 = r0 + gi * GT_ROWS;
+            const GtStage st = gt_decode<NACC>(it, NK);
+            if (st.gi >= ngroups) continue;
+            const int slot = n % g.NST, ph = (n / g.NST) & 1;
+            ++n;
+            const int g0 = r0 + st.gi * GT_ROWS;
             const int ng = min(GT_ROWS, r1 - g0);
             mbar_wait(&empty_bar[slot], ph ^ 1);
-            if (lane == 0) mbar_expect_tx(&full_bar[slot], (uint32_t)ng * slice_bytes * NACC);
+            if (lane == 0) mbar_expect_tx(&full_bar[slot], (uint32_t)ng * slice_bytes);
             __syncwarp();
-            unsigned char* sb = stages + (size_t)slot * stage_bytes;
-            for (int c = lane; c < ng * NACC; c += 32) {
-                const int q = c / ng, i = c % ng;
-                const bf16* src = (q == 0 ? a.W : a.W2) + (size_t)(g0 + i) * K + (size_t)kc * g.KC;
-                bulk_g2s(sb + ((size_t)q * GT_ROWS + i) * slice_bytes, src, slice_bytes, &full_bar[slot]);
+            if (lane < ng) {
+                const bf16* src = (st.q == 0 ? a.W : a.W2) + (size_t)(g0 + lane) * K + (size_t)st.kc * g.KC;
+                bulk_g2s(stages + (size_t)slot * stage_bytes + (size_t)lane * slice_bytes, src, slice_bytes, &full_bar[slot]);
             }
         }
         if (lane == 0) l2_prefetch_share(a.pf_ptr, a.pf_bytes, b, nb);
-        pdl_launch_dependents();
         return;
     }
 
@@ -153,51 +179,80 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemv_tma_kernel(GemvArgs a, Gem
     }
     consumer_sync();
 
+    const int my_team = warp / GT_TEAM_WARPS, row = warp % GT_TEAM_WARPS;
     const int SC8 = g.KC >> 3;  // uint4 per row slice
     float acc[NACC][M];
+    int n = 0;
     for (int it = 0; it < total; ++it) {
-        const int slot = it % g.NST, ph = (it / g.NST) & 1;
-        const int gi = it / NK, kc = it % NK;
-        const int g0 = r0 + gi * GT_ROWS;
+        const GtStage st = gt_decode<NACC>(it, NK);
+        if (st.gi >= ngroups) continue;
+        const int slot = n % g.NST, ph = (n / g.NST) & 1;
+        ++n;
+        if (st.team != my_team) {
+            // every consumer warp observes and releases every stage, in order: an mbarrier waiter may be neither more
+            // than one phase ahead (parity aliasing) nor behind (slot recycled under it) of the barrier it waits on
+            mbar_wait(&full_bar[slot], ph);
+            if (lane == 0) mbar_arrive(&empty_bar[slot]);
+            continue;
+        }
+        const int g0 = r0 + st.gi * GT_ROWS;
         const int ng = min(GT_ROWS, r1 - g0);
-        if (kc == 0) {
+        if (st.kc == 0 && st.q == 0) {
 #pragma unroll
             for (int q = 0; q < NACC; ++q)
 #pragma unroll
                 for (int m = 0; m < M; ++m) acc[q][m] = 0.f;
         }
         mbar_wait(&full_bar[slot], ph);
-        if (warp < ng) {
-            const uint4* w0 = reinterpret_cast<const uint4*>(stages + (size_t)slot * stage_bytes + (size_t)warp * slice_bytes);
-            const uint4* w1 = reinterpret_cast<const uint4*>(stages + (size_t)slot * stage_bytes +
-                                                            ((size_t)GT_ROWS + warp) * slice_bytes);
-            const uint4* xk = xs + kc * SC8;
-#pragma unroll 2
-            for (int c = lane; c < SC8; c += 32) {
-                float wf[8], wf2[8];
-                unpack8(w0[c], wf);
-                if (NACC == 2) unpack8(w1[c], wf2);
+        if (row < ng) {
+            const uint4* w0 = reinterpret_cast<const uint4*>(stages + (size_t)slot * stage_bytes + (size_t)row * slice_bytes);
+            const uint4* xk = xs + st.kc * SC8;
+            // whole row slice of this lane in registers first (<= GT_CPL 128-bit LDS in flight), then the FMAs on two
+            // independent partial sums per row of x: a single serial chain per warp was latency-bound
+            float part[M];
+            uint4 wv[GT_CPL];
 #pragma unroll
-                for (int m = 0; m < M; ++m) {
-                    float xf[8];
-                    unpack8(xk[m * KC8 + c], xf);
+            for (int i = 0; i < GT_CPL; ++i) {
+                const int c = lane + 32 * i;
+                wv[i] = (c < SC8) ? w0[c] : make_uint4(0, 0, 0, 0);
+            }
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        acc[0][m] = fmaf(wf[i], xf[i], acc[0][m]);
-                        if (NACC == 2) acc[NACC - 1][m] = fmaf(wf2[i], xf[i], acc[NACC - 1][m]);
+            for (int m = 0; m < M; ++m) {
+                uint4 xv[GT_CPL];
+#pragma unroll
+                for (int i = 0; i < GT_CPL; ++i) {
+                    const int c = lane + 32 * i;
+                    xv[i] = (c < SC8) ? xk[m * KC8 + c] : make_uint4(0, 0, 0, 0);
+                }
+                float pa = 0.f, pb = 0.f;
+#pragma unroll
+                for (int i = 0; i < GT_CPL; ++i) {
+                    float wf[8], xf[8];
+                    unpack8(wv[i], wf);
+                    unpack8(xv[i], xf);
+#pragma unroll
+                    for (int e = 0; e < 8; e += 2) {
+                        pa = fmaf(wf[e], xf[e], pa);
+                        pb = fmaf(wf[e + 1], xf[e + 1], pb);
                     }
                 }
+                part[m] = pa + pb;
+            }
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                if (NACC == 2 && st.q == 1) acc[NACC - 1][m] += part[m];
+                else acc[0][m] += part[m];
             }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[slot]);
-        if (kc == NK - 1 && warp < ng) {
+        if (st.kc == NK - 1 && st.q == NACC - 1 && row < ng) {
 #pragma unroll
             for (int m = 0; m < M; ++m) {
                 const float s = warp_sum(acc[0][m]);
                 const float s2 = (NACC == 2) ? warp_sum(acc[NACC - 1][m]) : 0.f;
                 if (lane == 0 && m < a.M_valid) {
-                    const size_t oi = (size_t)m * a.N + (g0 + warp);
+                    const size_t oi = (size_t)m * a.N + (g0 + row);
                     float o = rbf(s);
                     if (EPI == EPI_RESIDUAL) {
                         o = __bfloat162float(a.res[oi]) + o;

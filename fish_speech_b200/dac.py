@@ -165,7 +165,8 @@ class DACB200:
             rc = self.lib.fsb_dac_create(C.byref(d), self._workspace.data_ptr(), nbytes, C.byref(self._h))
             self._ck(rc)
             dev_sd = {k: v.to(self.device) for k, v in state_dict.items()}
-            self.weights = {k: v.contiguous() for k, v in pack_weights(c, dev_sd, self.max_frames).items()}
+            self.weights = {k: v.to(self.device, torch.float32).contiguous()
+                            for k, v in pack_weights(c, dev_sd, self.max_frames).items()}
             for k, v in self.weights.items():
                 self._ck(self.lib.fsb_dac_bind_weight(self._h, k.encode(), v.data_ptr(), v.numel()))
 

@@ -47,10 +47,12 @@ def run(name, N, K, pro, epi, reps=3):
 
 
 configs = [dict(FSB_GEMV_TMA="0")]
-for nst, cps, kb in itertools.product([3, 4, 6], [1, 2], [20, 32]):
-    if cps * (nst * kb + 20) > 220:
-        continue
-    configs.append(dict(FSB_GEMV_TMA="1", FSB_GEMV_NST=str(nst), FSB_GEMV_CPS=str(cps), FSB_GEMV_STAGE_KB=str(kb)))
+for nst, cps in [(4, 1), (8, 1), (10, 1), (4, 2), (5, 2)]:
+    configs.append(dict(FSB_GEMV_TMA="1", FSB_GEMV_NST=str(nst), FSB_GEMV_CPS=str(cps), FSB_GEMV_STAGE_KB="20"))
+if len(sys.argv) > 1:
+    SHAPES = [s for s in SHAPES if s[0] in sys.argv[1].split(",")]
+if os.environ.get("SWEEP_ONE"):
+    configs = [dict()]
 for cfg in configs:
     os.environ.update(cfg)
     row = []
