@@ -23,16 +23,12 @@ struct EmbedArgs {
     const void* pf_ptr; size_t pf_bytes;
 };
 
-__global__ void __launch_bounds__(256) embed_kernel(EmbedArgs a) {
-    if (threadIdx.x == 0) l2_prefetch_share(a.pf_ptr, a.pf_bytes, blockIdx.x, gridDim.x);
-    pdl_wait();
-    pdl_launch_dependents();
-    const int m = blockIdx.x;
+__device__ __forceinline__ void embed_body(const EmbedArgs& a, int m, int tid, int nt) {
     const int32_t* t = a.tokens + (size_t)m * (a.C + 1);
-    const int tok = t[0];
+    const int tok = lda(&t[0]);
     const bool sem = tok >= a.sem_begin && tok <= a.sem_end;
     const int DC = a.D >> 3;
-    for (int c = threadIdx.x; c < DC; c += blockDim.x) {
+    for (int c = tid; c < DC; c += nt) {
         float e[8], s[8];
         unpack8(reinterpret_cast<const uint4*>(a.emb + (size_t)tok * a.D)[c], e);
 #pragma unroll
@@ -40,7 +36,7 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedArgs a) {
         if (sem) {
             for (int k = 0; k < a.C; ++k) {
                 float f[8];
-                const size_t row = (size_t)t[k + 1] + (size_t)k * a.cb;
+                const size_t row = (size_t)lda(&t[k + 1]) + (size_t)k * a.cb;
                 unpack8(reinterpret_cast<const uint4*>(a.cb_emb + row * a.D)[c], f);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) s[i] += f[i];
@@ -57,6 +53,12 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedArgs a) {
         reinterpret_cast<uint4*>(a.x + (size_t)m * a.D)[c] = o;
     }
 }
+__global__ void __launch_bounds__(256) embed_kernel(EmbedArgs a) {
+    if (threadIdx.x == 0) l2_prefetch_share(a.pf_ptr, a.pf_bytes, blockIdx.x, gridDim.x);
+    pdl_wait();
+    pdl_launch_dependents();
+    embed_body(a, blockIdx.x, threadIdx.x, blockDim.x);
+}
 
 // ----------------------------------------------------------------------------- head prep: per-head RMSNorm (single rounding) + RoPE
 // One warp per head vector; lane owns EPL = HD/32 contiguous elements (whole interleaved pairs).
@@ -70,7 +72,7 @@ __device__ __forceinline__ void head_norm_rope(const bf16* src, const bf16* norm
     const int lane = threadIdx.x & 31;
     float v[EPL];
 #pragma unroll
-    for (int i = 0; i < EPL; ++i) v[i] = __bfloat162float(src[lane * EPL + i]);
+    for (int i = 0; i < EPL; ++i) v[i] = lda(&src[lane * EPL + i]);
     if (qk_norm) {
         float ss = 0.f;
 #pragma unroll
@@ -132,7 +134,7 @@ __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
     } else {
         const bf16* v = a.qkv + (size_t)m * qkv_w + (a.H + a.KV + h) * HD;
 #pragma unroll
-        for (int i = 0; i < EPL; ++i) a.vcache[co + lane * EPL + i] = v[lane * EPL + i];
+        for (int i = 0; i < EPL; ++i) a.vcache[co + lane * EPL + i] = lda_raw(&v[lane * EPL + i]);
     }
 }
 
@@ -140,8 +142,11 @@ __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
 #define ATTN_THREADS 128
 #define ATTN_TILE 128
 
-template <int HD, int GQ>
-__global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
+// one (split, kv head, row) work item on ATTN_THREADS threads synchronised through SY; tid = index inside the group
+// QREG: keep q in registers (standalone kernel) or read it from shared memory in the FMA loop (persistent frame kernel,
+// which is capped at 96 registers per thread by its 17 warps per SM)
+template <int HD, int GQ, class SY, bool QREG = true>
+__device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, int h, int m, int tid) {
     constexpr int EPL = HD / 32;
     constexpr int LPK = HD / 8;              // lanes per key row (16 B each)
     constexpr int KPI = ATTN_THREADS / LPK;  // keys per CTA step
@@ -152,13 +157,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
     __shared__ float mrun[GQ], lrun[GQ], corr[GQ];
     __shared__ int is_last;
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
-    if (tid == 0)
-        l2_prefetch_share(a.pf_ptr, a.pf_bytes, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
-                          gridDim.x * gridDim.y * gridDim.z);
-    pdl_wait();
-    pdl_launch_dependents();
+    const int lane = tid & 31, warp = tid >> 5;
 
     const int pos = a.pos[m];
     const int slot = a.slots ? a.slots[m] : m;
@@ -193,21 +192,23 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
             const bf16* v = row + (a.H + a.KV + h) * HD;
 #pragma unroll
             for (int i = 0; i < EPL; ++i) {
-                const bf16 t = v[lane * EPL + i];
+                const bf16 t = lda_raw(&v[lane * EPL + i]);
                 vnew[lane * EPL + i] = __bfloat162float(t);
                 a.vcache[co + lane * EPL + i] = t;
             }
         }
     }
     if (tid < GQ) { mrun[tid] = -INFINITY; lrun[tid] = 0.f; }
-    __syncthreads();
+    SY::sync();
 
     const int kslot = tid / LPK, chunk = tid % LPK;
-    float qreg[GQ][8];
+    float qreg[QREG ? GQ : 1][8];
+    if (QREG) {
 #pragma unroll
-    for (int g = 0; g < GQ; ++g)
+        for (int g = 0; g < GQ; ++g)
 #pragma unroll
-        for (int i = 0; i < 8; ++i) qreg[g][i] = qs[g][chunk * 8 + i];
+            for (int i = 0; i < 8; ++i) qreg[g][i] = qs[g][chunk * 8 + i];
+    }
     float acc[GQ][8];
 #pragma unroll
     for (int g = 0; g < GQ; ++g)
@@ -237,7 +238,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
             for (int g = 0; g < GQ; ++g) {
                 float s = 0.f;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) s = fmaf(qreg[g][i], kf[i], s);
+                for (int i = 0; i < 8; ++i) s = fmaf(QREG ? qreg[QREG ? g : 0][i] : qs[g][chunk * 8 + i], kf[i], s);
                 d[g] = s;
             }
 #pragma unroll
@@ -248,7 +249,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
 #pragma unroll
                 for (int g = 0; g < GQ; ++g) sc[g][j - t0] = d[g] * a.scale;
         }
-        __syncthreads();
+        SY::sync();
         // -- online softmax bookkeeping: warp g owns head g
         for (int g = warp; g < GQ; g += ATTN_THREADS / 32) {
             float mx = -INFINITY;
@@ -270,7 +271,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
                 lrun[g] = lrun[g] * c + sum;
             }
         }
-        __syncthreads();
+        SY::sync();
         // -- rescale and accumulate P.V
 #pragma unroll
         for (int g = 0; g < GQ; ++g) {
@@ -293,7 +294,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
                 for (int i = 0; i < 8; ++i) acc[g][i] = fmaf(p, vf[i], acc[g][i]);
             }
         }
-        __syncthreads();
+        SY::sync();
     }
 
     // ---- reduce acc over the KPI key slots
@@ -301,7 +302,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
     for (int g = 0; g < GQ; ++g)
 #pragma unroll
         for (int i = 0; i < 8; ++i) accs[kslot][g][chunk * 8 + i] = acc[g][i];
-    __syncthreads();
+    SY::sync();
 
     const int H = a.H;
     if (a.splits == 1) {
@@ -328,12 +329,12 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
         a.ws_ml[(pbase * GQ + tid) * 2 + 1] = lrun[tid];
     }
     __threadfence();
-    __syncthreads();
+    SY::sync();
     if (tid == 0) {
         const int prev = atomicAdd(&a.counters[m * a.KV + h], 1);
         is_last = (prev == a.splits - 1);
     }
-    __syncthreads();
+    SY::sync();
     if (!is_last) return;
     __threadfence();
     const size_t b0 = ((size_t)m * a.KV + h) * a.splits;
@@ -353,20 +354,24 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
     }
     if (tid == 0) a.counters[m * a.KV + h] = 0;  // re-arm for the next launch
 }
+template <int HD, int GQ>
+__global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
+    if (threadIdx.x == 0)
+        l2_prefetch_share(a.pf_ptr, a.pf_bytes, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
+                          gridDim.x * gridDim.y * gridDim.z);
+    pdl_wait();
+    pdl_launch_dependents();
+    attn_decode_body<HD, GQ, SyncBlock<ATTN_THREADS>>(a, blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
+}
 
 // ----------------------------------------------------------------------------- fast-AR attention (context <= 16)
 #define FAST_MAX_CTX 16
 
-template <int HD, int GQ>
-__global__ void __launch_bounds__(32 * GQ) fast_attn_kernel(AttnArgs a) {
+template <int HD, int GQ, class SY>
+__device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, int tid) {
     constexpr int EPL = HD / 32;
     __shared__ float knew[HD], vnew[HD];
-    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
-    const int h = blockIdx.x, m = blockIdx.y;
-    if (threadIdx.x == 0)
-        l2_prefetch_share(a.pf_ptr, a.pf_bytes, blockIdx.y * gridDim.x + blockIdx.x, gridDim.x * gridDim.y);
-    pdl_wait();
-    pdl_launch_dependents();
+    const int lane = tid & 31, g = tid >> 5;
 
     const int pos = a.pos_fixed;  // codebook index of this pass
     const int slot = a.slots ? a.slots[m] : m;
@@ -390,12 +395,12 @@ __global__ void __launch_bounds__(32 * GQ) fast_attn_kernel(AttnArgs a) {
         const bf16* v = row + (a.H + a.KV + h) * HD;
 #pragma unroll
         for (int i = 0; i < EPL; ++i) {
-            const bf16 t = v[lane * EPL + i];
+            const bf16 t = lda_raw(&v[lane * EPL + i]);
             vnew[lane * EPL + i] = __bfloat162float(t);
             a.vcache[cbase + (size_t)pos * HD + lane * EPL + i] = t;
         }
     }
-    __syncthreads();
+    SY::sync();
 
     // scores: bf16(q.k) then bf16(* scale)   (llama.py:964-966; masked entries never enter the softmax)
     float s[FAST_MAX_CTX];
@@ -408,7 +413,7 @@ __global__ void __launch_bounds__(32 * GQ) fast_attn_kernel(AttnArgs a) {
 #pragma unroll
             for (int i = 0; i < EPL; ++i) {
                 const float kv = (j == pos) ? knew[lane * EPL + i]
-                                            : __bfloat162float(a.kcache[cbase + (size_t)j * HD + lane * EPL + i]);
+                                            : lda(&a.kcache[cbase + (size_t)j * HD + lane * EPL + i]);
                 d = fmaf(q[i], kv, d);
             }
             d = warp_sum(d);
@@ -430,11 +435,19 @@ __global__ void __launch_bounds__(32 * GQ) fast_attn_kernel(AttnArgs a) {
 #pragma unroll
             for (int i = 0; i < EPL; ++i) {
                 const float vv = (j == pos) ? vnew[lane * EPL + i]
-                                            : __bfloat162float(a.vcache[cbase + (size_t)j * HD + lane * EPL + i]);
+                                            : lda(&a.vcache[cbase + (size_t)j * HD + lane * EPL + i]);
                 o[i] = fmaf(p, vv, o[i]);
             }
         }
 #pragma unroll
     for (int i = 0; i < EPL; ++i)
         a.y[(size_t)m * a.H * HD + (h * GQ + g) * HD + lane * EPL + i] = __float2bfloat16_rn(o[i]);
+}
+template <int HD, int GQ>
+__global__ void __launch_bounds__(32 * GQ) fast_attn_kernel(AttnArgs a) {
+    if (threadIdx.x == 0)
+        l2_prefetch_share(a.pf_ptr, a.pf_bytes, blockIdx.y * gridDim.x + blockIdx.x, gridDim.x * gridDim.y);
+    pdl_wait();
+    pdl_launch_dependents();
+    fast_attn_body<HD, GQ, SyncBlock<32 * GQ>>(a, blockIdx.x, blockIdx.y, threadIdx.x);
 }

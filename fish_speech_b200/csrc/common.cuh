@@ -101,3 +101,40 @@ __device__ __forceinline__ float block_max(float v, float* red) {
     t = warp_max(t);
     return t;
 }
+
+// ----------------------------------------------------------------------------- thread-group sync policies
+// Device "bodies" (attention, sampling, ...) are written against a policy so that the same code runs as a whole
+// CTA of a standalone kernel (SyncBlock) or on a subset of the warps of the persistent frame kernel (SyncNamed).
+template <int NT_>
+struct SyncBlock {
+    static constexpr int NT = NT_;
+    static __device__ __forceinline__ void sync() { __syncthreads(); }
+};
+template <int ID, int NT_>
+struct SyncNamed {
+    static constexpr int NT = NT_;
+    static __device__ __forceinline__ void sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(NT_) : "memory"); }
+};
+// group-wide sum over SY::NT threads (tid = index inside the group); `red` >= 32 floats of shared memory
+template <class SY>
+__device__ __forceinline__ float group_sum(float v, float* red, int tid) {
+    const int lane = tid & 31, w = tid >> 5;
+    v = warp_sum(v);
+    SY::sync();
+    if (lane == 0) red[w] = v;
+    SY::sync();
+    float t = (lane < SY::NT / 32) ? red[lane] : 0.f;
+    return warp_sum(t);
+}
+
+// ----------------------------------------------------------------------------- activation loads
+// Activations are produced by other CTAs of the same launch in the persistent frame kernel, so they are always read
+// through L2 (ld.global.cg): L1 is not coherent across SMs within a launch.
+__device__ __forceinline__ float lda(const bf16* p) {
+    return bf16_bits_to_f(__ldcg(reinterpret_cast<const unsigned short*>(p)));
+}
+__device__ __forceinline__ bf16 lda_raw(const bf16* p) {
+    return __ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(p)));
+}
+__device__ __forceinline__ uint4 lda(const uint4* p) { return __ldcg(p); }
+__device__ __forceinline__ int lda(const int* p) { return __ldcg(p); }

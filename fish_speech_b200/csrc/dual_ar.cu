@@ -12,6 +12,7 @@
 #include "../../include/fish_b200.h"
 #include "attn.cuh"
 #include "gemv.cuh"
+#include "frame_mega.cuh"
 #include "gemv_tma.cuh"
 #include "sample.cuh"
 
@@ -24,6 +25,8 @@ struct LayerW {
 };
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+constexpr size_t MEGA_BUF_BYTES = 512 * 1024;
+constexpr size_t MEGA_TRACE_WORDS = 160 * 512 * 4;  // [CTAs][ops][4] time stamps of one frame (profiling aid)
 
 struct GemvCfg {
     int n_sm = 148;
@@ -50,9 +53,21 @@ struct fsb_dual_ar {
          *xfast = nullptr, *xf = nullptr, *xf2 = nullptr, *slow_logits = nullptr, *fast_logits = nullptr;
     float *ws_acc = nullptr, *ws_ml = nullptr;
     int32_t *counters = nullptr, *pf_pos = nullptr, *pf_slot = nullptr;
+    char* mega_buf = nullptr;        // device copy of the persistent frame kernel's op list (MEGA_BUF_BYTES)
+    unsigned* mega_sync = nullptr;   // grid barrier counters
+    unsigned long long* mega_prof = nullptr;  // cycle counters of CTA 0 when option "mega_prof" is on
+    int mega_prof_on = 0;
+    unsigned long long* mega_trace = nullptr;
+    int mega_trace_on = 0;
+    int mega_copy_bytes = 5120;      // bulk-copy granularity inside a ring stage
+    int mega_pf_stages = 16;         // L2 prefetch look-ahead of the frame kernel's weight stream (ring stages)
     int max_splits = 32;
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
+    int use_mega = 1;                // batch-1 frames as ONE persistent cooperative kernel (frame_mega.cuh)
+    bool mega_supported = false;     // shape fits the frame kernel's stage geometry and it is resident at 1 CTA/SM
+    MegaPlan mega_plan{};
+    std::vector<char> mega_host;
     GemvCfg gc;
     int n_sm = 148;
     // graph cache
@@ -238,6 +253,94 @@ int splits_for(const fsb_dual_ar* h, int M) {
     return std::max(1, std::min(std::min(by_len, by_sm), h->max_splits));
 }
 
+// ------------------------------------------------------------------------------------------- op argument builders
+AttnArgs make_attn_args(const fsb_dual_ar* h, const LayerW& w, bool fast, const int32_t* pos, const int32_t* slots,
+                        int pos_fixed) {
+    const fsb_dual_ar_desc& d = h->d;
+    AttnArgs a{};
+    a.qkv = h->qkv; a.kcache = w.kc; a.vcache = w.vc; a.q_norm = w.q_norm; a.k_norm = w.k_norm;
+    a.rope = fast ? h->fast_rope : h->rope;
+    a.pos = pos; a.slots = slots; a.y = h->y; a.ws_acc = h->ws_acc; a.ws_ml = h->ws_ml;
+    a.counters = h->counters; a.H = d.n_head; a.KV = d.n_kv_head;
+    a.S = fast ? h->fkv_max_seq : h->kv_max_seq;
+    a.qk_norm = d.qk_norm; a.eps = d.norm_eps; a.scale = (float)(1.0 / std::sqrt((double)d.head_dim));
+    a.pos_fixed = pos_fixed;
+    a.splits = 1; a.fused_append = 1;
+    return a;
+}
+
+EmbedArgs make_embed_args(const fsb_dual_ar* h, const int32_t* tokens) {
+    const fsb_dual_ar_desc& d = h->d;
+    EmbedArgs e{};
+    e.tokens = tokens; e.emb = h->emb; e.cb_emb = h->cb_emb; e.x = h->x2;  // x2: layer 0 reads it as x_in
+    e.D = d.dim; e.C = d.num_codebooks; e.cb = d.codebook_size;
+    e.sem_begin = d.semantic_begin_id; e.sem_end = d.semantic_end_id; e.scale = d.scale_codebook_embeddings;
+    e.inv_div = (float)std::sqrt((double)(d.num_codebooks + 1));
+    e.pf_ptr = nullptr; e.pf_bytes = 0;
+    return e;
+}
+
+// sampling of the main (slow) token: two draws + RAS selection + code 0 (inference.py:118-155)
+SampleArgs make_slow_sample(const fsb_dual_ar* h, const fsb_frame_args& fa) {
+    const fsb_dual_ar_desc& d = h->d;
+    const int C = d.num_codebooks, V = d.vocab, cb = d.codebook_size;
+    SampleArgs sa{};
+    sa.logits = h->slow_logits; sa.ld_logits = V; sa.V = V;
+    sa.bias = (const bf16*)fa.logit_bias;
+    if (fa.restrict_scan && fa.logit_bias) {
+        // finite support of semantic_logit_bias (inference.py:308-320), ascending
+        int lo0 = d.im_end_id, hi0 = d.im_end_id + 1, lo1 = d.semantic_begin_id, hi1 = d.semantic_end_id + 1;
+        if (lo0 >= lo1 && lo0 < hi1) { lo0 = hi0 = 0; }
+        else if (lo0 > lo1) { std::swap(lo0, lo1); std::swap(hi0, hi1); }
+        sa.seg_lo[0] = lo0; sa.seg_hi[0] = hi0; sa.seg_lo[1] = lo1; sa.seg_hi[1] = hi1;
+    } else {
+        sa.seg_lo[0] = 0; sa.seg_hi[0] = V; sa.seg_lo[1] = sa.seg_hi[1] = 0;
+    }
+    sa.top_k = fa.top_k;
+    sa.n_variants = 2;
+    sa.temp[0] = fa.temperature; sa.top_p[0] = fa.top_p;
+    sa.temp[1] = 1.0f;         // RAS_HIGH_TEMP  (inference.py:50)
+    sa.top_p[1] = 0.8984375f;  // RAS_HIGH_TOP_P 0.9 as bf16 (inference.py:51, tensor built in the model dtype)
+    sa.uniforms = (const bf16*)fa.uniforms;
+    sa.u_stride = 2LL * V + (long long)(C - 1) * cb;
+    sa.u_offset = 0;
+    sa.seed = fa.seed; sa.frame_counter = fa.frame_counter; sa.draw_id = 0;
+    sa.mode = 1; sa.tokens = fa.cur_tokens; sa.out_col = 0; sa.n_cols = C + 1;
+    sa.ras_window = fa.ras_window;
+    sa.sem_begin = d.semantic_begin_id; sa.sem_end = d.semantic_end_id; sa.im_end = d.im_end_id;
+    sa.codebook_size = cb; sa.done = fa.done;
+    sa.fast_emb = h->fast_emb; sa.xfast = h->xfast; sa.D = d.dim;
+    return sa;
+}
+
+// sampling of codebook i (1 <= i < C) from the fast logits (inference.py:157-176)
+SampleArgs make_fast_sample(const fsb_dual_ar* h, const fsb_frame_args& fa, int i) {
+    const fsb_dual_ar_desc& d = h->d;
+    const int C = d.num_codebooks, V = d.vocab, cb = d.codebook_size;
+    SampleArgs fs{};
+    fs.logits = h->fast_logits + (size_t)i * h->R * cb; fs.ld_logits = cb; fs.V = cb;
+    fs.bias = nullptr;
+    fs.seg_lo[0] = 0; fs.seg_hi[0] = cb; fs.seg_lo[1] = fs.seg_hi[1] = 0;
+    fs.top_k = fa.top_k; fs.n_variants = 1;
+    fs.temp[0] = fa.temperature; fs.top_p[0] = fa.top_p; fs.temp[1] = 1.f; fs.top_p[1] = 1.f;
+    fs.uniforms = (const bf16*)fa.uniforms;
+    fs.u_stride = 2LL * V + (long long)(C - 1) * cb; fs.u_offset = 2LL * V + (long long)(i - 1) * cb;
+    fs.seed = fa.seed; fs.frame_counter = fa.frame_counter; fs.draw_id = i;
+    fs.mode = 0; fs.tokens = fa.cur_tokens; fs.out_col = i + 1; fs.n_cols = C + 1;
+    fs.ras_window = nullptr;
+    fs.sem_begin = d.semantic_begin_id; fs.sem_end = d.semantic_end_id; fs.im_end = d.im_end_id;
+    fs.codebook_size = cb; fs.done = nullptr;
+    fs.fast_emb = (i + 1 < C) ? h->fast_emb : nullptr; fs.xfast = h->xfast; fs.D = d.dim;
+    return fs;
+}
+
+FrameEndArgs make_frame_end(const fsb_dual_ar* h, const fsb_frame_args& fa) {
+    FrameEndArgs fe{};
+    fe.tokens = fa.cur_tokens; fe.pos = fa.pos; fe.ras_window = fa.ras_window; fe.out_tokens = fa.out_tokens;
+    fe.frame_counter = fa.frame_counter; fe.B = fa.batch; fe.n_cols = h->d.num_codebooks + 1; fe.max_frames = fa.max_frames;
+    return fe;
+}
+
 // ------------------------------------------------------------------------------------------- the passes
 // transformer layers over M rows. x_in: [M][D] input (not modified); result in h->x (slow) / h->xf (fast)
 int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_in, const int32_t* pos,
@@ -259,14 +362,7 @@ int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_i
             return fail(h, "unbound weights / kv cache in layer " + std::to_string(l));
         CK(run_gemv(h->gc, pdl, s, M, QKV, D, PRO_RMSNORM, EPI_STORE, w.wqkv, nullptr, cur,
                     w.attn_norm, nullptr, h->qkv, nullptr, d.norm_eps, nullptr, 0));
-        AttnArgs a{};
-        a.qkv = h->qkv; a.kcache = w.kc; a.vcache = w.vc; a.q_norm = w.q_norm; a.k_norm = w.k_norm;
-        a.rope = fast ? h->fast_rope : h->rope;
-        a.pos = pos; a.slots = slots; a.y = h->y; a.ws_acc = h->ws_acc; a.ws_ml = h->ws_ml;
-        a.counters = h->counters; a.H = H; a.KV = KV;
-        a.S = fast ? h->fkv_max_seq : h->kv_max_seq;
-        a.qk_norm = d.qk_norm; a.eps = d.norm_eps; a.scale = (float)(1.0 / std::sqrt((double)HD));
-        a.pos_fixed = pos_fixed;
+        AttnArgs a = make_attn_args(h, w, fast, pos, slots, pos_fixed);
         a.pf_ptr = w.wo; a.pf_bytes = (size_t)D * H * HD * sizeof(bf16);
         if (fast) {
             CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
@@ -294,12 +390,8 @@ int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_i
 int run_embed(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens) {
     const fsb_dual_ar_desc& d = h->d;
     if (!h->emb || !h->cb_emb) return fail(h, "embeddings not bound");
-    EmbedArgs e{};
-    e.tokens = tokens; e.emb = h->emb; e.cb_emb = h->cb_emb; e.x = h->x2;  // x2: layer 0 reads it as x_in
-    e.D = d.dim; e.C = d.num_codebooks; e.cb = d.codebook_size;
-    e.sem_begin = d.semantic_begin_id; e.sem_end = d.semantic_end_id; e.scale = d.scale_codebook_embeddings;
-    e.inv_div = (float)std::sqrt((double)(d.num_codebooks + 1));
-    e.pf_ptr = nullptr; e.pf_bytes = 0;
+    (void)d;
+    EmbedArgs e = make_embed_args(h, tokens);
     CK(launch(embed_kernel, dim3(M), dim3(256), 0, s, h->use_pdl != 0, e));
     return 0;
 }
@@ -339,32 +431,7 @@ int enqueue_frame(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     const bool pdl = h->use_pdl != 0;
     if (int r = run_slow_step(h, s, B, fa.cur_tokens, fa.pos, fa.slots)) return r;
 
-    SampleArgs sa{};
-    sa.logits = h->slow_logits; sa.ld_logits = V; sa.V = V;
-    sa.bias = (const bf16*)fa.logit_bias;
-    if (fa.restrict_scan && fa.logit_bias) {
-        // finite support of semantic_logit_bias (inference.py:308-320), ascending
-        int lo0 = d.im_end_id, hi0 = d.im_end_id + 1, lo1 = d.semantic_begin_id, hi1 = d.semantic_end_id + 1;
-        if (lo0 >= lo1 && lo0 < hi1) { lo0 = hi0 = 0; }
-        else if (lo0 > lo1) { std::swap(lo0, lo1); std::swap(hi0, hi1); }
-        sa.seg_lo[0] = lo0; sa.seg_hi[0] = hi0; sa.seg_lo[1] = lo1; sa.seg_hi[1] = hi1;
-    } else {
-        sa.seg_lo[0] = 0; sa.seg_hi[0] = V; sa.seg_lo[1] = sa.seg_hi[1] = 0;
-    }
-    sa.top_k = fa.top_k;
-    sa.n_variants = 2;
-    sa.temp[0] = fa.temperature; sa.top_p[0] = fa.top_p;
-    sa.temp[1] = 1.0f;       // RAS_HIGH_TEMP  (inference.py:50)
-    sa.top_p[1] = 0.8984375f;  // RAS_HIGH_TOP_P 0.9 as bf16 (inference.py:51, tensor built in the model dtype)
-    sa.uniforms = (const bf16*)fa.uniforms;
-    sa.u_stride = 2LL * V + (long long)(C - 1) * cb;
-    sa.u_offset = 0;
-    sa.seed = fa.seed; sa.frame_counter = fa.frame_counter; sa.draw_id = 0;
-    sa.mode = 1; sa.tokens = fa.cur_tokens; sa.out_col = 0; sa.n_cols = C + 1;
-    sa.ras_window = fa.ras_window;
-    sa.sem_begin = d.semantic_begin_id; sa.sem_end = d.semantic_end_id; sa.im_end = d.im_end_id;
-    sa.codebook_size = cb; sa.done = fa.done;
-    sa.fast_emb = h->fast_emb; sa.xfast = h->xfast; sa.D = d.dim;
+    SampleArgs sa = make_slow_sample(h, fa);
     CK(launch(sample_kernel, dim3(B), dim3(SAMPLE_THREADS), 0, s, pdl, sa));
 
     // fast AR: pass 0 on the slow hidden state (output discarded, inference.py:148-149), then C-1 sampled passes
@@ -372,28 +439,158 @@ int enqueue_frame(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     if (int r = run_fast_step(h, s, B, fin, 0, false)) return r;
     for (int i = 1; i < C; ++i) {
         if (int r = run_fast_step(h, s, B, h->xfast, i, true)) return r;
-        SampleArgs fs{};
-        fs.logits = h->fast_logits + (size_t)i * h->R * cb; fs.ld_logits = cb; fs.V = cb;
-        fs.bias = nullptr;
-        fs.seg_lo[0] = 0; fs.seg_hi[0] = cb; fs.seg_lo[1] = fs.seg_hi[1] = 0;
-        fs.top_k = fa.top_k; fs.n_variants = 1;
-        fs.temp[0] = fa.temperature; fs.top_p[0] = fa.top_p; fs.temp[1] = 1.f; fs.top_p[1] = 1.f;
-        fs.uniforms = (const bf16*)fa.uniforms;
-        fs.u_stride = sa.u_stride; fs.u_offset = 2LL * V + (long long)(i - 1) * cb;
-        fs.seed = fa.seed; fs.frame_counter = fa.frame_counter; fs.draw_id = i;
-        fs.mode = 0; fs.tokens = fa.cur_tokens; fs.out_col = i + 1; fs.n_cols = C + 1;
-        fs.ras_window = nullptr;
-        fs.sem_begin = d.semantic_begin_id; fs.sem_end = d.semantic_end_id; fs.im_end = d.im_end_id;
-        fs.codebook_size = cb; fs.done = nullptr;
-        fs.fast_emb = (i + 1 < C) ? h->fast_emb : nullptr; fs.xfast = h->xfast; fs.D = d.dim;
+        SampleArgs fs = make_fast_sample(h, fa, i);
         CK(launch(sample_kernel, dim3(B), dim3(SAMPLE_THREADS), 0, s, pdl, fs));
     }
-    FrameEndArgs fe{};
-    fe.tokens = fa.cur_tokens; fe.pos = fa.pos; fe.ras_window = fa.ras_window; fe.out_tokens = fa.out_tokens;
-    fe.frame_counter = fa.frame_counter; fe.B = B; fe.n_cols = C + 1; fe.max_frames = fa.max_frames;
+    FrameEndArgs fe = make_frame_end(h, fa);
     CK(launch(frame_end_kernel, dim3(1), dim3(64), 0, s, pdl, fe));
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------- persistent frame kernel
+typedef void (*mega_fn)(MegaPlan);
+mega_fn pick_mega(int hd, int gq) {
+    if (hd == 128 && gq == 4) return frame_mega_kernel<128, 4>;
+    if (hd == 64 && gq == 4) return frame_mega_kernel<64, 4>;
+    return nullptr;
+}
+
+// stage geometry of one GEMV inside the frame kernel: rows per stage (log2) or -1 if the shape does not fit
+int mega_rshift(int K) {
+    if (K % 8 || (size_t)K * 2 > MG_X_BYTES || (size_t)K * 2 > MG_STAGE_BYTES) return -1;
+    int rs = 3;
+    while (rs > 0 && ((size_t)K * 2 << rs) > MG_STAGE_BYTES) --rs;
+    const int segw = rs >= 2 ? 1 : (4 >> rs);  // warps of a group sharing one row
+    const int cpw = (K / 8 + segw - 1) / segw;
+    return cpw <= 32 * MG_CPL ? rs : -1;
+}
+
+bool mega_shape_ok(const fsb_dual_ar_desc& d) {
+    return pick_mega(d.head_dim, d.n_head / d.n_kv_head) != nullptr && mega_rshift(d.dim) >= 0 &&
+           mega_rshift(d.n_head * d.head_dim) >= 0 && mega_rshift(d.ffn) >= 0;
+}
+
+struct MegaBuilder {
+    std::vector<MegaOp> ops;
+    std::vector<MegaGemv> gemv;
+    std::vector<AttnArgs> attn;
+    std::vector<SampleArgs> samp;
+    void op(int type, int idx, int sync) { ops.push_back(MegaOp{type, idx, sync, 0}); }
+    void add_gemv(int N, int K, int pro, int epi, const bf16* W, const bf16* W2, const bf16* x, const bf16* norm_w,
+                  const bf16* res, bf16* out, bf16* xnorm_out, float eps) {
+        MegaGemv g{};
+        g.W = W; g.W2 = W2; g.x = x; g.norm_w = norm_w; g.res = res; g.out = out; g.xnorm_out = xnorm_out;
+        g.N = N; g.K = K; g.pro = pro; g.epi = epi; g.eps = eps; g.rshift = mega_rshift(K);
+        gemv.push_back(g);
+        op(MOP_GEMV, (int)gemv.size() - 1, MSYNC_GRID);
+    }
+    void add_layers(const fsb_dual_ar* h, bool fast, const bf16* x_in, const int32_t* pos, const int32_t* slots,
+                    int pos_fixed, int splits) {
+        const fsb_dual_ar_desc& d = h->d;
+        const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn, QKV = (H + 2 * KV) * HD;
+        const std::vector<LayerW>& L = fast ? h->fast : h->slow;
+        bf16* xa = fast ? h->xf : h->x;
+        bf16* xb = fast ? h->xf2 : h->x2;
+        const bf16* cur = x_in;
+        for (const LayerW& w : L) {
+            add_gemv(QKV, D, PRO_RMSNORM, EPI_STORE, w.wqkv, nullptr, cur, w.attn_norm, nullptr, h->qkv, nullptr, d.norm_eps);
+            AttnArgs a = make_attn_args(h, w, fast, pos, slots, pos_fixed);
+            a.splits = fast ? 1 : splits;
+            attn.push_back(a);
+            op(fast ? MOP_FATTN : MOP_ATTN, (int)attn.size() - 1, MSYNC_GRID);
+            add_gemv(D, H * HD, PRO_NONE, EPI_RESIDUAL, w.wo, nullptr, h->y, nullptr, cur, xb, nullptr, d.norm_eps);
+            add_gemv(F, D, PRO_RMSNORM, EPI_SWIGLU, w.w1, w.w3, xb, w.ffn_norm, nullptr, h->ff, nullptr, d.norm_eps);
+            add_gemv(D, F, PRO_NONE, EPI_RESIDUAL, w.w2, nullptr, h->ff, nullptr, xb, xa, nullptr, d.norm_eps);
+            cur = xa;
+        }
+    }
+};
+
+int check_bound(fsb_dual_ar* h) {
+    const fsb_dual_ar_desc& d = h->d;
+    for (int f = 0; f < 2; ++f) {
+        const std::vector<LayerW>& L = f ? h->fast : h->slow;
+        for (size_t l = 0; l < L.size(); ++l) {
+            const LayerW& w = L[l];
+            if (!w.wqkv || !w.wo || !w.w1 || !w.w2 || !w.w3 || !w.attn_norm || !w.ffn_norm || !w.kc || !w.vc)
+                return fail(h, std::string("unbound weights / kv cache in ") + (f ? "fast " : "") + "layer " + std::to_string(l));
+        }
+    }
+    if (!h->emb || !h->cb_emb) return fail(h, "embeddings not bound");
+    if (!(d.tie_word_embeddings ? h->emb : h->out_w) || !h->norm) return fail(h, "LM head / final norm not bound");
+    if (!h->fast_out || !h->fast_norm) return fail(h, "fast head not bound");
+    return 0;
+}
+
+// op list of one batch-1 frame, in the order enqueue_frame launches the same work; uploaded on `s` (stream-ordered
+// after earlier launches that still read the previous plan)
+int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
+    const fsb_dual_ar_desc& d = h->d;
+    if (int r = check_bound(h)) return r;
+    const int C = d.num_codebooks;
+    MegaBuilder mb;
+    mb.op(MOP_EMBED, 0, MSYNC_GRID);
+    int splits = h->attn_splits > 0 ? h->attn_splits : std::max(1, h->n_sm / d.n_kv_head);
+    splits = std::max(1, std::min(splits, h->max_splits));
+    mb.add_layers(h, false, h->x2, fa.pos, fa.slots, -1, splits);
+    const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
+    mb.add_gemv(d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head, nullptr, h->x, h->norm, nullptr, h->slow_logits, h->hidden,
+                d.norm_eps);
+    mb.samp.push_back(make_slow_sample(h, fa));
+    mb.op(MOP_SAMPLE, 0, MSYNC_GRID);
+    const bf16* fin = d.norm_fastlayer_input ? h->hidden : h->x;
+    mb.add_layers(h, true, fin, nullptr, nullptr, 0, 1);
+    for (int i = 1; i < C; ++i) {
+        mb.add_layers(h, true, h->xfast, nullptr, nullptr, i, 1);
+        mb.add_gemv(d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE, h->fast_out, nullptr, h->xf, h->fast_norm, nullptr,
+                    h->fast_logits + (size_t)i * h->R * d.codebook_size, nullptr, d.norm_eps);
+        mb.samp.push_back(make_fast_sample(h, fa, i));
+        mb.op(MOP_SAMPLE, (int)mb.samp.size() - 1, i + 1 < C ? MSYNC_GRID : MSYNC_CTA);  // last: only CTA 0 follows
+    }
+    mb.op(MOP_END, 0, MSYNC_NONE);
+    const EmbedArgs emb = make_embed_args(h, fa.cur_tokens);
+    const FrameEndArgs fend = make_frame_end(h, fa);
+
+    // pack: [ops][gemv][attn][samp][embed][fend], each 16-byte aligned
+    size_t off = 0;
+    auto place = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 16); return o; };
+    const size_t o_ops = place(mb.ops.size() * sizeof(MegaOp)), o_g = place(mb.gemv.size() * sizeof(MegaGemv)),
+                 o_a = place(mb.attn.size() * sizeof(AttnArgs)), o_s = place(mb.samp.size() * sizeof(SampleArgs)),
+                 o_e = place(sizeof(EmbedArgs)), o_f = place(sizeof(FrameEndArgs));
+    if (off > MEGA_BUF_BYTES) return fail(h, "frame op list exceeds its device buffer");
+    h->mega_host.assign(off, 0);
+    char* hp = h->mega_host.data();
+    memcpy(hp + o_ops, mb.ops.data(), mb.ops.size() * sizeof(MegaOp));
+    memcpy(hp + o_g, mb.gemv.data(), mb.gemv.size() * sizeof(MegaGemv));
+    memcpy(hp + o_a, mb.attn.data(), mb.attn.size() * sizeof(AttnArgs));
+    memcpy(hp + o_s, mb.samp.data(), mb.samp.size() * sizeof(SampleArgs));
+    memcpy(hp + o_e, &emb, sizeof(EmbedArgs));
+    memcpy(hp + o_f, &fend, sizeof(FrameEndArgs));
+    CK(cudaMemcpyAsync(h->mega_buf, hp, off, cudaMemcpyHostToDevice, s));
+    MegaPlan& p = h->mega_plan;
+    p.ops = (const MegaOp*)(h->mega_buf + o_ops); p.n_ops = (int)mb.ops.size(); p.B = 1;
+    p.gemv = (const MegaGemv*)(h->mega_buf + o_g); p.attn = (const AttnArgs*)(h->mega_buf + o_a);
+    p.samp = (const SampleArgs*)(h->mega_buf + o_s); p.embed = (const EmbedArgs*)(h->mega_buf + o_e);
+    p.fend = (const FrameEndArgs*)(h->mega_buf + o_f); p.sync = h->mega_sync;
+    p.prof = h->mega_prof_on ? h->mega_prof : nullptr;
+    p.pf_stages = h->mega_pf_stages;
+    p.trace = (h->mega_trace_on && (size_t)h->n_sm * mb.ops.size() * 4 <= MEGA_TRACE_WORDS) ? h->mega_trace : nullptr;
+    p.copy_bytes = std::max(1024, h->mega_copy_bytes) & ~15;
+    return 0;
+}
+
+int launch_mega(fsb_dual_ar* h, cudaStream_t s) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(h->n_sm); cfg.blockDim = dim3(MG_THREADS); cfg.dynamicSmemBytes = MG_SMEM; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident: the in-kernel grid barrier depends on it
+    at[0].val.cooperative = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, pick_mega(h->d.head_dim, h->d.n_head / h->d.n_kv_head), h->mega_plan));
+    return 0;
+}
+
+bool mega_active(const fsb_dual_ar* h, int batch) { return h->use_mega && h->mega_supported && batch == 1; }
 
 __global__ void fill_prefill_kernel(int32_t* pos, int32_t* slot, int n, int pos0, int slot_v) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -425,6 +622,8 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
     T(ws_acc, float, R * d.n_kv_head * max_splits * gq * d.head_dim)
     T(ws_ml, float, R * d.n_kv_head * max_splits * gq * 2)
     T(counters, int32_t, R * d.n_kv_head)
+    T(mega_buf, char, MEGA_BUF_BYTES) T(mega_sync, unsigned, 64) T(mega_prof, unsigned long long, 16)
+    T(mega_trace, unsigned long long, MEGA_TRACE_WORDS)
     T(pf_pos, int32_t, (size_t)max_seq_len + 8) T(pf_slot, int32_t, (size_t)max_seq_len + 8)
 #undef T
     *total = off;
@@ -463,6 +662,19 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
     CK(set_gemv_attrs());
     CK(set_gemv_tma_attrs());
     CK(cudaMemset(h->counters, 0, (size_t)std::max(d.max_rows, 8) * d.n_kv_head * sizeof(int32_t)));
+    CK(cudaMemset(h->mega_sync, 0, 64 * sizeof(unsigned)));
+    CK(cudaMemset(h->mega_prof, 0, 16 * sizeof(unsigned long long)));
+    if (mega_shape_ok(d)) {
+        mega_fn mf = pick_mega(d.head_dim, d.n_head / d.n_kv_head);
+        int coop = 0, occ = 0;
+        CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+        CK(cudaFuncSetAttribute((const void*)mf, cudaFuncAttributeMaxDynamicSharedMemorySize, MG_SMEM));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)mf, MG_THREADS, MG_SMEM));
+        h->mega_supported = coop && occ >= 1;
+    }
+    if (const char* e = getenv("FSB_MEGA")) h->use_mega = atoi(e);
+    if (const char* e = getenv("FSB_MEGA_PF")) h->mega_pf_stages = atoi(e);
+    if (const char* e = getenv("FSB_MEGA_COPY")) h->mega_copy_bytes = atoi(e);
     h->slow.resize(d.n_layer);
     h->fast.resize(d.n_fast_layer);
     if (const char* e = getenv("FSB_PDL")) h->use_pdl = atoi(e);
@@ -496,6 +708,11 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "gemv_ctas_per_sm") h->gc.ctas_per_sm = (int)value;
     else if (n == "gemv_stage_kb") h->gc.stage_kb = (int)value;
     else if (n == "attn_splits") h->attn_splits = (int)value;
+    else if (n == "mega") h->use_mega = (int)value;
+    else if (n == "mega_prof") h->mega_prof_on = (int)value;
+    else if (n == "mega_trace") h->mega_trace_on = (int)value;
+    else if (n == "mega_pf_stages") h->mega_pf_stages = (int)value;
+    else if (n == "mega_copy_bytes") h->mega_copy_bytes = (int)value;
     else return fail(h, "unknown option " + n);
     h->cached_valid = false;
     return 0;
@@ -624,6 +841,9 @@ int fsb_dual_ar_buffer(fsb_dual_ar* h, const char* name, void** dptr, size_t* by
     else if (n == "fast_logits") { *dptr = h->fast_logits; *bytes = (size_t)d.num_codebooks * R * d.codebook_size * 2; }
     else if (n == "x") { *dptr = h->x; *bytes = R * d.dim * 2; }
     else if (n == "xfast") { *dptr = h->xfast; *bytes = R * d.dim * 2; }
+    else if (n == "mega_prof") { *dptr = h->mega_prof; *bytes = 16 * sizeof(unsigned long long); }
+    else if (n == "mega_trace") { *dptr = h->mega_trace; *bytes = MEGA_TRACE_WORDS * sizeof(unsigned long long); }
+    else if (n == "mega_plan") { *dptr = h->mega_buf; *bytes = MEGA_BUF_BYTES; }
     else return fail(h, "unknown buffer " + n);
     return 0;
 }
@@ -635,17 +855,26 @@ int fsb_dual_ar_decode_frames(fsb_dual_ar* h, const fsb_frame_args* args, int32_
     if (args->top_k < 1 || args->top_k > SAMPLE_MAXK) return fail(h, "top_k must be in [1, 64]");
     if (!h->fast_emb) return fail(h, "fast_embeddings not bound");
     cudaStream_t s = (cudaStream_t)stream;
+    const bool mega = mega_active(h, args->batch);
+    const bool fresh = !h->cached_valid || memcmp(&h->cached, args, sizeof(fsb_frame_args)) != 0;
+    if (mega && fresh) {
+        if (int r = build_mega_plan(h, s, *args)) return r;
+        if (!h->use_graph) {  // the plan is the cache in this mode
+            memcpy(&h->cached, args, sizeof(fsb_frame_args));
+            h->cached_valid = true;
+        }
+    }
     if (!h->use_graph) {
         for (int i = 0; i < n_frames; ++i)
-            if (int r = enqueue_frame(h, s, *args)) return r;
+            if (int r = mega ? launch_mega(h, s) : enqueue_frame(h, s, *args)) return r;
         return 0;
     }
-    if (!h->cached_valid || memcmp(&h->cached, args, sizeof(fsb_frame_args)) != 0) {
+    if (fresh || !h->exec) {
         if (h->exec) { cudaGraphExecDestroy(h->exec); h->exec = nullptr; }
         cudaGraph_t g = nullptr;
         if (!h->cap_stream) CK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
         CK(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
-        int r = enqueue_frame(h, h->cap_stream, *args);
+        int r = mega ? launch_mega(h, h->cap_stream) : enqueue_frame(h, h->cap_stream, *args);
         cudaError_t e = cudaStreamEndCapture(h->cap_stream, &g);
         if (r) { if (g) cudaGraphDestroy(g); return r; }
         if (e != cudaSuccess) return fail(h, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
@@ -674,6 +903,7 @@ double fsb_dual_ar_frame_bytes(const fsb_dual_ar* h, int32_t batch, int64_t ctx_
 int32_t fsb_dual_ar_launches_per_frame(const fsb_dual_ar* h, int32_t batch) {
     if (!h) return 0;
     const fsb_dual_ar_desc& d = h->d;
+    if (mega_active(h, batch)) return 1;  // the whole frame is one persistent kernel
     const int passes = (batch + 7) / 8;  // GEMV passes of <= 8 rows
     const int per_layer = 4 * passes + 1;
     const int C = d.num_codebooks;

@@ -70,21 +70,20 @@ __device__ __forceinline__ uint32_t philox_u32(unsigned long long seed, uint32_t
 }
 
 // visit every scanned element: f(index, bf16 bits of logit(+bias))
-template <typename F>
-__device__ __forceinline__ void sample_scan(const SampleArgs& a, const bf16* lg, F f) {
-    const int tid = threadIdx.x;
+template <int NT, typename F>
+__device__ __forceinline__ void sample_scan(const SampleArgs& a, const bf16* lg, int tid, F f) {
     for (int s = 0; s < 2; ++s) {
         const int lo = a.seg_lo[s], hi = a.seg_hi[s];
         if (hi <= lo) continue;
         const int alo = min(hi, (lo + 7) & ~7), ahi = max(alo, hi & ~7);
-        for (int i = lo + tid; i < alo; i += SAMPLE_THREADS) {  // unaligned head
-            float v = __bfloat162float(lg[i]);
+        for (int i = lo + tid; i < alo; i += NT) {  // unaligned head
+            float v = lda(&lg[i]);
             if (a.bias) v = rbf(v + __bfloat162float(a.bias[i]));
             f(i, f_to_bf16_bits(v));
         }
-        for (int c = (alo >> 3) + tid; c < (ahi >> 3); c += SAMPLE_THREADS) {  // 128-bit body
+        for (int c = (alo >> 3) + tid; c < (ahi >> 3); c += NT) {  // 128-bit body
             float v[8];
-            unpack8(reinterpret_cast<const uint4*>(lg)[c], v);
+            unpack8(lda(&reinterpret_cast<const uint4*>(lg)[c]), v);
             if (a.bias) {
                 float bb[8];
                 unpack8(reinterpret_cast<const uint4*>(a.bias)[c], bb);
@@ -94,29 +93,30 @@ __device__ __forceinline__ void sample_scan(const SampleArgs& a, const bf16* lg,
 #pragma unroll
             for (int i = 0; i < 8; ++i) f(c * 8 + i, f_to_bf16_bits(v[i]));
         }
-        for (int i = ahi + tid; i < hi; i += SAMPLE_THREADS) {  // tail
+        for (int i = ahi + tid; i < hi; i += NT) {  // tail
             if (i < alo) continue;
-            float v = __bfloat162float(lg[i]);
+            float v = lda(&lg[i]);
             if (a.bias) v = rbf(v + __bfloat162float(a.bias[i]));
             f(i, f_to_bf16_bits(v));
         }
     }
 }
 
-// block-wide exclusive prefix sum of one int per thread (1024 threads); returns exclusive prefix, total in *total
-__device__ __forceinline__ int block_excl_scan(int v, int* wsum, int* total) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+// group-wide exclusive prefix sum of one int per thread (SY::NT threads); returns exclusive prefix, total in *total
+template <class SY>
+__device__ __forceinline__ int block_excl_scan(int v, int* wsum, int* total, int tid) {
+    const int lane = tid & 31, w = tid >> 5;
     int inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += t;
     }
-    __syncthreads();
+    SY::sync();
     if (lane == 31) wsum[w] = inc;
-    __syncthreads();
+    SY::sync();
     if (w == 0) {
-        int s = wsum[lane];
+        int s = (lane < SY::NT / 32) ? wsum[lane] : 0;
         int si = s;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -126,12 +126,15 @@ __device__ __forceinline__ int block_excl_scan(int v, int* wsum, int* total) {
         wsum[lane] = si - s;  // exclusive warp offsets
         if (lane == 31) wsum[32] = si;
     }
-    __syncthreads();
+    SY::sync();
     *total = wsum[32];
     return wsum[w] + inc - v;
 }
 
-__global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a) {
+// one request (row b of nB) on SY::NT threads; tid = index inside the group
+template <class SY>
+__device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, int tid) {
+    constexpr int NT = SY::NT;
     __shared__ uint32_t hist[2048];
     __shared__ unsigned long long cand[SAMPLE_CAND_CAP];
     __shared__ unsigned long long top[SAMPLE_MAXK];
@@ -141,19 +144,16 @@ __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a)
     __shared__ float probs[SAMPLE_MAXK], cums[SAMPLE_MAXK];
     __shared__ int sh_tok[2];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int b = blockIdx.x;
-    pdl_wait();
-    pdl_launch_dependents();
+    const int lane = tid & 31, warp = tid >> 5;
     const bf16* lg = a.logits + (size_t)b * a.ld_logits;
 
     // ---- pass A: 11-bit histogram of the order key over finite entries, running max
-    for (int i = tid; i < 2048; i += SAMPLE_THREADS) hist[i] = 0;
+    for (int i = tid; i < 2048; i += NT) hist[i] = 0;
     if (tid < 8) sh_i[tid] = 0;
-    __syncthreads();
+    SY::sync();
     uint32_t kmax = 0;
     int nfin = 0;
-    sample_scan(a, lg, [&](int, uint16_t bits) {
+    sample_scan<NT>(a, lg, tid, [&](int, uint16_t bits) {
         if (bits != 0xFF80u) {
             const uint32_t k = order_key(bits);
             atomicAdd(&hist[k >> 5], 1u);
@@ -163,11 +163,11 @@ __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a)
     });
     kmax = __reduce_max_sync(0xffffffffu, kmax);
     if (lane == 0) wsum[warp] = (int)kmax;
-    __syncthreads();
-    kmax = (uint32_t)wsum[lane];
+    SY::sync();
+    kmax = (lane < NT / 32) ? (uint32_t)wsum[lane] : 0u;
     kmax = __reduce_max_sync(0xffffffffu, kmax);
     int nfin_total;
-    block_excl_scan(nfin, wsum, &nfin_total);
+    block_excl_scan<SY>(nfin, wsum, &nfin_total, tid);
     const int k_eff = min(min(a.top_k, SAMPLE_MAXK), nfin_total);
     if (k_eff <= 0) {  // no finite logit at all: nothing sensible to sample
         if (tid == 0 && a.tokens) a.tokens[(size_t)b * a.n_cols + a.out_col] = 0;
@@ -177,30 +177,36 @@ __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a)
 
     // ---- locate the 11-bit bin holding the k-th largest key (suffix scan from the top bin)
     {
-        const int bh = 2047 - 2 * tid, bl = bh - 1;
-        const int ch = (int)hist[bh], cl = (int)hist[bl];
+        constexpr int BPT = 2048 / NT;  // bins per thread, highest bins first
+        const int bh = 2047 - BPT * tid;
+        int cnt[BPT], sum = 0;
+#pragma unroll
+        for (int j = 0; j < BPT; ++j) { cnt[j] = (int)hist[bh - j]; sum += cnt[j]; }
         int tot;
-        const int ex = block_excl_scan(ch + cl, wsum, &tot);
-        if (ex < k_eff && k_eff <= ex + ch) { sh_i[0] = bh; sh_i[1] = ex; }
-        else if (ex + ch < k_eff && k_eff <= ex + ch + cl) { sh_i[0] = bl; sh_i[1] = ex + ch; }
+        int cum = block_excl_scan<SY>(sum, wsum, &tot, tid);
+#pragma unroll
+        for (int j = 0; j < BPT; ++j) {
+            if (cum < k_eff && k_eff <= cum + cnt[j]) { sh_i[0] = bh - j; sh_i[1] = cum; }
+            cum += cnt[j];
+        }
     }
-    __syncthreads();
+    SY::sync();
     const int bin1 = sh_i[0], above1 = sh_i[1];
-    __syncthreads();
+    SY::sync();
 
     // ---- pass B: 5-bit histogram inside that bin + softmax denominator over everything
     if (tid < 32) hist[tid] = 0;
-    __syncthreads();
+    SY::sync();
     float den = 0.f;
-    sample_scan(a, lg, [&](int, uint16_t bits) {
+    sample_scan<NT>(a, lg, tid, [&](int, uint16_t bits) {
         if (bits != 0xFF80u) {
             const uint32_t k = order_key(bits);
             if ((int)(k >> 5) == bin1) atomicAdd(&hist[k & 31], 1u);
             den += expf(bf16_bits_to_f(bits) - maxv);
         }
     });
-    den = block_sum(den, red);
-    __syncthreads();
+    den = group_sum<SY>(den, red, tid);
+    SY::sync();
     if (tid == 0) {
         int cum = above1, b2 = 31;
         for (; b2 >= 0; --b2) {
@@ -213,14 +219,14 @@ __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a)
         sh_i[5] = 0;                 // candidate counter
         sh_i[6] = 0;                 // ordered-tie counter
     }
-    __syncthreads();
+    SY::sync();
     const uint32_t tkey = (uint32_t)sh_i[2];
     const int n_gt = sh_i[3], n_eq = sh_i[4];
     const int need_eq = k_eff - n_gt;
     const bool small = (n_gt + n_eq) <= SAMPLE_CAND_CAP;
 
     // ---- pass C: collect candidates (composite = key << 32 | ~index: larger is earlier in sort order)
-    sample_scan(a, lg, [&](int i, uint16_t bits) {
+    sample_scan<NT>(a, lg, tid, [&](int i, uint16_t bits) {
         if (bits != 0xFF80u) {
             const uint32_t k = order_key(bits);
             if (k > tkey || (small && k == tkey)) {
@@ -229,40 +235,40 @@ __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a)
             }
         }
     });
-    __syncthreads();
+    SY::sync();
     if (!small) {
         // massive tie at the threshold: take the `need_eq` lowest indices in index order
         int taken = 0;
         for (int s = 0; s < 2 && taken < need_eq; ++s) {
-            for (int base = a.seg_lo[s]; base < a.seg_hi[s] && taken < need_eq; base += SAMPLE_THREADS) {
+            for (int base = a.seg_lo[s]; base < a.seg_hi[s] && taken < need_eq; base += NT) {
                 const int i = base + tid;
                 int eq = 0;
                 if (i < a.seg_hi[s]) {
-                    float v = __bfloat162float(lg[i]);
+                    float v = lda(&lg[i]);
                     if (a.bias) v = rbf(v + __bfloat162float(a.bias[i]));
                     const uint16_t bits = f_to_bf16_bits(v);
                     eq = (bits != 0xFF80u && order_key(bits) == tkey) ? 1 : 0;
                 }
                 int tot;
-                const int ex = block_excl_scan(eq, wsum, &tot);
+                const int ex = block_excl_scan<SY>(eq, wsum, &tot, tid);
                 if (eq && taken + ex < need_eq)
                     cand[n_gt + taken + ex] = ((unsigned long long)tkey << 32) | (uint32_t)(~(uint32_t)i);
                 taken += tot;
-                __syncthreads();
+                SY::sync();
             }
         }
     }
-    __syncthreads();
+    SY::sync();
     const int n_cand = small ? sh_i[5] : k_eff;
 
     // ---- rank by counting (composites are unique), keep the first k_eff
-    if (tid < n_cand) {
-        const unsigned long long me = cand[tid];
+    for (int c = tid; c < n_cand; c += NT) {
+        const unsigned long long me = cand[c];
         int rank = 0;
         for (int j = 0; j < n_cand; ++j) rank += (cand[j] > me) ? 1 : 0;
         if (rank < k_eff) top[rank] = me;
     }
-    __syncthreads();
+    SY::sync();
     if (warp != 0) return;
 
     // ---- warp 0: the <= 64 survivors
@@ -315,7 +321,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a)
             const float p = rbf(__fdiv_rn(e2[s], s2));
             float u;
             if (a.uniforms) {
-                u = __bfloat162float(a.uniforms[((size_t)fr * gridDim.x + b) * a.u_stride + a.u_offset +
+                u = __bfloat162float(a.uniforms[((size_t)fr * nB + b) * a.u_stride + a.u_offset +
                                                 (size_t)v * a.V + idx[s]]);
             } else {
                 const uint32_t r = philox_u32(a.seed, (uint32_t)idx[s], (uint32_t)(a.draw_id * 2 + v), (uint32_t)fr,
@@ -371,6 +377,11 @@ __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a)
         for (int c = lane; c < (a.D >> 3); c += 32) dst[c] = src[c];
     }
 }
+__global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a) {
+    pdl_wait();
+    pdl_launch_dependents();
+    sample_body<SyncBlock<SAMPLE_THREADS>>(a, blockIdx.x, gridDim.x, threadIdx.x);
+}
 
 // ----------------------------------------------------------------------------- frame epilogue (decode_n_tokens bookkeeping)
 struct FrameEndArgs {
@@ -382,21 +393,25 @@ struct FrameEndArgs {
     int B, n_cols, max_frames;
 };
 // inference.py:224-230: input_pos += 1; previous_tokens.roll(-1); previous_tokens[:, -1] = next_token
-__global__ void frame_end_kernel(FrameEndArgs a) {
-    pdl_wait();
-    pdl_launch_dependents();
+template <class SY>
+__device__ __forceinline__ void frame_end_body(const FrameEndArgs& a, int tid) {
     const int fr = *a.frame_counter;
-    for (int b = threadIdx.x; b < a.B; b += blockDim.x) {
+    for (int b = tid; b < a.B; b += SY::NT) {
         a.pos[b] += 1;
         if (a.ras_window) {
             int32_t* w = a.ras_window + (size_t)b * RAS_WIN;
             for (int i = 0; i + 1 < RAS_WIN; ++i) w[i] = w[i + 1];
-            w[RAS_WIN - 1] = a.tokens[(size_t)b * a.n_cols];
+            w[RAS_WIN - 1] = lda(&a.tokens[(size_t)b * a.n_cols]);
         }
         if (a.out_tokens && fr < a.max_frames)
             for (int c = 0; c < a.n_cols; ++c)
-                a.out_tokens[((size_t)fr * a.B + b) * a.n_cols + c] = a.tokens[(size_t)b * a.n_cols + c];
+                a.out_tokens[((size_t)fr * a.B + b) * a.n_cols + c] = lda(&a.tokens[(size_t)b * a.n_cols + c]);
     }
-    __syncthreads();
-    if (threadIdx.x == 0) *a.frame_counter = fr + 1;
+    SY::sync();
+    if (tid == 0) *a.frame_counter = fr + 1;
+}
+__global__ void __launch_bounds__(64) frame_end_kernel(FrameEndArgs a) {
+    pdl_wait();
+    pdl_launch_dependents();
+    frame_end_body<SyncBlock<64>>(a, threadIdx.x);
 }

@@ -109,10 +109,58 @@ def test_sampled_free_run_vs_golden():
     assert first_bad >= 1  # frame 0 (prompt pass + full sampling chain) must match exactly
 
 
-def test_execution_modes_are_bit_identical(tiny):
-    """graph replay vs eager launches, PDL on/off, restricted vs full-vocabulary sampling scan: same tokens."""
+def _one_frame(m, g, k, **opts):
+    """Prompt pass over the golden sequence up to frame k, then ONE fused frame through fsb_dual_ar_decode_frames;
+    returns (slow logits, fast logits [C-1, cb], sampled frame)."""
+    from fish_speech_b200 import dual_ar
+    cfg = m.config
+    for name, v in opts.items():
+        m.set_option(name, v)
+    T = g["prompt"].shape[1]
+    seq = g["seq"][:, : T + k]
+    bias = dual_ar.make_semantic_logit_bias(m)
+    s = g["sampling"]
+    tok = dual_ar.decode_one_token_ar(m, seq[None].cuda(), torch.arange(seq.shape[1]), s["temperature"], s["top_p"],
+                                      s["top_k"], bias)
+    torch.cuda.synchronize()
+    V, cb, C = cfg.vocab_size, cfg.codebook_size, cfg.num_codebooks
+    slow = m._buffer("slow_logits")[:V].clone().cpu()
+    fl = m._buffer("fast_logits")
+    R_ = fl.numel() // (C * cb)
+    fast = fl.view(C, R_, cb)[1:, 0].clone().cpu()
+    return slow, fast, tok.cpu()
+
+
+def test_persistent_frame_kernel_vs_kernel_chain_and_golden(tiny):
+    """The one-launch frame kernel (frame_mega.cuh) against the per-op kernel chain on identical inputs, and both
+    against the reference's logits: the two paths only differ in fp32 accumulation order."""
     g, cfg, sd, m = tiny
-    base = _run_generate(m, g, 24, graph=1, pdl=1)
+    assert m.launches_per_frame(1) == 1  # the persistent kernel is the default batch-1 path
+    for k in g["frames_kept"][:3]:
+        slow_m, fast_m, tok_m = _one_frame(m, g, k, mega=1)
+        slow_c, fast_c, tok_c = _one_frame(m, g, k, mega=0)
+        assert m.launches_per_frame(1) > 100
+        m.set_option("mega", 1)
+        _check_logits(f"frame kernel slow logits frame {k}", slow_m, g["slow_logits"][k])
+        mabs, mrel, _ = err_stats(slow_m, slow_c)
+        print(f"[parity] frame kernel vs chain, slow logits frame {k}: max-abs {mabs:.4f}")
+        assert mabs <= ABS_TOL
+        # the fast logits depend on the sampled main token / codes: comparable only while both paths drew the same
+        if torch.equal(tok_m, tok_c):
+            mabs, _, _ = err_stats(fast_m, fast_c)
+            print(f"[parity] frame kernel vs chain, fast logits frame {k}: max-abs {mabs:.4f}")
+            assert mabs <= ABS_TOL
+        assert bool((tok_m[1:] >= 0).all()) and bool((tok_m[1:] < cfg.codebook_size).all())
+
+
+def test_execution_modes_are_bit_identical(tiny):
+    """graph replay vs eager launches, PDL on/off, restricted vs full-vocabulary sampling scan: same tokens —
+    for the kernel chain (mega=0) and for the persistent frame kernel (mega=1, graph on/off)."""
+    g, cfg, sd, m = tiny
+    mega_g = _run_generate(m, g, 24, mega=1, graph=1)
+    assert torch.equal(mega_g, _run_generate(m, g, 24, mega=1, graph=0))
+    assert torch.equal(mega_g, _run_generate(m, g, 24, mega=1, graph=1))  # replay is deterministic
+    base = _run_generate(m, g, 24, mega=0, graph=1, pdl=1)
     assert torch.equal(base, _run_generate(m, g, 24, graph=0, pdl=0))
     assert torch.equal(base, _run_generate(m, g, 24, graph=0, pdl=1))
     assert torch.equal(base, _run_generate(m, g, 24, graph=1, pdl=0))
@@ -125,6 +173,7 @@ def test_execution_modes_are_bit_identical(tiny):
         assert torch.equal(base, _run_generate(m, g, 24))
     finally:
         dual_ar._bias_is_standard = real
+        m.set_option("mega", 1)
 
 
 def test_generate_errors_like_reference(tiny):
