@@ -18,12 +18,13 @@ struct EmbedArgs {
     const bf16* emb;         // [V][D]
     const bf16* cb_emb;      // [C*cb][D]
     bf16* x;                 // [M][D]
+    uint32_t* x_t;           // flag-in-data copy of x for the persistent frame kernel (written instead of x), or nullptr
     int D, C, cb, sem_begin, sem_end, scale;
     float inv_div;           // sqrt(C+1) as float (the reference divides)
     const void* pf_ptr; size_t pf_bytes;
 };
 
-__device__ __forceinline__ void embed_body(const EmbedArgs& a, int m, int tid, int nt) {
+__device__ __forceinline__ void embed_body(const EmbedArgs& a, int m, int tid, int nt, unsigned tag = 0) {
     const int32_t* t = a.tokens + (size_t)m * (a.C + 1);
     const int tok = lda(&t[0]);
     const bool sem = tok >= a.sem_begin && tok <= a.sem_end;
@@ -50,7 +51,13 @@ __device__ __forceinline__ void embed_body(const EmbedArgs& a, int m, int tid, i
         }
         uint4 o;
         o.x = pack2(e[0], e[1]); o.y = pack2(e[2], e[3]); o.z = pack2(e[4], e[5]); o.w = pack2(e[6], e[7]);
-        reinterpret_cast<uint4*>(a.x + (size_t)m * a.D)[c] = o;
+        if (a.x_t != nullptr) {
+            uint32_t* d = a.x_t + (size_t)m * a.D + (size_t)c * 8;
+            st_tagged4(d, o.x, o.y, tag);
+            st_tagged4(d + 4, o.z, o.w, tag);
+        } else {
+            reinterpret_cast<uint4*>(a.x + (size_t)m * a.D)[c] = o;
+        }
     }
 }
 __global__ void __launch_bounds__(256) embed_kernel(EmbedArgs a) {
@@ -65,14 +72,78 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedArgs a) {
 // F.rms_norm on bf16 computes x*rsqrt(mean(x^2)+eps)*w in fp32 and rounds once [probe]; RoPE multiplies
 // fp32 values with the bf16 table and rounds once (llama.py:1025-1037); products are not fused (the
 // reference issues separate mul/sub ops).
+// this lane's EPL elements of one head vector: plain bf16 (through L2) or flag-in-data words (spins until current)
+template <int HD, bool TAG>
+__device__ __forceinline__ void load_head(const bf16* src, const uint32_t* src_t, unsigned tag, float (&v)[HD / 32]) {
+    constexpr int EPL = HD / 32;
+    const int lane = threadIdx.x & 31;
+    if (TAG) {
+        if (EPL == 4) {
+            const uint2 pk = ld_tagged4(src_t + lane * 4, tag);
+            v[0] = bf16_lo(pk.x); v[1] = bf16_hi(pk.x); v[EPL - 2] = bf16_lo(pk.y); v[EPL - 1] = bf16_hi(pk.y);
+        } else {
+#pragma unroll
+            for (int i = 0; i < EPL; i += 2) {
+                const uint32_t pk = ld_tagged2(src_t + lane * EPL + i, tag);
+                v[i] = bf16_lo(pk); v[i + 1] = bf16_hi(pk);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) v[i] = lda(&src[lane * EPL + i]);
+    }
+}
+
+// norm weights and RoPE (cos, sin) of this lane's elements, fetched ahead of the data they will be applied to
 template <int HD>
-__device__ __forceinline__ void head_norm_rope(const bf16* src, const bf16* norm_w, const bf16* rope_row,
+struct HeadCoef {
+    float w[HD / 32], c[HD / 64], s[HD / 64];
+    __device__ __forceinline__ void load(const bf16* norm_w, const bf16* rope_row, bool qk_norm) {
+        constexpr int EPL = HD / 32;
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) w[i] = qk_norm ? __bfloat162float(norm_w[lane * EPL + i]) : 1.f;
+#pragma unroll
+        for (int i = 0; i < EPL; i += 2) {
+            const int pair = (lane * EPL + i) >> 1;
+            c[i >> 1] = __bfloat162float(rope_row[pair * 2 + 0]);
+            s[i >> 1] = __bfloat162float(rope_row[pair * 2 + 1]);
+        }
+    }
+};
+template <int HD>
+__device__ __forceinline__ void head_norm_rope(const float (&in)[HD / 32], const HeadCoef<HD>& k, bool qk_norm, float eps,
+                                               float (&out)[HD / 32]) {
+    constexpr int EPL = HD / 32;
+    float v[EPL];
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) v[i] = in[i];
+    if (qk_norm) {
+        float ss = 0.f;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) ss += v[i] * v[i];
+        ss = warp_sum(ss);
+        const float rs = __frsqrt_rn(__fadd_rn(__fdiv_rn(ss, (float)HD), eps));
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) v[i] = rbf(__fmul_rn(__fmul_rn(v[i], rs), k.w[i]));
+    }
+#pragma unroll
+    for (int i = 0; i < EPL; i += 2) {
+        const float c = k.c[i >> 1], s = k.s[i >> 1];
+        const float x0 = v[i], x1 = v[i + 1];
+        out[i] = rbf(__fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, s)));
+        out[i + 1] = rbf(__fadd_rn(__fmul_rn(x1, c), __fmul_rn(x0, s)));
+    }
+}
+
+template <int HD>
+__device__ __forceinline__ void head_norm_rope(const float (&in)[HD / 32], const bf16* norm_w, const bf16* rope_row,
                                                bool qk_norm, float eps, float (&out)[HD / 32]) {
     constexpr int EPL = HD / 32;
     const int lane = threadIdx.x & 31;
     float v[EPL];
 #pragma unroll
-    for (int i = 0; i < EPL; ++i) v[i] = lda(&src[lane * EPL + i]);
+    for (int i = 0; i < EPL; ++i) v[i] = in[i];
     if (qk_norm) {
         float ss = 0.f;
 #pragma unroll
@@ -104,6 +175,12 @@ struct AttnArgs {
     const int32_t* pos;     // [M] position of each row (device)
     const int32_t* slots;   // [M] kv slot per row, or nullptr -> slot = row
     bf16* y;                // [M][H*HD]
+    const uint32_t* qkv_t;  // flag-in-data versions of qkv / y used by the persistent frame kernel (else nullptr)
+    uint32_t* y_t;
+    int tag_in_op, tag_out_op;  // op indices whose tags qkv_t carries / y_t gets
+    uint2* ll_acc;          // [M][KV][splits][GQ*HD] {fp32, tag} partial numerators of the frame kernel's split attention
+    uint2* ll_ml;           // [M][KV][splits][GQ][2]  {max, sum}
+    const bf16 *next_k, *next_v;  // KV cache of the next slow layer (L2 prefetch one layer ahead), or nullptr
     float* ws_acc;          // [M][KV][splits][GQ][HD]
     float* ws_ml;           // [M][KV][splits][GQ][2]
     int32_t* counters;      // [M][KV]
@@ -126,9 +203,9 @@ __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const size_t co = (((size_t)slot * a.KV + h) * a.S + pos) * HD;
     if (warp == 0) {
-        float k[EPL];
-        head_norm_rope<HD>(a.qkv + (size_t)m * qkv_w + (a.H + h) * HD, a.k_norm, a.rope + (size_t)pos * HD,
-                           a.qk_norm, a.eps, k);
+        float kin[EPL], k[EPL];
+        load_head<HD, false>(a.qkv + (size_t)m * qkv_w + (a.H + h) * HD, nullptr, 0, kin);
+        head_norm_rope<HD>(kin, a.k_norm, a.rope + (size_t)pos * HD, a.qk_norm, a.eps, k);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) a.kcache[co + lane * EPL + i] = __float2bfloat16_rn(k[i]);
     } else {
@@ -145,8 +222,9 @@ __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
 // one (split, kv head, row) work item on ATTN_THREADS threads synchronised through SY; tid = index inside the group
 // QREG: keep q in registers (standalone kernel) or read it from shared memory in the FMA loop (persistent frame kernel,
 // which is capped at 96 registers per thread by its 17 warps per SM)
-template <int HD, int GQ, class SY, bool QREG = true>
-__device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, int h, int m, int tid) {
+template <int HD, int GQ, class SY, bool QREG = true, bool TAG = false>
+__device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, int h, int m, int tid, unsigned tag_in = 0,
+                                                 unsigned tag_out = 0) {
     constexpr int EPL = HD / 32;
     constexpr int LPK = HD / 8;              // lanes per key row (16 B each)
     constexpr int KPI = ATTN_THREADS / LPK;  // keys per CTA step
@@ -163,6 +241,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const bf16* row = a.qkv + (size_t)m * qkv_w;
+    const uint32_t* row_t = TAG ? a.qkv_t + (size_t)m * qkv_w : nullptr;
     const int n_keys = pos + 1;
     const int per = (n_keys + a.splits - 1) / a.splits;
     const int k0 = split * per;
@@ -172,16 +251,18 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
 
     // ---- q prep (one warp per q head of this GQA group), optional fused K/V append
     for (int g = warp; g < GQ; g += ATTN_THREADS / 32) {
-        float q[EPL];
-        head_norm_rope<HD>(row + (h * GQ + g) * HD, a.q_norm, rope_row, a.qk_norm, a.eps, q);
+        float qin[EPL], q[EPL];
+        load_head<HD, TAG>(row + (h * GQ + g) * HD, row_t + (h * GQ + g) * HD, tag_in, qin);
+        head_norm_rope<HD>(qin, a.q_norm, rope_row, a.qk_norm, a.eps, q);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) qs[g][lane * EPL + i] = q[i];
     }
     if (owns_new) {
         const size_t co = (((size_t)slot * a.KV + h) * a.S + pos) * HD;
         if (warp == (GQ % (ATTN_THREADS / 32))) {  // spread the extra work to a different warp when possible
-            float k[EPL];
-            head_norm_rope<HD>(row + (a.H + h) * HD, a.k_norm, rope_row, a.qk_norm, a.eps, k);
+            float kin[EPL], k[EPL];
+            load_head<HD, TAG>(row + (a.H + h) * HD, row_t + (a.H + h) * HD, tag_in, kin);
+            head_norm_rope<HD>(kin, a.k_norm, rope_row, a.qk_norm, a.eps, k);
 #pragma unroll
             for (int i = 0; i < EPL; ++i) {
                 knew[lane * EPL + i] = k[i];
@@ -189,12 +270,12 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
             }
         }
         if (warp == ((GQ + 1) % (ATTN_THREADS / 32))) {
-            const bf16* v = row + (a.H + a.KV + h) * HD;
+            float vin[EPL];
+            load_head<HD, TAG>(row + (a.H + a.KV + h) * HD, row_t + (a.H + a.KV + h) * HD, tag_in, vin);
 #pragma unroll
             for (int i = 0; i < EPL; ++i) {
-                const bf16 t = lda_raw(&v[lane * EPL + i]);
-                vnew[lane * EPL + i] = __bfloat162float(t);
-                a.vcache[co + lane * EPL + i] = t;
+                vnew[lane * EPL + i] = vin[i];
+                a.vcache[co + lane * EPL + i] = __float2bfloat16_rn(vin[i]);  // exact: vin is a bf16 value
             }
         }
     }
@@ -311,7 +392,9 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
             float s = 0.f;
 #pragma unroll
             for (int k = 0; k < KPI; ++k) s += accs[k][g][d];
-            a.y[(size_t)m * H * HD + (h * GQ + g) * HD + d] = __float2bfloat16_rn(s / lrun[g]);
+            const size_t yi = (size_t)m * H * HD + (h * GQ + g) * HD + d;
+            if (TAG) st_tagged(a.y_t + yi, s / lrun[g], tag_out);
+            else a.y[yi] = __float2bfloat16_rn(s / lrun[g]);
         }
         return;
     }
@@ -350,7 +433,9 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
             num = fmaf(w, __ldcg(&a.ws_acc[(b0 + s) * GQ * HD + e]), num);
             den = fmaf(w, ls, den);
         }
-        a.y[(size_t)m * H * HD + (h * GQ) * HD + e] = __float2bfloat16_rn(num / den);
+        const size_t yi = (size_t)m * H * HD + (h * GQ) * HD + e;
+        if (TAG) st_tagged(a.y_t + yi, num / den, tag_out);
+        else a.y[yi] = __float2bfloat16_rn(num / den);
     }
     if (tid == 0) a.counters[m * a.KV + h] = 0;  // re-arm for the next launch
 }
@@ -364,11 +449,317 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
     attn_decode_body<HD, GQ, SyncBlock<ATTN_THREADS>>(a, blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
 }
 
+// ----------------------------------------------------------------------------- slow-AR decode attention, latency form
+// Same math as attn_decode_body for ONE (split, kv head, row) item, shaped for the persistent frame kernel where this
+// op sits on a ~400-step dependent chain: the split's whole key range (<= ASP_MAXKEYS) is one tile, and every K and V
+// row of the tile is requested from memory BEFORE the item waits for this frame's q/k/v (the cache does not depend on
+// them), so the DRAM latency is paid once and overlaps the wait for the producer op.  Activations are flag-in-data.
+#define ASP_THREADS 512
+#define ASP_KPT 4  // keys per thread: 4 K + 4 V 128-bit loads in flight per thread
+#define ASP_MAXS 16  // splits per (row, kv head) the merge step is unrolled for
+__host__ __device__ constexpr int asp_max_keys(int hd) { return (ASP_THREADS / (hd / 8)) * ASP_KPT; }  // 128 at hd 128
+
+// shared-memory index of element d of a head vector, arranged so that a lane's 8 elements (chunk = d / 8) are two
+// float4 whose neighbours in the warp are contiguous: [half][chunk][4]  (conflict-free LDS.128 / STS.128)
+template <int HD>
+__device__ __forceinline__ int asp_idx(int d) {
+    return (((d & 7) >> 2) * (HD / 8) + (d >> 3)) * 4 + (d & 3);
+}
+
+template <int HD, int GQ>
+struct AttnSplitSmem {
+    alignas(16) float qs[GQ][HD];
+    alignas(16) float knew[HD], vnew[HD];
+    alignas(16) float sc[GQ][asp_max_keys(HD)];
+    alignas(16) float red[ASP_THREADS / 64][GQ][HD];
+    float mrun[GQ], lrun[GQ];
+    int is_last;
+};
+
+// L2 prefetch of the cached keys/values one (split, kv head, row) item will read: a demand load that misses L2 queues
+// behind the weight stream's outstanding bulk copies (~4 us under load), so the item's KV range is pulled in a layer ahead
+template <int HD>
+__device__ __forceinline__ void attn_split_prefetch(const AttnArgs& a, const bf16* kc, const bf16* vc, int split, int h, int m) {
+    const int pos = a.pos[m];
+    const int slot = a.slots ? a.slots[m] : m;
+    const int per = (pos + 1 + a.splits - 1) / a.splits;
+    const int k0 = split * per, k1 = min(pos, k0 + per);
+    l2_prefetch_bulk(a.rope + (size_t)pos * HD, HD * 2);
+    if (k1 <= k0) return;
+    const size_t off = (((size_t)slot * a.KV + h) * a.S + k0) * HD;
+    const uint32_t bytes = (uint32_t)(k1 - k0) * HD * 2;
+    l2_prefetch_bulk(kc + off, bytes);
+    l2_prefetch_bulk(vc + off, bytes);
+}
+
+template <int HD, int GQ, class SY>
+__device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem<HD, GQ>& sm, int split, int h, int m,
+                                                int tid, unsigned tag_in, unsigned tag_out,
+                                                unsigned long long* trace = nullptr) {
+    constexpr int EPL = HD / 32;
+    constexpr int LPK = HD / 8;               // lanes per key row (16 B each)
+    constexpr int KPI = ASP_THREADS / LPK;    // key slots
+    constexpr int NW = ASP_THREADS / 32;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int kslot = tid / LPK, chunk = tid % LPK;
+
+    const int pos = a.pos[m];
+    const int slot = a.slots ? a.slots[m] : m;
+    const int qkv_w = (a.H + 2 * a.KV) * HD;
+    const uint32_t* row_t = a.qkv_t + (size_t)m * qkv_w;
+    const int n_keys = pos + 1;
+    const int per = (n_keys + a.splits - 1) / a.splits;
+    const int k0 = split * per;
+    const int k1 = min(n_keys, k0 + per);
+    const int nk = max(0, k1 - k0);                       // keys of this split (<= asp_max_keys, checked by the host)
+    const bool owns_new = (pos >= k0) && (pos < k1);      // the new key/value come from this frame's qkv
+    const int kc1 = owns_new ? pos : k1;                  // keys [k0, kc1) are read from the cache
+    const bf16* kbase = a.kcache + ((size_t)slot * a.KV + h) * a.S * HD;
+    const bf16* vbase = a.vcache + ((size_t)slot * a.KV + h) * a.S * HD;
+
+    // ---- 1. request the whole K and V tile now (independent of this frame's activations)
+    uint4 kq[ASP_KPT], vq[ASP_KPT];
+#pragma unroll
+    for (int i = 0; i < ASP_KPT; ++i) {
+        const int j = k0 + kslot + KPI * i;
+        kq[i] = (j < kc1) ? ld_stream(kbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int i = 0; i < ASP_KPT; ++i) {
+        const int j = k0 + kslot + KPI * i;
+        vq[i] = (j < kc1) ? ld_stream(vbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
+    }
+
+    // ---- 2. q heads (warps 0..GQ-1), new k (warp GQ), new v (warp GQ+1): spin on the producer's tags; the norm
+    //         weights and the RoPE row are fetched first (they do not depend on the frame)
+    const bf16* rope_row = a.rope + (size_t)pos * HD;
+    HeadCoef<HD> coef;
+    if (warp <= GQ) coef.load(warp < GQ ? a.q_norm : a.k_norm, rope_row, a.qk_norm);
+    if (warp < GQ) {
+        float qin[EPL], q[EPL];
+        load_head<HD, true>(nullptr, row_t + (h * GQ + warp) * HD, tag_in, qin);
+        head_norm_rope<HD>(qin, coef, a.qk_norm, a.eps, q);
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) sm.qs[warp][asp_idx<HD>(lane * EPL + i)] = q[i];
+    } else if (owns_new && warp == GQ) {
+        const size_t co = (((size_t)slot * a.KV + h) * a.S + pos) * HD;
+        float kin[EPL], k[EPL];
+        load_head<HD, true>(nullptr, row_t + (a.H + h) * HD, tag_in, kin);
+        head_norm_rope<HD>(kin, coef, a.qk_norm, a.eps, k);
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) {
+            sm.knew[asp_idx<HD>(lane * EPL + i)] = k[i];
+            a.kcache[co + lane * EPL + i] = __float2bfloat16_rn(k[i]);
+        }
+    } else if (owns_new && warp == GQ + 1) {
+        const size_t co = (((size_t)slot * a.KV + h) * a.S + pos) * HD;
+        float vin[EPL];
+        load_head<HD, true>(nullptr, row_t + (a.H + a.KV + h) * HD, tag_in, vin);
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) {
+            sm.vnew[asp_idx<HD>(lane * EPL + i)] = vin[i];
+            a.vcache[co + lane * EPL + i] = __float2bfloat16_rn(vin[i]);
+        }
+    }
+    SY::sync();
+#define ASP_TRACE(point)                                              \
+    if (trace && tid == 0 && a.pf_bytes == (size_t)(point)) {         \
+        unsigned long long t_;                                        \
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_));         \
+        trace[1] = t_;                                                \
+    }
+    ASP_TRACE(0)
+
+    // ---- 3. scores
+#pragma unroll
+    for (int i = 0; i < ASP_KPT; ++i) {
+        const int jl = kslot + KPI * i;       // key index inside the split (warp-uniform validity: nk is uniform)
+        if (KPI * i >= nk) break;
+        float kf[8];
+        if (k0 + jl < kc1) unpack8(kq[i], kf);
+        else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) kf[e] = (jl < nk) ? sm.knew[asp_idx<HD>(chunk * 8 + e)] : 0.f;
+        }
+        float d[GQ];
+#pragma unroll
+        for (int g = 0; g < GQ; ++g) {
+            const float4 qa = *reinterpret_cast<const float4*>(&sm.qs[g][chunk * 4]);
+            const float4 qb = *reinterpret_cast<const float4*>(&sm.qs[g][(LPK + chunk) * 4]);
+            float s = qa.x * kf[0];
+            s = fmaf(qa.y, kf[1], s); s = fmaf(qa.z, kf[2], s); s = fmaf(qa.w, kf[3], s);
+            s = fmaf(qb.x, kf[4], s); s = fmaf(qb.y, kf[5], s); s = fmaf(qb.z, kf[6], s); s = fmaf(qb.w, kf[7], s);
+            d[g] = s;
+        }
+#pragma unroll
+        for (int o = LPK / 2; o > 0; o >>= 1)
+#pragma unroll
+            for (int g = 0; g < GQ; ++g) d[g] += __shfl_xor_sync(0xffffffffu, d[g], o);
+        if (chunk == 0 && jl < nk)
+#pragma unroll
+            for (int g = 0; g < GQ; ++g) sm.sc[g][jl] = d[g] * a.scale;
+    }
+    SY::sync();
+    ASP_TRACE(1)
+
+    // ---- 4. softmax over the split (fp32, like the MATH SDPA backend): warp g owns head g
+    if (warp < GQ) {
+        float mx = -INFINITY;
+        for (int j = lane; j < nk; j += 32) mx = fmaxf(mx, sm.sc[warp][j]);
+        mx = warp_max(mx);
+        float sum = 0.f;
+        for (int j = lane; j < nk; j += 32) {
+            const float pj = expf(sm.sc[warp][j] - mx);
+            sm.sc[warp][j] = pj;
+            sum += pj;
+        }
+        sum = warp_sum(sum);
+        if (lane == 0) { sm.mrun[warp] = mx; sm.lrun[warp] = sum; }
+    }
+    SY::sync();
+    ASP_TRACE(2)
+
+    // ---- 5. P.V
+    float acc[GQ][8];
+#pragma unroll
+    for (int g = 0; g < GQ; ++g)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
+#pragma unroll
+    for (int i = 0; i < ASP_KPT; ++i) {
+        const int jl = kslot + KPI * i;
+        if (jl < nk) {
+            float vf[8];
+            if (k0 + jl < kc1) unpack8(vq[i], vf);
+            else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) vf[e] = sm.vnew[asp_idx<HD>(chunk * 8 + e)];
+            }
+#pragma unroll
+            for (int g = 0; g < GQ; ++g) {
+                const float pj = sm.sc[g][jl];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[g][e] = fmaf(pj, vf[e], acc[g][e]);
+            }
+        }
+    }
+    // key slots of one warp (32 / LPK of them), then the warps through shared memory, in a fixed order
+#pragma unroll
+    for (int o = LPK; o < 32; o <<= 1)
+#pragma unroll
+        for (int g = 0; g < GQ; ++g)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[g][e] += __shfl_xor_sync(0xffffffffu, acc[g][e], o);
+    if (warp >= NW / 2 && lane < LPK) {  // upper half of the warps hands its partials to the lower half
+#pragma unroll
+        for (int g = 0; g < GQ; ++g) {
+            float* r = sm.red[warp - NW / 2][g];
+            *reinterpret_cast<float4*>(&r[chunk * 4]) = make_float4(acc[g][0], acc[g][1], acc[g][2], acc[g][3]);
+            *reinterpret_cast<float4*>(&r[(LPK + chunk) * 4]) = make_float4(acc[g][4], acc[g][5], acc[g][6], acc[g][7]);
+        }
+    }
+    SY::sync();
+    if (warp < NW / 2 && lane < LPK) {
+#pragma unroll
+        for (int g = 0; g < GQ; ++g) {
+            float* r = sm.red[warp][g];
+            float4 lo = *reinterpret_cast<float4*>(&r[chunk * 4]), hi = *reinterpret_cast<float4*>(&r[(LPK + chunk) * 4]);
+            lo.x += acc[g][0]; lo.y += acc[g][1]; lo.z += acc[g][2]; lo.w += acc[g][3];
+            hi.x += acc[g][4]; hi.y += acc[g][5]; hi.z += acc[g][6]; hi.w += acc[g][7];
+            *reinterpret_cast<float4*>(&r[chunk * 4]) = lo;
+            *reinterpret_cast<float4*>(&r[(LPK + chunk) * 4]) = hi;
+        }
+    }
+    SY::sync();
+
+    ASP_TRACE(3)
+    const int H = a.H;
+    const size_t pbase = (((size_t)m * a.KV + h) * a.splits + split);
+    const uint32_t ptag = tag_out | 0x10000u;  // 32-bit tag of this op's partials (never 0)
+    for (int e = tid; e < GQ * HD; e += ASP_THREADS) {
+        const int g = e / HD, d = e % HD;
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < NW / 2; ++w) s += sm.red[w][g][asp_idx<HD>(d)];
+        if (a.splits == 1) st_tagged(a.y_t + (size_t)m * H * HD + (h * GQ + g) * HD + d, s / sm.lrun[g], tag_out);
+        else st_ll64(a.ll_acc + pbase * GQ * HD + e, s, ptag);
+    }
+    if (a.splits == 1) return;
+    // the (max, sum) records are published after the numerators: barrier + fence by the publishing threads make
+    // "record visible" imply "numerators visible", so the merging item fetches them once instead of re-polling
+    SY::sync();
+    if (tid < GQ) {
+        __threadfence();
+        st_ll64(a.ll_ml + (pbase * GQ + tid) * 2 + 0, (nk > 0) ? sm.mrun[tid] : -INFINITY, ptag);
+        st_ll64(a.ll_ml + (pbase * GQ + tid) * 2 + 1, (nk > 0) ? sm.lrun[tid] : 0.f, ptag);
+    }
+    // ---- 6. the split-0 item of each (row, kv head) merges the partials: it spins on their tags (no fence, no atomic,
+    //         no "last arriver" election), all loads of a thread in flight together
+    ASP_TRACE(4)
+    if (split != 0) return;
+    static_assert(GQ * HD <= ASP_THREADS, "one output element per thread in the merge");
+    const size_t b0 = ((size_t)m * a.KV + h) * a.splits;
+    float* mlbuf = &sm.red[0][0][0];                 // [splits][GQ][2]; the reduction buffer is free after the sync
+    float* wbuf = mlbuf + ASP_MAXS * GQ * 2;         // [splits][GQ] merge weights, then [GQ] 1 / denominators
+    const int e = tid;
+    const bool has = e < GQ * HD;
+    SY::sync();
+    {
+        // wait on the small (max, sum) records only — a few threads, with back-off — then fetch the numerators, which the
+        // same CTAs stored just before (their tags are still checked: stores are not ordered)
+        unsigned spins = 0;
+        long long t0 = 0;
+        for (int i = tid; i < a.splits * GQ * 2; i += ASP_THREADS) {
+            float v;
+            while (!ld_ll64_try(a.ll_ml + b0 * GQ * 2 + i, ptag, v)) spin_watchdog(spins, t0);
+            mlbuf[i] = v;
+        }
+    }
+    SY::sync();
+    ASP_TRACE(5)
+    float pv[ASP_MAXS];
+    {
+        unsigned spins = 0;
+        long long t0 = 0;
+        bool ok;
+        do {
+            ok = true;
+#pragma unroll
+            for (int s = 0; s < ASP_MAXS; ++s) {
+                pv[s] = 0.f;
+                if (has && s < a.splits) ok &= ld_ll64_try(a.ll_acc + (b0 + s) * GQ * HD + e, ptag, pv[s]);
+            }
+            if (!ok) spin_watchdog(spins, t0);
+        } while (!ok);
+    }
+    if (warp < GQ) {  // warp g, lane s: global max, weights exp(m_s - M), sum(w_s l_s) — a serial loop on one thread
+        static_assert(ASP_MAXS <= 32, "one lane per split");      // costs microseconds on this dependent chain
+        const bool live = lane < a.splits;
+        const float ms = live ? mlbuf[(lane * GQ + warp) * 2] : -INFINITY;
+        const float ls = live ? mlbuf[(lane * GQ + warp) * 2 + 1] : 0.f;
+        const float M = warp_max(ms);
+        const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+        const float den = warp_sum(w * ls);
+        if (lane < ASP_MAXS) wbuf[lane * GQ + warp] = w;
+        if (lane == 0) wbuf[ASP_MAXS * GQ + warp] = den;
+    }
+    SY::sync();
+    ASP_TRACE(6)
+    if (has) {
+        const int g = e / HD;
+        float num = 0.f;
+#pragma unroll
+        for (int s = 0; s < ASP_MAXS; ++s) num = fmaf(wbuf[s * GQ + g], pv[s], num);
+        st_tagged(a.y_t + (size_t)m * H * HD + (h * GQ) * HD + e, num / wbuf[ASP_MAXS * GQ + g], tag_out);
+    }
+}
+
 // ----------------------------------------------------------------------------- fast-AR attention (context <= 16)
 #define FAST_MAX_CTX 16
 
-template <int HD, int GQ, class SY>
-__device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, int tid) {
+template <int HD, int GQ, class SY, bool TAG = false>
+__device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, int tid, unsigned tag_in = 0,
+                                               unsigned tag_out = 0) {
     constexpr int EPL = HD / 32;
     __shared__ float knew[HD], vnew[HD];
     const int lane = tid & 31, g = tid >> 5;
@@ -377,14 +768,34 @@ __device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, 
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const bf16* row = a.qkv + (size_t)m * qkv_w;
+    const uint32_t* row_t = TAG ? a.qkv_t + (size_t)m * qkv_w : nullptr;
     const bf16* rope_row = a.rope + (size_t)pos * HD;
     const size_t cbase = ((size_t)slot * a.KV + h) * a.S * HD;
 
-    float q[EPL];
-    head_norm_rope<HD>(row + (h * GQ + g) * HD, a.q_norm, rope_row, a.qk_norm, a.eps, q);
+    // everything that does not depend on this pass's activations is requested first: norm weights, the RoPE row and
+    // the cached keys/values of the earlier codebook positions (latency hides behind the wait for the producer op)
+    HeadCoef<HD> cq, ck;
+    cq.load(a.q_norm, rope_row, a.qk_norm);
+    if (g == 0) ck.load(a.k_norm, rope_row, a.qk_norm);
+    uint32_t kraw[FAST_MAX_CTX][EPL / 2], vraw[FAST_MAX_CTX][EPL / 2];
+#pragma unroll
+    for (int j = 0; j < FAST_MAX_CTX; ++j)
+#pragma unroll
+        for (int i = 0; i < EPL / 2; ++i) {
+            kraw[j][i] = 0; vraw[j][i] = 0;
+            if (j < pos) {
+                kraw[j][i] = __ldcg(reinterpret_cast<const uint32_t*>(a.kcache + cbase + (size_t)j * HD + lane * EPL) + i);
+                vraw[j][i] = __ldcg(reinterpret_cast<const uint32_t*>(a.vcache + cbase + (size_t)j * HD + lane * EPL) + i);
+            }
+        }
+
+    float qin[EPL], q[EPL];
+    load_head<HD, TAG>(row + (h * GQ + g) * HD, row_t + (h * GQ + g) * HD, tag_in, qin);
+    head_norm_rope<HD>(qin, cq, a.qk_norm, a.eps, q);
     if (g == 0) {
-        float k[EPL];
-        head_norm_rope<HD>(row + (a.H + h) * HD, a.k_norm, rope_row, a.qk_norm, a.eps, k);
+        float kin[EPL], k[EPL];
+        load_head<HD, TAG>(row + (a.H + h) * HD, row_t + (a.H + h) * HD, tag_in, kin);
+        head_norm_rope<HD>(kin, ck, a.qk_norm, a.eps, k);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) {
             knew[lane * EPL + i] = k[i];
@@ -392,12 +803,12 @@ __device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, 
         }
     }
     if (g == GQ - 1) {
-        const bf16* v = row + (a.H + a.KV + h) * HD;
+        float vin[EPL];
+        load_head<HD, TAG>(row + (a.H + a.KV + h) * HD, row_t + (a.H + a.KV + h) * HD, tag_in, vin);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) {
-            const bf16 t = lda_raw(&v[lane * EPL + i]);
-            vnew[lane * EPL + i] = __bfloat162float(t);
-            a.vcache[cbase + (size_t)pos * HD + lane * EPL + i] = t;
+            vnew[lane * EPL + i] = vin[i];
+            a.vcache[cbase + (size_t)pos * HD + lane * EPL + i] = __float2bfloat16_rn(vin[i]);
         }
     }
     SY::sync();
@@ -412,8 +823,8 @@ __device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, 
             float d = 0.f;
 #pragma unroll
             for (int i = 0; i < EPL; ++i) {
-                const float kv = (j == pos) ? knew[lane * EPL + i]
-                                            : lda(&a.kcache[cbase + (size_t)j * HD + lane * EPL + i]);
+                const uint32_t kw = kraw[j][i >> 1];
+                const float kv = (j == pos) ? knew[lane * EPL + i] : ((i & 1) ? bf16_hi(kw) : bf16_lo(kw));
                 d = fmaf(q[i], kv, d);
             }
             d = warp_sum(d);
@@ -434,14 +845,17 @@ __device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, 
             const float p = rbf(__fdiv_rn(s[j], den));  // softmax output in bf16
 #pragma unroll
             for (int i = 0; i < EPL; ++i) {
-                const float vv = (j == pos) ? vnew[lane * EPL + i]
-                                            : lda(&a.vcache[cbase + (size_t)j * HD + lane * EPL + i]);
+                const uint32_t vw = vraw[j][i >> 1];
+                const float vv = (j == pos) ? vnew[lane * EPL + i] : ((i & 1) ? bf16_hi(vw) : bf16_lo(vw));
                 o[i] = fmaf(p, vv, o[i]);
             }
         }
 #pragma unroll
-    for (int i = 0; i < EPL; ++i)
-        a.y[(size_t)m * a.H * HD + (h * GQ + g) * HD + lane * EPL + i] = __float2bfloat16_rn(o[i]);
+    for (int i = 0; i < EPL; ++i) {
+        const size_t yi = (size_t)m * a.H * HD + (h * GQ + g) * HD + lane * EPL + i;
+        if (TAG) st_tagged(a.y_t + yi, o[i], tag_out);
+        else a.y[yi] = __float2bfloat16_rn(o[i]);
+    }
 }
 template <int HD, int GQ>
 __global__ void __launch_bounds__(32 * GQ) fast_attn_kernel(AttnArgs a) {

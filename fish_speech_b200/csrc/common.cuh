@@ -138,3 +138,78 @@ __device__ __forceinline__ bf16 lda_raw(const bf16* p) {
 }
 __device__ __forceinline__ uint4 lda(const uint4* p) { return __ldcg(p); }
 __device__ __forceinline__ int lda(const int* p) { return __ldcg(p); }
+
+// ----------------------------------------------------------------------------- flag-in-data activations
+// Inside the persistent frame kernel an activation element travels as ONE 32-bit word (tag << 16) | bf16 bits, where
+// the tag names the op instance that produced it.  A 32-bit store is single-copy atomic, so a reader that sees the
+// expected tag also sees the value: producers need no fence and no flag, consumers spin on the data they have to
+// load anyway.  This replaces "fence + grid barrier + reload" between dependent ops (the same idea as the
+// low-latency protocol of collective libraries).
+#ifndef FSB_SPIN_NS
+#define FSB_SPIN_NS 200
+#endif
+__device__ __forceinline__ void st_tagged(uint32_t* p, float v, unsigned tag) {
+    const uint32_t w = (tag << 16) | (uint32_t)f_to_bf16_bits(v);
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
+}
+__device__ __forceinline__ void st_tagged4(uint32_t* p, uint32_t lo_pair, uint32_t hi_pair, unsigned tag) {
+    const uint32_t t = tag << 16;
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(t | (lo_pair & 0xffffu)),
+                 "r"(t | (lo_pair >> 16)), "r"(t | (hi_pair & 0xffffu)), "r"(t | (hi_pair >> 16))
+                 : "memory");
+}
+__device__ __forceinline__ void spin_watchdog(unsigned& spins, long long& t0) {
+    // back off between polls: tens of thousands of threads polling the same L2 slices delay the very stores they wait for
+    __nanosleep(FSB_SPIN_NS);
+    if ((++spins & 0x3ffu) == 0) {  // a lost producer must fault, not hang the GPU
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 4000000000LL) __trap();
+    }
+}
+// 4 consecutive elements (16-byte aligned); returns them as two packed bf16 pairs once all four carry `tag`
+__device__ __forceinline__ uint2 ld_tagged4(const uint32_t* p, unsigned tag) {
+    uint32_t a, b, c, d;
+    unsigned spins = 0;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(p) : "memory");
+        if ((a >> 16) == tag && (b >> 16) == tag && (c >> 16) == tag && (d >> 16) == tag) break;
+        spin_watchdog(spins, t0);
+    }
+    return make_uint2((a & 0xffffu) | (b << 16), (c & 0xffffu) | (d << 16));
+}
+// one attempt: false if any of the 4 words does not carry `tag` yet
+__device__ __forceinline__ bool ld_tagged4_try(const uint32_t* p, unsigned tag, uint2& out) {
+    uint32_t a, b, c, d;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(p) : "memory");
+    out = make_uint2((a & 0xffffu) | (b << 16), (c & 0xffffu) | (d << 16));
+    return (a >> 16) == tag && (b >> 16) == tag && (c >> 16) == tag && (d >> 16) == tag;
+}
+__device__ __forceinline__ uint32_t ld_tagged2(const uint32_t* p, unsigned tag) {
+    uint32_t a, b;
+    unsigned spins = 0;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
+        if ((a >> 16) == tag && (b >> 16) == tag) break;
+        spin_watchdog(spins, t0);
+    }
+    return (a & 0xffffu) | (b << 16);
+}
+// value of an element whose tag is already known to be current (validated earlier by this CTA)
+__device__ __forceinline__ float ld_tagged_value(const uint32_t* p) {
+    uint32_t a;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(a) : "l"(p) : "memory");
+    return bf16_bits_to_f((uint16_t)(a & 0xffffu));
+}
+
+// 64-bit flag-in-data words for fp32 payloads (split-attention partials): {value, tag}, one 8-byte store
+__device__ __forceinline__ void st_ll64(uint2* p, float v, uint32_t tag) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(tag) : "memory");
+}
+__device__ __forceinline__ bool ld_ll64_try(const uint2* p, uint32_t tag, float& v) {
+    uint32_t a, b;
+    asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
+    v = __uint_as_float(a);
+    return b == tag;
+}

@@ -55,12 +55,15 @@ struct fsb_dual_ar {
     int32_t *counters = nullptr, *pf_pos = nullptr, *pf_slot = nullptr;
     char* mega_buf = nullptr;        // device copy of the persistent frame kernel's op list (MEGA_BUF_BYTES)
     unsigned* mega_sync = nullptr;   // grid barrier counters
+    uint2 *ll_acc = nullptr, *ll_ml = nullptr;  // {fp32, tag} split-attention partials of the frame kernel
+    uint32_t* tg_base = nullptr;     // flag-in-data activations: x, x2, qkv, y, ff, hidden, xfast, xf, xf2
+    size_t tg_words = 0;
     unsigned long long* mega_prof = nullptr;  // cycle counters of CTA 0 when option "mega_prof" is on
     int mega_prof_on = 0;
     unsigned long long* mega_trace = nullptr;
     int mega_trace_on = 0;
     int mega_copy_bytes = 5120;      // bulk-copy granularity inside a ring stage
-    int mega_pf_stages = 16;         // L2 prefetch look-ahead of the frame kernel's weight stream (ring stages)
+    int mega_pf_stages = 0;          // L2 prefetch look-ahead of the frame kernel's weight stream (ring stages)
     int max_splits = 32;
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
@@ -470,37 +473,86 @@ bool mega_shape_ok(const fsb_dual_ar_desc& d) {
            mega_rshift(d.n_head * d.head_dim) >= 0 && mega_rshift(d.ffn) >= 0;
 }
 
+struct MegaTagged {  // flag-in-data activation buffers carved from tg_base
+    uint32_t *x, *x2, *qkv, *y, *ff, *hidden, *xfast, *xf, *xf2;
+    explicit MegaTagged(const fsb_dual_ar* h) {
+        const fsb_dual_ar_desc& d = h->d;
+        uint32_t* p = h->tg_base;
+        auto take = [&](size_t n) { uint32_t* r = p; p += n; return r; };
+        x = take(d.dim); x2 = take(d.dim); qkv = take((size_t)(d.n_head + 2 * d.n_kv_head) * d.head_dim);
+        y = take((size_t)d.n_head * d.head_dim); ff = take(d.ffn); hidden = take(d.dim); xfast = take(d.dim);
+        xf = take(d.dim); xf2 = take(d.dim);
+    }
+};
+
 struct MegaBuilder {
+    int n_cta = 148;
     std::vector<MegaOp> ops;
     std::vector<MegaGemv> gemv;
     std::vector<AttnArgs> attn;
     std::vector<SampleArgs> samp;
-    void op(int type, int idx, int sync) { ops.push_back(MegaOp{type, idx, sync, 0}); }
-    void add_gemv(int N, int K, int pro, int epi, const bf16* W, const bf16* W2, const bf16* x, const bf16* norm_w,
-                  const bf16* res, bf16* out, bf16* xnorm_out, float eps) {
-        MegaGemv g{};
-        g.W = W; g.W2 = W2; g.x = x; g.norm_w = norm_w; g.res = res; g.out = out; g.xnorm_out = xnorm_out;
-        g.N = N; g.K = K; g.pro = pro; g.epi = epi; g.eps = eps; g.rshift = mega_rshift(K);
-        gemv.push_back(g);
-        op(MOP_GEMV, (int)gemv.size() - 1, MSYNC_GRID);
+    std::vector<std::pair<const uint32_t*, int>> writer;  // last op that wrote each tagged buffer
+    std::vector<uint4> hot;                               // {ptr lo, ptr hi, bytes, 0}
+    void add_hot(const void* p, size_t bytes) {
+        if (!p || bytes < 16) return;
+        for (const uint4& q : hot)
+            if ((((unsigned long long)q.y << 32) | q.x) == (unsigned long long)(uintptr_t)p) return;
+        for (size_t off = 0; off < bytes; off += 32768) {  // one bulk prefetch per <= 32 KB piece
+            const unsigned long long v = (unsigned long long)(uintptr_t)p + off;
+            const size_t n = std::min<size_t>(32768, bytes - off) & ~(size_t)15;
+            if (n) hot.push_back(make_uint4((unsigned)(v & 0xffffffffu), (unsigned)(v >> 32), (unsigned)n, 0u));
+        }
     }
-    void add_layers(const fsb_dual_ar* h, bool fast, const bf16* x_in, const int32_t* pos, const int32_t* slots,
-                    int pos_fixed, int splits) {
+    int writer_of(const uint32_t* p) const {
+        for (auto it = writer.rbegin(); it != writer.rend(); ++it)
+            if (it->first == p) return it->second;
+        return -1;
+    }
+    void wrote(const uint32_t* p) { writer.emplace_back(p, (int)ops.size() - 1); }
+    void op(int type, int idx, int sync) { ops.push_back(MegaOp{type, idx, sync, 0}); }
+    // out_t != nullptr: tagged output vector; else plain bf16 logits at `out` followed by a grid barrier
+    void add_gemv(int N, int K, int pro, int epi, const bf16* W, const bf16* W2, const uint32_t* x_t, const bf16* norm_w,
+                  const uint32_t* res_t, uint32_t* out_t, bf16* out, bf16* xnorm_out, uint32_t* xnorm_out_t, float eps) {
+        MegaGemv g{};
+        g.W = W; g.W2 = W2; g.x_t = x_t; g.norm_w = norm_w; g.res_t = res_t; g.out_t = out_t; g.out = out;
+        g.xnorm_out = xnorm_out; g.xnorm_out_t = xnorm_out_t;
+        g.N = N; g.K = K; g.pro = pro; g.epi = epi; g.eps = eps; g.rshift = mega_rshift(K);
+        g.x_op = writer_of(x_t);
+        g.rows_q = N / n_cta; g.rows_rem = N % n_cta;
+        if (pro == PRO_RMSNORM) add_hot(norm_w, (size_t)K * 2);
+        gemv.push_back(g);
+        op(MOP_GEMV, (int)gemv.size() - 1, out_t ? MSYNC_CTA : MSYNC_GRID);
+        if (out_t) wrote(out_t);
+        if (xnorm_out_t) wrote(xnorm_out_t);
+    }
+    void add_layers(const fsb_dual_ar* h, const MegaTagged& t, bool fast, const uint32_t* x_in, const int32_t* pos,
+                    const int32_t* slots, int pos_fixed, int splits) {
         const fsb_dual_ar_desc& d = h->d;
         const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn, QKV = (H + 2 * KV) * HD;
         const std::vector<LayerW>& L = fast ? h->fast : h->slow;
-        bf16* xa = fast ? h->xf : h->x;
-        bf16* xb = fast ? h->xf2 : h->x2;
-        const bf16* cur = x_in;
+        uint32_t* xa = fast ? t.xf : t.x;
+        uint32_t* xb = fast ? t.xf2 : t.x2;
+        const uint32_t* cur = x_in;
         for (const LayerW& w : L) {
-            add_gemv(QKV, D, PRO_RMSNORM, EPI_STORE, w.wqkv, nullptr, cur, w.attn_norm, nullptr, h->qkv, nullptr, d.norm_eps);
+            add_gemv(QKV, D, PRO_RMSNORM, EPI_STORE, w.wqkv, nullptr, cur, w.attn_norm, nullptr, t.qkv, nullptr, nullptr,
+                     nullptr, d.norm_eps);
             AttnArgs a = make_attn_args(h, w, fast, pos, slots, pos_fixed);
             a.splits = fast ? 1 : splits;
+            a.qkv_t = t.qkv; a.y_t = t.y; a.ll_acc = h->ll_acc; a.ll_ml = h->ll_ml;
+            a.pf_ptr = nullptr; a.pf_bytes = getenv("FSB_ATTN_TRACE_POINT") ? (size_t)atoi(getenv("FSB_ATTN_TRACE_POINT")) : 0;
+            if (!fast && (&w - &L[0]) + 1 < (long)L.size()) { a.next_k = (&w)[1].kc; a.next_v = (&w)[1].vc; }
+            if (d.qk_norm) { add_hot(w.q_norm, (size_t)HD * 2); add_hot(w.k_norm, (size_t)HD * 2); }
+            if (fast) add_hot(h->fast_rope + (size_t)pos_fixed * HD, (size_t)HD * 2);
+            a.tag_in_op = writer_of(t.qkv); a.tag_out_op = (int)ops.size();
             attn.push_back(a);
-            op(fast ? MOP_FATTN : MOP_ATTN, (int)attn.size() - 1, MSYNC_GRID);
-            add_gemv(D, H * HD, PRO_NONE, EPI_RESIDUAL, w.wo, nullptr, h->y, nullptr, cur, xb, nullptr, d.norm_eps);
-            add_gemv(F, D, PRO_RMSNORM, EPI_SWIGLU, w.w1, w.w3, xb, w.ffn_norm, nullptr, h->ff, nullptr, d.norm_eps);
-            add_gemv(D, F, PRO_NONE, EPI_RESIDUAL, w.w2, nullptr, h->ff, nullptr, xb, xa, nullptr, d.norm_eps);
+            op(fast ? MOP_FATTN : MOP_ATTN, (int)attn.size() - 1, MSYNC_CTA);
+            wrote(t.y);
+            add_gemv(D, H * HD, PRO_NONE, EPI_RESIDUAL, w.wo, nullptr, t.y, nullptr, cur, xb, nullptr, nullptr, nullptr,
+                     d.norm_eps);
+            add_gemv(F, D, PRO_RMSNORM, EPI_SWIGLU, w.w1, w.w3, xb, w.ffn_norm, nullptr, t.ff, nullptr, nullptr, nullptr,
+                     d.norm_eps);
+            add_gemv(D, F, PRO_NONE, EPI_RESIDUAL, w.w2, nullptr, t.ff, nullptr, xb, xa, nullptr, nullptr, nullptr,
+                     d.norm_eps);
             cur = xa;
         }
     }
@@ -529,26 +581,45 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     if (int r = check_bound(h)) return r;
     const int C = d.num_codebooks;
     MegaBuilder mb;
-    mb.op(MOP_EMBED, 0, MSYNC_GRID);
+    mb.n_cta = h->n_sm;
+    const MegaTagged t(h);
+    mb.op(MOP_EMBED, 0, MSYNC_CTA);
+    mb.wrote(t.x2);
     int splits = h->attn_splits > 0 ? h->attn_splits : std::max(1, h->n_sm / d.n_kv_head);
-    splits = std::max(1, std::min(splits, h->max_splits));
-    mb.add_layers(h, false, h->x2, fa.pos, fa.slots, -1, splits);
+    const int msplit = std::min(h->max_splits, ASP_MAXS);
+    splits = std::max(1, std::min(splits, msplit));
+    // the frame kernel's attention holds a split's whole key range in one tile
+    while (splits < msplit && (h->kv_max_seq + splits - 1) / splits > asp_max_keys(d.head_dim)) ++splits;
+    if ((h->kv_max_seq + splits - 1) / splits > asp_max_keys(d.head_dim))
+        return fail(h, "context too long for the persistent frame kernel (set option mega=0)");
+    mb.add_layers(h, t, false, t.x2, fa.pos, fa.slots, -1, splits);
     const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
-    mb.add_gemv(d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head, nullptr, h->x, h->norm, nullptr, h->slow_logits, h->hidden,
-                d.norm_eps);
-    mb.samp.push_back(make_slow_sample(h, fa));
-    mb.op(MOP_SAMPLE, 0, MSYNC_GRID);
-    const bf16* fin = d.norm_fastlayer_input ? h->hidden : h->x;
-    mb.add_layers(h, true, fin, nullptr, nullptr, 0, 1);
+    mb.add_gemv(d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head, nullptr, t.x, h->norm, nullptr, nullptr, h->slow_logits,
+                h->hidden, t.hidden, d.norm_eps);
+    {
+        SampleArgs sa = make_slow_sample(h, fa);
+        sa.xfast_t = t.xfast;
+        mb.samp.push_back(sa);
+        mb.op(MOP_SAMPLE, 0, MSYNC_CTA);
+        mb.wrote(t.xfast);
+    }
+    const uint32_t* fin = d.norm_fastlayer_input ? t.hidden : t.x;
+    mb.add_layers(h, t, true, fin, nullptr, nullptr, 0, 1);
     for (int i = 1; i < C; ++i) {
-        mb.add_layers(h, true, h->xfast, nullptr, nullptr, i, 1);
-        mb.add_gemv(d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE, h->fast_out, nullptr, h->xf, h->fast_norm, nullptr,
-                    h->fast_logits + (size_t)i * h->R * d.codebook_size, nullptr, d.norm_eps);
-        mb.samp.push_back(make_fast_sample(h, fa, i));
-        mb.op(MOP_SAMPLE, (int)mb.samp.size() - 1, i + 1 < C ? MSYNC_GRID : MSYNC_CTA);  // last: only CTA 0 follows
+        mb.add_layers(h, t, true, t.xfast, nullptr, nullptr, i, 1);
+        mb.add_gemv(d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE, h->fast_out, nullptr, t.xf, h->fast_norm, nullptr,
+                    nullptr, h->fast_logits + (size_t)i * h->R * d.codebook_size, nullptr, nullptr, d.norm_eps);
+        SampleArgs fs = make_fast_sample(h, fa, i);
+        fs.xfast_t = (i + 1 < C) ? t.xfast : nullptr;
+        mb.samp.push_back(fs);
+        mb.op(MOP_SAMPLE, (int)mb.samp.size() - 1, MSYNC_CTA);
+        if (i + 1 < C) mb.wrote(t.xfast);
     }
     mb.op(MOP_END, 0, MSYNC_NONE);
-    const EmbedArgs emb = make_embed_args(h, fa.cur_tokens);
+    if (fa.logit_bias) mb.add_hot(fa.logit_bias, (size_t)d.vocab * 2);
+    if ((int)mb.ops.size() >= 512) return fail(h, "frame has too many ops for the 9-bit op field of the activation tags");
+    EmbedArgs emb = make_embed_args(h, fa.cur_tokens);
+    emb.x_t = t.x2;
     const FrameEndArgs fend = make_frame_end(h, fa);
 
     // pack: [ops][gemv][attn][samp][embed][fend], each 16-byte aligned
@@ -556,7 +627,8 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     auto place = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 16); return o; };
     const size_t o_ops = place(mb.ops.size() * sizeof(MegaOp)), o_g = place(mb.gemv.size() * sizeof(MegaGemv)),
                  o_a = place(mb.attn.size() * sizeof(AttnArgs)), o_s = place(mb.samp.size() * sizeof(SampleArgs)),
-                 o_e = place(sizeof(EmbedArgs)), o_f = place(sizeof(FrameEndArgs));
+                 o_e = place(sizeof(EmbedArgs)), o_f = place(sizeof(FrameEndArgs)),
+                 o_h = place(mb.hot.size() * sizeof(uint4));
     if (off > MEGA_BUF_BYTES) return fail(h, "frame op list exceeds its device buffer");
     h->mega_host.assign(off, 0);
     char* hp = h->mega_host.data();
@@ -566,14 +638,17 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     memcpy(hp + o_s, mb.samp.data(), mb.samp.size() * sizeof(SampleArgs));
     memcpy(hp + o_e, &emb, sizeof(EmbedArgs));
     memcpy(hp + o_f, &fend, sizeof(FrameEndArgs));
+    memcpy(hp + o_h, mb.hot.data(), mb.hot.size() * sizeof(uint4));
     CK(cudaMemcpyAsync(h->mega_buf, hp, off, cudaMemcpyHostToDevice, s));
     MegaPlan& p = h->mega_plan;
     p.ops = (const MegaOp*)(h->mega_buf + o_ops); p.n_ops = (int)mb.ops.size(); p.B = 1;
-    p.gemv = (const MegaGemv*)(h->mega_buf + o_g); p.attn = (const AttnArgs*)(h->mega_buf + o_a);
+    p.gemv = (const MegaGemv*)(h->mega_buf + o_g); p.n_gemv = (int)mb.gemv.size(); p.attn = (const AttnArgs*)(h->mega_buf + o_a);
     p.samp = (const SampleArgs*)(h->mega_buf + o_s); p.embed = (const EmbedArgs*)(h->mega_buf + o_e);
     p.fend = (const FrameEndArgs*)(h->mega_buf + o_f); p.sync = h->mega_sync;
     p.prof = h->mega_prof_on ? h->mega_prof : nullptr;
     p.pf_stages = h->mega_pf_stages;
+    p.hot = (const uint4*)(h->mega_buf + o_h); p.n_hot = (int)mb.hot.size(); p.n_attn_slow = d.n_layer;
+    p.debug_l2 = getenv("FSB_MEGA_DEBUG_L2") ? atoi(getenv("FSB_MEGA_DEBUG_L2")) : 0;
     p.trace = (h->mega_trace_on && (size_t)h->n_sm * mb.ops.size() * 4 <= MEGA_TRACE_WORDS) ? h->mega_trace : nullptr;
     p.copy_bytes = std::max(1024, h->mega_copy_bytes) & ~15;
     return 0;
@@ -623,6 +698,10 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
     T(ws_ml, float, R * d.n_kv_head * max_splits * gq * 2)
     T(counters, int32_t, R * d.n_kv_head)
     T(mega_buf, char, MEGA_BUF_BYTES) T(mega_sync, unsigned, 64) T(mega_prof, unsigned long long, 16)
+    // flag-in-data activations of the persistent frame kernel (batch 1): one u32 per element
+    const size_t tg = (size_t)2 * d.dim + QKV + (size_t)d.n_head * d.head_dim + d.ffn + (size_t)4 * d.dim;
+    T(tg_base, uint32_t, tg)
+    T(ll_acc, uint2, (size_t)d.n_kv_head * max_splits * gq * d.head_dim) T(ll_ml, uint2, (size_t)d.n_kv_head * max_splits * gq * 2)
     T(mega_trace, unsigned long long, MEGA_TRACE_WORDS)
     T(pf_pos, int32_t, (size_t)max_seq_len + 8) T(pf_slot, int32_t, (size_t)max_seq_len + 8)
 #undef T
@@ -663,6 +742,16 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
     CK(set_gemv_tma_attrs());
     CK(cudaMemset(h->counters, 0, (size_t)std::max(d.max_rows, 8) * d.n_kv_head * sizeof(int32_t)));
     CK(cudaMemset(h->mega_sync, 0, 64 * sizeof(unsigned)));
+    {
+        const unsigned one = 1;  // launch sequence starts at 1: tag 0 (the cleared buffers) is never expected
+        CK(cudaMemcpy(h->mega_sync + 2, &one, sizeof(one), cudaMemcpyHostToDevice));
+        h->tg_words = (size_t)2 * d.dim + (size_t)(d.n_head + 2 * d.n_kv_head) * d.head_dim +
+                      (size_t)d.n_head * d.head_dim + d.ffn + (size_t)4 * d.dim;
+        CK(cudaMemset(h->tg_base, 0, h->tg_words * sizeof(uint32_t)));
+        const size_t gq_ = d.n_head / d.n_kv_head;
+        CK(cudaMemset(h->ll_acc, 0, (size_t)d.n_kv_head * h->max_splits * gq_ * d.head_dim * sizeof(uint2)));
+        CK(cudaMemset(h->ll_ml, 0, (size_t)d.n_kv_head * h->max_splits * gq_ * 2 * sizeof(uint2)));
+    }
     CK(cudaMemset(h->mega_prof, 0, 16 * sizeof(unsigned long long)));
     if (mega_shape_ok(d)) {
         mega_fn mf = pick_mega(d.head_dim, d.n_head / d.n_kv_head);

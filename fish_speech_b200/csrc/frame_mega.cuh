@@ -8,7 +8,10 @@
 //   * the producer walks the frame's op list and streams EVERY GEMV's weight rows of this CTA through one ring of
 //     MG_NST x 20 KB shared-memory stages, one contiguous cp.async.bulk per stage (whole rows: R rows x K columns,
 //     16-20 KB per copy), throttled only by the ring — it runs ahead of the dependent chain across op boundaries;
-//   * consumers execute the ops in order; dependent ops are separated by a grid barrier (release/acquire counter);
+//   * consumers execute the ops in order.  Activations travel between ops as flag-in-data words (common.cuh): the
+//     consumer of a vector spins on the tags of the words it has to load anyway, so dependent ops need no fence, no
+//     grid barrier and no reload; a grid barrier (release/acquire counter) remains only in front of the sampling ops,
+//     which read plain bf16 logits;
 //   * a stage holds R whole rows and belongs to ONE of four consumer groups (4 warps each): stage n -> group n % 4, ring
 //     slot n % 8, so a slot's full/empty barriers are only ever used by its own group (no cross-group coupling) and
 //     four stages are in different phases of wait / FMA / reduce / epilogue at any time;
@@ -35,30 +38,47 @@ enum { MOP_EMBED = 0, MOP_GEMV = 1, MOP_ATTN = 2, MOP_FATTN = 3, MOP_SAMPLE = 4,
 enum { MSYNC_NONE = 0, MSYNC_GRID = 1, MSYNC_CTA = 2 };
 
 struct MegaGemv {
-    const bf16 *W, *W2, *x, *norm_w, *res;
-    bf16 *out, *xnorm_out;
+    const bf16 *W, *W2, *norm_w;
+    const uint32_t *x_t, *res_t;  // flag-in-data input vector [K] / residual [N]
+    uint32_t* out_t;              // flag-in-data output [N], or nullptr when the output is plain bf16 logits
+    bf16* out;                    // plain output (LM heads), or nullptr
+    bf16* xnorm_out;              // plain copy of the normalised input ("hidden"), CTA 0 only, or nullptr
+    uint32_t* xnorm_out_t;        // flag-in-data copy of the same (tag = this op)
     int N, K, pro, epi;
     float eps;
     int rshift;  // log2(rows per stage); rows * K * 2 <= MG_STAGE_BYTES
+    int x_op;    // index of the op that produced x_t (its tag)
+    int rows_q, rows_rem;  // N / grid, N % grid: CTA b owns rows [b*q + min(b, rem), +q + (b < rem)) — no division on device
+    int pad_[5];
 };
+static_assert(sizeof(MegaGemv) % 16 == 0, "MegaGemv is copied in 16-byte words");
 struct MegaOp { int type, idx, sync, pad; };
 struct MegaPlan {
     const MegaOp* ops;
     int n_ops, B;
     const MegaGemv* gemv;
+    int n_gemv;  // GEMV ops are stored in frame order: the producer walks this array alone
+    int n_attn_slow;  // attn[0 .. n_attn_slow) are the slow layers in order
     const AttnArgs* attn;
     const SampleArgs* samp;
     const EmbedArgs* embed;
     const FrameEndArgs* fend;
-    unsigned* sync;  // [0] barrier arrivals, [1] exits; both zero between launches
+    unsigned* sync;  // [0] barrier arrivals, [1] exits (both zero between launches), [2] launch sequence number
     unsigned long long* prof;  // optional [16] cycle counters of CTA 0 (profiling aid), or nullptr
     int pf_stages;             // L2 prefetch look-ahead of the weight stream, in ring stages (0 = off)
     int copy_bytes;            // bulk-copy granularity inside a stage (multiple of 16)
+    const uint4* hot;          // [n_hot] {ptr lo, ptr hi, bytes, 0}: small operands every CTA reads on the critical path
+    int n_hot;                 // (norm weights, RoPE rows, sampling bias): prefetched into L2 with evict_last at launch
+    int debug_l2;              // timing experiment only: stream every stage from the CTA's first rows (wrong results)
     unsigned long long* trace; // optional [grid][n_ops][4] globaltimer stamps (op start, x staged, op end, barrier passed)
 };
 enum { MP_XSTAGE = 0, MP_LOOP, MP_GRID, MP_ATTN, MP_FATTN, MP_SAMPLE, MP_MISC, MP_TOTAL, MP_FRAMES };
 
 typedef SyncNamed<1, MG_CONSUMERS> MgAll;
+
+// tag of op `oi` in the launch with sequence number `seq`: unique among everything written in this and the previous
+// launch (every activation word is rewritten at least once per launch), never 0 in the first launches
+__device__ __forceinline__ unsigned mg_tag(unsigned seq, int oi) { return ((seq << 9) + (unsigned)oi) & 0xffffu; }
 
 __device__ __forceinline__ unsigned long long mg_now() {
     unsigned long long t;
@@ -95,10 +115,10 @@ __device__ __forceinline__ void mg_grid_sync(unsigned* ctr, unsigned& epoch, int
 // ever skipped and slot ownership stays fixed.
 struct MgGeom {
     int r0, r1, ngroups, total, ns, rshift;
-    __device__ __forceinline__ MgGeom(int N, int epi, int rshift_, int b, int nb) {
+    __device__ __forceinline__ MgGeom(int rows_q, int rows_rem, int epi, int rshift_, int b) {
         rshift = rshift_;
-        r0 = (int)(((long long)N * b) / nb);
-        r1 = (int)(((long long)N * (b + 1)) / nb);
+        r0 = b * rows_q + min(b, rows_rem);
+        r1 = r0 + rows_q + (b < rows_rem ? 1 : 0);
         ngroups = (r1 - r0 + (1 << rshift) - 1) >> rshift;
         ns = (epi == EPI_SWIGLU) ? 1 : 0;
         total = ((ngroups + 3) >> 2) << (2 + ns);
@@ -106,51 +126,6 @@ struct MgGeom {
     __device__ __forceinline__ void decode(int it, int& q, int& gi) const {
         q = (it >> 2) & ns;
         gi = ((it >> (2 + ns)) << 2) + (it & 3);
-    }
-};
-
-// walks the stage sequence of this CTA over all GEMV ops of the frame (the order consumers use); non-GEMV ops are
-// reported through `other` so the look-ahead cursor can prefetch their operands
-struct MgCursor {
-    const MegaPlan& p;
-    int b, nb, oi, it;
-    bool have;
-    int K, R, rshift, r0, r1, ngroups, total, ns;
-    const bf16 *W, *W2;
-    __device__ __forceinline__ MgCursor(const MegaPlan& p_, int b_, int nb_)
-        : p(p_), b(b_), nb(nb_), oi(0), it(0), have(false) {}
-    // false at the end of the frame; bytes == 0 for an empty stage
-    template <class OtherOp>
-    __device__ __forceinline__ bool next(const bf16*& src, uint32_t& bytes, OtherOp other) {
-        for (;;) {
-            if (!have) {
-                while (oi < p.n_ops) {
-                    const MegaOp op = p.ops[oi];
-                    if (op.type == MOP_GEMV) break;
-                    other(op);
-                    ++oi;
-                }
-                if (oi >= p.n_ops) return false;
-                const MegaGemv* g = p.gemv + p.ops[oi].idx;
-                const MgGeom geo(g->N, g->epi, g->rshift, b, nb);
-                K = g->K; W = g->W; W2 = g->W2; rshift = geo.rshift; R = 1 << rshift;
-                r0 = geo.r0; r1 = geo.r1; ngroups = geo.ngroups; total = geo.total; ns = geo.ns;
-                it = 0;
-                have = true;
-            }
-            if (it < total) {
-                const int i = it++;
-                const int q = (i >> 2) & ns, gi = ((i >> (2 + ns)) << 2) + (i & 3);
-                if (gi >= ngroups) { src = W; bytes = 0; return true; }
-                const int g0 = r0 + (gi << rshift);
-                const int ng = min(R, r1 - g0);
-                src = (q ? W2 : W) + (size_t)g0 * K;
-                bytes = (uint32_t)ng * (uint32_t)K * 2u;
-                return true;
-            }
-            have = false;
-            ++oi;
-        }
     }
 };
 
@@ -162,80 +137,82 @@ __device__ __forceinline__ void bulk_g2s_evict_first(void* dst_smem, const void*
         "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
         : "memory");
 }
-__device__ __forceinline__ void l2_prefetch_range(const void* p, size_t bytes) {
-    const char* c = (const char*)((uintptr_t)p & ~(uintptr_t)15);
-    size_t n = (bytes + ((uintptr_t)p & 15) + 15) & ~(size_t)15;
-    while (n > 0) {
-        const uint32_t k = n > 32768 ? 32768u : (uint32_t)n;
-        l2_prefetch_bulk(c, k);
-        c += k; n -= k;
-    }
+__device__ __forceinline__ bool mbar_test(uint64_t* b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(b)), "r"(parity)
+        : "memory");
+    return ok != 0;
 }
 
-// operands of the attention ops that do not depend on this frame's activations: this CTA's KV split, RoPE row, norms
-template <int HD>
-__device__ __forceinline__ void mg_prefetch_attn(const MegaPlan& p, const MegaOp& op, int b) {
-    if (op.type != MOP_ATTN && op.type != MOP_FATTN) return;
-    const AttnArgs* a = p.attn + op.idx;
-    const int KV = a->KV;
-    if (op.type == MOP_ATTN) {
-        const int splits = a->splits;
-        if (b >= KV * splits * p.B) return;
-        const int split = b % splits, hm = b / splits, h = hm % KV, m = hm / KV;
-        const int pos = a->pos[m];
-        const int slot = a->slots ? a->slots[m] : m;
-        const int per = (pos + 1 + splits - 1) / splits;
-        const int k0 = split * per, k1 = min(pos, k0 + per);  // key `pos` itself is produced in this frame
-        const size_t base = ((size_t)slot * KV + h) * a->S * HD;
-        if (k1 > k0) {
-            l2_prefetch_range(a->kcache + base + (size_t)k0 * HD, (size_t)(k1 - k0) * HD * 2);
-            l2_prefetch_range(a->vcache + base + (size_t)k0 * HD, (size_t)(k1 - k0) * HD * 2);
+// Producer warp: lane l (< MG_NST) owns ring slot l, i.e. the stages n = l, l + 8, l + 16, ... of this CTA's stream over
+// ALL GEMV ops of the frame.  Eight lanes poll their slots' empty barriers and issue their bulk copies independently
+// (a single in-order producer thread was the bottleneck: ~450 cycles of dependent integer code per 20 KB stage).
+// Each lane walks the GEMV list on its own; the list is immutable, so it is read through the read-only path (L1).
+struct MgLaneCursor {
+    const MegaGemv* gl;
+    int n_gemv, b, j, it;
+    int K, rshift, r0, r1, ngroups, total, ns;
+    const bf16 *W, *W2;
+    bool live;
+    __device__ __forceinline__ void load(int jj) {
+        const MegaGemv* g = gl + jj;
+        const MgGeom geo(__ldg(&g->rows_q), __ldg(&g->rows_rem), __ldg(&g->epi), __ldg(&g->rshift), b);
+        K = __ldg(&g->K);
+        W = (const bf16*)__ldg((const unsigned long long*)&g->W);
+        W2 = (const bf16*)__ldg((const unsigned long long*)&g->W2);
+        rshift = geo.rshift; r0 = geo.r0; r1 = geo.r1; ngroups = geo.ngroups; total = geo.total; ns = geo.ns;
+    }
+    __device__ __forceinline__ void normalise() {
+        while (live && it >= total) {
+            it -= total;
+            if (++j >= n_gemv) { live = false; break; }
+            load(j);
         }
-        l2_prefetch_range(a->rope + (size_t)pos * HD, HD * 2);
-    } else {
-        if (b >= KV * p.B) return;
-        l2_prefetch_range(a->rope + (size_t)a->pos_fixed * HD, HD * 2);
     }
-    if (a->qk_norm) { l2_prefetch_range(a->q_norm, HD * 2); l2_prefetch_range(a->k_norm, HD * 2); }
-}
+    __device__ __forceinline__ MgLaneCursor(const MegaPlan& p, int b_, int first)
+        : gl(p.gemv), n_gemv(p.n_gemv), b(b_), j(0), it(first) {
+        live = n_gemv > 0;
+        if (live) { load(0); normalise(); }
+    }
+    __device__ __forceinline__ void stage(const bf16*& src, uint32_t& bytes) const {
+        const int q = (it >> 2) & ns, gi = ((it >> (2 + ns)) << 2) + (it & 3);
+        if (gi >= ngroups) { src = W; bytes = 0; return; }
+        const int g0 = r0 + (gi << rshift);
+        const int ng = min(1 << rshift, r1 - g0);
+        src = (q ? W2 : W) + (size_t)g0 * K;
+        bytes = (uint32_t)ng * (uint32_t)K * 2u;
+    }
+    __device__ __forceinline__ void advance(int k) { it += k; normalise(); }
+};
 
-// producer thread: the smem ring is filled in order; an L2 prefetch cursor runs `pf_stages` stages ahead of it, so the
-// HBM stream keeps going while the consumers sit in a barrier / attention / sampling op and the ring is full
 template <int HD>
 __device__ __forceinline__ void mg_producer(const MegaPlan& p, unsigned char* stages, uint64_t* full_bar,
-                                            uint64_t* empty_bar, int b, int nb) {
+                                            uint64_t* empty_bar, int b, int lane) {
+    if (lane >= MG_NST) return;
     uint64_t policy;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
-    MgCursor cp(p, b, nb), pf(p, b, nb);
-    const bf16* src;
-    uint32_t bytes;
-    bool pf_live = p.pf_stages > 0;
-    auto pf_other = [&](const MegaOp& op) { mg_prefetch_attn<HD>(p, op, b); };
-    auto no_other = [](const MegaOp&) {};
-    for (int i = 0; i < p.pf_stages && pf_live; ++i) {
-        pf_live = pf.next(src, bytes, pf_other);
-        if (pf_live && bytes) l2_prefetch_bulk(src, bytes);
-    }
-    unsigned n = 0;
-    const uint32_t chunk = (uint32_t)p.copy_bytes;
-    while (cp.next(src, bytes, no_other)) {
-        if (pf_live) {
-            const bf16* s2;
-            uint32_t b2;
-            pf_live = pf.next(s2, b2, pf_other);
-            if (pf_live && b2) l2_prefetch_bulk(s2, b2);
+    MgLaneCursor cur(p, b, lane);
+    unsigned char* dst = stages + (size_t)lane * MG_STAGE_BYTES;
+    unsigned round = 0, spins = 0;
+    long long t0 = 0;
+    while (cur.live) {
+        if (!mbar_test(&empty_bar[lane], (round & 1u) ^ 1u)) { spin_watchdog(spins, t0); continue; }
+        const bf16* src;
+        uint32_t bytes;
+        cur.stage(src, bytes);
+        if (bytes == 0) {
+            mbar_arrive(&full_bar[lane]);  // empty stage: the phase completes at once
+        } else {
+            mbar_expect_tx(&full_bar[lane], bytes);
+            bulk_g2s_evict_first(dst, src, bytes, &full_bar[lane], policy);
         }
-        const unsigned slot = n & (MG_NST - 1), ph = (n / MG_NST) & 1u;
-        ++n;
-        mbar_wait(&empty_bar[slot], ph ^ 1u);
-        if (bytes == 0) { mbar_arrive(&full_bar[slot]); continue; }  // empty stage: the phase completes at once
-        mbar_expect_tx(&full_bar[slot], bytes);
-        unsigned char* dst = stages + (size_t)slot * MG_STAGE_BYTES;
-        const char* sp = (const char*)src;
-        for (uint32_t o = 0; o < bytes; o += chunk) {
-            const uint32_t c = min(chunk, bytes - o);
-            bulk_g2s_evict_first(dst + o, sp + o, c, &full_bar[slot], policy);
-        }
+        ++round;
+        cur.advance(MG_NST);
     }
 }
 
@@ -244,7 +221,8 @@ __device__ __forceinline__ void mg_group_sync(int group) {
 }
 
 // epilogue of one output row (lane 0 of the finalising warp); rounding points as in gemv.cuh
-__device__ __forceinline__ void mg_finish_row(const MegaGemv& g, size_t oi, float s, float s2, float resv) {
+__device__ __forceinline__ void mg_finish_row(const MegaGemv& g, size_t oi, float s, float s2, float resv,
+                                              unsigned tag_out) {
     float o = rbf(s);
     if (g.epi == EPI_RESIDUAL) {
         o = resv + o;
@@ -253,7 +231,8 @@ __device__ __forceinline__ void mg_finish_row(const MegaGemv& g, size_t oi, floa
         const float sl = rbf(__fdiv_rn(o, 1.f + expf(-o)));
         o = sl * u;
     }
-    g.out[oi] = __float2bfloat16_rn(o);
+    if (g.out_t != nullptr) st_tagged(g.out_t + oi, o, tag_out);
+    else g.out[oi] = __float2bfloat16_rn(o);
 }
 
 // dot product of one row segment in shared memory with the activation chunks of the same columns, MG_CPL chunks per lane
@@ -284,44 +263,93 @@ __device__ __forceinline__ float mg_dot(const uint4* w0, const uint4* xs, int c_
 
 __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stages, uint4* xs, uint64_t* full_bar,
                                         uint64_t* empty_bar, float* red, float (*pbuf)[2][2][4], unsigned& n, int b,
-                                        int nb, int tid, unsigned long long* prof, unsigned long long* trace) {
+                                        int nb, int tid, unsigned seq, int oi, unsigned long long* prof,
+                                        unsigned long long* trace) {
     const long long tp0 = prof ? clock64() : 0;
     const int lane = tid & 31, warp = tid >> 5;
     const int grp = warp >> 2, wg = warp & 3;
-    const MegaGemv g = *gp;
+    MegaGemv g;
+    {   // immutable plan data: read-only path (L1); the next op's entry was prefetched while the previous op ran
+        const uint4* src = reinterpret_cast<const uint4*>(gp);
+        uint4* dst = reinterpret_cast<uint4*>(&g);
+#pragma unroll
+        for (int i = 0; i < (int)(sizeof(MegaGemv) / 16); ++i) dst[i] = __ldg(src + i);
+    }
     const int K = g.K, K8 = K >> 3;
-    // ---- stage the activation row (one rounding chain: llama.py:995-1000 RMSNorm, double rounding)
-    const uint4* xg = reinterpret_cast<const uint4*>(g.x);
+    const unsigned tag_in = mg_tag(seq, g.x_op), tag_out = mg_tag(seq, oi);
+    // ---- stage the activation row: spin on the producer's tags while loading (this IS the inter-op dependency), keep
+    //      the chunks in registers for the RMSNorm second pass (llama.py:995-1000, double rounding)
+    constexpr int XC = (MG_X_BYTES / 16 + MG_CONSUMERS - 1) / MG_CONSUMERS;  // chunks of 8 elements per thread
+    uint4 nw[XC];  // RMSNorm weights of this thread's chunks: requested before the spin, they do not depend on x
+#pragma unroll
+    for (int i = 0; i < XC; ++i) {
+        const int c = tid + i * MG_CONSUMERS;
+        nw[i] = (g.pro == PRO_RMSNORM && c < K8) ? __ldg(reinterpret_cast<const uint4*>(g.norm_w) + c) : make_uint4(0, 0, 0, 0);
+    }
+    uint4 xv[XC];
+    {
+        // all of this thread's words are requested together and re-requested together until every tag is current: one
+        // L2 round trip once the producer is done (a word-by-word spin would serialise up to 2*XC round trips)
+        unsigned spins = 0;
+        long long t0 = 0;
+        bool ok;
+        do {
+            ok = true;
+#pragma unroll
+            for (int i = 0; i < XC; ++i) {
+                const int c = tid + i * MG_CONSUMERS;
+                uint2 lo = make_uint2(0, 0), hi = make_uint2(0, 0);
+                if (c < K8) {
+                    ok &= ld_tagged4_try(g.x_t + (size_t)c * 8, tag_in, lo);
+                    ok &= ld_tagged4_try(g.x_t + (size_t)c * 8 + 4, tag_in, hi);
+                }
+                xv[i] = make_uint4(lo.x, lo.y, hi.x, hi.y);
+            }
+            if (!ok) spin_watchdog(spins, t0);
+        } while (!ok);
+    }
     if (g.pro == PRO_RMSNORM) {
         float ss = 0.f;
-        for (int c = tid; c < K8; c += MG_CONSUMERS) {
-            float f[8];
-            unpack8(lda(&xg[c]), f);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) ss += f[i] * f[i];
+        for (int i = 0; i < XC; ++i) {
+            float f[8];
+            unpack8(xv[i], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) ss += f[e] * f[e];
         }
         ss = group_sum<MgAll>(ss, red, tid);
         const float rs = __frsqrt_rn(__fadd_rn(__fdiv_rn(ss, (float)K), g.eps));
-        const uint4* wgt = reinterpret_cast<const uint4*>(g.norm_w);
-        for (int c = tid; c < K8; c += MG_CONSUMERS) {
-            float f[8], w[8];
-            unpack8(lda(&xg[c]), f);
-            unpack8(wgt[c], w);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = rbf(__fmul_rn(f[i], rs)) * w[i];
-            uint4 o;
-            o.x = pack2(f[0], f[1]); o.y = pack2(f[2], f[3]); o.z = pack2(f[4], f[5]); o.w = pack2(f[6], f[7]);
-            if (g.xnorm_out != nullptr && b == 0) reinterpret_cast<uint4*>(g.xnorm_out)[c] = o;
-            xs[c] = o;
+        for (int i = 0; i < XC; ++i) {
+            const int c = tid + i * MG_CONSUMERS;
+            if (c < K8) {
+                float f[8], w[8];
+                unpack8(xv[i], f);
+                unpack8(nw[i], w);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] = rbf(__fmul_rn(f[e], rs)) * w[e];
+                uint4 o;
+                o.x = pack2(f[0], f[1]); o.y = pack2(f[2], f[3]); o.z = pack2(f[4], f[5]); o.w = pack2(f[6], f[7]);
+                if (b == 0 && g.xnorm_out != nullptr) reinterpret_cast<uint4*>(g.xnorm_out)[c] = o;
+                if (b == 0 && g.xnorm_out_t != nullptr) {
+                    st_tagged4(g.xnorm_out_t + (size_t)c * 8, o.x, o.y, tag_out);
+                    st_tagged4(g.xnorm_out_t + (size_t)c * 8 + 4, o.z, o.w, tag_out);
+                }
+                xs[c] = o;
+            }
         }
     } else {
-        for (int c = tid; c < K8; c += MG_CONSUMERS) xs[c] = lda(&xg[c]);
+#pragma unroll
+        for (int i = 0; i < XC; ++i) {
+            const int c = tid + i * MG_CONSUMERS;
+            if (c < K8) xs[c] = xv[i];
+        }
     }
     MgAll::sync();
     const long long tp1 = prof ? clock64() : 0;
     if (trace && tid == 0) trace[1] = mg_now();
 
-    const MgGeom geo(g.N, g.epi, g.rshift, b, nb);
+    const MgGeom geo(g.rows_q, g.rows_rem, g.epi, g.rshift, b);
     const int R = 1 << geo.rshift;
     // rows per warp / warps per row inside a stage: R = 8: 2 rows per warp; 4: 1; 2: two warps per row; 1: four
     const int rpw = (R >= 8) ? 2 : 1;
@@ -347,7 +375,7 @@ __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stage
         if (g.epi == EPI_RESIDUAL && lane == 0 && seg == 0) {
 #pragma unroll
             for (int r = 0; r < 2; ++r)
-                if (r < rpw && row0 + 4 * r < ng) resv[r] = lda(&g.res[(size_t)(g0 + row0 + 4 * r)]);
+                if (r < rpw && row0 + 4 * r < ng) resv[r] = ld_tagged_value(g.res_t + (size_t)(g0 + row0 + 4 * r));
         }
         mbar_wait(&full_bar[slot], ph);
         const unsigned char* st = stages + (size_t)slot * MG_STAGE_BYTES;
@@ -367,7 +395,7 @@ __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stage
                     const int row = row0 + 4 * r;
                     if (r < rpw && row < ng) {
                         if (!last_q) acc0[r] = part[r];
-                        else mg_finish_row(g, (size_t)(g0 + row), geo.ns ? acc0[r] : part[r], part[r], resv[r]);
+                        else mg_finish_row(g, (size_t)(g0 + row), geo.ns ? acc0[r] : part[r], part[r], resv[r], tag_out);
                     }
                 }
             }
@@ -380,7 +408,7 @@ __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stage
                     for (int j = 0; j < SEGW; ++j) s += pbuf[grp][par][0][wg + j];
                     if (geo.ns)
                         for (int j = 0; j < SEGW; ++j) s2 += pbuf[grp][par][1][wg + j];
-                    mg_finish_row(g, (size_t)(g0 + row0), s, s2, resv[0]);
+                    mg_finish_row(g, (size_t)(g0 + row0), s, s2, resv[0], tag_out);
                 }
                 par ^= 1;
             }
@@ -400,6 +428,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) frame_mega_kernel(MegaPlan p) {
     __shared__ __align__(8) uint64_t empty_bar[MG_NST];
     __shared__ float red[32];
     __shared__ float pbuf[MG_GROUPS][2][2][4];  // [group][parity][matrix][warp of group]
+    __shared__ AttnSplitSmem<HD, GQ> asm_;
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int nb = gridDim.x, b = blockIdx.x;
@@ -413,51 +442,88 @@ __global__ void __launch_bounds__(MG_THREADS, 1) frame_mega_kernel(MegaPlan p) {
     __syncthreads();
 
     if (warp == MG_CONSUMERS / 32) {  // producer warp: weights only, never waits for an activation
-        if ((tid & 31) == 0) mg_producer<HD>(p, stages, full_bar, empty_bar, b, nb);
+        mg_producer<HD>(p, stages, full_bar, empty_bar, b, tid & 31);
         return;
     }
 
-    typedef SyncNamed<6, ATTN_THREADS> AttnSync;
     typedef SyncNamed<6, 32 * GQ> FastSync;
     unsigned n = 0, epoch = 0;
+    const unsigned seq = p.sync[2];  // written by the previous launch's last CTA
+    if (tid < 32) {  // launch-time L2 prefetches (warp 0; nothing waits for them)
+        uint64_t keep;
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
+        for (int i = b * 32 + tid; i < p.n_hot; i += nb * 32) {
+            const uint4 hr = __ldg(p.hot + i);
+            const void* ptr = (const void*)(((unsigned long long)hr.y << 32) | hr.x);
+            asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" ::"l"(ptr), "r"(hr.z), "l"(keep) : "memory");
+        }
+        if (tid == 0 && p.n_attn_slow > 0) {
+            const AttnArgs* a0 = p.attn;
+            const int splits = a0->splits;
+            if (b < a0->KV * splits * p.B) {
+                const int hm = b / splits;
+                attn_split_prefetch<HD>(*a0, a0->kcache, a0->vcache, b % splits, hm % a0->KV, hm / a0->KV);
+            }
+        }
+    }
     unsigned long long* prof = (b == 0) ? p.prof : nullptr;
     const long long tk0 = prof ? clock64() : 0;
     for (int oi = 0; oi < p.n_ops; ++oi) {
-        const MegaOp op = p.ops[oi];
+        MegaOp op;
+        *reinterpret_cast<uint4*>(&op) = __ldg(reinterpret_cast<const uint4*>(p.ops + oi));
+        if (tid == 0 && oi + 1 < p.n_ops) {  // pull the next op's descriptors into L1 while this op runs
+            const MegaOp nx = p.ops[oi + 1];
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(p.ops + oi + 2));
+            if (op.type == MOP_GEMV && nx.type == MOP_ATTN) {  // pull this CTA's KV split into L2 one op ahead
+                const AttnArgs* an = p.attn + nx.idx;
+                const int splits = __ldg(&an->splits);
+                if (b < __ldg(&an->KV) * splits * p.B) {
+                    const AttnArgs a2 = *an;
+                    const int hm = b / splits;
+                    attn_split_prefetch<HD>(a2, a2.kcache, a2.vcache, b % splits, hm % a2.KV, hm / a2.KV);
+                }
+            }
+            if (nx.type == MOP_GEMV) {
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(p.gemv + nx.idx));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"((const char*)(p.gemv + nx.idx) + 64));
+            }
+        }
         const long long to0 = prof ? clock64() : 0;
         unsigned long long* tr = p.trace ? p.trace + ((size_t)b * p.n_ops + oi) * 4 : nullptr;
         if (tr && tid == 0) tr[0] = mg_now();
         switch (op.type) {
         case MOP_GEMV:
-            mg_gemv(p.gemv + op.idx, stages, xs, full_bar, empty_bar, red, pbuf, n, b, nb, tid, prof, tr);
+            mg_gemv(p.gemv + op.idx, stages, xs, full_bar, empty_bar, red, pbuf, n, b, nb, tid, seq, oi, prof, tr);
             break;
         case MOP_EMBED:
-            if (b < p.B) embed_body(*p.embed, b, tid, MG_CONSUMERS);
+            if (b < p.B) embed_body(*p.embed, b, tid, MG_CONSUMERS, mg_tag(seq, oi));
             break;
-        case MOP_ATTN:
-            if (tid < ATTN_THREADS) {
-                const AttnArgs a = p.attn[op.idx];
-                const int items = a.KV * a.splits * p.B;
-                for (int item = b; item < items; item += nb) {
-                    const int split = item % a.splits, hm = item / a.splits;
-                    attn_decode_body<HD, GQ, AttnSync, false>(a, split, hm % a.KV, hm / a.KV, tid);
-                    AttnSync::sync();
-                }
+        case MOP_ATTN: {
+            const AttnArgs a = p.attn[op.idx];
+            const int items = a.KV * a.splits * p.B;
+            for (int item = b; item < items; item += nb) {
+                const int split = item % a.splits, hm = item / a.splits;
+                if (tid == 0 && a.next_k != nullptr) attn_split_prefetch<HD>(a, a.next_k, a.next_v, split, hm % a.KV, hm / a.KV);
+                attn_split_body<HD, GQ, MgAll>(a, asm_, split, hm % a.KV, hm / a.KV, tid, mg_tag(seq, a.tag_in_op),
+                                               mg_tag(seq, a.tag_out_op), tr);
+                MgAll::sync();
             }
             break;
+        }
         case MOP_FATTN:
             if (tid < 32 * GQ) {
                 const AttnArgs a = p.attn[op.idx];
                 const int items = a.KV * p.B;
                 for (int item = b; item < items; item += nb) {
-                    fast_attn_body<HD, GQ, FastSync>(a, item % a.KV, item / a.KV, tid);
+                    fast_attn_body<HD, GQ, FastSync, true>(a, item % a.KV, item / a.KV, tid, mg_tag(seq, a.tag_in_op),
+                                                           mg_tag(seq, a.tag_out_op));
                     FastSync::sync();
                 }
             }
             break;
         case MOP_SAMPLE:
             for (int r = b; r < p.B; r += nb) {
-                sample_body<MgAll>(p.samp[op.idx], r, p.B, tid);
+                sample_body<MgAll>(p.samp[op.idx], r, p.B, tid, mg_tag(seq, oi));
                 MgAll::sync();
             }
             break;
@@ -486,6 +552,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) frame_mega_kernel(MegaPlan p) {
         if (old == (unsigned)nb - 1u) {
             p.sync[0] = 0u;
             p.sync[1] = 0u;
+            p.sync[2] = seq + 1u;
             __threadfence();
         }
     }

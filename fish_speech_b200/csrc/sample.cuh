@@ -44,6 +44,7 @@ struct SampleArgs {
     int32_t* done;             // [B] EOS flag (mode 1) or nullptr
     const bf16* fast_emb;      // [cb][D]: next fast-AR input row gathered here (llama.py fast_embeddings), or nullptr
     bf16* xfast;               // [B][D]
+    uint32_t* xfast_t;         // flag-in-data copy for the persistent frame kernel (written instead of xfast), or nullptr
     int D;
 };
 
@@ -133,7 +134,7 @@ __device__ __forceinline__ int block_excl_scan(int v, int* wsum, int* total, int
 
 // one request (row b of nB) on SY::NT threads; tid = index inside the group
 template <class SY>
-__device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, int tid) {
+__device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, int tid, unsigned xtag = 0) {
     constexpr int NT = SY::NT;
     __shared__ uint32_t hist[2048];
     __shared__ unsigned long long cand[SAMPLE_CAND_CAP];
@@ -373,8 +374,17 @@ __device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, 
     }
     if (a.fast_emb != nullptr) {  // next fast-AR input = fast_embeddings(code)
         const uint4* src = reinterpret_cast<const uint4*>(a.fast_emb + (size_t)tok * a.D);
-        uint4* dst = reinterpret_cast<uint4*>(a.xfast + (size_t)b * a.D);
-        for (int c = lane; c < (a.D >> 3); c += 32) dst[c] = src[c];
+        if (a.xfast_t != nullptr) {
+            for (int c = lane; c < (a.D >> 3); c += 32) {
+                const uint4 v = src[c];
+                uint32_t* d = a.xfast_t + (size_t)b * a.D + (size_t)c * 8;
+                st_tagged4(d, v.x, v.y, xtag);
+                st_tagged4(d + 4, v.z, v.w, xtag);
+            }
+        } else {
+            uint4* dst = reinterpret_cast<uint4*>(a.xfast + (size_t)b * a.D);
+            for (int c = lane; c < (a.D >> 3); c += 32) dst[c] = src[c];
+        }
     }
 }
 __global__ void __launch_bounds__(SAMPLE_THREADS, 1) sample_kernel(SampleArgs a) {

@@ -54,3 +54,37 @@ for k, v in agg.items():
     tot += float(t[:, 6].sum())
     print(f"{k:9s} {len(v):4d} {m[1]:8.2f} {m[2]:8.2f} {m[3]:8.2f} {m[4]:10.2f} {m[5]:8.2f} {m[6]:8.2f} {m[7]:7.2f}   {float(t[:, 6].sum()) / 1e3:8.3f}")
 print(f"sum of walls {tot / 1e3:.3f} ms")
+
+# detail of a few consecutive ops in the middle of the slow stack: per-CTA percentiles (us, relative to the first start)
+import os
+if os.environ.get("TRACE_DETAIL", "1") == "1":
+    base = 1 + 5 * 10
+    for o in range(base, base + 6):
+        st, x1, en, ba = tr[:, o, 0], tr[:, o, 1], tr[:, o, 2], tr[:, o, 3]
+        ref = float(tr[:, base, 0].min())
+        q = lambda v: "%.2f/%.2f/%.2f" % (float(v.min()) - ref, float(v.median()) - ref, float(v.max()) - ref)
+        print(f"op {o} {kinds[o]:6s} start {q(st)}  xstaged {q(x1)}  end {q(en)}")
+
+# per-CTA consistency: is the same CTA slow in every op of a kind?
+for kind in ("w13", "w2", "f.w13"):
+    idx = [o for o, k in enumerate(kinds) if k == kind]
+    loop = (tr[:, idx, 2] - tr[:, idx, 1])          # [cta, ops] loop duration
+    per_cta = loop.mean(1)
+    rank = loop.argsort(0).argsort(0).double()       # rank of each CTA within each op
+    rank_mean = rank.mean(1)
+    order = per_cta.argsort()
+    print(f"{kind}: loop us per CTA min {float(per_cta.min()):.2f} median {float(per_cta.median()):.2f} max {float(per_cta.max()):.2f};"
+          f" rank stability: slowest CTAs {order[-8:].tolist()} mean rank {[round(float(rank_mean[i])) for i in order[-8:]]}"
+          f" fastest {order[:8].tolist()} mean rank {[round(float(rank_mean[i])) for i in order[:8]]}")
+
+# attention ops: time from op start to "q ready" (tr[1]) and from there to the end, CTAs with an item only
+idx = [o for o, k in enumerate(kinds) if k == "attn"]
+a0, a1, a2 = tr[:, idx, 0], tr[:, idx, 1], tr[:, idx, 2]
+has = (a2 - a0) > 1.0
+has = has & (a1 > 0)
+wait_q = (a1 - a0)[has]
+rest = (a2 - a1)[has]
+print(f"attn items: start->q ready mean {float(wait_q.mean()):.2f} max {float(wait_q.max()):.2f} us; q ready->end mean {float(rest.mean()):.2f} median {float(rest.median()):.2f} max {float(rest.max()):.2f} us")
+comb = has & ((a2 - a0) > (a2 - a0)[has].median() + 2.0)
+if comb.any():
+    print(f"  combiner items only: start->point mean {float((a1 - a0)[comb].mean()):.2f} max {float((a1 - a0)[comb].max()):.2f}; point->end mean {float((a2 - a1)[comb].mean()):.2f} max {float((a2 - a1)[comb].max()):.2f}  (n={int(comb.sum())})")
