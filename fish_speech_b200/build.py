@@ -38,7 +38,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     srcs = [str(CSRC / s) for s in SOURCES if (CSRC / s).exists()]
-    cmd = [nvcc, *NVCC_FLAGS, "-o", str(LIB), *srcs, "-lcudart"]
+    cmd = [nvcc, *NVCC_FLAGS, "-o", str(LIB), *srcs, "-lcudart", "-lcublas"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
     (PKG / "build.log").write_text(" ".join(cmd) + "\n" + log)

@@ -1,5 +1,6 @@
 // Dual-AR decode engine: handle, launch plumbing (PDL-chained kernels, CUDA-graph replay) and the C ABI.
 // See include/fish_b200.h for the boundary and DESIGN.md for the kernel inventory.
+#include <cublas_v2.h>
 #include <cuda_runtime.h>
 
 #include <cmath>
@@ -14,6 +15,7 @@
 #include "gemv.cuh"
 #include "frame_mega.cuh"
 #include "gemv_tma.cuh"
+#include "prefill.cuh"
 #include "sample.cuh"
 
 namespace {
@@ -26,6 +28,7 @@ struct LayerW {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 constexpr size_t MEGA_BUF_BYTES = 512 * 1024;
+constexpr size_t CUBLAS_WS_BYTES = 32u << 20;
 constexpr size_t MEGA_TRACE_WORDS = 160 * 512 * 4;  // [CTAs][ops][4] time stamps of one frame (profiling aid)
 
 struct GemvCfg {
@@ -62,8 +65,12 @@ struct fsb_dual_ar {
     int mega_prof_on = 0;
     unsigned long long* mega_trace = nullptr;
     int mega_trace_on = 0;
-    int mega_copy_bytes = 5120;      // bulk-copy granularity inside a ring stage
-    int mega_pf_stages = 0;          // L2 prefetch look-ahead of the frame kernel's weight stream (ring stages)
+    // prompt pass scratch (PREFILL_ROWS rows each) and the cuBLAS handle used for its plain GEMMs
+    bf16 *pxa = nullptr, *pxb = nullptr, *pxn = nullptr, *pqkv = nullptr, *py = nullptr, *ptmp = nullptr, *pf1 = nullptr,
+         *pf3 = nullptr;
+    char* cublas_ws = nullptr;
+    cublasHandle_t blas = nullptr;
+    int prefill_gemm = 1;            // 1: whole-chunk prompt pass (cuBLAS GEMMs), 0: 8-row passes through the decode kernels
     int max_splits = 32;
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
@@ -646,11 +653,8 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     p.samp = (const SampleArgs*)(h->mega_buf + o_s); p.embed = (const EmbedArgs*)(h->mega_buf + o_e);
     p.fend = (const FrameEndArgs*)(h->mega_buf + o_f); p.sync = h->mega_sync;
     p.prof = h->mega_prof_on ? h->mega_prof : nullptr;
-    p.pf_stages = h->mega_pf_stages;
     p.hot = (const uint4*)(h->mega_buf + o_h); p.n_hot = (int)mb.hot.size(); p.n_attn_slow = d.n_layer;
-    p.debug_l2 = getenv("FSB_MEGA_DEBUG_L2") ? atoi(getenv("FSB_MEGA_DEBUG_L2")) : 0;
     p.trace = (h->mega_trace_on && (size_t)h->n_sm * mb.ops.size() * 4 <= MEGA_TRACE_WORDS) ? h->mega_trace : nullptr;
-    p.copy_bytes = std::max(1024, h->mega_copy_bytes) & ~15;
     return 0;
 }
 
@@ -697,6 +701,12 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
     T(ws_acc, float, R * d.n_kv_head * max_splits * gq * d.head_dim)
     T(ws_ml, float, R * d.n_kv_head * max_splits * gq * 2)
     T(counters, int32_t, R * d.n_kv_head)
+    {
+        const size_t PR = PREFILL_ROWS;
+        T(pxa, bf16, PR * d.dim) T(pxb, bf16, PR * d.dim) T(pxn, bf16, PR * d.dim) T(pqkv, bf16, PR * QKV)
+        T(py, bf16, PR * d.n_head * d.head_dim) T(ptmp, bf16, PR * d.dim) T(pf1, bf16, PR * d.ffn) T(pf3, bf16, PR * d.ffn)
+        T(cublas_ws, char, CUBLAS_WS_BYTES)
+    }
     T(mega_buf, char, MEGA_BUF_BYTES) T(mega_sync, unsigned, 64) T(mega_prof, unsigned long long, 16)
     // flag-in-data activations of the persistent frame kernel (batch 1): one u32 per element
     const size_t tg = (size_t)2 * d.dim + QKV + (size_t)d.n_head * d.head_dim + d.ffn + (size_t)4 * d.dim;
@@ -762,8 +772,6 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
         h->mega_supported = coop && occ >= 1;
     }
     if (const char* e = getenv("FSB_MEGA")) h->use_mega = atoi(e);
-    if (const char* e = getenv("FSB_MEGA_PF")) h->mega_pf_stages = atoi(e);
-    if (const char* e = getenv("FSB_MEGA_COPY")) h->mega_copy_bytes = atoi(e);
     h->slow.resize(d.n_layer);
     h->fast.resize(d.n_fast_layer);
     if (const char* e = getenv("FSB_PDL")) h->use_pdl = atoi(e);
@@ -780,6 +788,7 @@ int fsb_dual_ar_destroy(fsb_dual_ar* h) {
     if (!h) return 0;
     if (h->exec) cudaGraphExecDestroy(h->exec);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
+    if (h->blas) cublasDestroy(h->blas);
     delete h;
     return 0;
 }
@@ -798,10 +807,9 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "gemv_stage_kb") h->gc.stage_kb = (int)value;
     else if (n == "attn_splits") h->attn_splits = (int)value;
     else if (n == "mega") h->use_mega = (int)value;
+    else if (n == "prefill_gemm") h->prefill_gemm = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
-    else if (n == "mega_pf_stages") h->mega_pf_stages = (int)value;
-    else if (n == "mega_copy_bytes") h->mega_copy_bytes = (int)value;
     else return fail(h, "unknown option " + n);
     h->cached_valid = false;
     return 0;
@@ -889,6 +897,45 @@ static int check_ready(fsb_dual_ar* h, int B) {
     return 0;
 }
 
+// C[T][N] = X[T][K] . W[N][K]^T, bf16 in / fp32 accumulate / bf16 out (one rounding per Linear)
+static int prefill_linear(fsb_dual_ar* h, const bf16* W, const bf16* X, bf16* C, int T, int N, int K) {
+    const float one = 1.f, zero = 0.f;
+    cublasStatus_t st = cublasGemmEx(h->blas, CUBLAS_OP_T, CUBLAS_OP_N, N, T, K, &one, W, CUDA_R_16BF, K, X, CUDA_R_16BF, K,
+                                     &zero, C, CUDA_R_16BF, N, CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT);
+    if (st != CUBLAS_STATUS_SUCCESS) return fail(h, "cublasGemmEx failed with status " + std::to_string((int)st));
+    return 0;
+}
+
+// slow stack over a chunk of T <= PREFILL_ROWS prompt rows already embedded in h->pxa; fills the KV cache
+static int prefill_chunk(fsb_dual_ar* h, cudaStream_t s, int T, const int32_t* pos, const int32_t* slots) {
+    const fsb_dual_ar_desc& d = h->d;
+    const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn, QKV = (H + 2 * KV) * HD;
+    AttnKernels ak;
+    if (!pick_attn(HD, H / KV, &ak)) return fail(h, "unsupported head_dim / GQA ratio");
+    const int ew_blocks = 4 * h->n_sm;
+    bf16* cur = h->pxa;
+    for (size_t l = 0; l < h->slow.size(); ++l) {
+        const LayerW& w = h->slow[l];
+        rmsnorm_rows_kernel<<<T, 256, 0, s>>>(cur, w.attn_norm, h->pxn, D, d.norm_eps);
+        if (int r = prefill_linear(h, w.wqkv, h->pxn, h->pqkv, T, QKV, D)) return r;
+        AttnArgs a = make_attn_args(h, w, false, pos, slots, -1);
+        a.qkv = h->pqkv; a.y = h->py; a.splits = 1; a.fused_append = 0;
+        CK(launch(ak.append, dim3(KV, T), dim3(64), 0, s, false, a));
+        CK(launch(ak.decode, dim3(1, KV, T), dim3(ATTN_THREADS), 0, s, false, a));
+        if (int r = prefill_linear(h, w.wo, h->py, h->ptmp, T, D, H * HD)) return r;
+        add_rows_kernel<<<ew_blocks, 256, 0, s>>>(cur, h->ptmp, h->pxb, (size_t)T * D / 8);
+        rmsnorm_rows_kernel<<<T, 256, 0, s>>>(h->pxb, w.ffn_norm, h->pxn, D, d.norm_eps);
+        if (int r = prefill_linear(h, w.w1, h->pxn, h->pf1, T, F, D)) return r;
+        if (int r = prefill_linear(h, w.w3, h->pxn, h->pf3, T, F, D)) return r;
+        swiglu_rows_kernel<<<ew_blocks, 256, 0, s>>>(h->pf1, h->pf3, h->pf1, (size_t)T * F / 8);
+        if (int r = prefill_linear(h, w.w2, h->pf1, h->ptmp, T, D, F)) return r;
+        add_rows_kernel<<<ew_blocks, 256, 0, s>>>(h->pxb, h->ptmp, h->pxa, (size_t)T * D / 8);
+        cur = h->pxa;
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
 int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_t slot, int32_t pos0, void* stream) {
     if (int r = check_ready(h, 1)) return r;
     if (T <= 0) return 0;
@@ -898,6 +945,22 @@ int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_
     fill_prefill_kernel<<<(T + 255) / 256, 256, 0, s>>>(h->pf_pos, h->pf_slot, T, pos0, slot);
     CK(cudaGetLastError());
     const int C1 = h->d.num_codebooks + 1;
+    if (h->prefill_gemm) {
+        if (int r = check_bound(h)) return r;
+        if (!h->blas) {
+            if (cublasCreate(&h->blas) != CUBLAS_STATUS_SUCCESS) { h->blas = nullptr; return fail(h, "cublasCreate failed"); }
+            cublasSetWorkspace(h->blas, h->cublas_ws, CUBLAS_WS_BYTES);  // caller-owned scratch: no hidden allocations
+        }
+        if (cublasSetStream(h->blas, s) != CUBLAS_STATUS_SUCCESS) return fail(h, "cublasSetStream failed");
+        for (int t0 = 0; t0 < T; t0 += PREFILL_ROWS) {
+            const int M = std::min<int>(PREFILL_ROWS, T - t0);
+            EmbedArgs e = make_embed_args(h, tokens + (size_t)t0 * C1);
+            e.x = h->pxa;
+            CK(launch(embed_kernel, dim3(M), dim3(256), 0, s, false, e));
+            if (int r = prefill_chunk(h, s, M, h->pf_pos + t0, h->pf_slot + t0)) return r;
+        }
+        return 0;
+    }
     const int chunk = 8;
     for (int t0 = 0; t0 < T; t0 += chunk) {
         const int M = std::min(chunk, T - t0);

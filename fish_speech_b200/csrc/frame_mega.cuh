@@ -65,11 +65,8 @@ struct MegaPlan {
     const FrameEndArgs* fend;
     unsigned* sync;  // [0] barrier arrivals, [1] exits (both zero between launches), [2] launch sequence number
     unsigned long long* prof;  // optional [16] cycle counters of CTA 0 (profiling aid), or nullptr
-    int pf_stages;             // L2 prefetch look-ahead of the weight stream, in ring stages (0 = off)
-    int copy_bytes;            // bulk-copy granularity inside a stage (multiple of 16)
     const uint4* hot;          // [n_hot] {ptr lo, ptr hi, bytes, 0}: small operands every CTA reads on the critical path
     int n_hot;                 // (norm weights, RoPE rows, sampling bias): prefetched into L2 with evict_last at launch
-    int debug_l2;              // timing experiment only: stream every stage from the CTA's first rows (wrong results)
     unsigned long long* trace; // optional [grid][n_ops][4] globaltimer stamps (op start, x staged, op end, barrier passed)
 };
 enum { MP_XSTAGE = 0, MP_LOOP, MP_GRID, MP_ATTN, MP_FATTN, MP_SAMPLE, MP_MISC, MP_TOTAL, MP_FRAMES };
