@@ -18,6 +18,7 @@ struct fsb_dac {
     std::map<std::string, long long> wn;
     float* buf[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t buf_elems = 0;
+    int tf32 = 1;  // 1: GEMM-shaped layers on the tensor cores (TF32 operands, fp32 accumulate); 0: fp32 SIMT (parity anchor)
     std::string err;
 };
 
@@ -71,6 +72,11 @@ struct Runner {
         a.alpha = alpha; a.res = res; a.gamma = gamma;
         a.B = B; a.T = T; a.Cin = Cin; a.N = N; a.taps = taps; a.dil = dil; a.bias_mod = bias_mod > 0 ? bias_mod : N; a.epi = epi;
         if (rc) return;
+        if (h->tf32 && (taps - 1) * dil <= CM_HALO && Cin % 4 == 0 && N % 4 == 0) {
+            dim3 grid((T + CM_BM - 1) / CM_BM, (N + CM_BN - 1) / CM_BN, B);
+            conv_mma_kernel<<<grid, 256, CM_SMEM, s>>>(a);
+            return;
+        }
         dim3 grid((T + CG_BM - 1) / CG_BM, (N + CG_BN - 1) / CG_BN, B);
         conv_gemm_kernel<<<grid, 256, 0, s>>>(a);
     }
@@ -135,6 +141,14 @@ double fsb_dac_flops(const fsb_dac* h, int32_t B, int32_t T) {
     }
     f += len * 2.0 * 7 * ch;
     return f * B;
+}
+
+int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
+    if (!h || !name) return 1;
+    const std::string n(name);
+    if (n == "tf32") h->tf32 = (int)value;
+    else return dfail(h, "unknown option " + n);
+    return 0;
 }
 
 int fsb_dac_stage(fsb_dac* h, const char* name, void** dptr, size_t* bytes) {

@@ -105,6 +105,124 @@ __global__ void __launch_bounds__(256) conv_gemm_kernel(ConvArgs a) {
     }
 }
 
+// ----------------------------------------------------------------------------- tensor-core implicit GEMM (TF32)
+// Same op as conv_gemm_kernel on the tensor cores: mma.sync m16n8k8 TF32 (10-bit mantissa operands, fp32 accumulate),
+// activations stay fp32 in memory.  CTA tile 128 (time) x 128 (N) x 32 (channels); the A tile is staged ONCE per channel
+// chunk with its causal halo ((taps-1)*dil rows), Snake applied once per element, and every tap reads the same
+// shared-memory tile at a row offset — the SIMT version re-read and re-Snaked A for every tap.
+#define CM_BM 128
+#define CM_BN 128
+#define CM_BK 32
+#define CM_HALO 56                // >= (taps - 1) * dil of every layer (7-tap convs with dilation <= 9)
+#define CM_AS (CM_BK + 4)         // A row stride in floats: conflict-free fragment loads
+#define CM_BS (CM_BN + 8)         // B row stride
+#define CM_SMEM (((CM_BM + CM_HALO) * CM_AS + CM_BK * CM_BS) * 4)
+
+__device__ __forceinline__ uint32_t f2tf32(float f) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(f));
+    return r;
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+__global__ void __launch_bounds__(256, 2) conv_mma_kernel(ConvArgs a) {
+    extern __shared__ __align__(16) float cm_smem[];
+    uint32_t* As = reinterpret_cast<uint32_t*>(cm_smem);                   // [(BM + HALO)][AS] tf32 bits
+    uint32_t* Bs = As + (CM_BM + CM_HALO) * CM_AS;                         // [BK][BS]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t4 = lane & 3;
+    const int wm = warp & 1, wn = warp >> 1;                               // 2 x 4 warps: 64 rows x 32 columns each
+    const int t0 = blockIdx.x * CM_BM, n0 = blockIdx.y * CM_BN, b = blockIdx.z;
+    const float* Ab = a.A + (size_t)b * a.T * a.Cin;
+    const int halo = (a.taps - 1) * a.dil;
+    const int rows = CM_BM + halo;
+
+    float acc[4][4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc[i][j][k] = 0.f;
+
+    for (int k0 = 0; k0 < a.Cin; k0 += CM_BK) {
+        __syncthreads();  // the previous chunk's MMAs are done with As / Bs
+        for (int e = tid; e < rows * (CM_BK / 4); e += 256) {
+            const int r = e >> 3, c4 = (e & 7) * 4;
+            const int t = t0 - halo + r, k = k0 + c4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (t >= 0 && t < a.T && k < a.Cin) {
+                v = *reinterpret_cast<const float4*>(Ab + (size_t)t * a.Cin + k);
+                if (a.alpha) {
+                    const float4 al = *reinterpret_cast<const float4*>(a.alpha + k);
+                    v.x = snake_f(v.x, al.x, 1.f / (al.x + 1e-9f));
+                    v.y = snake_f(v.y, al.y, 1.f / (al.y + 1e-9f));
+                    v.z = snake_f(v.z, al.z, 1.f / (al.z + 1e-9f));
+                    v.w = snake_f(v.w, al.w, 1.f / (al.w + 1e-9f));
+                }
+            }
+            *reinterpret_cast<uint4*>(&As[r * CM_AS + c4]) = make_uint4(f2tf32(v.x), f2tf32(v.y), f2tf32(v.z), f2tf32(v.w));
+        }
+        for (int j = 0; j < a.taps; ++j) {
+            const float* Wj = a.W + ((size_t)j * a.Cin + k0) * a.N;
+            if (j > 0) __syncthreads();  // MMAs of the previous tap are done with Bs
+            for (int e = tid; e < CM_BK * (CM_BN / 4); e += 256) {
+                const int kk = e >> 5, c4 = (e & 31) * 4;
+                float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (k0 + kk < a.Cin && n0 + c4 < a.N) w = *reinterpret_cast<const float4*>(Wj + (size_t)kk * a.N + n0 + c4);
+                *reinterpret_cast<uint4*>(&Bs[kk * CM_BS + c4]) = make_uint4(f2tf32(w.x), f2tf32(w.y), f2tf32(w.z), f2tf32(w.w));
+            }
+            __syncthreads();
+            const int roff = halo - (a.taps - 1 - j) * a.dil;  // output row r reads staged row r + roff
+#pragma unroll
+            for (int ks = 0; ks < CM_BK; ks += 8) {
+                uint32_t af[4][4], bf[4][2];
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt) {
+                    const uint32_t* p = As + (wm * 64 + mt * 16 + g + roff) * CM_AS + ks + t4;
+                    af[mt][0] = p[0]; af[mt][1] = p[8 * CM_AS]; af[mt][2] = p[4]; af[mt][3] = p[8 * CM_AS + 4];
+                }
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt) {
+                    const uint32_t* p = Bs + (ks + t4) * CM_BS + wn * 32 + nt * 8 + g;
+                    bf[nt][0] = p[0]; bf[nt][1] = p[4 * CM_BS];
+                }
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                    for (int nt = 0; nt < 4; ++nt) mma_tf32(acc[mt][nt], af[mt], bf[nt]);
+            }
+        }
+    }
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int t = t0 + wm * 64 + mt * 16 + g + half * 8;
+            if (t >= a.T) continue;
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const int n = n0 + wn * 32 + nt * 8 + 2 * t4 + c;
+                    if (n >= a.N) continue;
+                    float v = acc[mt][nt][half * 2 + c];
+                    if (a.bias) v += a.bias[n % a.bias_mod];
+                    if (a.epi == DEPI_GELU) v = 0.5f * v * (1.f + erff(v * 0.70710678118654752f));
+                    if (a.gamma) v *= a.gamma[n];
+                    const size_t o = ((size_t)b * a.T + t) * a.N + n;
+                    if (a.res) v += a.res[o];
+                    if (a.epi == DEPI_TANH) v = tanhf(v);
+                    a.out[o] = v;
+                }
+        }
+}
+
 // Final conv (Cout = 1) + tanh: one warp per output sample (modded_dac.py:793-795)
 __global__ void __launch_bounds__(256) conv_out1_kernel(ConvArgs a) {
     const int lane = threadIdx.x & 31;

@@ -137,6 +137,91 @@ def pack_weights(c: DACConfig, sd: Dict[str, Tensor], max_frames: int) -> Dict[s
     return out
 
 
+def state_dict_shapes(c: "DACConfig") -> Dict[str, tuple]:
+    """Reference state-dict keys the decode path consumes and their shapes (modded_dac.py / rvq.py module registration
+    order; weight norm in the `parametrizations.weight.original0/1` style for the decoder and `weight_g/weight_v` for
+    the descript quantizers).  Used for synthetic-weight benchmarks and as the list of tensors `pack_weights` needs."""
+    D = c.latent_dim
+    out: Dict[str, tuple] = {}
+
+    def vq(p, size):
+        out[p + "codebook.weight"] = (size, c.codebook_dim)
+        out[p + "out_proj.weight_g"] = (D, 1, 1)
+        out[p + "out_proj.weight_v"] = (D, c.codebook_dim, 1)
+        out[p + "out_proj.bias"] = (D,)
+
+    vq("quantizer.semantic_quantizer.quantizers.0.", c.semantic_codebook_size)
+    for i in range(c.n_codebooks):
+        vq(f"quantizer.quantizer.quantizers.{i}.", c.codebook_size)
+    for i in range(c.tf_layers):
+        p = f"quantizer.post_module.layers.{i}."
+        out[p + "attention.wqkv.weight"] = (3 * c.tf_heads * c.tf_head_dim, c.tf_dim)
+        out[p + "attention.wo.weight"] = (c.tf_dim, c.tf_heads * c.tf_head_dim)
+        out[p + "feed_forward.w1.weight"] = (c.tf_ffn, c.tf_dim)
+        out[p + "feed_forward.w3.weight"] = (c.tf_ffn, c.tf_dim)
+        out[p + "feed_forward.w2.weight"] = (c.tf_dim, c.tf_ffn)
+        for k in ("ffn_norm.weight", "attention_norm.weight", "attention_layer_scale.gamma", "ffn_layer_scale.gamma"):
+            out[p + k] = (c.tf_dim,)
+    out["quantizer.post_module.norm.weight"] = (c.tf_dim,)
+    for i, f in enumerate(c.upsample_factors):
+        p = f"quantizer.upsample.{i}."
+        out[p + "0.conv.weight"] = (D, D, f)
+        out[p + "0.conv.bias"] = (D,)
+        out[p + "1.dwconv.conv.weight"] = (D, 1, 7)
+        out[p + "1.dwconv.conv.bias"] = (D,)
+        out[p + "1.norm.weight"] = (D,)
+        out[p + "1.norm.bias"] = (D,)
+        out[p + "1.pwconv1.weight"] = (c.convnext_ratio * D, D)
+        out[p + "1.pwconv1.bias"] = (c.convnext_ratio * D,)
+        out[p + "1.pwconv2.weight"] = (D, c.convnext_ratio * D)
+        out[p + "1.pwconv2.bias"] = (D,)
+        out[p + "1.gamma"] = (D,)
+
+    def wnconv(p, cout, cin, k, transposed=False):
+        shape = (cin, cout, k) if transposed else (cout, cin, k)
+        out[p + "conv.parametrizations.weight.original0"] = (shape[0], 1, 1)
+        out[p + "conv.parametrizations.weight.original1"] = shape
+        out[p + "conv.bias"] = (cout,)
+
+    wnconv("decoder.model.0.", c.decoder_dim, D, 7)
+    ch = c.decoder_dim
+    for i, s_ in enumerate(c.decoder_rates):
+        cin, cout = ch // 2 ** i, ch // 2 ** (i + 1)
+        p = f"decoder.model.{i + 1}.block."
+        out[p + "0.alpha"] = (1, cin, 1)
+        wnconv(p + "1.", cout, cin, 2 * s_, transposed=True)
+        for j in range(3):
+            q = p + f"{2 + j}.block."
+            out[q + "0.alpha"] = (1, cout, 1)
+            wnconv(q + "1.", cout, cout, 7)
+            out[q + "2.alpha"] = (1, cout, 1)
+            wnconv(q + "3.", cout, cout, 1)
+    n = len(c.decoder_rates)
+    out[f"decoder.model.{n + 1}.alpha"] = (1, ch // 2 ** n, 1)
+    wnconv(f"decoder.model.{n + 2}.", 1, ch // 2 ** n, 7)
+    return out
+
+
+def synthetic_state_dict(c: "DACConfig", seed: int = 0, device="cpu") -> Dict[str, Tensor]:
+    """Random decode-path weights of the right shapes (benchmarks only: bounded activations, no claim of audio)."""
+    g = torch.Generator().manual_seed(seed)
+    sd: Dict[str, Tensor] = {}
+    for name, shape in state_dict_shapes(c).items():
+        if name.endswith("alpha"):
+            w = 0.5 + torch.rand(shape, generator=g)
+        elif name.endswith(("gamma", "original0", "weight_g")):
+            w = 0.3 * (0.5 + torch.rand(shape, generator=g))
+        elif name.endswith("norm.weight"):
+            w = torch.ones(shape)
+        elif name.endswith("bias"):
+            w = torch.zeros(shape)
+        else:
+            fan = shape[1] * (shape[2] if len(shape) == 3 else 1) if len(shape) > 1 else 1
+            w = torch.randn(shape, generator=g) / math.sqrt(max(1, fan))
+        sd[name] = w.to(device)
+    return sd
+
+
 class DACB200:
     """Engine-backed stand-in for modded_dac.DAC on the decode side."""
 
@@ -181,6 +266,10 @@ class DACB200:
                 self._h = C.c_void_p()
         except Exception:
             pass
+
+    def set_option(self, name: str, value: int):
+        """"tf32": 1 = tensor-core GEMMs with TF32 operands (default), 0 = fp32 CUDA-core path (parity anchor)."""
+        self._ck(self.lib.fsb_dac_set_option(self._h, name.encode(), int(value)))
 
     def flops(self, B: int, T: int) -> float:
         return float(self.lib.fsb_dac_flops(self._h, B, T))

@@ -141,6 +141,9 @@ const char* fsb_dac_last_error(const fsb_dac* h);
 int fsb_dac_bind_weight(fsb_dac* h, const char* name, const void* dptr, int64_t numel);
 /* DAC.from_indices: codes int64 [B][1+n_codebooks][T] (clamped IN PLACE like rvq.py:354-359) -> wav fp32 [B][hop*T]. */
 int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, void* stream);
+/* Options: "tf32" (1 = GEMM-shaped layers on the tensor cores with TF32 operands and fp32 accumulation, the default;
+ * 0 = fp32 CUDA-core path, the parity anchor). */
+int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value);
 /* internal activation buffers "buf0".."buf3" (tests / profiling) */
 int fsb_dac_stage(fsb_dac* h, const char* name, void** dptr, size_t* bytes);
 /* algorithmic FLOPs of one decode call (GEMM-shaped work only) */

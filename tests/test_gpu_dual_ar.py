@@ -182,3 +182,41 @@ def test_generate_errors_like_reference(tiny):
     with pytest.raises(ValueError):  # inference.py:262-265
         generate(model=m, prompt=torch.zeros((cfg.num_codebooks + 1, cfg.max_seq_len), dtype=torch.long).cuda(),
                  max_new_tokens=4)
+
+
+def test_batched_frames_match_single_requests(tiny):
+    """Config-3 style decode: B requests with different context lengths advance together through
+    fsb_dual_ar_decode_frames (per-row positions, KV slots, RAS windows, uniform records); every request must
+    produce exactly the tokens it produces when decoded alone with the same draws."""
+    g, cfg, sd, _ = tiny
+    B, frames = 3, 6
+    C1 = cfg.num_codebooks + 1
+    V, cb, C = cfg.vocab_size, cfg.codebook_size, cfg.num_codebooks
+    lens = [16, 12, 9]
+    prompts = [R.make_prompt(cfg, T, seed=100 + i) for i, T in enumerate(lens)]
+    gen = torch.Generator().manual_seed(5)
+    rec = (torch.randint(0, 256, (frames, B, 2 * V + (C - 1) * cb), generator=gen).float() / 256).to(torch.bfloat16)
+    bias = torch.full((V,), float("-inf"), dtype=torch.bfloat16)
+    bias[cfg.semantic_begin_id: cfg.semantic_end_id + 1] = 0.0
+
+    def run(model, ps, uni):
+        n = len(ps)
+        for k, p in enumerate(ps):
+            model.prefill(p[:, :-1].cuda(), 0, k)
+        s = model.session(n, frames + 1)
+        s.bias, s.restrict_scan, s.uniforms = bias.cuda(), True, uni.cuda().contiguous()
+        s.cur_tokens.copy_(torch.stack([p[:, -1] for p in ps]).to(torch.int32))
+        s.pos.copy_(torch.tensor([p.shape[1] - 1 for p in ps], dtype=torch.int32))
+        s.frame_counter.zero_(); s.ras_window.zero_(); s.done.zero_()
+        s.run(frames, 0.8008, 0.8008, 30, True)
+        torch.cuda.synchronize()
+        return s.out_tokens[:frames].cpu().clone()
+
+    mb = _mk(cfg, sd, max_rows=B)
+    got = run(mb, prompts, rec)                      # [frames][B][C+1]
+    assert bool((got[:, :, 1:] >= 0).all()) and bool((got[:, :, 1:] < cb).all())
+    for k in range(B):
+        m1 = _mk(cfg, sd, max_rows=1)
+        m1.set_option("mega", 0)                     # same kernel family as the batched path: bit-identical rows
+        alone = run(m1, [prompts[k]], rec[:, k: k + 1])
+        assert torch.equal(alone[:, 0], got[:, k]), (k, alone[:, 0], got[:, k])
