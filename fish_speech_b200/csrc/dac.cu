@@ -73,8 +73,13 @@ struct Runner {
         a.B = B; a.T = T; a.Cin = Cin; a.N = N; a.taps = taps; a.dil = dil; a.bias_mod = bias_mod > 0 ? bias_mod : N; a.epi = epi;
         if (rc) return;
         if (h->tf32 && (taps - 1) * dil <= CM_HALO && Cin % 4 == 0 && N % 4 == 0) {
-            dim3 grid((T + CM_BM - 1) / CM_BM, (N + CM_BN - 1) / CM_BN, B);
-            conv_mma_kernel<<<grid, 256, CM_SMEM, s>>>(a);
+            if (N % 96 == 0 && N % 128 != 0) {
+                dim3 grid((T + CM_BM - 1) / CM_BM, N / 96, B);
+                conv_mma_kernel<3><<<grid, 256, CM_SMEM, s>>>(a);
+            } else {
+                dim3 grid((T + CM_BM - 1) / CM_BM, (N + CM_BN - 1) / CM_BN, B);
+                conv_mma_kernel<4><<<grid, 256, CM_SMEM, s>>>(a);
+            }
             return;
         }
         dim3 grid((T + CG_BM - 1) / CG_BM, (N + CG_BN - 1) / CG_BN, B);

@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(256) conv_gemm_kernel(ConvArgs a) {
 // chunk with its causal halo ((taps-1)*dil rows), Snake applied once per element, and every tap reads the same
 // shared-memory tile at a row offset — the SIMT version re-read and re-Snaked A for every tap.
 #define CM_BM 128
-#define CM_BN 128
+#define CM_BN 128                 // widest N tile (NT = 4 n8-tiles per warp); NT = 3 gives 96-wide tiles
 #define CM_BK 32
 #define CM_HALO 56                // >= (taps - 1) * dil of every layer (7-tap convs with dilation <= 9)
 #define CM_AS (CM_BK + 4)         // A row stride in floats: conflict-free fragment loads
@@ -130,23 +130,32 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], 
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
 }
 
+// Snake for the tensor-core path: MUFU sine (abs error ~1e-7 on the O(1) arguments here, far below TF32 rounding)
+__device__ __forceinline__ float snake_fast(float x, float a, float inv) {
+    const float s = __sinf(a * x);
+    return fmaf(inv * s, s, x);
+}
+
+// NT: n8-tiles per warp -> CTA N tile = 32 * NT (128 or 96: every decoder width 1536/768/384/192/96 is a multiple of 96)
+template <int NT>
 __global__ void __launch_bounds__(256, 2) conv_mma_kernel(ConvArgs a) {
+    constexpr int BN = 32 * NT;
     extern __shared__ __align__(16) float cm_smem[];
     uint32_t* As = reinterpret_cast<uint32_t*>(cm_smem);                   // [(BM + HALO)][AS] tf32 bits
     uint32_t* Bs = As + (CM_BM + CM_HALO) * CM_AS;                         // [BK][BS]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t4 = lane & 3;
     const int wm = warp & 1, wn = warp >> 1;                               // 2 x 4 warps: 64 rows x 32 columns each
-    const int t0 = blockIdx.x * CM_BM, n0 = blockIdx.y * CM_BN, b = blockIdx.z;
+    const int t0 = blockIdx.x * CM_BM, n0 = blockIdx.y * BN, b = blockIdx.z;
     const float* Ab = a.A + (size_t)b * a.T * a.Cin;
     const int halo = (a.taps - 1) * a.dil;
     const int rows = CM_BM + halo;
 
-    float acc[4][4][4];
+    float acc[4][NT][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < NT; ++j)
 #pragma unroll
             for (int k = 0; k < 4; ++k) acc[i][j][k] = 0.f;
 
@@ -160,10 +169,10 @@ __global__ void __launch_bounds__(256, 2) conv_mma_kernel(ConvArgs a) {
                 v = *reinterpret_cast<const float4*>(Ab + (size_t)t * a.Cin + k);
                 if (a.alpha) {
                     const float4 al = *reinterpret_cast<const float4*>(a.alpha + k);
-                    v.x = snake_f(v.x, al.x, 1.f / (al.x + 1e-9f));
-                    v.y = snake_f(v.y, al.y, 1.f / (al.y + 1e-9f));
-                    v.z = snake_f(v.z, al.z, 1.f / (al.z + 1e-9f));
-                    v.w = snake_f(v.w, al.w, 1.f / (al.w + 1e-9f));
+                    v.x = snake_fast(v.x, al.x, 1.f / (al.x + 1e-9f));
+                    v.y = snake_fast(v.y, al.y, 1.f / (al.y + 1e-9f));
+                    v.z = snake_fast(v.z, al.z, 1.f / (al.z + 1e-9f));
+                    v.w = snake_fast(v.w, al.w, 1.f / (al.w + 1e-9f));
                 }
             }
             *reinterpret_cast<uint4*>(&As[r * CM_AS + c4]) = make_uint4(f2tf32(v.x), f2tf32(v.y), f2tf32(v.z), f2tf32(v.w));
@@ -171,8 +180,8 @@ __global__ void __launch_bounds__(256, 2) conv_mma_kernel(ConvArgs a) {
         for (int j = 0; j < a.taps; ++j) {
             const float* Wj = a.W + ((size_t)j * a.Cin + k0) * a.N;
             if (j > 0) __syncthreads();  // MMAs of the previous tap are done with Bs
-            for (int e = tid; e < CM_BK * (CM_BN / 4); e += 256) {
-                const int kk = e >> 5, c4 = (e & 31) * 4;
+            for (int e = tid; e < CM_BK * (BN / 4); e += 256) {
+                const int kk = e / (BN / 4), c4 = (e % (BN / 4)) * 4;
                 float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (k0 + kk < a.Cin && n0 + c4 < a.N) w = *reinterpret_cast<const float4*>(Wj + (size_t)kk * a.N + n0 + c4);
                 *reinterpret_cast<uint4*>(&Bs[kk * CM_BS + c4]) = make_uint4(f2tf32(w.x), f2tf32(w.y), f2tf32(w.z), f2tf32(w.w));
@@ -181,21 +190,21 @@ __global__ void __launch_bounds__(256, 2) conv_mma_kernel(ConvArgs a) {
             const int roff = halo - (a.taps - 1 - j) * a.dil;  // output row r reads staged row r + roff
 #pragma unroll
             for (int ks = 0; ks < CM_BK; ks += 8) {
-                uint32_t af[4][4], bf[4][2];
+                uint32_t af[4][4], bf[NT][2];
 #pragma unroll
                 for (int mt = 0; mt < 4; ++mt) {
                     const uint32_t* p = As + (wm * 64 + mt * 16 + g + roff) * CM_AS + ks + t4;
                     af[mt][0] = p[0]; af[mt][1] = p[8 * CM_AS]; af[mt][2] = p[4]; af[mt][3] = p[8 * CM_AS + 4];
                 }
 #pragma unroll
-                for (int nt = 0; nt < 4; ++nt) {
-                    const uint32_t* p = Bs + (ks + t4) * CM_BS + wn * 32 + nt * 8 + g;
+                for (int nt = 0; nt < NT; ++nt) {
+                    const uint32_t* p = Bs + (ks + t4) * CM_BS + wn * (8 * NT) + nt * 8 + g;
                     bf[nt][0] = p[0]; bf[nt][1] = p[4 * CM_BS];
                 }
 #pragma unroll
                 for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-                    for (int nt = 0; nt < 4; ++nt) mma_tf32(acc[mt][nt], af[mt], bf[nt]);
+                    for (int nt = 0; nt < NT; ++nt) mma_tf32(acc[mt][nt], af[mt], bf[nt]);
             }
         }
     }
@@ -206,10 +215,10 @@ __global__ void __launch_bounds__(256, 2) conv_mma_kernel(ConvArgs a) {
             const int t = t0 + wm * 64 + mt * 16 + g + half * 8;
             if (t >= a.T) continue;
 #pragma unroll
-            for (int nt = 0; nt < 4; ++nt)
+            for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
-                    const int n = n0 + wn * 32 + nt * 8 + 2 * t4 + c;
+                    const int n = n0 + wn * (8 * NT) + nt * 8 + 2 * t4 + c;
                     if (n >= a.N) continue;
                     float v = acc[mt][nt][half * 2 + c];
                     if (a.bias) v += a.bias[n % a.bias_mod];

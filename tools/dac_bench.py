@@ -35,4 +35,4 @@ peaks = json.load(open("MEASURED_PEAKS.json")) if __import__("os").path.exists("
 peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1375.8)))
 print(json.dumps({"workload": f"DAC decode B={B} T={T}", "ms": ms, "audio_s_per_s": audio_s / (ms / 1e3),
                   "tflops": flops / (ms * 1e-3) / 1e12, "frac_of_bf16_peak": flops / (ms * 1e-3) / 1e12 / peak,
-                  "finite": bool(torch.isfinite(wav).all()), "dtype": "fp32 SIMT implicit GEMM"}))
+                  "finite": bool(torch.isfinite(wav).all()), "dtype": "tf32 tensor-core implicit GEMM (fp32 accumulate)"}))
