@@ -145,9 +145,8 @@ __device__ __forceinline__ int lda(const int* p) { return __ldcg(p); }
 // expected tag also sees the value: producers need no fence and no flag, consumers spin on the data they have to
 // load anyway.  This replaces "fence + grid barrier + reload" between dependent ops (the same idea as the
 // low-latency protocol of collective libraries).
-#ifndef FSB_SPIN_NS
-#define FSB_SPIN_NS 200
-#endif
+// poll back-off in ns (tunable at handle creation: env FSB_SPIN_NS)
+static __device__ unsigned fsb_spin_ns = 100;
 __device__ __forceinline__ void st_tagged(uint32_t* p, float v, unsigned tag) {
     const uint32_t w = (tag << 16) | (uint32_t)f_to_bf16_bits(v);
     asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
@@ -160,7 +159,7 @@ __device__ __forceinline__ void st_tagged4(uint32_t* p, uint32_t lo_pair, uint32
 }
 __device__ __forceinline__ void spin_watchdog(unsigned& spins, long long& t0) {
     // back off between polls: tens of thousands of threads polling the same L2 slices delay the very stores they wait for
-    __nanosleep(FSB_SPIN_NS);
+    __nanosleep(fsb_spin_ns);
     if ((++spins & 0x3ffu) == 0) {  // a lost producer must fault, not hang the GPU
         if (t0 == 0) t0 = clock64();
         else if (clock64() - t0 > 4000000000LL) __trap();

@@ -772,6 +772,10 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
         h->mega_supported = coop && occ >= 1;
     }
     if (const char* e = getenv("FSB_MEGA")) h->use_mega = atoi(e);
+    if (const char* e = getenv("FSB_SPIN_NS")) {
+        const unsigned ns = (unsigned)atoi(e);
+        CK(cudaMemcpyToSymbol(fsb_spin_ns, &ns, sizeof(ns)));
+    }
     h->slow.resize(d.n_layer);
     h->fast.resize(d.n_fast_layer);
     if (const char* e = getenv("FSB_PDL")) h->use_pdl = atoi(e);
