@@ -71,6 +71,8 @@ struct fsb_dual_ar {
     char* cublas_ws = nullptr;
     cublasHandle_t blas = nullptr;
     int prefill_gemm = 1;            // 1: whole-chunk prompt pass (cuBLAS GEMMs), 0: 8-row passes through the decode kernels
+    int batch_gemm = 1;              // decode steps with more than 8 rows: 1 = every Linear once over all rows (weights streamed once
+                                     // per step), 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
     int max_splits = 32;
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
@@ -352,9 +354,85 @@ FrameEndArgs make_frame_end(const fsb_dual_ar* h, const fsb_frame_args& fa) {
 }
 
 // ------------------------------------------------------------------------------------------- the passes
+int ensure_blas(fsb_dual_ar* h, cudaStream_t s) {
+    if (!h->blas) {
+        if (cublasCreate(&h->blas) != CUBLAS_STATUS_SUCCESS) { h->blas = nullptr; return fail(h, "cublasCreate failed"); }
+        cublasSetWorkspace(h->blas, h->cublas_ws, CUBLAS_WS_BYTES);  // caller-owned scratch: no hidden allocations
+    }
+    if (cublasSetStream(h->blas, s) != CUBLAS_STATUS_SUCCESS) return fail(h, "cublasSetStream failed");
+    return 0;
+}
+
+// C[T][N] = X[T][K] . W[N][K]^T, bf16 in / fp32 accumulate / bf16 out (one rounding per Linear)
+int rows_linear(fsb_dual_ar* h, const bf16* W, const bf16* X, bf16* C, int T, int N, int K) {
+    const float one = 1.f, zero = 0.f;
+    cublasStatus_t st = cublasGemmEx(h->blas, CUBLAS_OP_T, CUBLAS_OP_N, N, T, K, &one, W, CUDA_R_16BF, K, X, CUDA_R_16BF, K,
+                                     &zero, C, CUDA_R_16BF, N, CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT);
+    if (st != CUBLAS_STATUS_SUCCESS) return fail(h, "cublasGemmEx failed with status " + std::to_string((int)st));
+    return 0;
+}
+
+bool batch_gemm_active(const fsb_dual_ar* h, int M) { return h->batch_gemm && M > 8 && M <= PREFILL_ROWS; }
+
+// transformer layers over 8 < M <= PREFILL_ROWS decode rows (one row per request, each with its own position and KV
+// slot): every Linear runs ONCE over all rows, so a step streams the weights once however many requests are in flight.
+// Same contract as run_layers (result in h->x / h->xf); scratch = the prompt-pass buffers.
+int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_in, const int32_t* pos,
+                    const int32_t* slots, int pos_fixed) {
+    const fsb_dual_ar_desc& d = h->d;
+    const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn, QKV = (H + 2 * KV) * HD;
+    AttnKernels ak;
+    if (!pick_attn(HD, H / KV, &ak)) return fail(h, "unsupported head_dim / GQA ratio");
+    if (int r = ensure_blas(h, s)) return r;
+    const std::vector<LayerW>& L = fast ? h->fast : h->slow;
+    bf16* xa = fast ? h->xf : h->x;
+    bf16* xb = fast ? h->xf2 : h->x2;
+    const int ew_blocks = 2 * h->n_sm;
+    const int splits = splits_for(h, M);
+    const bf16* cur = x_in;
+    for (size_t l = 0; l < L.size(); ++l) {
+        const LayerW& w = L[l];
+        if (!w.wqkv || !w.wo || !w.w1 || !w.w2 || !w.w3 || !w.attn_norm || !w.ffn_norm || !w.kc || !w.vc)
+            return fail(h, "unbound weights / kv cache in layer " + std::to_string(l));
+        rmsnorm_rows_kernel<<<M, 256, 0, s>>>(cur, w.attn_norm, h->pxn, D, d.norm_eps);
+        if (int r = rows_linear(h, w.wqkv, h->pxn, h->qkv, M, QKV, D)) return r;
+        AttnArgs a = make_attn_args(h, w, fast, pos, slots, pos_fixed);
+        if (fast) {
+            CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, false, a));
+        } else {
+            a.splits = splits;
+            a.fused_append = 1;
+            CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, false, a));
+        }
+        if (int r = rows_linear(h, w.wo, h->y, h->ptmp, M, D, H * HD)) return r;
+        add_rows_kernel<<<ew_blocks, 256, 0, s>>>(cur, h->ptmp, xb, (size_t)M * D / 8);
+        rmsnorm_rows_kernel<<<M, 256, 0, s>>>(xb, w.ffn_norm, h->pxn, D, d.norm_eps);
+        if (int r = rows_linear(h, w.w1, h->pxn, h->pf1, M, F, D)) return r;
+        if (int r = rows_linear(h, w.w3, h->pxn, h->pf3, M, F, D)) return r;
+        swiglu_rows_kernel<<<ew_blocks, 256, 0, s>>>(h->pf1, h->pf3, h->ff, (size_t)M * F / 8);
+        if (int r = rows_linear(h, w.w2, h->ff, h->ptmp, M, D, F)) return r;
+        add_rows_kernel<<<ew_blocks, 256, 0, s>>>(xb, h->ptmp, xa, (size_t)M * D / 8);
+        cur = xa;
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// logits[M][N] = head . (RMSNorm(x) * norm_w); the normalised rows are kept in xnorm (the slow stack's `hidden`)
+int run_head_rows(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* head, int N, const bf16* x, const bf16* norm_w,
+                  bf16* xnorm, bf16* logits) {
+    const fsb_dual_ar_desc& d = h->d;
+    if (int r = ensure_blas(h, s)) return r;
+    rmsnorm_rows_kernel<<<M, 256, 0, s>>>(x, norm_w, xnorm, d.dim, d.norm_eps);
+    if (int r = rows_linear(h, head, xnorm, logits, M, N, d.dim)) return r;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 // transformer layers over M rows. x_in: [M][D] input (not modified); result in h->x (slow) / h->xf (fast)
 int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_in, const int32_t* pos,
                const int32_t* slots, bool fused_append, int pos_fixed) {
+    if (fused_append && batch_gemm_active(h, M)) return run_layers_rows(h, s, fast, M, x_in, pos, slots, pos_fixed);
     const fsb_dual_ar_desc& d = h->d;
     const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn;
     const int QKV = (H + 2 * KV) * HD;
@@ -417,6 +495,7 @@ int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, 
     if (int r = run_layers(h, s, false, M, h->x2, pos, slots, true, -1)) return r;
     const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
     if (!head || !h->norm) return fail(h, "LM head / final norm not bound");
+    if (batch_gemm_active(h, M)) return run_head_rows(h, s, M, head, d.vocab, h->x, h->norm, h->hidden, h->slow_logits);
     CK(run_gemv(h->gc, h->use_pdl != 0, s, M, d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head,
                 nullptr, h->x, h->norm, nullptr, h->slow_logits, h->hidden, d.norm_eps, nullptr, 0));
     return 0;
@@ -429,6 +508,7 @@ int run_fast_step(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* x_in, int c
     if (want_logits) {
         if (!h->fast_out || !h->fast_norm) return fail(h, "fast head not bound");
         bf16* lg = h->fast_logits + (size_t)cb_idx * h->R * d.codebook_size;
+        if (batch_gemm_active(h, M)) return run_head_rows(h, s, M, h->fast_out, d.codebook_size, h->xf, h->fast_norm, h->pxb, lg);
         CK(run_gemv(h->gc, h->use_pdl != 0, s, M, d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE,
                     h->fast_out, nullptr, h->xf, h->fast_norm, nullptr, lg, nullptr, d.norm_eps, nullptr, 0));
     }
@@ -812,6 +892,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "attn_splits") h->attn_splits = (int)value;
     else if (n == "mega") h->use_mega = (int)value;
     else if (n == "prefill_gemm") h->prefill_gemm = (int)value;
+    else if (n == "batch_gemm") h->batch_gemm = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
     else return fail(h, "unknown option " + n);
@@ -951,11 +1032,7 @@ int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_
     const int C1 = h->d.num_codebooks + 1;
     if (h->prefill_gemm) {
         if (int r = check_bound(h)) return r;
-        if (!h->blas) {
-            if (cublasCreate(&h->blas) != CUBLAS_STATUS_SUCCESS) { h->blas = nullptr; return fail(h, "cublasCreate failed"); }
-            cublasSetWorkspace(h->blas, h->cublas_ws, CUBLAS_WS_BYTES);  // caller-owned scratch: no hidden allocations
-        }
-        if (cublasSetStream(h->blas, s) != CUBLAS_STATUS_SUCCESS) return fail(h, "cublasSetStream failed");
+        if (int r = ensure_blas(h, s)) return r;
         for (int t0 = 0; t0 < T; t0 += PREFILL_ROWS) {
             const int M = std::min<int>(PREFILL_ROWS, T - t0);
             EmbedArgs e = make_embed_args(h, tokens + (size_t)t0 * C1);
@@ -1012,6 +1089,8 @@ int fsb_dual_ar_decode_frames(fsb_dual_ar* h, const fsb_frame_args* args, int32_
     if (!h->fast_emb) return fail(h, "fast_embeddings not bound");
     cudaStream_t s = (cudaStream_t)stream;
     const bool mega = mega_active(h, args->batch);
+    if (batch_gemm_active(h, args->batch))  // the handle must exist before a stream capture begins
+        if (int r = ensure_blas(h, s)) return r;
     const bool fresh = !h->cached_valid || memcmp(&h->cached, args, sizeof(fsb_frame_args)) != 0;
     if (mega && fresh) {
         if (int r = build_mega_plan(h, s, *args)) return r;

@@ -220,3 +220,68 @@ def test_batched_frames_match_single_requests(tiny):
         m1.set_option("mega", 0)                     # same kernel family as the batched path: bit-identical rows
         alone = run(m1, [prompts[k]], rec[:, k: k + 1])
         assert torch.equal(alone[:, 0], got[:, k]), (k, alone[:, 0], got[:, k])
+
+
+def test_many_row_step_streams_weights_once_and_matches_oracle(tiny):
+    """Config-3 regime (more than 8 requests in flight): every Linear runs once over all rows.  Slow logits of each row
+    against the oracle's prompt-route logits for that request, fast logits against the 8-row GEMV passes, and a short
+    fused decode for range/termination."""
+    g, cfg, sd, _ = tiny
+    import ctypes as C
+    from fish_speech_b200.dual_ar import _stream
+    B = 12
+    V, cb, D = cfg.vocab_size, cfg.codebook_size, cfg.dim
+    lens = [9 + 2 * i for i in range(B)]
+    prompts = [R.make_prompt(cfg, T, seed=300 + i, voice_span=4 if i % 2 else 0) for i, T in enumerate(lens)]
+    m = _mk(cfg, sd, max_rows=B)
+    om = R.DualARRef(cfg, sd)
+    om.setup_caches(1, cfg.max_seq_len)
+
+    def slow(mode):
+        m.set_option("batch_gemm", mode)
+        for k, p in enumerate(prompts):
+            m.prefill(p[:, :-1].cuda(), 0, k)
+        tok = torch.stack([p[:, -1] for p in prompts]).to(torch.int32).cuda().contiguous()
+        pos = torch.tensor([T - 1 for T in lens], dtype=torch.int32).cuda()
+        m._ck(m.lib.fsb_dual_ar_slow_step(m._h, B, tok.data_ptr(), pos.data_ptr(), None, _stream()))
+        torch.cuda.synchronize()
+        return m._buffer("slow_logits")[: B * V].view(B, V).clone().cpu(), m._buffer("hidden")[: B * D].view(B, D).clone()
+
+    lg1, hid1 = slow(1)
+    lg0, _ = slow(0)
+    for k, p in enumerate(prompts):
+        ref, _ = om.forward_generate(p[None], torch.arange(p.shape[1]))
+        _check_logits(f"many-row slow logits row {k}", lg1[k], ref[0, -1])
+    mabs, _, _ = err_stats(lg1, lg0)
+    print(f"[parity] many-row step vs 8-row passes, slow logits: max-abs {mabs:.4f}")
+    assert mabs <= ABS_TOL
+    # fast stack: positions 0 and 1 on identical inputs in both modes
+    codes = torch.randint(0, cb, (B,), generator=torch.Generator().manual_seed(9))
+    emb = m.fast_embeddings(codes.cuda()).view(B, 1, -1)
+    outs = {}
+    for mode in (1, 0):
+        m.set_option("batch_gemm", mode)
+        m.forward_generate_fast(hid1.view(B, 1, D), torch.tensor([0]))
+        outs[mode] = m.forward_generate_fast(emb, torch.tensor([1])).cpu()
+    mabs, _, _ = err_stats(outs[1], outs[0])
+    print(f"[parity] many-row step vs 8-row passes, fast logits: max-abs {mabs:.4f}")
+    assert mabs <= ABS_TOL
+    # fused frames over all rows
+    m.set_option("batch_gemm", 1)
+    frames = 5
+    for k, p in enumerate(prompts):
+        m.prefill(p[:, :-1].cuda(), 0, k)
+    s = m.session(B, frames + 1)
+    bias = torch.full((V,), float("-inf"), dtype=torch.bfloat16)
+    bias[cfg.semantic_begin_id: cfg.semantic_end_id + 1] = 0.0
+    s.bias, s.restrict_scan, s.seed = bias.cuda(), True, 77
+    s.cur_tokens.copy_(torch.stack([p[:, -1] for p in prompts]).to(torch.int32))
+    s.pos.copy_(torch.tensor([T - 1 for T in lens], dtype=torch.int32))
+    s.frame_counter.zero_(); s.ras_window.zero_(); s.done.zero_()
+    s.run(frames, 0.8008, 0.8008, 30, True)
+    torch.cuda.synchronize()
+    got = s.out_tokens[:frames].cpu()
+    assert int(s.frame_counter) == frames
+    assert bool((got[:, :, 1:] >= 0).all()) and bool((got[:, :, 1:] < cb).all())
+    assert bool((got[:, :, 0] >= cfg.semantic_begin_id).all()) and bool((got[:, :, 0] <= cfg.semantic_end_id).all())
+    assert bool((s.pos.cpu() == torch.tensor([T - 1 + frames for T in lens], dtype=torch.int32)).all())
