@@ -218,6 +218,7 @@ __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
 // ----------------------------------------------------------------------------- slow-AR decode attention
 #define ATTN_THREADS 128
 #define ATTN_TILE 128
+#define ATTN_UNROLL 4  // key rows in flight per thread (16 B each): the loop is latency-bound without them
 
 // one (split, kv head, row) work item on ATTN_THREADS threads synchronised through SY; tid = index inside the group
 // QREG: keep q in registers (standalone kernel) or read it from shared memory in the FMA loop (persistent frame kernel,
@@ -303,32 +304,41 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
 
     for (int t0 = k0; t0 < k1; t0 += ATTN_TILE) {
         const int t1 = min(k1, t0 + ATTN_TILE);
-        // -- scores for this tile
-        for (int jb = t0; jb < t1; jb += KPI) {  // warp-uniform trip count (shuffles below)
-            const int j = jb + kslot;
-            const bool jv = j < t1;
-            float kf[8];
-            if (jv && j < kc1) {
-                unpack8(*reinterpret_cast<const uint4*>(kbase + (size_t)j * HD + chunk * 8), kf);
-            } else {
+        // -- scores for this tile: ATTN_UNROLL key rows are requested per thread before the first one is used
+        for (int jb = t0; jb < t1; jb += KPI * ATTN_UNROLL) {  // warp-uniform trip count (shuffles below)
+            uint4 kraw[ATTN_UNROLL];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) kf[i] = jv ? knew[chunk * 8 + i] : 0.f;
-            }
-            float d[GQ];
-#pragma unroll
-            for (int g = 0; g < GQ; ++g) {
-                float s = 0.f;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) s = fmaf(QREG ? qreg[QREG ? g : 0][i] : qs[g][chunk * 8 + i], kf[i], s);
-                d[g] = s;
+            for (int u = 0; u < ATTN_UNROLL; ++u) {
+                const int j = jb + u * KPI + kslot;
+                kraw[u] = (j < t1 && j < kc1) ? ld_stream(kbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
             }
 #pragma unroll
-            for (int o = LPK / 2; o > 0; o >>= 1)
+            for (int u = 0; u < ATTN_UNROLL; ++u) {
+                const int j = jb + u * KPI + kslot;
+                const bool jv = j < t1;
+                float kf[8];
+                if (jv && j < kc1) {
+                    unpack8(kraw[u], kf);
+                } else {
 #pragma unroll
-                for (int g = 0; g < GQ; ++g) d[g] += __shfl_xor_sync(0xffffffffu, d[g], o);
-            if (chunk == 0 && jv)
+                    for (int i = 0; i < 8; ++i) kf[i] = jv ? knew[chunk * 8 + i] : 0.f;
+                }
+                float d[GQ];
 #pragma unroll
-                for (int g = 0; g < GQ; ++g) sc[g][j - t0] = d[g] * a.scale;
+                for (int g = 0; g < GQ; ++g) {
+                    float s = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) s = fmaf(QREG ? qreg[QREG ? g : 0][i] : qs[g][chunk * 8 + i], kf[i], s);
+                    d[g] = s;
+                }
+#pragma unroll
+                for (int o = LPK / 2; o > 0; o >>= 1)
+#pragma unroll
+                    for (int g = 0; g < GQ; ++g) d[g] += __shfl_xor_sync(0xffffffffu, d[g], o);
+                if (chunk == 0 && jv)
+#pragma unroll
+                    for (int g = 0; g < GQ; ++g) sc[g][j - t0] = d[g] * a.scale;
+            }
         }
         SY::sync();
         // -- online softmax bookkeeping: warp g owns head g
@@ -360,19 +370,30 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
 #pragma unroll
             for (int i = 0; i < 8; ++i) acc[g][i] *= c;
         }
-        for (int j = t0 + kslot; j < t1; j += KPI) {
-            float vf[8];
-            if (j < kc1) {
-                unpack8(*reinterpret_cast<const uint4*>(vbase + (size_t)j * HD + chunk * 8), vf);
-            } else {
+        for (int jb = t0; jb < t1; jb += KPI * ATTN_UNROLL) {
+            uint4 vraw[ATTN_UNROLL];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) vf[i] = vnew[chunk * 8 + i];
+            for (int u = 0; u < ATTN_UNROLL; ++u) {
+                const int j = jb + u * KPI + kslot;
+                vraw[u] = (j < t1 && j < kc1) ? ld_stream(vbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
             }
 #pragma unroll
-            for (int g = 0; g < GQ; ++g) {
-                const float p = sc[g][j - t0];
+            for (int u = 0; u < ATTN_UNROLL; ++u) {
+                const int j = jb + u * KPI + kslot;
+                if (j >= t1) continue;
+                float vf[8];
+                if (j < kc1) {
+                    unpack8(vraw[u], vf);
+                } else {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) acc[g][i] = fmaf(p, vf[i], acc[g][i]);
+                    for (int i = 0; i < 8; ++i) vf[i] = vnew[chunk * 8 + i];
+                }
+#pragma unroll
+                for (int g = 0; g < GQ; ++g) {
+                    const float p = sc[g][j - t0];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) acc[g][i] = fmaf(p, vf[i], acc[g][i]);
+                }
             }
         }
         SY::sync();

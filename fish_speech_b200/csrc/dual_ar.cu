@@ -259,9 +259,10 @@ bool pick_attn(int hd, int gq, AttnKernels* k) {
 
 int splits_for(const fsb_dual_ar* h, int M) {
     if (h->attn_splits > 0) return std::min(h->attn_splits, h->max_splits);
-    // enough CTAs to cover the chip at small M, tiles of >= 128 keys at the longest context
+    // enough CTAs to cover the chip (about 12 resident CTAs per SM keep ~80 KB of key/value rows in flight per SM),
+    // tiles of >= 128 keys at the longest context
     int by_len = std::max(1, (h->max_seq_len + 255) / 256);
-    int by_sm = std::max(1, (2 * h->n_sm) / std::max(1, M * h->d.n_kv_head));
+    int by_sm = std::max(1, (12 * h->n_sm + M * h->d.n_kv_head - 1) / std::max(1, M * h->d.n_kv_head));
     return std::max(1, std::min(std::min(by_len, by_sm), h->max_splits));
 }
 
