@@ -7,7 +7,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../include/fish_b200.h"
@@ -16,6 +18,7 @@
 #include "frame_mega.cuh"
 #include "gemv_tma.cuh"
 #include "prefill.cuh"
+#include "rows_gemm.cuh"
 #include "sample.cuh"
 
 namespace {
@@ -29,6 +32,7 @@ struct LayerW {
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 constexpr size_t MEGA_BUF_BYTES = 512 * 1024;
 constexpr size_t CUBLAS_WS_BYTES = 32u << 20;
+constexpr int RG_GRID_MAX = 160;  // SMs the stream-K partial slabs are sized for
 constexpr size_t MEGA_TRACE_WORDS = 160 * 512 * 4;  // [CTAs][ops][4] time stamps of one frame (profiling aid)
 
 struct GemvCfg {
@@ -72,7 +76,12 @@ struct fsb_dual_ar {
     cublasHandle_t blas = nullptr;
     int prefill_gemm = 1;            // 1: whole-chunk prompt pass (cuBLAS GEMMs), 0: 8-row passes through the decode kernels
     int batch_gemm = 1;              // decode steps with more than 8 rows: 1 = every Linear once over all rows (weights streamed once
-                                     // per step), 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
+                                     // per step) on this library's tcgen05 stream-K kernel (rows_gemm.cuh), 2 = the same through
+                                     // cuBLAS, 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
+    float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
+    int* rg_counters = nullptr;      // per-tile arrival counters (zero between launches)
+    bool rg_ok = false;              // tensor-map encoder available, attributes set
+    std::map<std::tuple<const void*, int, int, int>, CUtensorMap> rg_maps;  // (ptr, rows, cols, box rows) -> TMA map
     int max_splits = 32;
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
@@ -242,13 +251,15 @@ cudaError_t run_gemv(const GemvCfg& gc, bool pdl, cudaStream_t s, int M, int N, 
 
 // ------------------------------------------------------------------------------------------- attention dispatch
 typedef void (*attn_fn)(AttnArgs);
-struct AttnKernels { attn_fn decode, append, fast; int threads_fast; };
+struct AttnKernels { attn_fn decode, append, fast, rows; int threads_fast; size_t rows_smem; };
 bool pick_attn(int hd, int gq, AttnKernels* k) {
 #define CASE(HD, GQ)                                                               \
     if (hd == HD && gq == GQ) {                                                    \
         k->decode = attn_decode_kernel<HD, GQ>;                                    \
         k->append = rope_append_kernel<HD>;                                        \
         k->fast = fast_attn_kernel<HD, GQ>;                                        \
+        k->rows = attn_rows_kernel<HD, GQ>;                                        \
+        k->rows_smem = ar_smem_bytes<HD, GQ>();                                       \
         k->threads_fast = 32 * GQ;                                                 \
         return true;                                                               \
     }
@@ -374,17 +385,64 @@ int rows_linear(fsb_dual_ar* h, const bf16* W, const bf16* X, bf16* C, int T, in
 }
 
 bool batch_gemm_active(const fsb_dual_ar* h, int M) { return h->batch_gemm && M > 8 && M <= PREFILL_ROWS; }
+bool rows_tc_active(const fsb_dual_ar* h, int M) { return h->batch_gemm == 1 && h->rg_ok && M <= 128; }
+
+// the whole layer stack runs on the tcgen05 kernel (every Linear's K is a multiple of the 64-column k block)
+bool rows_tc_layers(const fsb_dual_ar* h, int M) {
+    const fsb_dual_ar_desc& d = h->d;
+    return batch_gemm_active(h, M) && rows_tc_active(h, M) && d.dim % RG_BK == 0 && d.ffn % RG_BK == 0 &&
+           (d.n_head * d.head_dim) % RG_BK == 0;
+}
+
+const CUtensorMap* rows_map(fsb_dual_ar* h, const void* ptr, int rows, int cols, int box_rows) {
+    auto key = std::make_tuple(ptr, rows, cols, box_rows);
+    auto it = h->rg_maps.find(key);
+    if (it != h->rg_maps.end()) return &it->second;
+    CUtensorMap m;
+    if (!rg_make_map(&m, ptr, (uint64_t)rows, (uint64_t)cols, (uint32_t)box_rows)) return nullptr;
+    return &h->rg_maps.emplace(key, m).first->second;
+}
+
+// out[M][N] = epi(X[M][K] . W[N][K]^T) on the tcgen05 stream-K kernel; returns -1 if the shape is not covered
+int rows_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, const bf16* W2, const bf16* X, int M, int N, int K, int epi,
+                   const bf16* res, bf16* out, int defer = 0) {
+    if (K % RG_BK || (N + RG_BM - 1) / RG_BM > RG_MAX_TILES) return -1;
+    const int bn = rg_bn_for(M);
+    const CUtensorMap* mW = rows_map(h, W, N, K, RG_BM);
+    const CUtensorMap* mW2 = W2 ? rows_map(h, W2, N, K, RG_BM) : mW;
+    const CUtensorMap* mX = rows_map(h, X, M, K, bn);
+    if (!mW || !mW2 || !mX) return fail(h, "cuTensorMapEncodeTiled failed");
+    CK(rg_launch(s, h->use_pdl != 0, h->n_sm, *mW, *mW2, *mX, M, N, K, epi, res, out, h->rg_partial, h->rg_counters, defer));
+    return 0;
+}
+
+// finish of a deferred Linear (sum of its partial tiles + residual -> x_out) and/or the RMSNorm that follows it
+int rows_finish_norm(fsb_dual_ar* h, cudaStream_t s, int M, int N, int K_pending, const bf16* res, const bf16* x_in, bf16* x_out,
+                     const bf16* norm_w, bf16* xn) {
+    RowsFinishArgs f{};
+    f.partial = K_pending > 0 ? h->rg_partial : nullptr;
+    f.res = res; f.x_in = x_in; f.x_out = x_out; f.norm_w = norm_w; f.xn = xn;
+    f.N = N; f.bn = rg_bn_for(M); f.kb = K_pending > 0 ? K_pending / RG_BK : 1; f.n_tiles = (N + RG_BM - 1) / RG_BM;
+    const long long U = (long long)f.n_tiles * f.kb;
+    f.G = (int)(U < h->n_sm ? U : h->n_sm);
+    f.eps = h->d.norm_eps;
+    if (f.partial == nullptr && norm_w == nullptr) return 0;
+    CK(launch(rows_finish_norm_kernel, dim3(M), dim3(RF_THREADS), 0, s, h->use_pdl != 0, f));
+    return 0;
+}
 
 // transformer layers over 8 < M <= PREFILL_ROWS decode rows (one row per request, each with its own position and KV
 // slot): every Linear runs ONCE over all rows, so a step streams the weights once however many requests are in flight.
 // Same contract as run_layers (result in h->x / h->xf); scratch = the prompt-pass buffers.
 int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_in, const int32_t* pos,
-                    const int32_t* slots, int pos_fixed) {
+                    const int32_t* slots, int pos_fixed, const bf16* tail_norm_w, bf16* tail_xn) {
     const fsb_dual_ar_desc& d = h->d;
     const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn, QKV = (H + 2 * KV) * HD;
     AttnKernels ak;
     if (!pick_attn(HD, H / KV, &ak)) return fail(h, "unsupported head_dim / GQA ratio");
-    if (int r = ensure_blas(h, s)) return r;
+    const bool tc = rows_tc_layers(h, M);
+    if (!tc)
+        if (int r = ensure_blas(h, s)) return r;
     const std::vector<LayerW>& L = fast ? h->fast : h->slow;
     bf16* xa = fast ? h->xf : h->x;
     bf16* xb = fast ? h->xf2 : h->x2;
@@ -395,16 +453,34 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
         const LayerW& w = L[l];
         if (!w.wqkv || !w.wo || !w.w1 || !w.w2 || !w.w3 || !w.attn_norm || !w.ffn_norm || !w.kc || !w.vc)
             return fail(h, "unbound weights / kv cache in layer " + std::to_string(l));
-        rmsnorm_rows_kernel<<<M, 256, 0, s>>>(cur, w.attn_norm, h->pxn, D, d.norm_eps);
-        if (int r = rows_linear(h, w.wqkv, h->pxn, h->qkv, M, QKV, D)) return r;
+        if (!tc) rmsnorm_rows_kernel<<<M, 256, 0, s>>>(cur, w.attn_norm, h->pxn, D, d.norm_eps);
         AttnArgs a = make_attn_args(h, w, fast, pos, slots, pos_fixed);
-        if (fast) {
-            CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, false, a));
-        } else {
-            a.splits = splits;
-            a.fused_append = 1;
-            CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, false, a));
+        a.splits = splits;
+        a.fused_append = 1;
+        if (tc) {
+            // Linears with few weight tiles (wo, w2: N = dim) leave fp32 partial tiles behind; the RMSNorm pass that follows
+            // them anyway finishes them (sum in CTA order + residual) row-parallel.  wqkv / gate-up finish in-kernel.
+            const bool pdl = h->use_pdl != 0;
+            const bool last = l + 1 == L.size();
+            if (l == 0)
+                if (int r = rows_finish_norm(h, s, M, D, 0, nullptr, cur, nullptr, w.attn_norm, h->pxn)) return r;
+            if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, h->qkv)) return r;
+            if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
+            else CK(launch(ak.rows, dim3(splits, KV, M), dim3(AR_THREADS), ak.rows_smem, s, pdl, a));
+            const bool dfr = D <= RF_MAX_TILES * RG_BM;
+            if (int r = rows_linear_tc(h, s, w.wo, nullptr, h->y, M, D, H * HD, RG_EPI_RESIDUAL, cur, xb, dfr)) return r;
+            if (int r = rows_finish_norm(h, s, M, D, dfr ? H * HD : 0, cur, xb, xb, w.ffn_norm, h->pxn)) return r;
+            if (int r = rows_linear_tc(h, s, w.w1, w.w3, h->pxn, M, F, D, RG_EPI_SWIGLU, nullptr, h->ff)) return r;
+            if (int r = rows_linear_tc(h, s, w.w2, nullptr, h->ff, M, D, F, RG_EPI_RESIDUAL, xb, xa, dfr)) return r;
+            const bf16* nw = last ? tail_norm_w : L[l + 1].attn_norm;
+            bf16* nx = last ? tail_xn : h->pxn;
+            if (int r = rows_finish_norm(h, s, M, D, dfr ? F : 0, xb, xa, xa, nw, nx)) return r;
+            cur = xa;
+            continue;
         }
+        if (int r = rows_linear(h, w.wqkv, h->pxn, h->qkv, M, QKV, D)) return r;
+        if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, false, a));
+        else CK(launch(ak.rows, dim3(splits, KV, M), dim3(AR_THREADS), ak.rows_smem, s, false, a));
         if (int r = rows_linear(h, w.wo, h->y, h->ptmp, M, D, H * HD)) return r;
         add_rows_kernel<<<ew_blocks, 256, 0, s>>>(cur, h->ptmp, xb, (size_t)M * D / 8);
         rmsnorm_rows_kernel<<<M, 256, 0, s>>>(xb, w.ffn_norm, h->pxn, D, d.norm_eps);
@@ -423,8 +499,13 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
 int run_head_rows(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* head, int N, const bf16* x, const bf16* norm_w,
                   bf16* xnorm, bf16* logits) {
     const fsb_dual_ar_desc& d = h->d;
+    // on the tcgen05 path the layer stack's last finish pass has already produced the normalised rows (tail norm)
+    if (!rows_tc_layers(h, M)) rmsnorm_rows_kernel<<<M, 256, 0, s>>>(x, norm_w, xnorm, d.dim, d.norm_eps);
+    if (rows_tc_active(h, M)) {
+        const int r = rows_linear_tc(h, s, head, nullptr, xnorm, M, N, d.dim, RG_EPI_STORE, nullptr, logits);
+        if (r >= 0) return r;
+    }
     if (int r = ensure_blas(h, s)) return r;
-    rmsnorm_rows_kernel<<<M, 256, 0, s>>>(x, norm_w, xnorm, d.dim, d.norm_eps);
     if (int r = rows_linear(h, head, xnorm, logits, M, N, d.dim)) return r;
     CK(cudaGetLastError());
     return 0;
@@ -432,8 +513,10 @@ int run_head_rows(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* head, int N
 
 // transformer layers over M rows. x_in: [M][D] input (not modified); result in h->x (slow) / h->xf (fast)
 int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_in, const int32_t* pos,
-               const int32_t* slots, bool fused_append, int pos_fixed) {
-    if (fused_append && batch_gemm_active(h, M)) return run_layers_rows(h, s, fast, M, x_in, pos, slots, pos_fixed);
+               const int32_t* slots, bool fused_append, int pos_fixed, const bf16* tail_norm_w = nullptr,
+               bf16* tail_xn = nullptr) {
+    if (fused_append && batch_gemm_active(h, M))
+        return run_layers_rows(h, s, fast, M, x_in, pos, slots, pos_fixed, tail_norm_w, tail_xn);
     const fsb_dual_ar_desc& d = h->d;
     const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn;
     const int QKV = (H + 2 * KV) * HD;
@@ -493,9 +576,9 @@ int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, 
     // embed wrote x2; layer 0 uses it as input and as the wo residual, writes xb = x2?  -> use a distinct buffer
     // (run_layers writes xb = h->x2 in layer 0 while `cur` == h->x2 is still the residual source of the same
     //  kernel: same element read-then-written by the same thread only, which is safe for EPI_RESIDUAL.)
-    if (int r = run_layers(h, s, false, M, h->x2, pos, slots, true, -1)) return r;
     const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
     if (!head || !h->norm) return fail(h, "LM head / final norm not bound");
+    if (int r = run_layers(h, s, false, M, h->x2, pos, slots, true, -1, h->norm, h->hidden)) return r;
     if (batch_gemm_active(h, M)) return run_head_rows(h, s, M, head, d.vocab, h->x, h->norm, h->hidden, h->slow_logits);
     CK(run_gemv(h->gc, h->use_pdl != 0, s, M, d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head,
                 nullptr, h->x, h->norm, nullptr, h->slow_logits, h->hidden, d.norm_eps, nullptr, 0));
@@ -505,9 +588,9 @@ int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, 
 int run_fast_step(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* x_in, int cb_idx, bool want_logits) {
     const fsb_dual_ar_desc& d = h->d;
     if (cb_idx < 0 || cb_idx >= d.num_codebooks) return fail(h, "codebook_idx out of range");
-    if (int r = run_layers(h, s, true, M, x_in, nullptr, nullptr, true, cb_idx)) return r;
+    if (want_logits && (!h->fast_out || !h->fast_norm)) return fail(h, "fast head not bound");
+    if (int r = run_layers(h, s, true, M, x_in, nullptr, nullptr, true, cb_idx, want_logits ? h->fast_norm : nullptr, h->pxb)) return r;
     if (want_logits) {
-        if (!h->fast_out || !h->fast_norm) return fail(h, "fast head not bound");
         bf16* lg = h->fast_logits + (size_t)cb_idx * h->R * d.codebook_size;
         if (batch_gemm_active(h, M)) return run_head_rows(h, s, M, h->fast_out, d.codebook_size, h->xf, h->fast_norm, h->pxb, lg);
         CK(run_gemv(h->gc, h->use_pdl != 0, s, M, d.codebook_size, d.dim, PRO_RMSNORM, EPI_STORE,
@@ -788,6 +871,9 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
         T(py, bf16, PR * d.n_head * d.head_dim) T(ptmp, bf16, PR * d.dim) T(pf1, bf16, PR * d.ffn) T(pf3, bf16, PR * d.ffn)
         T(cublas_ws, char, CUBLAS_WS_BYTES)
     }
+    if (d.max_rows > 8) {
+        T(rg_partial, float, rg_partial_bytes(RG_GRID_MAX, 128) / sizeof(float)) T(rg_counters, int, RG_MAX_TILES)
+    }
     T(mega_buf, char, MEGA_BUF_BYTES) T(mega_sync, unsigned, 64) T(mega_prof, unsigned long long, 16)
     // flag-in-data activations of the persistent frame kernel (batch 1): one u32 per element
     const size_t tg = (size_t)2 * d.dim + QKV + (size_t)d.n_head * d.head_dim + d.ffn + (size_t)4 * d.dim;
@@ -831,6 +917,7 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
     h->gc.n_sm = h->n_sm;
     CK(set_gemv_attrs());
     CK(set_gemv_tma_attrs());
+    CK(cudaFuncSetAttribute((const void*)ak.rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ak.rows_smem));
     CK(cudaMemset(h->counters, 0, (size_t)std::max(d.max_rows, 8) * d.n_kv_head * sizeof(int32_t)));
     CK(cudaMemset(h->mega_sync, 0, 64 * sizeof(unsigned)));
     {
@@ -844,6 +931,11 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
         CK(cudaMemset(h->ll_ml, 0, (size_t)d.n_kv_head * h->max_splits * gq_ * 2 * sizeof(uint2)));
     }
     CK(cudaMemset(h->mega_prof, 0, 16 * sizeof(unsigned long long)));
+    if (h->rg_counters) {
+        CK(cudaMemset(h->rg_counters, 0, RG_MAX_TILES * sizeof(int)));
+        h->rg_ok = h->n_sm <= RG_GRID_MAX && rg_get_encode() != nullptr && rg_set_attrs() == cudaSuccess;
+    }
+    if (const char* e = getenv("FSB_BATCH_GEMM")) h->batch_gemm = atoi(e);
     if (mega_shape_ok(d)) {
         mega_fn mf = pick_mega(d.head_dim, d.n_head / d.n_kv_head);
         int coop = 0, occ = 0;
@@ -1090,7 +1182,7 @@ int fsb_dual_ar_decode_frames(fsb_dual_ar* h, const fsb_frame_args* args, int32_
     if (!h->fast_emb) return fail(h, "fast_embeddings not bound");
     cudaStream_t s = (cudaStream_t)stream;
     const bool mega = mega_active(h, args->batch);
-    if (batch_gemm_active(h, args->batch))  // the handle must exist before a stream capture begins
+    if (batch_gemm_active(h, args->batch) && !rows_tc_active(h, args->batch))  // the handle must exist before a stream capture begins
         if (int r = ensure_blas(h, s)) return r;
     const bool fresh = !h->cached_valid || memcmp(&h->cached, args, sizeof(fsb_frame_args)) != 0;
     if (mega && fresh) {
@@ -1169,6 +1261,32 @@ int fsb_gemv(const void* W, const void* W2, const void* x, const void* norm_w, c
                              eps, nullptr, 0);
     (void)h;
     return e == cudaSuccess ? 0 : 3;
+}
+
+size_t fsb_rows_gemm_scratch_bytes(void) {  // counters | partial tiles | 8 clock stamps per CTA (written when FSB_RG_TRACE is set)
+    return RG_MAX_TILES * sizeof(int) + rg_partial_bytes(RG_GRID_MAX, 128) + RG_GRID_MAX * 8 * sizeof(unsigned long long);
+}
+
+int fsb_rows_gemm(const void* W, const void* W2, const void* x, const void* res, void* out, int32_t M, int32_t N, int32_t K,
+                  int32_t epi, void* scratch, size_t scratch_bytes, void* stream) {
+    if (!W || !x || !out || !scratch || M < 1 || M > 128 || N < 1 || K < RG_BK || K % RG_BK) return 1;
+    if ((N + RG_BM - 1) / RG_BM > RG_MAX_TILES || scratch_bytes < fsb_rows_gemm_scratch_bytes()) return 1;
+    if (epi < RG_EPI_STORE || epi > RG_EPI_SWIGLU || (epi == RG_EPI_SWIGLU && !W2) || (epi == RG_EPI_RESIDUAL && !res)) return 1;
+    int dev = 0, n_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 2;
+    if (n_sm > RG_GRID_MAX || rg_set_attrs() != cudaSuccess) return 2;
+    CUtensorMap mW, mW2, mX;
+    if (!rg_make_map(&mW, W, (uint64_t)N, (uint64_t)K, RG_BM)) return 3;
+    if (!rg_make_map(&mW2, W2 ? W2 : W, (uint64_t)N, (uint64_t)K, RG_BM)) return 3;
+    if (!rg_make_map(&mX, x, (uint64_t)M, (uint64_t)K, (uint32_t)rg_bn_for(M))) return 3;
+    int* counters = (int*)scratch;
+    float* partial = (float*)((char*)scratch + RG_MAX_TILES * sizeof(int));
+    static const bool want_trace = getenv("FSB_RG_TRACE") != nullptr;
+    static const int defer = getenv("FSB_RG_DEFER") ? atoi(getenv("FSB_RG_DEFER")) : 0;  // profiling: skip the in-kernel finish
+    unsigned long long* trace = want_trace ? (unsigned long long*)((char*)partial + rg_partial_bytes(RG_GRID_MAX, 128)) : nullptr;
+    cudaError_t e = rg_launch((cudaStream_t)stream, false, n_sm, mW, mW2, mX, M, N, K, epi, (const bf16*)res, (bf16*)out, partial, counters,
+                              defer, trace);
+    return e == cudaSuccess ? 0 : 4;
 }
 
 int fsb_sample(const void* logits, const void* bias, int32_t B, int32_t V, int32_t top_k, float temperature, float top_p,

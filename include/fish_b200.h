@@ -111,6 +111,13 @@ int32_t fsb_dual_ar_launches_per_frame(const fsb_dual_ar* h, int32_t batch);
  * epi: 0 store, 1 + res (llama.py:841-842), 2 SwiGLU with W2 (llama.py:986). All bf16. */
 int fsb_gemv(const void* W, const void* W2, const void* x, const void* norm_w, const void* res, void* out,
              int32_t M, int32_t N, int32_t K, int32_t pro, int32_t epi, float eps, void* stream);
+/* Many-row Linear of a batched decode step on the tcgen05 stream-K kernel (csrc/rows_gemm.cuh):
+ * out[m][n] = epi(sum_k W[n][k] * x[m][k]), 1 <= M <= 128, K % 64 == 0, all bf16, W row-major [N][K] (llama.py:856-860,
+ * 981-983).  epi: 0 store, 1 bf16(res + bf16(acc)) (llama.py:841-842), 2 SwiGLU with W2 (llama.py:986).
+ * `scratch`: fsb_rows_gemm_scratch_bytes() bytes of device memory, zeroed once by the caller. */
+size_t fsb_rows_gemm_scratch_bytes(void);
+int fsb_rows_gemm(const void* W, const void* W2, const void* x, const void* res, void* out, int32_t M, int32_t N,
+                  int32_t K, int32_t epi, void* scratch, size_t scratch_bytes, void* stream);
 /* sample() of inference.py:80-93 on device. logits bf16 [B][V]; uniforms bf16 [B][n_variants][V] or NULL;
  * out int32 [B][2]: the index drawn with (temperature, top_p) and, if n_variants == 2, with (temp2, top_p2). */
 int fsb_sample(const void* logits, const void* bias, int32_t B, int32_t V, int32_t top_k, float temperature,

@@ -116,3 +116,80 @@ def test_sampling_golden_cases(lib):
     # against the recorded CPU reference only tie-order-dependent cases may differ (torch's CPU sort is unstable)
     assert all(t in ("all_equal", "quantised_ties", "random", "biased") for _, t in mism_ref), mism_ref
     assert len(mism_ref) <= max(3, len(cases) // 20), mism_ref
+
+
+# ------------------------------------------------------------------------------------------- many-row Linear (tcgen05 stream-K)
+def _rows_gemm(lib, W, x, W2=None, res=None, epi=0, scratch=None):
+    M, K = x.shape
+    N = W.shape[0]
+    out = torch.empty((M, N), dtype=torch.bfloat16, device="cuda")
+    nbytes = lib.fsb_rows_gemm_scratch_bytes()
+    if scratch is None:
+        scratch = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+    p = lambda t: None if t is None else t.data_ptr()
+    rc = lib.fsb_rows_gemm(p(W), p(W2), p(x), p(res), p(out), M, N, K, epi, scratch.data_ptr(), nbytes,
+                           torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+    return out
+
+
+def _rows_ref(W, x, W2=None, res=None, epi=0):
+    """fp32 reference of the same op with the reference's rounding points (one rounding per Linear, llama.py:838-843,985-986)."""
+    acc = x.float() @ W.float().t()
+    if epi == 0:
+        return acc.bfloat16()
+    if epi == 1:
+        return (res.float() + acc.bfloat16().float()).bfloat16()
+    g = acc.bfloat16().float()
+    up = (x.float() @ W2.float().t()).bfloat16().float()
+    return ((g / (1 + torch.exp(-g))).bfloat16().float() * up).bfloat16()
+
+
+ROWS_SHAPES = [  # (M, N, K): every Linear of the path at tiny and S2-Pro sizes, ragged N and M, tile-count edge cases
+    (12, 768, 512), (12, 512, 512), (12, 1536, 512), (12, 512, 1536), (33, 1000, 1536), (9, 130, 64), (64, 128, 9728),
+    (64, 6144, 2560), (64, 2560, 4096), (64, 9728, 2560), (64, 2560, 9728), (64, 4096, 2560), (17, 2560, 4096),
+    (128, 6144, 2560), (100, 2560, 9728),
+]
+
+
+@pytest.mark.parametrize("M,N,K", ROWS_SHAPES)
+@pytest.mark.parametrize("epi", [0, 1, 2])
+def test_rows_gemm_matches_fp32_reference(lib, M, N, K, epi):
+    g = torch.Generator().manual_seed(M * 131 + N * 7 + K + epi)
+    W = (torch.randn(N, K, generator=g) * 0.02).bfloat16().cuda()
+    W2 = (torch.randn(N, K, generator=g) * 0.02).bfloat16().cuda() if epi == 2 else None
+    x = torch.randn(M, K, generator=g).bfloat16().cuda()
+    res = torch.randn(M, N, generator=g).bfloat16().cuda() if epi == 1 else None
+    scratch = torch.zeros(lib.fsb_rows_gemm_scratch_bytes(), dtype=torch.uint8, device="cuda")
+    got = _rows_gemm(lib, W, x, W2, res, epi, scratch)
+    ref = _rows_ref(W, x, W2, res, epi)
+    # fp32 accumulation order differs from torch's, so the Linear output may round to the neighbouring bf16 value:
+    # allow one bf16 ulp of the LARGEST operand of the epilogue (2^-7 relative) + a small absolute term
+    err = (got.float() - ref.float()).abs()
+    lin = (x.float() @ W.float().t()).abs()
+    mag = ref.float().abs()
+    if epi == 1:
+        mag = mag + lin + res.float().abs()
+    if epi == 2:
+        mag = mag + lin * (x.float() @ W2.float().t()).abs()
+    tol = mag * 2.0 ** -7 + 2e-3
+    bad = int((err > tol).sum())
+    print(f"[parity] rows_gemm M={M} N={N} K={K} epi={epi}: max-abs {float(err.max()):.5f}, exact {float((got == ref).float().mean()):.4f}")
+    assert bad == 0, (bad, float(err.max()))
+    # stream-K partial sums are added in CTA order: a second launch on the same scratch is bit-identical
+    again = _rows_gemm(lib, W, x, W2, res, epi, scratch)
+    assert torch.equal(got, again)
+    assert int(scratch[: 2048 * 4].view(torch.int32).abs().sum()) == 0  # arrival counters re-armed
+
+
+def test_rows_gemm_lm_head_shape(lib):
+    """The S2-Pro LM head (N = 155776 rows, 1217 weight tiles) over 64 rows."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    N, K, M = 155776, 2560, 64
+    W = torch.empty(N, K, dtype=torch.bfloat16, device="cuda").normal_(0, 0.02, generator=g)
+    x = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    got = _rows_gemm(lib, W, x)
+    ref = _rows_ref(W, x)
+    err = (got.float() - ref.float()).abs()
+    assert int((err > ref.float().abs() * 2.0 ** -7 + 2e-3).sum()) == 0, float(err.max())
