@@ -470,285 +470,6 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
     attn_decode_body<HD, GQ, SyncBlock<ATTN_THREADS>>(a, blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
 }
 
-// ----------------------------------------------------------------------------- slow-AR decode attention, many rows
-// Same math and the same (split, kv head, row) work item as attn_decode_body, shaped for steps with many requests in flight
-// (config 3: 64 rows x 2k keys = 537 MB of cached K/V per layer), where the op is a pure HBM stream: the cached keys and
-// values of an item are one contiguous byte range each ([S][HD] per (slot, kv head)), so they are pulled through a ring
-// of AR_STAGES shared-memory stages by bulk async copies (one K and one V copy of AR_TILE rows per stage, mbarrier
-// complete_tx) instead of per-thread register loads: 2 resident CTAs keep ~190 KB in flight per SM, whatever the
-// register budget.  The first ring fill is issued before griddepcontrol.wait (old cache rows do not depend on this step).
-#define AR_THREADS 256
-#define AR_TILE 64
-#define AR_STAGES 3
-__device__ __forceinline__ uint32_t ar_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void ar_mbar_init(uint64_t* b, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ar_smem_u32(b)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void ar_mbar_expect_tx(uint64_t* b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(ar_smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void ar_mbar_wait(uint64_t* b, uint32_t parity) {
-    uint32_t ok, spins = 0;
-    long long t0 = 0;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(ar_smem_u32(b)), "r"(parity) : "memory");
-        if (!ok && (++spins & 0xfffu) == 0) {  // a lost copy must fault, not hang the GPU
-            if (t0 == 0) t0 = clock64();
-            else if (clock64() - t0 > 4000000000LL) __trap();
-        }
-    } while (!ok);
-}
-__device__ __forceinline__ void ar_bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(ar_smem_u32(dst_smem)),
-                 "l"(src), "r"(bytes), "r"(ar_smem_u32(bar)) : "memory");
-}
-template <int HD, int GQ>
-__host__ __device__ constexpr size_t ar_smem_bytes() {  // the ring, or the final reduction buffer that reuses its memory
-    constexpr size_t ring = (size_t)AR_STAGES * AR_TILE * HD * 2 * 2;
-    constexpr size_t red = (size_t)(AR_THREADS / (HD / 8)) * GQ * (HD + 4) * 4;
-    return ring > red ? ring : red;
-}
-
-template <int HD, int GQ>
-__global__ void __launch_bounds__(AR_THREADS, 2) attn_rows_kernel(AttnArgs a) {
-    constexpr int EPL = HD / 32;
-    constexpr int LPK = HD / 8;              // lanes per key row (16 B each)
-    constexpr int KPI = AR_THREADS / LPK;    // keys per CTA step
-    constexpr int NWARP = AR_THREADS / 32;
-    constexpr uint32_t HALF = AR_TILE * HD * 2;  // bytes of the K (or V) rows of one stage
-    extern __shared__ __align__(128) unsigned char ar_ring[];
-    __shared__ uint64_t full_bar[AR_STAGES];
-    __shared__ float qs[GQ][HD];
-    __shared__ float knew[HD], vnew[HD];
-    __shared__ float sc[GQ][AR_TILE];
-    __shared__ float mrun[GQ], lrun[GQ], corr[GQ];
-    __shared__ int is_last;
-
-    const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // pos / slots are written by earlier steps' frame_end kernels and by the host, never by the kernel just before this one
-    const int pos = a.pos[m];
-    const int slot = a.slots ? a.slots[m] : m;
-    const int qkv_w = (a.H + 2 * a.KV) * HD;
-    const bf16* row = a.qkv + (size_t)m * qkv_w;
-    const int n_keys = pos + 1;
-    const int per = (n_keys + a.splits - 1) / a.splits;
-    const int k0 = split * per;
-    const int k1 = min(n_keys, k0 + per);
-    const bool owns_new = (pos >= k0) && (pos < k1);
-    const int kc1 = owns_new ? min(k1, pos) : k1;  // keys [k0, kc1) come from the cache
-    const int n_tiles = (k1 > k0) ? (k1 - k0 + AR_TILE - 1) / AR_TILE : 0;
-    const bf16* kbase = a.kcache + ((size_t)slot * a.KV + h) * a.S * HD;
-    const bf16* vbase = a.vcache + ((size_t)slot * a.KV + h) * a.S * HD;
-
-    auto issue = [&](int i) {  // one thread: tile i of this item into stage i % AR_STAGES
-        const int st = i % AR_STAGES, t0 = k0 + i * AR_TILE;
-        const int nc = max(0, min(kc1, t0 + AR_TILE) - t0);
-        const uint32_t bytes = (uint32_t)nc * HD * 2;
-        ar_mbar_expect_tx(&full_bar[st], 2 * bytes);
-        if (bytes) {
-            ar_bulk_g2s(ar_ring + (size_t)st * 2 * HALF, kbase + (size_t)t0 * HD, bytes, &full_bar[st]);
-            ar_bulk_g2s(ar_ring + (size_t)st * 2 * HALF + HALF, vbase + (size_t)t0 * HD, bytes, &full_bar[st]);
-        }
-    };
-    if (tid == 0) {
-        for (int s2 = 0; s2 < AR_STAGES; ++s2) ar_mbar_init(&full_bar[s2], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        for (int i = 0; i < min(n_tiles, AR_STAGES); ++i) issue(i);
-        l2_prefetch_share(a.pf_ptr, a.pf_bytes, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
-                          gridDim.x * gridDim.y * gridDim.z);
-    }
-    pdl_wait();
-    pdl_launch_dependents();
-
-    // ---- q prep (one warp per q head of this GQA group), fused K/V append by the split that owns the new position
-    const bf16* rope_row = a.rope + (size_t)pos * HD;
-    for (int g = warp; g < GQ; g += NWARP) {
-        float qin[EPL], q[EPL];
-        load_head<HD, false>(row + (h * GQ + g) * HD, nullptr, 0, qin);
-        head_norm_rope<HD>(qin, a.q_norm, rope_row, a.qk_norm, a.eps, q);
-#pragma unroll
-        for (int i = 0; i < EPL; ++i) qs[g][lane * EPL + i] = q[i];
-    }
-    if (owns_new) {
-        const size_t co = (((size_t)slot * a.KV + h) * a.S + pos) * HD;
-        if (warp == (GQ % NWARP)) {
-            float kin[EPL], k[EPL];
-            load_head<HD, false>(row + (a.H + h) * HD, nullptr, 0, kin);
-            head_norm_rope<HD>(kin, a.k_norm, rope_row, a.qk_norm, a.eps, k);
-#pragma unroll
-            for (int i = 0; i < EPL; ++i) {
-                knew[lane * EPL + i] = k[i];
-                if (a.fused_append) a.kcache[co + lane * EPL + i] = __float2bfloat16_rn(k[i]);
-            }
-        }
-        if (warp == ((GQ + 1) % NWARP)) {
-            float vin[EPL];
-            load_head<HD, false>(row + (a.H + a.KV + h) * HD, nullptr, 0, vin);
-#pragma unroll
-            for (int i = 0; i < EPL; ++i) {
-                vnew[lane * EPL + i] = vin[i];
-                if (a.fused_append) a.vcache[co + lane * EPL + i] = __float2bfloat16_rn(vin[i]);
-            }
-        }
-    }
-    if (tid < GQ) { mrun[tid] = -INFINITY; lrun[tid] = 0.f; }
-    __syncthreads();
-
-    const int kslot = tid / LPK, chunk = tid % LPK;
-    float qreg[GQ][8];
-#pragma unroll
-    for (int g = 0; g < GQ; ++g)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) qreg[g][i] = qs[g][chunk * 8 + i];
-    float acc[GQ][8];
-#pragma unroll
-    for (int g = 0; g < GQ; ++g)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc[g][i] = 0.f;
-
-    for (int it = 0; it < n_tiles; ++it) {
-        const int st = it % AR_STAGES;
-        const int t0 = k0 + it * AR_TILE, t1 = min(k1, t0 + AR_TILE);
-        const unsigned char* ks = ar_ring + (size_t)st * 2 * HALF;
-        const unsigned char* vs = ks + HALF;
-        ar_mbar_wait(&full_bar[st], (uint32_t)(it / AR_STAGES) & 1u);
-        // -- scores
-        for (int jb = t0; jb < t1; jb += KPI) {  // warp-uniform trip count (shuffles below)
-            const int j = jb + kslot;
-            const bool jv = j < t1;
-            float kf[8];
-            if (jv && j < kc1) {
-                unpack8(*reinterpret_cast<const uint4*>(ks + ((size_t)(j - t0) * HD + chunk * 8) * 2), kf);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) kf[i] = jv ? knew[chunk * 8 + i] : 0.f;
-            }
-            float d[GQ];
-#pragma unroll
-            for (int g = 0; g < GQ; ++g) {
-                float s2 = 0.f;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) s2 = fmaf(qreg[g][i], kf[i], s2);
-                d[g] = s2;
-            }
-#pragma unroll
-            for (int o = LPK / 2; o > 0; o >>= 1)
-#pragma unroll
-                for (int g = 0; g < GQ; ++g) d[g] += __shfl_xor_sync(0xffffffffu, d[g], o);
-            if (chunk == 0 && jv)
-#pragma unroll
-                for (int g = 0; g < GQ; ++g) sc[g][j - t0] = d[g] * a.scale;
-        }
-        __syncthreads();
-        // -- online softmax bookkeeping: warp g owns head g
-        for (int g = warp; g < GQ; g += NWARP) {
-            float mx = -INFINITY;
-            for (int j = lane; j < t1 - t0; j += 32) mx = fmaxf(mx, sc[g][j]);
-            mx = warp_max(mx);
-            const float mold = mrun[g];
-            const float mnew = fmaxf(mold, mx);
-            float sum = 0.f;
-            for (int j = lane; j < t1 - t0; j += 32) {
-                const float p = expf(sc[g][j] - mnew);
-                sc[g][j] = p;
-                sum += p;
-            }
-            sum = warp_sum(sum);
-            if (lane == 0) {
-                const float c = (mold == -INFINITY) ? 0.f : expf(mold - mnew);
-                corr[g] = c;
-                mrun[g] = mnew;
-                lrun[g] = lrun[g] * c + sum;
-            }
-        }
-        __syncthreads();
-        // -- rescale and accumulate P.V
-#pragma unroll
-        for (int g = 0; g < GQ; ++g) {
-            const float c = corr[g];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) acc[g][i] *= c;
-        }
-        for (int j = t0 + kslot; j < t1; j += KPI) {
-            float vf[8];
-            if (j < kc1) {
-                unpack8(*reinterpret_cast<const uint4*>(vs + ((size_t)(j - t0) * HD + chunk * 8) * 2), vf);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) vf[i] = vnew[chunk * 8 + i];
-            }
-#pragma unroll
-            for (int g = 0; g < GQ; ++g) {
-                const float p = sc[g][j - t0];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) acc[g][i] = fmaf(p, vf[i], acc[g][i]);
-            }
-        }
-        __syncthreads();  // every thread is done with this stage (and with sc): it can be refilled
-        if (tid == 0 && it + AR_STAGES < n_tiles) issue(it + AR_STAGES);
-    }
-
-    // ---- reduce acc over the KPI key slots (the ring is idle now: reuse it)
-    float (*accs)[GQ][HD + 4] = reinterpret_cast<float (*)[GQ][HD + 4]>(ar_ring);
-#pragma unroll
-    for (int g = 0; g < GQ; ++g)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) accs[kslot][g][chunk * 8 + i] = acc[g][i];
-    __syncthreads();
-
-    const int H = a.H;
-    if (a.splits == 1) {
-        for (int e = tid; e < GQ * HD; e += AR_THREADS) {
-            const int g = e / HD, d = e % HD;
-            float s2 = 0.f;
-#pragma unroll
-            for (int k = 0; k < KPI; ++k) s2 += accs[k][g][d];
-            a.y[(size_t)m * H * HD + (h * GQ + g) * HD + d] = __float2bfloat16_rn(s2 / lrun[g]);
-        }
-        return;
-    }
-    // ---- write partial, last CTA of this (row, kv head) merges
-    const size_t pbase = (((size_t)m * a.KV + h) * a.splits + split);
-    for (int e = tid; e < GQ * HD; e += AR_THREADS) {
-        const int g = e / HD, d = e % HD;
-        float s2 = 0.f;
-#pragma unroll
-        for (int k = 0; k < KPI; ++k) s2 += accs[k][g][d];
-        a.ws_acc[pbase * GQ * HD + e] = s2;
-    }
-    if (tid < GQ) {
-        a.ws_ml[(pbase * GQ + tid) * 2 + 0] = mrun[tid];
-        a.ws_ml[(pbase * GQ + tid) * 2 + 1] = lrun[tid];
-    }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        const int prev = atomicAdd(&a.counters[m * a.KV + h], 1);
-        is_last = (prev == a.splits - 1);
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    const size_t b0 = ((size_t)m * a.KV + h) * a.splits;
-    for (int e = tid; e < GQ * HD; e += AR_THREADS) {
-        const int g = e / HD;
-        float Mx = -INFINITY;
-        for (int s2 = 0; s2 < a.splits; ++s2) Mx = fmaxf(Mx, __ldcg(&a.ws_ml[((b0 + s2) * GQ + g) * 2]));
-        float num = 0.f, den = 0.f;
-        for (int s2 = 0; s2 < a.splits; ++s2) {
-            const float ms = __ldcg(&a.ws_ml[((b0 + s2) * GQ + g) * 2]);
-            const float ls = __ldcg(&a.ws_ml[((b0 + s2) * GQ + g) * 2 + 1]);
-            const float w = (ms == -INFINITY) ? 0.f : expf(ms - Mx);
-            num = fmaf(w, __ldcg(&a.ws_acc[(b0 + s2) * GQ * HD + e]), num);
-            den = fmaf(w, ls, den);
-        }
-        a.y[(size_t)m * H * HD + (h * GQ) * HD + e] = __float2bfloat16_rn(num / den);
-    }
-    if (tid == 0) a.counters[m * a.KV + h] = 0;  // re-arm for the next launch
-}
-
 // ----------------------------------------------------------------------------- slow-AR decode attention, latency form
 // Same math as attn_decode_body for ONE (split, kv head, row) item, shaped for the persistent frame kernel where this
 // op sits on a ~400-step dependent chain: the split's whole key range (<= ASP_MAXKEYS) is one tile, and every K and V

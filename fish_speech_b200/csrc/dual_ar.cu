@@ -32,7 +32,8 @@ struct LayerW {
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 constexpr size_t MEGA_BUF_BYTES = 512 * 1024;
 constexpr size_t CUBLAS_WS_BYTES = 32u << 20;
-constexpr int RG_GRID_MAX = 160;  // SMs the stream-K partial slabs are sized for
+constexpr int RG_SM_MAX = 160;                           // SMs the stream-K partial slabs are sized for
+constexpr int RG_GRID_MAX = RG_CTAS_PER_SM * RG_SM_MAX;   // (the constant is defined in rows_gemm.cuh, included below)
 constexpr size_t MEGA_TRACE_WORDS = 160 * 512 * 4;  // [CTAs][ops][4] time stamps of one frame (profiling aid)
 
 struct GemvCfg {
@@ -79,7 +80,6 @@ struct fsb_dual_ar {
                                      // per step) on this library's tcgen05 stream-K kernel (rows_gemm.cuh), 2 = the same through
                                      // cuBLAS, 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
     float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
-    int* rg_counters = nullptr;      // per-tile arrival counters (zero between launches)
     bool rg_ok = false;              // tensor-map encoder available, attributes set
     std::map<std::tuple<const void*, int, int, int>, CUtensorMap> rg_maps;  // (ptr, rows, cols, box rows) -> TMA map
     int max_splits = 32;
@@ -251,15 +251,13 @@ cudaError_t run_gemv(const GemvCfg& gc, bool pdl, cudaStream_t s, int M, int N, 
 
 // ------------------------------------------------------------------------------------------- attention dispatch
 typedef void (*attn_fn)(AttnArgs);
-struct AttnKernels { attn_fn decode, append, fast, rows; int threads_fast; size_t rows_smem; };
+struct AttnKernels { attn_fn decode, append, fast; int threads_fast; };
 bool pick_attn(int hd, int gq, AttnKernels* k) {
 #define CASE(HD, GQ)                                                               \
     if (hd == HD && gq == GQ) {                                                    \
         k->decode = attn_decode_kernel<HD, GQ>;                                    \
         k->append = rope_append_kernel<HD>;                                        \
         k->fast = fast_attn_kernel<HD, GQ>;                                        \
-        k->rows = attn_rows_kernel<HD, GQ>;                                        \
-        k->rows_smem = ar_smem_bytes<HD, GQ>();                                       \
         k->threads_fast = 32 * GQ;                                                 \
         return true;                                                               \
     }
@@ -390,7 +388,7 @@ bool rows_tc_active(const fsb_dual_ar* h, int M) { return h->batch_gemm == 1 && 
 // the whole layer stack runs on the tcgen05 kernel (every Linear's K is a multiple of the 64-column k block)
 bool rows_tc_layers(const fsb_dual_ar* h, int M) {
     const fsb_dual_ar_desc& d = h->d;
-    return batch_gemm_active(h, M) && rows_tc_active(h, M) && d.dim % RG_BK == 0 && d.ffn % RG_BK == 0 &&
+    return batch_gemm_active(h, M) && rows_tc_active(h, M) && d.dim % RG_BK == 0 && d.ffn % RG_BM == 0 &&
            (d.n_head * d.head_dim) % RG_BK == 0;
 }
 
@@ -403,17 +401,32 @@ const CUtensorMap* rows_map(fsb_dual_ar* h, const void* ptr, int rows, int cols,
     return &h->rg_maps.emplace(key, m).first->second;
 }
 
-// out[M][N] = epi(X[M][K] . W[N][K]^T) on the tcgen05 stream-K kernel; returns -1 if the shape is not covered
+// out = epi(X[M][K] . W[N][K]^T) on the tcgen05 stream-K kernel (+ the finish of its split tiles); returns -1 if the
+// shape is not covered.  epi SWIGLU: W2 = up projection, `pre` = [M][2N] scratch for the pre-activation halves, out = [M][N].
+// all_partial = 1 leaves every tile as fp32 partials for rows_finish_norm (then `out` is not written here).
 int rows_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, const bf16* W2, const bf16* X, int M, int N, int K, int epi,
-                   const bf16* res, bf16* out, int defer = 0) {
-    if (K % RG_BK || (N + RG_BM - 1) / RG_BM > RG_MAX_TILES) return -1;
+                   const bf16* res, bf16* out, bf16* pre = nullptr, int all_partial = 0) {
+    const bool sw = epi == RG_EPI_SWIGLU;
+    const int NV = sw ? 2 * N : N;  // rows of the virtual weight matrix [W; W2]
+    if (K % RG_BK || (NV + RG_BM - 1) / RG_BM > RG_MAX_TILES || (sw && (N % RG_BM || !pre || !W2))) return -1;
+    if ((long long)((NV + RG_BM - 1) / RG_BM) * (K / RG_BK) * RG_GRID_MAX >= (1LL << 31)) return -1;  // 32-bit range arithmetic
     const int bn = rg_bn_for(M);
     const CUtensorMap* mW = rows_map(h, W, N, K, RG_BM);
     const CUtensorMap* mW2 = W2 ? rows_map(h, W2, N, K, RG_BM) : mW;
     const CUtensorMap* mX = rows_map(h, X, M, K, bn);
     if (!mW || !mW2 || !mX) return fail(h, "cuTensorMapEncodeTiled failed");
-    CK(rg_launch(s, h->use_pdl != 0, h->n_sm, *mW, *mW2, *mX, M, N, K, epi, res, out, h->rg_partial, h->rg_counters, defer));
+    const bool pdl = h->use_pdl != 0;
+    const int tiles_w = (N + RG_BM - 1) / RG_BM;
+    CK(rg_launch(s, pdl, h->n_sm, *mW, *mW2, *mX, M, NV, tiles_w, K, sw ? RG_EPI_STORE : epi, res, sw ? pre : out, h->rg_partial,
+                 all_partial));
+    if (!all_partial) CK(rg_finish_tiles(s, pdl, h->n_sm, M, NV, K, epi, h->rg_partial, sw ? pre : out, res, out));
     return 0;
+}
+
+// every tile of out = X . W^T can stay an fp32 partial for rows_finish_norm: a CTA's range then spans at most two tiles
+bool rows_all_partial_ok(const fsb_dual_ar* h, int N, int K) {
+    const int n_tiles = (N + RG_BM - 1) / RG_BM;
+    return n_tiles <= RF_MAX_TILES && n_tiles <= RG_CTAS_PER_SM * h->n_sm;  // tile-aligned ranges: one partial tile per CTA
 }
 
 // finish of a deferred Linear (sum of its partial tiles + residual -> x_out) and/or the RMSNorm that follows it
@@ -423,8 +436,7 @@ int rows_finish_norm(fsb_dual_ar* h, cudaStream_t s, int M, int N, int K_pending
     f.partial = K_pending > 0 ? h->rg_partial : nullptr;
     f.res = res; f.x_in = x_in; f.x_out = x_out; f.norm_w = norm_w; f.xn = xn;
     f.N = N; f.bn = rg_bn_for(M); f.kb = K_pending > 0 ? K_pending / RG_BK : 1; f.n_tiles = (N + RG_BM - 1) / RG_BM;
-    const long long U = (long long)f.n_tiles * f.kb;
-    f.G = (int)(U < h->n_sm ? U : h->n_sm);
+    f.G = rg_grid(f.n_tiles, f.kb, h->n_sm);
     f.eps = h->d.norm_eps;
     if (f.partial == nullptr && norm_w == nullptr) return 0;
     CK(launch(rows_finish_norm_kernel, dim3(M), dim3(RF_THREADS), 0, s, h->use_pdl != 0, f));
@@ -466,21 +478,21 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
                 if (int r = rows_finish_norm(h, s, M, D, 0, nullptr, cur, nullptr, w.attn_norm, h->pxn)) return r;
             if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, h->qkv)) return r;
             if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
-            else CK(launch(ak.rows, dim3(splits, KV, M), dim3(AR_THREADS), ak.rows_smem, s, pdl, a));
-            const bool dfr = D <= RF_MAX_TILES * RG_BM;
-            if (int r = rows_linear_tc(h, s, w.wo, nullptr, h->y, M, D, H * HD, RG_EPI_RESIDUAL, cur, xb, dfr)) return r;
-            if (int r = rows_finish_norm(h, s, M, D, dfr ? H * HD : 0, cur, xb, xb, w.ffn_norm, h->pxn)) return r;
-            if (int r = rows_linear_tc(h, s, w.w1, w.w3, h->pxn, M, F, D, RG_EPI_SWIGLU, nullptr, h->ff)) return r;
-            if (int r = rows_linear_tc(h, s, w.w2, nullptr, h->ff, M, D, F, RG_EPI_RESIDUAL, xb, xa, dfr)) return r;
+            else CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, pdl, a));
+            const bool dfr_o = rows_all_partial_ok(h, D, H * HD), dfr_2 = rows_all_partial_ok(h, D, F);
+            if (int r = rows_linear_tc(h, s, w.wo, nullptr, h->y, M, D, H * HD, RG_EPI_RESIDUAL, cur, xb, nullptr, dfr_o)) return r;
+            if (int r = rows_finish_norm(h, s, M, D, dfr_o ? H * HD : 0, cur, xb, xb, w.ffn_norm, h->pxn)) return r;
+            if (int r = rows_linear_tc(h, s, w.w1, w.w3, h->pxn, M, F, D, RG_EPI_SWIGLU, nullptr, h->ff, h->pf1)) return r;
+            if (int r = rows_linear_tc(h, s, w.w2, nullptr, h->ff, M, D, F, RG_EPI_RESIDUAL, xb, xa, nullptr, dfr_2)) return r;
             const bf16* nw = last ? tail_norm_w : L[l + 1].attn_norm;
             bf16* nx = last ? tail_xn : h->pxn;
-            if (int r = rows_finish_norm(h, s, M, D, dfr ? F : 0, xb, xa, xa, nw, nx)) return r;
+            if (int r = rows_finish_norm(h, s, M, D, dfr_2 ? F : 0, xb, xa, xa, nw, nx)) return r;
             cur = xa;
             continue;
         }
         if (int r = rows_linear(h, w.wqkv, h->pxn, h->qkv, M, QKV, D)) return r;
         if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, false, a));
-        else CK(launch(ak.rows, dim3(splits, KV, M), dim3(AR_THREADS), ak.rows_smem, s, false, a));
+        else CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, false, a));
         if (int r = rows_linear(h, w.wo, h->y, h->ptmp, M, D, H * HD)) return r;
         add_rows_kernel<<<ew_blocks, 256, 0, s>>>(cur, h->ptmp, xb, (size_t)M * D / 8);
         rmsnorm_rows_kernel<<<M, 256, 0, s>>>(xb, w.ffn_norm, h->pxn, D, d.norm_eps);
@@ -872,7 +884,7 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
         T(cublas_ws, char, CUBLAS_WS_BYTES)
     }
     if (d.max_rows > 8) {
-        T(rg_partial, float, rg_partial_bytes(RG_GRID_MAX, 128) / sizeof(float)) T(rg_counters, int, RG_MAX_TILES)
+        T(rg_partial, float, rg_partial_bytes(RG_GRID_MAX, 128) / sizeof(float))
     }
     T(mega_buf, char, MEGA_BUF_BYTES) T(mega_sync, unsigned, 64) T(mega_prof, unsigned long long, 16)
     // flag-in-data activations of the persistent frame kernel (batch 1): one u32 per element
@@ -917,7 +929,6 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
     h->gc.n_sm = h->n_sm;
     CK(set_gemv_attrs());
     CK(set_gemv_tma_attrs());
-    CK(cudaFuncSetAttribute((const void*)ak.rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ak.rows_smem));
     CK(cudaMemset(h->counters, 0, (size_t)std::max(d.max_rows, 8) * d.n_kv_head * sizeof(int32_t)));
     CK(cudaMemset(h->mega_sync, 0, 64 * sizeof(unsigned)));
     {
@@ -931,10 +942,7 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
         CK(cudaMemset(h->ll_ml, 0, (size_t)d.n_kv_head * h->max_splits * gq_ * 2 * sizeof(uint2)));
     }
     CK(cudaMemset(h->mega_prof, 0, 16 * sizeof(unsigned long long)));
-    if (h->rg_counters) {
-        CK(cudaMemset(h->rg_counters, 0, RG_MAX_TILES * sizeof(int)));
-        h->rg_ok = h->n_sm <= RG_GRID_MAX && rg_get_encode() != nullptr && rg_set_attrs() == cudaSuccess;
-    }
+    if (h->rg_partial) h->rg_ok = h->n_sm <= RG_SM_MAX && rg_get_encode() != nullptr && rg_set_attrs() == cudaSuccess;
     if (const char* e = getenv("FSB_BATCH_GEMM")) h->batch_gemm = atoi(e);
     if (mega_shape_ok(d)) {
         mega_fn mf = pick_mega(d.head_dim, d.n_head / d.n_kv_head);
@@ -1263,29 +1271,34 @@ int fsb_gemv(const void* W, const void* W2, const void* x, const void* norm_w, c
     return e == cudaSuccess ? 0 : 3;
 }
 
-size_t fsb_rows_gemm_scratch_bytes(void) {  // counters | partial tiles | 8 clock stamps per CTA (written when FSB_RG_TRACE is set)
-    return RG_MAX_TILES * sizeof(int) + rg_partial_bytes(RG_GRID_MAX, 128) + RG_GRID_MAX * 8 * sizeof(unsigned long long);
+size_t fsb_rows_gemm_scratch_bytes(void) {  // partial tiles | 8 clock stamps per CTA (written when FSB_RG_TRACE is set) | SwiGLU pre-activations
+    return rg_partial_bytes(RG_GRID_MAX, 128) + RG_GRID_MAX * 8 * sizeof(unsigned long long) + (size_t)128 * 2 * 32768 * sizeof(bf16);
 }
 
 int fsb_rows_gemm(const void* W, const void* W2, const void* x, const void* res, void* out, int32_t M, int32_t N, int32_t K,
                   int32_t epi, void* scratch, size_t scratch_bytes, void* stream) {
     if (!W || !x || !out || !scratch || M < 1 || M > 128 || N < 1 || K < RG_BK || K % RG_BK) return 1;
-    if ((N + RG_BM - 1) / RG_BM > RG_MAX_TILES || scratch_bytes < fsb_rows_gemm_scratch_bytes()) return 1;
-    if (epi < RG_EPI_STORE || epi > RG_EPI_SWIGLU || (epi == RG_EPI_SWIGLU && !W2) || (epi == RG_EPI_RESIDUAL && !res)) return 1;
+    const bool sw = epi == RG_EPI_SWIGLU;
+    const int NV = sw ? 2 * N : N;
+    if ((NV + RG_BM - 1) / RG_BM > RG_MAX_TILES || scratch_bytes < fsb_rows_gemm_scratch_bytes()) return 1;
+    if ((long long)((NV + RG_BM - 1) / RG_BM) * (K / RG_BK) * RG_GRID_MAX >= (1LL << 31)) return 1;
+    if (epi < RG_EPI_STORE || epi > RG_EPI_SWIGLU || (sw && (!W2 || N % RG_BM || N > 32768)) || (epi == RG_EPI_RESIDUAL && !res)) return 1;
     int dev = 0, n_sm = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 2;
-    if (n_sm > RG_GRID_MAX || rg_set_attrs() != cudaSuccess) return 2;
+    if (n_sm > RG_SM_MAX || rg_set_attrs() != cudaSuccess) return 2;
     CUtensorMap mW, mW2, mX;
     if (!rg_make_map(&mW, W, (uint64_t)N, (uint64_t)K, RG_BM)) return 3;
     if (!rg_make_map(&mW2, W2 ? W2 : W, (uint64_t)N, (uint64_t)K, RG_BM)) return 3;
     if (!rg_make_map(&mX, x, (uint64_t)M, (uint64_t)K, (uint32_t)rg_bn_for(M))) return 3;
-    int* counters = (int*)scratch;
-    float* partial = (float*)((char*)scratch + RG_MAX_TILES * sizeof(int));
+    float* partial = (float*)scratch;
     static const bool want_trace = getenv("FSB_RG_TRACE") != nullptr;
-    static const int defer = getenv("FSB_RG_DEFER") ? atoi(getenv("FSB_RG_DEFER")) : 0;  // profiling: skip the in-kernel finish
-    unsigned long long* trace = want_trace ? (unsigned long long*)((char*)partial + rg_partial_bytes(RG_GRID_MAX, 128)) : nullptr;
-    cudaError_t e = rg_launch((cudaStream_t)stream, false, n_sm, mW, mW2, mX, M, N, K, epi, (const bf16*)res, (bf16*)out, partial, counters,
-                              defer, trace);
+    unsigned long long* trace = (unsigned long long*)((char*)scratch + rg_partial_bytes(RG_GRID_MAX, 128));
+    bf16* pre = (bf16*)(trace + RG_GRID_MAX * 8);
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e = rg_launch(s, false, n_sm, mW, mW2, mX, M, NV, (N + RG_BM - 1) / RG_BM, K, sw ? RG_EPI_STORE : epi, (const bf16*)res,
+                              sw ? pre : (bf16*)out, partial, 0, want_trace ? trace : nullptr);
+    if (e != cudaSuccess) return 4;
+    e = rg_finish_tiles(s, false, n_sm, M, NV, K, epi, partial, sw ? pre : (const bf16*)out, (const bf16*)res, (bf16*)out);
     return e == cudaSuccess ? 0 : 4;
 }
 

@@ -3,24 +3,28 @@
 // exactly as the reference state dict stores a Linear weight (llama.py:856-860, 981-983).
 //
 // The op is HBM-bound (every weight byte is used for M <= 128 rows, ~2*M FLOP per byte against a ridge of ~220), so the
-// design goal is the same as for the batch-1 GEMV: keep ~190 KB of weight bytes in flight per SM and never re-read a
-// byte.  Tensor cores are used because CUDA-core FMAs cannot keep up with the stream at M = 64.
+// design goal is the same as for the batch-1 GEMV: keep the weight stream running and never re-read a byte.  Tensor cores
+// are used because CUDA-core FMAs cannot keep up with the stream at M = 64.
 //
 //  * Orientation: the WEIGHT tile is the MMA's A operand (128 weight rows = the 128 TMEM lanes), the activation rows are
 //    the B operand (N = BN = 32/64/128 batch rows), both K-major, so neither needs a transpose:
 //    D[n_local][m] (fp32, TMEM, 128 lanes x BN columns) += W[n0 + n_local][k] * X[m][k].
 //  * tcgen05.mma.cta_group::1.kind::f16 (bf16 x bf16 -> fp32), issued by one thread; operands in shared memory in the
 //    canonical 128-byte-swizzled K-major layout, which is what a TMA tensor-map box {64 k, rows} with SWIZZLE_128B writes.
-//  * Pipeline: TMA producer warp -> ring of NST stages {W tile 16 KB (x2 for gate/up), X tile BN x 128 B} -> MMA warp ->
-//    two TMEM accumulator buffers -> 4 epilogue warps (tcgen05.ld).  Weight tiles are requested BEFORE
-//    griddepcontrol.wait (they do not depend on the previous kernel), activations after it.
+//  * Pipeline: TMA producer warp -> ring of 3 stages {W tile 16 KB, X tile BN x 128 B} -> MMA warp -> two TMEM
+//    accumulator buffers -> 4 epilogue warps (tcgen05.ld).  Weight tiles are requested BEFORE griddepcontrol.wait (they
+//    do not depend on the previous kernel), activations after it.  A CTA needs 73 KB of shared memory and 128 TMEM
+//    columns at 64 rows, so three fit one SM: a launch uses two CTAs per SM and the third slot lets the NEXT kernel of
+//    the PDL chain start its weight stream while this one drains (a short op is otherwise dominated by the ~5 us it takes
+//    the first ring fill of all SMs to come back from HBM).
 //  * Work split = stream-K: the (weight tile, k block) units are cut into one contiguous range per CTA, so every SM
 //    streams the same number of bytes whatever N is (2560 rows = 20 tiles would otherwise use 20 of 148 SMs).  A tile
-//    whose k range is shared by several CTAs is finished by the LAST CTA to arrive: every contributor writes its fp32
-//    partial tile to a per-CTA slab, and the finisher adds the partials in CTA order (its own from TMEM), so the result
-//    does not depend on arrival order.  No second launch, no atomics on data.
-//  * Epilogues (one rounding per Linear like the reference, llama.py:838-843, 985-986): store bf16; bf16(res + bf16(acc));
-//    SwiGLU over two accumulators bf16(bf16(silu(bf16 a)) * bf16 b).
+//    whose k range belongs to one CTA is finished in place (bf16, optional residual); a tile shared by several CTAs is
+//    left as fp32 partial tiles in per-CTA slabs and finished by the small kernel that follows (rows_finish_tiles_kernel,
+//    or rows_finish_norm_kernel fused with the RMSNorm after wo / w2), which adds the pieces in CTA order: deterministic,
+//    no atomics, nothing serial on the GEMM's critical path.
+//  * gate/up (w1, w3) run as ONE launch over the 2F rows of both matrices; the finish kernel applies SwiGLU
+//    bf16(bf16(silu(bf16 a)) * bf16 b) (llama.py:986).  One rounding per Linear like the reference (llama.py:838-843).
 #pragma once
 #include <cuda.h>
 
@@ -31,35 +35,29 @@
 #define RG_BK 64
 #define RG_THREADS 192
 #define RG_EPI_THREADS 128
-#define RG_MAX_STAGES 10
-#define RG_MAX_TILES 2048
-#define RG_SMEM_BUDGET (222 * 1024)
+#define RG_STAGES_MAX 6      // ring depth: 6 x 24 KB when a launch has one CTA per SM, 3 x 24 KB when it has two (either way a CTA
+#define RG_STAGES_MIN 3      //   of the NEXT kernel fits beside them and starts its weight stream early)
+#define RG_CTAS_PER_SM 2     // most CTAs of one launch per SM
+#define RG_MAX_TILES 4096
 
 enum { RG_EPI_STORE = 0, RG_EPI_RESIDUAL = 1, RG_EPI_SWIGLU = 2 };
 
 struct RowsGemmArgs {
-    bf16* out;         // [M][N]
-    const bf16* res;   // [M][N] (RG_EPI_RESIDUAL), may alias out
-    float* partial;    // [grid][2][NW][BN][128] fp32 partial tiles of the stream-K split
-    int* counters;     // [n_tiles] arrivals per tile; zero between launches
+    bf16* out;         // [M][N] bf16 outputs of tiles whose whole k range belongs to one CTA (N = rows of W + rows of W2)
+    const bf16* res;   // [M][N] residual (RG_EPI_RESIDUAL), may alias out
+    float* partial;    // [grid][2][BN][128] fp32 partial tiles of the stream-K split
     int M, N, K, epi;
-    int n_tiles, kb;   // tiles of 128 weight rows, k blocks of 64
-    int nst;           // ring depth
+    int n_tiles, kb;   // tiles of 128 weight rows over W then W2, k blocks of 64
+    int tiles_w;       // tiles that belong to W (the rest index W2)
+    int nst;           // ring depth of this launch
+    int all_partial;   // 1: every tile segment is left as an fp32 partial (rows_finish_norm_kernel finishes the op)
     unsigned long long* trace;  // profiling aid: 8 clock64 stamps per CTA (nullptr = off)
-    int defer;         // 1: every tile segment only writes its fp32 partial; rows_finish_norm_kernel sums them (few-tile ops)
 };
 
-__host__ __device__ constexpr uint32_t rg_stage_bytes(int bn, int nw) { return (uint32_t)(nw * RG_BM * RG_BK * 2 + bn * RG_BK * 2); }
-__host__ __device__ constexpr int rg_tmem_cols(int bn, int nw) {
-    const int c = 2 * nw * bn;
-    return c <= 32 ? 32 : c <= 64 ? 64 : c <= 128 ? 128 : c <= 256 ? 256 : 512;
-}
-inline int rg_stages(int bn, int nw) {
-    int n = (int)((RG_SMEM_BUDGET - 1024) / rg_stage_bytes(bn, nw));
-    return n > RG_MAX_STAGES ? RG_MAX_STAGES : n;
-}
-inline size_t rg_smem_bytes(int bn, int nw) { return (size_t)rg_stages(bn, nw) * rg_stage_bytes(bn, nw) + 1024; }
-inline size_t rg_partial_bytes(int grid, int bn) { return (size_t)grid * 2 * 2 * bn * RG_BM * sizeof(float); }
+__host__ __device__ constexpr uint32_t rg_stage_bytes(int bn) { return (uint32_t)(RG_BM * RG_BK * 2 + bn * RG_BK * 2); }
+__host__ __device__ constexpr int rg_tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 256; }
+inline size_t rg_smem_bytes(int bn, int nst) { return (size_t)nst * rg_stage_bytes(bn) + 1024; }
+inline size_t rg_partial_bytes(int grid, int bn) { return (size_t)grid * 2 * bn * RG_BM * sizeof(float); }
 
 // ----------------------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ void rg_tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, uint64_t policy) {
@@ -104,40 +102,62 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, float (&v)[16]) {
 }
 __device__ __forceinline__ void rg_epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(RG_EPI_THREADS) : "memory"); }
 
-// CTA that owns unit u when U units are cut into G contiguous ranges [U*c/G, U*(c+1)/G)
-__device__ __forceinline__ int rg_owner(long long u, long long U, int G) {
-    int c = (int)((u * G) / U);
-    while (c + 1 < G && (U * (c + 1)) / G <= u) ++c;
-    while (c > 0 && (U * c) / G > u) --c;
-    return c;
+// ----------------------------------------------------------------------------- stream-K bookkeeping
+// U = n_tiles * kb units are cut into G contiguous ranges [U*c/G, U*(c+1)/G), one per CTA.
+// (32-bit arithmetic: U * G < 2^31 is checked on the host; 64-bit divisions cost ~100 instructions each on the device)
+struct RgSplit {
+    unsigned U;
+    int G, kb;
+    __host__ __device__ int start(int c) const { return (int)((U * (unsigned)c) / (unsigned)G); }
+    __host__ __device__ int owner(int u) const {
+        int c = (int)(((unsigned)u * (unsigned)G) / U);
+        while (c + 1 < G && start(c + 1) <= u) ++c;
+        while (c > 0 && start(c) > u) --c;
+        return c;
+    }
+    // contributors of tile t: CTAs cf..cl; the first one holds its piece in slot sf, every later one in slot 0 (a CTA's
+    // slot 0 is the tile its range starts in, slot 1 the tile it ends in)
+    __host__ __device__ void tile(int t, int& cf, int& cl, int& sf) const {
+        cf = owner(t * kb);
+        cl = owner(t * kb + kb - 1);
+        sf = (start(cf) / kb == t) ? 0 : 1;
+    }
+};
+// CTAs of a launch.  Few tiles (<= 2 per SM): G = n_tiles * s, which makes the ranges tile-aligned (start(c) = kb*c/s), so
+// every CTA holds exactly one partial tile and a tile has exactly s contributors - s = 3 (wqkv, 144 CTAs), 7 (wo / w2, 140),
+// 2 (gate/up, 304).  Many tiles (LM head): plain stream-K over 2 CTAs per SM, ~300 split tiles out of 1217.
+inline int rg_grid(int n_tiles, int kb, int n_sm) {
+    if (n_tiles > RG_CTAS_PER_SM * n_sm) return RG_CTAS_PER_SM * n_sm;
+    int s = n_tiles <= n_sm ? n_sm / n_tiles : (2 * n_tiles <= 3 * n_sm ? 2 : 1);
+    if (s > kb) s = kb;
+    return n_tiles * s;
 }
+inline int rg_stages_for(int grid, int n_sm) { return grid <= n_sm ? RG_STAGES_MAX : RG_STAGES_MIN; }
 
 #define RG_STAMP(i) do { if (a.trace) a.trace[(size_t)blockIdx.x * 8 + (i)] = clock64(); } while (0)
 #define RG_POLICY_EVICT_FIRST 0x12F0000000000000ull
 #define RG_POLICY_EVICT_LAST 0x14F0000000000000ull
 
-template <int BN, int NW>
-__global__ void __launch_bounds__(RG_THREADS, 1)
+template <int BN>
+__global__ void __launch_bounds__(RG_THREADS, 3)
 rows_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmW2,
                  const __grid_constant__ CUtensorMap tmX, RowsGemmArgs a) {
     constexpr uint32_t W_BYTES = RG_BM * RG_BK * 2;
-    constexpr uint32_t STAGE = rg_stage_bytes(BN, NW);
-    constexpr int TCOLS = rg_tmem_cols(BN, NW);
+    constexpr uint32_t STAGE = rg_stage_bytes(BN);
+    constexpr int TCOLS = rg_tmem_cols(BN);
     extern __shared__ uint8_t rg_smem_raw[];
-    __shared__ uint64_t full_bar[RG_MAX_STAGES], empty_bar[RG_MAX_STAGES], tfull_bar[2], tempty_bar[2];
+    __shared__ uint64_t full_bar[RG_STAGES_MAX], empty_bar[RG_STAGES_MAX], tfull_bar[2], tempty_bar[2];
     __shared__ uint32_t tmem_base_s;
-    __shared__ int s_last, s_cf, s_cl;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) RG_STAMP(0);
     const uint32_t sbase = (smem_u32(rg_smem_raw) + 1023u) & ~1023u;
-    const int nst = a.nst;
-    const long long U = (long long)a.n_tiles * a.kb;
+    const unsigned U = (unsigned)(a.n_tiles * a.kb);
     const int G = gridDim.x, c = blockIdx.x;
-    const int u0 = (int)((U * c) / G), u1 = (int)((U * (c + 1)) / G);
+    const int u0 = (int)((U * (unsigned)c) / (unsigned)G), u1 = (int)((U * (unsigned)(c + 1)) / (unsigned)G);
 
     if (tid == 0) {
-        for (int s = 0; s < nst; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < a.nst; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -156,34 +176,32 @@ rows_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
         // ===== TMA producer
         if (lane == 0) {
             rg_prefetch_map(&tmW);
-            if (NW == 2) rg_prefetch_map(&tmW2);
+            rg_prefetch_map(&tmW2);
             rg_prefetch_map(&tmX);
             const int n_units = u1 - u0;
-            const int npre = n_units < nst ? n_units : nst;
+            const int npre = n_units < a.nst ? n_units : a.nst;
             // weights of the first ring fill do not depend on the previous kernel: request them before the dependency wait
             for (int i = 0; i < npre; ++i) {
                 const int u = u0 + i, t = u / a.kb, kbi = u - t * a.kb;
-                const uint32_t st = sbase + (uint32_t)i * STAGE, bar = smem_u32(&full_bar[i]);
                 mbar_expect_tx(&full_bar[i], STAGE);
-                rg_tma_load_2d(st, &tmW, bar, kbi * RG_BK, t * RG_BM, RG_POLICY_EVICT_FIRST);
-                if (NW == 2) rg_tma_load_2d(st + W_BYTES, &tmW2, bar, kbi * RG_BK, t * RG_BM, RG_POLICY_EVICT_FIRST);
+                if (t < a.tiles_w) rg_tma_load_2d(sbase + (uint32_t)i * STAGE, &tmW, smem_u32(&full_bar[i]), kbi * RG_BK, t * RG_BM, RG_POLICY_EVICT_FIRST);
+                else rg_tma_load_2d(sbase + (uint32_t)i * STAGE, &tmW2, smem_u32(&full_bar[i]), kbi * RG_BK, (t - a.tiles_w) * RG_BM, RG_POLICY_EVICT_FIRST);
             }
             pdl_wait();
             for (int i = 0; i < npre; ++i) {
                 const int u = u0 + i, t = u / a.kb, kbi = u - t * a.kb;
-                rg_tma_load_2d(sbase + (uint32_t)i * STAGE + NW * W_BYTES, &tmX, smem_u32(&full_bar[i]), kbi * RG_BK, 0,
-                               RG_POLICY_EVICT_LAST);
+                rg_tma_load_2d(sbase + (uint32_t)i * STAGE + W_BYTES, &tmX, smem_u32(&full_bar[i]), kbi * RG_BK, 0, RG_POLICY_EVICT_LAST);
             }
             for (int i = npre; i < n_units; ++i) {
                 const int u = u0 + i, t = u / a.kb, kbi = u - t * a.kb;
-                const int s = i % nst;
-                const uint32_t use = (uint32_t)(i / nst);
+                const int s = i % a.nst;
+                const uint32_t use = (uint32_t)(i / a.nst);
                 mbar_wait(&empty_bar[s], (use & 1u) ^ 1u);
                 const uint32_t st = sbase + (uint32_t)s * STAGE, bar = smem_u32(&full_bar[s]);
                 mbar_expect_tx(&full_bar[s], STAGE);
-                rg_tma_load_2d(st, &tmW, bar, kbi * RG_BK, t * RG_BM, RG_POLICY_EVICT_FIRST);
-                if (NW == 2) rg_tma_load_2d(st + W_BYTES, &tmW2, bar, kbi * RG_BK, t * RG_BM, RG_POLICY_EVICT_FIRST);
-                rg_tma_load_2d(st + NW * W_BYTES, &tmX, bar, kbi * RG_BK, 0, RG_POLICY_EVICT_LAST);
+                if (t < a.tiles_w) rg_tma_load_2d(st, &tmW, bar, kbi * RG_BK, t * RG_BM, RG_POLICY_EVICT_FIRST);
+                else rg_tma_load_2d(st, &tmW2, bar, kbi * RG_BK, (t - a.tiles_w) * RG_BM, RG_POLICY_EVICT_FIRST);
+                rg_tma_load_2d(st + W_BYTES, &tmX, bar, kbi * RG_BK, 0, RG_POLICY_EVICT_LAST);
             }
         }
     } else if (warp == 1) {
@@ -198,21 +216,17 @@ rows_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
             mbar_wait(&tempty_bar[buf], (use & 1u) ^ 1u);  // the epilogue has drained this accumulator buffer
             tc_fence_after();
             for (int i = 0; i < nk; ++i) {
-                const int idx = (u - u0) + i, s = idx % nst;
-                mbar_wait(&full_bar[s], (uint32_t)(idx / nst) & 1u);
+                const int idx = (u - u0) + i, s = idx % a.nst;
+                mbar_wait(&full_bar[s], (uint32_t)(idx / a.nst) & 1u);
                 tc_fence_after();
-                if (lane == 0 && idx == 0) RG_STAMP(2);
                 if (lane == 0) {
+                    if (idx == 0) RG_STAMP(2);
                     const uint32_t st = sbase + (uint32_t)s * STAGE;
-                    const uint64_t bdesc = tc_smem_desc(st + NW * W_BYTES);
+                    const uint64_t adesc = tc_smem_desc(st), bdesc = tc_smem_desc(st + W_BYTES);
+                    const uint32_t d = tmem + (uint32_t)(buf * BN);
 #pragma unroll
-                    for (int w = 0; w < NW; ++w) {
-                        const uint64_t adesc = tc_smem_desc(st + w * W_BYTES);
-                        const uint32_t d = tmem + (uint32_t)((buf * NW + w) * BN);
-#pragma unroll
-                        for (int k = 0; k < RG_BK / 16; ++k)  // K = 16 per instruction: +32 B inside the swizzle atom
-                            tc_mma_bf16(d, adesc + 2 * k, bdesc + 2 * k, IDESC, (i > 0 || k > 0) ? 1u : 0u);
-                    }
+                    for (int k = 0; k < RG_BK / 16; ++k)  // K = 16 per instruction: +32 B inside the swizzle atom
+                        tc_mma_bf16(d, adesc + 2 * k, bdesc + 2 * k, IDESC, (i > 0 || k > 0) ? 1u : 0u);
                     tc_commit(&empty_bar[s]);  // arrives when the MMAs above have read the stage
                 }
                 __syncwarp();
@@ -234,107 +248,30 @@ rows_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
             const int t = u / a.kb, k0 = u - t * a.kb;
             const int nk = min(a.kb - k0, u1 - u);
             const int buf = iseg & 1;
-            const bool whole = (nk == a.kb);
+            const bool whole = (nk == a.kb) && !a.all_partial;
             mbar_wait(&tfull_bar[buf], (uint32_t)(iseg >> 1) & 1u);
             tc_fence_after();
             if (et == 0) { if (iseg == 0) RG_STAMP(4); if (u + nk >= u1) RG_STAMP(5); }
-            const uint32_t tacc = tmem + tlane + (uint32_t)(buf * NW * BN);
-            bool finish = whole && !a.defer;
-            int c_first = c, c_last = c;
-            if (!finish) {
-                const int slot = (t == u0 / a.kb) ? 0 : 1;
-                float* P = a.partial + (size_t)(c * 2 + slot) * NW * BN * RG_BM;
+            const uint32_t tacc = tmem + tlane + (uint32_t)(buf * BN);
+            const int n = t * RG_BM + r;
+            float* P = a.partial + ((size_t)(c * 2 + ((t == u0 / a.kb) ? 0 : 1)) * BN) * RG_BM + r;
 #pragma unroll 1
-                for (int w = 0; w < NW; ++w)
-#pragma unroll 1
-                    for (int ch = 0; ch < BN / 16; ++ch) {
-                        if (ch * 16 >= a.M) break;
-                        float v[16];
-                        tc_ld16(tacc + (uint32_t)(w * BN + ch * 16), v);
+            for (int ch = 0; ch < BN / 16; ++ch) {
+                if (ch * 16 >= a.M) break;
+                float v[16];
+                tc_ld16(tacc + (uint32_t)(ch * 16), v);
+                if (!whole) {  // a piece of the tile's k range: fp32, finished by the kernel that follows
 #pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (ch * 16 + j < a.M) P[(size_t)(w * BN + ch * 16 + j) * RG_BM + r] = v[j];
-                    }
-            }
-            if (!finish && !a.defer) {
-                __threadfence();
-                rg_epi_bar();
-                if (et == 0) {
-                    const int cf = rg_owner((long long)t * a.kb, U, G), cl = rg_owner((long long)t * a.kb + a.kb - 1, U, G);
-                    const int prev = atomicAdd(&a.counters[t], 1);
-                    const int last = (prev == cl - cf);
-                    if (last) a.counters[t] = 0;  // re-arm for the next launch
-                    s_last = last;
-                    s_cf = cf;
-                    s_cl = cl;
-                }
-                rg_epi_bar();
-                finish = s_last != 0;
-                if (finish) {
-                    __threadfence();
-                    c_first = s_cf;
-                    c_last = s_cl;
-                }
-            }
-            if (finish) {
-                const int n = t * RG_BM + r;
-                const bool nv = n < a.N;
-                constexpr int GRP = (NW == 2) ? 2 : 4;  // contributors whose partial tiles are in flight together
-#pragma unroll 1
-                for (int ch = 0; ch < BN / 16; ++ch) {
-                    if (ch * 16 >= a.M) break;
-                    float acc[NW][16];
+                    for (int j = 0; j < 16; ++j)
+                        if (ch * 16 + j < a.M) P[(size_t)(ch * 16 + j) * RG_BM] = v[j];
+                } else if (n < a.N) {
 #pragma unroll
-                    for (int w = 0; w < NW; ++w) tc_ld16(tacc + (uint32_t)(w * BN + ch * 16), acc[w]);
-                    if (!whole) {
-                        float own[NW][16];
-#pragma unroll
-                        for (int w = 0; w < NW; ++w)
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) { own[w][j] = acc[w][j]; acc[w][j] = 0.f; }
-                        for (int cc0 = c_first; cc0 <= c_last; cc0 += GRP) {
-                            float pv[GRP][NW][16];
-#pragma unroll
-                            for (int g = 0; g < GRP; ++g) {
-                                const int cc = cc0 + g;
-                                if (cc <= c_last && cc != c) {
-                                    const int slot = ((int)((U * cc) / G) / a.kb == t) ? 0 : 1;
-                                    const float* P = a.partial + (size_t)(cc * 2 + slot) * NW * BN * RG_BM;
-#pragma unroll
-                                    for (int w = 0; w < NW; ++w)
-#pragma unroll
-                                        for (int j = 0; j < 16; ++j)
-                                            pv[g][w][j] = (ch * 16 + j < a.M) ? __ldcg(&P[(size_t)(w * BN + ch * 16 + j) * RG_BM + r]) : 0.f;
-                                }
-                            }
-#pragma unroll
-                            for (int g = 0; g < GRP; ++g) {  // fixed CTA order: the sum does not depend on who finishes
-                                const int cc = cc0 + g;
-                                if (cc > c_last) break;
-#pragma unroll
-                                for (int w = 0; w < NW; ++w)
-#pragma unroll
-                                    for (int j = 0; j < 16; ++j) acc[w][j] += (cc == c) ? own[w][j] : pv[g][w][j];
-                            }
-                        }
-                    }
-                    if (nv) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int m = ch * 16 + j;
-                            if (m >= a.M) break;
-                            const size_t oi = (size_t)m * a.N + n;
-                            float o;
-                            if (NW == 2) {  // SwiGLU (llama.py:986): silu(w1 x) * w3 x, each op rounded to bf16
-                                const float g = rbf(acc[0][j]), up = rbf(acc[NW - 1][j]);
-                                o = rbf(__fdiv_rn(g, 1.f + expf(-g))) * up;
-                            } else if (a.epi == RG_EPI_RESIDUAL) {
-                                o = lda(&a.res[oi]) + rbf(acc[0][j]);
-                            } else {
-                                o = acc[0][j];
-                            }
-                            a.out[oi] = __float2bfloat16_rn(o);
-                        }
+                    for (int j = 0; j < 16; ++j) {
+                        const int m = ch * 16 + j;
+                        if (m >= a.M) break;
+                        const size_t oi = (size_t)m * a.N + n;
+                        const float o = (a.epi == RG_EPI_RESIDUAL) ? lda(&a.res[oi]) + rbf(v[j]) : v[j];
+                        a.out[oi] = __float2bfloat16_rn(o);
                     }
                 }
             }
@@ -347,20 +284,107 @@ rows_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
     }
     tc_fence_before();
     __syncthreads();
-    if (tid == 0) RG_STAMP(7);
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS) : "memory");
     }
 }
 
-// ----------------------------------------------------------------------------- deferred finish + RMSNorm
-// Row-parallel second half of a few-tile Linear (wo, w2: 20 weight tiles shared by ~8 CTAs each): sums the fp32 partial
-// tiles rows_gemm_kernel left behind (defer = 1) in CTA order, applies the residual (llama.py:841-842) and, since an
-// RMSNorm follows every such Linear on the path (ffn_norm, the next layer's attention_norm, the final norms), produces
-// the normalised rows for the next Linear in the same pass (llama.py:995-1000, double rounding).  One CTA per row: the
-// partial reads are spread over M SMs instead of landing on the 20 SMs that would finish the tiles in-kernel.
+// ----------------------------------------------------------------------------- finish of split tiles
+// rows_gemm_kernel leaves every tile whose k range is shared by several CTAs as fp32 partial tiles.  The finish is a
+// separate, embarrassingly parallel pass (a last-arriver fix-up inside the GEMM put 10-25 us of serial L2 round trips on
+// the critical path of a 15 us kernel): one CTA per (tile, 16 rows), one thread per weight row, the contributors' values
+// are added in CTA order (deterministic).  PDL-chained: it starts while the GEMM drains, and the next GEMM's CTAs start
+// their weight stream while it runs.
+//   mode RG_EPI_STORE / RG_EPI_RESIDUAL : out[m][n] = epi(bf16(sum))            for split tiles only
+//   mode RG_EPI_SWIGLU                  : ff[m][n] = bf16(bf16(silu(g)) * up), g / up = the w1 / w3 halves of the GEMM's
+//                                         N = 2F columns, each read from `pre` (whole tiles) or summed (split tiles)
+#define RFT_ROWS 4    // rows per CTA, unrolled: 4 x <= 16 partial loads in flight per thread, one L2 round trip per CTA
+struct RowsFinishTilesArgs {
+    const float* partial;
+    const bf16* pre;   // [M][N] bf16 outputs of whole tiles (SwiGLU mode input; aliases out in the other modes)
+    const bf16* res;
+    bf16* out;         // [M][N] (store / residual) or [M][N/2] (SwiGLU)
+    int M, N, bn, G, kb, n_tiles, mode;
+};
+__device__ __forceinline__ float rft_ld(const float* p) {  // volatile: the loads of one sum are issued back to back
+    float v;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+template <int SEG>  // contributors whose pieces are in flight together
+__device__ __forceinline__ float rft_sum(const float* partial, int bn, int cf, int cl, int sf, int m, int r) {
+    float v = 0.f;
+    for (int c0 = cf; c0 <= cl; c0 += SEG) {
+        float pv[SEG];
+#pragma unroll
+        for (int g = 0; g < SEG; ++g) {
+            const int cc = min(c0 + g, cl);  // past the end: re-read the last piece (dropped below) instead of branching
+            pv[g] = rft_ld(&partial[((size_t)(cc * 2 + ((cc == cf) ? sf : 0)) * bn + m) * RG_BM + r]);
+        }
+#pragma unroll
+        for (int g = 0; g < SEG; ++g) v += (c0 + g <= cl) ? pv[g] : 0.f;
+    }
+    return v;
+}
+// grid.x: SwiGLU mode = the F/128 output tiles; otherwise the G-1 boundaries between CTA ranges (only a boundary that
+// falls inside a tile splits it, and the first boundary inside a tile owns its finish), so a 1217-tile LM head launches
+// ~300 small CTAs per row group, not one per tile.
+__global__ void __launch_bounds__(RG_BM) rows_finish_tiles_kernel(RowsFinishTilesArgs a) {
+    __shared__ int s_seg[2][3];
+    pdl_launch_dependents();
+    const int r = threadIdx.x;
+    const int m0 = blockIdx.y * RFT_ROWS;
+    const RgSplit sp{(unsigned)(a.n_tiles * a.kb), a.G, a.kb};
+    const bool swiglu = a.mode == RG_EPI_SWIGLU;
+    const int half_tiles = a.n_tiles / 2;
+    int t = blockIdx.x;
+    if (!swiglu) {
+        const int u = sp.start(blockIdx.x + 1);
+        if (u % a.kb == 0) return;  // the boundary coincides with a tile boundary
+        t = u / a.kb;
+    }
+    if (r < (swiglu ? 2 : 1)) sp.tile(t + r * half_tiles, s_seg[r][0], s_seg[r][1], s_seg[r][2]);
+    __syncthreads();
+    if (!swiglu && s_seg[0][0] != (int)blockIdx.x) return;  // an earlier boundary inside the same tile finishes it
+    pdl_wait();
+    const int n = t * RG_BM + r;
+    if (!swiglu) {
+        if (n >= a.N) return;
+        float v[RFT_ROWS];
+#pragma unroll
+        for (int i = 0; i < RFT_ROWS; ++i)
+            v[i] = (m0 + i < a.M) ? rft_sum<4>(a.partial, a.bn, s_seg[0][0], s_seg[0][1], s_seg[0][2], m0 + i, r) : 0.f;
+#pragma unroll
+        for (int i = 0; i < RFT_ROWS; ++i) {
+            if (m0 + i >= a.M) break;
+            const size_t oi = (size_t)(m0 + i) * a.N + n;
+            a.out[oi] = __float2bfloat16_rn(a.mode == RG_EPI_RESIDUAL ? lda(&a.res[oi]) + rbf(v[i]) : v[i]);
+        }
+        return;
+    }
+    const int F = a.N / 2;
+    const bool split_g = s_seg[0][0] != s_seg[0][1], split_u = s_seg[1][0] != s_seg[1][1];
+    float g[RFT_ROWS], up[RFT_ROWS];
+#pragma unroll
+    for (int i = 0; i < RFT_ROWS; ++i) {
+        const int m = min(m0 + i, a.M - 1);
+        g[i] = split_g ? rbf(rft_sum<4>(a.partial, a.bn, s_seg[0][0], s_seg[0][1], s_seg[0][2], m, r)) : lda(&a.pre[(size_t)m * a.N + n]);
+        up[i] = split_u ? rbf(rft_sum<4>(a.partial, a.bn, s_seg[1][0], s_seg[1][1], s_seg[1][2], m, r)) : lda(&a.pre[(size_t)m * a.N + F + n]);
+    }
+#pragma unroll
+    for (int i = 0; i < RFT_ROWS; ++i)
+        if (m0 + i < a.M)
+            a.out[(size_t)(m0 + i) * F + n] = __float2bfloat16_rn(rbf(__fdiv_rn(g[i], 1.f + expf(-g[i]))) * up[i]);  // llama.py:986
+}
+
+// ----------------------------------------------------------------------------- row-parallel finish + RMSNorm
+// For the Linears with few weight tiles (wo, w2: N = dim = 20 tiles, every tile shared by ~15 CTAs) the GEMM leaves ALL
+// tiles as partials and this kernel finishes whole rows: sum in CTA order, residual (llama.py:841-842) and, since an
+// RMSNorm follows every such Linear on the path (ffn_norm, the next layer's attention_norm, the final norms), the
+// normalised rows for the next Linear in the same pass (llama.py:995-1000, double rounding).  One CTA per row.
 #define RF_THREADS 512
+#define RF_EPT 5
 #define RF_MAX_TILES 128
 struct RowsFinishArgs {
     const float* partial;  // partial tiles of the pending Linear, or nullptr: x_in already holds finished rows
@@ -375,44 +399,38 @@ struct RowsFinishArgs {
 __global__ void __launch_bounds__(RF_THREADS) rows_finish_norm_kernel(RowsFinishArgs a) {
     __shared__ float red[32];
     __shared__ int s_cf[RF_MAX_TILES], s_cl[RF_MAX_TILES], s_sf[RF_MAX_TILES];
-    const int m = blockIdx.x, tid = threadIdx.x;
-    const long long U = (long long)a.n_tiles * a.kb;
-    if (a.partial != nullptr)
-        for (int t = tid; t < a.n_tiles; t += RF_THREADS) {
-            const int cf = rg_owner((long long)t * a.kb, U, a.G);
-            s_cf[t] = cf;
-            s_cl[t] = rg_owner((long long)t * a.kb + a.kb - 1, U, a.G);
-            s_sf[t] = ((int)((U * cf) / a.G) / a.kb == t) ? 0 : 1;
-        }
-    pdl_wait();
     pdl_launch_dependents();
+    const int m = blockIdx.x, tid = threadIdx.x;
+    if (a.partial != nullptr) {
+        const RgSplit sp{(unsigned)(a.n_tiles * a.kb), a.G, a.kb};
+        for (int t = tid; t < a.n_tiles; t += RF_THREADS) sp.tile(t, s_cf[t], s_cl[t], s_sf[t]);
+    }
+    pdl_wait();
     __syncthreads();
     float ss = 0.f;
     const size_t row = (size_t)m * a.N;
     if (a.partial != nullptr) {
-        // all of a thread's partial values are requested before the first one is used (8 contributors per pass): the loop
-        // is a chain of L2 round trips otherwise
-        constexpr int SEG = 8;
-        for (int n = tid; n < a.N; n += RF_THREADS) {
-            const int t = n >> 7, r = n & 127;
-            const int cf = s_cf[t], cl = s_cl[t], slot_f = s_sf[t];
-            const float resv = lda(&a.res[row + n]);
-            float v = 0.f;
-            for (int c0 = cf; c0 <= cl; c0 += SEG) {
-                float pv[SEG];
+        // up to RF_EPT elements per thread, all of their partial values requested before the first sum is used
+        for (int nb = 0; nb < a.N; nb += RF_THREADS * RF_EPT) {
+            float v[RF_EPT], resv[RF_EPT];
 #pragma unroll
-                for (int g = 0; g < SEG; ++g) {
-                    const int cc = c0 + g;
-                    const int slot = (cc == cf) ? slot_f : 0;  // a CTA that starts inside this tile holds it in slot 0
-                    pv[g] = (cc <= cl) ? __ldcg(&a.partial[((size_t)(cc * 2 + slot) * a.bn + m) * RG_BM + r]) : 0.f;
+            for (int e = 0; e < RF_EPT; ++e) {
+                const int n = nb + e * RF_THREADS + tid;
+                v[e] = 0.f; resv[e] = 0.f;
+                if (n < a.N) {
+                    resv[e] = lda(&a.res[row + n]);
+                    v[e] = rft_sum<8>(a.partial, a.bn, s_cf[n >> 7], s_cl[n >> 7], s_sf[n >> 7], m, n & 127);
                 }
-#pragma unroll
-                for (int g = 0; g < SEG; ++g)
-                    if (c0 + g <= cl) v += pv[g];  // CTA order
             }
-            const float o = rbf(resv + rbf(v));
-            a.x_out[row + n] = __float2bfloat16_rn(o);
-            ss += o * o;
+#pragma unroll
+            for (int e = 0; e < RF_EPT; ++e) {
+                const int n = nb + e * RF_THREADS + tid;
+                if (n < a.N) {
+                    const float o = rbf(resv[e] + rbf(v[e]));
+                    a.x_out[row + n] = __float2bfloat16_rn(o);
+                    ss += o * o;
+                }
+            }
         }
     } else {
         for (int n = tid; n < a.N; n += RF_THREADS) {
@@ -459,42 +477,60 @@ inline bool rg_make_map(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t
 }
 
 typedef void (*rows_gemm_fn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, RowsGemmArgs);
-inline rows_gemm_fn rg_pick(int bn, int nw) {
-    if (nw == 2) return bn == 32 ? rows_gemm_kernel<32, 2> : bn == 64 ? rows_gemm_kernel<64, 2> : rows_gemm_kernel<128, 2>;
-    return bn == 32 ? rows_gemm_kernel<32, 1> : bn == 64 ? rows_gemm_kernel<64, 1> : rows_gemm_kernel<128, 1>;
-}
+inline rows_gemm_fn rg_pick(int bn) { return bn == 32 ? rows_gemm_kernel<32> : bn == 64 ? rows_gemm_kernel<64> : rows_gemm_kernel<128>; }
 inline int rg_bn_for(int M) { return M <= 32 ? 32 : M <= 64 ? 64 : 128; }
 inline cudaError_t rg_set_attrs() {
     static bool done = false;
     if (done) return cudaSuccess;
     const int bns[3] = {32, 64, 128};
-    for (int nw = 1; nw <= 2; ++nw)
-        for (int i = 0; i < 3; ++i) {
-            cudaError_t e = cudaFuncSetAttribute((const void*)rg_pick(bns[i], nw), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 (int)rg_smem_bytes(bns[i], nw));
-            if (e != cudaSuccess) return e;
-        }
+    for (int i = 0; i < 3; ++i) {
+        cudaError_t e = cudaFuncSetAttribute((const void*)rg_pick(bns[i]), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)rg_smem_bytes(bns[i], RG_STAGES_MAX));
+        if (e != cudaSuccess) return e;
+    }
     done = true;
     return cudaSuccess;
 }
-
-// One launch.  Requirements (checked by the callers): K % 64 == 0, N <= 128 * RG_MAX_TILES, M <= 128, 16-byte aligned
-// pointers; `partial` holds rg_partial_bytes(grid, BN) bytes and `counters` RG_MAX_TILES zeroed ints.
-inline cudaError_t rg_launch(cudaStream_t s, bool pdl, int n_sm, const CUtensorMap& mW, const CUtensorMap& mW2, const CUtensorMap& mX,
-                             int M, int N, int K, int epi, const bf16* res, bf16* out, float* partial, int* counters, int defer = 0,
-                             unsigned long long* trace = nullptr) {
-    const int bn = rg_bn_for(M), nw = (epi == RG_EPI_SWIGLU) ? 2 : 1;
-    RowsGemmArgs a{};
-    a.out = out; a.res = res; a.partial = partial; a.counters = counters;
-    a.M = M; a.N = N; a.K = K; a.epi = epi;
-    a.n_tiles = (N + RG_BM - 1) / RG_BM; a.kb = K / RG_BK; a.nst = rg_stages(bn, nw); a.defer = defer; a.trace = trace;
-    const long long U = (long long)a.n_tiles * a.kb;
-    const int grid = (int)(U < n_sm ? U : n_sm);
+template <typename Args>
+inline cudaError_t rg_launch_pdl(void (*k)(Args), dim3 grid, dim3 block, cudaStream_t s, bool pdl, const Args& a) {
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(RG_THREADS); cfg.dynamicSmemBytes = rg_smem_bytes(bn, nw); cfg.stream = s;
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = s;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, rg_pick(bn, nw), mW, mW2, mX, a);
+    return cudaLaunchKernelEx(&cfg, k, a);
+}
+
+// The GEMM launch.  N = rows of W (+ rows of W2, which must equal rows of W and be a multiple of 128 when W2 is given).
+// Requirements (checked by the callers): K % 64 == 0, tiles <= RG_MAX_TILES, M <= 128, 16-byte aligned pointers; `partial`
+// holds rg_partial_bytes(RG_CTAS_PER_SM * n_sm, BN) bytes.  Split tiles are left for rg_finish_tiles / rows_finish_norm_kernel.
+inline cudaError_t rg_launch(cudaStream_t s, bool pdl, int n_sm, const CUtensorMap& mW, const CUtensorMap& mW2, const CUtensorMap& mX,
+                             int M, int N, int tiles_w, int K, int epi, const bf16* res, bf16* out, float* partial, int all_partial,
+                             unsigned long long* trace = nullptr) {
+    const int bn = rg_bn_for(M);
+    RowsGemmArgs a{};
+    a.out = out; a.res = res; a.partial = partial;
+    a.M = M; a.N = N; a.K = K; a.epi = epi;
+    a.n_tiles = (N + RG_BM - 1) / RG_BM; a.kb = K / RG_BK; a.tiles_w = tiles_w; a.all_partial = all_partial; a.trace = trace;
+    const int grid = rg_grid(a.n_tiles, a.kb, n_sm);
+    a.nst = rg_stages_for(grid, n_sm);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(RG_THREADS); cfg.dynamicSmemBytes = rg_smem_bytes(bn, a.nst); cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, rg_pick(bn), mW, mW2, mX, a);
+}
+// finish of the split tiles of the launch above (same M, N, K, n_sm); mode SWIGLU: pre = the GEMM's out, out = [M][N/2]
+inline cudaError_t rg_finish_tiles(cudaStream_t s, bool pdl, int n_sm, int M, int N, int K, int mode, const float* partial,
+                                   const bf16* pre, const bf16* res, bf16* out) {
+    RowsFinishTilesArgs f{};
+    f.partial = partial; f.pre = pre; f.res = res; f.out = out;
+    f.M = M; f.N = N; f.bn = rg_bn_for(M); f.kb = K / RG_BK; f.n_tiles = (N + RG_BM - 1) / RG_BM; f.mode = mode;
+    f.G = rg_grid(f.n_tiles, f.kb, n_sm);
+    const int gx = mode == RG_EPI_SWIGLU ? f.n_tiles / 2 : f.G - 1;
+    if (gx < 1) return cudaSuccess;
+    return rg_launch_pdl(rows_finish_tiles_kernel, dim3(gx, (M + RFT_ROWS - 1) / RFT_ROWS), dim3(RG_BM), s, pdl, f);
 }
