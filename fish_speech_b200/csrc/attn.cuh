@@ -470,6 +470,235 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
     attn_decode_body<HD, GQ, SyncBlock<ATTN_THREADS>>(a, blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
 }
 
+// ----------------------------------------------------------------------------- slow-AR decode attention, many rows
+// Same math and the same (split, kv head, row) work item as attn_decode_body, for steps with many requests in flight
+// (config 3: 64 rows x 2k keys = 537 MB of cached K/V per layer).  attn_decode_body spends ~61 warp instructions per key
+// (fp32 FMAs for 4 query heads plus a 16-lane shuffle reduction per key), which caps it at ~40 % of the HBM rate; here
+// Q.K^T and P.V run on the tensor cores (mma.sync.m16n8k16, bf16 x bf16 -> fp32): ~12 instructions per key.
+//  * The 4 query heads of a GQA group are rows 0-3 of the 16-row A operand (rows 4-15 are zero).
+//  * No shared-memory staging and no ldmatrix: the reduction index of an MMA may be permuted freely as long as both
+//    operands agree, so every lane reads whole 16-byte pieces of the K / V rows straight from global memory
+//    (ld.global.nc, each byte read once, 64 B or 128 B contiguous per row and instruction):
+//      S = Q.K^T : lane (n = lane/4, q = lane%4) holds K[key n][8(4j+q) .. +8), j = 0..3; MMA k-step 2j uses its first four
+//                  elements as k = {2q, 2q+1, 2q+8, 2q+9}, k-step 2j+1 the last four; the Q fragments are built with the
+//                  same assignment.
+//      O += P.V  : lane (g = lane/4, q) holds V[keys 2q, 2q+1, 2q+8, 2q+9][8(g+8j) .. +8), j = 0..1; MMA (j, e) takes element
+//                  e of each piece (two PRMTs make its B registers), so its output column g is d = 8(g+8j)+e.
+//  * P is split into two bf16 terms (p = hi + lo, 16 mantissa bits) so that P.V keeps fp32-level accuracy like the
+//    reference's MATH SDPA (inference.py:210); Q and K are bf16 values, so the products of Q.K^T are exact.
+//  * A warp owns every 4th block of 16 keys of the item with its own running (max, sum, O); the four warps are merged
+//    through shared memory, then the split partials by the last CTA to arrive (as in attn_decode_body).
+//  * The new key / value of the step must already be in the cache (rope_append_kernel runs first).
+#define ATC_THREADS 128
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+template <int HD, int GQ>
+__global__ void __launch_bounds__(ATC_THREADS, 2) attn_tc_kernel(AttnArgs a) {
+    static_assert(HD == 128 && GQ <= 8, "tensor-core decode attention: head_dim 128, up to 8 query heads per kv head");
+    constexpr int EPL = HD / 32;
+    constexpr int NWARP = ATC_THREADS / 32;
+    __shared__ float qs[GQ][HD];
+    __shared__ float so[NWARP][GQ][HD];   // per-warp numerators
+    __shared__ float sm[NWARP][GQ], sl[NWARP][GQ];
+    __shared__ int is_last;
+    if (threadIdx.x == 0)
+        l2_prefetch_share(a.pf_ptr, a.pf_bytes, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
+                          gridDim.x * gridDim.y * gridDim.z);
+    pdl_wait();
+    pdl_launch_dependents();
+    const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const int pos = a.pos[m];
+    const int slot = a.slots ? a.slots[m] : m;
+    const int qkv_w = (a.H + 2 * a.KV) * HD;
+    const bf16* row = a.qkv + (size_t)m * qkv_w;
+    const int n_keys = pos + 1;
+    const int per = (n_keys + a.splits - 1) / a.splits;
+    const int k0 = split * per;
+    const int k1 = min(n_keys, k0 + per);
+    const bf16* rope_row = a.rope + (size_t)pos * HD;
+    for (int gg = warp; gg < GQ; gg += NWARP) {
+        float qin[EPL], qv[EPL];
+        load_head<HD, false>(row + (h * GQ + gg) * HD, nullptr, 0, qin);
+        head_norm_rope<HD>(qin, a.q_norm, rope_row, a.qk_norm, a.eps, qv);
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) qs[gg][lane * EPL + i] = qv[i];
+    }
+    __syncthreads();
+    // Q fragments: k-step 2j -> (a0 | a2) = Q[g][8(4j+q) + {0,1 | 2,3}], k-step 2j+1 -> + {4,5 | 6,7}; rows >= GQ are zero
+    uint32_t qa[8][2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int d0 = 8 * (4 * j + q);
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            qa[2 * j + (e >> 1)][e & 1] = (g < GQ) ? pack2(qs[g < GQ ? g : 0][d0 + 2 * e], qs[g < GQ ? g : 0][d0 + 2 * e + 1]) : 0u;
+    }
+    const bf16* kbase = a.kcache + ((size_t)slot * a.KV + h) * a.S * HD;
+    const bf16* vbase = a.vcache + ((size_t)slot * a.KV + h) * a.S * HD;
+    float o[2][8][4];  // MMA (j, e): c0, c1 = O[g][column 2q + {0,1}] -> d = 8((2q+{0,1}) + 8j) + e
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[j][e][i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;  // of head g, replicated in the 4 lanes of the row (l_run: this lane's share)
+
+    for (int kb = k0 + warp * 16; kb < k1; kb += NWARP * 16) {
+        // ---- loads: K rows kb + g and kb + 8 + g (4 pieces each), V rows kb + {2q, 2q+1, 2q+8, 2q+9} (2 pieces each)
+        uint4 kr[2][4], vr[4][2];
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+            const int key = kb + nb * 8 + g;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                kr[nb][j] = key < k1 ? ld_stream(kbase + (size_t)key * HD + 8 * (4 * j + q)) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int key = kb + 2 * q + (r & 1) + (r >> 1) * 8;
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                vr[r][j] = key < k1 ? ld_stream(vbase + (size_t)key * HD + 8 * (g + 8 * j)) : make_uint4(0, 0, 0, 0);
+        }
+        // ---- S = Q.K^T for the two 8-key blocks
+        float sc[2][4];
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) sc[nb][i] = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                mma_bf16_16816(sc[nb], qa[2 * j][0], 0u, qa[2 * j][1], 0u, kr[nb][j].x, kr[nb][j].y);
+                mma_bf16_16816(sc[nb], qa[2 * j + 1][0], 0u, qa[2 * j + 1][1], 0u, kr[nb][j].z, kr[nb][j].w);
+            }
+        }
+        // ---- online softmax of row g over the 16 keys (this lane: keys kb + nb*8 + 2q + {0,1})
+        float p[2][2];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb)
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int key = kb + nb * 8 + 2 * q + i;
+                p[nb][i] = key < k1 ? sc[nb][i] * a.scale : -INFINITY;
+                mx = fmaxf(mx, p[nb][i]);
+            }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float m_new = fmaxf(m_run, mx);  // finite: key kb of this block is valid for every lane's row
+        const float corr = (m_run == -INFINITY) ? 0.f : expf(m_run - m_new);
+        float psum = 0.f;
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb)
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                p[nb][i] = expf(p[nb][i] - m_new);
+                psum += p[nb][i];
+            }
+        l_run = l_run * corr + psum;
+        if (__any_sync(0xffffffffu, m_new != m_run)) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) { o[j][e][0] *= corr; o[j][e][1] *= corr; }
+        }
+        m_run = m_new;
+        // ---- P = hi + lo (bf16 each); A fragment: a0 = keys 2q,2q+1 (block 0), a2 = keys 8+2q, 9+2q (block 1)
+        uint32_t ph[2], pl[2];
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+            const float h0 = rbf(p[nb][0]), h1 = rbf(p[nb][1]);
+            ph[nb] = pack2(h0, h1);
+            pl[nb] = pack2(p[nb][0] - h0, p[nb][1] - h1);
+        }
+        // ---- O += P.V
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t va[4] = {vr[0][j].x, vr[0][j].y, vr[0][j].z, vr[0][j].w};  // key 2q
+            const uint32_t vb[4] = {vr[1][j].x, vr[1][j].y, vr[1][j].z, vr[1][j].w};  // key 2q+1
+            const uint32_t vc[4] = {vr[2][j].x, vr[2][j].y, vr[2][j].z, vr[2][j].w};  // key 2q+8
+            const uint32_t vd[4] = {vr[3][j].x, vr[3][j].y, vr[3][j].z, vr[3][j].w};  // key 2q+9
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const uint32_t sel = (e & 1) ? 0x7632u : 0x5410u;  // high / low halves of the two source registers
+                const uint32_t b0 = __byte_perm(va[e >> 1], vb[e >> 1], sel);
+                const uint32_t b1 = __byte_perm(vc[e >> 1], vd[e >> 1], sel);
+                mma_bf16_16816(o[j][e], ph[0], 0u, ph[1], 0u, b0, b1);
+                mma_bf16_16816(o[j][e], pl[0], 0u, pl[1], 0u, b0, b1);
+            }
+        }
+    }
+    // ---- merge the warps: row sums over the 4 lanes of a row, then (max, sum, O) through shared memory
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    if (g < GQ) {
+        if (q == 0) { sm[warp][g] = m_run; sl[warp][g] = l_run; }
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                so[warp][g][8 * (2 * q + 8 * j) + e] = o[j][e][0];
+                so[warp][g][8 * (2 * q + 1 + 8 * j) + e] = o[j][e][1];
+            }
+    }
+    __syncthreads();
+    const int H = a.H;
+    const size_t pbase = (((size_t)m * a.KV + h) * a.splits + split);
+    for (int e = tid; e < GQ * HD; e += ATC_THREADS) {
+        const int gg = e / HD, d = e % HD;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < NWARP; ++w) M = fmaxf(M, sm[w][gg]);
+        float num = 0.f, den = 0.f;
+#pragma unroll
+        for (int w = 0; w < NWARP; ++w) {
+            const float wgt = (sm[w][gg] == -INFINITY) ? 0.f : expf(sm[w][gg] - M);
+            num = fmaf(wgt, so[w][gg][d], num);
+            den = fmaf(wgt, sl[w][gg], den);
+        }
+        if (a.splits == 1) {
+            a.y[(size_t)m * H * HD + (h * GQ + gg) * HD + d] = __float2bfloat16_rn(num / den);
+        } else {
+            a.ws_acc[pbase * GQ * HD + e] = num;
+            if (d == 0) {
+                a.ws_ml[(pbase * GQ + gg) * 2 + 0] = M;
+                a.ws_ml[(pbase * GQ + gg) * 2 + 1] = den;
+            }
+        }
+    }
+    if (a.splits == 1) return;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const int prev = atomicAdd(&a.counters[m * a.KV + h], 1);
+        is_last = (prev == a.splits - 1);
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    const size_t b0 = ((size_t)m * a.KV + h) * a.splits;
+    for (int e = tid; e < GQ * HD; e += ATC_THREADS) {
+        const int gg = e / HD;
+        float M = -INFINITY;
+        for (int s2 = 0; s2 < a.splits; ++s2) M = fmaxf(M, __ldcg(&a.ws_ml[((b0 + s2) * GQ + gg) * 2]));
+        float num = 0.f, den = 0.f;
+        for (int s2 = 0; s2 < a.splits; ++s2) {
+            const float ms = __ldcg(&a.ws_ml[((b0 + s2) * GQ + gg) * 2]);
+            const float ls = __ldcg(&a.ws_ml[((b0 + s2) * GQ + gg) * 2 + 1]);
+            const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+            num = fmaf(w, __ldcg(&a.ws_acc[(b0 + s2) * GQ * HD + e]), num);
+            den = fmaf(w, ls, den);
+        }
+        a.y[(size_t)m * H * HD + (h * GQ) * HD + e] = __float2bfloat16_rn(num / den);
+    }
+    if (tid == 0) a.counters[m * a.KV + h] = 0;  // re-arm for the next launch
+}
+
 // ----------------------------------------------------------------------------- slow-AR decode attention, latency form
 // Same math as attn_decode_body for ONE (split, kv head, row) item, shaped for the persistent frame kernel where this
 // op sits on a ~400-step dependent chain: the split's whole key range (<= ASP_MAXKEYS) is one tile, and every K and V

@@ -80,6 +80,7 @@ struct fsb_dual_ar {
                                      // per step) on this library's tcgen05 stream-K kernel (rows_gemm.cuh), 2 = the same through
                                      // cuBLAS, 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
     float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
+    int attn_tc = 1;                 // many-row steps: tensor-core decode attention (attn_tc_kernel) instead of attn_decode_kernel
     bool rg_ok = false;              // tensor-map encoder available, attributes set
     std::map<std::tuple<const void*, int, int, int>, CUtensorMap> rg_maps;  // (ptr, rows, cols, box rows) -> TMA map
     int max_splits = 32;
@@ -251,13 +252,19 @@ cudaError_t run_gemv(const GemvCfg& gc, bool pdl, cudaStream_t s, int M, int N, 
 
 // ------------------------------------------------------------------------------------------- attention dispatch
 typedef void (*attn_fn)(AttnArgs);
-struct AttnKernels { attn_fn decode, append, fast; int threads_fast; };
+template <int HD, int GQ>
+attn_fn attn_tc_pick() {
+    if constexpr (HD == 128) return attn_tc_kernel<HD, GQ>;
+    else return nullptr;
+}
+struct AttnKernels { attn_fn decode, append, fast, tc; int threads_fast; };  // tc: tensor-core many-row decode (head_dim 128) or nullptr
 bool pick_attn(int hd, int gq, AttnKernels* k) {
 #define CASE(HD, GQ)                                                               \
     if (hd == HD && gq == GQ) {                                                    \
         k->decode = attn_decode_kernel<HD, GQ>;                                    \
         k->append = rope_append_kernel<HD>;                                        \
         k->fast = fast_attn_kernel<HD, GQ>;                                        \
+        k->tc = attn_tc_pick<HD, GQ>();                                            \
         k->threads_fast = 32 * GQ;                                                 \
         return true;                                                               \
     }
@@ -443,6 +450,22 @@ int rows_finish_norm(fsb_dual_ar* h, cudaStream_t s, int M, int N, int K_pending
     return 0;
 }
 
+// slow-AR attention of a many-row step: K/V append + tensor-core decode attention (head_dim 128), else the fused kernel
+int rows_attention(fsb_dual_ar* h, cudaStream_t s, const AttnKernels& ak, AttnArgs a, int splits, int KV, int M, bool pdl) {
+    a.splits = splits;
+    if (ak.tc && h->attn_tc) {
+        AttnArgs ap = a;
+        ap.pf_ptr = nullptr; ap.pf_bytes = 0; ap.fused_append = 0;
+        CK(launch(ak.append, dim3(KV, M), dim3(64), 0, s, pdl, ap));
+        a.fused_append = 0;
+        CK(launch(ak.tc, dim3(splits, KV, M), dim3(ATC_THREADS), 0, s, pdl, a));
+        return 0;
+    }
+    a.fused_append = 1;
+    CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, pdl, a));
+    return 0;
+}
+
 // transformer layers over 8 < M <= PREFILL_ROWS decode rows (one row per request, each with its own position and KV
 // slot): every Linear runs ONCE over all rows, so a step streams the weights once however many requests are in flight.
 // Same contract as run_layers (result in h->x / h->xf); scratch = the prompt-pass buffers.
@@ -478,7 +501,7 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
                 if (int r = rows_finish_norm(h, s, M, D, 0, nullptr, cur, nullptr, w.attn_norm, h->pxn)) return r;
             if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, h->qkv)) return r;
             if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
-            else CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, pdl, a));
+            else if (int r = rows_attention(h, s, ak, a, splits, KV, M, pdl)) return r;
             const bool dfr_o = rows_all_partial_ok(h, D, H * HD), dfr_2 = rows_all_partial_ok(h, D, F);
             if (int r = rows_linear_tc(h, s, w.wo, nullptr, h->y, M, D, H * HD, RG_EPI_RESIDUAL, cur, xb, nullptr, dfr_o)) return r;
             if (int r = rows_finish_norm(h, s, M, D, dfr_o ? H * HD : 0, cur, xb, xb, w.ffn_norm, h->pxn)) return r;
@@ -492,7 +515,7 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
         }
         if (int r = rows_linear(h, w.wqkv, h->pxn, h->qkv, M, QKV, D)) return r;
         if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, false, a));
-        else CK(launch(ak.decode, dim3(splits, KV, M), dim3(ATTN_THREADS), 0, s, false, a));
+        else if (int r = rows_attention(h, s, ak, a, splits, KV, M, false)) return r;
         if (int r = rows_linear(h, w.wo, h->y, h->ptmp, M, D, H * HD)) return r;
         add_rows_kernel<<<ew_blocks, 256, 0, s>>>(cur, h->ptmp, xb, (size_t)M * D / 8);
         rmsnorm_rows_kernel<<<M, 256, 0, s>>>(xb, w.ffn_norm, h->pxn, D, d.norm_eps);
@@ -994,6 +1017,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "mega") h->use_mega = (int)value;
     else if (n == "prefill_gemm") h->prefill_gemm = (int)value;
     else if (n == "batch_gemm") h->batch_gemm = (int)value;
+    else if (n == "attn_tc") h->attn_tc = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
     else return fail(h, "unknown option " + n);

@@ -285,3 +285,39 @@ def test_many_row_step_streams_weights_once_and_matches_oracle(tiny):
     assert bool((got[:, :, 1:] >= 0).all()) and bool((got[:, :, 1:] < cb).all())
     assert bool((got[:, :, 0] >= cfg.semantic_begin_id).all()) and bool((got[:, :, 0] <= cfg.semantic_end_id).all())
     assert bool((s.pos.cpu() == torch.tensor([T - 1 + frames for T in lens], dtype=torch.int32)).all())
+
+
+def test_many_row_tensor_core_attention_matches_oracle():
+    """Head-dim-128 model (the S2-Pro attention geometry: GQA 4, hd 128) with contexts long enough for several 16-key blocks,
+    split-KV merging and ragged tails: many-row slow logits with the tensor-core decode attention (attn_tc_kernel) against the
+    oracle's prompt-route logits, and against the CUDA-core attention kernel."""
+    from fish_speech_b200.dual_ar import _stream
+    cfg = R.tiny_config(n_head=4, n_local_heads=1, head_dim=128, n_layer=2, max_seq_len=512)
+    sd = R.make_state_dict(cfg, seed=3)
+    B, V = 10, cfg.vocab_size
+    lens = [1, 2, 15, 16, 17, 63, 130, 257, 300, 431]
+    prompts = [R.make_prompt(cfg, T, seed=500 + i) for i, T in enumerate(lens)]
+    m = _mk(cfg, sd, max_rows=B)
+    om = R.DualARRef(cfg, sd)
+    om.setup_caches(1, cfg.max_seq_len)
+
+    def slow(tc, splits):
+        m.set_option("attn_tc", tc)
+        m.set_option("attn_splits", splits)
+        for k, p in enumerate(prompts):
+            m.prefill(p[:, :-1].cuda(), 0, k)
+        tok = torch.stack([p[:, -1] for p in prompts]).to(torch.int32).cuda().contiguous()
+        pos = torch.tensor([T - 1 for T in lens], dtype=torch.int32).cuda()
+        m._ck(m.lib.fsb_dual_ar_slow_step(m._h, B, tok.data_ptr(), pos.data_ptr(), None, _stream()))
+        torch.cuda.synchronize()
+        return m._buffer("slow_logits")[: B * V].view(B, V).clone().cpu()
+
+    refs = [om.forward_generate(p[None], torch.arange(p.shape[1]))[0][0, -1] for p in prompts]
+    base = slow(0, 0)
+    for splits in (1, 3, 0):
+        lg = slow(1, splits)
+        for k in range(B):
+            _check_logits(f"tensor-core attention splits={splits} ctx {lens[k]}", lg[k], refs[k])
+        mabs, _, _ = err_stats(lg, base)
+        print(f"[parity] tensor-core vs CUDA-core attention (splits={splits}): max-abs {mabs:.4f}")
+        assert mabs <= ABS_TOL
