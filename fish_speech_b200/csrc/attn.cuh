@@ -490,12 +490,15 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
 //    through shared memory, then the split partials by the last CTA to arrive (as in attn_decode_body).
 //  * The new key / value of the step must already be in the cache (rope_append_kernel runs first).
 #define ATC_THREADS 128
-__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+// D rows 0-7 (+)= A rows 0-7 . B; rows 8-15 of A are zero here (only <= 8 query heads), so their accumulators are not kept
+__device__ __forceinline__ void mma_bf16_top(float& c0, float& c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "{\n\t.reg .f32 z2, z3;\n\t"
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,z2,z3}, {%2,%6,%3,%6}, {%4,%5}, {%0,%1,%7,%7};\n\t}"
+        : "+f"(c0), "+f"(c1) : "r"(a0), "r"(a2), "r"(b0), "r"(b1), "r"(0u), "r"(0u), "r"(0u), "f"(0.f));
 }
 template <int HD, int GQ>
-__global__ void __launch_bounds__(ATC_THREADS, 2) attn_tc_kernel(AttnArgs a) {
+__global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     static_assert(HD == 128 && GQ <= 8, "tensor-core decode attention: head_dim 128, up to 8 query heads per kv head");
     constexpr int EPL = HD / 32;
     constexpr int NWARP = ATC_THREADS / 32;
@@ -539,17 +542,16 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attn_tc_kernel(AttnArgs a) {
     }
     const bf16* kbase = a.kcache + ((size_t)slot * a.KV + h) * a.S * HD;
     const bf16* vbase = a.vcache + ((size_t)slot * a.KV + h) * a.S * HD;
-    float o[2][8][4];  // MMA (j, e): c0, c1 = O[g][column 2q + {0,1}] -> d = 8((2q+{0,1}) + 8j) + e
+    float o[2][8][2];  // MMA (j, e): c0, c1 = O[g][column 2q + {0,1}] -> d = 8((2q+{0,1}) + 8j) + e
 #pragma unroll
     for (int j = 0; j < 2; ++j)
 #pragma unroll
-        for (int e = 0; e < 8; ++e)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) o[j][e][i] = 0.f;
+        for (int e = 0; e < 8; ++e) o[j][e][0] = o[j][e][1] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;  // of head g, replicated in the 4 lanes of the row (l_run: this lane's share)
 
     for (int kb = k0 + warp * 16; kb < k1; kb += NWARP * 16) {
-        // ---- loads: K rows kb + g and kb + 8 + g (4 pieces each), V rows kb + {2q, 2q+1, 2q+8, 2q+9} (2 pieces each)
+        // ---- loads: K rows kb + g and kb + 8 + g (4 pieces each), V rows kb + {2q, 2q+1, 2q+8, 2q+9} (2 pieces each); all 16
+        //      requests of the block are in flight together (requesting block i+1 early was measured slower: spills)
         uint4 kr[2][4], vr[4][2];
 #pragma unroll
         for (int nb = 0; nb < 2; ++nb) {
@@ -566,15 +568,14 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attn_tc_kernel(AttnArgs a) {
                 vr[r][j] = key < k1 ? ld_stream(vbase + (size_t)key * HD + 8 * (g + 8 * j)) : make_uint4(0, 0, 0, 0);
         }
         // ---- S = Q.K^T for the two 8-key blocks
-        float sc[2][4];
+        float sc[2][2];
 #pragma unroll
         for (int nb = 0; nb < 2; ++nb) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) sc[nb][i] = 0.f;
+            sc[nb][0] = sc[nb][1] = 0.f;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                mma_bf16_16816(sc[nb], qa[2 * j][0], 0u, qa[2 * j][1], 0u, kr[nb][j].x, kr[nb][j].y);
-                mma_bf16_16816(sc[nb], qa[2 * j + 1][0], 0u, qa[2 * j + 1][1], 0u, kr[nb][j].z, kr[nb][j].w);
+                mma_bf16_top(sc[nb][0], sc[nb][1], qa[2 * j][0], qa[2 * j][1], kr[nb][j].x, kr[nb][j].y);
+                mma_bf16_top(sc[nb][0], sc[nb][1], qa[2 * j + 1][0], qa[2 * j + 1][1], kr[nb][j].z, kr[nb][j].w);
             }
         }
         // ---- online softmax of row g over the 16 keys (this lane: keys kb + nb*8 + 2q + {0,1})
@@ -628,8 +629,8 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attn_tc_kernel(AttnArgs a) {
                 const uint32_t sel = (e & 1) ? 0x7632u : 0x5410u;  // high / low halves of the two source registers
                 const uint32_t b0 = __byte_perm(va[e >> 1], vb[e >> 1], sel);
                 const uint32_t b1 = __byte_perm(vc[e >> 1], vd[e >> 1], sel);
-                mma_bf16_16816(o[j][e], ph[0], 0u, ph[1], 0u, b0, b1);
-                mma_bf16_16816(o[j][e], pl[0], 0u, pl[1], 0u, b0, b1);
+                mma_bf16_top(o[j][e][0], o[j][e][1], ph[0], ph[1], b0, b1);
+                mma_bf16_top(o[j][e][0], o[j][e][1], pl[0], pl[1], b0, b1);
             }
         }
     }

@@ -454,6 +454,14 @@ int rows_finish_norm(fsb_dual_ar* h, cudaStream_t s, int M, int N, int K_pending
 int rows_attention(fsb_dual_ar* h, cudaStream_t s, const AttnKernels& ak, AttnArgs a, int splits, int KV, int M, bool pdl) {
     a.splits = splits;
     if (ak.tc && h->attn_tc) {
+        if (h->attn_splits <= 0) {
+            // a (split, kv head, row) item costs ~2 us of q prep / merge besides its stream, and 3 CTAs fit an SM: about two
+            // rounds of CTAs measured best (64 rows x 8 kv heads: 2 splits 11.7 ms per step, 4: 12.1, 8: 13.1)
+            const int by_len = std::max(1, (h->max_seq_len + 255) / 256);
+            const int want = (6 * h->n_sm + M * KV - 1) / (M * KV);
+            splits = std::max(1, std::min(std::min(want, by_len), h->max_splits));
+            a.splits = splits;
+        }
         AttnArgs ap = a;
         ap.pf_ptr = nullptr; ap.pf_bytes = 0; ap.fused_append = 0;
         CK(launch(ak.append, dim3(KV, M), dim3(64), 0, s, pdl, ap));
@@ -1264,6 +1272,16 @@ int32_t fsb_dual_ar_launches_per_frame(const fsb_dual_ar* h, int32_t batch) {
     if (!h) return 0;
     const fsb_dual_ar_desc& d = h->d;
     if (mega_active(h, batch)) return 1;  // the whole frame is one persistent kernel
+    const int C_ = d.num_codebooks;
+    if (rows_tc_layers(h, batch)) {
+        // many-row step on this library's kernels: per slow layer wqkv GEMM + tile finish, K/V append, attention, wo GEMM,
+        // finish+norm, gate/up GEMM + SwiGLU finish, w2 GEMM, finish+norm (10; the fused attention kernel saves the append);
+        // per fast layer the same with one attention kernel (9); +1 leading norm per stack, heads = GEMM + tile finish
+        AttnKernels ak{};
+        const bool tc_attn = pick_attn(d.head_dim, d.n_head / d.n_kv_head, &ak) && ak.tc && h->attn_tc;
+        const int slow = 1 + d.n_layer * (tc_attn ? 10 : 9), fast = 1 + d.n_fast_layer * 9;
+        return 1 /*embed*/ + slow + 2 /*LM head*/ + 1 /*sample*/ + C_ * fast + (C_ - 1) * 3 /*fast head + sample*/ + 1 /*frame end*/;
+    }
     const int passes = (batch + 7) / 8;  // GEMV passes of <= 8 rows
     const int per_layer = 4 * passes + 1;
     const int C = d.num_codebooks;

@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--mode", type=int, default=1, help="batch_gemm option: 1 = every Linear once over all rows, 0 = 8-row GEMV passes")
     ap.add_argument("--json", default="")
+    ap.add_argument("--opt", action="append", default=[], help="engine option name=value (e.g. attn_splits=8), repeatable")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -50,6 +51,9 @@ def main():
     del sd
     model.setup_caches(B, S)
     model.set_option("batch_gemm", args.mode)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        model.set_option(k, int(v))
     g = torch.Generator(device=dev).manual_seed(3 + rank)
     for k, v in model.kv_cache:
         k[:, :, : args.ctx].normal_(0.0, 0.5, generator=g)
