@@ -194,6 +194,58 @@ def time_dominant_kernel(model, iters=4):
     return nbytes, ms
 
 
+def measure_batched(dev, rank, world, batch=64, ctx=2048, frames=48, steps=2):
+    """BASELINE configs[2] beside the headline: `batch` requests per GPU, each with a `ctx`-token KV context already
+    resident (synthetic prefill: caches filled with N(0, 0.5)), decoded together for `frames` frames per step; every
+    Linear runs once over all rows on the tcgen05 stream-K kernel (csrc/rows_gemm.cuh), attention on attn_tc_kernel.
+    Returns (ms per step measured with CUDA events, algorithmic bytes per step, launches per step)."""
+    import torch
+    from fish_speech_b200 import DualARTransformerB200, s2_pro_config
+    S = (ctx + frames + 8 + 7) // 8 * 8
+    cfg = s2_pro_config(max_seq_len=S)
+    sd = synth_state_dict(cfg, dev, seed=0)
+    model = DualARTransformerB200(cfg, sd, device=dev, max_rows=batch)
+    del sd
+    model.setup_caches(batch, S)
+    g = torch.Generator(device=dev).manual_seed(3 + rank)
+    for k, v in model.kv_cache:
+        k[:, :, :ctx].normal_(0.0, 0.5, generator=g)
+        v[:, :, :ctx].normal_(0.0, 0.5, generator=g)
+    sess = model.session(batch, frames + 1)
+    bias = torch.full((cfg.vocab_size,), float("-inf"), dtype=torch.bfloat16, device=dev)
+    bias[cfg.semantic_begin_id: cfg.semantic_end_id + 1] = 0.0
+    sess.bias, sess.restrict_scan, sess.seed = bias, True, 99 + rank
+    C1 = cfg.num_codebooks + 1
+    start = torch.zeros((batch, C1), dtype=torch.int32, device=dev)
+    start[:, 0] = cfg.semantic_begin_id + torch.randint(0, cfg.codebook_size, (batch,), device=dev, generator=g).int()
+    start[:, 1:] = torch.randint(0, cfg.codebook_size, (batch, C1 - 1), device=dev, generator=g).int()
+
+    def reset():
+        sess.cur_tokens.copy_(start)
+        sess.pos.fill_(ctx)
+        sess.frame_counter.zero_()
+        sess.ras_window.zero_()
+        sess.done.zero_()
+    for _ in range(3):
+        reset()
+        sess.run(min(frames, 8), 0.8008, 0.8008, 30, True)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        reset()
+        sess.run(frames, 0.8008, 0.8008, 30, True)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_step = e0.elapsed_time(e1) / (steps * frames)
+    ok = bool((sess.out_tokens[:frames, :, 1:] >= 0).all()) and bool((sess.out_tokens[:frames, :, 1:] < cfg.codebook_size).all())
+    fbytes = model.frame_bytes(batch, int((ctx + (frames - 1) / 2.0) * batch), masked_head=False)
+    launches = model.launches_per_frame(batch)
+    del sess, model
+    torch.cuda.empty_cache()
+    return ms_step, fbytes, launches, ok
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -286,12 +338,20 @@ def run_ours(args):
             e2e_frames += host.shape[1] - PROMPT_T
             e2e_t += dt
     _da.make_semantic_logit_bias = _real_bias
-    tms = torch.tensor([ms, e2e_t], dtype=torch.float64, device=dev)
+    b64 = None
+    if not args.no_batched:
+        fb1 = model.frame_bytes(1, int(PROMPT_T + (F - 1) / 2.0), masked_head=False)
+        launches_bs1 = model.launches_per_frame(1)
+        kb_kms = time_dominant_kernel(model)
+        del sess, model
+        torch.cuda.empty_cache()
+        b64 = measure_batched(dev, rank, world, batch=args.batch, ctx=args.batch_ctx, frames=args.batch_frames)
+    tms = torch.tensor([ms, e2e_t, b64[0] if b64 else 0.0], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(args.steps * F), float(e2e_frames)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    ms_max, e2e_t_max = float(tms[0]), float(tms[1])
+    ms_max, e2e_t_max, b64_ms_max = float(tms[0]), float(tms[1]), float(tms[2])
     total_frames, total_e2e_frames = float(cnt[0]), float(cnt[1])
     if rank != 0:
         if world > 1:
@@ -301,9 +361,12 @@ def run_ours(args):
     value = total_frames * FRAME_SEC / (ms_max / 1e3)
     ms_per_frame = ms_max / (args.steps * F)
     ctx_avg = PROMPT_T + (F - 1) / 2.0
-    fbytes = model.frame_bytes(1, int(ctx_avg), masked_head=False)
-    kb, kms = time_dominant_kernel(model)
-    launches = model.launches_per_frame(1)
+    if b64 is not None:
+        fbytes, launches, (kb, kms) = fb1, launches_bs1, kb_kms
+    else:
+        fbytes = model.frame_bytes(1, int(ctx_avg), masked_head=False)
+        kb, kms = time_dominant_kernel(model)
+        launches = model.launches_per_frame(1)
     persistent = launches == 1
     line = {
         "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -318,7 +381,7 @@ def run_ours(args):
         "e2e": {"value": (total_e2e_frames * FRAME_SEC / e2e_t_max) if e2e_t_max > 0 else None, "unit": "audio-s/s",
                 "h2d_bytes_per_step": int(prompt.numel() * 8), "d2h_bytes_per_step": int(C1 * (PROMPT_T + F) * 8),
                 "frames": total_e2e_frames, "includes": "pinned-host prompt H2D, 512-token prompt pass, decode loop, D2H of codes"},
-        "gpu_launches": int(model.launches_per_frame(1) * F * args.steps),
+        "gpu_launches": int(launches * F * args.steps),
         # dominant kernel: with the persistent frame kernel ONE launch is the whole frame (every weight byte of the frame
         # streams through it), so its launch duration is the frame time measured above with CUDA events
         "roofline": ({"bound": "hbm", "kernel": "frame_mega_kernel<128,4> (persistent cooperative kernel, one launch = one frame)",
@@ -336,6 +399,18 @@ def run_ours(args):
                            "frac": fbytes / (ms_per_frame * 1e-3) / 1e9 / peak, "bytes_per_frame": fbytes,
                            "note": "algorithmic weight+KV bytes per frame (SURVEY §8d) / mean frame time, full LM head counted"},
     }
+    if b64 is not None:
+        # BASELINE configs[2] (metric: "bs1 & bs64"): weak scaling, every GPU decodes its own `batch` requests
+        line["bs64"] = {
+            "workload": "S2-Pro-shape Dual-AR batched decode, %d requests per GPU x %d GPU(s), %d-token KV context resident, %d frames/step (BASELINE configs[2])"
+                        % (args.batch, world, args.batch_ctx, args.batch_frames),
+            "value": world * args.batch * FRAME_SEC / (b64_ms_max * 1e-3), "unit": "audio-s/s", "ms_per_step": b64_ms_max,
+            "frames_per_s": world * args.batch / (b64_ms_max * 1e-3), "codes_in_range": b64[3], "launches_per_step": b64[2],
+            "roofline": {"bound": "hbm", "achieved": b64[1] / (b64_ms_max * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": b64[1] / (b64_ms_max * 1e-3) / 1e9 / peak, "bytes_per_step": b64[1],
+                         "note": "algorithmic weight + KV bytes of one step for all requests (SURVEY §8d) / CUDA-event step time; "
+                                 "kernels: rows_gemm_kernel (tcgen05 stream-K), attn_tc_kernel, finish kernels"},
+        }
     if not args.no_cpu and world >= 1:
         try:
             v, cores, sample, _ = cpu_reference_leg(args.ref_frames)
@@ -357,6 +432,10 @@ def main():
     ap.add_argument("--ref-frames", type=int, default=2)
     ap.add_argument("--e2e-steps", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-batched", action="store_true", help="skip the config-3 (bs64) section")
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--batch-ctx", type=int, default=2048)
+    ap.add_argument("--batch-frames", type=int, default=48)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
