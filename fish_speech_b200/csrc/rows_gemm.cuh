@@ -410,23 +410,36 @@ __global__ void __launch_bounds__(RF_THREADS) rows_finish_norm_kernel(RowsFinish
     float ss = 0.f;
     const size_t row = (size_t)m * a.N;
     if (a.partial != nullptr) {
-        // up to RF_EPT elements per thread, all of their partial values requested before the first sum is used
+        // up to RF_EPT elements per thread; ALL of their partial values (8 contributors each) are requested before the first
+        // one is used: written as a load phase of volatile loads followed by a sum phase, otherwise the compiler keeps the
+        // round trips in a chain (one per element and group)
         for (int nb = 0; nb < a.N; nb += RF_THREADS * RF_EPT) {
-            float v[RF_EPT], resv[RF_EPT];
+            float pv[RF_EPT][8], resv[RF_EPT];
+            int cnt[RF_EPT];
 #pragma unroll
             for (int e = 0; e < RF_EPT; ++e) {
-                const int n = nb + e * RF_THREADS + tid;
-                v[e] = 0.f; resv[e] = 0.f;
-                if (n < a.N) {
-                    resv[e] = lda(&a.res[row + n]);
-                    v[e] = rft_sum<8>(a.partial, a.bn, s_cf[n >> 7], s_cl[n >> 7], s_sf[n >> 7], m, n & 127);
+                const int n = min(nb + e * RF_THREADS + tid, a.N - 1);
+                const int t = n >> 7, r = n & 127, cf = s_cf[t], cl = s_cl[t], sf = s_sf[t];
+                cnt[e] = cl - cf + 1;
+                resv[e] = lda(&a.res[row + n]);
+#pragma unroll
+                for (int g2 = 0; g2 < 8; ++g2) {
+                    const int cc = min(cf + g2, cl);
+                    pv[e][g2] = rft_ld(&a.partial[((size_t)(cc * 2 + ((cc == cf) ? sf : 0)) * a.bn + m) * RG_BM + r]);
                 }
             }
 #pragma unroll
             for (int e = 0; e < RF_EPT; ++e) {
                 const int n = nb + e * RF_THREADS + tid;
                 if (n < a.N) {
-                    const float o = rbf(resv[e] + rbf(v[e]));
+                    float v = 0.f;
+#pragma unroll
+                    for (int g2 = 0; g2 < 8; ++g2) v += (g2 < cnt[e]) ? pv[e][g2] : 0.f;  // CTA order
+                    if (cnt[e] > 8) {  // more than 8 contributors (not on the S2 shapes): the rest in a second pass
+                        const int t = n >> 7;
+                        v += rft_sum<8>(a.partial, a.bn, s_cf[t] + 8, s_cl[t], 0, m, n & 127);
+                    }
+                    const float o = rbf(resv[e] + rbf(v));
                     a.x_out[row + n] = __float2bfloat16_rn(o);
                     ss += o * o;
                 }
