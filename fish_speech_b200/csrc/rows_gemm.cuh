@@ -327,6 +327,29 @@ __device__ __forceinline__ float rft_sum(const float* partial, int bn, int cf, i
     }
     return v;
 }
+// sums of RFT_ROWS consecutive rows at once: load phase (RFT_ROWS x 4 volatile loads) then sum phase; contributors past
+// the 4th (not on the S2 shapes of the ops that use this kernel) go through rft_sum
+__device__ __forceinline__ void rft_sum_rows(const float* partial, int bn, int cf, int cl, int sf, int m0, int M, int r, float (&v)[RFT_ROWS]) {
+    float pv[RFT_ROWS][4];
+#pragma unroll
+    for (int i = 0; i < RFT_ROWS; ++i) {
+        const int m = min(m0 + i, M - 1);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const int cc = min(cf + g, cl);
+            pv[i][g] = rft_ld(&partial[((size_t)(cc * 2 + ((cc == cf) ? sf : 0)) * bn + m) * RG_BM + r]);
+        }
+    }
+    const int cnt = cl - cf + 1;
+#pragma unroll
+    for (int i = 0; i < RFT_ROWS; ++i) {
+        float x = 0.f;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) x += (g < cnt) ? pv[i][g] : 0.f;  // CTA order
+        if (cnt > 4) x += rft_sum<4>(partial, bn, cf + 4, cl, 0, min(m0 + i, M - 1), r);
+        v[i] = x;
+    }
+}
 // grid.x: SwiGLU mode = the F/128 output tiles; otherwise the G-1 boundaries between CTA ranges (only a boundary that
 // falls inside a tile splits it, and the first boundary inside a tile owns its finish), so a 1217-tile LM head launches
 // ~300 small CTAs per row group, not one per tile.
@@ -352,9 +375,7 @@ __global__ void __launch_bounds__(RG_BM) rows_finish_tiles_kernel(RowsFinishTile
     if (!swiglu) {
         if (n >= a.N) return;
         float v[RFT_ROWS];
-#pragma unroll
-        for (int i = 0; i < RFT_ROWS; ++i)
-            v[i] = (m0 + i < a.M) ? rft_sum<4>(a.partial, a.bn, s_seg[0][0], s_seg[0][1], s_seg[0][2], m0 + i, r) : 0.f;
+        rft_sum_rows(a.partial, a.bn, s_seg[0][0], s_seg[0][1], s_seg[0][2], m0, a.M, r, v);
 #pragma unroll
         for (int i = 0; i < RFT_ROWS; ++i) {
             if (m0 + i >= a.M) break;
@@ -366,11 +387,13 @@ __global__ void __launch_bounds__(RG_BM) rows_finish_tiles_kernel(RowsFinishTile
     const int F = a.N / 2;
     const bool split_g = s_seg[0][0] != s_seg[0][1], split_u = s_seg[1][0] != s_seg[1][1];
     float g[RFT_ROWS], up[RFT_ROWS];
+    if (split_g) rft_sum_rows(a.partial, a.bn, s_seg[0][0], s_seg[0][1], s_seg[0][2], m0, a.M, r, g);
+    if (split_u) rft_sum_rows(a.partial, a.bn, s_seg[1][0], s_seg[1][1], s_seg[1][2], m0, a.M, r, up);
 #pragma unroll
     for (int i = 0; i < RFT_ROWS; ++i) {
         const int m = min(m0 + i, a.M - 1);
-        g[i] = split_g ? rbf(rft_sum<4>(a.partial, a.bn, s_seg[0][0], s_seg[0][1], s_seg[0][2], m, r)) : lda(&a.pre[(size_t)m * a.N + n]);
-        up[i] = split_u ? rbf(rft_sum<4>(a.partial, a.bn, s_seg[1][0], s_seg[1][1], s_seg[1][2], m, r)) : lda(&a.pre[(size_t)m * a.N + F + n]);
+        g[i] = split_g ? rbf(g[i]) : lda(&a.pre[(size_t)m * a.N + n]);
+        up[i] = split_u ? rbf(up[i]) : lda(&a.pre[(size_t)m * a.N + F + n]);
     }
 #pragma unroll
     for (int i = 0; i < RFT_ROWS; ++i)
