@@ -80,6 +80,8 @@ struct fsb_dual_ar {
                                      // per step) on this library's tcgen05 stream-K kernel (rows_gemm.cuh), 2 = the same through
                                      // cuBLAS, 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
     float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
+    int masked_head = 1;             // fused frames with the constrained-decode bias: compute only the LM-head rows the sampler can
+                                     // read (semantic range + <|im_end|>) instead of all `vocab` rows; batch 1 paths
     int attn_tc = 1;                 // many-row steps: tensor-core decode attention (attn_tc_kernel) instead of attn_decode_kernel
     bool rg_ok = false;              // tensor-map encoder available, attributes set
     std::map<std::tuple<const void*, int, int, int>, CUtensorMap> rg_maps;  // (ptr, rows, cols, box rows) -> TMA map
@@ -307,6 +309,19 @@ EmbedArgs make_embed_args(const fsb_dual_ar* h, const int32_t* tokens) {
     e.inv_div = (float)std::sqrt((double)(d.num_codebooks + 1));
     e.pf_ptr = nullptr; e.pf_bytes = 0;
     return e;
+}
+
+// LM-head rows a fused frame has to compute: with the constrained-decode bias (inference.py:308-320) every logit outside
+// [semantic_begin, semantic_end] + {im_end} is -inf after the bias add, so the sampler (restrict_scan) never reads it.
+// One contiguous 8-aligned row range covers both (im_end sits 35 rows below the semantic range at the S2 ids).
+void head_rows(const fsb_dual_ar_desc& d, bool restricted, int* lo, int* n) {
+    if (!restricted) { *lo = 0; *n = d.vocab; return; }
+    const int a = std::min(d.im_end_id, d.semantic_begin_id) & ~7;
+    const int b = std::min(d.vocab, (std::max(d.im_end_id, d.semantic_end_id) + 1 + 7) & ~7);
+    *lo = a; *n = b - a;
+}
+bool head_restricted(const fsb_dual_ar* h, const fsb_frame_args& fa) {
+    return h->masked_head && fa.restrict_scan && fa.logit_bias && fa.batch == 1;
 }
 
 // sampling of the main (slow) token: two draws + RAS selection + code 0 (inference.py:118-155)
@@ -613,7 +628,7 @@ int run_embed(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens) {
 
 // slow stack + final norm + LM head for M decode rows
 int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, const int32_t* pos,
-                  const int32_t* slots) {
+                  const int32_t* slots, bool restricted_head = false) {
     const fsb_dual_ar_desc& d = h->d;
     if (int r = run_embed(h, s, M, tokens)) return r;
     // embed wrote x2; layer 0 uses it as input and as the wo residual, writes xb = x2?  -> use a distinct buffer
@@ -623,8 +638,10 @@ int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, 
     if (!head || !h->norm) return fail(h, "LM head / final norm not bound");
     if (int r = run_layers(h, s, false, M, h->x2, pos, slots, true, -1, h->norm, h->hidden)) return r;
     if (batch_gemm_active(h, M)) return run_head_rows(h, s, M, head, d.vocab, h->x, h->norm, h->hidden, h->slow_logits);
-    CK(run_gemv(h->gc, h->use_pdl != 0, s, M, d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head,
-                nullptr, h->x, h->norm, nullptr, h->slow_logits, h->hidden, d.norm_eps, nullptr, 0));
+    int lo = 0, n = d.vocab;
+    head_rows(d, restricted_head && M == 1, &lo, &n);
+    CK(run_gemv(h->gc, h->use_pdl != 0, s, M, n, d.dim, PRO_RMSNORM, EPI_STORE, head + (size_t)lo * d.dim,
+                nullptr, h->x, h->norm, nullptr, h->slow_logits + lo, h->hidden, d.norm_eps, nullptr, 0));
     return 0;
 }
 
@@ -646,7 +663,7 @@ int enqueue_frame(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     const fsb_dual_ar_desc& d = h->d;
     const int B = fa.batch, C = d.num_codebooks, V = d.vocab, cb = d.codebook_size;
     const bool pdl = h->use_pdl != 0;
-    if (int r = run_slow_step(h, s, B, fa.cur_tokens, fa.pos, fa.slots)) return r;
+    if (int r = run_slow_step(h, s, B, fa.cur_tokens, fa.pos, fa.slots, head_restricted(h, fa))) return r;
 
     SampleArgs sa = make_slow_sample(h, fa);
     CK(launch(sample_kernel, dim3(B), dim3(SAMPLE_THREADS), 0, s, pdl, sa));
@@ -808,8 +825,10 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
         return fail(h, "context too long for the persistent frame kernel (set option mega=0)");
     mb.add_layers(h, t, false, t.x2, fa.pos, fa.slots, -1, splits);
     const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
-    mb.add_gemv(d.vocab, d.dim, PRO_RMSNORM, EPI_STORE, head, nullptr, t.x, h->norm, nullptr, nullptr, h->slow_logits,
-                h->hidden, t.hidden, d.norm_eps);
+    int head_lo = 0, head_n = d.vocab;
+    head_rows(d, head_restricted(h, fa), &head_lo, &head_n);
+    mb.add_gemv(head_n, d.dim, PRO_RMSNORM, EPI_STORE, head + (size_t)head_lo * d.dim, nullptr, t.x, h->norm, nullptr, nullptr,
+                h->slow_logits + head_lo, h->hidden, t.hidden, d.norm_eps);
     {
         SampleArgs sa = make_slow_sample(h, fa);
         sa.xfast_t = t.xfast;
@@ -1026,6 +1045,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "prefill_gemm") h->prefill_gemm = (int)value;
     else if (n == "batch_gemm") h->batch_gemm = (int)value;
     else if (n == "attn_tc") h->attn_tc = (int)value;
+    else if (n == "masked_head") h->masked_head = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
     else return fail(h, "unknown option " + n);
@@ -1261,7 +1281,9 @@ double fsb_dual_ar_frame_bytes(const fsb_dual_ar* h, int32_t batch, int64_t ctx_
     const fsb_dual_ar_desc& d = h->d;
     const double D = d.dim, HD = d.head_dim, H = d.n_head, KV = d.n_kv_head, F = d.ffn, C = d.num_codebooks;
     const double p_layer = D * (H + 2 * KV) * HD + H * HD * D + 3 * D * F;
-    const double v_eff = masked_head ? (d.semantic_end_id - d.semantic_begin_id + 2) : d.vocab;
+    int hl = 0, hn = d.vocab;
+    head_rows(d, masked_head != 0 && h->masked_head && batch == 1, &hl, &hn);
+    const double v_eff = hn;  // rows the fused frame's LM head streams (4136 of 155776 at the S2 ids when restricted)
     double bytes = 2.0 * (d.n_layer * p_layer + v_eff * D) + 2.0 * (C * d.n_fast_layer * p_layer + (C - 1) * d.codebook_size * D);
     bytes += (double)ctx_sum * 2.0 * d.n_layer * 2.0 * KV * HD;
     (void)batch;

@@ -102,7 +102,9 @@ typedef struct {
 int fsb_dual_ar_decode_frames(fsb_dual_ar* h, const fsb_frame_args* args, int32_t n_frames, void* stream);
 
 /* Algorithmic HBM bytes of one frame (SURVEY.md §8d shared formula): weights + KV for `ctx_sum` = sum of
- * context lengths over the batch. masked_head = 1 counts only the 4097 finite LM-head rows. */
+ * context lengths over the batch. masked_head = 1 counts the LM-head rows a fused batch-1 frame streams when the
+ * constrained-decode bias is in use (option masked_head, default on): the 8-aligned row range that covers
+ * [semantic_begin, semantic_end] and <|im_end|> (4136 of 155776 rows at the S2-Pro ids), else all rows. */
 double fsb_dual_ar_frame_bytes(const fsb_dual_ar* h, int32_t batch, int64_t ctx_sum, int32_t masked_head);
 int32_t fsb_dual_ar_launches_per_frame(const fsb_dual_ar* h, int32_t batch);
 

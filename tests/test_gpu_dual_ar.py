@@ -136,11 +136,20 @@ def test_persistent_frame_kernel_vs_kernel_chain_and_golden(tiny):
     against the reference's logits: the two paths only differ in fp32 accumulation order."""
     g, cfg, sd, m = tiny
     assert m.launches_per_frame(1) == 1  # the persistent kernel is the default batch-1 path
+    lo = min(cfg.im_end_id, cfg.semantic_begin_id) & ~7
+    hi = (max(cfg.im_end_id, cfg.semantic_end_id) + 1 + 7) & ~7
     for k in g["frames_kept"][:3]:
-        slow_m, fast_m, tok_m = _one_frame(m, g, k, mega=1)
-        slow_c, fast_c, tok_c = _one_frame(m, g, k, mega=0)
+        # restricted LM head (default for fused frames: only the rows the constrained-decode sampler can read are computed):
+        # same tokens and bit-identical logits inside the row range as the full head, on both paths
+        for mega in (1, 0):
+            s_r, f_r, t_r = _one_frame(m, g, k, mega=mega, masked_head=1)
+            s_f, f_f, t_f = _one_frame(m, g, k, mega=mega, masked_head=0)
+            assert torch.equal(t_r, t_f) and torch.equal(s_r[lo:hi], s_f[lo:hi]) and torch.equal(f_r, f_f)
+        slow_m, fast_m, tok_m = _one_frame(m, g, k, mega=1, masked_head=0)  # parity of ALL logits needs the full head
+        slow_c, fast_c, tok_c = _one_frame(m, g, k, mega=0, masked_head=0)
         assert m.launches_per_frame(1) > 100
         m.set_option("mega", 1)
+        m.set_option("masked_head", 1)
         _check_logits(f"frame kernel slow logits frame {k}", slow_m, g["slow_logits"][k])
         mabs, mrel, _ = err_stats(slow_m, slow_c)
         print(f"[parity] frame kernel vs chain, slow logits frame {k}: max-abs {mabs:.4f}")
