@@ -25,7 +25,7 @@ sys.path.insert(0, str(ROOT))
 FRAME_SEC = 2048.0 / 44100.0  # one Dual-AR frame = 2048 samples @ 44.1 kHz
 PROMPT_T = 512
 # dram__bytes_read.sum + dram__bytes_write.sum of one frame_mega_kernel launch (ncu --set full, profiles/r1_frame_mega_full.md)
-NCU_TRAFFIC_BYTES = 16.406060e9 + 0.027120e9
+NCU_TRAFFIC_BYTES = 15.627865e9 + 0.027879e9  # restricted LM head (profiles/r1_frame_mega_full.md, addendum)
 
 METRIC = "audio_sec_per_sec_dual_ar_decode_bs1"
 
