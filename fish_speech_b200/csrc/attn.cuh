@@ -490,6 +490,10 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(AttnArgs a) {
 //    through shared memory, then the split partials by the last CTA to arrive (as in attn_decode_body).
 //  * The new key / value of the step must already be in the cache (rope_append_kernel runs first).
 #define ATC_THREADS 128
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
 // D rows 0-7 (+)= A rows 0-7 . B; rows 8-15 of A are zero here (only <= 8 query heads), so their accumulators are not kept
 __device__ __forceinline__ void mma_bf16_top(float& c0, float& c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
     asm volatile(
@@ -542,11 +546,16 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     }
     const bf16* kbase = a.kcache + ((size_t)slot * a.KV + h) * a.S * HD;
     const bf16* vbase = a.vcache + ((size_t)slot * a.KV + h) * a.S * HD;
-    float o[2][8][2];  // MMA (j, e): c0, c1 = O[g][column 2q + {0,1}] -> d = 8((2q+{0,1}) + 8j) + e
+    // O is accumulated TRANSPOSED: O^T[d][head] = V^T[d][key] . P^T[key][head], V^T as the A operand (all 16 rows are d
+    // values), P^T as the B operand - which is exactly the C layout of S = Q.K^T (lane (g, q) holds P[head g][keys 2q, 2q+1]).
+    // MMA (j, ee): rows g / g+8 <-> d = 8(g+8j) + ee / + ee + 4, columns 2q, 2q+1 <-> heads.  8 MMAs per 16 keys (x2 for hi/lo).
+    float o[2][4][4];
 #pragma unroll
     for (int j = 0; j < 2; ++j)
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[j][e][0] = o[j][e][1] = 0.f;
+        for (int e = 0; e < 4; ++e)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[j][e][i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;  // of head g, replicated in the 4 lanes of the row (l_run: this lane's share)
 
     for (int kb = k0 + warp * 16; kb < k1; kb += NWARP * 16) {
@@ -568,14 +577,14 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
                 vr[r][j] = key < k1 ? ld_stream(vbase + (size_t)key * HD + 8 * (g + 8 * j)) : make_uint4(0, 0, 0, 0);
         }
         // ---- S = Q.K^T for the two 8-key blocks
-        float sc[2][2];
+        float sc[2][4];  // [2], [3]: the unused rows 8-15 (A rows are zero there, they stay 0)
 #pragma unroll
         for (int nb = 0; nb < 2; ++nb) {
-            sc[nb][0] = sc[nb][1] = 0.f;
+            sc[nb][0] = sc[nb][1] = sc[nb][2] = sc[nb][3] = 0.f;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                mma_bf16_top(sc[nb][0], sc[nb][1], qa[2 * j][0], qa[2 * j][1], kr[nb][j].x, kr[nb][j].y);
-                mma_bf16_top(sc[nb][0], sc[nb][1], qa[2 * j + 1][0], qa[2 * j + 1][1], kr[nb][j].z, kr[nb][j].w);
+                mma_bf16_16816(sc[nb], qa[2 * j][0], 0u, qa[2 * j][1], 0u, kr[nb][j].x, kr[nb][j].y);
+                mma_bf16_16816(sc[nb], qa[2 * j + 1][0], 0u, qa[2 * j + 1][1], 0u, kr[nb][j].z, kr[nb][j].w);
             }
         }
         // ---- online softmax of row g over the 16 keys (this lane: keys kb + nb*8 + 2q + {0,1})
@@ -602,14 +611,15 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
                 psum += p[nb][i];
             }
         l_run = l_run * corr + psum;
-        if (__any_sync(0xffffffffu, m_new != m_run)) {
+        if (__any_sync(0xffffffffu, m_new != m_run)) {  // this lane's accumulator columns are heads 2q and 2q+1
+            const float c0 = __shfl_sync(0xffffffffu, corr, (2 * q) * 4), c1 = __shfl_sync(0xffffffffu, corr, (2 * q + 1) * 4);
 #pragma unroll
             for (int j = 0; j < 2; ++j)
 #pragma unroll
-                for (int e = 0; e < 8; ++e) { o[j][e][0] *= corr; o[j][e][1] *= corr; }
+                for (int e = 0; e < 4; ++e) { o[j][e][0] *= c0; o[j][e][1] *= c1; o[j][e][2] *= c0; o[j][e][3] *= c1; }
         }
         m_run = m_new;
-        // ---- P = hi + lo (bf16 each); A fragment: a0 = keys 2q,2q+1 (block 0), a2 = keys 8+2q, 9+2q (block 1)
+        // ---- P = hi + lo (bf16 each); B fragment of P^T: b0 = keys 2q, 2q+1 (block 0), b1 = keys 8+2q, 9+2q (block 1)
         uint32_t ph[2], pl[2];
 #pragma unroll
         for (int nb = 0; nb < 2; ++nb) {
@@ -617,7 +627,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
             ph[nb] = pack2(h0, h1);
             pl[nb] = pack2(p[nb][0] - h0, p[nb][1] - h1);
         }
-        // ---- O += P.V
+        // ---- O^T += V^T.P^T
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             const uint32_t va[4] = {vr[0][j].x, vr[0][j].y, vr[0][j].z, vr[0][j].w};  // key 2q
@@ -625,27 +635,31 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
             const uint32_t vc[4] = {vr[2][j].x, vr[2][j].y, vr[2][j].z, vr[2][j].w};  // key 2q+8
             const uint32_t vd[4] = {vr[3][j].x, vr[3][j].y, vr[3][j].z, vr[3][j].w};  // key 2q+9
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const uint32_t sel = (e & 1) ? 0x7632u : 0x5410u;  // high / low halves of the two source registers
-                const uint32_t b0 = __byte_perm(va[e >> 1], vb[e >> 1], sel);
-                const uint32_t b1 = __byte_perm(vc[e >> 1], vd[e >> 1], sel);
-                mma_bf16_top(o[j][e][0], o[j][e][1], ph[0], ph[1], b0, b1);
-                mma_bf16_top(o[j][e][0], o[j][e][1], pl[0], pl[1], b0, b1);
+            for (int e = 0; e < 4; ++e) {
+                const uint32_t sel = (e & 1) ? 0x7632u : 0x5410u;  // element e (row g) and e + 4 (row g + 8) of the 8-d piece
+                const uint32_t a0 = __byte_perm(va[e >> 1], vb[e >> 1], sel), a1 = __byte_perm(va[2 + (e >> 1)], vb[2 + (e >> 1)], sel);
+                const uint32_t a2 = __byte_perm(vc[e >> 1], vd[e >> 1], sel), a3 = __byte_perm(vc[2 + (e >> 1)], vd[2 + (e >> 1)], sel);
+                mma_bf16_16816(o[j][e], a0, a1, a2, a3, ph[0], ph[1]);
+                mma_bf16_16816(o[j][e], a0, a1, a2, a3, pl[0], pl[1]);
             }
         }
     }
     // ---- merge the warps: row sums over the 4 lanes of a row, then (max, sum, O) through shared memory
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
-    if (g < GQ) {
-        if (q == 0) { sm[warp][g] = m_run; sl[warp][g] = l_run; }
+    if (g < GQ && q == 0) { sm[warp][g] = m_run; sl[warp][g] = l_run; }
 #pragma unroll
-        for (int j = 0; j < 2; ++j)
+    for (int c = 0; c < 2; ++c) {
+        const int head = 2 * q + c;
+        if (head < GQ) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                so[warp][g][8 * (2 * q + 8 * j) + e] = o[j][e][0];
-                so[warp][g][8 * (2 * q + 1 + 8 * j) + e] = o[j][e][1];
-            }
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    so[warp][head][8 * (g + 8 * j) + e] = o[j][e][c];
+                    so[warp][head][8 * (g + 8 * j) + e + 4] = o[j][e][2 + c];
+                }
+        }
     }
     __syncthreads();
     const int H = a.H;
