@@ -187,6 +187,7 @@ struct AttnArgs {
     int H, KV, S, splits, qk_norm, fused_append, pos_fixed;  // pos_fixed >= 0 overrides pos[] (fast AR)
     float eps, scale;
     const void* pf_ptr; size_t pf_bytes;
+    unsigned long long* trace;  // profiling aid (attn_tc_kernel): 4 clock64 stamps per CTA, or nullptr
 };
 
 // ----------------------------------------------------------------------------- prompt rows: k-norm + RoPE + scatter
@@ -518,6 +519,8 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, q = lane & 3;
+    unsigned long long* tr = a.trace ? a.trace + 4 * (size_t)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) : nullptr;
+    if (tr && tid == 0) tr[0] = clock64();
     const int pos = a.pos[m];
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
@@ -557,6 +560,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) o[j][e][i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;  // of head g, replicated in the 4 lanes of the row (l_run: this lane's share)
+    if (tr && tid == 0) tr[1] = clock64();
 
     for (int kb = k0 + warp * 16; kb < k1; kb += NWARP * 16) {
         // ---- loads: K rows kb + g and kb + 8 + g (4 pieces each), V rows kb + {2q, 2q+1, 2q+8, 2q+9} (2 pieces each); all 16
@@ -645,6 +649,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
         }
     }
     // ---- merge the warps: row sums over the 4 lanes of a row, then (max, sum, O) through shared memory
+    if (tr && tid == 0) tr[2] = clock64();
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
     if (g < GQ && q == 0) { sm[warp][g] = m_run; sl[warp][g] = l_run; }
@@ -692,6 +697,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     if (tid == 0) {
         const int prev = atomicAdd(&a.counters[m * a.KV + h], 1);
         is_last = (prev == a.splits - 1);
+        if (tr) tr[3] = clock64();
     }
     __syncthreads();
     if (!is_last) return;
