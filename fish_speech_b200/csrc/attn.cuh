@@ -185,6 +185,7 @@ struct AttnArgs {
     float* ws_ml;           // [M][KV][splits][GQ][2]
     int32_t* counters;      // [M][KV]
     int H, KV, S, splits, qk_norm, fused_append, pos_fixed;  // pos_fixed >= 0 overrides pos[] (fast AR)
+    int tc_u1, tc_s2;       // attn_tc_kernel with a 1-D grid: (row, head) units [0, tc_u1) are cut into `splits` items, the rest into tc_s2
     float eps, scale;
     const void* pf_ptr; size_t pf_bytes;
     unsigned long long* trace;  // profiling aid (attn_tc_kernel): 4 clock64 stamps per CTA, or nullptr
@@ -511,22 +512,30 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     __shared__ float so[NWARP][GQ][HD];   // per-warp numerators
     __shared__ float sm[NWARP][GQ], sl[NWARP][GQ];
     __shared__ int is_last;
-    if (threadIdx.x == 0)
-        l2_prefetch_share(a.pf_ptr, a.pf_bytes, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
-                          gridDim.x * gridDim.y * gridDim.z);
+    if (threadIdx.x == 0) l2_prefetch_share(a.pf_ptr, a.pf_bytes, blockIdx.x, gridDim.x);
     pdl_wait();
     pdl_launch_dependents();
-    const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
+    // 1-D grid, big items first: units [0, tc_u1) have `splits` items each and fill whole rounds of resident CTAs, the
+    // remaining units are cut finer (tc_s2 items) so that the last, partial round is short (64 rows x 8 heads x 2 splits =
+    // 1024 equal items on 444 slots would cost three rounds for 2.3 rounds of work)
+    int unit, split, nsp;
+    {
+        const int i = blockIdx.x, n1 = a.tc_u1 * a.splits;
+        if (i < n1) { unit = i / a.splits; split = i - unit * a.splits; nsp = a.splits; }
+        else { unit = a.tc_u1 + (i - n1) / a.tc_s2; split = (i - n1) % a.tc_s2; nsp = a.tc_s2; }
+    }
+    const int m = unit / a.KV, h = unit - m * a.KV;
+    const int stride = max(a.splits, a.tc_s2);  // partial slots per unit in the workspace
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, q = lane & 3;
-    unsigned long long* tr = a.trace ? a.trace + 4 * (size_t)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) : nullptr;
+    unsigned long long* tr = a.trace ? a.trace + 4 * (size_t)blockIdx.x : nullptr;
     if (tr && tid == 0) tr[0] = clock64();
     const int pos = a.pos[m];
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const bf16* row = a.qkv + (size_t)m * qkv_w;
     const int n_keys = pos + 1;
-    const int per = (n_keys + a.splits - 1) / a.splits;
+    const int per = (n_keys + nsp - 1) / nsp;
     const int k0 = split * per;
     const int k1 = min(n_keys, k0 + per);
     const bf16* rope_row = a.rope + (size_t)pos * HD;
@@ -668,7 +677,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     }
     __syncthreads();
     const int H = a.H;
-    const size_t pbase = (((size_t)m * a.KV + h) * a.splits + split);
+    const size_t pbase = (((size_t)m * a.KV + h) * stride + split);
     for (int e = tid; e < GQ * HD; e += ATC_THREADS) {
         const int gg = e / HD, d = e % HD;
         float M = -INFINITY;
@@ -681,7 +690,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
             num = fmaf(wgt, so[w][gg][d], num);
             den = fmaf(wgt, sl[w][gg], den);
         }
-        if (a.splits == 1) {
+        if (nsp == 1) {
             a.y[(size_t)m * H * HD + (h * GQ + gg) * HD + d] = __float2bfloat16_rn(num / den);
         } else {
             a.ws_acc[pbase * GQ * HD + e] = num;
@@ -691,24 +700,24 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
             }
         }
     }
-    if (a.splits == 1) return;
+    if (nsp == 1) return;
     __threadfence();
     __syncthreads();
     if (tid == 0) {
         const int prev = atomicAdd(&a.counters[m * a.KV + h], 1);
-        is_last = (prev == a.splits - 1);
+        is_last = (prev == nsp - 1);
         if (tr) tr[3] = clock64();
     }
     __syncthreads();
     if (!is_last) return;
     __threadfence();
-    const size_t b0 = ((size_t)m * a.KV + h) * a.splits;
+    const size_t b0 = ((size_t)m * a.KV + h) * stride;
     for (int e = tid; e < GQ * HD; e += ATC_THREADS) {
         const int gg = e / HD;
         float M = -INFINITY;
-        for (int s2 = 0; s2 < a.splits; ++s2) M = fmaxf(M, __ldcg(&a.ws_ml[((b0 + s2) * GQ + gg) * 2]));
+        for (int s2 = 0; s2 < nsp; ++s2) M = fmaxf(M, __ldcg(&a.ws_ml[((b0 + s2) * GQ + gg) * 2]));
         float num = 0.f, den = 0.f;
-        for (int s2 = 0; s2 < a.splits; ++s2) {
+        for (int s2 = 0; s2 < nsp; ++s2) {
             const float ms = __ldcg(&a.ws_ml[((b0 + s2) * GQ + gg) * 2]);
             const float ls = __ldcg(&a.ws_ml[((b0 + s2) * GQ + gg) * 2 + 1]);
             const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);

@@ -82,6 +82,7 @@ struct fsb_dual_ar {
     float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
     int masked_head = 1;             // fused frames with the constrained-decode bias: compute only the LM-head rows the sampler can
                                      // read (semantic range + <|im_end|>) instead of all `vocab` rows; batch 1 paths
+    int attn_tail = 1;               // attn_tc_kernel: cut the units of the last, partial round of CTAs finer
     int attn_trace = 0;              // profiling: attn_tc_kernel writes 4 clock stamps per CTA into the mega_trace buffer
     int attn_tc = 1;                 // many-row steps: tensor-core decode attention (attn_tc_kernel) instead of attn_decode_kernel
     bool rg_ok = false;              // tensor-map encoder available, attributes set
@@ -482,8 +483,18 @@ int rows_attention(fsb_dual_ar* h, cudaStream_t s, const AttnKernels& ak, AttnAr
         ap.pf_ptr = nullptr; ap.pf_bytes = 0; ap.fused_append = 0;
         CK(launch(ak.append, dim3(KV, M), dim3(64), 0, s, pdl, ap));
         a.fused_append = 0;
-        a.trace = (h->attn_trace && (size_t)splits * KV * M * 4 <= MEGA_TRACE_WORDS) ? h->mega_trace : nullptr;
-        CK(launch(ak.tc, dim3(splits, KV, M), dim3(ATC_THREADS), 0, s, pdl, a));
+        // items: `splits` per (row, head) unit while they fill whole rounds of the 3 resident CTAs per SM, the remaining
+        // units cut finer so that the last round is short
+        const int units = M * KV, slots = 3 * h->n_sm;
+        int u1 = units, s2 = splits;
+        if (h->attn_splits <= 0 && h->attn_tail && units * splits > slots) {
+            u1 = std::min(units, (units * splits / slots) * slots / splits);
+            if (u1 < units) s2 = std::max(splits, std::min(h->max_splits, std::min((slots + units - u1 - 1) / (units - u1), std::max(1, (h->max_seq_len + 255) / 256))));
+        }
+        a.tc_u1 = u1; a.tc_s2 = s2;
+        const int G = u1 * splits + (units - u1) * s2;
+        a.trace = (h->attn_trace && (size_t)G * 4 <= MEGA_TRACE_WORDS) ? h->mega_trace : nullptr;
+        CK(launch(ak.tc, dim3(G), dim3(ATC_THREADS), 0, s, pdl, a));
         return 0;
     }
     a.fused_append = 1;
@@ -1049,6 +1060,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "attn_tc") h->attn_tc = (int)value;
     else if (n == "masked_head") h->masked_head = (int)value;
     else if (n == "attn_trace") h->attn_trace = (int)value;
+    else if (n == "attn_tail") h->attn_tail = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
     else return fail(h, "unknown option " + n);
