@@ -35,7 +35,7 @@
 #define RG_BK 64
 #define RG_THREADS 192
 #define RG_EPI_THREADS 128
-#define RG_STAGES_MAX 6      // ring depth: 6 x 24 KB when a launch has one CTA per SM, 3 x 24 KB when it has two (either way a CTA
+#define RG_STAGES_MAX 9      // barrier arrays; the ring depth of a launch comes from rg_stages_for()
 #define RG_STAGES_MIN 3      //   of the NEXT kernel fits beside them and starts its weight stream early)
 #define RG_CTAS_PER_SM 2     // most CTAs of one launch per SM
 #define RG_MAX_TILES 4096
@@ -132,7 +132,15 @@ inline int rg_grid(int n_tiles, int kb, int n_sm) {
     if (s > kb) s = kb;
     return n_tiles * s;
 }
-inline int rg_stages_for(int grid, int n_sm) { return grid <= n_sm ? RG_STAGES_MAX : RG_STAGES_MIN; }
+inline int rg_stages_for(int grid, int n_sm, int bn) {
+    if (grid > n_sm) return RG_STAGES_MIN;
+    // one CTA per SM: 6 stages (144 KB in flight per SM at 64 rows).  Deeper is slower: every SM requests its whole ring at
+    // launch, and the first stage of a CTA only lands when most of that burst has (9 stages: wqkv 11.1 us instead of 9.4)
+    static const int want = getenv("FSB_RG_STAGES") ? atoi(getenv("FSB_RG_STAGES")) : 6;
+    const int fit = (int)((225 * 1024 - 1024) / rg_stage_bytes(bn));
+    const int n = want < RG_STAGES_MAX ? want : RG_STAGES_MAX;
+    return fit < n ? fit : n;
+}
 
 #define RG_STAMP(i) do { if (a.trace) a.trace[(size_t)blockIdx.x * 8 + (i)] = clock64(); } while (0)
 #define RG_POLICY_EVICT_FIRST 0x12F0000000000000ull
@@ -521,7 +529,7 @@ inline cudaError_t rg_set_attrs() {
     const int bns[3] = {32, 64, 128};
     for (int i = 0; i < 3; ++i) {
         cudaError_t e = cudaFuncSetAttribute((const void*)rg_pick(bns[i]), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)rg_smem_bytes(bns[i], RG_STAGES_MAX));
+                                             (int)rg_smem_bytes(bns[i], rg_stages_for(1, 1, bns[i])));
         if (e != cudaSuccess) return e;
     }
     done = true;
@@ -550,7 +558,7 @@ inline cudaError_t rg_launch(cudaStream_t s, bool pdl, int n_sm, const CUtensorM
     a.M = M; a.N = N; a.K = K; a.epi = epi;
     a.n_tiles = (N + RG_BM - 1) / RG_BM; a.kb = K / RG_BK; a.tiles_w = tiles_w; a.all_partial = all_partial; a.trace = trace;
     const int grid = rg_grid(a.n_tiles, a.kb, n_sm);
-    a.nst = rg_stages_for(grid, n_sm);
+    a.nst = rg_stages_for(grid, n_sm, bn);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(RG_THREADS); cfg.dynamicSmemBytes = rg_smem_bytes(bn, a.nst); cfg.stream = s;
     cudaLaunchAttribute at[1];
