@@ -94,6 +94,28 @@ __device__ __forceinline__ void load_head(const bf16* src, const uint32_t* src_t
     }
 }
 
+// this lane's EPL elements of the head that starts at column col0 of row m of qkv, from the partial tiles of the wqkv GEMM
+template <int HD>
+__device__ __forceinline__ void load_head_part(const float* part, int s, int bn, int m, int col0, float (&v)[HD / 32]) {
+    constexpr int EPL = HD / 32;
+    static_assert(EPL == 4 || EPL == 2, "a lane's elements are one 16- or 8-byte piece of a partial-tile row");
+    const int n = col0 + (threadIdx.x & 31) * EPL, t = n >> 7, r = n & 127;
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) v[i] = 0.f;
+    for (int g = 0; g < s; ++g) {  // CTA order
+        const float* p = part + ((size_t)((t * s + g) * 2) * bn + m) * 128 + r;
+        if (EPL == 4) {
+            const float4 x = __ldcg(reinterpret_cast<const float4*>(p));
+            v[0] += x.x; v[1] += x.y; v[EPL - 2] += x.z; v[EPL - 1] += x.w;
+        } else {
+            const float2 x = __ldcg(reinterpret_cast<const float2*>(p));
+            v[0] += x.x; v[1] += x.y;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) v[i] = rbf(v[i]);
+}
+
 // norm weights and RoPE (cos, sin) of this lane's elements, fetched ahead of the data they will be applied to
 template <int HD>
 struct HeadCoef {
@@ -189,6 +211,10 @@ struct AttnArgs {
     float eps, scale;
     const void* pf_ptr; size_t pf_bytes;
     unsigned long long* trace;  // profiling aid (attn_tc_kernel): 4 clock64 stamps per CTA, or nullptr
+    // many-row steps: qkv left by rows_gemm_kernel as fp32 partial tiles (tile-aligned split: tile t = CTAs t*s .. t*s+s-1, slot 0),
+    // summed in CTA order and rounded to bf16 (one rounding per Linear) by the kernels that read q / k / v; nullptr: read `qkv`
+    const float* qkv_part;
+    int qkv_s, qkv_bn;
 };
 
 // ----------------------------------------------------------------------------- prompt rows: k-norm + RoPE + scatter
@@ -206,10 +232,16 @@ __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
     const size_t co = (((size_t)slot * a.KV + h) * a.S + pos) * HD;
     if (warp == 0) {
         float kin[EPL], k[EPL];
-        load_head<HD, false>(a.qkv + (size_t)m * qkv_w + (a.H + h) * HD, nullptr, 0, kin);
+        if (a.qkv_part) load_head_part<HD>(a.qkv_part, a.qkv_s, a.qkv_bn, m, (a.H + h) * HD, kin);
+        else load_head<HD, false>(a.qkv + (size_t)m * qkv_w + (a.H + h) * HD, nullptr, 0, kin);
         head_norm_rope<HD>(kin, a.k_norm, a.rope + (size_t)pos * HD, a.qk_norm, a.eps, k);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) a.kcache[co + lane * EPL + i] = __float2bfloat16_rn(k[i]);
+    } else if (a.qkv_part) {
+        float vin[EPL];
+        load_head_part<HD>(a.qkv_part, a.qkv_s, a.qkv_bn, m, (a.H + a.KV + h) * HD, vin);
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) a.vcache[co + lane * EPL + i] = __float2bfloat16_rn(vin[i]);
     } else {
         const bf16* v = a.qkv + (size_t)m * qkv_w + (a.H + a.KV + h) * HD;
 #pragma unroll
@@ -541,7 +573,8 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     const bf16* rope_row = a.rope + (size_t)pos * HD;
     for (int gg = warp; gg < GQ; gg += NWARP) {
         float qin[EPL], qv[EPL];
-        load_head<HD, false>(row + (h * GQ + gg) * HD, nullptr, 0, qin);
+        if (a.qkv_part) load_head_part<HD>(a.qkv_part, a.qkv_s, a.qkv_bn, m, (h * GQ + gg) * HD, qin);
+        else load_head<HD, false>(row + (h * GQ + gg) * HD, nullptr, 0, qin);
         head_norm_rope<HD>(qin, a.q_norm, rope_row, a.qk_norm, a.eps, qv);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) qs[gg][lane * EPL + i] = qv[i];
@@ -1070,11 +1103,14 @@ __device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, 
         }
 
     float qin[EPL], q[EPL];
-    load_head<HD, TAG>(row + (h * GQ + g) * HD, row_t + (h * GQ + g) * HD, tag_in, qin);
+    const bool part = !TAG && a.qkv_part != nullptr;
+    if (part) load_head_part<HD>(a.qkv_part, a.qkv_s, a.qkv_bn, m, (h * GQ + g) * HD, qin);
+    else load_head<HD, TAG>(row + (h * GQ + g) * HD, row_t + (h * GQ + g) * HD, tag_in, qin);
     head_norm_rope<HD>(qin, cq, a.qk_norm, a.eps, q);
     if (g == 0) {
         float kin[EPL], k[EPL];
-        load_head<HD, TAG>(row + (a.H + h) * HD, row_t + (a.H + h) * HD, tag_in, kin);
+        if (part) load_head_part<HD>(a.qkv_part, a.qkv_s, a.qkv_bn, m, (a.H + h) * HD, kin);
+        else load_head<HD, TAG>(row + (a.H + h) * HD, row_t + (a.H + h) * HD, tag_in, kin);
         head_norm_rope<HD>(kin, ck, a.qk_norm, a.eps, k);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) {
@@ -1084,7 +1120,8 @@ __device__ __forceinline__ void fast_attn_body(const AttnArgs& a, int h, int m, 
     }
     if (g == GQ - 1) {
         float vin[EPL];
-        load_head<HD, TAG>(row + (a.H + a.KV + h) * HD, row_t + (a.H + a.KV + h) * HD, tag_in, vin);
+        if (part) load_head_part<HD>(a.qkv_part, a.qkv_s, a.qkv_bn, m, (a.H + a.KV + h) * HD, vin);
+        else load_head<HD, TAG>(row + (a.H + a.KV + h) * HD, row_t + (a.H + a.KV + h) * HD, tag_in, vin);
 #pragma unroll
         for (int i = 0; i < EPL; ++i) {
             vnew[lane * EPL + i] = vin[i];

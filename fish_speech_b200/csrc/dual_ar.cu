@@ -82,6 +82,7 @@ struct fsb_dual_ar {
     float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
     int masked_head = 1;             // fused frames with the constrained-decode bias: compute only the LM-head rows the sampler can
                                      // read (semantic range + <|im_end|>) instead of all `vocab` rows; batch 1 paths
+    int qkv_fold = 1;                // many-row steps: q / k / v partial tiles summed by their readers instead of a finish launch
     int attn_tail = 1;               // attn_tc_kernel: cut the units of the last, partial round of CTAs finer
     int attn_trace = 0;              // profiling: attn_tc_kernel writes 4 clock stamps per CTA into the mega_trace buffer
     int attn_tc = 1;                 // many-row steps: tensor-core decode attention (attn_tc_kernel) instead of attn_decode_kernel
@@ -535,7 +536,18 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
             const bool last = l + 1 == L.size();
             if (l == 0)
                 if (int r = rows_finish_norm(h, s, M, D, 0, nullptr, cur, nullptr, w.attn_norm, h->pxn)) return r;
-            if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, h->qkv)) return r;
+            // wqkv: its split tiles are finished by the kernels that read q / k / v (K/V append, attention), not by a
+            // finish launch, whenever those kernels can (tile-aligned split; the CUDA-core slow attention cannot)
+            const int qkv_tiles = (QKV + RG_BM - 1) / RG_BM;
+            const bool qkv_part = (fast || (ak.tc && h->attn_tc)) && h->qkv_fold && qkv_tiles <= RG_CTAS_PER_SM * h->n_sm &&
+                                  QKV % RG_BM == 0;
+            a.qkv_part = nullptr;
+            if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, h->qkv, nullptr, qkv_part)) return r;
+            if (qkv_part) {
+                a.qkv_part = h->rg_partial;
+                a.qkv_s = rg_grid(qkv_tiles, D / RG_BK, h->n_sm) / qkv_tiles;
+                a.qkv_bn = rg_bn_for(M);
+            }
             if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
             else if (int r = rows_attention(h, s, ak, a, splits, KV, M, pdl)) return r;
             const bool dfr_o = rows_all_partial_ok(h, D, H * HD), dfr_2 = rows_all_partial_ok(h, D, F);
@@ -1061,6 +1073,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "masked_head") h->masked_head = (int)value;
     else if (n == "attn_trace") h->attn_trace = (int)value;
     else if (n == "attn_tail") h->attn_tail = (int)value;
+    else if (n == "qkv_fold") h->qkv_fold = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
     else return fail(h, "unknown option " + n);
@@ -1316,7 +1329,8 @@ int32_t fsb_dual_ar_launches_per_frame(const fsb_dual_ar* h, int32_t batch) {
         // per fast layer the same with one attention kernel (9); +1 leading norm per stack, heads = GEMM + tile finish
         AttnKernels ak{};
         const bool tc_attn = pick_attn(d.head_dim, d.n_head / d.n_kv_head, &ak) && ak.tc && h->attn_tc;
-        const int slow = 1 + d.n_layer * (tc_attn ? 10 : 9), fast = 1 + d.n_fast_layer * 9;
+        const int fold = h->qkv_fold ? 1 : 0;  // wqkv tile finish folded into the readers of q / k / v
+        const int slow = 1 + d.n_layer * ((tc_attn ? 10 : 9) - (tc_attn ? fold : 0)), fast = 1 + d.n_fast_layer * (9 - fold);
         return 1 /*embed*/ + slow + 2 /*LM head*/ + 1 /*sample*/ + C_ * fast + (C_ - 1) * 3 /*fast head + sample*/ + 1 /*frame end*/;
     }
     const int passes = (batch + 7) / 8;  // GEMV passes of <= 8 rows
