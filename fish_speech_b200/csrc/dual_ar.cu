@@ -82,6 +82,8 @@ struct fsb_dual_ar {
     float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
     int masked_head = 1;             // fused frames with the constrained-decode bias: compute only the LM-head rows the sampler can
                                      // read (semantic range + <|im_end|>) instead of all `vocab` rows; batch 1 paths
+    int rows_narrow = 0;             // many-row Linears with a plain store on narrow weight tiles without a k split
+                                     // (rows_gemm_narrow_kernel); measured slower than the 3-way split + folded finish: off
     int qkv_fold = 1;                // many-row steps: q / k / v partial tiles summed by their readers instead of a finish launch
     int attn_tail = 1;               // attn_tc_kernel: cut the units of the last, partial round of CTAs finer
     int attn_trace = 0;              // profiling: attn_tc_kernel writes 4 clock stamps per CTA into the mega_trace buffer
@@ -435,6 +437,17 @@ int rows_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, const bf16* W2
     const int NV = sw ? 2 * N : N;  // rows of the virtual weight matrix [W; W2]
     if (K % RG_BK || (NV + RG_BM - 1) / RG_BM > RG_MAX_TILES || (sw && (N % RG_BM || !pre || !W2))) return -1;
     if ((long long)((NV + RG_BM - 1) / RG_BM) * (K / RG_BK) * RG_GRID_MAX >= (1LL << 31)) return -1;  // 32-bit range arithmetic
+    const bool pdl0 = h->use_pdl != 0;
+    if (epi == RG_EPI_STORE && !all_partial && h->rows_narrow) {  // enough narrow weight tiles for one CTA per SM: no k split
+        const int nw = rgn_pick_nw(N, h->n_sm);
+        if (nw) {
+            const CUtensorMap* nW = rows_map(h, W, N, K, nw);
+            const CUtensorMap* nX = rows_map(h, X, M, K, 128);
+            if (!nW || !nX) return fail(h, "cuTensorMapEncodeTiled failed");
+            CK(rgn_launch(s, pdl0, *nW, *nX, M, N, K, nw, out));
+            return 0;
+        }
+    }
     const int bn = rg_bn_for(M);
     const CUtensorMap* mW = rows_map(h, W, N, K, RG_BM);
     const CUtensorMap* mW2 = W2 ? rows_map(h, W2, N, K, RG_BM) : mW;
@@ -540,7 +553,7 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
             // finish launch, whenever those kernels can (tile-aligned split; the CUDA-core slow attention cannot)
             const int qkv_tiles = (QKV + RG_BM - 1) / RG_BM;
             const bool qkv_part = (fast || (ak.tc && h->attn_tc)) && h->qkv_fold && qkv_tiles <= RG_CTAS_PER_SM * h->n_sm &&
-                                  QKV % RG_BM == 0;
+                                  QKV % RG_BM == 0 && !(h->rows_narrow && rgn_pick_nw(QKV, h->n_sm));
             a.qkv_part = nullptr;
             if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, h->qkv, nullptr, qkv_part)) return r;
             if (qkv_part) {
@@ -1074,6 +1087,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "attn_trace") h->attn_trace = (int)value;
     else if (n == "attn_tail") h->attn_tail = (int)value;
     else if (n == "qkv_fold") h->qkv_fold = (int)value;
+    else if (n == "rows_narrow") h->rows_narrow = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
     else return fail(h, "unknown option " + n);
@@ -1393,6 +1407,14 @@ int fsb_rows_gemm(const void* W, const void* W2, const void* x, const void* res,
     if (e != cudaSuccess) return 4;
     e = rg_finish_tiles(s, false, n_sm, M, NV, K, epi, partial, sw ? pre : (const bf16*)out, (const bf16*)res, (bf16*)out);
     return e == cudaSuccess ? 0 : 4;
+}
+
+int fsb_rows_gemm_narrow(const void* W, const void* x, void* out, int32_t M, int32_t N, int32_t K, int32_t nw, void* stream) {
+    if (!W || !x || !out || M < 1 || M > 128 || K < RG_BK || K % RG_BK || nw < 16 || nw > 64 || nw % 16 || N < nw || N % nw) return 1;
+    CUtensorMap mW, mX;
+    if (!rg_make_map(&mW, W, (uint64_t)N, (uint64_t)K, (uint32_t)nw)) return 3;
+    if (!rg_make_map(&mX, x, (uint64_t)M, (uint64_t)K, 128)) return 3;
+    return rgn_launch((cudaStream_t)stream, false, mW, mX, M, N, K, nw, (bf16*)out) == cudaSuccess ? 0 : 4;
 }
 
 int fsb_sample(const void* logits, const void* bias, int32_t B, int32_t V, int32_t top_k, float temperature, float top_p,

@@ -298,6 +298,140 @@ rows_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
     }
 }
 
+// ----------------------------------------------------------------------------- narrow weight tiles, no k split
+// Mid-size Linears (wqkv: 6144 rows, fast head: 4096) have too few 128-row weight tiles for 148 SMs, and a k split costs
+// partial-tile traffic plus a finish.  Here the operands are swapped: the ACTIVATION rows are the MMA's A operand (M = 128
+// TMEM lanes = batch rows; rows past the batch are TMA out-of-bounds zero fill and cost no traffic) and the weight tile is
+// the B operand, whose height NW only has to be a multiple of 16 - 48 rows give 128 CTAs for wqkv, each streaming its rows
+// over the whole K with no split, no partials and a direct bf16 store (what cuBLAS picks for this shape, 9.4 us vs 12.8 us
+// + finish for the 3-way split).  Price: an 8 KB activation block from L2 per 6 KB weight block - and that price decided
+// it: measured in the step, this kernel for wqkv and the fast head is 3 % SLOWER than the 3-way split whose partial tiles
+// are summed by the readers of q / k / v (10.54 vs 10.23 ms per step), so it is off by default (option rows_narrow).
+//   D[m][n_local] (fp32, TMEM, 128 lanes x NW columns) += X[m][k] * W[n0 + n_local][k]
+#define RGN_STAGES 8
+#define RGN_STAGE_BYTES (16384 + 8192)  // X block 128 x 128 B | W block (<= 64 rows x 128 B)
+struct RowsGemmNArgs {
+    bf16* out;   // [M][N]
+    int M, N, K, nw, kb;
+};
+__global__ void __launch_bounds__(RG_THREADS, 1)
+rows_gemm_narrow_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, RowsGemmNArgs a) {
+    extern __shared__ uint8_t rgn_smem_raw[];
+    __shared__ uint64_t full_bar[RGN_STAGES], empty_bar[RGN_STAGES], tfull_bar;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t sbase = (smem_u32(rgn_smem_raw) + 1023u) & ~1023u;
+    const int n0 = blockIdx.x * a.nw;
+    const uint32_t stage_tx = 16384u + (uint32_t)a.nw * 128u;
+    if (tid == 0) {
+        for (int s = 0; s < RGN_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&tfull_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(64) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+    pdl_launch_dependents();
+    if (warp == 0) {
+        if (lane == 0) {
+            rg_prefetch_map(&tmW);
+            rg_prefetch_map(&tmX);
+            const int npre = a.kb < RGN_STAGES ? a.kb : RGN_STAGES;
+            for (int i = 0; i < npre; ++i) {  // weights first: they do not depend on the previous kernel
+                mbar_expect_tx(&full_bar[i], stage_tx);
+                rg_tma_load_2d(sbase + (uint32_t)i * RGN_STAGE_BYTES + 16384, &tmW, smem_u32(&full_bar[i]), i * RG_BK, n0, RG_POLICY_EVICT_FIRST);
+            }
+            pdl_wait();
+            for (int i = 0; i < npre; ++i)
+                rg_tma_load_2d(sbase + (uint32_t)i * RGN_STAGE_BYTES, &tmX, smem_u32(&full_bar[i]), i * RG_BK, 0, RG_POLICY_EVICT_LAST);
+            for (int i = npre; i < a.kb; ++i) {
+                const int s = i % RGN_STAGES;
+                mbar_wait(&empty_bar[s], ((uint32_t)(i / RGN_STAGES) & 1u) ^ 1u);
+                const uint32_t st = sbase + (uint32_t)s * RGN_STAGE_BYTES, bar = smem_u32(&full_bar[s]);
+                mbar_expect_tx(&full_bar[s], stage_tx);
+                rg_tma_load_2d(st + 16384, &tmW, bar, i * RG_BK, n0, RG_POLICY_EVICT_FIRST);
+                rg_tma_load_2d(st, &tmX, bar, i * RG_BK, 0, RG_POLICY_EVICT_LAST);
+            }
+        }
+    } else if (warp == 1) {
+        const uint32_t idesc = tc_idesc_bf16(a.nw);  // M = 128 (batch rows), N = nw (weight rows)
+        for (int i = 0; i < a.kb; ++i) {
+            const int s = i % RGN_STAGES;
+            mbar_wait(&full_bar[s], (uint32_t)(i / RGN_STAGES) & 1u);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint32_t st = sbase + (uint32_t)s * RGN_STAGE_BYTES;
+                const uint64_t adesc = tc_smem_desc(st), bdesc = tc_smem_desc(st + 16384);
+#pragma unroll
+                for (int k = 0; k < RG_BK / 16; ++k) tc_mma_bf16(tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (i > 0 || k > 0) ? 1u : 0u);
+                tc_commit(&empty_bar[s]);
+            }
+            __syncwarp();
+        }
+        if (lane == 0) tc_commit(&tfull_bar);
+        __syncwarp();
+    } else {
+        // epilogue: TMEM lane = batch row; warps 4, 5 own lanes 0-63, warps 2, 3 lanes 64-127 (rows 64.. only when M > 64)
+        const int lg = warp & 3, m = lg * 32 + lane;
+        pdl_wait();
+        mbar_wait(&tfull_bar, 0);
+        tc_fence_after();
+        if (lg * 32 < a.M) {
+            const uint32_t tacc = tmem + ((uint32_t)(lg * 32) << 16);
+            for (int ch = 0; ch < a.nw / 16; ++ch) {
+                float v[16];
+                tc_ld16(tacc + (uint32_t)(ch * 16), v);
+                if (m < a.M) {
+                    uint4 o0, o1;
+                    o0.x = pack2(v[0], v[1]); o0.y = pack2(v[2], v[3]); o0.z = pack2(v[4], v[5]); o0.w = pack2(v[6], v[7]);
+                    o1.x = pack2(v[8], v[9]); o1.y = pack2(v[10], v[11]); o1.z = pack2(v[12], v[13]); o1.w = pack2(v[14], v[15]);
+                    uint4* dst = reinterpret_cast<uint4*>(a.out + (size_t)m * a.N + n0 + ch * 16);
+                    dst[0] = o0; dst[1] = o1;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(64) : "memory");
+    }
+}
+inline size_t rgn_smem_bytes() { return (size_t)RGN_STAGES * RGN_STAGE_BYTES + 1024; }
+// weight-tile height for a no-split launch: a multiple of 16 that divides N, N >= 16-byte aligned rows, and gives between
+// 0.8 and 1.0 CTAs per SM; 0 if there is none (then the 128-row stream-K kernel is used)
+inline int rgn_pick_nw(int N, int n_sm) {
+    for (int nw = 64; nw >= 16; nw -= 16) {
+        if (N % nw) continue;
+        const int ctas = N / nw;
+        if (ctas <= n_sm && ctas * 5 >= n_sm * 4) return nw;
+    }
+    return 0;
+}
+inline cudaError_t rgn_launch(cudaStream_t s, bool pdl, const CUtensorMap& mW, const CUtensorMap& mX, int M, int N, int K, int nw, bf16* out) {
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute((const void*)rows_gemm_narrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rgn_smem_bytes());
+        if (e != cudaSuccess) return e;
+        attr = true;
+    }
+    RowsGemmNArgs a{};
+    a.out = out; a.M = M; a.N = N; a.K = K; a.nw = nw; a.kb = K / RG_BK;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(N / nw); cfg.blockDim = dim3(RG_THREADS); cfg.dynamicSmemBytes = rgn_smem_bytes(); cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, rows_gemm_narrow_kernel, mW, mX, a);
+}
+
 // ----------------------------------------------------------------------------- finish of split tiles
 // rows_gemm_kernel leaves every tile whose k range is shared by several CTAs as fp32 partial tiles.  The finish is a
 // separate, embarrassingly parallel pass (a last-arriver fix-up inside the GEMM put 10-25 us of serial L2 round trips on

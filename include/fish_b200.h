@@ -120,6 +120,9 @@ int fsb_gemv(const void* W, const void* W2, const void* x, const void* norm_w, c
 size_t fsb_rows_gemm_scratch_bytes(void);
 int fsb_rows_gemm(const void* W, const void* W2, const void* x, const void* res, void* out, int32_t M, int32_t N,
                   int32_t K, int32_t epi, void* scratch, size_t scratch_bytes, void* stream);
+/* The same Linear with a plain store on narrow weight tiles (nw = 16/32/48/64 rows per CTA, N % nw == 0) and no k split:
+ * activations as the MMA's A operand, weights as the B operand (csrc/rows_gemm.cuh, rows_gemm_narrow_kernel). */
+int fsb_rows_gemm_narrow(const void* W, const void* x, void* out, int32_t M, int32_t N, int32_t K, int32_t nw, void* stream);
 /* sample() of inference.py:80-93 on device. logits bf16 [B][V]; uniforms bf16 [B][n_variants][V] or NULL;
  * out int32 [B][2]: the index drawn with (temperature, top_p) and, if n_variants == 2, with (temp2, top_p2). */
 int fsb_sample(const void* logits, const void* bias, int32_t B, int32_t V, int32_t top_k, float temperature,

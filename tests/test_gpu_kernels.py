@@ -194,3 +194,21 @@ def test_rows_gemm_lm_head_shape(lib):
     ref = _rows_ref(W, x)
     err = (got.float() - ref.float()).abs()
     assert int((err > ref.float().abs() * 2.0 ** -7 + 2e-3).sum()) == 0, float(err.max())
+
+
+@pytest.mark.parametrize("M,N,K,nw", [(64, 6144, 2560, 48), (12, 4096, 2560, 32), (100, 768, 512, 16), (64, 1024, 64, 64),
+                                      (1, 96, 128, 48), (128, 6144, 2560, 48), (33, 4096, 9728, 32)])
+def test_rows_gemm_narrow_matches_fp32_reference(lib, M, N, K, nw):
+    """No-split variant (activations as the A operand, nw weight rows per CTA as the B operand)."""
+    g = torch.Generator().manual_seed(M * 17 + N + K + nw)
+    W = (torch.randn(N, K, generator=g) * 0.02).bfloat16().cuda()
+    x = torch.randn(M, K, generator=g).bfloat16().cuda()
+    out = torch.full((M, N), 7.0, dtype=torch.bfloat16, device="cuda")
+    rc = lib.fsb_rows_gemm_narrow(W.data_ptr(), x.data_ptr(), out.data_ptr(), M, N, K, nw, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+    ref = _rows_ref(W, x)
+    err = (out.float() - ref.float()).abs()
+    tol = ref.float().abs() * 2.0 ** -7 + 2e-3
+    print(f"[parity] rows_gemm_narrow M={M} N={N} K={K} nw={nw}: max-abs {float(err.max()):.5f}, exact {float((out == ref).float().mean()):.4f}")
+    assert int((err > tol).sum()) == 0, float(err.max())
