@@ -239,7 +239,7 @@ def measure_batched(dev, rank, world, batch=64, ctx=2048, frames=48, steps=2):
     torch.cuda.synchronize()
     ms_step = e0.elapsed_time(e1) / (steps * frames)
     ok = bool((sess.out_tokens[:frames, :, 1:] >= 0).all()) and bool((sess.out_tokens[:frames, :, 1:] < cfg.codebook_size).all())
-    fbytes = model.frame_bytes(batch, int((ctx + (frames - 1) / 2.0) * batch), masked_head=False)
+    fbytes = model.frame_bytes(batch, int((ctx + (frames - 1) / 2.0) * batch), masked_head=True)  # restricted LM head (V_eff rows)
     launches = model.launches_per_frame(batch)
     del sess, model
     torch.cuda.empty_cache()

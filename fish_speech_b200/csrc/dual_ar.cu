@@ -325,8 +325,9 @@ void head_rows(const fsb_dual_ar_desc& d, bool restricted, int* lo, int* n) {
     const int b = std::min(d.vocab, (std::max(d.im_end_id, d.semantic_end_id) + 1 + 7) & ~7);
     *lo = a; *n = b - a;
 }
+bool rows_tc_layers(const fsb_dual_ar* h, int M);
 bool head_restricted(const fsb_dual_ar* h, const fsb_frame_args& fa) {
-    return h->masked_head && fa.restrict_scan && fa.logit_bias && fa.batch == 1;
+    return h->masked_head && fa.restrict_scan && fa.logit_bias && (fa.batch == 1 || rows_tc_layers(h, fa.batch));
 }
 
 // sampling of the main (slow) token: two draws + RAS selection + code 0 (inference.py:118-155)
@@ -432,13 +433,13 @@ const CUtensorMap* rows_map(fsb_dual_ar* h, const void* ptr, int rows, int cols,
 // shape is not covered.  epi SWIGLU: W2 = up projection, `pre` = [M][2N] scratch for the pre-activation halves, out = [M][N].
 // all_partial = 1 leaves every tile as fp32 partials for rows_finish_norm (then `out` is not written here).
 int rows_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, const bf16* W2, const bf16* X, int M, int N, int K, int epi,
-                   const bf16* res, bf16* out, bf16* pre = nullptr, int all_partial = 0) {
+                   const bf16* res, bf16* out, bf16* pre = nullptr, int all_partial = 0, int ldo = 0) {
     const bool sw = epi == RG_EPI_SWIGLU;
     const int NV = sw ? 2 * N : N;  // rows of the virtual weight matrix [W; W2]
     if (K % RG_BK || (NV + RG_BM - 1) / RG_BM > RG_MAX_TILES || (sw && (N % RG_BM || !pre || !W2))) return -1;
     if ((long long)((NV + RG_BM - 1) / RG_BM) * (K / RG_BK) * RG_GRID_MAX >= (1LL << 31)) return -1;  // 32-bit range arithmetic
     const bool pdl0 = h->use_pdl != 0;
-    if (epi == RG_EPI_STORE && !all_partial && h->rows_narrow) {  // enough narrow weight tiles for one CTA per SM: no k split
+    if (epi == RG_EPI_STORE && !all_partial && h->rows_narrow && ldo == 0) {  // enough narrow weight tiles for one CTA per SM: no k split
         const int nw = rgn_pick_nw(N, h->n_sm);
         if (nw) {
             const CUtensorMap* nW = rows_map(h, W, N, K, nw);
@@ -456,8 +457,8 @@ int rows_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, const bf16* W2
     const bool pdl = h->use_pdl != 0;
     const int tiles_w = (N + RG_BM - 1) / RG_BM;
     CK(rg_launch(s, pdl, h->n_sm, *mW, *mW2, *mX, M, NV, tiles_w, K, sw ? RG_EPI_STORE : epi, res, sw ? pre : out, h->rg_partial,
-                 all_partial));
-    if (!all_partial) CK(rg_finish_tiles(s, pdl, h->n_sm, M, NV, K, epi, h->rg_partial, sw ? pre : out, res, out));
+                 all_partial, nullptr, sw ? 0 : ldo));
+    if (!all_partial) CK(rg_finish_tiles(s, pdl, h->n_sm, M, NV, K, epi, h->rg_partial, sw ? pre : out, res, out, sw ? 0 : ldo));
     return 0;
 }
 
@@ -593,8 +594,13 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
 
 // logits[M][N] = head . (RMSNorm(x) * norm_w); the normalised rows are kept in xnorm (the slow stack's `hidden`)
 int run_head_rows(fsb_dual_ar* h, cudaStream_t s, int M, const bf16* head, int N, const bf16* x, const bf16* norm_w,
-                  bf16* xnorm, bf16* logits) {
+                  bf16* xnorm, bf16* logits, int lo = 0, int n_rows = 0) {
     const fsb_dual_ar_desc& d = h->d;
+    if (n_rows > 0 && n_rows < N && rows_tc_layers(h, M)) {  // restricted LM head: rows [lo, lo + n_rows) of the weight, same columns of the logits
+        const int r = rows_linear_tc(h, s, head + (size_t)lo * d.dim, nullptr, xnorm, M, n_rows, d.dim, RG_EPI_STORE, nullptr, logits + lo,
+                                     nullptr, 0, N);
+        if (r >= 0) return r;
+    }
     // on the tcgen05 path the layer stack's last finish pass has already produced the normalised rows (tail norm)
     if (!rows_tc_layers(h, M)) rmsnorm_rows_kernel<<<M, 256, 0, s>>>(x, norm_w, xnorm, d.dim, d.norm_eps);
     if (rows_tc_active(h, M)) {
@@ -675,7 +681,11 @@ int run_slow_step(fsb_dual_ar* h, cudaStream_t s, int M, const int32_t* tokens, 
     const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
     if (!head || !h->norm) return fail(h, "LM head / final norm not bound");
     if (int r = run_layers(h, s, false, M, h->x2, pos, slots, true, -1, h->norm, h->hidden)) return r;
-    if (batch_gemm_active(h, M)) return run_head_rows(h, s, M, head, d.vocab, h->x, h->norm, h->hidden, h->slow_logits);
+    if (batch_gemm_active(h, M)) {
+        int lo = 0, n = d.vocab;
+        head_rows(d, restricted_head, &lo, &n);
+        return run_head_rows(h, s, M, head, d.vocab, h->x, h->norm, h->hidden, h->slow_logits, lo, n);
+    }
     int lo = 0, n = d.vocab;
     head_rows(d, restricted_head && M == 1, &lo, &n);
     CK(run_gemv(h->gc, h->use_pdl != 0, s, M, n, d.dim, PRO_RMSNORM, EPI_STORE, head + (size_t)lo * d.dim,
@@ -1324,7 +1334,7 @@ double fsb_dual_ar_frame_bytes(const fsb_dual_ar* h, int32_t batch, int64_t ctx_
     const double D = d.dim, HD = d.head_dim, H = d.n_head, KV = d.n_kv_head, F = d.ffn, C = d.num_codebooks;
     const double p_layer = D * (H + 2 * KV) * HD + H * HD * D + 3 * D * F;
     int hl = 0, hn = d.vocab;
-    head_rows(d, masked_head != 0 && h->masked_head && batch == 1, &hl, &hn);
+    head_rows(d, masked_head != 0 && h->masked_head && (batch == 1 || rows_tc_layers(h, batch)), &hl, &hn);
     const double v_eff = hn;  // rows the fused frame's LM head streams (4136 of 155776 at the S2 ids when restricted)
     double bytes = 2.0 * (d.n_layer * p_layer + v_eff * D) + 2.0 * (C * d.n_fast_layer * p_layer + (C - 1) * d.codebook_size * D);
     bytes += (double)ctx_sum * 2.0 * d.n_layer * 2.0 * KV * HD;

@@ -47,6 +47,7 @@ struct RowsGemmArgs {
     const bf16* res;   // [M][N] residual (RG_EPI_RESIDUAL), may alias out
     float* partial;    // [grid][2][BN][128] fp32 partial tiles of the stream-K split
     int M, N, K, epi;
+    int ldo;           // row stride of out / res in elements (N, or the full width when the launch covers a column range)
     int n_tiles, kb;   // tiles of 128 weight rows over W then W2, k blocks of 64
     int tiles_w;       // tiles that belong to W (the rest index W2)
     int nst;           // ring depth of this launch
@@ -277,7 +278,7 @@ rows_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant_
                     for (int j = 0; j < 16; ++j) {
                         const int m = ch * 16 + j;
                         if (m >= a.M) break;
-                        const size_t oi = (size_t)m * a.N + n;
+                        const size_t oi = (size_t)m * a.ldo + n;
                         const float o = (a.epi == RG_EPI_RESIDUAL) ? lda(&a.res[oi]) + rbf(v[j]) : v[j];
                         a.out[oi] = __float2bfloat16_rn(o);
                     }
@@ -447,7 +448,7 @@ struct RowsFinishTilesArgs {
     const bf16* pre;   // [M][N] bf16 outputs of whole tiles (SwiGLU mode input; aliases out in the other modes)
     const bf16* res;
     bf16* out;         // [M][N] (store / residual) or [M][N/2] (SwiGLU)
-    int M, N, bn, G, kb, n_tiles, mode;
+    int M, N, bn, G, kb, n_tiles, mode, ldo;  // ldo: row stride of out / res (store, residual modes)
 };
 __device__ __forceinline__ float rft_ld(const float* p) {  // volatile: the loads of one sum are issued back to back
     float v;
@@ -521,7 +522,7 @@ __global__ void __launch_bounds__(RG_BM) rows_finish_tiles_kernel(RowsFinishTile
 #pragma unroll
         for (int i = 0; i < RFT_ROWS; ++i) {
             if (m0 + i >= a.M) break;
-            const size_t oi = (size_t)(m0 + i) * a.N + n;
+            const size_t oi = (size_t)(m0 + i) * a.ldo + n;
             a.out[oi] = __float2bfloat16_rn(a.mode == RG_EPI_RESIDUAL ? lda(&a.res[oi]) + rbf(v[i]) : v[i]);
         }
         return;
@@ -685,11 +686,11 @@ inline cudaError_t rg_launch_pdl(void (*k)(Args), dim3 grid, dim3 block, cudaStr
 // holds rg_partial_bytes(RG_CTAS_PER_SM * n_sm, BN) bytes.  Split tiles are left for rg_finish_tiles / rows_finish_norm_kernel.
 inline cudaError_t rg_launch(cudaStream_t s, bool pdl, int n_sm, const CUtensorMap& mW, const CUtensorMap& mW2, const CUtensorMap& mX,
                              int M, int N, int tiles_w, int K, int epi, const bf16* res, bf16* out, float* partial, int all_partial,
-                             unsigned long long* trace = nullptr) {
+                             unsigned long long* trace = nullptr, int ldo = 0) {
     const int bn = rg_bn_for(M);
     RowsGemmArgs a{};
     a.out = out; a.res = res; a.partial = partial;
-    a.M = M; a.N = N; a.K = K; a.epi = epi;
+    a.M = M; a.N = N; a.K = K; a.epi = epi; a.ldo = ldo > 0 ? ldo : N;
     a.n_tiles = (N + RG_BM - 1) / RG_BM; a.kb = K / RG_BK; a.tiles_w = tiles_w; a.all_partial = all_partial; a.trace = trace;
     const int grid = rg_grid(a.n_tiles, a.kb, n_sm);
     a.nst = rg_stages_for(grid, n_sm, bn);
@@ -703,10 +704,10 @@ inline cudaError_t rg_launch(cudaStream_t s, bool pdl, int n_sm, const CUtensorM
 }
 // finish of the split tiles of the launch above (same M, N, K, n_sm); mode SWIGLU: pre = the GEMM's out, out = [M][N/2]
 inline cudaError_t rg_finish_tiles(cudaStream_t s, bool pdl, int n_sm, int M, int N, int K, int mode, const float* partial,
-                                   const bf16* pre, const bf16* res, bf16* out) {
+                                   const bf16* pre, const bf16* res, bf16* out, int ldo = 0) {
     RowsFinishTilesArgs f{};
     f.partial = partial; f.pre = pre; f.res = res; f.out = out;
-    f.M = M; f.N = N; f.bn = rg_bn_for(M); f.kb = K / RG_BK; f.n_tiles = (N + RG_BM - 1) / RG_BM; f.mode = mode;
+    f.M = M; f.N = N; f.bn = rg_bn_for(M); f.kb = K / RG_BK; f.n_tiles = (N + RG_BM - 1) / RG_BM; f.mode = mode; f.ldo = ldo > 0 ? ldo : N;
     f.G = rg_grid(f.n_tiles, f.kb, n_sm);
     const int gx = mode == RG_EPI_SWIGLU ? f.n_tiles / 2 : f.G - 1;
     if (gx < 1) return cudaSuccess;

@@ -102,7 +102,7 @@ def main():
         peak, src = measured_peaks()
         ms_step = ms / (args.steps * F)
         ctx_avg = args.ctx + (F - 1) / 2.0
-        fbytes = model.frame_bytes(B, int(ctx_avg * B), masked_head=False)
+        fbytes = model.frame_bytes(B, int(ctx_avg * B), masked_head=True)  # counts the LM-head rows the step actually streams
         out = {
             "workload": f"S2-Pro-shape Dual-AR batched decode, {B} requests/GPU x {world} GPU(s), {args.ctx}-token KV context, {F} frames",
             "batch_gemm": args.mode, "n_gpus": world, "audio_s_per_s": world * B * args.steps * F * FRAME_SEC / (ms / 1e3),
