@@ -246,6 +246,34 @@ def measure_batched(dev, rank, world, batch=64, ctx=2048, frames=48, steps=2):
     return ms_step, fbytes, launches, ok
 
 
+def measure_dac(dev, B=32, T=646, iters=2):
+    """BASELINE configs[3]: DAC codec decode of B clips x T code frames (30 s each) -> 44.1 kHz waveform, synthetic weights
+    and codes; the step includes the H2D of the codes (int64 [B][10][T]) - the waveform stays on the device.
+    Returns (ms per decode, audio seconds per decode, GEMM-shaped FLOPs per decode, finite)."""
+    import torch
+    from fish_speech_b200.dac import DACB200, DACConfig, synthetic_state_dict
+    cfg = DACConfig()
+    m = DACB200(cfg, synthetic_state_dict(cfg, 0), device=dev, max_batch=4, max_frames=max(T, 8))
+    g = torch.Generator().manual_seed(2)
+    codes = torch.randint(0, cfg.codebook_size, (B, cfg.n_codebooks + 1, T), generator=g)
+    codes[:, 0] = torch.randint(0, cfg.semantic_codebook_size, (B, T), generator=g)
+    codes = codes.pin_memory()
+    for _ in range(2):
+        wav = m.from_indices(codes.to(dev, non_blocking=True))
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        wav = m.from_indices(codes.to(dev, non_blocking=True))
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    out = (ms, B * T * cfg.hop / cfg.sample_rate, m.flops(B, T), bool(torch.isfinite(wav).all()))
+    del m, wav
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -346,12 +374,18 @@ def run_ours(args):
         del sess, model
         torch.cuda.empty_cache()
         b64 = measure_batched(dev, rank, world, batch=args.batch, ctx=args.batch_ctx, frames=args.batch_frames)
-    tms = torch.tensor([ms, e2e_t, b64[0] if b64 else 0.0], dtype=torch.float64, device=dev)
+    dac = None
+    if not args.no_dac:
+        try:
+            dac = measure_dac(dev)
+        except Exception as e:  # the Dual-AR numbers stand on their own
+            dac = e
+    tms = torch.tensor([ms, e2e_t, b64[0] if b64 else 0.0, dac[0] if isinstance(dac, tuple) else 0.0], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(args.steps * F), float(e2e_frames)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    ms_max, e2e_t_max, b64_ms_max = float(tms[0]), float(tms[1]), float(tms[2])
+    ms_max, e2e_t_max, b64_ms_max, dac_ms_max = float(tms[0]), float(tms[1]), float(tms[2]), float(tms[3])
     total_frames, total_e2e_frames = float(cnt[0]), float(cnt[1])
     if rank != 0:
         if world > 1:
@@ -413,6 +447,16 @@ def run_ours(args):
                          "note": "algorithmic weight + KV bytes of one step for all requests (SURVEY §8d) / CUDA-event step time; "
                                  "kernels: rows_gemm_kernel (tcgen05 stream-K), attn_tc_kernel, finish kernels"},
         }
+    if isinstance(dac, tuple):
+        pk = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
+        tpeak = float(pk.get("bf16_tflops_sustained", pk.get("bf16_tflops", 1375.8)))
+        tf = dac[2] / (dac_ms_max * 1e-3) / 1e12
+        line["dac"] = {"workload": "DAC codec decode, 32 clips x 646 code frames (30 s) per GPU x %d GPU(s) -> 44.1 kHz (BASELINE configs[3])" % world,
+                       "value": world * dac[1] / (dac_ms_max * 1e-3), "unit": "audio-s/s", "ms_per_step": dac_ms_max, "finite": dac[3],
+                       "roofline": {"bound": "tensor", "achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak,
+                                    "note": "TF32 mma.sync implicit-GEMM conv (csrc/dac_kernels.cuh) against the measured bf16 tensor peak"}}
+    elif dac is not None:
+        line["dac"] = {"error": str(dac)}
     if not args.no_cpu and world >= 1:
         try:
             v, cores, sample, _ = cpu_reference_leg(args.ref_frames)
@@ -435,6 +479,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the config-3 (bs64) section")
+    ap.add_argument("--no-dac", action="store_true", help="skip the config-4 (DAC decode) section")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--batch-ctx", type=int, default=2048)
     ap.add_argument("--batch-frames", type=int, default=48)
