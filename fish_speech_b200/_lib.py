@@ -52,6 +52,7 @@ EXPORTS = {
     "fsb_dual_ar_fast_step": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "fsb_dual_ar_buffer": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "fsb_dual_ar_decode_frames": (C.c_int, [C.c_void_p, C.POINTER(FrameArgs), C.c_int32, C.c_void_p]),
+    "fsb_dual_ar_device_error": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]),
     "fsb_dual_ar_frame_bytes": (C.c_double, [C.c_void_p, C.c_int32, C.c_int64, C.c_int32]),
     "fsb_dual_ar_launches_per_frame": (C.c_int32, [C.c_void_p, C.c_int32]),
     "fsb_gemv": (C.c_int, [C.c_void_p] * 6 + [C.c_int32] * 5 + [C.c_float, C.c_void_p]),

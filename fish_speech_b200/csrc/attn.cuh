@@ -217,6 +217,10 @@ struct AttnArgs {
     int qkv_s, qkv_bn;
 };
 
+// position of row m, kept inside the bound cache: a position past the end (the reference raises an index error there,
+// llama.py:205-214; the host mirror raises ValueError before the launch) must never scatter K/V outside the buffer
+__device__ __forceinline__ int attn_pos(const AttnArgs& a, int m) { return max(0, min(a.pos[m], a.S - 1)); }
+
 // ----------------------------------------------------------------------------- prompt rows: k-norm + RoPE + scatter
 template <int HD>
 __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
@@ -226,7 +230,7 @@ __global__ void __launch_bounds__(64) rope_append_kernel(AttnArgs a) {
     pdl_launch_dependents();
     constexpr int EPL = HD / 32;
     const int h = blockIdx.x, m = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int pos = a.pos[m];
+    const int pos = attn_pos(a, m);
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const size_t co = (((size_t)slot * a.KV + h) * a.S + pos) * HD;
@@ -272,7 +276,7 @@ __device__ __forceinline__ void attn_decode_body(const AttnArgs& a, int split, i
 
     const int lane = tid & 31, warp = tid >> 5;
 
-    const int pos = a.pos[m];
+    const int pos = attn_pos(a, m);
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const bf16* row = a.qkv + (size_t)m * qkv_w;
@@ -562,7 +566,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 3) attn_tc_kernel(AttnArgs a) {
     const int g = lane >> 2, q = lane & 3;
     unsigned long long* tr = a.trace ? a.trace + 4 * (size_t)blockIdx.x : nullptr;
     if (tr && tid == 0) tr[0] = clock64();
-    const int pos = a.pos[m];
+    const int pos = attn_pos(a, m);
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const bf16* row = a.qkv + (size_t)m * qkv_w;
@@ -793,7 +797,7 @@ struct AttnSplitSmem {
 // behind the weight stream's outstanding bulk copies (~4 us under load), so the item's KV range is pulled in a layer ahead
 template <int HD>
 __device__ __forceinline__ void attn_split_prefetch(const AttnArgs& a, const bf16* kc, const bf16* vc, int split, int h, int m) {
-    const int pos = a.pos[m];
+    const int pos = attn_pos(a, m);
     const int slot = a.slots ? a.slots[m] : m;
     const int per = (pos + 1 + a.splits - 1) / a.splits;
     const int k0 = split * per, k1 = min(pos, k0 + per);
@@ -816,7 +820,7 @@ __device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem
     const int lane = tid & 31, warp = tid >> 5;
     const int kslot = tid / LPK, chunk = tid % LPK;
 
-    const int pos = a.pos[m];
+    const int pos = attn_pos(a, m);
     const int slot = a.slots ? a.slots[m] : m;
     const int qkv_w = (a.H + 2 * a.KV) * HD;
     const uint32_t* row_t = a.qkv_t + (size_t)m * qkv_w;
@@ -1024,7 +1028,8 @@ __device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem
         long long t0 = 0;
         for (int i = tid; i < a.splits * GQ * 2; i += ASP_THREADS) {
             float v;
-            while (!ld_ll64_try(a.ll_ml + b0 * GQ * 2 + i, ptag, v)) spin_watchdog(spins, t0);
+            while (!ld_ll64_try(a.ll_ml + b0 * GQ * 2 + i, ptag, v))
+                if (spin_watchdog(spins, t0, FSB_ERR_PARTIAL_WAIT)) break;
             mlbuf[i] = v;
         }
     }
@@ -1042,7 +1047,7 @@ __device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem
                 pv[s] = 0.f;
                 if (has && s < a.splits) ok &= ld_ll64_try(a.ll_acc + (b0 + s) * GQ * HD + e, ptag, pv[s]);
             }
-            if (!ok) spin_watchdog(spins, t0);
+            if (!ok && spin_watchdog(spins, t0, FSB_ERR_PARTIAL_WAIT)) break;
         } while (!ok);
     }
     if (warp < GQ) {  // warp g, lane s: global max, weights exp(m_s - M), sum(w_s l_s) — a serial loop on one thread

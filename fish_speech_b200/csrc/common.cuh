@@ -4,6 +4,20 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+#include <set>
+#include <utility>
+// Function attributes (dynamic shared memory opt-in) are per device: one-time setup is keyed by (current device, key) so
+// that a thread-per-GPU host sets them on every device it uses.  true = first call for this key on the current device.
+inline bool fsb_first_on_device(int key) {
+    static std::mutex mu;
+    static std::set<std::pair<int, int>> seen;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return true;
+    std::lock_guard<std::mutex> lock(mu);
+    return seen.insert(std::make_pair(dev, key)).second;
+}
+
 #ifndef __CUDA_ARCH__
 #define FSB_ARCH_OK 1
 #elif __CUDA_ARCH__ >= 1000
@@ -145,8 +159,24 @@ __device__ __forceinline__ int lda(const int* p) { return __ldcg(p); }
 // expected tag also sees the value: producers need no fence and no flag, consumers spin on the data they have to
 // load anyway.  This replaces "fence + grid barrier + reload" between dependent ops (the same idea as the
 // low-latency protocol of collective libraries).
-// poll back-off in ns (tunable at handle creation: env FSB_SPIN_NS)
+// poll back-off in ns (tunable per device: option "spin_ns")
 static __device__ unsigned fsb_spin_ns = 100;
+// Watchdog word: a wait that outlives FSB_WATCHDOG_CLOCKS (a lost producer, a protocol bug) records a code here and
+// gives up; once it is non-zero every other wait of the launch gives up at its next check, so the kernel drains and
+// ends normally with garbage results instead of hanging the GPU or killing the context with a trap.  The host reads and
+// clears it (fsb_dual_ar_device_error) and reports it through *_last_error.
+static __device__ unsigned fsb_dev_error = 0;
+#define FSB_WATCHDOG_CLOCKS 4000000000LL
+enum { FSB_ERR_TAG_WAIT = 1, FSB_ERR_MBAR_WAIT = 2, FSB_ERR_GRID_WAIT = 3, FSB_ERR_RING_WAIT = 4, FSB_ERR_PARTIAL_WAIT = 5 };
+// called every `mask + 1` failed polls; true = stop waiting
+__device__ __forceinline__ bool fsb_watchdog(unsigned& spins, long long& t0, unsigned mask, unsigned code) {
+    if ((++spins & mask) != 0) return false;
+    if (*(volatile unsigned*)&fsb_dev_error != 0) return true;
+    if (t0 == 0) { t0 = clock64(); return false; }
+    if (clock64() - t0 <= FSB_WATCHDOG_CLOCKS) return false;
+    atomicCAS(&fsb_dev_error, 0u, code);
+    return true;
+}
 __device__ __forceinline__ void st_tagged(uint32_t* p, float v, unsigned tag) {
     const uint32_t w = (tag << 16) | (uint32_t)f_to_bf16_bits(v);
     asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
@@ -157,13 +187,11 @@ __device__ __forceinline__ void st_tagged4(uint32_t* p, uint32_t lo_pair, uint32
                  "r"(t | (lo_pair >> 16)), "r"(t | (hi_pair & 0xffffu)), "r"(t | (hi_pair >> 16))
                  : "memory");
 }
-__device__ __forceinline__ void spin_watchdog(unsigned& spins, long long& t0) {
-    // back off between polls: tens of thousands of threads polling the same L2 slices delay the very stores they wait for
+// back off between polls (tens of thousands of threads polling the same L2 slices delay the very stores they wait
+// for); true = the watchdog expired, stop waiting
+__device__ __forceinline__ bool spin_watchdog(unsigned& spins, long long& t0, unsigned code = FSB_ERR_TAG_WAIT) {
     __nanosleep(fsb_spin_ns);
-    if ((++spins & 0x3ffu) == 0) {  // a lost producer must fault, not hang the GPU
-        if (t0 == 0) t0 = clock64();
-        else if (clock64() - t0 > 4000000000LL) __trap();
-    }
+    return fsb_watchdog(spins, t0, 0x3ffu, code);
 }
 // 4 consecutive elements (16-byte aligned); returns them as two packed bf16 pairs once all four carry `tag`
 __device__ __forceinline__ uint2 ld_tagged4(const uint32_t* p, unsigned tag) {
@@ -173,7 +201,7 @@ __device__ __forceinline__ uint2 ld_tagged4(const uint32_t* p, unsigned tag) {
     for (;;) {
         asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(p) : "memory");
         if ((a >> 16) == tag && (b >> 16) == tag && (c >> 16) == tag && (d >> 16) == tag) break;
-        spin_watchdog(spins, t0);
+        if (spin_watchdog(spins, t0)) break;
     }
     return make_uint2((a & 0xffffu) | (b << 16), (c & 0xffffu) | (d << 16));
 }
@@ -191,7 +219,7 @@ __device__ __forceinline__ uint32_t ld_tagged2(const uint32_t* p, unsigned tag) 
     for (;;) {
         asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
         if ((a >> 16) == tag && (b >> 16) == tag) break;
-        spin_watchdog(spins, t0);
+        if (spin_watchdog(spins, t0)) break;
     }
     return (a & 0xffffu) | (b << 16);
 }

@@ -86,6 +86,7 @@ struct fsb_dual_ar {
                                      // (rows_gemm_narrow_kernel); measured slower than the 3-way split + folded finish: off
     int qkv_fold = 1;                // many-row steps: q / k / v partial tiles summed by their readers instead of a finish launch
     int attn_tail = 1;               // attn_tc_kernel: cut the units of the last, partial round of CTAs finer
+    int attn_trace_point = 0;        // profiling: which point of attn_split_body the frame kernel's trace records
     int attn_trace = 0;              // profiling: attn_tc_kernel writes 4 clock stamps per CTA into the mega_trace buffer
     int attn_tc = 1;                 // many-row steps: tensor-core decode attention (attn_tc_kernel) instead of attn_decode_kernel
     bool rg_ok = false;              // tensor-map encoder available, attributes set
@@ -159,8 +160,7 @@ gemv_fn pick_gemv(int M, int pro, int epi) {
 int m_bucket(int M) { return M <= 1 ? 1 : M <= 2 ? 2 : M <= 4 ? 4 : 8; }
 
 cudaError_t set_gemv_attrs() {
-    static bool done = false;
-    if (done) return cudaSuccess;
+    if (!fsb_first_on_device(0)) return cudaSuccess;
     const int ms[4] = {1, 2, 4, 8};
     for (int pro = 0; pro < 2; ++pro)
         for (int epi = 0; epi < 3; ++epi)
@@ -169,7 +169,6 @@ cudaError_t set_gemv_attrs() {
                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
                 if (e != cudaSuccess) return e;
             }
-    done = true;
     return cudaSuccess;
 }
 
@@ -192,8 +191,7 @@ gemv_tma_fn pick_gemv_tma(int M, int pro, int epi) {
     return pick_gemv_tma<PRO_NONE, EPI_SWIGLU>(M);
 }
 cudaError_t set_gemv_tma_attrs() {
-    static bool done = false;
-    if (done) return cudaSuccess;
+    if (!fsb_first_on_device(1)) return cudaSuccess;
     const int ms[4] = {1, 2, 4, 8};
     for (int pro = 0; pro < 2; ++pro)
         for (int epi = 0; epi < 3; ++epi)
@@ -202,7 +200,6 @@ cudaError_t set_gemv_tma_attrs() {
                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
                 if (e != cudaSuccess) return e;
             }
-    done = true;
     return cudaSuccess;
 }
 // largest KC <= limit that divides K and is a multiple of 8 (0 if none)
@@ -818,7 +815,7 @@ struct MegaBuilder {
             AttnArgs a = make_attn_args(h, w, fast, pos, slots, pos_fixed);
             a.splits = fast ? 1 : splits;
             a.qkv_t = t.qkv; a.y_t = t.y; a.ll_acc = h->ll_acc; a.ll_ml = h->ll_ml;
-            a.pf_ptr = nullptr; a.pf_bytes = getenv("FSB_ATTN_TRACE_POINT") ? (size_t)atoi(getenv("FSB_ATTN_TRACE_POINT")) : 0;
+            a.pf_ptr = nullptr; a.pf_bytes = (size_t)h->attn_trace_point;
             if (!fast && (&w - &L[0]) + 1 < (long)L.size()) { a.next_k = (&w)[1].kc; a.next_v = (&w)[1].vc; }
             if (d.qk_norm) { add_hot(w.q_norm, (size_t)HD * 2); add_hot(w.k_norm, (size_t)HD * 2); }
             if (fast) add_hot(h->fast_rope + (size_t)pos_fixed * HD, (size_t)HD * 2);
@@ -1041,7 +1038,6 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
     }
     CK(cudaMemset(h->mega_prof, 0, 16 * sizeof(unsigned long long)));
     if (h->rg_partial) h->rg_ok = h->n_sm <= RG_SM_MAX && rg_get_encode() != nullptr && rg_set_attrs() == cudaSuccess;
-    if (const char* e = getenv("FSB_BATCH_GEMM")) h->batch_gemm = atoi(e);
     if (mega_shape_ok(d)) {
         mega_fn mf = pick_mega(d.head_dim, d.n_head / d.n_kv_head);
         int coop = 0, occ = 0;
@@ -1050,20 +1046,22 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)mf, MG_THREADS, MG_SMEM));
         h->mega_supported = coop && occ >= 1;
     }
-    if (const char* e = getenv("FSB_MEGA")) h->use_mega = atoi(e);
-    if (const char* e = getenv("FSB_SPIN_NS")) {
-        const unsigned ns = (unsigned)atoi(e);
-        CK(cudaMemcpyToSymbol(fsb_spin_ns, &ns, sizeof(ns)));
-    }
     h->slow.resize(d.n_layer);
     h->fast.resize(d.n_fast_layer);
-    if (const char* e = getenv("FSB_PDL")) h->use_pdl = atoi(e);
-    if (const char* e = getenv("FSB_GRAPH")) h->use_graph = atoi(e);
-    if (const char* e = getenv("FSB_SELF_PF_KB")) h->gc.self_pf = (size_t)atol(e) * 1024;
-    if (const char* e = getenv("FSB_GEMV_TMA")) h->gc.tma = atoi(e);
-    if (const char* e = getenv("FSB_GEMV_NST")) h->gc.nst = atoi(e);
-    if (const char* e = getenv("FSB_GEMV_CPS")) h->gc.ctas_per_sm = atoi(e);
-    if (const char* e = getenv("FSB_GEMV_STAGE_KB")) h->gc.stage_kb = atoi(e);
+    // the one environment hook: FSB_OPTIONS="name=value,name=value" is applied through fsb_dual_ar_set_option
+    if (const char* e = getenv("FSB_OPTIONS")) {
+        std::string all(e);
+        size_t i = 0;
+        while (i < all.size()) {
+            size_t j = all.find(',', i);
+            if (j == std::string::npos) j = all.size();
+            const std::string kv = all.substr(i, j - i);
+            const size_t eq = kv.find('=');
+            if (eq != std::string::npos && eq > 0)
+                if (fsb_dual_ar_set_option(h, kv.substr(0, eq).c_str(), atoll(kv.c_str() + eq + 1))) return 1;
+            i = j + 1;
+        }
+    }
     return 0;
 }
 
@@ -1100,6 +1098,11 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "rows_narrow") h->rows_narrow = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
+    else if (n == "attn_trace_point") h->attn_trace_point = (int)value;
+    else if (n == "spin_ns") {  // poll back-off of tagged-load spins on the current device
+        const unsigned ns = (unsigned)value;
+        if (cudaMemcpyToSymbol(fsb_spin_ns, &ns, sizeof(ns)) != cudaSuccess) return fail(h, "cudaMemcpyToSymbol(fsb_spin_ns) failed");
+    }
     else return fail(h, "unknown option " + n);
     h->cached_valid = false;
     return 0;
@@ -1328,6 +1331,21 @@ int fsb_dual_ar_decode_frames(fsb_dual_ar* h, const fsb_frame_args* args, int32_
     return 0;
 }
 
+int fsb_dual_ar_device_error(fsb_dual_ar* h, int32_t* code, void* stream) {
+    if (!h) return 1;
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    unsigned v = 0;
+    CK(cudaMemcpyFromSymbol(&v, fsb_dev_error, sizeof(v)));
+    if (code) *code = (int32_t)v;
+    if (v == 0) return 0;
+    const unsigned zero = 0;
+    CK(cudaMemcpyToSymbol(fsb_dev_error, &zero, sizeof(zero)));
+    static const char* what[] = {"", "activation tag", "shared-memory stage (mbarrier)", "grid barrier", "weight ring slot",
+                                 "split-attention partial"};
+    return fail(h, std::string("device watchdog: a wait for a ") + (v < 6 ? what[v] : "dependency") +
+                       " timed out; the results of that launch are invalid");
+}
+
 double fsb_dual_ar_frame_bytes(const fsb_dual_ar* h, int32_t batch, int64_t ctx_sum, int32_t masked_head) {
     if (!h) return 0;
     const fsb_dual_ar_desc& d = h->d;
@@ -1377,10 +1395,6 @@ int fsb_gemv(const void* W, const void* W2, const void* x, const void* norm_w, c
     cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     GemvCfg gc;
     gc.n_sm = n_sm;
-    if (const char* e = getenv("FSB_GEMV_TMA")) gc.tma = atoi(e);
-    if (const char* e = getenv("FSB_GEMV_NST")) gc.nst = atoi(e);
-    if (const char* e = getenv("FSB_GEMV_CPS")) gc.ctas_per_sm = atoi(e);
-    if (const char* e = getenv("FSB_GEMV_STAGE_KB")) gc.stage_kb = atoi(e);
     cudaError_t e = run_gemv(gc, false, (cudaStream_t)stream, M, N, K, pro, epi, (const bf16*)W,
                              (const bf16*)W2, (const bf16*)x, (const bf16*)norm_w, (const bf16*)res, (bf16*)out, nullptr,
                              eps, nullptr, 0);

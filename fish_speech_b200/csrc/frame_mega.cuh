@@ -95,10 +95,7 @@ __device__ __forceinline__ void mg_grid_sync(unsigned* ctr, unsigned& epoch, int
         long long t0 = 0;
         do {
             asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-            if (v < target && (++spins & 0x3ffu) == 0) {  // watchdog: a lost CTA must fault, not hang the GPU
-                if (t0 == 0) t0 = clock64();
-                else if (clock64() - t0 > 4000000000LL) __trap();
-            }
+            if (v < target && fsb_watchdog(spins, t0, 0x3ffu, FSB_ERR_GRID_WAIT)) break;  // a lost CTA must end, not hang the GPU
         } while (v < target);
         __threadfence();
     }
@@ -198,7 +195,7 @@ __device__ __forceinline__ void mg_producer(const MegaPlan& p, unsigned char* st
     unsigned round = 0, spins = 0;
     long long t0 = 0;
     while (cur.live) {
-        if (!mbar_test(&empty_bar[lane], (round & 1u) ^ 1u)) { spin_watchdog(spins, t0); continue; }
+        if (!mbar_test(&empty_bar[lane], (round & 1u) ^ 1u)) { if (spin_watchdog(spins, t0, FSB_ERR_RING_WAIT)) break; continue; }
         const bf16* src;
         uint32_t bytes;
         cur.stage(src, bytes);
@@ -302,7 +299,7 @@ __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stage
                 }
                 xv[i] = make_uint4(lo.x, lo.y, hi.x, hi.y);
             }
-            if (!ok) spin_watchdog(spins, t0);
+            if (!ok && spin_watchdog(spins, t0)) break;
         } while (!ok);
     }
     if (g.pro == PRO_RMSNORM) {

@@ -47,10 +47,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
             : "=r"(ok)
             : "r"(smem_u32(b)), "r"(parity)
             : "memory");
-        if (!ok && (++spins & 0xfffu) == 0) {  // watchdog: a protocol bug must fault, not hang the GPU
-            if (t0 == 0) t0 = clock64();
-            else if (clock64() - t0 > 4000000000LL) __trap();
-        }
+        if (!ok && fsb_watchdog(spins, t0, 0xfffu, FSB_ERR_MBAR_WAIT)) break;  // a protocol bug must end, not hang the GPU
     } while (!ok);
 }
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {

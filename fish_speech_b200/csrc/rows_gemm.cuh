@@ -416,11 +416,9 @@ inline int rgn_pick_nw(int N, int n_sm) {
     return 0;
 }
 inline cudaError_t rgn_launch(cudaStream_t s, bool pdl, const CUtensorMap& mW, const CUtensorMap& mX, int M, int N, int K, int nw, bf16* out) {
-    static bool attr = false;
-    if (!attr) {
+    if (fsb_first_on_device(3)) {
         cudaError_t e = cudaFuncSetAttribute((const void*)rows_gemm_narrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rgn_smem_bytes());
         if (e != cudaSuccess) return e;
-        attr = true;
     }
     RowsGemmNArgs a{};
     a.out = out; a.M = M; a.N = N; a.K = K; a.nw = nw; a.kb = K / RG_BK;
@@ -659,15 +657,13 @@ typedef void (*rows_gemm_fn)(const CUtensorMap, const CUtensorMap, const CUtenso
 inline rows_gemm_fn rg_pick(int bn) { return bn == 32 ? rows_gemm_kernel<32> : bn == 64 ? rows_gemm_kernel<64> : rows_gemm_kernel<128>; }
 inline int rg_bn_for(int M) { return M <= 32 ? 32 : M <= 64 ? 64 : 128; }
 inline cudaError_t rg_set_attrs() {
-    static bool done = false;
-    if (done) return cudaSuccess;
+    if (!fsb_first_on_device(2)) return cudaSuccess;
     const int bns[3] = {32, 64, 128};
     for (int i = 0; i < 3; ++i) {
         cudaError_t e = cudaFuncSetAttribute((const void*)rg_pick(bns[i]), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)rg_smem_bytes(bns[i], rg_stages_for(1, 1, bns[i])));
         if (e != cudaSuccess) return e;
     }
-    done = true;
     return cudaSuccess;
 }
 template <typename Args>

@@ -170,10 +170,15 @@ __device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, 
     int nfin_total;
     block_excl_scan<SY>(nfin, wsum, &nfin_total, tid);
     const int k_eff = min(min(a.top_k, SAMPLE_MAXK), nfin_total);
-    if (k_eff <= 0) {  // no finite logit at all: nothing sensible to sample
-        if (tid == 0 && a.tokens) a.tokens[(size_t)b * a.n_cols + a.out_col] = 0;
-        return;
-    }
+    // no finite logit at all: the reference's softmax is NaN everywhere and its argmax returns index 0; the token is
+    // still written through the common output section (code, EOS flag, the next fast-AR input row and its tag — a
+    // consumer of the persistent frame kernel waits for that row)
+    const bool degenerate = k_eff <= 0;
+    if (degenerate) {
+        if (warp != 0) return;
+        if (lane == 0) { sh_tok[0] = 0; sh_tok[1] = 0; }
+        __syncwarp();
+    } else {
     const float maxv = bf16_bits_to_f(key_to_bits(kmax));
 
     // ---- locate the 11-bit bin holding the k-th largest key (suffix scan from the top bin)
@@ -343,6 +348,7 @@ __device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, 
         if (lane == 0) sh_tok[v] = besti;
     }
     __syncwarp();
+    }  // !degenerate
 
     // ---- outputs
     int tok = sh_tok[0];

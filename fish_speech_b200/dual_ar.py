@@ -260,6 +260,8 @@ class DualARTransformerB200:
         B, C1, Tq = inp.shape
         if input_pos is None:
             input_pos = torch.arange(Tq, device=self.device)
+        if int(input_pos[-1]) >= self.max_seq_len or int(input_pos[0]) < 0:
+            raise ValueError(f"input_pos {int(input_pos[-1])} is outside the KV cache (max_seq_len {self.max_seq_len})")
         if Tq > 1:
             if B != 1:
                 raise ValueError("prompt pass supports batch 1 (reference: inference.py:284-288)")
@@ -336,10 +338,23 @@ class DecodeSession:
             logit_bias=_ptr(self.bias), restrict_scan=int(self.restrict_scan and self.bias is not None),
             temperature=temperature, top_p=top_p, top_k=top_k, uniforms=_ptr(self.uniforms), seed=self.seed)
 
-    def run(self, n_frames: int, temperature: float, top_p: float, top_k: int, use_ras: bool):
+    def run(self, n_frames: int, temperature: float, top_p: float, top_k: int, use_ras: bool,
+            pos_bound: Optional[int] = None):
+        """n_frames fused frames.  The reference's KVCache.update raises an index error past the end of the cache
+        (llama.py:205-214); here the positions are checked on the host BEFORE the launch: `pos_bound` = the largest
+        current position if the caller knows it, else it is read from the device (one small synchronising copy)."""
         m = self.model
+        hi = int(self.pos.max().item()) if pos_bound is None else int(pos_bound)
+        if hi + n_frames > m.max_seq_len:
+            raise ValueError(f"decode would write position {hi + n_frames - 1} past the KV cache (max_seq_len {m.max_seq_len})")
         a = self.args(temperature, top_p, top_k, use_ras)
         m._ck(m.lib.fsb_dual_ar_decode_frames(m._h, C.byref(a), n_frames, _stream()))
+
+    def check_device(self):
+        """Raises if a device-side watchdog expired since the last check (synchronises the stream)."""
+        m = self.model
+        code = C.c_int32(0)
+        m._ck(m.lib.fsb_dual_ar_device_error(m._h, C.byref(code), _stream()))
 
 
 def _as_bf16_float(v) -> float:
@@ -360,11 +375,14 @@ def make_semantic_logit_bias(model: DualARTransformerB200) -> Tensor:
 
 def _bias_is_standard(model: DualARTransformerB200, bias: Tensor) -> bool:
     """True when `bias` is exactly the constrained-decode bias of inference.py:308-320 (then the sampler may
-    scan only its finite support).  Checked once per tensor and cached on it."""
+    scan only its finite support).  Checked once per tensor content (data_ptr, in-place version counter) and cached."""
     key = "_fsb_standard"
-    if not hasattr(bias, key):
-        setattr(bias, key, bool(torch.equal(bias.reshape(-1), make_semantic_logit_bias(model).reshape(-1))))
-    return getattr(bias, key)
+    stamp = (bias.data_ptr(), bias._version, tuple(bias.shape))
+    cached = getattr(bias, key, None)
+    if cached is None or cached[0] != stamp:  # re-checked when the tensor was mutated in place or re-allocated
+        cached = (stamp, bool(torch.equal(bias.reshape(-1), make_semantic_logit_bias(model).reshape(-1))))
+        setattr(bias, key, cached)
+    return cached[1]
 
 
 def decode_one_token_ar(model: DualARTransformerB200, x: Tensor, input_pos: Tensor, temperature, top_p, top_k: int,
@@ -377,19 +395,22 @@ def decode_one_token_ar(model: DualARTransformerB200, x: Tensor, input_pos: Tens
     C1 = c.num_codebooks + 1
     x = x.reshape(1, C1, -1)
     Tq = x.shape[-1]
+    p_last = int(input_pos.reshape(-1)[-1])
+    if p_last >= model.max_seq_len or p_last - (Tq - 1) < 0:
+        raise ValueError(f"input_pos {p_last} is outside the KV cache (max_seq_len {model.max_seq_len})")
     if Tq > 1:
         model.prefill(x[0, :, :-1], int(input_pos[0]), 0)
     s = model.session(1, getattr(model, "_session_frames", 4096))
     if Tq > 1:  # a new generation starts: frame records (injected uniforms / Philox counters) restart at 0
         s.frame_counter.zero_()
     s.cur_tokens.copy_(x[0, :, -1].to(torch.int32).view(1, C1))
-    s.pos.fill_(int(input_pos[-1]))
+    s.pos.fill_(p_last)
     use_ras = previous_tokens is not None
     if use_ras:
         s.ras_window.copy_(previous_tokens[0].to(torch.int32).view(1, RAS_WIN_SIZE))
     s.bias = semantic_logit_bias.reshape(-1).to(device=model.device, dtype=torch.bfloat16).contiguous()
     s.restrict_scan = _bias_is_standard(model, semantic_logit_bias)
-    s.run(1, _as_bf16_float(temperature), _as_bf16_float(top_p), int(top_k), use_ras)
+    s.run(1, _as_bf16_float(temperature), _as_bf16_float(top_p), int(top_k), use_ras, pos_bound=p_last)
     return s.cur_tokens.view(C1, 1).clone()
 
 
@@ -403,9 +424,13 @@ def decode_n_tokens(model: DualARTransformerB200, cur_token: Tensor, input_pos: 
     C1 = c.num_codebooks + 1
     if num_new_tokens <= 0:
         return torch.zeros((C1, 0), dtype=torch.int32, device=model.device)
+    p0 = int(input_pos.reshape(-1)[-1])
+    if p0 < 0 or p0 + num_new_tokens > model.max_seq_len:  # the reference fails in KVCache.update (llama.py:205-214)
+        raise ValueError(f"decoding {num_new_tokens} frames from position {p0} exceeds the KV cache "
+                         f"(max_seq_len {model.max_seq_len})")
     s = model.session(1, max(num_new_tokens, getattr(model, "_session_frames", 0)))
     s.cur_tokens.copy_(cur_token.reshape(C1).to(torch.int32).view(1, C1))
-    s.pos.fill_(int(input_pos.reshape(-1)[-1]))
+    s.pos.fill_(p0)
     s.ras_window.zero_()  # previous_tokens = zeros((C+1, RAS_WIN_SIZE)) (inference.py:199-203)
     s.done.zero_()
     f0 = int(s.frame_counter.item())
@@ -418,10 +443,11 @@ def decode_n_tokens(model: DualARTransformerB200, cur_token: Tensor, input_pos: 
     n = 0
     while n < num_new_tokens:
         step = min(eos_poll, num_new_tokens - n)
-        s.run(step, T, P, K, True)
+        s.run(step, T, P, K, True, pos_bound=p0 + n)
         n += step
         if bool(s.done.any().item()):
             break
+    s.check_device()
     out = s.out_tokens[f0: f0 + n, 0, :]  # [n, C+1]
     hit = (out[:, 0] == c.im_end_id).nonzero()
     if hit.numel() > 0:

@@ -56,7 +56,9 @@ int fsb_dual_ar_bind_rope(fsb_dual_ar* h, int32_t is_fast, const void* table, in
 /* KVCache buffers, bf16 [max_batch][n_kv_head][max_seq][head_dim] (llama.py:196-214, setup_caches:707-721). */
 int fsb_dual_ar_bind_kv(fsb_dual_ar* h, int32_t is_fast, int32_t layer, void* k, void* v, int32_t max_batch,
                         int32_t max_seq);
-/* Options: "pdl" (0/1), "graph" (0/1), "self_prefetch_kb", "attn_splits" (0 = auto). */
+/* Options: "pdl" (0/1), "graph" (0/1), "self_prefetch_kb", "attn_splits" (0 = auto), "mega", "masked_head", "batch_gemm",
+ * "prefill_gemm", "spin_ns", ... — the full list with defaults is in DESIGN.md §2; every FSB_* environment override of
+ * round 1 is an option here (the environment is no longer read, except FSB_OPTIONS="name=value,..." applied at create). */
 int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value);
 
 /* Prompt pass over the slow stack: fills KV for positions [pos0, pos0+T) of `slot`; no logits.
@@ -100,6 +102,12 @@ typedef struct {
 
 /* n_frames back-to-back frames, no host synchronisation in between (CUDA graph replay when enabled). */
 int fsb_dual_ar_decode_frames(fsb_dual_ar* h, const fsb_frame_args* args, int32_t n_frames, void* stream);
+/* Device watchdog: a wait inside a kernel that outlived its limit (a lost producer; never seen on a healthy device)
+ * records a code and lets the launch drain instead of hanging or trapping.  This call SYNCHRONISES `stream`, reads and
+ * clears the word of the current device; returns 0 and *code = 0 when nothing happened, else 1 with the message in
+ * fsb_dual_ar_last_error (results of that launch are invalid).  The host mirror calls it where the reference's loop
+ * synchronises anyway (the <|im_end|> test, inference.py:233). */
+int fsb_dual_ar_device_error(fsb_dual_ar* h, int32_t* code, void* stream);
 
 /* Algorithmic HBM bytes of one frame (SURVEY.md §8d shared formula): weights + KV for `ctx_sum` = sum of
  * context lengths over the batch. masked_head = 1 counts the LM-head rows a fused batch-1 frame streams when the
