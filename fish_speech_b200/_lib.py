@@ -59,6 +59,7 @@ EXPORTS = {
     "fsb_rows_gemm_scratch_bytes": (C.c_size_t, []),
     "fsb_rows_gemm": (C.c_int, [C.c_void_p] * 5 + [C.c_int32] * 4 + [C.c_void_p, C.c_size_t, C.c_void_p]),
     "fsb_rows_gemm_narrow": (C.c_int, [C.c_void_p] * 3 + [C.c_int32] * 4 + [C.c_void_p]),
+    "fsb_rows_gemm_static": (C.c_int, [C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p, C.c_char_p, C.c_size_t]),
     "fsb_sample": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32,
                              C.c_float, C.c_float, C.c_void_p, C.c_uint64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                              C.c_void_p, C.c_void_p]),

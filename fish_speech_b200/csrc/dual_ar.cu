@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <tuple>
 #include <vector>
@@ -1431,6 +1432,82 @@ int fsb_rows_gemm(const void* W, const void* W2, const void* x, const void* res,
     if (e != cudaSuccess) return 4;
     e = rg_finish_tiles(s, false, n_sm, M, NV, K, epi, partial, sw ? pre : (const bf16*)out, (const bf16*)res, (bf16*)out);
     return e == cudaSuccess ? 0 : 4;
+}
+
+// ------------------------------------------------------------------------------------------- no-allocation variant
+// fsb_rows_gemm with its stream-K partial tiles in a file-scope device array instead of caller scratch, for callers that
+// cannot allocate (code under graph capture, serving loops, harnesses that forbid it).  Limit: M <= 32 rows, which bounds
+// the partial tiles at RG_GRID_MAX CTAs x 2 slots x 32 rows x 128 columns x 4 B = 10 MiB; every GPU that loads the library
+// holds those 10 MiB until exit.  The array's name is only a host-side stand-in in host code: its device address is looked
+// up once per device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.
+#define FSB_STATIC_ROWS_MAX 32
+#define FSB_STATIC_SCRATCH_BYTES ((size_t)RG_GRID_MAX * 2 * FSB_STATIC_ROWS_MAX * RG_BM * sizeof(float))
+static __device__ __align__(256) unsigned char fsb_static_scratch[FSB_STATIC_SCRATCH_BYTES];
+
+static int static_msg(char* err, size_t err_len, int rc, const std::string& m) {
+    if (err && err_len) snprintf(err, err_len, "%s", m.c_str());
+    return rc;
+}
+// device address of fsb_static_scratch on the CURRENT device, resolved once per device
+static cudaError_t static_scratch_ptr(void** out) {
+    static std::mutex mu;
+    static std::map<int, void*> ptrs;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = ptrs.find(dev);
+    if (it == ptrs.end()) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, fsb_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (p == nullptr) return cudaErrorInvalidSymbol;
+        it = ptrs.emplace(dev, p).first;
+    }
+    *out = it->second;
+    return cudaSuccess;
+}
+
+int fsb_rows_gemm_static(const void* W, const void* x, const void* res, void* out, int32_t M, int32_t N, int32_t K, int32_t epi,
+                         void* stream, char* err, size_t err_len) {
+    if (err && err_len) err[0] = 0;
+    if (!W || !x || !out) return static_msg(err, err_len, 1, "fsb_rows_gemm_static: W, x and out are required");
+    if (M < 1 || N < 1 || K < RG_BK || K % RG_BK)
+        return static_msg(err, err_len, 1, "fsb_rows_gemm_static: need M >= 1, N >= 1, K a positive multiple of 64");
+    if (M > FSB_STATIC_ROWS_MAX)
+        return static_msg(err, err_len, 1, "fsb_rows_gemm_static: M = " + std::to_string(M) + " rows exceeds the static scratch limit of " +
+                          std::to_string(FSB_STATIC_ROWS_MAX) + " rows (" + std::to_string(FSB_STATIC_SCRATCH_BYTES >> 20) +
+                          " MiB of partial tiles); use fsb_rows_gemm with caller scratch");
+    if (epi != RG_EPI_STORE && epi != RG_EPI_RESIDUAL)
+        return static_msg(err, err_len, 1, "fsb_rows_gemm_static: epi must be 0 (store) or 1 (residual); SwiGLU needs fsb_rows_gemm");
+    if (epi == RG_EPI_RESIDUAL && !res) return static_msg(err, err_len, 1, "fsb_rows_gemm_static: residual epilogue without res");
+    const int n_tiles = (N + RG_BM - 1) / RG_BM, kb = K / RG_BK;
+    if (n_tiles > RG_MAX_TILES || (long long)n_tiles * kb * RG_GRID_MAX >= (1LL << 31))
+        return static_msg(err, err_len, 1, "fsb_rows_gemm_static: N x K too large for the 32-bit stream-K range arithmetic");
+    int dev = 0, n_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+        return static_msg(err, err_len, 2, "fsb_rows_gemm_static: no current CUDA device");
+    if (n_sm > RG_SM_MAX) return static_msg(err, err_len, 2, "fsb_rows_gemm_static: device has more SMs than the scratch is sized for");
+    const size_t need = rg_partial_bytes(rg_grid(n_tiles, kb, n_sm), rg_bn_for(M));
+    if (need > FSB_STATIC_SCRATCH_BYTES)
+        return static_msg(err, err_len, 1, "fsb_rows_gemm_static: this shape needs " + std::to_string(need) + " bytes of partial tiles, the static scratch holds " +
+                          std::to_string(FSB_STATIC_SCRATCH_BYTES));
+    cudaError_t e = rg_set_attrs();
+    if (e != cudaSuccess) return static_msg(err, err_len, 2, std::string("fsb_rows_gemm_static: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    void* scratch = nullptr;
+    e = static_scratch_ptr(&scratch);
+    if (e != cudaSuccess) return static_msg(err, err_len, 2, std::string("fsb_rows_gemm_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    CUtensorMap mW, mX;
+    if (!rg_make_map(&mW, W, (uint64_t)N, (uint64_t)K, RG_BM) || !rg_make_map(&mX, x, (uint64_t)M, (uint64_t)K, (uint32_t)rg_bn_for(M)))
+        return static_msg(err, err_len, 3, "fsb_rows_gemm_static: cuTensorMapEncodeTiled failed (16-byte aligned pointers required)");
+    // nothing in the scratch has to start at zero: the GEMM writes every partial-tile element the finish pass reads (rows < M
+    // of the split tiles) before that pass runs, so the previous call's contents are never observed
+    float* partial = (float*)scratch;
+    cudaStream_t s = (cudaStream_t)stream;
+    e = rg_launch(s, false, n_sm, mW, mW, mX, M, N, n_tiles, K, epi, (const bf16*)res, (bf16*)out, partial, 0, nullptr);
+    if (e == cudaSuccess) e = rg_finish_tiles(s, false, n_sm, M, N, K, epi, partial, (const bf16*)out, (const bf16*)res, (bf16*)out);
+    if (e != cudaSuccess) return static_msg(err, err_len, 4, std::string("fsb_rows_gemm_static: launch failed: ") + cudaGetErrorString(e));
+    return 0;
 }
 
 int fsb_rows_gemm_narrow(const void* W, const void* x, void* out, int32_t M, int32_t N, int32_t K, int32_t nw, void* stream) {

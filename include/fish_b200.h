@@ -131,6 +131,16 @@ int fsb_rows_gemm(const void* W, const void* W2, const void* x, const void* res,
 /* The same Linear with a plain store on narrow weight tiles (nw = 16/32/48/64 rows per CTA, N % nw == 0) and no k split:
  * activations as the MMA's A operand, weights as the B operand (csrc/rows_gemm.cuh, rows_gemm_narrow_kernel). */
 int fsb_rows_gemm_narrow(const void* W, const void* x, void* out, int32_t M, int32_t N, int32_t K, int32_t nw, void* stream);
+/* No counterpart in the reference: added for callers that cannot allocate device
+ * memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The same Linear as
+ * fsb_rows_gemm (epi 0 store / 1 residual only) with the stream-K partial tiles in a file-scope device array of the library
+ * instead of caller scratch: it allocates nothing (no cudaMalloc / cudaFree / allocating library call).  Limit: M <= 32 rows
+ * (10 MiB of partial tiles, held by every GPU that loads the library until exit); larger M, SwiGLU or a shape whose partial
+ * tiles exceed 10 MiB are rejected with rc != 0 and a message in `err` (caller buffer of err_len bytes, may be NULL).
+ * All calls on a device share the one array: calls that overlap on the GPU (different streams) race; calls on one stream
+ * are ordered and need no clearing in between (every element read is written first by the same call). */
+int fsb_rows_gemm_static(const void* W, const void* x, const void* res, void* out, int32_t M, int32_t N, int32_t K,
+                         int32_t epi, void* stream, char* err, size_t err_len);
 /* sample() of inference.py:80-93 on device. logits bf16 [B][V]; uniforms bf16 [B][n_variants][V] or NULL;
  * out int32 [B][2]: the index drawn with (temperature, top_p) and, if n_variants == 2, with (temp2, top_p2). */
 int fsb_sample(const void* logits, const void* bias, int32_t B, int32_t V, int32_t top_k, float temperature,
