@@ -346,14 +346,7 @@ def run_ours(args):
     e2e_frames, e2e_t = 0, 0.0
     # same fixed-length workload as the device-resident leg: generate() builds its own constrained-decode bias
     # (inference.py:308-320); the <|im_end|> entry is masked here so every run decodes exactly F frames
-    import fish_speech_b200.dual_ar as _da
-    _real_bias = _da.make_semantic_logit_bias
-
-    def _bias_no_eos(m):
-        b = _real_bias(m)
-        b[0, 0, m.config.im_end_id] = float("-inf")
-        return b
-    _da.make_semantic_logit_bias = _bias_no_eos
+    model.ignore_eos = True  # supported switch (dual_ar.make_semantic_logit_bias): same restricted LM head / scan as the device-resident leg
     for it in range(1 + args.e2e_steps):
         barrier()
         t0 = time.perf_counter()
@@ -365,7 +358,7 @@ def run_ours(args):
         if it > 0:
             e2e_frames += host.shape[1] - PROMPT_T
             e2e_t += dt
-    _da.make_semantic_logit_bias = _real_bias
+    model.ignore_eos = False
     b64 = None
     if not args.no_batched:
         fb1 = model.frame_bytes(1, int(PROMPT_T + (F - 1) / 2.0), masked_head=True)

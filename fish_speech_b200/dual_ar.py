@@ -365,22 +365,40 @@ def _as_bf16_float(v) -> float:
 
 
 def make_semantic_logit_bias(model: DualARTransformerB200) -> Tensor:
-    """inference.py:308-320."""
+    """inference.py:308-320.  Extension: `model.ignore_eos = True` leaves <|im_end|> masked (-inf) so that a run decodes
+    exactly max_new_tokens frames (fixed-length benchmarking); default off = the reference's bias."""
     c = model.config
     b = torch.full((1, 1, c.vocab_size), float("-inf"), dtype=torch.bfloat16, device=model.device)
     b[0, 0, c.semantic_begin_id: c.semantic_end_id + 1] = 0.0
-    b[0, 0, model.tokenizer.get_token_id("<|im_end|>")] = 0.0
+    if not getattr(model, "ignore_eos", False):
+        b[0, 0, model.tokenizer.get_token_id("<|im_end|>")] = 0.0
     return b
 
 
 def _bias_is_standard(model: DualARTransformerB200, bias: Tensor) -> bool:
-    """True when `bias` is exactly the constrained-decode bias of inference.py:308-320 (then the sampler may
-    scan only its finite support).  Checked once per tensor content (data_ptr, in-place version counter) and cached."""
+    """True when `bias` has the support of the constrained-decode bias of inference.py:308-320: every entry outside
+    [semantic_begin, semantic_end] and <|im_end|> is -inf.  Then no token outside can ever be drawn, the sampler may scan
+    only that support and the fused frame may compute only those LM-head rows (the values INSIDE the support are free:
+    the sampler adds them itself).  Cached per tensor content (data_ptr, in-place version counter); tensors built under
+    inference_mode carry no version counter and are checked every time."""
+    def check() -> bool:
+        outside = getattr(model, "_bias_outside", None)
+        if outside is None:
+            c = model.config
+            outside = torch.ones(c.vocab_size, dtype=torch.bool, device=model.device)
+            outside[c.semantic_begin_id: c.semantic_end_id + 1] = False
+            outside[model.tokenizer.get_token_id("<|im_end|>")] = False
+            model._bias_outside = outside
+        flat = bias.reshape(-1).to(model.device)
+        return flat.numel() == outside.numel() and bool(torch.isneginf(flat[outside]).all())
+
+    if bias.is_inference():
+        return check()
     key = "_fsb_standard"
     stamp = (bias.data_ptr(), bias._version, tuple(bias.shape))
     cached = getattr(bias, key, None)
     if cached is None or cached[0] != stamp:  # re-checked when the tensor was mutated in place or re-allocated
-        cached = (stamp, bool(torch.equal(bias.reshape(-1), make_semantic_logit_bias(model).reshape(-1))))
+        cached = (stamp, check())
         setattr(bias, key, cached)
     return cached[1]
 

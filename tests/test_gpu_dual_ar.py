@@ -92,8 +92,11 @@ def test_greedy_free_run_vs_golden(tiny):
     assert seq.shape == g["seq"].shape and seq.dtype == g["seq"].dtype
     assert torch.equal(seq[:, : g["prompt"].shape[1]], g["prompt"])
     matched, n = compare_free_run(seq, g)
-    print(f"[parity] greedy free run: {matched}/{n} frames identical before the first near-tie")
-    assert matched >= 1
+    # compare_free_run asserts that the first mismatch sits on a near-tie; every golden frame holds one (margins), so the
+    # free run carries no bound beyond that — the per-decision bound is test_every_greedy_decision_of_all_128_frames_teacher_forced
+    first_risky = next((f for f in range(g["margins"].shape[0]) if bool((g["margins"][f] < 0.06).any())), n)
+    print(f"[parity] greedy free run: {matched}/{n} frames identical before the first near-tie (first frame holding one: {first_risky})")
+    assert matched >= first_risky
     assert bool((seq[1:, g["prompt"].shape[1]:] >= 0).all()) and bool((seq[1:, g["prompt"].shape[1]:] < cfg.codebook_size).all())
 
 
@@ -349,3 +352,187 @@ def test_many_row_tensor_core_attention_matches_oracle():
         mabs, _, _ = err_stats(lg, base)
         print(f"[parity] tensor-core vs CUDA-core attention (splits={splits}): max-abs {mabs:.4f}")
         assert mabs <= ABS_TOL
+
+
+# ------------------------------------------------------------------------------------------- all-frame teacher forcing, EOS, reference loop
+def _uniform_records(g, frames, cfg):
+    """the reference's draws of every frame, in its order: V, V, then cb x (C-1)"""
+    feeder = UniformFeeder(g["useed"])
+    V, cb, C = cfg.vocab_size, cfg.codebook_size, cfg.num_codebooks
+    rec = torch.empty((frames, 1, 2 * V + (C - 1) * cb), dtype=torch.bfloat16)
+    for f in range(frames):
+        parts = [feeder(torch.empty(V, dtype=torch.bfloat16)), feeder(torch.empty(V, dtype=torch.bfloat16))]
+        parts += [feeder(torch.empty(cb, dtype=torch.bfloat16)) for _ in range(C - 1)]
+        rec[f, 0] = torch.cat(parts)
+    return rec
+
+
+def test_every_greedy_decision_of_all_128_frames_teacher_forced(tiny):
+    """North star: 'greedy code sequences identical'.  On random-init weights half of the 1280 decisions of the golden run are
+    top-2 near-ties at bf16 resolution (every frame holds at least one), so a free run cannot stay identical on any two
+    machines — the reference's own CPU result depends on the GEMM summation order.  What must hold: with the reference's
+    sequence fed back (teacher forcing, per DECISION: slow step + 9 fast steps on the golden codes), EVERY decision whose
+    golden top-2 margin exceeds 2 x the logit tolerance is the reference's.  All 128 frames, stage entry points."""
+    g, cfg, sd, m = tiny
+    T, C = g["prompt"].shape[1], cfg.num_codebooks
+    bias = R.make_semantic_logit_bias(cfg)[0, 0].float()
+    n_hi = n_ok = n_u0 = n_lo = n_lo_ok = 0
+    for k in range(g["margins"].shape[0]):
+        seq = g["seq"][:, : T + k]
+        out = m.forward_generate(seq[None].cuda(), torch.arange(seq.shape[1]))
+        gold = g["seq"][:, T + k]
+        picks = [int((out.logits[0, 0].float().cpu() + bias).argmax())]
+        m.forward_generate_fast(out.hidden_states, torch.tensor([0]))
+        for i in range(1, C):
+            fl = m.forward_generate_fast(m.fast_embeddings(gold[i: i + 1].cuda()).view(1, 1, -1), torch.tensor([i]))
+            picks.append(int(fl[0, 0].float().argmax()))
+        golds = [int(gold[0])] + [int(gold[i + 1]) for i in range(1, C)]
+        for d in range(C):
+            hi = float(g["margins"][k, d]) > 2 * ABS_TOL
+            same = picks[d] == golds[d]
+            if not same and golds[d] == 0:  # the reference drew u = 0 for its only candidate: argmax of all-zero scores = index 0
+                n_u0 += 1
+                continue
+            if hi:
+                n_hi += 1
+                n_ok += int(same)
+            else:
+                n_lo += 1
+                n_lo_ok += int(same)
+    print(f"[parity] teacher-forced greedy decisions over 128 frames: {n_ok}/{n_hi} with margin > {2 * ABS_TOL} identical, "
+          f"{n_lo_ok}/{n_lo} near-ties identical, {n_u0} u=0 draws skipped")
+    assert n_hi >= 600 and n_ok == n_hi, (n_ok, n_hi)
+    assert n_u0 <= 16
+
+
+def test_fused_frame_kernel_on_all_128_golden_frames(tiny):
+    """The same through the product path: prompt pass over the golden prefix + ONE fused frame (persistent frame kernel,
+    on-device sampling with the reference's recorded uniforms).  Inside a frame a flipped near-tie changes the input of
+    the later codebooks, so decisions are compared in order up to the first mismatch, which must be a near-tie."""
+    from fish_speech_b200 import dual_ar
+    g, cfg, sd, m = tiny
+    T, C = g["prompt"].shape[1], cfg.num_codebooks
+    n = g["margins"].shape[0]
+    rec = _uniform_records(g, n, cfg)
+    bias = dual_ar.make_semantic_logit_bias(m)
+    s = g["sampling"]
+    m.set_option("mega", 1)
+    m._session_frames = 8
+    sess = m.session(1, 8)
+    full = checked = 0
+    for k in range(n):
+        sess.uniforms = rec[k: k + 1].cuda()
+        seq = g["seq"][:, : T + k]
+        tok = dual_ar.decode_one_token_ar(m, seq[None].cuda(), torch.arange(seq.shape[1]), s["temperature"], s["top_p"],
+                                          s["top_k"], bias).cpu().view(-1).long()
+        gold = g["seq"][:, T + k]
+        if torch.equal(tok, gold):
+            full += 1
+            checked += int((g["margins"][k] > 2 * ABS_TOL).sum())
+            continue
+        row = int((tok != gold).nonzero()[0])
+        dec = 0 if row <= 1 else row - 1
+        assert float(g["margins"][k, dec]) <= 2 * ABS_TOL, (k, row, float(g["margins"][k, dec]))
+        checked += int((g["margins"][k, :dec] > 2 * ABS_TOL).sum())
+    sess.check_device()
+    sess.uniforms = None
+    print(f"[parity] fused frames on the golden prefixes: {full}/{n} frames identical in all 11 rows, "
+          f"{checked} decisions with margin > {2 * ABS_TOL} verified, no mismatch above that margin")
+    assert checked >= 300
+
+
+def test_eos_flag_poll_and_trim_match_reference_loop(tiny):
+    """<|im_end|> at a chosen frame: the device `done` flag, the 32-frame poll and the trim (dual_ar.py decode_n_tokens)
+    against the oracle's decode_n_tokens (inference.py:184-238: break on im_end, the EOS frame is kept).
+    EOS is forced through the DRAWS, not the logits: the bias (+3) lifts <|im_end|> to rank 0 at p ~ 0.025 (kept by the top-k / top-p mask without crowding the others out), its
+    uniform is 0 in every frame (score 0: never drawn) except frame K where it is 255/256 against 1/256 for everyone else."""
+    from fish_speech_b200 import generate, dual_ar
+    g, cfg, sd, m = tiny
+    V, cb, C = cfg.vocab_size, cfg.codebook_size, cfg.num_codebooks
+    K, frames = 37, 100
+    gen = torch.Generator().manual_seed(8)
+    rec = (torch.randint(1, 256, (frames, 1, 2 * V + (C - 1) * cb), generator=gen).float() / 256).to(torch.bfloat16)
+    for v in (0, 1):
+        rec[:, 0, v * V + cfg.im_end_id] = 0.0
+        rec[K, 0, v * V: (v + 1) * V] = 1.0 / 256
+        rec[K, 0, v * V + cfg.im_end_id] = 255.0 / 256
+    real_bias = dual_ar.make_semantic_logit_bias
+
+    def eos_bias(model):
+        b = real_bias(model)
+        b[0, 0, cfg.im_end_id] = 3.0
+        return b
+
+    prompt = g["prompt"]
+    m.set_option("mega", 1)
+    m._session_frames = frames + 1
+    sess = m.session(1, frames + 1)
+    sess.uniforms = rec.cuda()
+    dual_ar.make_semantic_logit_bias = eos_bias
+    try:
+        seq = generate(model=m, prompt=prompt.cuda(), max_new_tokens=frames, temperature=0.8, top_p=0.8, top_k=30).cpu()
+    finally:
+        dual_ar.make_semantic_logit_bias = real_bias
+        sess.uniforms = None
+    T = prompt.shape[1]
+    assert seq.shape[1] == T + K + 1, seq.shape          # frames 0..K, the EOS frame kept, nothing after it
+    assert int(seq[0, -1]) == cfg.im_end_id and not bool((seq[0, T:-1] == cfg.im_end_id).any())
+    assert int(sess.done[0]) == 1 and int(sess.frame_counter) == 1 + 64  # prefill frame + two 32-frame polls ran on the device
+    # the oracle's loop with the same draws and bias stops at the same frame
+    om = R.DualARRef(cfg, sd)
+    om.setup_caches(1, cfg.max_seq_len)
+    state = {"f": 0, "off": 0}
+
+    def feed(t):  # the oracle asks for V, V, cb x 9 per frame, in order
+        n_ = t.numel()
+        u = rec[state["f"], 0, state["off"]: state["off"] + n_].clone().view(t.shape)
+        state["off"] += n_
+        if state["off"] >= rec.shape[2]:
+            state["f"] += 1
+            state["off"] = 0
+        return u
+
+    ob = R.make_semantic_logit_bias(cfg)
+    ob[0, 0, cfg.im_end_id] = 3.0
+    t_, p_ = torch.tensor(0.8, dtype=torch.bfloat16), torch.tensor(0.8, dtype=torch.bfloat16)
+    first = R.decode_one_token_ar(om, prompt.view(1, C + 1, -1), torch.arange(T), t_, p_, 30, ob, rand_like=feed)
+    rest = R.decode_n_tokens(om, first.view(1, C + 1, -1), torch.tensor([T], dtype=torch.int), frames - 1, t_, p_, 30, ob,
+                             rand_like=feed)
+    assert 1 + rest.shape[1] == K + 1 and int(rest[0, -1]) == cfg.im_end_id
+
+
+def test_reference_frame_loop_drives_decode_one_token_ar(tiny):
+    """INTEGRATION.md §1a binding: the REFERENCE's own per-frame loop (decode_n_tokens, inference.py:184-238, here the oracle's
+    statement-for-statement copy, which takes the callable like the reference does) calls fish_speech_b200.decode_one_token_ar
+    once per frame with host-side previous_tokens / input_pos bookkeeping.  Must equal this library's device-side loop
+    (same draws), i.e. the RAS window roll, position increment and token hand-over agree with the reference's."""
+    from fish_speech_b200 import dual_ar, generate
+    g, cfg, sd, m = tiny
+    C = cfg.num_codebooks
+    frames = 40
+    gs = load_golden("dual_ar_tiny_sampled")
+    prompt, s = gs["prompt"], gs["sampling"]
+    T = prompt.shape[1]
+    rec = _uniform_records(gs, frames, cfg)
+    m.set_option("mega", 1)
+    m._session_frames = frames + 1
+    sess = m.session(1, frames + 1)
+    sess.uniforms = rec.cuda()
+    dev = generate(model=m, prompt=prompt.cuda(), max_new_tokens=frames, temperature=s["temperature"], top_p=s["top_p"],
+                   top_k=s["top_k"]).cpu()
+    bias = dual_ar.make_semantic_logit_bias(m)
+
+    def one(model, x, input_pos, temperature, top_p, top_k, semantic_logit_bias, previous_tokens=None, rand_like=None,
+            trace=None):
+        pt = None if previous_tokens is None else previous_tokens.cuda()
+        return dual_ar.decode_one_token_ar(m, x.cuda(), input_pos, temperature, top_p, top_k, bias, previous_tokens=pt).cpu()
+
+    t_ = torch.tensor(s["temperature"], dtype=torch.bfloat16)
+    p_ = torch.tensor(s["top_p"], dtype=torch.bfloat16)
+    first = one(None, prompt.view(1, C + 1, -1), torch.arange(T), t_, p_, s["top_k"], None)  # resets the frame records to 0
+    rest = R.decode_n_tokens(R.DualARRef(cfg, sd), first.view(1, C + 1, -1),
+                             torch.tensor([T], dtype=torch.int), frames - 1, t_, p_, s["top_k"], None, decode_one_token=one)
+    sess.check_device()
+    sess.uniforms = None
+    host = torch.cat([first.long(), rest.long()], dim=1)
+    assert torch.equal(host, dev[:, T:]), (host[0], dev[0, T:])

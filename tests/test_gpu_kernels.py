@@ -212,3 +212,99 @@ def test_rows_gemm_narrow_matches_fp32_reference(lib, M, N, K, nw):
     tol = ref.float().abs() * 2.0 ** -7 + 2e-3
     print(f"[parity] rows_gemm_narrow M={M} N={N} K={K} nw={nw}: max-abs {float(err.max()):.5f}, exact {float((out == ref).float().mean()):.4f}")
     assert int((err > tol).sum()) == 0, float(err.max())
+
+
+# ------------------------------------------------------------------------------------------- sampling at scale (>= 1e5 cases)
+def _make_sampling_batch(kind, B, V, gen):
+    """bf16 logits [B][V] + bf16 uniforms [B][V] of one family of cases"""
+    lg = torch.randn(B, V, generator=gen) * 2.0
+    u = torch.randint(0, 256, (B, V), generator=gen).float() / 256
+    if kind == "ties":            # heavy quantisation: many exact ties at every rank, incl. across the top-k boundary
+        lg = (lg * 2).round() / 2
+    elif kind == "u0":            # a quarter of the draws are u = 0 (score 0), some rows entirely
+        u = torch.where(torch.rand(B, V, generator=gen) < 0.25, torch.zeros(()), u)
+        u[: B // 16] = 0.0
+    elif kind == "top_p_edge":    # a few dominant candidates whose cumulative mass sits near top_p
+        lg[:, :4] += torch.tensor([6.0, 5.5, 5.0, 4.5])
+        lg = lg[:, torch.randperm(V, generator=gen)]
+    elif kind == "masked":        # -inf-biased vocabulary: only a short range is finite (constrained decode)
+        lo = int(torch.randint(0, V - 40, (1,), generator=gen))
+        keep = torch.zeros(V, dtype=torch.bool)
+        keep[lo: lo + 33] = True
+        keep[int(torch.randint(0, V, (1,), generator=gen))] = True
+        lg = torch.where(keep, lg, torch.full((), float("-inf")))
+    elif kind == "flat":          # all equal
+        lg = torch.zeros(B, V) + 0.5
+    return lg.bfloat16(), u.bfloat16()
+
+
+def test_sampling_100k_on_the_fly_cases_vs_oracle(lib):
+    """>= 1e5 random cases of sample() (inference.py:80-93): fsb_sample on the GPU against the oracle's restatement with a
+    stable sort (ties by ascending index, what torch.sort yields on CUDA), identical bf16 logits and uniforms -> the drawn
+    index must be IDENTICAL in every case.  Families: random, quantised ties, u = 0, top-p boundary, -inf-masked vocabulary,
+    all-equal; top_k in {1, 30}; T in {0.8, 1.0, 0.3}; top_p in {0.8, 0.9, 0.5}."""
+    import oracle.dual_ar_ref as M
+    V, B = 512, 2048
+    gen = torch.Generator().manual_seed(2024)
+    combos = [(0.8, 0.8, 30), (1.0, 0.9, 30), (0.8, 0.8, 1), (0.3, 0.5, 30), (1.0, 0.9, 7)]
+    kinds = ["random", "ties", "u0", "top_p_edge", "masked", "flat", "random", "ties", "u0", "masked"]
+    real = torch.sort
+    torch.sort = lambda x, descending=False, **k: real(x, descending=descending, stable=True)
+    total = bad = 0
+    worst = []
+    try:
+        for kind in kinds:
+            for (T, P, K) in combos:
+                lg, u = _make_sampling_batch(kind, B, V, gen)
+                got = _sample(lib, lg.cuda(), T, P, K, u.cuda().view(B, 1, V))[:, 0]
+                t_, p_ = torch.tensor(T, dtype=torch.bfloat16), torch.tensor(P, dtype=torch.bfloat16)
+                for b in range(B):
+                    row_u = u[b]
+                    idx, _ = M.sample(lg[b][None, None], t_, p_, K, rand_like=lambda t: row_u)
+                    total += 1
+                    if int(idx) != int(got[b]):
+                        bad += 1
+                        if len(worst) < 5:
+                            worst.append((kind, T, P, K, b, int(idx), int(got[b])))
+    finally:
+        torch.sort = real
+    print(f"[parity] sampling: {total} on-the-fly cases, {bad} mismatches")
+    assert total >= 100000
+    assert bad == 0, worst
+
+
+def test_philox_mode_draws_follow_the_reference_distribution(lib):
+    """Production mode (no injected uniforms: Philox4x32-10 keyed by seed, counters = index / draw / frame / request).
+    Two-sample chi-square of 2^17 GPU draws against 2^17 draws of the oracle's multinomial_sample_one_no_sync with torch's
+    bf16 rand_like (the reference's RNG, 8 random bits per draw) on the same 24-way distribution; and two seeds must differ."""
+    import oracle.dual_ar_ref as M
+    V, N = 24, 1 << 17
+    g = torch.Generator().manual_seed(77)
+    lg = (torch.randn(V, generator=g) * 1.5).bfloat16()
+    T, P, K = 1.0, 0.9, 30
+    rows = lg[None].expand(N, V).contiguous().cuda()
+    out = torch.full((N, 2), -7, dtype=torch.int32, device="cuda")
+    bf = lambda v: float(torch.tensor(v, dtype=torch.bfloat16).float())
+
+    def draw(seed):
+        rc = lib.fsb_sample(rows.data_ptr(), None, N, V, K, bf(T), bf(P), 1, 1.0, 1.0, None, seed, 0, 0, 0, 0, out.data_ptr(),
+                            torch.cuda.current_stream().cuda_stream)
+        assert rc == 0
+        torch.cuda.synchronize()
+        return out[:, 0].cpu().long().clone()
+
+    a, a2 = draw(12345), draw(999)
+    assert not torch.equal(a, a2)                                   # the seed matters
+    assert torch.equal(a, draw(12345))                              # and the stream is reproducible
+    probs = M.logits_to_probs(lg, torch.tensor(T, dtype=torch.bfloat16), torch.tensor(P, dtype=torch.bfloat16), K)
+    torch.manual_seed(5)
+    q = -torch.log(torch.rand((N, V), dtype=torch.bfloat16))
+    b = torch.argmax(probs[None] / q, dim=-1)
+    ca, cb_ = torch.bincount(a, minlength=V).double(), torch.bincount(b, minlength=V).double()
+    live = (ca + cb_) > 0
+    chi2 = float((((ca - cb_) ** 2) / (ca + cb_).clamp_min(1))[live].sum())
+    dof = int(live.sum()) - 1
+    print(f"[parity] Philox draws vs torch bf16 rand_like draws: chi2 {chi2:.1f} on {dof} dof; support {int(live.sum())} of {V}")
+    # 99.99 % quantile of chi-square is below dof + 4 * sqrt(2 * dof) + 12 for dof <= 30
+    assert chi2 < dof + 4 * (2 * dof) ** 0.5 + 12, (chi2, dof)
+    assert int((ca > 0).sum()) == int((cb_ > 0).sum())              # same support (the top-p mask removes the same tail)
