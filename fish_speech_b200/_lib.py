@@ -36,6 +36,18 @@ class DACDesc(C.Structure):
         "tf_head_dim", "tf_window", "convnext_ratio", "max_batch", "max_frames")] + [("tf_norm_eps", C.c_float)]
 
 
+class TcConvArgs(C.Structure):
+    _fields_ = [
+        ("A16", C.c_void_p), ("W16", C.c_void_p),
+        ("B", C.c_int32), ("T", C.c_int32), ("Cin", C.c_int32), ("N", C.c_int32), ("taps", C.c_int32), ("dil", C.c_int32),
+        ("f16", C.c_int32), ("use_simt", C.c_int32),
+        ("bias", C.c_void_p), ("bias_mod", C.c_int32), ("gamma", C.c_void_p),
+        ("res32", C.c_void_p), ("res16", C.c_void_p), ("ldres", C.c_int32),
+        ("alpha", C.c_void_p), ("alpha_mod", C.c_int32), ("act", C.c_int32), ("round_lin", C.c_int32),
+        ("out16", C.c_void_p), ("ld16", C.c_int32), ("out32", C.c_void_p), ("ld32", C.c_int32),
+    ]
+
+
 EXPORTS = {
     # name: (restype, argtypes)
     "fsb_abi_version": (C.c_int, []),
@@ -74,6 +86,7 @@ DAC_EXPORTS = {
     "fsb_dac_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "fsb_dac_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "fsb_dac_stage": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "fsb_tc_conv": (C.c_int, [C.POINTER(TcConvArgs), C.c_void_p]),
     "fsb_dac_flops": (C.c_double, [C.c_void_p, C.c_int32, C.c_int32]),
 }
 

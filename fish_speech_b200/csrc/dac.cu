@@ -11,6 +11,7 @@
 
 #include "../../include/fish_b200.h"
 #include "dac_kernels.cuh"
+#include "tc_conv.cuh"
 
 struct fsb_dac {
     fsb_dac_desc d;
@@ -165,6 +166,33 @@ int fsb_dac_stage(fsb_dac* h, const char* name, void** dptr, size_t* bytes) {
         return 0;
     }
     return dfail(h, "unknown stage buffer " + n);
+}
+
+static TcConvArgs tcv_from_abi(const fsb_tc_conv_args& x) {
+    TcConvArgs a{};
+    a.B = x.B; a.T = x.T; a.N = x.N; a.Cin = x.Cin; a.taps = x.taps; a.dil = x.dil;
+    a.A16 = x.A16; a.W16 = x.W16; a.out16 = x.out16; a.out32 = x.out32; a.ld16 = x.ld16; a.ld32 = x.ld32;
+    a.bias = x.bias; a.gamma = x.gamma; a.res32 = x.res32; a.res16 = x.res16; a.alpha = x.alpha;
+    a.bias_mod = x.bias_mod > 0 ? x.bias_mod : x.N; a.alpha_mod = x.alpha_mod > 0 ? x.alpha_mod : x.N; a.ldres = x.ldres;
+    a.act = x.act; a.round_lin = x.round_lin;
+    return a;
+}
+
+int fsb_tc_conv(const fsb_tc_conv_args* x, void* stream) {
+    if (!x || !x->A16 || !x->W16 || (!x->out16 && !x->out32)) return 1;
+    if (x->B < 1 || x->T < 1 || x->Cin < 1 || x->N < 1 || x->taps < 1 || x->dil < 1) return 1;
+    if (x->act == TCV_ACT_SWIGLU && (!x->out16 || (x->N & 1))) return 1;
+    TcConvArgs a = tcv_from_abi(*x);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (x->use_simt || !tcv_tc_ok(x->Cin, x->N)) return tcv_launch_simt(s, x->f16 != 0, a) == cudaSuccess ? 0 : 4;
+    int dev = 0, n_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 2;
+    if (tcv_set_attrs() != cudaSuccess) return 2;
+    const int bn = tcv_pick_bn(x->N);
+    CUtensorMap mA, mW;
+    if (!tcv_make_map(&mA, x->A16, x->f16 != 0, (uint64_t)x->Cin, (uint64_t)x->T, (uint64_t)x->B, TCV_BM)) return 3;
+    if (!tcv_make_map(&mW, x->W16, x->f16 != 0, (uint64_t)x->Cin, (uint64_t)x->N, (uint64_t)x->taps, (uint32_t)bn)) return 3;
+    return tcv_launch(s, n_sm, x->f16 != 0, bn, mA, mW, a) == cudaSuccess ? 0 : 4;
 }
 
 // codes: device int64 [B][1+n_codebooks][T] (clamped in place like rvq.py:354-359); wav: device fp32 [B][hop*T]

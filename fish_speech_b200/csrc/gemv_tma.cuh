@@ -17,6 +17,7 @@
 #pragma once
 #include "common.cuh"
 #include "gemv.cuh"
+#include "tc_common.cuh"  // smem_u32, mbar_*, bulk_g2s
 
 #define GT_ROWS 8
 #define GT_TEAM_WARPS 8
@@ -26,36 +27,6 @@
 #define GT_MAX_STAGES 10
 #define GT_CPL 10  // 128-bit chunks per lane per row slice: KC <= 1280 columns
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
-    uint32_t ok, spins = 0;
-    long long t0 = 0;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok)
-            : "r"(smem_u32(b)), "r"(parity)
-            : "memory");
-        if (!ok && fsb_watchdog(spins, t0, 0xfffu, FSB_ERR_MBAR_WAIT)) break;  // a protocol bug must end, not hang the GPU
-    } while (!ok);
-}
-__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst_smem)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(GT_CONSUMERS) : "memory"); }
 
 // sum over the 256 consumer threads (named barrier 1), result broadcast

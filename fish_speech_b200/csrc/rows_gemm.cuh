@@ -29,12 +29,12 @@
 #include <cuda.h>
 
 #include "common.cuh"
-#include "gemv_tma.cuh"  // smem_u32, mbar_*
+#include "gemv_tma.cuh"
+#include "tc_common.cuh"  // smem_u32, mbar_*, tcgen05 / TMA wrappers
 
 #define RG_BM 128
 #define RG_BK 64
 #define RG_THREADS 192
-#define RG_EPI_THREADS 128
 #define RG_STAGES_MAX 9      // barrier arrays; the ring depth of a launch comes from rg_stages_for()
 #define RG_STAGES_MIN 3      //   of the NEXT kernel fits beside them and starts its weight stream early)
 #define RG_CTAS_PER_SM 2     // most CTAs of one launch per SM
@@ -59,49 +59,6 @@ __host__ __device__ constexpr uint32_t rg_stage_bytes(int bn) { return (uint32_t
 __host__ __device__ constexpr int rg_tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 256; }
 inline size_t rg_smem_bytes(int bn, int nst) { return (size_t)nst * rg_stage_bytes(bn) + 1024; }
 inline size_t rg_partial_bytes(int grid, int bn) { return (size_t)grid * 2 * bn * RG_BM * sizeof(float); }
-
-// ----------------------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ void rg_tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, uint64_t policy) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
-}
-__device__ __forceinline__ void rg_prefetch_map(const CUtensorMap* map) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// D[tmem] (+)= A[smem] . B[smem]^T, bf16 inputs, fp32 accumulate; `acc` = 0 overwrites D
-__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-// shared-memory matrix descriptor: K-major tile of rows x 64 bf16 (128 B per row), SWIZZLE_128B, 8-row groups 1024 B apart
-__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr) {
-    return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)(1024u >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
-}
-// instruction descriptor: D fp32, A/B bf16, both K-major, M = 128, N = bn
-__host__ __device__ constexpr uint32_t tc_idesc_bf16(int bn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(RG_BM >> 4) << 24);
-}
-// 16 consecutive fp32 columns of this thread's TMEM lane
-__device__ __forceinline__ void tc_ld16(uint32_t taddr, float (&v)[16]) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-__device__ __forceinline__ void rg_epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(RG_EPI_THREADS) : "memory"); }
 
 // ----------------------------------------------------------------------------- stream-K bookkeeping
 // U = n_tiles * kb units are cut into G contiguous ranges [U*c/G, U*(c+1)/G), one per CTA.
@@ -144,8 +101,6 @@ inline int rg_stages_for(int grid, int n_sm, int bn) {
 }
 
 #define RG_STAMP(i) do { if (a.trace) a.trace[(size_t)blockIdx.x * 8 + (i)] = clock64(); } while (0)
-#define RG_POLICY_EVICT_FIRST 0x12F0000000000000ull
-#define RG_POLICY_EVICT_LAST 0x14F0000000000000ull
 
 template <int BN>
 __global__ void __launch_bounds__(RG_THREADS, 3)
@@ -626,20 +581,6 @@ __global__ void __launch_bounds__(RF_THREADS) rows_finish_norm_kernel(RowsFinish
 }
 
 // ----------------------------------------------------------------------------- host side
-typedef CUresult (*rg_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-inline rg_encode_fn rg_get_encode() {
-    static rg_encode_fn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = (rg_encode_fn)p;
-    }
-    return fn;
-}
 // 2-D map over a row-major bf16 matrix [rows][cols]: box = 64 columns (one 128-byte swizzle atom) x box_rows rows;
 // rows beyond `rows` read as zero (weight tiles past N, activation rows past M)
 inline bool rg_make_map(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {

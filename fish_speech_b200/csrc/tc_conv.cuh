@@ -1,0 +1,430 @@
+// Causal conv / transposed conv / Linear over MANY rows as one implicit GEMM on the 5th-generation tensor cores:
+//
+//     out[b][t][n] = epi( sum_j sum_k A[b][t - (taps-1-j)*dil][k] * W[j][n][k] ),   rows t < 0 read as zero
+//
+//   * the DAC decoder's dense layers (modded_dac.py:521-580 causal conv / transposed conv, :599-620 ResidualUnit,
+//     :712-801 DecoderBlock / Decoder; rvq.py:58-191 ConvNeXt / upsample convs; modded_dac.py:97-346 transformer Linears);
+//   * the Linears of the Dual-AR prompt pass (llama.py:390-466 with Tq > 1), where W is the state dict's [N][K] as it is
+//     (taps = 1).
+//
+// Operands are 16-bit (bf16 for the LLM, fp16 or bf16 for the codec), K-major, accumulation is fp32 in TMEM:
+//   * A tile = 128 time rows x 64 channels, fetched by TMA from a 3-D tensor map {C, T, B} at row coordinate
+//     t0 - shift_j: rows before the start of the clip are OUT OF BOUNDS and arrive as zeros, which IS the causal left
+//     padding (no halo logic, no masks); rows past T and channels past C are zeros too;
+//   * W tile = BN output channels x 64 input channels of tap j from a 3-D map {Cin, N, taps};
+//   * every (tap, channel chunk) step is 4 tcgen05.mma (M = 128, N = BN, K = 16) into the same TMEM accumulator, so a
+//     7-tap conv is just a 7x longer reduction;
+//   * warp roles: TMA producer / MMA issuer (one thread) / 4 epilogue warps; a ring of shared-memory stages; TWO TMEM
+//     accumulators so the epilogue of tile i overlaps the MMAs of tile i+1; persistent CTAs walk the tile list;
+//   * epilogue (fp32): bias, exact GELU, LayerScale / ConvNeXt gamma, residual (fp32 stream or 16-bit), tanh, SwiGLU over
+//     interleaved gate/up columns, and Snake1d of the CONSUMING layer (x + sin^2(alpha x) / (alpha + 1e-9)) applied to the
+//     16-bit copy that the next GEMM reads, while the raw value goes to the fp32 residual stream: activations are
+//     transformed once, by their producer, and the next layer's operand needs no prologue.
+//
+// tcv_simt_kernel is the same op with the same epilogue on CUDA cores for shapes TMA cannot address (channel counts that
+// are not multiples of 8, as in the reduced test configuration) and the cross-check of the tensor-core kernel in tests.
+#pragma once
+#include <cuda_fp16.h>
+
+#include "tc_common.cuh"  // tcgen05 / TMA / mbarrier wrappers
+
+#define TCV_BM 128
+#define TCV_BK 64
+#define TCV_THREADS 192
+#define TCV_STAGES_MAX 8
+#define TCV_A_BYTES (TCV_BM * TCV_BK * 2)
+#define TCV_POLICY_EVICT_NORMAL 0x1000000000000000ull
+
+enum { TCV_ACT_NONE = 0, TCV_ACT_GELU = 1, TCV_ACT_TANH = 2, TCV_ACT_SWIGLU = 3 };
+
+struct TcConvArgs {
+    int B, T, N, Cin, taps, dil;
+    int tiles_t, tiles_n, n_tiles, kchunks, nst;
+    // ---- operands of the SIMT variant (the tensor-core kernel reads them through its tensor maps)
+    const void* A16;     // [B][T][Cin] 16-bit
+    const void* W16;     // [taps][N][Cin] 16-bit
+    // ---- epilogue
+    void* out16;         // [B*T][ld16] 16-bit copy (snaked when alpha != nullptr), or nullptr
+    float* out32;        // [B*T][ld32] fp32 copy (never snaked), or nullptr
+    int ld16, ld32;
+    const float* bias;   // [bias_mod] or nullptr (transposed conv: bias_mod = Cout, N = stride * Cout)
+    const float* gamma;  // [N] or nullptr
+    const float* res32;  // [B*T][ldres] fp32 residual, may alias out32, or nullptr
+    const void* res16;   // [B*T][ldres] 16-bit residual, may alias out16, or nullptr
+    const float* alpha;  // [alpha_mod] Snake of the consumer applied to out16, or nullptr
+    int bias_mod, alpha_mod, ldres;
+    int act;             // TCV_ACT_*; SWIGLU: columns (2i, 2i+1) = (gate, up) -> out column i, out width N / 2
+    int vec_ok;          // 1: every row pitch / pointer allows the 16-byte vector paths of the epilogue
+    int round_lin;       // 1: round the reduction to the 16-bit type BEFORE the residual add (the bf16 LLM's rounding points:
+                         //    one rounding per Linear, one per add, llama.py:838-843)
+};
+
+// ----------------------------------------------------------------------------- 16-bit type policy
+template <bool F16> struct Tcv16;
+template <> struct Tcv16<true> {
+    static __device__ __forceinline__ uint16_t pack(float v) {
+        v = fminf(fmaxf(v, -65504.f), 65504.f);  // fp16 operands saturate instead of turning into inf
+        return __half_as_ushort(__float2half_rn(v));
+    }
+    static __device__ __forceinline__ float unpack(uint16_t b) { return __half2float(__ushort_as_half(b)); }
+};
+template <> struct Tcv16<false> {
+    static __device__ __forceinline__ uint16_t pack(float v) { return f_to_bf16_bits(v); }
+    static __device__ __forceinline__ float unpack(uint16_t b) { return bf16_bits_to_f(b); }
+};
+
+__device__ __forceinline__ float tcv_snake(float x, float a) {
+    const float s = __sinf(a * x);  // MUFU sine: abs error ~1e-7 on the O(1) arguments here, far below the 16-bit rounding
+    return fmaf(__fdividef(1.f, a + 1e-9f) * s, s, x);
+}
+__device__ __forceinline__ float tcv_gelu(float v) { return 0.5f * v * (1.f + erff(v * 0.70710678118654752f)); }
+
+// ----------------------------------------------------------------------------- epilogue of 16 consecutive columns of one row
+// v[i] = reduction of column n0 + i of row `row` (global row index b*T + t); nv = valid columns (16 except at a ragged edge)
+template <bool F16>
+__device__ __forceinline__ void tcv_epilogue16(const TcConvArgs& a, size_t row, int n0, float (&v)[16], int nv) {
+    typedef Tcv16<F16> H;
+    const bool vec = (nv == 16) && a.vec_ok;
+    if (a.round_lin) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = H::unpack(H::pack(v[i]));
+    }
+    if (a.bias) {
+        if (vec && (a.bias_mod & 15) == 0) {
+            const float4* bp = reinterpret_cast<const float4*>(a.bias + (n0 % a.bias_mod));
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const float4 b4 = __ldg(bp + q); v[4 * q] += b4.x; v[4 * q + 1] += b4.y; v[4 * q + 2] += b4.z; v[4 * q + 3] += b4.w; }
+        } else {
+            for (int i = 0; i < nv; ++i) v[i] += __ldg(a.bias + ((n0 + i) % a.bias_mod));
+        }
+    }
+    if (a.act == TCV_ACT_GELU) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = tcv_gelu(v[i]);
+    }
+    if (a.act == TCV_ACT_SWIGLU) {  // (gate, up) pairs -> 8 outputs at columns n0 / 2 ..
+        uint16_t o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float g = v[2 * i], u = v[2 * i + 1];
+            o[i] = H::pack(__fdividef(g, 1.f + __expf(-g)) * u);
+        }
+        uint16_t* dst = reinterpret_cast<uint16_t*>(a.out16) + row * a.ld16 + (n0 >> 1);
+        if (vec) {
+            *reinterpret_cast<uint4*>(dst) = make_uint4(o[0] | ((uint32_t)o[1] << 16), o[2] | ((uint32_t)o[3] << 16),
+                                                        o[4] | ((uint32_t)o[5] << 16), o[6] | ((uint32_t)o[7] << 16));
+        } else {
+            for (int i = 0; i < nv / 2; ++i) dst[i] = o[i];
+        }
+        return;
+    }
+    if (a.gamma) {
+        if (vec) {
+            const float4* gp = reinterpret_cast<const float4*>(a.gamma + n0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const float4 g4 = __ldg(gp + q); v[4 * q] *= g4.x; v[4 * q + 1] *= g4.y; v[4 * q + 2] *= g4.z; v[4 * q + 3] *= g4.w; }
+        } else {
+            for (int i = 0; i < nv; ++i) v[i] *= __ldg(a.gamma + n0 + i);
+        }
+    }
+    if (a.res32) {
+        const float* rp = a.res32 + row * a.ldres + n0;
+        if (vec) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const float4 r4 = *reinterpret_cast<const float4*>(rp + 4 * q); v[4 * q] += r4.x; v[4 * q + 1] += r4.y; v[4 * q + 2] += r4.z; v[4 * q + 3] += r4.w; }
+        } else {
+            for (int i = 0; i < nv; ++i) v[i] += rp[i];
+        }
+    } else if (a.res16) {
+        const uint16_t* rp = reinterpret_cast<const uint16_t*>(a.res16) + row * a.ldres + n0;
+        if (vec) {
+            const uint4 r0 = *reinterpret_cast<const uint4*>(rp), r1 = *reinterpret_cast<const uint4*>(rp + 8);
+            const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+            for (int q = 0; q < 8; ++q) { v[2 * q] += H::unpack((uint16_t)(w[q] & 0xffffu)); v[2 * q + 1] += H::unpack((uint16_t)(w[q] >> 16)); }
+        } else {
+            for (int i = 0; i < nv; ++i) v[i] += H::unpack(rp[i]);
+        }
+    }
+    if (a.act == TCV_ACT_TANH) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = tanhf(v[i]);
+    }
+    if (a.out32) {
+        float* op = a.out32 + row * a.ld32 + n0;
+        if (vec) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) *reinterpret_cast<float4*>(op + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+        } else {
+            for (int i = 0; i < nv; ++i) op[i] = v[i];
+        }
+    }
+    if (a.out16) {
+        if (a.alpha) {
+            if (vec && (a.alpha_mod & 15) == 0) {
+                const float4* ap = reinterpret_cast<const float4*>(a.alpha + (n0 % a.alpha_mod));
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 a4 = __ldg(ap + q);
+                    v[4 * q] = tcv_snake(v[4 * q], a4.x); v[4 * q + 1] = tcv_snake(v[4 * q + 1], a4.y);
+                    v[4 * q + 2] = tcv_snake(v[4 * q + 2], a4.z); v[4 * q + 3] = tcv_snake(v[4 * q + 3], a4.w);
+                }
+            } else {
+                for (int i = 0; i < nv; ++i) v[i] = tcv_snake(v[i], __ldg(a.alpha + ((n0 + i) % a.alpha_mod)));
+            }
+        }
+        uint16_t* op = reinterpret_cast<uint16_t*>(a.out16) + row * a.ld16 + n0;
+        if (vec) {
+            uint32_t w[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) w[q] = (uint32_t)H::pack(v[2 * q]) | ((uint32_t)H::pack(v[2 * q + 1]) << 16);
+            *reinterpret_cast<uint4*>(op) = make_uint4(w[0], w[1], w[2], w[3]);
+            *reinterpret_cast<uint4*>(op + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+        } else {
+            for (int i = 0; i < nv; ++i) op[i] = H::pack(v[i]);
+        }
+    }
+}
+
+// ----------------------------------------------------------------------------- the tensor-core kernel
+__host__ __device__ constexpr uint32_t tcv_stage_bytes(int bn) { return (uint32_t)(TCV_A_BYTES + bn * TCV_BK * 2); }
+__host__ __device__ constexpr int tcv_tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512; }
+inline size_t tcv_smem_bytes(int bn, int nst) { return (size_t)nst * tcv_stage_bytes(bn) + 1024; }
+
+__device__ __forceinline__ void tcv_tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4, %5}], [%2], %6;"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(policy) : "memory");
+}
+// instruction descriptor: D fp32, A/B both bf16 (1) or both fp16 (0), K-major, M = 128, N = bn
+__host__ __device__ constexpr uint32_t tcv_idesc(int bn, bool f16) {
+    return (1u << 4) | ((f16 ? 0u : 1u) << 7) | ((f16 ? 0u : 1u) << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(TCV_BM >> 4) << 24);
+}
+
+template <int BN, bool F16>
+__global__ void __launch_bounds__(TCV_THREADS, 1)
+tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, TcConvArgs a) {
+    constexpr uint32_t STAGE = tcv_stage_bytes(BN);
+    constexpr int TCOLS = tcv_tmem_cols(BN);
+    extern __shared__ uint8_t tcv_smem_raw[];
+    __shared__ uint64_t full_bar[TCV_STAGES_MAX], empty_bar[TCV_STAGES_MAX], tfull_bar[2], tempty_bar[2];
+    __shared__ uint32_t tmem_base_s;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t sbase = (smem_u32(tcv_smem_raw) + 1023u) & ~1023u;
+    if (tid == 0) {
+        for (int s = 0; s < a.nst; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(TCOLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+    const int nk = a.taps * a.kchunks;  // reduction steps per tile
+
+    if (warp == 0) {
+        // ===== TMA producer
+        if (lane == 0) {
+            rg_prefetch_map(&tmA);
+            rg_prefetch_map(&tmW);
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
+                const int t0 = tt * TCV_BM, n0 = tn * BN;
+                for (int j = 0; j < a.taps; ++j) {
+                    const int trow = t0 - (a.taps - 1 - j) * a.dil;  // negative rows: out of bounds = zeros = causal padding
+                    for (int kc = 0; kc < a.kchunks; ++kc, ++it) {
+                        const uint32_t s = it % (uint32_t)a.nst, use = it / (uint32_t)a.nst;
+                        mbar_wait(&empty_bar[s], (use & 1u) ^ 1u);
+                        const uint32_t st = sbase + s * STAGE, bar = smem_u32(&full_bar[s]);
+                        mbar_expect_tx(&full_bar[s], STAGE);
+                        tcv_tma_load_3d(st, &tmA, bar, kc * TCV_BK, trow, b, TCV_POLICY_EVICT_NORMAL);  // re-read by the other taps / column tiles: keep in L2
+                        tcv_tma_load_3d(st + TCV_A_BYTES, &tmW, bar, kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer
+        constexpr uint32_t IDESC = tcv_idesc(BN, F16);
+        uint32_t it = 0, iseg = 0;
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
+            const uint32_t buf = iseg & 1u;
+            mbar_wait(&tempty_bar[buf], ((iseg >> 1) & 1u) ^ 1u);  // the epilogue has drained this accumulator
+            tc_fence_after();
+            for (int i = 0; i < nk; ++i, ++it) {
+                const uint32_t s = it % (uint32_t)a.nst;
+                mbar_wait(&full_bar[s], (it / (uint32_t)a.nst) & 1u);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t st = sbase + s * STAGE;
+                    const uint64_t adesc = tc_smem_desc(st), bdesc = tc_smem_desc(st + TCV_A_BYTES);
+                    const uint32_t d = tmem + buf * BN;
+#pragma unroll
+                    for (int k = 0; k < TCV_BK / 16; ++k)
+                        tc_mma_bf16(d, adesc + 2 * k, bdesc + 2 * k, IDESC, (i > 0 || k > 0) ? 1u : 0u);
+                    tc_commit(&empty_bar[s]);
+                }
+                __syncwarp();
+            }
+            if (lane == 0) tc_commit(&tfull_bar[buf]);
+            __syncwarp();
+        }
+    } else {
+        // ===== epilogue: warp w owns TMEM lanes 32*(w%4) .. +31; one thread = one time row of the tile
+        const int et = tid - 64, lg = warp & 3;
+        const uint32_t tlane = (uint32_t)(lg * 32) << 16;
+        uint32_t iseg = 0;
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
+            const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
+            const int t = tt * TCV_BM + lg * 32 + lane, n0 = tn * BN;
+            const uint32_t buf = iseg & 1u;
+            mbar_wait(&tfull_bar[buf], (iseg >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t tacc = tmem + tlane + buf * BN;
+            const size_t row = (size_t)b * a.T + t;
+#pragma unroll 1
+            for (int ch = 0; ch < BN / 16; ++ch) {
+                const int nc = n0 + ch * 16;
+                if (nc >= a.N) break;  // uniform across the CTA
+                float v[16];
+                tc_ld16(tacc + (uint32_t)(ch * 16), v);
+                if (t < a.T) tcv_epilogue16<F16>(a, row, nc, v, min(16, a.N - nc));
+            }
+            tc_fence_before();
+            rg_epi_bar();
+            if (et == 0) mbar_arrive(&tempty_bar[buf]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS) : "memory");
+    }
+}
+
+// ----------------------------------------------------------------------------- the same op on CUDA cores
+// one thread = 16 consecutive output columns of one row; for channel counts TMA cannot address and as the cross-check
+template <bool F16>
+__global__ void __launch_bounds__(128) tcv_simt_kernel(TcConvArgs a) {
+    typedef Tcv16<F16> H;
+    const int chunks = (a.N + 15) / 16;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)a.B * a.T * chunks) return;
+    const int ch = (int)(idx % chunks);
+    const long long bt = idx / chunks;
+    const int t = (int)(bt % a.T), b = (int)(bt / a.T);
+    const int n0 = ch * 16, nv = min(16, a.N - n0);
+    const uint16_t* A = reinterpret_cast<const uint16_t*>(a.A16);
+    const uint16_t* W = reinterpret_cast<const uint16_t*>(a.W16);
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = 0.f;
+    for (int j = 0; j < a.taps; ++j) {
+        const int tr = t - (a.taps - 1 - j) * a.dil;
+        if (tr < 0) continue;
+        const uint16_t* ar = A + ((size_t)b * a.T + tr) * a.Cin;
+        const uint16_t* wj = W + ((size_t)j * a.N + n0) * a.Cin;
+        for (int k = 0; k < a.Cin; ++k) {
+            const float x = H::unpack(ar[k]);
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                if (i < nv) v[i] = fmaf(x, H::unpack(wj[(size_t)i * a.Cin + k]), v[i]);
+        }
+    }
+    tcv_epilogue16<F16>(a, (size_t)b * a.T + t, n0, v, nv);
+}
+
+// ----------------------------------------------------------------------------- host side
+// 3-D map over a 16-bit tensor [d2][d1][d0] (d0 contiguous): box = 64 x box_rows x 1, 128-byte swizzle, zero fill out of bounds
+inline bool tcv_make_map(CUtensorMap* m, const void* ptr, bool f16, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box_rows) {
+    rg_encode_fn enc = rg_get_encode();
+    if (!enc) return false;
+    const cuuint64_t gdim[3] = {d0, d1, d2};
+    const cuuint64_t gstr[2] = {d0 * 2, d0 * d1 * 2};
+    const cuuint32_t box[3] = {TCV_BK, box_rows, 1};
+    const cuuint32_t est[3] = {1, 1, 1};
+    return enc(m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box, est,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+// column-tile width: the widest of the UMMA widths that divides N (no wasted columns), else 256 / the next multiple of 16
+inline int tcv_pick_bn(int N) {
+    const int cands[6] = {256, 192, 128, 96, 64, 32};
+    if (N >= 96)
+        for (int i = 0; i < 4; ++i)
+            if (N % cands[i] == 0) return cands[i];
+    if (N > 256) return 256;
+    for (int i = 5; i >= 0; --i)
+        if (N <= cands[i]) return cands[i];
+    return 256;
+}
+// shapes the tensor-core kernel can address: 16-byte row pitches for TMA; anything else goes to tcv_simt_kernel
+inline bool tcv_tc_ok(int Cin, int N) { return Cin % 8 == 0 && Cin >= 8 && N >= 1; }
+
+typedef void (*tcv_fn)(const CUtensorMap, const CUtensorMap, TcConvArgs);
+template <bool F16>
+inline tcv_fn tcv_pick(int bn) {
+    switch (bn) {
+    case 256: return tcv_kernel<256, F16>;
+    case 192: return tcv_kernel<192, F16>;
+    case 128: return tcv_kernel<128, F16>;
+    case 96: return tcv_kernel<96, F16>;
+    case 64: return tcv_kernel<64, F16>;
+    default: return tcv_kernel<32, F16>;
+    }
+}
+inline int tcv_stages_for(int bn) {
+    const int fit = (int)((225 * 1024 - 1024) / tcv_stage_bytes(bn));
+    return fit < TCV_STAGES_MAX ? fit : TCV_STAGES_MAX;
+}
+inline cudaError_t tcv_set_attrs() {
+    if (!fsb_first_on_device(4)) return cudaSuccess;
+    const int bns[6] = {256, 192, 128, 96, 64, 32};
+    for (int f = 0; f < 2; ++f)
+        for (int i = 0; i < 6; ++i) {
+            const void* k = f ? (const void*)tcv_pick<true>(bns[i]) : (const void*)tcv_pick<false>(bns[i]);
+            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcv_smem_bytes(bns[i], tcv_stages_for(bns[i])));
+            if (e != cudaSuccess) return e;
+        }
+    return cudaSuccess;
+}
+// fills the tiling fields of `a` for column-tile width bn
+inline void tcv_plan(TcConvArgs& a, int bn) {
+    a.tiles_t = (a.T + TCV_BM - 1) / TCV_BM;
+    a.tiles_n = (a.N + bn - 1) / bn;
+    a.n_tiles = a.B * a.tiles_t * a.tiles_n;
+    a.kchunks = (a.Cin + TCV_BK - 1) / TCV_BK;
+    a.nst = tcv_stages_for(bn);
+}
+inline bool tcv_vec_ok(const TcConvArgs& a) {
+    auto al = [](const void* p) { return (((uintptr_t)p) & 15) == 0; };
+    return al(a.out16) && al(a.out32) && al(a.res32) && al(a.res16) && al(a.bias) && al(a.gamma) && al(a.alpha) &&
+           a.ld16 % 8 == 0 && a.ld32 % 4 == 0 && a.ldres % 8 == 0;
+}
+// tensor-core launch (maps built by the caller with box rows 128 for A and `bn` for W); persistent grid of <= n_sm CTAs
+inline cudaError_t tcv_launch(cudaStream_t s, int n_sm, bool f16, int bn, const CUtensorMap& mA, const CUtensorMap& mW, TcConvArgs a) {
+    tcv_plan(a, bn);
+    a.vec_ok = tcv_vec_ok(a) ? 1 : 0;
+    if (a.n_tiles <= 0) return cudaSuccess;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(a.n_tiles < n_sm ? a.n_tiles : n_sm); cfg.blockDim = dim3(TCV_THREADS);
+    cfg.dynamicSmemBytes = tcv_smem_bytes(bn, a.nst); cfg.stream = s;
+    tcv_fn k = f16 ? tcv_pick<true>(bn) : tcv_pick<false>(bn);
+    return cudaLaunchKernelEx(&cfg, k, mA, mW, a);
+}
+inline cudaError_t tcv_launch_simt(cudaStream_t s, bool f16, TcConvArgs a) {
+    a.vec_ok = tcv_vec_ok(a) ? 1 : 0;
+    const long long n = (long long)a.B * a.T * ((a.N + 15) / 16);
+    if (n <= 0) return cudaSuccess;
+    const int blocks = (int)((n + 127) / 128);
+    if (f16) tcv_simt_kernel<true><<<blocks, 128, 0, s>>>(a);
+    else tcv_simt_kernel<false><<<blocks, 128, 0, s>>>(a);
+    return cudaGetLastError();
+}

@@ -179,6 +179,28 @@ int fsb_dac_stage(fsb_dac* h, const char* name, void** dptr, size_t* bytes);
 /* algorithmic FLOPs of one decode call (GEMM-shaped work only) */
 double fsb_dac_flops(const fsb_dac* h, int32_t B, int32_t T);
 
+/* ---- stage entry point of the tcgen05 implicit-GEMM conv (csrc/tc_conv.cuh): tests / profiling.
+ *   out[b][t][n] = epi( sum_j sum_k A[b][t - (taps-1-j)*dil][k] * W[j][n][k] ),  rows t < 0 read as zero
+ * = CausalConvNet / CausalTransConvNet (modded_dac.py:521-580) in the channels-last packing of fish_speech_b200/dac.py, and
+ * nn.Linear (taps = 1, W = the state dict's [N][K]).  epi (fp32): [round to the 16-bit type], + bias[n % bias_mod], GELU,
+ * * gamma[n], + residual, tanh | SwiGLU over interleaved (gate, up) columns; out32 = raw fp32, out16 = 16-bit copy with the
+ * consumer's Snake1d (alpha[n % alpha_mod]) applied when alpha != NULL. */
+typedef struct {
+    const void* A16;   /* [B][T][Cin] fp16 (f16 = 1) or bf16 (f16 = 0) */
+    const void* W16;   /* [taps][N][Cin] same type */
+    int32_t B, T, Cin, N, taps, dil;
+    int32_t f16, use_simt; /* use_simt = 1: the CUDA-core twin kernel (also chosen automatically when Cin % 8 != 0) */
+    const float* bias; int32_t bias_mod;
+    const float* gamma;
+    const float* res32; const void* res16; int32_t ldres;
+    const float* alpha; int32_t alpha_mod;
+    int32_t act;       /* 0 none, 1 GELU, 2 tanh, 3 SwiGLU (out16 width N / 2) */
+    int32_t round_lin;
+    void* out16; int32_t ld16;
+    float* out32; int32_t ld32;
+} fsb_tc_conv_args;
+int fsb_tc_conv(const fsb_tc_conv_args* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
