@@ -45,6 +45,7 @@ class TcConvArgs(C.Structure):
         ("res32", C.c_void_p), ("res16", C.c_void_p), ("ldres", C.c_int32),
         ("alpha", C.c_void_p), ("alpha_mod", C.c_int32), ("act", C.c_int32), ("round_lin", C.c_int32),
         ("out16", C.c_void_p), ("ld16", C.c_int32), ("out32", C.c_void_p), ("ld32", C.c_int32),
+        ("out16r", C.c_void_p), ("ld16r", C.c_int32),
     ]
 
 

@@ -7,6 +7,7 @@
 #include <cmath>
 #include <map>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../include/fish_b200.h"
@@ -20,6 +21,13 @@ struct fsb_dac {
     float* buf[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t buf_elems = 0;
     int tf32 = 1;  // 1: GEMM-shaped layers on the tensor cores (TF32 operands, fp32 accumulate); 0: fp32 SIMT (parity anchor)
+    int tc = 1;    // 1: tcgen05 pipeline (csrc/tc_conv.cuh: 16-bit operands, fp32 TMEM accumulation, fp32 residual stream) when the
+                   //    16-bit weights are bound and the device has the tensor-map encoder; 0: the round-1 kernels above
+    int half = 1;  // operand type of the tcgen05 pipeline: 1 fp16 (11-bit significand, as TF32), 0 bf16; set by the host mirror to
+                   //    match the type it packed the ".h" weights in
+    int force_simt = 0;  // tcgen05 pipeline with every GEMM on the CUDA-core twin kernel (cross-check)
+    int n_sm = 148;
+    std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, int>, CUtensorMap> maps;
     std::string err;
 };
 
@@ -86,7 +94,42 @@ struct Runner {
         dim3 grid((T + CG_BM - 1) / CG_BM, (N + CG_BN - 1) / CG_BN, B);
         conv_gemm_kernel<<<grid, 256, 0, s>>>(a);
     }
+    // ---- tcgen05 pipeline: one GEMM-shaped layer.  A16 [B][T][Cin] 16-bit; weight `wn` + ".h" = [taps][N][Cin] 16-bit.
+    const CUtensorMap* map(const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box_rows) {
+        auto key = std::make_tuple(ptr, d0, d1, d2, box_rows, h->half);
+        auto it = h->maps.find(key);
+        if (it != h->maps.end()) return &it->second;
+        CUtensorMap m;
+        if (!tcv_make_map(&m, ptr, h->half != 0, d0, d1, d2, box_rows)) { if (!rc) rc = dfail(h, "cuTensorMapEncodeTiled failed"); return nullptr; }
+        return &h->maps.emplace(key, m).first->second;
+    }
+    void tc(const void* A16, int T, int Cin, int N, int taps, int dil, const std::string& wn, const std::string& bn, int bias_mod,
+            const float* gamma, const float* res32, const float* alpha, int alpha_mod, int act, void* out16, float* out32,
+            const void* res16 = nullptr, void* out16r = nullptr) {
+        TcConvArgs a{};
+        a.B = B; a.T = T; a.N = N; a.Cin = Cin; a.taps = taps; a.dil = dil;
+        a.A16 = A16; a.W16 = W(wn + ".h");
+        a.bias = bn.empty() ? nullptr : W(bn);
+        a.bias_mod = bias_mod > 0 ? bias_mod : N; a.alpha_mod = alpha_mod > 0 ? alpha_mod : N;
+        a.gamma = gamma; a.res32 = res32; a.alpha = alpha; a.act = act;
+        a.out16 = out16; a.out32 = out32; a.ld16 = act == TCV_ACT_SWIGLU ? N / 2 : N; a.ld32 = N; a.ldres = N;
+        a.res16 = res16; a.out16r = out16r; a.ld16r = N;
+        if (rc) return;
+        cudaError_t e;
+        if (h->force_simt || !tcv_tc_ok(Cin, N)) {
+            e = tcv_launch_simt(s, h->half != 0, a);
+        } else {
+            const int bnw = tcv_pick_bn(N);
+            const CUtensorMap* mA = map(A16, (uint64_t)Cin, (uint64_t)T, (uint64_t)B, TCV_BM);
+            const CUtensorMap* mW = map(a.W16, (uint64_t)Cin, (uint64_t)N, (uint64_t)taps, (uint32_t)bnw);
+            if (!mA || !mW) return;
+            e = tcv_launch(s, h->n_sm, h->half != 0, bnw, *mA, *mW, a);
+        }
+        if (e != cudaSuccess && !rc) rc = dfail(h, std::string("tc_conv launch (") + wn + "): " + cudaGetErrorString(e));
+    }
 };
+
+int decode_tc(fsb_dac* h, void* codes, int B, int T, float* wav, cudaStream_t s);
 
 }  // namespace
 
@@ -106,6 +149,11 @@ int fsb_dac_create(const fsb_dac_desc* desc, void* workspace, size_t workspace_b
         d.tf_window > 128 || (d.tf_head_dim != 64 && d.tf_head_dim != 32) || d.latent_dim % 4 || d.decoder_dim % 64)
         return dfail(h, "unsupported DAC shape");
     if (workspace_bytes < fsb_dac_workspace_bytes(desc)) return dfail(h, "workspace too small");
+    {
+        int dev = 0, n_sm = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n_sm > 0)
+            h->n_sm = n_sm;
+    }
     h->buf_elems = (size_t)d.max_batch * d.max_frames * per_frame_elems(d);
     char* p = (char*)workspace;
     for (int i = 0; i < 4; ++i) {
@@ -153,6 +201,9 @@ int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
     if (!h || !name) return 1;
     const std::string n(name);
     if (n == "tf32") h->tf32 = (int)value;
+    else if (n == "tc") h->tc = (int)value;
+    else if (n == "half") { h->half = (int)value; h->maps.clear(); }
+    else if (n == "force_simt") h->force_simt = (int)value;
     else return dfail(h, "unknown option " + n);
     return 0;
 }
@@ -172,6 +223,7 @@ static TcConvArgs tcv_from_abi(const fsb_tc_conv_args& x) {
     TcConvArgs a{};
     a.B = x.B; a.T = x.T; a.N = x.N; a.Cin = x.Cin; a.taps = x.taps; a.dil = x.dil;
     a.A16 = x.A16; a.W16 = x.W16; a.out16 = x.out16; a.out32 = x.out32; a.ld16 = x.ld16; a.ld32 = x.ld32;
+    a.out16r = x.out16r; a.ld16r = x.ld16r;
     a.bias = x.bias; a.gamma = x.gamma; a.res32 = x.res32; a.res16 = x.res16; a.alpha = x.alpha;
     a.bias_mod = x.bias_mod > 0 ? x.bias_mod : x.N; a.alpha_mod = x.alpha_mod > 0 ? x.alpha_mod : x.N; a.ldres = x.ldres;
     a.act = x.act; a.round_lin = x.round_lin;
@@ -179,7 +231,7 @@ static TcConvArgs tcv_from_abi(const fsb_tc_conv_args& x) {
 }
 
 int fsb_tc_conv(const fsb_tc_conv_args* x, void* stream) {
-    if (!x || !x->A16 || !x->W16 || (!x->out16 && !x->out32)) return 1;
+    if (!x || !x->A16 || !x->W16 || (!x->out16 && !x->out32 && !x->out16r)) return 1;
     if (x->B < 1 || x->T < 1 || x->Cin < 1 || x->N < 1 || x->taps < 1 || x->dil < 1) return 1;
     if (x->act == TCV_ACT_SWIGLU && (!x->out16 || (x->N & 1))) return 1;
     TcConvArgs a = tcv_from_abi(*x);
@@ -201,6 +253,7 @@ int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, voi
     const fsb_dac_desc& d = h->d;
     if (B < 1 || B > d.max_batch || T < 1 || T > d.max_frames) return dfail(h, "B/T exceed the workspace (max_batch/max_frames)");
     cudaStream_t s = (cudaStream_t)stream;
+    if (h->tc && h->w.count("dec.in_w.h")) return decode_tc(h, codes, B, T, (float*)wav, s);
     Runner r{h, s, B};
     const int D = d.latent_dim, NQ = d.n_codebooks + 1;
     float *b0 = h->buf[0], *b1 = h->buf[1], *b2 = h->buf[2], *b3 = h->buf[3];
@@ -292,3 +345,115 @@ int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, voi
 }
 
 }  // extern "C"
+
+// =============================================================================================== tcgen05 decode pipeline
+// Same layer plan as fsb_dac_decode above (modded_dac.py:925-927) with every GEMM-shaped layer on tcv_kernel: 16-bit operands
+// written by their producers (GEMM epilogues with the consumer's Snake folded in, or the small fp32 -> 16-bit kernels), fp32
+// residual stream, fp32 accumulation.  Buffers are the handle's four scratch slabs, used as raw bytes.
+namespace {
+
+template <bool F16>
+int decode_tc_t(fsb_dac* h, void* codes, int B, int T, float* wav, cudaStream_t s) {
+    const fsb_dac_desc& d = h->d;
+    if (!h->force_simt) {
+        if (rg_get_encode() == nullptr) return dfail(h, "tensor-map encoder not available (set option tc = 0)");
+        DCK(tcv_set_attrs());
+    }
+    Runner r{h, s, B};
+    const int D = d.latent_dim, NQ = d.n_codebooks + 1;
+    float *b0 = h->buf[0], *b1 = h->buf[1], *b2 = h->buf[2], *b3 = h->buf[3];
+    {   // K11: RVQ dequant -> b0 fp32 [B][T][D]
+        RvqArgs a{};
+        a.codes = (long long*)codes; a.codebooks = r.W("rvq.codebooks"); a.proj_w = r.W("rvq.proj_w");
+        a.proj_b = r.W("rvq.proj_b"); a.z = b0;
+        a.B = B; a.T = T; a.NQ = NQ; a.D = D; a.CD = d.codebook_dim; a.size0 = d.semantic_codebook_size;
+        a.size_rest = d.codebook_size;
+        if (r.rc) return r.rc;
+        rvq_dequant_kernel<<<dim3(T, B), 256, 0, s>>>(a);
+    }
+    // K12: window transformer.  residual stream x32 in b0 / h32 in b3; b1, b2 hold 16-bit operands and the fp32 qkv
+    const int H = d.tf_heads, HD = d.tf_head_dim, F = d.tf_ffn;
+    const long long rows = (long long)B * T;
+    const int nwb = (int)((rows * 32 + 255) / 256);
+    const float* rope = r.W("tf.rope");
+    for (int l = 0; l < d.tf_layers; ++l) {
+        const std::string p = "tf." + std::to_string(l) + ".";
+        const float *an = r.W(p + "attn_norm"), *fn = r.W(p + "ffn_norm"), *g1 = r.W(p + "gamma1"), *g2 = r.W(p + "gamma2");
+        if (r.rc) return r.rc;
+        rmsnorm_rows16_kernel<F16><<<nwb, 256, 0, s>>>(b0, an, b1, rows, D, d.tf_norm_eps);
+        r.tc(b1, T, D, 3 * H * HD, 1, 1, p + "wqkv", "", 0, nullptr, nullptr, nullptr, 0, TCV_ACT_NONE, nullptr, b2);
+        {
+            const long long n = rows * 2 * H * (HD / 2);
+            rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(b2, rope, B, T, H, HD);
+            dim3 grid((T + 3) / 4, H, B);
+            const float scale = 1.f / sqrtf((float)HD);
+            if (HD == 64) window_attn16_kernel<64, F16><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
+            else window_attn16_kernel<32, F16><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
+        }
+        r.tc(b1, T, H * HD, D, 1, 1, p + "wo", "", 0, g1, b0, nullptr, 0, TCV_ACT_NONE, nullptr, b3);      // h = x + gamma1 * wo(y)
+        rmsnorm_rows16_kernel<F16><<<nwb, 256, 0, s>>>(b3, fn, b1, rows, D, d.tf_norm_eps);
+        r.tc(b1, T, D, 2 * F, 1, 1, p + "w13", "", 0, nullptr, nullptr, nullptr, 0, TCV_ACT_SWIGLU, b2, nullptr);  // interleaved gate/up
+        r.tc(b2, T, F, D, 1, 1, p + "w2", "", 0, g2, b3, nullptr, 0, TCV_ACT_NONE, nullptr, b0);            // x = h + gamma2 * w2(..)
+    }
+    {
+        const float* nw = r.W("tf.norm");
+        if (r.rc) return r.rc;
+        rmsnorm_rows16_kernel<F16><<<nwb, 256, 0, s>>>(b0, nw, b1, rows, D, d.tf_norm_eps);
+    }
+    // K13: upsample stages.  16-bit input in b1 -> 16-bit output in b1
+    int len = T;
+    for (int i = 0; i < d.n_up; ++i) {
+        const int f = ups(d, i);
+        const std::string p = "up." + std::to_string(i) + ".";
+        r.tc(b1, len, D, f * D, 1, 1, p + "ct_w", p + "ct_b", D, nullptr, nullptr, nullptr, 0, TCV_ACT_NONE, nullptr, b0);
+        len *= f;
+        const float *dww = r.W(p + "dw_w"), *dwb = r.W(p + "dw_b"), *lw = r.W(p + "ln_w"), *lb = r.W(p + "ln_b");
+        const float* gm = r.W(p + "gamma");
+        if (r.rc) return r.rc;
+        dwconv_ln16_kernel<F16><<<dim3(len, B), 256, D * sizeof(float), s>>>(b0, dww, dwb, lw, lb, b2, len, D);
+        r.tc(b2, len, D, d.convnext_ratio * D, 1, 1, p + "pw1_w", p + "pw1_b", 0, nullptr, nullptr, nullptr, 0, TCV_ACT_GELU, b3, nullptr);
+        r.tc(b3, len, d.convnext_ratio * D, D, 1, 1, p + "pw2_w", p + "pw2_b", 0, gm, b0, nullptr, 0, TCV_ACT_NONE, b1, nullptr);
+    }
+    // K14: conv decoder.  Every producer applies the Snake of its consumer to the 16-bit copy (modded_dac.py:599-620, 712-757)
+    int ch = d.decoder_dim;
+    const int n_blk = d.n_rates;
+    r.tc(b1, len, D, ch, 7, 1, "dec.in_w", "dec.in_b", 0, nullptr, nullptr, r.W("dec.0.alpha"), 0, TCV_ACT_NONE, b0, nullptr);
+    void* cur16 = b0;
+    float* fr[3] = {b1, b2, b3};
+    for (int i = 0; i < n_blk; ++i) {
+        const int st = rates(d, i), co = ch / 2;
+        const std::string p = "dec." + std::to_string(i) + ".";
+        void *X16 = fr[0], *A16 = fr[1], *Y16 = fr[2];  // raw residual stream (16-bit), snaked operand, unit-internal operand
+        r.tc(cur16, len, ch, st * co, 2, 1, p + "ct_w", p + "ct_b", co, nullptr, nullptr, r.W(p + "r0.a1"), co, TCV_ACT_NONE, A16, nullptr,
+             nullptr, X16);
+        len *= st; ch = co;
+        const int dil[3] = {1, 3, 9};
+        for (int j = 0; j < 3; ++j) {
+            const std::string q = p + "r" + std::to_string(j) + ".";
+            r.tc(A16, len, ch, ch, 7, dil[j], q + "w1", q + "b1", 0, nullptr, nullptr, r.W(q + "a2"), 0, TCV_ACT_NONE, Y16, nullptr);
+            const bool last = j == 2;
+            const float* an = !last ? r.W(p + "r" + std::to_string(j + 1) + ".a1")
+                                    : (i + 1 < n_blk ? r.W("dec." + std::to_string(i + 1) + ".alpha") : r.W("dec.out_alpha"));
+            r.tc(Y16, len, ch, ch, 1, 1, q + "w2", q + "b2", 0, nullptr, nullptr, an, 0, TCV_ACT_NONE, A16, nullptr, X16, last ? nullptr : X16);
+        }
+        // the block's output (16-bit, snaked for its consumer) is in A16; the old input buffer becomes free
+        float* old_in = (float*)cur16;
+        cur16 = A16;
+        fr[0] = old_in; fr[1] = (float*)X16; fr[2] = (float*)Y16;
+        if (r.rc) return r.rc;
+    }
+    {
+        const float *ow = r.W("dec.out_w"), *ob = r.W("dec.out_b");
+        if (r.rc) return r.rc;
+        const long long warps = (long long)B * len;
+        conv_out1_16_kernel<F16><<<(int)((warps * 32 + 255) / 256), 256, 0, s>>>(cur16, ow, ob, wav, B, len, ch, 7);
+    }
+    DCK(cudaGetLastError());
+    return r.rc;
+}
+
+int decode_tc(fsb_dac* h, void* codes, int B, int T, float* wav, cudaStream_t s) {
+    return h->half ? decode_tc_t<true>(h, codes, B, T, wav, s) : decode_tc_t<false>(h, codes, B, T, wav, s);
+}
+
+}  // namespace

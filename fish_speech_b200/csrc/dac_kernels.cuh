@@ -417,3 +417,146 @@ __global__ void __launch_bounds__(128) window_attn_kernel(const float* qkv, floa
 #pragma unroll
     for (int e = 0; e < EPL; ++e) y[((size_t)b * T + t) * H * HD + (size_t)h * HD + lane * EPL + e] = o[e] * inv;
 }
+
+// ============================================================================= tcgen05 pipeline: the non-GEMM pieces
+// Data flow of the tensor-core decode path (csrc/tc_conv.cuh): GEMM operands are 16-bit (fp16 or bf16) channels-last
+// tensors written by their producer; the residual stream stays fp32.  These kernels are the fp32 -> 16-bit producers
+// that are not GEMM epilogues.  H = Tcv16<F16> (tc_conv.cuh) converts.
+#include "tc_conv.cuh"
+
+// RMSNorm (modded_dac.py:320-331) of fp32 rows -> 16-bit rows, one warp per row, float4 loads
+template <bool F16>
+__global__ void __launch_bounds__(256) rmsnorm_rows16_kernel(const float* x, const float* w, void* y16, long long rows, int C, float eps) {
+    typedef Tcv16<F16> H;
+    const int lane = threadIdx.x & 31;
+    const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (r >= rows) return;
+    const float* xr = x + r * C;
+    uint16_t* yr = reinterpret_cast<uint16_t*>(y16) + r * C;
+    float ss = 0.f;
+    if ((C & 3) == 0) {
+        for (int c = lane * 4; c < C; c += 128) { const float4 v = *reinterpret_cast<const float4*>(xr + c); ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
+    } else {
+        for (int c = lane; c < C; c += 32) ss += xr[c] * xr[c];
+    }
+    ss = warp_sum(ss);
+    const float rs = rsqrtf(ss / C + eps);
+    if ((C & 3) == 0) {
+        for (int c = lane * 4; c < C; c += 128) {
+            const float4 v = *reinterpret_cast<const float4*>(xr + c), g = __ldg(reinterpret_cast<const float4*>(w + c));
+            const uint32_t lo = (uint32_t)H::pack(v.x * rs * g.x) | ((uint32_t)H::pack(v.y * rs * g.y) << 16);
+            const uint32_t hi = (uint32_t)H::pack(v.z * rs * g.z) | ((uint32_t)H::pack(v.w * rs * g.w) << 16);
+            *reinterpret_cast<uint2*>(yr + c) = make_uint2(lo, hi);
+        }
+    } else {
+        for (int c = lane; c < C; c += 32) yr[c] = H::pack(xr[c] * rs * w[c]);
+    }
+}
+
+// ConvNeXt front half (rvq.py:173-179) fp32 in -> 16-bit out; one CTA per (b, t) row
+template <bool F16>
+__global__ void __launch_bounds__(256) dwconv_ln16_kernel(const float* x, const float* dw_w, const float* dw_b, const float* ln_w,
+                                                          const float* ln_b, void* y16, int T, int C) {
+    typedef Tcv16<F16> H;
+    extern __shared__ float v[];  // [C]
+    __shared__ float red[32];
+    const int t = blockIdx.x, b = blockIdx.y;
+    float s = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float acc = dw_b[c];
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+            const int tt = t - 6 + j;
+            if (tt >= 0) acc = fmaf(x[((size_t)b * T + tt) * C + c], dw_w[c * 7 + j], acc);
+        }
+        v[c] = acc;
+        s += acc;
+    }
+    const float mean = block_sum(s, red) / C;
+    float q = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) { const float d = v[c] - mean; q += d * d; }
+    const float var = block_sum(q, red) / C;
+    const float rs = rsqrtf(var + 1e-6f);
+    uint16_t* yr = reinterpret_cast<uint16_t*>(y16) + ((size_t)b * T + t) * C;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) yr[c] = H::pack((v[c] - mean) * rs * ln_w[c] + ln_b[c]);
+}
+
+// window attention as window_attn_kernel, output rows in the 16-bit operand type (the wo GEMM reads them)
+template <int HD, bool F16>
+__global__ void __launch_bounds__(128) window_attn16_kernel(const float* qkv, void* y16, int B, int T, int H, int window, float scale) {
+    typedef Tcv16<F16> Hh;
+    constexpr int EPL = HD / 32;
+    constexpr int MAXI = 4;  // window <= 128
+    __shared__ float qs[4][HD];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int t = blockIdx.x * 4 + w, h = blockIdx.y, b = blockIdx.z;
+    if (t >= T) return;
+    const size_t rs = (size_t)3 * H * HD;
+    const float* base = qkv + (size_t)b * T * rs;
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) qs[w][lane * EPL + i] = base[(size_t)t * rs + (size_t)h * HD + lane * EPL + i];
+    __syncwarp();
+    const int start = max(0, t - window + 1), n = t - start + 1;
+    float sc[MAXI], mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+        const int j = lane + 32 * i;
+        sc[i] = -INFINITY;
+        if (j < n) {
+            const float4* k = reinterpret_cast<const float4*>(base + (size_t)(start + j) * rs + (size_t)(H + h) * HD);
+            float d = 0.f;
+#pragma unroll
+            for (int e = 0; e < HD / 4; ++e) {
+                const float4 kv = k[e];
+                d = fmaf(qs[w][4 * e], kv.x, d); d = fmaf(qs[w][4 * e + 1], kv.y, d);
+                d = fmaf(qs[w][4 * e + 2], kv.z, d); d = fmaf(qs[w][4 * e + 3], kv.w, d);
+            }
+            sc[i] = d * scale;
+            mx = fmaxf(mx, sc[i]);
+        }
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) { sc[i] = (sc[i] == -INFINITY) ? 0.f : expf(sc[i] - mx); sum += sc[i]; }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    float o[EPL];
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) o[i] = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+        for (int src = 0; src < 32; ++src) {
+            const int j = src + 32 * i;
+            if (j >= n) break;  // uniform across the warp
+            const float p = __shfl_sync(0xffffffffu, sc[i], src);
+            const float* v = base + (size_t)(start + j) * rs + (size_t)(2 * H + h) * HD + lane * EPL;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) o[e] = fmaf(p, v[e], o[e]);
+        }
+    }
+    uint16_t* yr = reinterpret_cast<uint16_t*>(y16) + ((size_t)b * T + t) * H * HD + (size_t)h * HD + lane * EPL;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) yr[e] = Hh::pack(o[e] * inv);
+}
+
+// Final conv (Cout = 1) + tanh over the already-snaked 16-bit input (modded_dac.py:793-795): one warp per output sample
+template <bool F16>
+__global__ void __launch_bounds__(256) conv_out1_16_kernel(const void* A16, const float* W, const float* bias, float* out, int B, int T,
+                                                           int Cin, int taps) {
+    typedef Tcv16<F16> H;
+    const int lane = threadIdx.x & 31;
+    const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= (long long)B * T) return;
+    const int b = (int)(gw / T), t = (int)(gw % T);
+    const uint16_t* A = reinterpret_cast<const uint16_t*>(A16);
+    float s = 0.f;
+    for (int j = 0; j < taps; ++j) {
+        const int tt = t - (taps - 1 - j);
+        if (tt < 0) continue;
+        const uint16_t* row = A + ((size_t)b * T + tt) * Cin;
+        for (int k = lane; k < Cin; k += 32) s = fmaf(H::unpack(row[k]), __ldg(W + (size_t)j * Cin + k), s);
+    }
+    s = warp_sum(s);
+    if (lane == 0) out[(size_t)b * T + t] = tanhf(s + (bias ? bias[0] : 0.f));
+}

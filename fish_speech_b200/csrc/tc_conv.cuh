@@ -30,7 +30,8 @@
 
 #define TCV_BM 128
 #define TCV_BK 64
-#define TCV_THREADS 192
+#define TCV_EPI_WARPS 8          // two per TMEM lane quadrant: the quadrant's rows, alternate column blocks
+#define TCV_THREADS (64 + 32 * TCV_EPI_WARPS)
 #define TCV_STAGES_MAX 8
 #define TCV_A_BYTES (TCV_BM * TCV_BK * 2)
 #define TCV_POLICY_EVICT_NORMAL 0x1000000000000000ull
@@ -45,8 +46,9 @@ struct TcConvArgs {
     const void* W16;     // [taps][N][Cin] 16-bit
     // ---- epilogue
     void* out16;         // [B*T][ld16] 16-bit copy (snaked when alpha != nullptr), or nullptr
+    void* out16r;        // [B*T][ld16r] raw 16-bit copy (never snaked: the residual stream of the decoder blocks), or nullptr
     float* out32;        // [B*T][ld32] fp32 copy (never snaked), or nullptr
-    int ld16, ld32;
+    int ld16, ld16r, ld32;
     const float* bias;   // [bias_mod] or nullptr (transposed conv: bias_mod = Cout, N = stride * Cout)
     const float* gamma;  // [N] or nullptr
     const float* res32;  // [B*T][ldres] fp32 residual, may alias out32, or nullptr
@@ -79,111 +81,118 @@ __device__ __forceinline__ float tcv_snake(float x, float a) {
 }
 __device__ __forceinline__ float tcv_gelu(float v) { return 0.5f * v * (1.f + erff(v * 0.70710678118654752f)); }
 
-// ----------------------------------------------------------------------------- epilogue of 16 consecutive columns of one row
-// v[i] = reduction of column n0 + i of row `row` (global row index b*T + t); nv = valid columns (16 except at a ragged edge)
-template <bool F16>
-__device__ __forceinline__ void tcv_epilogue16(const TcConvArgs& a, size_t row, int n0, float (&v)[16], int nv) {
+// ----------------------------------------------------------------------------- epilogue of NC consecutive columns of one row
+// Per-column parameters of the block (index 0 = column n0), neutral where absent (bias 0, gamma 1): shared memory in the
+// tensor-core kernel (staged once per column tile, read as broadcasts), a few registers in the CUDA-core twin.
+struct TcvParams { const float *bias, *gamma, *alpha, *ainv; };
+
+// v[i] = reduction of column n0 + i of row `row` (global row index b*T + t); nv = valid columns (NC except at a ragged edge).
+// Everything is unrolled with compile-time indices (a run-time loop over v[] would put it in local memory).
+template <bool F16, int NC>
+__device__ __forceinline__ void tcv_epilogue(const TcConvArgs& a, const TcvParams& p, size_t row, int n0, float (&v)[NC], int nv) {
     typedef Tcv16<F16> H;
-    const bool vec = (nv == 16) && a.vec_ok;
+    const bool vec = (nv == NC) && a.vec_ok;
     if (a.round_lin) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = H::unpack(H::pack(v[i]));
+        for (int i = 0; i < NC; ++i) v[i] = H::unpack(H::pack(v[i]));
     }
-    if (a.bias) {
-        if (vec && (a.bias_mod & 15) == 0) {
-            const float4* bp = reinterpret_cast<const float4*>(a.bias + (n0 % a.bias_mod));
 #pragma unroll
-            for (int q = 0; q < 4; ++q) { const float4 b4 = __ldg(bp + q); v[4 * q] += b4.x; v[4 * q + 1] += b4.y; v[4 * q + 2] += b4.z; v[4 * q + 3] += b4.w; }
-        } else {
-            for (int i = 0; i < nv; ++i) v[i] += __ldg(a.bias + ((n0 + i) % a.bias_mod));
-        }
-    }
+    for (int i = 0; i < NC; ++i) v[i] += p.bias[i];
     if (a.act == TCV_ACT_GELU) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = tcv_gelu(v[i]);
+        for (int i = 0; i < NC; ++i) v[i] = tcv_gelu(v[i]);
     }
-    if (a.act == TCV_ACT_SWIGLU) {  // (gate, up) pairs -> 8 outputs at columns n0 / 2 ..
-        uint16_t o[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float g = v[2 * i], u = v[2 * i + 1];
-            o[i] = H::pack(__fdividef(g, 1.f + __expf(-g)) * u);
-        }
+    if (a.act == TCV_ACT_SWIGLU) {  // (gate, up) pairs -> NC / 2 outputs at columns n0 / 2 ..
         uint16_t* dst = reinterpret_cast<uint16_t*>(a.out16) + row * a.ld16 + (n0 >> 1);
+        uint32_t w[NC / 4];
+#pragma unroll
+        for (int q = 0; q < NC / 4; ++q) {
+            const float g0 = v[4 * q], u0 = v[4 * q + 1], g1 = v[4 * q + 2], u1 = v[4 * q + 3];
+            w[q] = (uint32_t)H::pack(__fdividef(g0, 1.f + __expf(-g0)) * u0) | ((uint32_t)H::pack(__fdividef(g1, 1.f + __expf(-g1)) * u1) << 16);
+        }
         if (vec) {
-            *reinterpret_cast<uint4*>(dst) = make_uint4(o[0] | ((uint32_t)o[1] << 16), o[2] | ((uint32_t)o[3] << 16),
-                                                        o[4] | ((uint32_t)o[5] << 16), o[6] | ((uint32_t)o[7] << 16));
+#pragma unroll
+            for (int q = 0; q < NC / 16; ++q) *reinterpret_cast<uint4*>(dst + 8 * q) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
         } else {
-            for (int i = 0; i < nv / 2; ++i) dst[i] = o[i];
+#pragma unroll
+            for (int i = 0; i < NC / 2; ++i)
+                if (2 * i + 1 < nv) dst[i] = (uint16_t)((i & 1) ? (w[i >> 1] >> 16) : (w[i >> 1] & 0xffffu));
         }
         return;
     }
-    if (a.gamma) {
-        if (vec) {
-            const float4* gp = reinterpret_cast<const float4*>(a.gamma + n0);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) { const float4 g4 = __ldg(gp + q); v[4 * q] *= g4.x; v[4 * q + 1] *= g4.y; v[4 * q + 2] *= g4.z; v[4 * q + 3] *= g4.w; }
-        } else {
-            for (int i = 0; i < nv; ++i) v[i] *= __ldg(a.gamma + n0 + i);
-        }
-    }
+    for (int i = 0; i < NC; ++i) v[i] *= p.gamma[i];
     if (a.res32) {
         const float* rp = a.res32 + row * a.ldres + n0;
         if (vec) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) { const float4 r4 = *reinterpret_cast<const float4*>(rp + 4 * q); v[4 * q] += r4.x; v[4 * q + 1] += r4.y; v[4 * q + 2] += r4.z; v[4 * q + 3] += r4.w; }
+            for (int q = 0; q < NC / 4; ++q) { const float4 r4 = *reinterpret_cast<const float4*>(rp + 4 * q); v[4 * q] += r4.x; v[4 * q + 1] += r4.y; v[4 * q + 2] += r4.z; v[4 * q + 3] += r4.w; }
         } else {
-            for (int i = 0; i < nv; ++i) v[i] += rp[i];
+#pragma unroll
+            for (int i = 0; i < NC; ++i)
+                if (i < nv) v[i] += rp[i];
         }
     } else if (a.res16) {
         const uint16_t* rp = reinterpret_cast<const uint16_t*>(a.res16) + row * a.ldres + n0;
         if (vec) {
-            const uint4 r0 = *reinterpret_cast<const uint4*>(rp), r1 = *reinterpret_cast<const uint4*>(rp + 8);
-            const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
-            for (int q = 0; q < 8; ++q) { v[2 * q] += H::unpack((uint16_t)(w[q] & 0xffffu)); v[2 * q + 1] += H::unpack((uint16_t)(w[q] >> 16)); }
+            for (int q = 0; q < NC / 8; ++q) {
+                const uint4 r = *reinterpret_cast<const uint4*>(rp + 8 * q);
+                v[8 * q] += H::unpack((uint16_t)(r.x & 0xffffu)); v[8 * q + 1] += H::unpack((uint16_t)(r.x >> 16));
+                v[8 * q + 2] += H::unpack((uint16_t)(r.y & 0xffffu)); v[8 * q + 3] += H::unpack((uint16_t)(r.y >> 16));
+                v[8 * q + 4] += H::unpack((uint16_t)(r.z & 0xffffu)); v[8 * q + 5] += H::unpack((uint16_t)(r.z >> 16));
+                v[8 * q + 6] += H::unpack((uint16_t)(r.w & 0xffffu)); v[8 * q + 7] += H::unpack((uint16_t)(r.w >> 16));
+            }
         } else {
-            for (int i = 0; i < nv; ++i) v[i] += H::unpack(rp[i]);
+#pragma unroll
+            for (int i = 0; i < NC; ++i)
+                if (i < nv) v[i] += H::unpack(rp[i]);
         }
     }
     if (a.act == TCV_ACT_TANH) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = tanhf(v[i]);
+        for (int i = 0; i < NC; ++i) v[i] = tanhf(v[i]);
     }
     if (a.out32) {
         float* op = a.out32 + row * a.ld32 + n0;
         if (vec) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) *reinterpret_cast<float4*>(op + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+            for (int q = 0; q < NC / 4; ++q) *reinterpret_cast<float4*>(op + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
         } else {
-            for (int i = 0; i < nv; ++i) op[i] = v[i];
+#pragma unroll
+            for (int i = 0; i < NC; ++i)
+                if (i < nv) op[i] = v[i];
         }
     }
-    if (a.out16) {
-        if (a.alpha) {
-            if (vec && (a.alpha_mod & 15) == 0) {
-                const float4* ap = reinterpret_cast<const float4*>(a.alpha + (n0 % a.alpha_mod));
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float4 a4 = __ldg(ap + q);
-                    v[4 * q] = tcv_snake(v[4 * q], a4.x); v[4 * q + 1] = tcv_snake(v[4 * q + 1], a4.y);
-                    v[4 * q + 2] = tcv_snake(v[4 * q + 2], a4.z); v[4 * q + 3] = tcv_snake(v[4 * q + 3], a4.w);
-                }
-            } else {
-                for (int i = 0; i < nv; ++i) v[i] = tcv_snake(v[i], __ldg(a.alpha + ((n0 + i) % a.alpha_mod)));
-            }
+    for (int pass = 0; pass < 2; ++pass) {  // 0: raw 16-bit copy (residual stream), 1: the consumer's operand (Snake applied)
+        uint16_t* base = reinterpret_cast<uint16_t*>(pass == 0 ? a.out16r : a.out16);
+        if (base == nullptr) continue;
+        if (pass == 1 && a.alpha) {
+#pragma unroll
+            for (int i = 0; i < NC; ++i) { const float sn = __sinf(p.alpha[i] * v[i]); v[i] = fmaf(p.ainv[i] * sn, sn, v[i]); }
         }
-        uint16_t* op = reinterpret_cast<uint16_t*>(a.out16) + row * a.ld16 + n0;
+        uint16_t* op = base + row * (pass == 0 ? a.ld16r : a.ld16) + n0;
         if (vec) {
-            uint32_t w[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) w[q] = (uint32_t)H::pack(v[2 * q]) | ((uint32_t)H::pack(v[2 * q + 1]) << 16);
-            *reinterpret_cast<uint4*>(op) = make_uint4(w[0], w[1], w[2], w[3]);
-            *reinterpret_cast<uint4*>(op + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+            for (int q = 0; q < NC / 8; ++q)
+                *reinterpret_cast<uint4*>(op + 8 * q) =
+                    make_uint4((uint32_t)H::pack(v[8 * q]) | ((uint32_t)H::pack(v[8 * q + 1]) << 16), (uint32_t)H::pack(v[8 * q + 2]) | ((uint32_t)H::pack(v[8 * q + 3]) << 16),
+                               (uint32_t)H::pack(v[8 * q + 4]) | ((uint32_t)H::pack(v[8 * q + 5]) << 16), (uint32_t)H::pack(v[8 * q + 6]) | ((uint32_t)H::pack(v[8 * q + 7]) << 16));
         } else {
-            for (int i = 0; i < nv; ++i) op[i] = H::pack(v[i]);
+#pragma unroll
+            for (int i = 0; i < NC; ++i)
+                if (i < nv) op[i] = H::pack(v[i]);
         }
     }
+}
+// per-column parameter values of column n (neutral when the array is absent or n is past the end)
+__device__ __forceinline__ void tcv_param(const TcConvArgs& a, int n, float& bias, float& gamma, float& alpha, float& ainv) {
+    const bool in = n < a.N;
+    bias = (a.bias && in) ? __ldg(a.bias + (n % a.bias_mod)) : 0.f;
+    gamma = (a.gamma && in) ? __ldg(a.gamma + n) : 1.f;
+    alpha = (a.alpha && in) ? __ldg(a.alpha + (n % a.alpha_mod)) : 0.f;
+    ainv = __fdividef(1.f, alpha + 1e-9f);
 }
 
 // ----------------------------------------------------------------------------- the tensor-core kernel
@@ -191,6 +200,7 @@ __host__ __device__ constexpr uint32_t tcv_stage_bytes(int bn) { return (uint32_
 __host__ __device__ constexpr int tcv_tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512; }
 inline size_t tcv_smem_bytes(int bn, int nst) { return (size_t)nst * tcv_stage_bytes(bn) + 1024; }
 
+__device__ __forceinline__ void tcv_epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(32 * TCV_EPI_WARPS) : "memory"); }
 __device__ __forceinline__ void tcv_tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, uint64_t policy) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4, %5}], [%2], %6;"
@@ -209,6 +219,7 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
     extern __shared__ uint8_t tcv_smem_raw[];
     __shared__ uint64_t full_bar[TCV_STAGES_MAX], empty_bar[TCV_STAGES_MAX], tfull_bar[2], tempty_bar[2];
     __shared__ uint32_t tmem_base_s;
+    __shared__ __align__(16) float ep_bias[BN], ep_gamma[BN], ep_alpha[BN], ep_ainv[BN];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t sbase = (smem_u32(tcv_smem_raw) + 1023u) & ~1023u;
@@ -276,28 +287,39 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             __syncwarp();
         }
     } else {
-        // ===== epilogue: warp w owns TMEM lanes 32*(w%4) .. +31; one thread = one time row of the tile
-        const int et = tid - 64, lg = warp & 3;
+        // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 (one thread = one time row of the tile); the two warps
+        // of a lane quadrant take alternate column blocks.  Per-column parameters come from shared memory (broadcast reads):
+        // a global load per block on this dependent chain cost more than the tile's MMAs (ncu: long-scoreboard stalls).
+        constexpr int NCB = (BN % 64 == 0) ? 32 : 16, NBLK = BN / NCB;
+        const int et = tid - 64, lg = warp & 3, half = (warp - 2) >> 2;
         const uint32_t tlane = (uint32_t)(lg * 32) << 16;
         uint32_t iseg = 0;
+        int tn_loaded = -1;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
             const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
             const int t = tt * TCV_BM + lg * 32 + lane, n0 = tn * BN;
+            if (tn != tn_loaded) {  // uniform over the epilogue threads; everyone is past the previous tile (barrier below)
+                for (int i = et; i < BN; i += 32 * TCV_EPI_WARPS) tcv_param(a, n0 + i, ep_bias[i], ep_gamma[i], ep_alpha[i], ep_ainv[i]);
+                tn_loaded = tn;
+                tcv_epi_bar();
+            }
             const uint32_t buf = iseg & 1u;
             mbar_wait(&tfull_bar[buf], (iseg >> 1) & 1u);
             tc_fence_after();
             const uint32_t tacc = tmem + tlane + buf * BN;
             const size_t row = (size_t)b * a.T + t;
 #pragma unroll 1
-            for (int ch = 0; ch < BN / 16; ++ch) {
-                const int nc = n0 + ch * 16;
-                if (nc >= a.N) break;  // uniform across the CTA
-                float v[16];
-                tc_ld16(tacc + (uint32_t)(ch * 16), v);
-                if (t < a.T) tcv_epilogue16<F16>(a, row, nc, v, min(16, a.N - nc));
+            for (int k = half; k < NBLK; k += 2) {
+                const int nc = n0 + k * NCB;
+                if (nc >= a.N) break;  // uniform
+                float v[NCB];
+                if (NCB == 32) tc_ld32(tacc + (uint32_t)(k * NCB), reinterpret_cast<float(&)[32]>(v));
+                else tc_ld16(tacc + (uint32_t)(k * NCB), reinterpret_cast<float(&)[16]>(v));
+                const TcvParams ps{ep_bias + k * NCB, ep_gamma + k * NCB, ep_alpha + k * NCB, ep_ainv + k * NCB};
+                if (t < a.T) tcv_epilogue<F16, NCB>(a, ps, row, nc, v, min(NCB, a.N - nc));
             }
             tc_fence_before();
-            rg_epi_bar();
+            tcv_epi_bar();
             if (et == 0) mbar_arrive(&tempty_bar[buf]);
         }
     }
@@ -338,7 +360,11 @@ __global__ void __launch_bounds__(128) tcv_simt_kernel(TcConvArgs a) {
                 if (i < nv) v[i] = fmaf(x, H::unpack(wj[(size_t)i * a.Cin + k]), v[i]);
         }
     }
-    tcv_epilogue16<F16>(a, (size_t)b * a.T + t, n0, v, nv);
+    float pb[16], pg[16], pa[16], pi[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tcv_param(a, n0 + i, pb[i], pg[i], pa[i], pi[i]);
+    const TcvParams ps{pb, pg, pa, pi};
+    tcv_epilogue<F16, 16>(a, ps, (size_t)b * a.T + t, n0, v, nv);
 }
 
 // ----------------------------------------------------------------------------- host side
@@ -381,7 +407,7 @@ inline tcv_fn tcv_pick(int bn) {
     }
 }
 inline int tcv_stages_for(int bn) {
-    const int fit = (int)((225 * 1024 - 1024) / tcv_stage_bytes(bn));
+    const int fit = (int)((225 * 1024 - 1024 - 16 * bn - 256) / tcv_stage_bytes(bn));  // static: 4 parameter rows + barriers
     return fit < TCV_STAGES_MAX ? fit : TCV_STAGES_MAX;
 }
 inline cudaError_t tcv_set_attrs() {
@@ -405,7 +431,7 @@ inline void tcv_plan(TcConvArgs& a, int bn) {
 }
 inline bool tcv_vec_ok(const TcConvArgs& a) {
     auto al = [](const void* p) { return (((uintptr_t)p) & 15) == 0; };
-    return al(a.out16) && al(a.out32) && al(a.res32) && al(a.res16) && al(a.bias) && al(a.gamma) && al(a.alpha) &&
+    return al(a.out16) && al(a.out16r) && a.ld16r % 8 == 0 && al(a.out32) && al(a.res32) && al(a.res16) &&
            a.ld16 % 8 == 0 && a.ld32 % 4 == 0 && a.ldres % 8 == 0;
 }
 // tensor-core launch (maps built by the caller with box rows 128 for A and `bn` for W); persistent grid of <= n_sm CTAs

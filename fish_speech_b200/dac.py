@@ -225,7 +225,8 @@ def synthetic_state_dict(c: "DACConfig", seed: int = 0, device="cpu") -> Dict[st
 class DACB200:
     """Engine-backed stand-in for modded_dac.DAC on the decode side."""
 
-    def __init__(self, config, state_dict: Dict[str, Tensor], device="cuda:0", max_batch: int = 4, max_frames: int = 1024):
+    def __init__(self, config, state_dict: Dict[str, Tensor], device="cuda:0", max_batch: int = 4, max_frames: int = 1024,
+                 operand: str = "f16"):
         _lib.require_cuda()
         self.lib = _lib.load()
         self.config = c = DACConfig.from_any(config)
@@ -252,8 +253,23 @@ class DACB200:
             dev_sd = {k: v.to(self.device) for k, v in state_dict.items()}
             self.weights = {k: v.to(self.device, torch.float32).contiguous()
                             for k, v in pack_weights(c, dev_sd, self.max_frames).items()}
+            # tcgen05 pipeline: every GEMM weight again as [taps][N][Cin] in the 16-bit operand type (K-major rows, what a TMA
+            # box reads); the transformer's gate/up matrix with its columns interleaved (SwiGLU in the GEMM epilogue)
+            self.operand = operand
+            hdt = torch.float16 if operand == "f16" else torch.bfloat16
+            for k in [k for k, v in self.weights.items() if v.dim() == 3 and k != "dec.out_w"] + \
+                     [k for k in self.weights if k.startswith("tf.") and k.split(".")[-1] in ("wqkv", "wo", "w13", "w2")] + \
+                     [k for k in self.weights if k.endswith(("pw1_w", "pw2_w"))]:
+                w = self.weights[k]
+                w = w[None] if w.dim() == 2 else w                      # [taps][Cin][N]
+                w = w.permute(0, 2, 1)                                  # [taps][N][Cin]
+                if k.endswith("w13"):
+                    F_ = w.shape[1] // 2
+                    w = torch.stack([w[:, :F_], w[:, F_:]], dim=2).reshape(w.shape[0], 2 * F_, w.shape[2])
+                self.weights[k + ".h"] = w.to(hdt).contiguous()
             for k, v in self.weights.items():
                 self._ck(self.lib.fsb_dac_bind_weight(self._h, k.encode(), v.data_ptr(), v.numel()))
+            self.set_option("half", 1 if operand == "f16" else 0)
 
     def _ck(self, rc: int):
         if rc != 0:
@@ -268,7 +284,9 @@ class DACB200:
             pass
 
     def set_option(self, name: str, value: int):
-        """"tf32": 1 = tensor-core GEMMs with TF32 operands (default), 0 = fp32 CUDA-core path (parity anchor)."""
+        """"tc": 1 = tcgen05 pipeline (default: 16-bit operands of the type chosen at construction, fp32 accumulation and
+        residual stream), 0 = the round-1 kernels, for which "tf32": 1 = mma.sync TF32 GEMMs, 0 = fp32 CUDA-core path (parity
+        anchor); "force_simt": 1 = the tcgen05 pipeline's data flow with its CUDA-core twin kernel (cross-check)."""
         self._ck(self.lib.fsb_dac_set_option(self._h, name.encode(), int(value)))
 
     def flops(self, B: int, T: int) -> float:

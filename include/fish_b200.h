@@ -198,6 +198,7 @@ typedef struct {
     int32_t round_lin;
     void* out16; int32_t ld16;
     float* out32; int32_t ld32;
+    void* out16r; int32_t ld16r; /* optional raw 16-bit copy (no Snake): the residual stream of the decoder blocks */
 } fsb_tc_conv_args;
 int fsb_tc_conv(const fsb_tc_conv_args* a, void* stream);
 

@@ -26,21 +26,24 @@ def _dt(f16):
 
 
 def _run(lib, A, W, f16, dil=1, simt=0, bias=None, bias_mod=0, gamma=None, res32=None, res16=None, alpha=None, alpha_mod=0,
-         act=0, round_lin=0, want32=True, want16=True):
+         act=0, round_lin=0, want32=True, want16=True, want16r=False):
     from fish_speech_b200._lib import TcConvArgs
     B, T, Cin = A.shape
     taps, N, _ = W.shape
     n16 = N // 2 if act == 3 else N
     out16 = torch.full((B, T, n16), 7.0, dtype=_dt(f16), device="cuda") if want16 else None
     out32 = torch.full((B, T, N), 7.0, dtype=torch.float32, device="cuda") if (want32 and act != 3) else None
+    out16r = torch.full((B, T, N), 7.0, dtype=_dt(f16), device="cuda") if want16r else None
     p = lambda t: None if t is None else t.data_ptr()
     a = TcConvArgs(A16=p(A), W16=p(W), B=B, T=T, Cin=Cin, N=N, taps=taps, dil=dil, f16=int(f16), use_simt=simt,
                    bias=p(bias), bias_mod=bias_mod, gamma=p(gamma), res32=p(res32), res16=p(res16), ldres=N,
                    alpha=p(alpha), alpha_mod=alpha_mod, act=act, round_lin=round_lin, out16=p(out16), ld16=n16,
-                   out32=p(out32), ld32=N)
+                   out32=p(out32), ld32=N, out16r=p(out16r), ld16r=N)
     rc = lib.fsb_tc_conv(C.byref(a), torch.cuda.current_stream().cuda_stream)
     assert rc == 0, rc
     torch.cuda.synchronize()
+    if want16r:
+        return out32, out16, out16r
     return out32, out16
 
 
@@ -152,3 +155,29 @@ def test_tc_conv_prompt_pass_linear_bf16_rounding(lib, T, N, K):
     exact = float((o2.float() == ref2).float().mean())
     print(f"[parity] tc_conv linear+residual T={T} N={N} K={K}: bit-identical to the fp32 reference in {exact:.4f} of the outputs")
     assert exact > 0.9
+
+
+@pytest.mark.parametrize("f16", [1, 0])
+def test_tc_conv_16bit_residual_stream_in_place(lib, f16):
+    """ResidualUnit's second conv as the decoder blocks run it (modded_dac.py:599-620): 16-bit residual in, raw 16-bit result
+    written IN PLACE over the residual, and the consumer's snaked copy; ragged T, N = 96 (16-column blocks) and 192."""
+    for N in (96, 192):
+        g = torch.Generator().manual_seed(N + f16)
+        dt = _dt(f16)
+        B, T = 2, 700
+        A = torch.randn(B, T, N, generator=g).to(dt).cuda()
+        W = (torch.randn(1, N, N, generator=g) / N ** 0.5).to(dt).cuda()
+        bias = (torch.randn(N, generator=g) * 0.1).cuda()
+        alpha = (0.5 + torch.rand(N, generator=g)).cuda()
+        res = torch.randn(B, T, N, generator=g).to(dt).cuda()
+        y_ref, z_ref = _ref(A, W, bias=bias, res=res, alpha=alpha)
+        from fish_speech_b200._lib import TcConvArgs
+        x = res.clone()
+        out16 = torch.empty(B, T, N, dtype=dt, device="cuda")
+        a = TcConvArgs(A16=A.data_ptr(), W16=W.data_ptr(), B=B, T=T, Cin=N, N=N, taps=1, dil=1, f16=int(f16), use_simt=0,
+                       bias=bias.data_ptr(), bias_mod=0, gamma=None, res32=None, res16=x.data_ptr(), ldres=N, alpha=alpha.data_ptr(),
+                       alpha_mod=0, act=0, round_lin=0, out16=out16.data_ptr(), ld16=N, out32=None, ld32=N, out16r=x.data_ptr(), ld16r=N)
+        assert lib.fsb_tc_conv(C.byref(a), torch.cuda.current_stream().cuda_stream) == 0
+        torch.cuda.synchronize()
+        _close(x, y_ref, f16, 1.0, f"in-place raw stream N={N}")
+        _close(out16, z_ref, f16, 1.0, f"snaked copy N={N}")
