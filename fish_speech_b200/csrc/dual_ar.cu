@@ -96,6 +96,11 @@ struct fsb_dual_ar {
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
     int use_mega = 1;                // batch-1 frames as ONE persistent cooperative kernel (frame_mega.cuh)
+    int mega_skip_dot = 0;           // experiment (results are garbage): no dot products in the frame kernel
+    int mega_detail_op = -1;         // profiling: op index whose per-iteration stamps are recorded (frame kernel)
+    int mega_mma = 0;                // frame kernel: GEMV dot products through mma.sync tiles (frame_mega.cuh: mg_dot_mma); measured no
+                                     // faster than the FMA loop (legacy HMMA issue rate), off
+    int mega_l2_ahead = 0;           // frame kernel: stages per producer lane prefetched into L2 while the ring is full
     bool mega_supported = false;     // shape fits the frame kernel's stage geometry and it is resident at 1 CTA/SM
     MegaPlan mega_plan{};
     std::vector<char> mega_host;
@@ -926,7 +931,14 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     p.fend = (const FrameEndArgs*)(h->mega_buf + o_f); p.sync = h->mega_sync;
     p.prof = h->mega_prof_on ? h->mega_prof : nullptr;
     p.hot = (const uint4*)(h->mega_buf + o_h); p.n_hot = (int)mb.hot.size(); p.n_attn_slow = d.n_layer;
+    p.l2_ahead = h->mega_l2_ahead;
+    p.use_mma = h->mega_mma;
     p.trace = (h->mega_trace_on && (size_t)h->n_sm * mb.ops.size() * 4 <= MEGA_TRACE_WORDS) ? h->mega_trace : nullptr;
+    p.detail_op = h->mega_detail_op;
+    p.skip_dot = h->mega_skip_dot;
+    p.detail_gemv = (h->mega_detail_op >= 0 && h->mega_detail_op < (int)mb.ops.size() && mb.ops[h->mega_detail_op].type == MOP_GEMV) ? mb.ops[h->mega_detail_op].idx : -1;
+    p.detail = (p.trace && h->mega_detail_op >= 0 && (size_t)h->n_sm * (mb.ops.size() * 4 + 64) <= MEGA_TRACE_WORDS)
+                   ? h->mega_trace + (size_t)h->n_sm * mb.ops.size() * 4 : nullptr;  // behind the op stamps
     return 0;
 }
 
@@ -1099,6 +1111,10 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "rows_narrow") h->rows_narrow = (int)value;
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
+    else if (n == "mega_l2_ahead") h->mega_l2_ahead = (int)value;
+    else if (n == "mega_mma") h->mega_mma = (int)value;
+    else if (n == "mega_detail_op") h->mega_detail_op = (int)value;
+    else if (n == "mega_skip_dot") h->mega_skip_dot = (int)value;
     else if (n == "attn_trace_point") h->attn_trace_point = (int)value;
     else if (n == "spin_ns") {  // poll back-off of tagged-load spins on the current device
         const unsigned ns = (unsigned)value;

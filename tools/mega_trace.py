@@ -23,6 +23,10 @@ sess.cur_tokens.copy_(prompt[:, -1].to(torch.int32).view(1, -1).to(dev))
 sess.pos.fill_(PROMPT_T - 1)
 sess.run(8, 0.8008, 0.8008, 30, True)
 torch.cuda.synchronize()
+import os
+for kv in os.environ.get("TRACE_OPTS", "").split(","):
+    if kv:
+        model.set_option(kv.split("=")[0], int(kv.split("=")[1]))
 model.set_option("mega_trace", 1)
 sess.run(1, 0.8008, 0.8008, 30, True)
 torch.cuda.synchronize()
@@ -88,3 +92,26 @@ print(f"attn items: start->q ready mean {float(wait_q.mean()):.2f} max {float(wa
 comb = has & ((a2 - a0) > (a2 - a0)[has].median() + 2.0)
 if comb.any():
     print(f"  combiner items only: start->point mean {float((a1 - a0)[comb].mean()):.2f} max {float((a1 - a0)[comb].max()):.2f}; point->end mean {float((a2 - a1)[comb].mean()):.2f} max {float((a2 - a1)[comb].max()):.2f}  (n={int(comb.sum())})")
+
+# per-iteration detail of one op (TRACE_OPTS=mega_detail_op=<index>): group 0 / lane 0 of every CTA
+dop = [int(kv.split("=")[1]) for kv in os.environ.get("TRACE_OPTS", "").split(",") if kv.startswith("mega_detail_op=")]
+if dop:
+    o = dop[0]
+    raw = model._buffer("mega_trace", torch.int64)[n_sm * n_ops * 4: n_sm * n_ops * 4 + n_sm * 64].view(n_sm, 64).cpu().double()
+    det = (raw - t0) / 1e3
+    ref = float(tr[:, o, 1].median())
+    print(f"detail of op {o} ({kinds[o]}): times relative to the median x-staged stamp; per iteration of group 0: stage seen / dot done / epilogue done (median over CTAs, [min..max])")
+    for itn in range(6):
+        cols = det[:, itn * 3: itn * 3 + 3]
+        ok = raw[:, itn * 3] > 0
+        if not bool(ok.any()):
+            break
+        f = lambda v: "%.2f [%.2f..%.2f]" % (float(v[ok].median()) - ref, float(v[ok].min()) - ref, float(v[ok].max()) - ref)
+        print(f"  it {itn}: seen {f(cols[:, 0])}  dot {f(cols[:, 1])}  epi {f(cols[:, 2])}   (CTAs {int(ok.sum())})")
+    print(f"  op end (tid 0): {float(tr[:, o, 2].median()) - ref:.2f}")
+    print("  producer: request time of the op's stages (median over CTAs [min..max]), same reference; previous op ended at "
+          f"{float(tr[:, o - 1, 2].median()) - ref:.2f}, the op before it at {float(tr[:, o - 2, 2].median()) - ref:.2f}")
+    for k in range(16):
+        col, ok = det[:, 32 + k], raw[:, 32 + k] > 0
+        if bool(ok.any()):
+            print(f"    stage {k:2d}: {float(col[ok].median()) - ref:7.2f} [{float(col[ok].min()) - ref:.2f}..{float(col[ok].max()) - ref:.2f}]")
