@@ -21,6 +21,7 @@
 #include "prefill.cuh"
 #include "rows_gemm.cuh"
 #include "sample.cuh"
+#include "tc_conv.cuh"
 
 namespace {
 
@@ -76,7 +77,8 @@ struct fsb_dual_ar {
          *pf3 = nullptr;
     char* cublas_ws = nullptr;
     cublasHandle_t blas = nullptr;
-    int prefill_gemm = 1;            // 1: whole-chunk prompt pass (cuBLAS GEMMs), 0: 8-row passes through the decode kernels
+    int prefill_gemm = 1;            // prompt pass: 1 = whole chunks, every Linear on this library's tcgen05 kernel (tc_conv.cuh: tcv_kernel),
+                                     // 2 = whole chunks with cuBLAS GEMMs (comparison only), 0 = 8-row passes through the decode kernels
     int batch_gemm = 1;              // decode steps with more than 8 rows: 1 = every Linear once over all rows (weights streamed once
                                      // per step) on this library's tcgen05 stream-K kernel (rows_gemm.cuh), 2 = the same through
                                      // cuBLAS, 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
@@ -92,6 +94,7 @@ struct fsb_dual_ar {
     int attn_tc = 1;                 // many-row steps: tensor-core decode attention (attn_tc_kernel) instead of attn_decode_kernel
     bool rg_ok = false;              // tensor-map encoder available, attributes set
     std::map<std::tuple<const void*, int, int, int>, CUtensorMap> rg_maps;  // (ptr, rows, cols, box rows) -> TMA map
+    std::map<std::tuple<const void*, int, int, int>, CUtensorMap> tcv_maps; // the same for tcv_kernel's 3-D maps (prompt pass)
     int max_splits = 32;
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
@@ -1216,6 +1219,35 @@ static int prefill_linear(fsb_dual_ar* h, const bf16* W, const bf16* X, bf16* C,
     return 0;
 }
 
+// C = epi(X[T][K] . W[N][K]^T) on tcv_kernel (bf16 in, fp32 accumulate): epi NONE = bf16 store (one rounding per Linear),
+// residual: C = bf16(res + bf16(lin)) (llama.py:841-842), GATE: C = bf16(bf16(silu(gate)) * bf16(lin)) (llama.py:986)
+static const CUtensorMap* tcv_map(fsb_dual_ar* h, const void* ptr, int rows, int cols, int box_rows) {
+    auto key = std::make_tuple(ptr, rows, cols, box_rows);
+    auto it = h->tcv_maps.find(key);
+    if (it != h->tcv_maps.end()) return &it->second;
+    CUtensorMap m;
+    if (!tcv_make_map(&m, ptr, false, (uint64_t)cols, (uint64_t)rows, 1, (uint32_t)box_rows)) return nullptr;
+    return &h->tcv_maps.emplace(key, m).first->second;
+}
+static int prefill_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, const bf16* X, bf16* C, int T, int N, int K,
+                             const bf16* res = nullptr, const bf16* gate = nullptr) {
+    if (K % 8) return fail(h, "prompt-pass Linear needs K % 8 == 0");
+    // column-tile width: enough tiles for the 148 SMs when the chunk is short
+    int bn = tcv_pick_bn(N);
+    const int tiles_t = (T + TCV_BM - 1) / TCV_BM;
+    while (bn > 64 && tiles_t * ((N + bn - 1) / bn) < h->n_sm && N % (bn / 2) == 0) bn /= 2;
+    const CUtensorMap* mA = tcv_map(h, X, T, K, TCV_BM);
+    const CUtensorMap* mW = tcv_map(h, W, N, K, bn);
+    if (!mA || !mW) return fail(h, "cuTensorMapEncodeTiled failed");
+    TcConvArgs a{};
+    a.B = 1; a.T = T; a.N = N; a.Cin = K; a.taps = 1; a.dil = 1;
+    a.out16 = C; a.ld16 = N; a.ldres = N; a.bias_mod = N; a.alpha_mod = N;
+    if (gate) { a.res16 = gate; a.act = TCV_ACT_GATE; }
+    else if (res) { a.res16 = res; a.round_lin = 1; }
+    CK(tcv_launch(s, h->n_sm, false, bn, *mA, *mW, a));
+    return 0;
+}
+
 // slow stack over a chunk of T <= PREFILL_ROWS prompt rows already embedded in h->pxa; fills the KV cache
 static int prefill_chunk(fsb_dual_ar* h, cudaStream_t s, int T, const int32_t* pos, const int32_t* slots) {
     const fsb_dual_ar_desc& d = h->d;
@@ -1226,12 +1258,22 @@ static int prefill_chunk(fsb_dual_ar* h, cudaStream_t s, int T, const int32_t* p
     bf16* cur = h->pxa;
     for (size_t l = 0; l < h->slow.size(); ++l) {
         const LayerW& w = h->slow[l];
+        const bool own = h->prefill_gemm == 1;  // this library's tcgen05 kernel with the adds / SwiGLU in its epilogue
         rmsnorm_rows_kernel<<<T, 256, 0, s>>>(cur, w.attn_norm, h->pxn, D, d.norm_eps);
-        if (int r = prefill_linear(h, w.wqkv, h->pxn, h->pqkv, T, QKV, D)) return r;
+        if (int r = own ? prefill_linear_tc(h, s, w.wqkv, h->pxn, h->pqkv, T, QKV, D) : prefill_linear(h, w.wqkv, h->pxn, h->pqkv, T, QKV, D)) return r;
         AttnArgs a = make_attn_args(h, w, false, pos, slots, -1);
         a.qkv = h->pqkv; a.y = h->py; a.splits = 1; a.fused_append = 0;
         CK(launch(ak.append, dim3(KV, T), dim3(64), 0, s, false, a));
         CK(launch(ak.decode, dim3(1, KV, T), dim3(ATTN_THREADS), 0, s, false, a));
+        if (own) {
+            if (int r = prefill_linear_tc(h, s, w.wo, h->py, h->pxb, T, D, H * HD, cur)) return r;           // pxb = cur + wo(y)
+            rmsnorm_rows_kernel<<<T, 256, 0, s>>>(h->pxb, w.ffn_norm, h->pxn, D, d.norm_eps);
+            if (int r = prefill_linear_tc(h, s, w.w1, h->pxn, h->pf1, T, F, D)) return r;
+            if (int r = prefill_linear_tc(h, s, w.w3, h->pxn, h->pf1, T, F, D, nullptr, h->pf1)) return r;   // pf1 = silu(pf1) * w3(x), in place
+            if (int r = prefill_linear_tc(h, s, w.w2, h->pf1, h->pxa, T, D, F, h->pxb)) return r;            // pxa = pxb + w2(ff)
+            cur = h->pxa;
+            continue;
+        }
         if (int r = prefill_linear(h, w.wo, h->py, h->ptmp, T, D, H * HD)) return r;
         add_rows_kernel<<<ew_blocks, 256, 0, s>>>(cur, h->ptmp, h->pxb, (size_t)T * D / 8);
         rmsnorm_rows_kernel<<<T, 256, 0, s>>>(h->pxb, w.ffn_norm, h->pxn, D, d.norm_eps);
@@ -1255,9 +1297,11 @@ int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_
     fill_prefill_kernel<<<(T + 255) / 256, 256, 0, s>>>(h->pf_pos, h->pf_slot, T, pos0, slot);
     CK(cudaGetLastError());
     const int C1 = h->d.num_codebooks + 1;
+    if (h->prefill_gemm == 1 && (rg_get_encode() == nullptr || h->d.dim % 8 || h->d.ffn % 8)) h->prefill_gemm = 0;  // no tensor-map encoder: decode kernels
     if (h->prefill_gemm) {
         if (int r = check_bound(h)) return r;
-        if (int r = ensure_blas(h, s)) return r;
+        if (h->prefill_gemm == 1) CK(tcv_set_attrs());
+        else if (int r = ensure_blas(h, s)) return r;
         for (int t0 = 0; t0 < T; t0 += PREFILL_ROWS) {
             const int M = std::min<int>(PREFILL_ROWS, T - t0);
             EmbedArgs e = make_embed_args(h, tokens + (size_t)t0 * C1);

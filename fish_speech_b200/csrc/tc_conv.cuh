@@ -36,7 +36,7 @@
 #define TCV_A_BYTES (TCV_BM * TCV_BK * 2)
 #define TCV_POLICY_EVICT_NORMAL 0x1000000000000000ull
 
-enum { TCV_ACT_NONE = 0, TCV_ACT_GELU = 1, TCV_ACT_TANH = 2, TCV_ACT_SWIGLU = 3 };
+enum { TCV_ACT_NONE = 0, TCV_ACT_GELU = 1, TCV_ACT_TANH = 2, TCV_ACT_SWIGLU = 3, TCV_ACT_GATE = 4 };
 
 struct TcConvArgs {
     int B, T, N, Cin, taps, dil;
@@ -55,7 +55,9 @@ struct TcConvArgs {
     const void* res16;   // [B*T][ldres] 16-bit residual, may alias out16, or nullptr
     const float* alpha;  // [alpha_mod] Snake of the consumer applied to out16, or nullptr
     int bias_mod, alpha_mod, ldres;
-    int act;             // TCV_ACT_*; SWIGLU: columns (2i, 2i+1) = (gate, up) -> out column i, out width N / 2
+    int act;             // TCV_ACT_*; SWIGLU: columns (2i, 2i+1) = (gate, up) -> out column i, out width N / 2;
+                         // GATE: out16 = rnd(rnd(silu(g)) * rnd(v)) with g read from res16 (the w1 GEMM's output): FeedForward of the
+                         // bf16 LLM with a rounding after every op like the reference (llama.py:985-986)
     int vec_ok;          // 1: every row pitch / pointer allows the 16-byte vector paths of the epilogue
     int round_lin;       // 1: round the reduction to the 16-bit type BEFORE the residual add (the bf16 LLM's rounding points:
                          //    one rounding per Linear, one per add, llama.py:838-843)
@@ -131,6 +133,27 @@ __device__ __forceinline__ void tcv_epilogue(const TcConvArgs& a, const TcvParam
 #pragma unroll
             for (int i = 0; i < NC; ++i)
                 if (i < nv) v[i] += rp[i];
+        }
+    } else if (a.res16 && a.act == TCV_ACT_GATE) {
+        const uint16_t* rp = reinterpret_cast<const uint16_t*>(a.res16) + row * a.ldres + n0;
+        float g[NC];
+        if (vec) {
+#pragma unroll
+            for (int q = 0; q < NC / 8; ++q) {
+                const uint4 r = *reinterpret_cast<const uint4*>(rp + 8 * q);
+                g[8 * q] = H::unpack((uint16_t)(r.x & 0xffffu)); g[8 * q + 1] = H::unpack((uint16_t)(r.x >> 16));
+                g[8 * q + 2] = H::unpack((uint16_t)(r.y & 0xffffu)); g[8 * q + 3] = H::unpack((uint16_t)(r.y >> 16));
+                g[8 * q + 4] = H::unpack((uint16_t)(r.z & 0xffffu)); g[8 * q + 5] = H::unpack((uint16_t)(r.z >> 16));
+                g[8 * q + 6] = H::unpack((uint16_t)(r.w & 0xffffu)); g[8 * q + 7] = H::unpack((uint16_t)(r.w >> 16));
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < NC; ++i) g[i] = (i < nv) ? H::unpack(rp[i]) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+            const float sl = H::unpack(H::pack(__fdiv_rn(g[i], 1.f + expf(-g[i]))));  // silu rounded to the 16-bit type
+            v[i] = sl * H::unpack(H::pack(v[i]));                                      // times the rounded up projection
         }
     } else if (a.res16) {
         const uint16_t* rp = reinterpret_cast<const uint16_t*>(a.res16) + row * a.ldres + n0;

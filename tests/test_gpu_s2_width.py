@@ -162,3 +162,24 @@ def test_64_row_step_long_context_at_s2_width_vs_oracle():
     for k in (0, 1, 2, 9, 23, 40, 57, 63):
         ref, _ = om.forward_generate(prompts[k][None], torch.arange(lens[k]))
         _check(f"64-row step row {k} ctx {lens[k]}", lg[k], ref[0, -1])
+
+
+def test_prompt_pass_on_own_tcgen05_kernel_vs_oracle_and_library(s2w):
+    """Prompt pass (forward_generate with Tq > 1, llama.py:390-466) with every Linear on tcv_kernel (option prefill_gemm = 1,
+    the default: bf16 store, residual add and SwiGLU in the GEMM epilogue with the reference's rounding points) against the
+    oracle, against the same pass with cuBLAS GEMMs (prefill_gemm = 2) and against 8-row passes through the decode kernels
+    (prefill_gemm = 0).  Ragged lengths: one tile, tile edge, several chunks."""
+    cfg, sd, m, om = s2w
+    for T in (2, 128, 129, 400):
+        seq = R.make_prompt(cfg, T, seed=900 + T, voice_span=T // 3)
+        ref, _ = om.forward_generate(seq[None], torch.arange(T))
+        outs = {}
+        for mode in (1, 2, 0):
+            m.set_option("prefill_gemm", mode)
+            outs[mode] = m.forward_generate(seq[None].cuda(), torch.arange(T)).logits[0, 0].float().cpu()
+        m.set_option("prefill_gemm", 1)
+        _check(f"prompt pass (own kernel) T={T}", outs[1], ref[0, -1])
+        for other in (2, 0):
+            mabs, mrel, _ = err_stats(outs[1], outs[other])
+            print(f"[parity] prompt pass own kernel vs mode {other} T={T}: max-abs {mabs:.4f}")
+            assert mabs <= _abs_tol(ref[0, -1])
