@@ -22,6 +22,7 @@
 #include "rows_gemm.cuh"
 #include "sample.cuh"
 #include "tc_conv.cuh"
+#include "fa_prefill.cuh"
 
 namespace {
 
@@ -75,6 +76,9 @@ struct fsb_dual_ar {
     // prompt pass scratch (PREFILL_ROWS rows each) and the cuBLAS handle used for its plain GEMMs
     bf16 *pxa = nullptr, *pxb = nullptr, *pxn = nullptr, *pqkv = nullptr, *py = nullptr, *ptmp = nullptr, *pf1 = nullptr,
          *pf3 = nullptr;
+    bf16 *pq = nullptr, *pvt = nullptr;  // flash attention of the prompt pass: normed + roped q [H][rows][hd], V^T [KV][hd][max_seq]
+    int prefill_fa = 1;                  // prompt-pass attention on fa_prefill_kernel (tcgen05) when head_dim = 128; 0: one decode-attention CTA per row
+    std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t>, CUtensorMap> fa_maps;
     char* cublas_ws = nullptr;
     cublasHandle_t blas = nullptr;
     int prefill_gemm = 1;            // prompt pass: 1 = whole chunks, every Linear on this library's tcgen05 kernel (tc_conv.cuh: tcv_kernel),
@@ -992,6 +996,7 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
         const size_t PR = PREFILL_ROWS;
         T(pxa, bf16, PR * d.dim) T(pxb, bf16, PR * d.dim) T(pxn, bf16, PR * d.dim) T(pqkv, bf16, PR * QKV)
         T(py, bf16, PR * d.n_head * d.head_dim) T(ptmp, bf16, PR * d.dim) T(pf1, bf16, PR * d.ffn) T(pf3, bf16, PR * d.ffn)
+        T(pq, bf16, PR * d.n_head * d.head_dim) T(pvt, bf16, (size_t)d.n_kv_head * d.head_dim * ((size_t)max_seq_len + 8))
         T(cublas_ws, char, CUBLAS_WS_BYTES)
     }
     if (d.max_rows > 8) {
@@ -1105,6 +1110,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "attn_splits") h->attn_splits = (int)value;
     else if (n == "mega") h->use_mega = (int)value;
     else if (n == "prefill_gemm") h->prefill_gemm = (int)value;
+    else if (n == "prefill_fa") h->prefill_fa = (int)value;
     else if (n == "batch_gemm") h->batch_gemm = (int)value;
     else if (n == "attn_tc") h->attn_tc = (int)value;
     else if (n == "masked_head") h->masked_head = (int)value;
@@ -1248,8 +1254,41 @@ static int prefill_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, cons
     return 0;
 }
 
+// attention of T prompt rows at absolute positions pos0 .. pos0 + T - 1 of `slot` on the tcgen05 flash kernel (fa_prefill.cuh):
+// q/k prep + KV append, V^T scratch of all keys so far, then one CTA per (head, 128-query block).  qkv in h->pqkv, result in h->py
+static const CUtensorMap* fa_map(fsb_dual_ar* h, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2) {
+    auto key = std::make_tuple(ptr, d0, d1, d2);
+    auto it = h->fa_maps.find(key);
+    if (it != h->fa_maps.end()) return &it->second;
+    CUtensorMap m;
+    if (!tcv_make_map(&m, ptr, false, d0, d1, d2, 128)) return nullptr;
+    return &h->fa_maps.emplace(key, m).first->second;
+}
+static int prefill_attention_fa(fsb_dual_ar* h, cudaStream_t s, const LayerW& w, int T, const int32_t* pos, int pos0, int slot) {
+    const fsb_dual_ar_desc& d = h->d;
+    const int H = d.n_head, KV = d.n_kv_head, S = h->kv_max_seq;
+    if (fsb_first_on_device(5)) CK(cudaFuncSetAttribute((const void*)fa_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
+    QkPrepArgs qa{};
+    qa.qkv = h->pqkv; qa.q_out = h->pq; qa.kcache = w.kc; qa.vcache = w.vc; qa.q_norm = w.q_norm; qa.k_norm = w.k_norm; qa.rope = h->rope;
+    qa.pos = pos; qa.T = T; qa.H = H; qa.KV = KV; qa.S = S; qa.slot = slot; qa.qk_norm = d.qk_norm; qa.eps = d.norm_eps;
+    qk_prep_kernel<<<dim3(H + KV, T), 64, 0, s>>>(qa);
+    const int n_keys = pos0 + T;
+    vt_transpose_kernel<<<dim3(((n_keys + FA_BK - 1) / FA_BK) * 2, 2, KV), 256, 0, s>>>(w.vc, h->pvt, KV, S, slot, n_keys);
+    const CUtensorMap* mQ = fa_map(h, h->pq, FA_HD, (uint64_t)T, (uint64_t)H);
+    const CUtensorMap* mK = fa_map(h, w.kc, FA_HD, (uint64_t)S, (uint64_t)h->kv_max_batch * KV);
+    const CUtensorMap* mV = fa_map(h, h->pvt, (uint64_t)S, FA_HD, (uint64_t)KV);
+    if (!mQ || !mK || !mV) return fail(h, "cuTensorMapEncodeTiled failed (flash attention maps)");
+    FaArgs fa{};
+    fa.T = T; fa.pos0 = pos0; fa.H = H; fa.KV = KV; fa.S = S; fa.slot = slot; fa.nqb = (T + FA_BQ - 1) / FA_BQ;
+    fa.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)FA_HD)); fa.y = h->py;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(H * fa.nqb); cfg.blockDim = dim3(FA_THREADS); cfg.dynamicSmemBytes = FA_SMEM; cfg.stream = s;
+    CK(cudaLaunchKernelEx(&cfg, fa_prefill_kernel, *mQ, *mK, *mV, fa));
+    return 0;
+}
+
 // slow stack over a chunk of T <= PREFILL_ROWS prompt rows already embedded in h->pxa; fills the KV cache
-static int prefill_chunk(fsb_dual_ar* h, cudaStream_t s, int T, const int32_t* pos, const int32_t* slots) {
+static int prefill_chunk(fsb_dual_ar* h, cudaStream_t s, int T, const int32_t* pos, const int32_t* slots, int pos0, int slot) {
     const fsb_dual_ar_desc& d = h->d;
     const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn, QKV = (H + 2 * KV) * HD;
     AttnKernels ak;
@@ -1261,10 +1300,14 @@ static int prefill_chunk(fsb_dual_ar* h, cudaStream_t s, int T, const int32_t* p
         const bool own = h->prefill_gemm == 1;  // this library's tcgen05 kernel with the adds / SwiGLU in its epilogue
         rmsnorm_rows_kernel<<<T, 256, 0, s>>>(cur, w.attn_norm, h->pxn, D, d.norm_eps);
         if (int r = own ? prefill_linear_tc(h, s, w.wqkv, h->pxn, h->pqkv, T, QKV, D) : prefill_linear(h, w.wqkv, h->pxn, h->pqkv, T, QKV, D)) return r;
-        AttnArgs a = make_attn_args(h, w, false, pos, slots, -1);
-        a.qkv = h->pqkv; a.y = h->py; a.splits = 1; a.fused_append = 0;
-        CK(launch(ak.append, dim3(KV, T), dim3(64), 0, s, false, a));
-        CK(launch(ak.decode, dim3(1, KV, T), dim3(ATTN_THREADS), 0, s, false, a));
+        if (own && h->prefill_fa && HD == FA_HD) {
+            if (int r = prefill_attention_fa(h, s, w, T, pos, pos0, slot)) return r;
+        } else {
+            AttnArgs a = make_attn_args(h, w, false, pos, slots, -1);
+            a.qkv = h->pqkv; a.y = h->py; a.splits = 1; a.fused_append = 0;
+            CK(launch(ak.append, dim3(KV, T), dim3(64), 0, s, false, a));
+            CK(launch(ak.decode, dim3(1, KV, T), dim3(ATTN_THREADS), 0, s, false, a));
+        }
         if (own) {
             if (int r = prefill_linear_tc(h, s, w.wo, h->py, h->pxb, T, D, H * HD, cur)) return r;           // pxb = cur + wo(y)
             rmsnorm_rows_kernel<<<T, 256, 0, s>>>(h->pxb, w.ffn_norm, h->pxn, D, d.norm_eps);
@@ -1307,7 +1350,7 @@ int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_
             EmbedArgs e = make_embed_args(h, tokens + (size_t)t0 * C1);
             e.x = h->pxa;
             CK(launch(embed_kernel, dim3(M), dim3(256), 0, s, false, e));
-            if (int r = prefill_chunk(h, s, M, h->pf_pos + t0, h->pf_slot + t0)) return r;
+            if (int r = prefill_chunk(h, s, M, h->pf_pos + t0, h->pf_slot + t0, pos0 + t0, slot)) return r;
         }
         return 0;
     }

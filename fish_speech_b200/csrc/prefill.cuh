@@ -8,7 +8,7 @@
 #pragma once
 #include "common.cuh"
 
-#define PREFILL_ROWS 512  // prompt rows per chunk: bounds the activation scratch (about 100 KB per row at the S2 shape)
+#define PREFILL_ROWS 2048  // prompt rows per chunk: bounds the activation scratch (about 100 KB per row at the S2 shape)
 
 // out[t][:] = bf16(bf16(x * rsqrt(mean(x^2) + eps)) * w)      (llama.py:995-1000)
 __global__ void __launch_bounds__(256) rmsnorm_rows_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,

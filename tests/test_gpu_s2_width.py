@@ -183,3 +183,29 @@ def test_prompt_pass_on_own_tcgen05_kernel_vs_oracle_and_library(s2w):
             mabs, mrel, _ = err_stats(outs[1], outs[other])
             print(f"[parity] prompt pass own kernel vs mode {other} T={T}: max-abs {mabs:.4f}")
             assert mabs <= _abs_tol(ref[0, -1])
+
+
+def test_flash_attention_prompt_pass_vs_per_row_attention_and_oracle(s2w):
+    """fa_prefill_kernel (tcgen05 causal flash attention, option prefill_fa = 1, the default at head_dim 128) against the
+    per-row decode attention (prefill_fa = 0) and the oracle: lengths around the 128-row / 128-key block edges, and a prompt
+    continued at a non-zero offset (second call attends to the keys of the first through the cache)."""
+    cfg, sd, m, om = s2w
+    for T in (1, 127, 128, 129, 255, 300, 511):
+        seq = R.make_prompt(cfg, T + 1, seed=1200 + T, voice_span=T // 4)
+        ref, _ = om.forward_generate(seq[None], torch.arange(T + 1))
+        out = {}
+        for fa in (1, 0):
+            m.set_option("prefill_fa", fa)
+            out[fa] = m.forward_generate(seq[None].cuda(), torch.arange(T + 1)).logits[0, 0].float().cpu()
+        m.set_option("prefill_fa", 1)
+        _check(f"flash prompt pass T={T}", out[1], ref[0, -1])
+        mabs, _, _ = err_stats(out[1], out[0])
+        print(f"[parity] flash vs per-row attention T={T}: max-abs {mabs:.4f}")
+        assert mabs <= _abs_tol(ref[0, -1])
+    # continuation: 200 tokens, then 150 more at offset 200, then the decode step
+    seq = R.make_prompt(cfg, 351, seed=77, voice_span=60)
+    ref, _ = om.forward_generate(seq[None], torch.arange(351))
+    m.prefill(seq[:, :200].cuda(), 0, 0)
+    m.prefill(seq[:, 200:350].cuda(), 200, 0)
+    got = m.forward_generate(seq[None, :, 350:].cuda(), torch.tensor([350])).logits[0, 0].float().cpu()
+    _check("flash prompt pass in two calls (offset 200)", got, ref[0, -1])
