@@ -24,8 +24,17 @@ sys.path.insert(0, str(ROOT))
 
 FRAME_SEC = 2048.0 / 44100.0  # one Dual-AR frame = 2048 samples @ 44.1 kHz
 PROMPT_T = 512
-# dram__bytes_read.sum + dram__bytes_write.sum of one frame_mega_kernel launch (ncu --set full, profiles/r1_frame_mega_full.md)
-NCU_TRAFFIC_BYTES = 15.627865e9 + 0.027879e9  # restricted LM head (profiles/r1_frame_mega_full.md, addendum)
+
+
+def ncu_traffic(kernel: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` summary
+    (profiles/r2_traffic.json, written by tools/ncu_summary.py traffic); None when there is no capture of it."""
+    p = ROOT / "profiles" / "r2_traffic.json"
+    if not p.exists():
+        return None, None
+    d = json.loads(p.read_text()).get(kernel)
+    return (d["dram_bytes_per_launch"], d.get("source")) if d else (None, None)
+
 
 METRIC = "audio_sec_per_sec_dual_ar_decode_bs1"
 
@@ -99,9 +108,8 @@ def synth_prompt(cfg, T, seed=1):
 def cpu_reference_leg(frames: int, steps: int = 1, warmup: int = 0):
     """The reference's CPU path for this workload: oracle/dual_ar_ref.py (a torch-CPU restatement pinned bit-exact
     to the reference's own generate(); the Python reference itself cannot travel to the GPU box), S2-Pro shape,
-    bf16, all host threads, `frames` decode frames after a 16-token prompt with max_seq_len 2048 (the reference
-    attends over the whole allocated cache each step, llama.py:441,909-933, so step cost does not depend on the
-    position).  Weights are a tiled random block (values do not affect timing; building 4.5 B fresh normals would
+    bf16, all host threads, the same 512-token prompt pass as the GPU arm (timed separately) and `frames` decode frames
+    after it with max_seq_len 2048.  Weights are a tiled random block (values do not affect timing; building 4.5 B fresh normals would
     dominate the run).  Returns (audio-sec/sec, cores, sample description, seconds per frame)."""
     import torch
     from oracle import dual_ar_ref as R
@@ -121,15 +129,17 @@ def cpu_reference_leg(frames: int, steps: int = 1, warmup: int = 0):
             sd[name] = block.repeat((n + block.numel() - 1) // block.numel())[:n].view(shape)
     m = R.DualARRef(cfg, sd)
     m.setup_caches(1, cfg.max_seq_len)
-    prompt = R.make_prompt(cfg, 16, seed=1)
+    prompt = R.make_prompt(cfg, PROMPT_T, seed=1)
     T = torch.tensor(0.8, dtype=torch.bfloat16)
     P = torch.tensor(0.8, dtype=torch.bfloat16)
     bias = R.make_semantic_logit_bias(cfg)
     bias[0, 0, cfg.im_end_id] = float("-inf")  # fixed frame count
     with torch.inference_mode():
-        first = R.decode_one_token_ar(m, prompt[None], torch.arange(16), T, P, 30, bias)
+        t0 = time.perf_counter()
+        first = R.decode_one_token_ar(m, prompt[None], torch.arange(PROMPT_T), T, P, 30, bias)
+        prefill_s = time.perf_counter() - t0
         times = []
-        pos = 16
+        pos = PROMPT_T
         cur = first.view(1, cfg.num_codebooks + 1, -1)
         for it in range(warmup + steps):
             t0 = time.perf_counter()
@@ -140,7 +150,8 @@ def cpu_reference_leg(frames: int, steps: int = 1, warmup: int = 0):
             if it >= warmup:
                 times.append(dt / max(1, out.shape[1]))
     spf = statistics.mean(times)
-    sample = f"{frames} decode frames/step x {steps} step(s), S2-Pro shape bf16, bs1, max_seq_len 2048, 16-token prompt, oracle port of generate()"
+    sample = (f"{frames} decode frames/step x {steps} step(s) after the {PROMPT_T}-token prompt pass ({prefill_s:.1f} s, not counted), "
+              f"S2-Pro shape bf16, bs1, max_seq_len 2048, oracle port of generate()")
     return FRAME_SEC / spf, cores, sample, spf
 
 
@@ -253,7 +264,7 @@ def measure_dac(dev, B=32, T=646, iters=2):
     import torch
     from fish_speech_b200.dac import DACB200, DACConfig, synthetic_state_dict
     cfg = DACConfig()
-    m = DACB200(cfg, synthetic_state_dict(cfg, 0), device=dev, max_batch=4, max_frames=max(T, 8))
+    m = DACB200(cfg, synthetic_state_dict(cfg, 0), device=dev, max_batch=8, max_frames=max(T, 8))
     g = torch.Generator().manual_seed(2)
     codes = torch.randint(0, cfg.codebook_size, (B, cfg.n_codebooks + 1, T), generator=g)
     codes[:, 0] = torch.randint(0, cfg.semantic_codebook_size, (B, T), generator=g)
@@ -270,6 +281,99 @@ def measure_dac(dev, B=32, T=646, iters=2):
     ms = e0.elapsed_time(e1) / iters
     out = (ms, B * T * cfg.hop / cfg.sample_rate, m.flops(B, T), bool(torch.isfinite(wav).all()))
     del m, wav
+    torch.cuda.empty_cache()
+    return out
+
+
+def cpu_dac_leg(frames=215):
+    """The reference's CPU codec path on a bounded sample: oracle/dac_ref.py (fp32 restatement of DAC.from_indices pinned to the
+    reference classes) on ONE clip of `frames` code frames (10 s of audio), all host threads; audio-s/s."""
+    import torch
+    from oracle import dac_ref as D
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    c = D.DACConfig()
+    sd = D.make_state_dict(c, seed=0)
+    codes = D.make_codes(c, 1, frames)
+    t0 = time.perf_counter()
+    D.from_indices(c, sd, codes)
+    dt = time.perf_counter() - t0
+    return {"value": frames * c.hop / c.sample_rate / dt, "unit": "audio-s/s", "cores": cores, "kind": "port",
+            "sample": f"1 clip x {frames} code frames ({frames * c.hop / c.sample_rate:.1f} s of audio), fp32, oracle port of DAC.from_indices; "
+                      "32 x 30 s clips would take 96x as long"}
+
+
+def measure_config5(dev, rank, T=8192, F=4096):
+    """BASELINE configs[4]: long-form voice clone on one GPU: T-token prompt (pinned host), prompt pass (own tcgen05 GEMM + flash
+    attention), F decode frames at max_seq_len 16384 (context 8k -> 12k: kernel chain, the persistent frame kernel's attention
+    holds <= 2048 keys), then the DAC on the F frames; wall clock around everything incl. H2D of the prompt and D2H of the
+    waveform, plus CUDA-event times of the three phases."""
+    import torch
+    from fish_speech_b200 import DualARTransformerB200, generate, s2_pro_config
+    from fish_speech_b200.dac import DACB200, DACConfig, synthetic_state_dict
+    import fish_speech_b200.dual_ar as DA
+    cfg = s2_pro_config(max_seq_len=16384)
+    model = DualARTransformerB200(cfg, synth_state_dict(cfg, dev, seed=0), device=dev, max_rows=1)
+    model.setup_caches(1, cfg.max_seq_len)
+    model.ignore_eos = True
+    dcfg = DACConfig()
+    dac = DACB200(dcfg, synthetic_state_dict(dcfg, 0), device=dev, max_batch=1, max_frames=F)
+    prompt = synth_prompt(cfg, T, seed=11 + rank)
+    # voice-clone prompt: the last 7/8 are reference-audio frames (semantic tokens + codes, content_sequence.py:206-209)
+    g = torch.Generator().manual_seed(5 + rank)
+    span = T - T // 8
+    codes = torch.randint(0, cfg.codebook_size, (cfg.num_codebooks, span), generator=g)
+    prompt[1:, T - span:] = codes
+    prompt[0, T - span:] = cfg.semantic_begin_id + codes[0]
+    hp = prompt.pin_memory()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    marks = {}
+    real_n = DA.decode_n_tokens
+
+    def timed_n(*a, **k):
+        ev[1].record()
+        r = real_n(*a, **k)
+        ev[2].record()
+        return r
+    # warm-up on a short prompt: graph capture, tensor maps, lazy module loading
+    generate(model=model, prompt=hp[:, :256].to(dev), max_new_tokens=8, temperature=0.8, top_p=0.8, top_k=30)
+    dac.from_indices(torch.zeros((1, dcfg.n_codebooks + 1, 64), dtype=torch.long, device=dev))
+    torch.cuda.synchronize()
+    DA.decode_n_tokens = timed_n
+    try:
+        t0 = time.perf_counter()
+        ev[0].record()
+        seq = generate(model=model, prompt=hp.to(dev, non_blocking=True), max_new_tokens=F, temperature=0.8, top_p=0.8, top_k=30)
+        new = seq[1:, T:][None].contiguous()     # [1, 10, F] codes of the generated frames (the codec clamps them like rvq.py:354-359)
+        wav = dac.from_indices(new)
+        ev[3].record()
+        host = wav.cpu()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+    finally:
+        DA.decode_n_tokens = real_n
+    pre_ms, dec_ms, dac_ms = ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])
+    n_new = seq.shape[1] - T
+    c = cfg
+    p_layer = c.dim * (c.n_head + 2 * c.n_local_heads) * c.head_dim + c.n_head * c.head_dim * c.dim + 3 * c.dim * c.intermediate_size
+    pre_flops = 2.0 * c.n_layer * p_layer * T + 4.0 * c.n_layer * c.n_head * c.head_dim * T * T / 2
+    peak, _ = measured_peaks()
+    pk = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
+    tpeak = float(pk.get("bf16_tflops_sustained", pk.get("bf16_tflops", 1395.3)))
+    fbytes = model.frame_bytes(1, int(T + (n_new - 1) / 2.0), masked_head=True)
+    ms_frame = dec_ms / max(1, n_new - 1)
+    out = {
+        "workload": f"long-form voice clone (BASELINE configs[4]) per GPU: {T}-token prompt, {n_new} frames decoded at max_seq_len 16384, DAC on the frames",
+        "value": n_new * FRAME_SEC / wall, "unit": "audio-s/s", "wall_s": wall, "audio_s": n_new * FRAME_SEC,
+        "h2d_bytes": int(prompt.numel() * 8), "d2h_bytes": int(host.numel() * 4), "finite": bool(torch.isfinite(host).all()),
+        "prefill": {"ms": pre_ms, "tflops": pre_flops / pre_ms / 1e9, "frac_of_tensor_peak": pre_flops / pre_ms / 1e9 / tpeak,
+                    "note": "includes the first frame; GEMM + causal attention FLOPs (SURVEY 8d); tcv_kernel + fa_prefill_kernel (tcgen05)"},
+        "decode": {"ms_per_frame": ms_frame, "gbs": fbytes / ms_frame / 1e6, "frac_of_hbm": fbytes / ms_frame / 1e6 / peak,
+                   "launches_per_frame": model.launches_per_frame(1),
+                   "note": "context 8k -> 12k: kernel chain (PDL-chained launches per frame in a CUDA graph), restricted LM head"},
+        "dac": {"ms": dac_ms, "tflops": dac.flops(1, n_new) / dac_ms / 1e9, "frac_of_tensor_peak": dac.flops(1, n_new) / dac_ms / 1e9 / tpeak},
+    }
+    del model, dac
     torch.cuda.empty_cache()
     return out
 
@@ -373,6 +477,18 @@ def run_ours(args):
             dac = measure_dac(dev)
         except Exception as e:  # the Dual-AR numbers stand on their own
             dac = e
+    dac_cpu = None
+    if not args.no_dac and not args.no_cpu and rank == 0:
+        try:
+            dac_cpu = cpu_dac_leg()
+        except Exception as e:
+            dac_cpu = {"value": None, "sample": f"failed: {e}"}
+    c5 = None
+    if args.config5:
+        try:
+            c5 = measure_config5(dev, rank)
+        except Exception as e:
+            c5 = {"error": str(e)}
     tms = torch.tensor([ms, e2e_t, b64[0] if b64 else 0.0, dac[0] if isinstance(dac, tuple) else 0.0], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(args.steps * F), float(e2e_frames)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -415,7 +531,8 @@ def run_ours(args):
         # streams through it), so its launch duration is the frame time measured above with CUDA events
         "roofline": ({"bound": "hbm", "kernel": "frame_mega_kernel<128,4> (persistent cooperative kernel, one launch = one frame)",
                       "achieved": fbytes / (ms_per_frame * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                      "frac": fbytes / (ms_per_frame * 1e-3) / 1e9 / peak, "traffic": NCU_TRAFFIC_BYTES,
+                      "frac": fbytes / (ms_per_frame * 1e-3) / 1e9 / peak, "traffic": ncu_traffic("frame_mega_kernel")[0],
+                      "traffic_source": ncu_traffic("frame_mega_kernel")[1],
                       "bytes_per_launch": fbytes, "ms_per_launch": ms_per_frame, "peak_source": peak_src}
                      if persistent else
                      {"bound": "hbm", "kernel": "gemv_tma_kernel<M=1,RMSNORM,SWIGLU> (w1/w3 gate-up, timed alone over 36 layers)",
@@ -447,9 +564,15 @@ def run_ours(args):
         line["dac"] = {"workload": "DAC codec decode, 32 clips x 646 code frames (30 s) per GPU x %d GPU(s) -> 44.1 kHz (BASELINE configs[3])" % world,
                        "value": world * dac[1] / (dac_ms_max * 1e-3), "unit": "audio-s/s", "ms_per_step": dac_ms_max, "finite": dac[3],
                        "roofline": {"bound": "tensor", "achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak,
-                                    "note": "TF32 mma.sync implicit-GEMM conv (csrc/dac_kernels.cuh) against the measured bf16 tensor peak"}}
+                                    "kernel": "tcv_kernel (csrc/tc_conv.cuh): tcgen05 implicit-GEMM conv, fp16 operands, fp32 TMEM accumulation",
+                                    "note": "algorithmic GEMM-shaped FLOPs of the decode (fsb_dac_flops, SURVEY 8d: 6.76 GFLOP per code frame) / CUDA-event time, "
+                                            "against the measured sustained bf16/fp16 tensor peak"}}
+        if dac_cpu is not None:
+            line["dac"]["cpu_baseline"] = dac_cpu
     elif dac is not None:
         line["dac"] = {"error": str(dac)}
+    if c5 is not None:
+        line["config5"] = c5
     if not args.no_cpu and world >= 1:
         try:
             v, cores, sample, _ = cpu_reference_leg(args.ref_frames)
@@ -473,6 +596,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the config-3 (bs64) section")
     ap.add_argument("--no-dac", action="store_true", help="skip the config-4 (DAC decode) section")
+    ap.add_argument("--no-config5", dest="config5", action="store_false", help="skip the long-form section (8k-token prompt + 4k frames + DAC, BASELINE configs[4], ~30 s)")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--batch-ctx", type=int, default=2048)
     ap.add_argument("--batch-frames", type=int, default=48)

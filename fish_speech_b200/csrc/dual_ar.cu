@@ -105,8 +105,6 @@ struct fsb_dual_ar {
     int use_mega = 1;                // batch-1 frames as ONE persistent cooperative kernel (frame_mega.cuh)
     int mega_skip_dot = 0;           // experiment (results are garbage): no dot products in the frame kernel
     int mega_detail_op = -1;         // profiling: op index whose per-iteration stamps are recorded (frame kernel)
-    int mega_mma = 0;                // frame kernel: GEMV dot products through mma.sync tiles (frame_mega.cuh: mg_dot_mma); measured no
-                                     // faster than the FMA loop (legacy HMMA issue rate), off
     int mega_l2_ahead = 0;           // frame kernel: stages per producer lane prefetched into L2 while the ring is full
     bool mega_supported = false;     // shape fits the frame kernel's stage geometry and it is resident at 1 CTA/SM
     MegaPlan mega_plan{};
@@ -939,7 +937,6 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     p.prof = h->mega_prof_on ? h->mega_prof : nullptr;
     p.hot = (const uint4*)(h->mega_buf + o_h); p.n_hot = (int)mb.hot.size(); p.n_attn_slow = d.n_layer;
     p.l2_ahead = h->mega_l2_ahead;
-    p.use_mma = h->mega_mma;
     p.trace = (h->mega_trace_on && (size_t)h->n_sm * mb.ops.size() * 4 <= MEGA_TRACE_WORDS) ? h->mega_trace : nullptr;
     p.detail_op = h->mega_detail_op;
     p.skip_dot = h->mega_skip_dot;
@@ -960,7 +957,12 @@ int launch_mega(fsb_dual_ar* h, cudaStream_t s) {
     return 0;
 }
 
-bool mega_active(const fsb_dual_ar* h, int batch) { return h->use_mega && h->mega_supported && batch == 1; }
+// the frame kernel's in-kernel attention holds one tile of asp_max_keys keys per split and at most ASP_MAXS splits: longer
+// caches (config 5: 8k-token prompts) take the kernel chain, whose attention loops over key tiles
+bool mega_active(const fsb_dual_ar* h, int batch) {
+    return h->use_mega && h->mega_supported && batch == 1 &&
+           h->kv_max_seq <= std::min(h->max_splits, ASP_MAXS) * asp_max_keys(h->d.head_dim);
+}
 
 __global__ void fill_prefill_kernel(int32_t* pos, int32_t* slot, int n, int pos0, int slot_v) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1121,7 +1123,6 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "mega_prof") h->mega_prof_on = (int)value;
     else if (n == "mega_trace") h->mega_trace_on = (int)value;
     else if (n == "mega_l2_ahead") h->mega_l2_ahead = (int)value;
-    else if (n == "mega_mma") h->mega_mma = (int)value;
     else if (n == "mega_detail_op") h->mega_detail_op = (int)value;
     else if (n == "mega_skip_dot") h->mega_skip_dot = (int)value;
     else if (n == "attn_trace_point") h->attn_trace_point = (int)value;

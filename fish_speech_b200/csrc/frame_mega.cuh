@@ -70,7 +70,6 @@ struct MegaPlan {
     int n_hot;                 // (norm weights, RoPE rows, sampling bias): prefetched into L2 with evict_last at launch
     unsigned long long* trace; // optional [grid][n_ops][4] globaltimer stamps (op start, x staged, op end, barrier passed)
     int l2_ahead;              // stages per producer lane prefetched into L2 while the ring is full (0 = off)
-    int use_mma;               // dot products of the GEMV ops on mma.sync (mg_dot_mma) where K % 256 == 0
     int skip_dot;              // experiment: consumers wait for and release the stages without reading them (results are garbage)
     int detail_op;             // profiling: op whose per-iteration stamps go to `detail` (-1 = none)
     int detail_gemv;           //            its index in the GEMV list (producer side)
@@ -263,68 +262,30 @@ __device__ __forceinline__ void mg_finish_row(const MegaGemv& g, size_t oi, floa
 }
 
 // dot product of one row segment in shared memory with the activation chunks of the same columns: chunk c of the segment
-// goes to lane (c - c_lo) % 32.  The trip count is warp-uniform (whole rounds of 32 chunks, then one predicated round for a
-// ragged end), loads of a batch are issued before its math, and the math is the native bf16 x bf16 + fp32 FMA (dot8_bf16).
+// goes to lane (c - c_lo) % 32; the math is the native bf16 x bf16 + fp32 FMA (dot8_bf16), bit-identical to unpack + FFMA.
 __device__ __forceinline__ float mg_dot(const uint4* w0, const uint4* xs, int c_lo, int c_hi, int lane) {
+    // MG_CPL chunks per lane in two batches of loads-then-math (x is re-read from shared memory: holding it in registers
+    // does not fit the 96-register cap); a fixed shape with predicated loads measured faster than a warp-uniform trip count
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    const int nch = c_hi - c_lo, full = nch >> 5;  // rounds in which every lane has a chunk
-    const uint4* wp = w0 + c_lo + lane;
-    const uint4* xp = xs + c_lo + lane;
-    int i = 0;
-    for (; i + 5 <= full; i += 5) {
-        uint4 wv[5], xv[5];
 #pragma unroll
-        for (int j = 0; j < 5; ++j) { wv[j] = wp[32 * (i + j)]; xv[j] = xp[32 * (i + j)]; }
+    for (int hb = 0; hb < 2; ++hb) {
+        uint4 wv[MG_CPL / 2], xv[MG_CPL / 2];
 #pragma unroll
-        for (int j = 0; j < 5; ++j) dot8_bf16(wv[j], xv[j], acc);
-    }
-    {   // up to 4 whole rounds + the ragged one
-        uint4 wv[5], xv[5];
-#pragma unroll
-        for (int j = 0; j < 5; ++j) {
-            const int r = i + j;
-            const bool ok = r < full || (r == full && lane < (nch & 31));
-            wv[j] = ok ? wp[32 * r] : make_uint4(0, 0, 0, 0);
-            xv[j] = ok ? xp[32 * r] : make_uint4(0, 0, 0, 0);
+        for (int i = 0; i < MG_CPL / 2; ++i) {
+            const int c = c_lo + lane + 32 * (hb * (MG_CPL / 2) + i);
+            const bool ok = c < c_hi;
+            wv[i] = ok ? w0[c] : make_uint4(0, 0, 0, 0);
+            xv[i] = ok ? xs[c] : make_uint4(0, 0, 0, 0);
         }
 #pragma unroll
-        for (int j = 0; j < 5; ++j) dot8_bf16(wv[j], xv[j], acc);
+        for (int i = 0; i < MG_CPL / 2; ++i) dot8_bf16(wv[i], xv[i], acc);
     }
     return (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
-
-// The same dot product on the tensor cores, used as an instruction-count reducer (the op stays HBM-bound): a 256-element
-// piece of a weight row times the matching piece of x is the DIAGONAL of a 16 x 16 product.  With ldmatrix.x4 and lane l
-// pointing at the l-th consecutive 16 bytes of the 512-byte tile, the four 8x8 matrices are exactly the A fragment of
-// mma.m16n8k16 for the element mapping A[m][k] = tile[((m>>3) + 2*(k>>3)) * 64 + (m&7) * 8 + (k&7)]; loading the x tile
-// the same way gives B fragments with B[k][n] = x at the index of (m = n, k) (registers 0/2 for the rows 0-7, 1/3 for the
-// rows 8-15), so two MMAs accumulate all 16 diagonal terms in fp32: ~4 warp instructions per 512 bytes of weights instead of
-// ~26 (unpack + FMA), exact bf16 products, conflict-free shared-memory reads.  Consumers that can run several times faster
-// than the stream drain the ring after a bubble of the dependent chain instead of staying behind it.
-__device__ __forceinline__ void mg_ldsm4(uint32_t addr, uint32_t (&r)[4]) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-// tiles [t_lo, t_hi) of one row (smem address `wrow`) against the same tiles of x (smem address `xsm`); per-lane partial,
-// the caller sums over the warp
-__device__ __forceinline__ float mg_dot_mma(uint32_t wrow, uint32_t xsm, int t_lo, int t_hi, int lane) {
-    float c1[4] = {0.f, 0.f, 0.f, 0.f}, c2[4] = {0.f, 0.f, 0.f, 0.f};
-    const uint32_t off = 16u * (uint32_t)lane;
-#pragma unroll 2
-    for (int t = t_lo; t < t_hi; ++t) {
-        uint32_t a[4], x[4];
-        mg_ldsm4(wrow + (uint32_t)t * 512u + off, a);
-        mg_ldsm4(xsm + (uint32_t)t * 512u + off, x);
-        mma_bf16_16816(c1, a[0], a[1], a[2], a[3], x[0], x[2]);
-        mma_bf16_16816(c2, a[0], a[1], a[2], a[3], x[1], x[3]);
-    }
-    const int g = lane >> 2, t4 = lane & 3;  // D fragment: c[0] = (row g, col 2*t4), c[1] = (g, 2*t4+1), c[2] = (g+8, 2*t4), c[3] = (g+8, 2*t4+1)
-    return (g == 2 * t4) ? c1[0] + c2[2] : (g == 2 * t4 + 1) ? c1[1] + c2[3] : 0.f;
-}
-
 __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stages, uint4* xs, uint64_t* full_bar,
                                         uint64_t* empty_bar, float* red, float* res_s, float (*pbuf)[2][2][4], unsigned& n, int b,
                                         int nb, int tid, unsigned seq, int oi, unsigned long long* prof,
-                                        unsigned long long* trace, bool mma_on, unsigned long long* detail, bool skip_dot) {
+                                        unsigned long long* trace, unsigned long long* detail, bool skip_dot) {
     const long long tp0 = prof ? clock64() : 0;
     const int lane = tid & 31, warp = tid >> 5;
     const int grp = warp >> 2, wg = warp & 3;
@@ -427,11 +388,6 @@ __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stage
     const int cpw = (K8 + SEGW - 1) >> seg_shift;  // chunks per segment (<= 32 * MG_CPL)
     const int c_lo = seg * cpw, c_hi = min(K8, c_lo + cpw);
     const size_t row_bytes = (size_t)K * 2;
-    // tensor-core dot (K a multiple of the 256-element tile): this warp's tiles of a row
-    const bool use_mma = mma_on && (K & 255) == 0;
-    const int n_tl = K >> 8;
-    const int tl_lo = (n_tl * seg) >> seg_shift, tl_hi = (n_tl * (seg + 1)) >> seg_shift;
-    const uint32_t xs_addr = smem_u32(xs);
     float acc0[2] = {0.f, 0.f};  // w1 row sums waiting for the w3 stage (SwiGLU, whole-row warps)
     int par = 0;
     const unsigned n0 = n;
@@ -460,8 +416,7 @@ __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stage
         for (int r = 0; r < 2; ++r) {
             const int row = row0 + 4 * r;
             if (r < rpw && row < ng && !skip_dot)
-                part[r] = warp_sum(use_mma ? mg_dot_mma(smem_u32(st + row * row_bytes), xs_addr, tl_lo, tl_hi, lane)
-                                           : mg_dot(reinterpret_cast<const uint4*>(st + row * row_bytes), xs, c_lo, c_hi, lane));
+                part[r] = warp_sum(mg_dot(reinterpret_cast<const uint4*>(st + row * row_bytes), xs, c_lo, c_hi, lane));
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[slot]);
@@ -573,7 +528,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) frame_mega_kernel(MegaPlan p) {
         if (tr && tid == 0) tr[0] = mg_now();
         switch (op.type) {
         case MOP_GEMV:
-            mg_gemv(p.gemv + op.idx, stages, xs, full_bar, empty_bar, red, res_s, pbuf, n, b, nb, tid, seq, oi, prof, tr, p.use_mma != 0, (p.detail && oi == p.detail_op) ? p.detail + (size_t)b * 64 : nullptr, p.skip_dot != 0);
+            mg_gemv(p.gemv + op.idx, stages, xs, full_bar, empty_bar, red, res_s, pbuf, n, b, nb, tid, seq, oi, prof, tr, (p.detail && oi == p.detail_op) ? p.detail + (size_t)b * 64 : nullptr, p.skip_dot != 0);
             break;
         case MOP_EMBED:
             if (b < p.B) embed_body(*p.embed, b, tid, MG_CONSUMERS, mg_tag(seq, oi));

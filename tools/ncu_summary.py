@@ -3,6 +3,7 @@
 
     python tools/ncu_summary.py launches <launch list .csv> "<command>" > profiles/<name>.md
     python tools/ncu_summary.py full <ncu --page raw --csv export> "<command>" > profiles/<name>.md
+    python tools/ncu_summary.py traffic <ncu --page raw --csv export> <kernel key> "<source note>"   (updates profiles/r2_traffic.json)
 
 launches: the `--metrics gpu__time_duration.sum --clock-control none --csv` pass (per-launch times are cold-cache and
 serialised: shares are what matters).  full: selected metrics of every captured launch of an `ncu --set full` report.
@@ -68,5 +69,29 @@ def full(path, cmd):
         print(f"{name} | {r[ig]} | {r[ib]} | " + " | ".join(vals))
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] in ("launches", "full"):
     {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
+
+
+def traffic(path, key, note):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the first captured launch -> profiles/r2_traffic.json[key] (bench.py reads it)"""
+    import json
+    import os
+    rows = list(csv.reader(open(path)))
+    hdr, units, vals = rows[0], rows[1], rows[2]
+    get = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    tot = 0.0
+    for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        v, u = get[name]
+        tot += float(v.replace(",", "")) * mult[u]
+    dur_v, dur_u = get["gpu__time_duration.sum"]
+    out = "profiles/r2_traffic.json"
+    d = json.load(open(out)) if os.path.exists(out) else {}
+    d[key] = {"dram_bytes_per_launch": tot, "gpu_time_duration": f"{dur_v} {dur_u}", "source": note}
+    json.dump(d, open(out, "w"), indent=1)
+    print(key, d[key])
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "traffic":
+    traffic(sys.argv[2], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "")
