@@ -12,3 +12,5 @@ from . import partition  # noqa: F401
 
 __all__ = ["DACB200", "DACConfig", "partition", "DualARConfig", "DualARTransformerB200", "decode_one_token_ar", "decode_n_tokens", "generate",
            "init_model_from_state_dict", "make_semantic_logit_bias", "s2_pro_config"]
+
+from .checkpoint import init_model, load_codec, load_config, load_weights  # noqa: E402,F401

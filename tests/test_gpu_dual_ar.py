@@ -536,3 +536,28 @@ def test_reference_frame_loop_drives_decode_one_token_ar(tiny):
     sess.uniforms = None
     host = torch.cat([first.long(), rest.long()], dim=1)
     assert torch.equal(host, dev[:, T:]), (host[0], dev[0, T:])
+
+
+def test_init_model_from_a_checkpoint_directory(tmp_path):
+    """§8(f1): init_model(checkpoint_path, device, precision, compile) on a synthetic fish_qwen3_omni checkpoint (sharded
+    safetensors, published key names, separate wq / wk / wv, tokenizer.json) gives the engine the in-memory constructor
+    gives: bit-identical logits, the tokenizer's ids in the config."""
+    from fish_speech_b200 import DualARTransformerB200
+    from fish_speech_b200.checkpoint import init_model
+    from tests.test_cpu_checkpoint import _tiny, write_omni_checkpoint
+    c = _tiny()
+    sd = R.make_state_dict(c, seed=4)
+    write_omni_checkpoint(tmp_path, c, sd)
+    model, decode_one_token = init_model(tmp_path, "cuda:0", torch.bfloat16, compile=False)
+    from fish_speech_b200 import dual_ar
+    assert decode_one_token is dual_ar.decode_one_token_ar and model._cache_setup_done is False
+    assert (model.config.semantic_begin_id, model.config.semantic_end_id, model.config.im_end_id) == (c.semantic_begin_id, c.semantic_end_id, c.im_end_id)
+    ref = DualARTransformerB200(c.__dict__, sd, device="cuda:0")
+    prompt = R.make_prompt(c, 20, seed=2, voice_span=5)
+    outs = []
+    for m in (model, ref):
+        m.setup_caches(1, c.max_seq_len)
+        outs.append(m.forward_generate(prompt[None].cuda(), torch.arange(20)).logits.cpu())
+    assert torch.equal(outs[0], outs[1])
+    with pytest.raises(ValueError):
+        init_model(tmp_path, "cuda:0", torch.float32)
