@@ -381,7 +381,7 @@ def measure_config5(dev, rank, T=8192, F=4096):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from fish_speech_b200 import DualARTransformerB200, generate, s2_pro_config
+    from fish_speech_b200 import DualARTransformerB200, generate, partition, s2_pro_config
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -395,7 +395,9 @@ def run_ours(args):
     model = DualARTransformerB200(cfg, sd, device=dev, max_rows=1)
     del sd
     model.setup_caches(1, cfg.max_seq_len)
-    prompt = synth_prompt(cfg, PROMPT_T, seed=1 + rank)  # a different utterance per rank
+    # one utterance per GPU, handed out by the request partitioner (fish_speech_b200/partition.py)
+    utterance = partition.assign(world, world)[rank][0]
+    prompt = synth_prompt(cfg, PROMPT_T, seed=1 + utterance)
     C1 = cfg.num_codebooks + 1
 
     # ---- device-resident leg (`value`): prompt pass once, then K timed steps of F frames from position 512
@@ -451,19 +453,21 @@ def run_ours(args):
     # same fixed-length workload as the device-resident leg: generate() builds its own constrained-decode bias
     # (inference.py:308-320); the <|im_end|> entry is masked here so every run decodes exactly F frames
     model.ignore_eos = True  # supported switch (dual_ar.make_semantic_logit_bias): same restricted LM head / scan as the device-resident leg
+    def one_utterance(u):  # the public call a user makes; result back on the host
+        assert u == utterance
+        return generate(model=model, prompt=hp.to(dev, non_blocking=True), max_new_tokens=F, temperature=0.8, top_p=0.8, top_k=30).cpu()
+
     for it in range(1 + args.e2e_steps):
         barrier()
         t0 = time.perf_counter()
-        seq = generate(model=model, prompt=hp.to(dev, non_blocking=True), max_new_tokens=F, temperature=0.8, top_p=0.8,
-                       top_k=30)
-        host = seq.cpu()
+        (_, host), = partition.run_partitioned(list(range(world)), one_utterance, gather=False)  # this rank's share: one utterance
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         if it > 0:
             e2e_frames += host.shape[1] - PROMPT_T
             e2e_t += dt
     model.ignore_eos = False
-    b64 = None
+    b64 = b64_strong = None
     if not args.no_batched:
         fb1 = model.frame_bytes(1, int(PROMPT_T + (F - 1) / 2.0), masked_head=True)
         launches_bs1 = model.launches_per_frame(1)
@@ -471,6 +475,10 @@ def run_ours(args):
         del sess, model
         torch.cuda.empty_cache()
         b64 = measure_batched(dev, rank, world, batch=args.batch, ctx=args.batch_ctx, frames=args.batch_frames)
+        if world > 1:
+            # strong-scaling pair (SURVEY §8e "report both"): the SAME pool of `batch` requests spread over the GPUs
+            pool = partition.assign(args.batch, world)[rank]
+            b64_strong = measure_batched(dev, rank, world, batch=len(pool), ctx=args.batch_ctx, frames=args.batch_frames)
     dac = None
     if not args.no_dac:
         try:
@@ -489,12 +497,13 @@ def run_ours(args):
             c5 = measure_config5(dev, rank)
         except Exception as e:
             c5 = {"error": str(e)}
-    tms = torch.tensor([ms, e2e_t, b64[0] if b64 else 0.0, dac[0] if isinstance(dac, tuple) else 0.0], dtype=torch.float64, device=dev)
+    tms = torch.tensor([ms, e2e_t, b64[0] if b64 else 0.0, dac[0] if isinstance(dac, tuple) else 0.0,
+                        b64_strong[0] if b64_strong else 0.0], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(args.steps * F), float(e2e_frames)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    ms_max, e2e_t_max, b64_ms_max, dac_ms_max = float(tms[0]), float(tms[1]), float(tms[2]), float(tms[3])
+    ms_max, e2e_t_max, b64_ms_max, dac_ms_max, strong_ms_max = (float(x) for x in tms)
     total_frames, total_e2e_frames = float(cnt[0]), float(cnt[1])
     if rank != 0:
         if world > 1:
@@ -557,6 +566,15 @@ def run_ours(args):
                          "note": "algorithmic weight + KV bytes of one step for all requests (SURVEY §8d) / CUDA-event step time; "
                                  "kernels: rows_gemm_kernel (tcgen05 stream-K), attn_tc_kernel, finish kernels"},
         }
+        if b64_strong is not None:
+            per_gpu = -(-args.batch // world)
+            line["bs64"]["strong"] = {
+                "workload": "the same %d requests spread over %d GPUs by partition.assign (%d per GPU), same context and frames" % (args.batch, world, per_gpu),
+                "value": args.batch * FRAME_SEC / (strong_ms_max * 1e-3), "unit": "audio-s/s", "ms_per_step": strong_ms_max,
+                "speedup_vs_one_gpu": b64_ms_max / strong_ms_max,
+                "roofline_limit": b64[1] / b64_strong[1],
+                "note": "one GPU's step over all %d requests is this run's weak-scaling step (every GPU runs it); the limit is the ratio of the "
+                        "algorithmic bytes of the two steps: the weights stream once per step for any number of rows" % args.batch}
     if isinstance(dac, tuple):
         pk = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
         tpeak = float(pk.get("bf16_tflops_sustained", pk.get("bf16_tflops", 1375.8)))

@@ -25,6 +25,7 @@ struct fsb_dac {
                    //    16-bit weights are bound and the device has the tensor-map encoder; 0: the round-1 kernels above
     int half = 1;  // operand type of the tcgen05 pipeline: 1 fp16 (11-bit significand, as TF32), 0 bf16; set by the host mirror to
                    //    match the type it packed the ".h" weights in
+    int pos_offset = 0;  // position of frame 0 of the next decode calls in the window transformer's RoPE table (pieces of a long clip)
     int force_simt = 0;  // tcgen05 pipeline with every GEMM on the CUDA-core twin kernel (cross-check)
     int n_sm = 148;
     std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, int>, CUtensorMap> maps;
@@ -204,6 +205,7 @@ int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
     else if (n == "tc") h->tc = (int)value;
     else if (n == "half") { h->half = (int)value; h->maps.clear(); }
     else if (n == "force_simt") h->force_simt = (int)value;
+    else if (n == "pos_offset") { if (value < 0) return dfail(h, "pos_offset < 0"); h->pos_offset = (int)value; }
     else return dfail(h, "unknown option " + n);
     return 0;
 }
@@ -252,6 +254,11 @@ int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, voi
     if (!h || !codes || !wav) return 1;
     const fsb_dac_desc& d = h->d;
     if (B < 1 || B > d.max_batch || T < 1 || T > d.max_frames) return dfail(h, "B/T exceed the workspace (max_batch/max_frames)");
+    {
+        auto it = h->wn.find("tf.rope");
+        if (it != h->wn.end() && (int64_t)(h->pos_offset + T) * d.tf_head_dim > it->second)
+            return dfail(h, "pos_offset + T exceeds the bound tf.rope table");
+    }
     cudaStream_t s = (cudaStream_t)stream;
     if (h->tc && h->w.count("dec.in_w.h")) return decode_tc(h, codes, B, T, (float*)wav, s);
     Runner r{h, s, B};
@@ -281,7 +288,7 @@ int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, voi
         r.conv(b1, b2, T, D, 3 * H * HD, 1, 1, p + "wqkv", "", 0, nullptr, nullptr, nullptr, DEPI_NONE);
         {
             const long long n = rows * 2 * H * (HD / 2);
-            rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(b2, rope, B, T, H, HD);
+            rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(b2, rope, B, T, H, HD, h->pos_offset);
             dim3 grid((T + 3) / 4, H, B);
             const float scale = 1.f / sqrtf((float)HD);
             if (HD == 64) window_attn_kernel<64><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
@@ -384,7 +391,7 @@ int decode_tc_t(fsb_dac* h, void* codes, int B, int T, float* wav, cudaStream_t 
         r.tc(b1, T, D, 3 * H * HD, 1, 1, p + "wqkv", "", 0, nullptr, nullptr, nullptr, 0, TCV_ACT_NONE, nullptr, b2);
         {
             const long long n = rows * 2 * H * (HD / 2);
-            rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(b2, rope, B, T, H, HD);
+            rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(b2, rope, B, T, H, HD, h->pos_offset);
             dim3 grid((T + 3) / 4, H, B);
             const float scale = 1.f / sqrtf((float)HD);
             if (HD == 64) window_attn16_kernel<64, F16><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);

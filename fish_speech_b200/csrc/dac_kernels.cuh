@@ -346,7 +346,8 @@ __global__ void swiglu_kernel(const float* gu, float* out, long long rows, int F
 
 // ----------------------------------------------------------------------------- window attention (K12)
 // RoPE in place on the q and k thirds of qkv [B][T][3][H][HD] (modded_dac.py:455-467, table bf16-rounded)
-__global__ void rope_qk_kernel(float* qkv, const float* table, int B, int T, int H, int HD) {
+// `pos0` = position of row 0 (a clip decoded in overlapping pieces keeps its absolute positions)
+__global__ void rope_qk_kernel(float* qkv, const float* table, int B, int T, int H, int HD, int pos0) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int half = HD / 2;
     const long long total = (long long)B * T * 2 * H * half;
@@ -355,7 +356,7 @@ __global__ void rope_qk_kernel(float* qkv, const float* table, int B, int T, int
     const int h = (int)((i / half) % H);
     const int which = (int)((i / ((long long)half * H)) % 2);
     const long long bt = i / ((long long)half * H * 2);
-    const int t = (int)(bt % T);
+    const int t = (int)(bt % T) + pos0;
     float* v = qkv + (bt * 3 + which) * H * HD + (size_t)h * HD + 2 * p;
     const float c = table[((size_t)t * half + p) * 2], s = table[((size_t)t * half + p) * 2 + 1];
     const float x0 = v[0], x1 = v[1];

@@ -300,15 +300,67 @@ class DACB200:
         if indices.dim() != 3 or indices.shape[1] != self.config.n_codebooks + 1:
             raise ValueError(f"expected [B, {self.config.n_codebooks + 1}, T] indices, got {tuple(indices.shape)}")
         B, _, T = indices.shape
-        if T > self.max_frames:
-            raise ValueError(f"T={T} exceeds the engine's max_frames={self.max_frames}")
         idx = indices
         if idx.device != self.device or idx.dtype != torch.int64 or not idx.is_contiguous():
             idx = indices.to(device=self.device, dtype=torch.int64).contiguous()
         wav = torch.empty((B, 1, self.hop_length * T), dtype=torch.float32, device=self.device)
         st = torch.cuda.current_stream().cuda_stream
-        for b0 in range(0, B, self.max_batch):
-            nb = min(self.max_batch, B - b0)
-            self._ck(self.lib.fsb_dac_decode(self._h, idx[b0: b0 + nb].data_ptr(), nb, T, wav[b0: b0 + nb].data_ptr(), st))
+        if T <= self.max_frames:
+            for b0 in range(0, B, self.max_batch):
+                nb = min(self.max_batch, B - b0)
+                self._ck(self.lib.fsb_dac_decode(self._h, idx[b0: b0 + nb].data_ptr(), nb, T, wav[b0: b0 + nb].data_ptr(), st))
+            return wav
+        # A clip longer than the workspace: overlapping pieces.  Every layer of the decode side is causal with a finite
+        # reach (context_frames), so a piece that starts `halo` frames early reproduces the frames after the halo exactly,
+        # given their absolute RoPE positions (option "pos_offset").
+        halo = self.context_frames()
+        stride = self.max_frames - halo
+        if stride < 1:
+            raise ValueError(f"T={T} exceeds max_frames={self.max_frames}, and pieces need max_frames > {halo} (the decode "
+                             f"side's context in frames)")
+        self._ensure_rope(T)
+        hop = self.hop_length
+        try:
+            for b0 in range(0, B, self.max_batch):
+                nb = min(self.max_batch, B - b0)
+                t0 = 0
+                while t0 < T:
+                    a = max(0, t0 - halo)                      # piece = frames [a, t1), kept = [t0, t1)
+                    t1 = min(T, a + self.max_frames)
+                    piece = idx[b0: b0 + nb, :, a:t1].contiguous()
+                    out = torch.empty((nb, 1, hop * (t1 - a)), dtype=torch.float32, device=self.device)
+                    self.set_option("pos_offset", a)
+                    self._ck(self.lib.fsb_dac_decode(self._h, piece.data_ptr(), nb, t1 - a, out.data_ptr(), st))
+                    wav[b0: b0 + nb, :, hop * t0: hop * t1] = out[:, :, hop * (t0 - a):]
+                    if idx is indices:                         # keep the reference's in-place clamp visible to the caller
+                        idx[b0: b0 + nb, :, t0:t1] = piece[:, :, t0 - a:]
+                    t0 = t1
+        finally:
+            self.set_option("pos_offset", 0)
         return wav
+
+    def context_frames(self) -> int:
+        """How many earlier code frames an output sample can depend on: the causal convs' taps walked back from the waveform
+        to the code frames (modded_dac.py:599-620, 712-801; rvq.py:263-276) plus the window transformer's layers x (window - 1)
+        (modded_dac.py:380-398)."""
+        c = self.config
+        ctx = 6                                                # output conv, 7 taps
+        for s_ in reversed(list(c.decoder_rates)):
+            ctx += 6 * (1 + 3 + 9)                             # three residual units: 7 taps at dilation 1, 3, 9 (+ 1-tap convs)
+            ctx = -(-ctx // s_) + 1                            # transposed conv, kernel 2s stride s: one earlier input row
+        ctx += 6                                               # input conv, 7 taps
+        for f in reversed(list(c.upsample_factors)):
+            ctx += 6                                           # ConvNeXt depthwise conv, 7 taps
+            ctx = -(-ctx // f)                                 # transposed conv, kernel = stride
+        return ctx + c.tf_layers * (c.tf_window - 1)
+
+    def _ensure_rope(self, positions: int):
+        c = self.config
+        if self.weights["tf.rope"].shape[0] >= positions:
+            return
+        n = max(positions, 2 * self.weights["tf.rope"].shape[0])
+        torch.cuda.current_stream().synchronize()              # earlier launches may still read the old table
+        t = _rope_table(n, c.tf_head_dim, c.tf_rope_base).to(self.device, torch.float32).contiguous()
+        self.weights["tf.rope"] = t
+        self._ck(self.lib.fsb_dac_bind_weight(self._h, b"tf.rope", t.data_ptr(), t.numel()))
 

@@ -90,6 +90,43 @@ def test_dac_shim_formulas_vs_hf_port():
     assert torch.allclose(sn(x), D.snake(x, sn.alpha.detach()), atol=1e-6)
 
 
+def test_rvq_from_codes_vs_hf_port():
+    """descript ResidualVectorQuantize.from_codes (absent dependency, restated in oracle/dac_ref.py:rvq_dequant) against the
+    transformers port of the same class: codebook lookup + 1x1 out_proj summed over the codebooks, for the semantic quantizer
+    (1 codebook) and the residual quantizer (n_codebooks) as rvq.py:352-363 combines them."""
+    try:
+        from transformers.models.dac.configuration_dac import DacConfig
+        from transformers.models.dac.modeling_dac import DacResidualVectorQuantizer
+    except Exception:
+        pytest.skip("transformers DAC port not importable")
+    c = D.small_config()
+    torch.manual_seed(1)
+
+    def hf_rvq(n, size):
+        q = DacResidualVectorQuantizer(DacConfig(n_codebooks=n, codebook_size=size, codebook_dim=c.codebook_dim,
+                                                 hidden_size=c.latent_dim)).eval()
+        for prm in q.parameters():
+            torch.nn.init.normal_(prm, std=0.3)
+        return q
+
+    sem, res = hf_rvq(1, c.semantic_codebook_size), hf_rvq(c.n_codebooks, c.codebook_size)
+    sd = {}
+    for prefix, q in (("quantizer.semantic_quantizer", sem), ("quantizer.quantizer", res)):
+        for i, vq in enumerate(q.quantizers):
+            w = vq.out_proj.weight.detach()
+            p = f"{prefix}.quantizers.{i}."
+            sd[p + "codebook.weight"] = vq.codebook.weight.detach()
+            sd[p + "out_proj.weight_v"] = w                       # weight_norm(v, g = ||v||) is v itself
+            sd[p + "out_proj.weight_g"] = w.flatten(1).norm(dim=1).view(-1, 1, 1)
+            sd[p + "out_proj.bias"] = vq.out_proj.bias.detach()
+    codes = D.make_codes(c, 2, 17)
+    with torch.no_grad():
+        want = sem.from_codes(codes[:, :1])[0] + res.from_codes(codes[:, 1:])[0]
+    got = D.rvq_dequant(c, sd, codes.clone())
+    assert got.shape == want.shape
+    assert float((got - want).abs().max()) < 1e-5
+
+
 def test_dac_causality_property():
     """rvq.py:374-399 self-check: decoding a prefix equals the prefix of the decode (all convs causal)."""
     c = D.small_config()

@@ -108,6 +108,35 @@ def test_causality_and_batch_chunking():
     assert torch.equal(one[0], full[3])
 
 
+def test_clip_longer_than_the_workspace_decodes_in_pieces_bit_identically():
+    """A clip longer than max_frames goes through overlapping pieces (halo = context_frames, absolute RoPE positions): the
+    waveform must equal the one-pass decode of an engine whose workspace holds the whole clip, bit for bit, in every mode,
+    and stay at the oracle's SNR."""
+    c = D.small_config()
+    sd = D.make_state_dict(c, seed=5)
+    codes = D.make_codes(c, 3, 90)
+    big = _model(c, sd, max_batch=2, max_frames=96)
+    small = _model(c, sd, max_batch=2, max_frames=40)
+    assert small.context_frames() == 24                       # 2 layers x (8 - 1) keys + 10 frames of conv taps
+    for opts in (dict(tc=1), dict(tc=1, force_simt=1), dict(tc=0, tf32=0)):
+        for k, v in opts.items():
+            big.set_option(k, v)
+            small.set_option(k, v)
+        want = big.from_indices(codes.clone().cuda())
+        got = small.from_indices(codes.clone().cuda())
+        assert got.shape == want.shape
+        assert torch.equal(got, want), (opts, float((got - want).abs().max()))
+    ref = D.from_indices(c, sd, codes.clone())
+    assert snr_db(ref, got.cpu()) >= 60.0
+    again = small.from_indices(codes[:, :, :30].clone().cuda())  # the offset is reset after a pieced decode
+    assert torch.equal(again, big.from_indices(codes[:, :, :30].clone().cuda()))
+    # the caller's tensor is clamped in place like the reference does (rvq.py:354-359), pieces or not
+    wild = codes.clone().cuda()
+    wild[0, 1, 77] = 10_000
+    small.from_indices(wild)
+    assert int(wild[0, 1, 77]) == c.codebook_size - 1
+
+
 def test_errors():
     c = D.small_config()
     m = _model(c, D.make_state_dict(c, seed=3), max_frames=8)
