@@ -60,7 +60,7 @@ def test_dual_ar_and_dac_on_two_threads_match_their_serial_results():
     seqs, wavs = _in_threads(lm, codec)
     assert all(torch.equal(s, want_seq) for s in seqs)
     assert all(torch.equal(w, want_wav) for w in wavs)
-    m.check_device()
+    m.session(1, 65).check_device()
 
 
 def test_two_dual_ar_handles_on_two_threads():
@@ -72,5 +72,5 @@ def test_two_dual_ar_handles_on_two_threads():
     assert torch.equal(_run_generate(b, g, 48), want)
     ra, rb = _in_threads(lambda: [_run_generate(a, g, 48) for _ in range(2)], lambda: [_run_generate(b, g, 48) for _ in range(2)])
     assert all(torch.equal(s, want) for s in ra + rb)
-    a.check_device()
-    b.check_device()
+    a.session(1, 49).check_device()
+    b.session(1, 49).check_device()
