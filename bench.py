@@ -305,8 +305,8 @@ def cpu_dac_leg(frames=215):
 
 def measure_config5(dev, rank, T=8192, F=4096):
     """BASELINE configs[4]: long-form voice clone on one GPU: T-token prompt (pinned host), prompt pass (own tcgen05 GEMM + flash
-    attention), F decode frames at max_seq_len 16384 (context 8k -> 12k: kernel chain, the persistent frame kernel's attention
-    holds <= 2048 keys), then the DAC on the F frames; wall clock around everything incl. H2D of the prompt and D2H of the
+    attention), F decode frames at max_seq_len 16384 (context 8k -> 12k: kernel chain; the persistent frame kernel's tiled
+    instantiation, option mega_long = 1, measured slower at this length), then the DAC on the F frames; wall clock around everything incl. H2D of the prompt and D2H of the
     waveform, plus CUDA-event times of the three phases."""
     import torch
     from fish_speech_b200 import DualARTransformerB200, generate, s2_pro_config
@@ -370,7 +370,9 @@ def measure_config5(dev, rank, T=8192, F=4096):
                     "note": "includes the first frame; GEMM + causal attention FLOPs (SURVEY 8d); tcv_kernel + fa_prefill_kernel (tcgen05)"},
         "decode": {"ms_per_frame": ms_frame, "gbs": fbytes / ms_frame / 1e6, "frac_of_hbm": fbytes / ms_frame / 1e6 / peak,
                    "launches_per_frame": model.launches_per_frame(1),
-                   "note": "context 8k -> 12k: kernel chain (PDL-chained launches per frame in a CUDA graph), restricted LM head"},
+                   "note": ("context 8k -> 12k: frame_mega_kernel<128,4,true> (persistent, attention splits walk their keys in tiles)"
+                            if model.launches_per_frame(1) == 1 else
+                            "context 8k -> 12k: kernel chain (PDL-chained launches per frame in a CUDA graph)") + ", restricted LM head"},
         "dac": {"ms": dac_ms, "tflops": dac.flops(1, n_new) / dac_ms / 1e9, "frac_of_tensor_peak": dac.flops(1, n_new) / dac_ms / 1e9 / tpeak},
     }
     del model, dac

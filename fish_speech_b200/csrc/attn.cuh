@@ -790,6 +790,7 @@ struct AttnSplitSmem {
     alignas(16) float sc[GQ][asp_max_keys(HD)];
     alignas(16) float red[ASP_THREADS / 64][GQ][HD];
     float mrun[GQ], lrun[GQ];
+    float corr[GQ];  // TILED: rescale factor of the running numerators for the current key tile
     int is_last;
 };
 
@@ -809,7 +810,10 @@ __device__ __forceinline__ void attn_split_prefetch(const AttnArgs& a, const bf1
     l2_prefetch_bulk(vc + off, bytes);
 }
 
-template <int HD, int GQ, class SY>
+// TILED = true: a split may hold more than asp_max_keys keys (long caches): its range is walked in tiles of asp_max_keys with
+// a running (max, sum) per head and rescaled numerators (flash-decoding); the next tile's keys are requested as soon as this
+// tile's are consumed.  With one tile it computes what the untiled form computes.
+template <int HD, int GQ, class SY, bool TILED = false>
 __device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem<HD, GQ>& sm, int split, int h, int m,
                                                 int tid, unsigned tag_in, unsigned tag_out,
                                                 unsigned long long* trace = nullptr) {
@@ -887,76 +891,175 @@ __device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem
     }
     ASP_TRACE(0)
 
-    // ---- 3. scores
-#pragma unroll
-    for (int i = 0; i < ASP_KPT; ++i) {
-        const int jl = kslot + KPI * i;       // key index inside the split (warp-uniform validity: nk is uniform)
-        if (KPI * i >= nk) break;
-        float kf[8];
-        if (k0 + jl < kc1) unpack8(kq[i], kf);
-        else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) kf[e] = (jl < nk) ? sm.knew[asp_idx<HD>(chunk * 8 + e)] : 0.f;
-        }
-        float d[GQ];
-#pragma unroll
-        for (int g = 0; g < GQ; ++g) {
-            const float4 qa = *reinterpret_cast<const float4*>(&sm.qs[g][chunk * 4]);
-            const float4 qb = *reinterpret_cast<const float4*>(&sm.qs[g][(LPK + chunk) * 4]);
-            float s = qa.x * kf[0];
-            s = fmaf(qa.y, kf[1], s); s = fmaf(qa.z, kf[2], s); s = fmaf(qa.w, kf[3], s);
-            s = fmaf(qb.x, kf[4], s); s = fmaf(qb.y, kf[5], s); s = fmaf(qb.z, kf[6], s); s = fmaf(qb.w, kf[7], s);
-            d[g] = s;
-        }
-#pragma unroll
-        for (int o = LPK / 2; o > 0; o >>= 1)
-#pragma unroll
-            for (int g = 0; g < GQ; ++g) d[g] += __shfl_xor_sync(0xffffffffu, d[g], o);
-        if (chunk == 0 && jl < nk)
-#pragma unroll
-            for (int g = 0; g < GQ; ++g) sm.sc[g][jl] = d[g] * a.scale;
-    }
-    SY::sync();
-    ASP_TRACE(1)
-
-    // ---- 4. softmax over the split (fp32, like the MATH SDPA backend): warp g owns head g
-    if (warp < GQ) {
-        float mx = -INFINITY;
-        for (int j = lane; j < nk; j += 32) mx = fmaxf(mx, sm.sc[warp][j]);
-        mx = warp_max(mx);
-        float sum = 0.f;
-        for (int j = lane; j < nk; j += 32) {
-            const float pj = expf(sm.sc[warp][j] - mx);
-            sm.sc[warp][j] = pj;
-            sum += pj;
-        }
-        sum = warp_sum(sum);
-        if (lane == 0) { sm.mrun[warp] = mx; sm.lrun[warp] = sum; }
-    }
-    SY::sync();
-    ASP_TRACE(2)
-
-    // ---- 5. P.V
     float acc[GQ][8];
 #pragma unroll
     for (int g = 0; g < GQ; ++g)
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
-#pragma unroll
-    for (int i = 0; i < ASP_KPT; ++i) {
-        const int jl = kslot + KPI * i;
-        if (jl < nk) {
-            float vf[8];
-            if (k0 + jl < kc1) unpack8(vq[i], vf);
+    if constexpr (!TILED) {
+        // ---- 3. scores
+    #pragma unroll
+        for (int i = 0; i < ASP_KPT; ++i) {
+            const int jl = kslot + KPI * i;       // key index inside the split (warp-uniform validity: nk is uniform)
+            if (KPI * i >= nk) break;
+            float kf[8];
+            if (k0 + jl < kc1) unpack8(kq[i], kf);
             else {
+    #pragma unroll
+                for (int e = 0; e < 8; ++e) kf[e] = (jl < nk) ? sm.knew[asp_idx<HD>(chunk * 8 + e)] : 0.f;
+            }
+            float d[GQ];
+    #pragma unroll
+            for (int g = 0; g < GQ; ++g) {
+                const float4 qa = *reinterpret_cast<const float4*>(&sm.qs[g][chunk * 4]);
+                const float4 qb = *reinterpret_cast<const float4*>(&sm.qs[g][(LPK + chunk) * 4]);
+                float s = qa.x * kf[0];
+                s = fmaf(qa.y, kf[1], s); s = fmaf(qa.z, kf[2], s); s = fmaf(qa.w, kf[3], s);
+                s = fmaf(qb.x, kf[4], s); s = fmaf(qb.y, kf[5], s); s = fmaf(qb.z, kf[6], s); s = fmaf(qb.w, kf[7], s);
+                d[g] = s;
+            }
+    #pragma unroll
+            for (int o = LPK / 2; o > 0; o >>= 1)
+    #pragma unroll
+                for (int g = 0; g < GQ; ++g) d[g] += __shfl_xor_sync(0xffffffffu, d[g], o);
+            if (chunk == 0 && jl < nk)
+    #pragma unroll
+                for (int g = 0; g < GQ; ++g) sm.sc[g][jl] = d[g] * a.scale;
+        }
+        SY::sync();
+        ASP_TRACE(1)
+
+        // ---- 4. softmax over the split (fp32, like the MATH SDPA backend): warp g owns head g
+        if (warp < GQ) {
+            float mx = -INFINITY;
+            for (int j = lane; j < nk; j += 32) mx = fmaxf(mx, sm.sc[warp][j]);
+            mx = warp_max(mx);
+            float sum = 0.f;
+            for (int j = lane; j < nk; j += 32) {
+                const float pj = expf(sm.sc[warp][j] - mx);
+                sm.sc[warp][j] = pj;
+                sum += pj;
+            }
+            sum = warp_sum(sum);
+            if (lane == 0) { sm.mrun[warp] = mx; sm.lrun[warp] = sum; }
+        }
+        SY::sync();
+        ASP_TRACE(2)
+
+        // ---- 5. P.V
+    #pragma unroll
+        for (int i = 0; i < ASP_KPT; ++i) {
+            const int jl = kslot + KPI * i;
+            if (jl < nk) {
+                float vf[8];
+                if (k0 + jl < kc1) unpack8(vq[i], vf);
+                else {
+    #pragma unroll
+                    for (int e = 0; e < 8; ++e) vf[e] = sm.vnew[asp_idx<HD>(chunk * 8 + e)];
+                }
+    #pragma unroll
+                for (int g = 0; g < GQ; ++g) {
+                    const float pj = sm.sc[g][jl];
+    #pragma unroll
+                    for (int e = 0; e < 8; ++e) acc[g][e] = fmaf(pj, vf[e], acc[g][e]);
+                }
+            }
+        }
+
+    } else {
+        constexpr int MAXK = asp_max_keys(HD);
+        const int ntiles = max(1, (nk + MAXK - 1) / MAXK);
+        for (int t = 0; t < ntiles; ++t) {
+            const int tb = t * MAXK;                 // first key of the tile, counted inside the split
+            const int nkt = min(MAXK, nk - tb);      // keys of the tile (0 only for an empty split)
+            // ---- 3. scores of the tile
 #pragma unroll
-                for (int e = 0; e < 8; ++e) vf[e] = sm.vnew[asp_idx<HD>(chunk * 8 + e)];
+            for (int i = 0; i < ASP_KPT; ++i) {
+                const int jl = kslot + KPI * i;
+                if (KPI * i >= nkt) break;
+                float kf[8];
+                if (k0 + tb + jl < kc1) unpack8(kq[i], kf);
+                else {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) kf[e] = (jl < nkt) ? sm.knew[asp_idx<HD>(chunk * 8 + e)] : 0.f;
+                }
+                float d[GQ];
+#pragma unroll
+                for (int g = 0; g < GQ; ++g) {
+                    const float4 qa = *reinterpret_cast<const float4*>(&sm.qs[g][chunk * 4]);
+                    const float4 qb = *reinterpret_cast<const float4*>(&sm.qs[g][(LPK + chunk) * 4]);
+                    float s = qa.x * kf[0];
+                    s = fmaf(qa.y, kf[1], s); s = fmaf(qa.z, kf[2], s); s = fmaf(qa.w, kf[3], s);
+                    s = fmaf(qb.x, kf[4], s); s = fmaf(qb.y, kf[5], s); s = fmaf(qb.z, kf[6], s); s = fmaf(qb.w, kf[7], s);
+                    d[g] = s;
+                }
+#pragma unroll
+                for (int o = LPK / 2; o > 0; o >>= 1)
+#pragma unroll
+                    for (int g = 0; g < GQ; ++g) d[g] += __shfl_xor_sync(0xffffffffu, d[g], o);
+                if (chunk == 0 && jl < nkt)
+#pragma unroll
+                    for (int g = 0; g < GQ; ++g) sm.sc[g][jl] = d[g] * a.scale;
+            }
+            if (t + 1 < ntiles) {  // the key registers are free: request the next tile's keys now
+#pragma unroll
+                for (int i = 0; i < ASP_KPT; ++i) {
+                    const int j = k0 + tb + MAXK + kslot + KPI * i;
+                    kq[i] = (j < kc1) ? ld_stream(kbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
+                }
+            }
+            SY::sync();
+            // ---- 4. softmax of the tile against the running (max, sum): warp g owns head g
+            if (warp < GQ) {
+                const float m_old = t ? sm.mrun[warp] : -INFINITY, l_old = t ? sm.lrun[warp] : 0.f;
+                float mx = -INFINITY;
+                for (int j = lane; j < nkt; j += 32) mx = fmaxf(mx, sm.sc[warp][j]);
+                mx = fmaxf(warp_max(mx), m_old);
+                float sum = 0.f;
+                for (int j = lane; j < nkt; j += 32) {
+                    const float pj = expf(sm.sc[warp][j] - mx);
+                    sm.sc[warp][j] = pj;
+                    sum += pj;
+                }
+                sum = warp_sum(sum);
+                const float corr = t ? expf(m_old - mx) : 0.f;
+                if (lane == 0) { sm.mrun[warp] = mx; sm.lrun[warp] = fmaf(l_old, corr, sum); sm.corr[warp] = corr; }
+            }
+            SY::sync();
+            // ---- 5. P.V of the tile on top of the rescaled numerators
+            if (t) {
+#pragma unroll
+                for (int g = 0; g < GQ; ++g) {
+                    const float c = sm.corr[g];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) acc[g][e] *= c;
+                }
             }
 #pragma unroll
-            for (int g = 0; g < GQ; ++g) {
-                const float pj = sm.sc[g][jl];
+            for (int i = 0; i < ASP_KPT; ++i) {
+                const int jl = kslot + KPI * i;
+                if (jl < nkt) {
+                    float vf[8];
+                    if (k0 + tb + jl < kc1) unpack8(vq[i], vf);
+                    else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) acc[g][e] = fmaf(pj, vf[e], acc[g][e]);
+                        for (int e = 0; e < 8; ++e) vf[e] = sm.vnew[asp_idx<HD>(chunk * 8 + e)];
+                    }
+#pragma unroll
+                    for (int g = 0; g < GQ; ++g) {
+                        const float pj = sm.sc[g][jl];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) acc[g][e] = fmaf(pj, vf[e], acc[g][e]);
+                    }
+                }
+            }
+            if (t + 1 < ntiles) {
+#pragma unroll
+                for (int i = 0; i < ASP_KPT; ++i) {
+                    const int j = k0 + tb + MAXK + kslot + KPI * i;
+                    vq[i] = (j < kc1) ? ld_stream(vbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
+                }
+                SY::sync();  // the scores and factors of this tile are overwritten by the next one
             }
         }
     }

@@ -103,6 +103,8 @@ struct fsb_dual_ar {
     // options
     int use_pdl = 1, use_graph = 1, attn_splits = 0;
     int use_mega = 1;                // batch-1 frames as ONE persistent cooperative kernel (frame_mega.cuh)
+    int mega_long = 0;               // caches longer than ASP_MAXS x asp_max_keys tokens: 0 = kernel chain (faster as measured: 6.04
+                                     // vs 6.29 ms per frame at 8k context), 1 = tiled frame kernel, 2 = tiled kernel at any length (tests)
     int mega_skip_dot = 0;           // experiment (results are garbage): no dot products in the frame kernel
     int mega_detail_op = -1;         // profiling: op index whose per-iteration stamps are recorded (frame kernel)
     int mega_l2_ahead = 0;           // frame kernel: stages per producer lane prefetched into L2 while the ring is full
@@ -739,10 +741,25 @@ int enqueue_frame(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
 
 // ------------------------------------------------------------------------------------------- persistent frame kernel
 typedef void (*mega_fn)(MegaPlan);
-mega_fn pick_mega(int hd, int gq) {
-    if (hd == 128 && gq == 4) return frame_mega_kernel<128, 4>;
-    if (hd == 64 && gq == 4) return frame_mega_kernel<64, 4>;
+// `tiled`: the attention walks a split's keys in tiles (caches longer than ASP_MAXS x asp_max_keys tokens)
+mega_fn pick_mega(int hd, int gq, bool tiled = false) {
+    if (hd == 128 && gq == 4) return tiled ? frame_mega_kernel<128, 4, true> : frame_mega_kernel<128, 4, false>;
+    if (hd == 64 && gq == 4) return tiled ? frame_mega_kernel<64, 4, true> : frame_mega_kernel<64, 4, false>;
     return nullptr;
+}
+// attention splits per kv head inside the frame kernel: one CTA per item while they last, more splits when a split's key range
+// would not fit one tile (mega_long = 2 keeps the requested count: the tiled kernel on short caches, for tests)
+int mega_splits(const fsb_dual_ar* h) {
+    const int msplit = std::min(h->max_splits, ASP_MAXS), mk = asp_max_keys(h->d.head_dim);
+    int splits = h->attn_splits > 0 ? h->attn_splits : std::max(1, h->n_sm / h->d.n_kv_head);
+    splits = std::max(1, std::min(splits, msplit));
+    if (h->mega_long != 2)
+        while (splits < msplit && (h->kv_max_seq + splits - 1) / splits > mk) ++splits;
+    return splits;
+}
+bool mega_tiled(const fsb_dual_ar* h) {
+    const int splits = mega_splits(h);
+    return (h->kv_max_seq + splits - 1) / splits > asp_max_keys(h->d.head_dim);
 }
 
 // stage geometry of one GEMV inside the frame kernel: rows per stage (log2) or -1 if the shape does not fit
@@ -872,13 +889,8 @@ int build_mega_plan(fsb_dual_ar* h, cudaStream_t s, const fsb_frame_args& fa) {
     const MegaTagged t(h);
     mb.op(MOP_EMBED, 0, MSYNC_CTA);
     mb.wrote(t.x2);
-    int splits = h->attn_splits > 0 ? h->attn_splits : std::max(1, h->n_sm / d.n_kv_head);
-    const int msplit = std::min(h->max_splits, ASP_MAXS);
-    splits = std::max(1, std::min(splits, msplit));
-    // the frame kernel's attention holds a split's whole key range in one tile
-    while (splits < msplit && (h->kv_max_seq + splits - 1) / splits > asp_max_keys(d.head_dim)) ++splits;
-    if ((h->kv_max_seq + splits - 1) / splits > asp_max_keys(d.head_dim))
-        return fail(h, "context too long for the persistent frame kernel (set option mega=0)");
+    // short caches: a split's whole key range is one tile; longer ones take the tiled instantiation (mega_tiled)
+    const int splits = mega_splits(h);
     mb.add_layers(h, t, false, t.x2, fa.pos, fa.slots, -1, splits);
     const bf16* head = d.tie_word_embeddings ? h->emb : h->out_w;
     int head_lo = 0, head_n = d.vocab;
@@ -953,15 +965,15 @@ int launch_mega(fsb_dual_ar* h, cudaStream_t s) {
     at[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident: the in-kernel grid barrier depends on it
     at[0].val.cooperative = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    CK(cudaLaunchKernelEx(&cfg, pick_mega(h->d.head_dim, h->d.n_head / h->d.n_kv_head), h->mega_plan));
+    CK(cudaLaunchKernelEx(&cfg, pick_mega(h->d.head_dim, h->d.n_head / h->d.n_kv_head, mega_tiled(h)), h->mega_plan));
     return 0;
 }
 
-// the frame kernel's in-kernel attention holds one tile of asp_max_keys keys per split and at most ASP_MAXS splits: longer
-// caches (config 5: 8k-token prompts) take the kernel chain, whose attention loops over key tiles
+// batch 1 runs the persistent frame kernel while a split's keys fit one tile (caches up to ASP_MAXS x asp_max_keys tokens).
+// Longer caches (config 5: 8k-token prompts) take the kernel chain, whose attention kernel streams long key ranges better than
+// the frame kernel's tiled instantiation does today (option mega_long = 1 selects the latter)
 bool mega_active(const fsb_dual_ar* h, int batch) {
-    return h->use_mega && h->mega_supported && batch == 1 &&
-           h->kv_max_seq <= std::min(h->max_splits, ASP_MAXS) * asp_max_keys(h->d.head_dim);
+    return h->use_mega && h->mega_supported && batch == 1 && (h->mega_long || !mega_tiled(h));
 }
 
 __global__ void fill_prefill_kernel(int32_t* pos, int32_t* slot, int n, int pos0, int slot_v) {
@@ -1062,12 +1074,16 @@ int fsb_dual_ar_create(const fsb_dual_ar_desc* desc, int32_t max_seq_len, void* 
     CK(cudaMemset(h->mega_prof, 0, 16 * sizeof(unsigned long long)));
     if (h->rg_partial) h->rg_ok = h->n_sm <= RG_SM_MAX && rg_get_encode() != nullptr && rg_set_attrs() == cudaSuccess;
     if (mega_shape_ok(d)) {
-        mega_fn mf = pick_mega(d.head_dim, d.n_head / d.n_kv_head);
-        int coop = 0, occ = 0;
+        int coop = 0;
         CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
-        CK(cudaFuncSetAttribute((const void*)mf, cudaFuncAttributeMaxDynamicSharedMemorySize, MG_SMEM));
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)mf, MG_THREADS, MG_SMEM));
-        h->mega_supported = coop && occ >= 1;
+        h->mega_supported = coop != 0;
+        for (int tiled = 0; tiled < 2; ++tiled) {
+            mega_fn mf = pick_mega(d.head_dim, d.n_head / d.n_kv_head, tiled != 0);
+            int occ = 0;
+            CK(cudaFuncSetAttribute((const void*)mf, cudaFuncAttributeMaxDynamicSharedMemorySize, MG_SMEM));
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)mf, MG_THREADS, MG_SMEM));
+            h->mega_supported = h->mega_supported && occ >= 1;
+        }
     }
     h->slow.resize(d.n_layer);
     h->fast.resize(d.n_fast_layer);
@@ -1125,6 +1141,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "mega_l2_ahead") h->mega_l2_ahead = (int)value;
     else if (n == "mega_detail_op") h->mega_detail_op = (int)value;
     else if (n == "mega_skip_dot") h->mega_skip_dot = (int)value;
+    else if (n == "mega_long") h->mega_long = (int)value;
     else if (n == "attn_trace_point") h->attn_trace_point = (int)value;
     else if (n == "spin_ns") {  // poll back-off of tagged-load spins on the current device
         const unsigned ns = (unsigned)value;

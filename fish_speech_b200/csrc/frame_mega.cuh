@@ -455,7 +455,9 @@ __device__ __forceinline__ void mg_gemv(const MegaGemv* gp, unsigned char* stage
     }
 }
 
-template <int HD, int GQ>
+// LONG = true: the slow-AR attention walks a split's keys in tiles (caches beyond ASP_MAXS x asp_max_keys tokens); a separate
+// instantiation so that the short-context kernel keeps its code and register allocation
+template <int HD, int GQ, bool LONG = false>
 __global__ void __launch_bounds__(MG_THREADS, 1) frame_mega_kernel(MegaPlan p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[MG_NST];
@@ -539,7 +541,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) frame_mega_kernel(MegaPlan p) {
             for (int item = b; item < items; item += nb) {
                 const int split = item % a.splits, hm = item / a.splits;
                 if (tid == 0 && a.next_k != nullptr) attn_split_prefetch<HD>(a, a.next_k, a.next_v, split, hm % a.KV, hm / a.KV);
-                attn_split_body<HD, GQ, MgAll>(a, asm_, split, hm % a.KV, hm / a.KV, tid, mg_tag(seq, a.tag_in_op),
+                attn_split_body<HD, GQ, MgAll, LONG>(a, asm_, split, hm % a.KV, hm / a.KV, tid, mg_tag(seq, a.tag_in_op),
                                                mg_tag(seq, a.tag_out_op), tr);
                 MgAll::sync();
             }

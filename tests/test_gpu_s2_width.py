@@ -106,6 +106,64 @@ def test_frame_kernel_128_at_s2_width_vs_oracle_and_chain(s2w):
             assert mabs <= 0.1
 
 
+def test_tiled_frame_kernel_vs_one_tile_kernel_chain_and_oracle(s2w):
+    """frame_mega_kernel<128,4,true>: a split walks its keys in tiles of 128 with a running softmax (caches longer than 16 x 128
+    tokens).  Forced onto the 512-token cache (mega_long = 2 keeps the requested split count): 1 split x 4 tiles and 3 splits
+    x 2 tiles (ragged last tile, the new key in the last tile of the last split) against the one-tile kernel, the kernel
+    chain and the oracle."""
+    cfg, sd, m, om = s2w
+    V, cb, C = cfg.vocab_size, cfg.codebook_size, cfg.num_codebooks
+    gen = torch.Generator().manual_seed(5)
+    try:
+        for T, span in ((511, 200), (300, 40), (130, 0)):
+            seq = R.make_prompt(cfg, T, seed=T, voice_span=span)
+            uni = (torch.randint(0, 256, (1, 1, 2 * V + (C - 1) * cb), generator=gen).float() / 256).to(torch.bfloat16)
+            slow_1, fast_1, tok_1 = _frame(m, seq, uni, mega=1, masked_head=0, mega_long=0, attn_splits=0)
+            ref, _ = om.forward_generate(seq[None], torch.arange(T))
+            for splits in (1, 3):
+                slow_t, fast_t, tok_t = _frame(m, seq, uni, mega=1, masked_head=0, mega_long=2, attn_splits=splits)
+                assert m.launches_per_frame(1) == 1
+                _check(f"tiled frame kernel ({splits} split(s)) slow logits T={T}", slow_t, ref[0, -1])
+                mabs, _, _ = err_stats(slow_t, slow_1)
+                print(f"[parity] tiled ({splits} split(s)) vs one-tile frame kernel slow logits T={T}: max-abs {mabs:.4f}")
+                assert mabs <= _abs_tol(ref[0, -1])
+                if torch.equal(tok_t, tok_1):
+                    assert float((fast_t - fast_1).abs().max()) <= 0.1
+    finally:
+        m.set_option("mega_long", 0)
+        m.set_option("attn_splits", 0)
+
+
+def test_frame_kernel_past_2048_tokens_runs_persistent_and_matches_chain_and_oracle():
+    """A 2560-token cache (more than 16 splits x 128 keys): with option mega_long = 1 the frame is still ONE launch (tiled
+    instantiation), and its slow / fast logits agree with the kernel chain (the default at this length) and the oracle at
+    context 2300."""
+    from fish_speech_b200 import DualARTransformerB200
+    cfg = s2w_config(max_seq_len=2560)
+    sd = R.make_state_dict(cfg, seed=12)
+    m = DualARTransformerB200(cfg.__dict__, sd, device="cuda:0", max_rows=1)
+    m.setup_caches(1, cfg.max_seq_len)
+    om = R.DualARRef(cfg, sd)
+    om.setup_caches(1, cfg.max_seq_len)
+    V, cb, C = cfg.vocab_size, cfg.codebook_size, cfg.num_codebooks
+    T = 2300
+    seq = R.make_prompt(cfg, T, seed=8, voice_span=900)
+    uni = (torch.randint(0, 256, (1, 1, 2 * V + (C - 1) * cb), generator=torch.Generator().manual_seed(9)).float() / 256).to(torch.bfloat16)
+    assert m.launches_per_frame(1) > 1
+    slow_c, fast_c, tok_c = _frame(m, seq, uni, mega=1, masked_head=0)
+    slow_m, fast_m, tok_m = _frame(m, seq, uni, mega=1, masked_head=0, mega_long=1)
+    assert m.launches_per_frame(1) == 1
+    m.set_option("mega_long", 0)
+    ref, _ = om.forward_generate(seq[None], torch.arange(T))
+    _check("tiled frame kernel slow logits T=2300", slow_m, ref[0, -1])
+    _check("kernel chain slow logits T=2300", slow_c, ref[0, -1])
+    mabs, _, _ = err_stats(slow_m, slow_c)
+    print(f"[parity] tiled frame kernel vs chain slow logits T=2300: max-abs {mabs:.4f}")
+    assert mabs <= _abs_tol(ref[0, -1])
+    if torch.equal(tok_m, tok_c):
+        assert float((fast_m - fast_c).abs().max()) <= 0.1
+
+
 def test_frame_kernel_128_free_run_is_deterministic_and_in_range(s2w):
     """48 frames back to back from one graph at the S2 width: replay-deterministic, graph == eager, codes in range."""
     from fish_speech_b200 import generate
