@@ -155,18 +155,93 @@ def cpu_reference_leg(frames: int, steps: int = 1, warmup: int = 0):
     return FRAME_SEC / spf, cores, sample, spf
 
 
+def cpu_reference_leg_ref(frames: int, steps: int = 1, warmup: int = 0):
+    """The same workload through THE REFERENCE'S OWN code: `generate()` of fish_speech/models/text2semantic/inference.py
+    (vendored unmodified into oracle/_ref by oracle/make_ref.py) on a `DualARTransformer` of the S2-Pro shape, bf16, all host
+    threads, 512-token prompt, `frames` new tokens per call.  The frames after the prompt pass are what is timed
+    (`decode_n_tokens`, inference.py:165-238), like the GPU arm's `value`; the prompt pass is reported in the sample text.
+    Returns (audio-sec/sec, cores, sample description, seconds per frame)."""
+    import torch
+    from oracle import dual_ar_ref as R
+    from oracle import make_ref
+    llama, inf = make_ref.import_vendored()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = R.s2_config(max_seq_len=2048)
+    g = torch.Generator().manual_seed(0)
+    block = (torch.randn(1 << 20, generator=g) * cfg.initializer_range).to(torch.bfloat16)
+    with torch.device("meta"):   # 4.5 B parameters: no default initialisation pass, the tiled block below is assigned instead
+        m = llama.DualARTransformer(llama.DualARModelArgs(**cfg.to_ref_kwargs())).eval().to(torch.bfloat16)
+    sd = {}
+    for name, prm in m.state_dict().items():
+        n = prm.numel()
+        sd[name] = (torch.ones(prm.shape, dtype=torch.bfloat16) if prm.dim() == 1
+                    else block.repeat((n + block.numel() - 1) // block.numel())[:n].view(prm.shape))
+    m.load_state_dict(sd, assign=True, strict=True)
+    # the non-persistent buffers were built on the meta device: rebuild them as the constructors do (llama.py:279-297, 696-704)
+    m.freqs_cis = llama.precompute_freqs_cis(cfg.max_seq_len, cfg.head_dim, cfg.rope_base)
+    m.causal_mask = torch.tril(torch.ones(cfg.max_seq_len, cfg.max_seq_len, dtype=torch.bool))
+    m.fast_freqs_cis = llama.precompute_freqs_cis(cfg.num_codebooks, m.config.fast_head_dim, cfg.rope_base)
+
+    class Tok:   # generate() asks the tokenizer for <|im_end|> only (inference.py:207, 320)
+        def get_token_id(self, _name):
+            return cfg.im_end_id
+    m.tokenizer = Tok()
+    prompt = R.make_prompt(cfg, PROMPT_T, seed=1)
+    real_n = inf.decode_n_tokens
+    spans = []
+
+    def timed_n(*a, **k):
+        t0 = time.perf_counter()
+        r = real_n(*a, **k)
+        spans.append((time.perf_counter() - t0, r.shape[1]))
+        return r
+    inf.decode_n_tokens = timed_n
+    times, prefill_s = [], 0.0
+    try:
+        with torch.inference_mode():
+            for it in range(warmup + steps):
+                t0 = time.perf_counter()
+                inf.generate(model=m, prompt=prompt, max_new_tokens=frames + 1, audio_masks=None, audio_parts=None,
+                             temperature=0.8, top_p=0.8, top_k=30)
+                total = time.perf_counter() - t0
+                dt, n = spans[-1]
+                prefill_s = total - dt
+                if it >= warmup and n > 0:
+                    times.append(dt / n)
+    finally:
+        inf.decode_n_tokens = real_n
+    spf = statistics.mean(times)
+    sample = (f"reference generate() (oracle/_ref, unmodified): {frames} decode frames/step x {steps} step(s) after its {PROMPT_T}-token "
+              f"prompt pass ({prefill_s:.1f} s, not counted), S2-Pro shape bf16, bs1, max_seq_len 2048")
+    return FRAME_SEC / spf, cores, sample, spf
+
+
+def cpu_leg(frames: int, steps: int = 1, warmup: int = 0):
+    """(value, cores, sample, s/frame, kind): the vendored reference when oracle/_ref exists, else the oracle port."""
+    from oracle import make_ref
+    if make_ref.available():
+        try:
+            return (*cpu_reference_leg_ref(frames, steps, warmup), "reference")
+        except Exception as e:  # a broken vendored copy must not cost the baseline
+            sys.stderr.write(f"[bench] vendored reference failed ({e}); timing the oracle port instead\n")
+    return (*cpu_reference_leg(frames, steps, warmup), "port")
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     frames = max(1, args.ref_frames)
-    v, cores, sample, spf = cpu_reference_leg(frames, steps=max(1, args.steps), warmup=min(args.warmup, 1))
+    v, cores, sample, spf, kind = cpu_leg(frames, steps=max(1, args.steps), warmup=min(args.warmup, 1))
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": spf * 1e3 * frames, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "S2-Pro-shape Dual-AR decode, batch 1, CPU", "frames_per_step": frames},
-        "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": "S2-Pro-shape Dual-AR decode, batch 1, 512-token prompt, %d-frame decode (BASELINE configs[1])" % args.frames,
+                   "prompt_tokens": PROMPT_T, "frames_per_step": frames,
+                   "sample": "host cores, %d frames per step after the prompt pass (a bounded sample of the %d-frame workload)" % (frames, args.frames)},
+        "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -286,20 +361,33 @@ def measure_dac(dev, B=32, T=646, iters=2):
 
 
 def cpu_dac_leg(frames=215):
-    """The reference's CPU codec path on a bounded sample: oracle/dac_ref.py (fp32 restatement of DAC.from_indices pinned to the
-    reference classes) on ONE clip of `frames` code frames (10 s of audio), all host threads; audio-s/s."""
+    """The reference's CPU codec path on a bounded sample: ONE clip of `frames` code frames (10 s of audio), fp32, all host
+    threads; audio-s/s.  With oracle/_ref present it is the reference's own `DAC.from_indices` (modded_dac.py:925-927, classes
+    instantiated as configs/modded_dac_vq.yaml describes), else oracle/dac_ref.py, the restatement pinned to those classes."""
     import torch
     from oracle import dac_ref as D
+    from oracle import make_ref
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     c = D.DACConfig()
     sd = D.make_state_dict(c, seed=0)
     codes = D.make_codes(c, 1, frames)
-    t0 = time.perf_counter()
-    D.from_indices(c, sd, codes)
-    dt = time.perf_counter() - t0
-    return {"value": frames * c.hop / c.sample_rate / dt, "unit": "audio-s/s", "cores": cores, "kind": "port",
-            "sample": f"1 clip x {frames} code frames ({frames * c.hop / c.sample_rate:.1f} s of audio), fp32, oracle port of DAC.from_indices; "
+    kind, fn = "port", (lambda: D.from_indices(c, sd, codes))
+    if make_ref.available() and (make_ref.DEST / "fish_speech/models/dac/modded_dac.py").exists():
+        try:
+            from oracle.gen_golden_dac import build_reference_dac
+            ref = build_reference_dac(c, importer=make_ref.import_vendored)
+            ref.load_state_dict(sd, strict=False)
+            kind, fn = "reference", (lambda: ref.from_indices(codes))
+        except Exception as e:
+            sys.stderr.write(f"[bench] vendored reference codec failed ({e}); timing the oracle port instead\n")
+    with torch.inference_mode():
+        t0 = time.perf_counter()
+        fn()
+        dt = time.perf_counter() - t0
+    what = "reference DAC.from_indices (oracle/_ref, unmodified)" if kind == "reference" else "oracle port of DAC.from_indices"
+    return {"value": frames * c.hop / c.sample_rate / dt, "unit": "audio-s/s", "cores": cores, "kind": kind,
+            "sample": f"1 clip x {frames} code frames ({frames * c.hop / c.sample_rate:.1f} s of audio), fp32, {what}; "
                       "32 x 30 s clips would take 96x as long"}
 
 
@@ -595,8 +683,8 @@ def run_ours(args):
         line["config5"] = c5
     if not args.no_cpu and world >= 1:
         try:
-            v, cores, sample, _ = cpu_reference_leg(args.ref_frames)
-            line["cpu_baseline"] = {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample}
+            v, cores, sample, _, kind = cpu_leg(args.ref_frames)
+            line["cpu_baseline"] = {"value": v, "unit": "audio-s/s", "cores": cores, "kind": kind, "sample": sample}
         except Exception as e:  # the GPU numbers stand on their own
             line["cpu_baseline"] = {"value": None, "unit": "audio-s/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
     print(json.dumps(line))

@@ -14,9 +14,10 @@ from oracle import dac_ref as D
 from oracle.gen_golden import GOLD, import_reference
 
 
-def build_reference_dac(c: D.DACConfig):
-    """Hand-instantiate what configs/modded_dac_vq.yaml describes (hydra is absent)."""
-    import_reference()
+def build_reference_dac(c: D.DACConfig, importer=import_reference):
+    """Hand-instantiate what configs/modded_dac_vq.yaml describes (hydra is absent).  `importer` puts the reference package on
+    the path: the read-only checkout (default) or its vendored copy (oracle.make_ref.import_vendored)."""
+    importer()
     from fish_speech.models.dac import modded_dac as M
     from fish_speech.models.dac import rvq
 

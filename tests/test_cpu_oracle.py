@@ -164,6 +164,21 @@ def test_product_path_fails_loudly_without_cuda():
         DualARTransformerB200(cfg, {}, device="cuda:0")
 
 
+def test_vendored_reference_recipe():
+    """oracle/make_ref.py: where the checkout exists the recipe fills oracle/_ref (git-ignored) and the vendored modules import
+    from there alone; the path-level functions bench.py's CPU arm calls are the reference's."""
+    from oracle import make_ref
+    if not make_ref.make(verbose=False) and not make_ref.available():
+        pytest.skip("no reference checkout and no vendored copy")
+    llama, inf = make_ref.import_vendored()
+    assert str(make_ref.DEST) in inf.__file__ and str(make_ref.DEST) in llama.__file__
+    for fn in ("generate", "decode_n_tokens", "decode_one_token_ar"):
+        assert callable(getattr(inf, fn))
+    assert "oracle/_ref/" in (ROOT / ".gitignore").read_text()
+    ignore = ROOT / ".gpurunignore"
+    assert not ignore.exists() or "oracle/_ref" not in ignore.read_text()
+
+
 def test_product_does_not_import_oracle():
     for p in (ROOT / "fish_speech_b200").rglob("*.py"):
         assert "oracle" not in re.sub(r'""".*?"""', "", p.read_text(), flags=re.S).replace("# oracle", ""), p
