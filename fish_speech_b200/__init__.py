@@ -14,3 +14,4 @@ __all__ = ["DACB200", "DACConfig", "partition", "DualARConfig", "DualARTransform
            "init_model_from_state_dict", "make_semantic_logit_bias", "s2_pro_config"]
 
 from .checkpoint import init_model, load_codec, load_config, load_weights  # noqa: E402,F401
+from . import scheduler  # noqa: E402,F401

@@ -1,0 +1,192 @@
+"""Host logic of the continuous-batching worker (fish_speech_b200/scheduler.py) against a CPU stand-in for the engine: the
+stand-in produces, for every KV slot, a token stream that depends only on the prompt in that slot and the position, so the
+expected output of a request is known whatever it was scheduled with.  (The GPU tests run the same scheduler on the engine.)"""
+import queue
+import types
+
+import pytest
+import torch
+
+from fish_speech_b200.scheduler import (ContinuousBatcher, GenerateRequest, GenerateResponse, WrappedGenerateResponse,
+                                        launch_thread_safe_queue)
+
+C = 3            # codebooks
+SEM0, CB, IM_END, S = 100, 16, 7, 64
+
+
+class FakeSession:
+    def __init__(self, model, batch, max_frames):
+        self.model, self.batch, self.max_frames = model, batch, max_frames
+        self.cur_tokens = torch.zeros((batch, C + 1), dtype=torch.int32)
+        self.pos = torch.zeros((batch,), dtype=torch.int32)
+        self.ras_window = torch.zeros((batch, 10), dtype=torch.int32)
+        self.out_tokens = torch.zeros((max_frames, batch, C + 1), dtype=torch.int32)
+        self.frame_counter = torch.zeros((1,), dtype=torch.int32)
+        self.done = torch.zeros((batch,), dtype=torch.int32)
+        self.bias = None
+        self.restrict_scan = True
+        self.calls = []
+
+    def run(self, n, temperature, top_p, top_k, use_ras, pos_bound=None):
+        m = self.model
+        assert n <= self.max_frames
+        assert int(self.pos.max()) + n <= m.max_seq_len, "a row would step past the cache"
+        self.calls.append((n, temperature, top_p, top_k, [int(d) for d in self.done]))
+        for f in range(n):
+            for r in range(self.batch):
+                p = int(self.pos[r])
+                tok = m.stream(r, p + 1)
+                self.cur_tokens[r] = torch.tensor(tok, dtype=torch.int32)
+                if tok[0] == IM_END:
+                    self.done[r] = 1
+                self.out_tokens[f, r] = self.cur_tokens[r]
+                self.pos[r] = p + 1
+            self.frame_counter += 1
+
+
+class FakeModel:
+    """Token at position p of the request whose prompt sums to h: main = SEM0 + (h + p) % CB, codes = (h + p + i) % CB;
+    <|im_end|> at position eos_at(h) = prompt_len + 3 + h % 9."""
+
+    def __init__(self, max_rows=3):
+        self.max_rows = max_rows
+        self.config = types.SimpleNamespace(num_codebooks=C, max_seq_len=S, im_end_id=IM_END, vocab_size=SEM0 + CB,
+                                            semantic_begin_id=SEM0, semantic_end_id=SEM0 + CB - 1, codebook_size=CB)
+        self.device = torch.device("cpu")
+        self.tokenizer = types.SimpleNamespace(get_token_id=lambda _n: IM_END)
+        self._cache_setup_done = False
+        self.max_batch_size = 0
+        self.slots = {}
+        self.admitted = []
+
+    def setup_caches(self, rows, max_seq_len, dtype=torch.bfloat16):
+        self.max_batch_size, self.max_seq_len, self._cache_setup_done = rows, max_seq_len, True
+
+    def session(self, batch, max_frames):
+        self._s = FakeSession(self, batch, max_frames)
+        return self._s
+
+    def prefill(self, cols, pos0, slot):
+        T = cols.shape[-1] + 1
+        h = int(cols.sum()) % 1000
+        self.slots[slot] = (h, T)
+        self.admitted.append(h)
+
+    def stream(self, slot, p):
+        if slot not in self.slots:
+            return [SEM0] * (C + 1)
+        h, T = self.slots[slot]
+        h2 = h + int(self._s.cur_tokens[slot].sum()) * 0      # the stream depends on the slot's prompt and position only
+        if p >= eos_at(h, T):
+            return [IM_END] + [0] * C
+        return [SEM0 + (h2 + p) % CB] + [(h2 + p + i) % CB for i in range(C)]
+
+
+def eos_at(h, T):
+    return T + 3 + h % 9
+
+
+def prompt(T, seed):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randint(0, 50, (C + 1, T), generator=g)
+
+
+def expected(p, max_new):
+    T = p.shape[1]
+    h = int(p[:, :-1].sum()) % 1000
+    budget = min(max_new, S - T) if max_new else S - T
+    frames = []
+    for k in range(budget):
+        pos = T + k
+        if pos >= eos_at(h, T):
+            frames.append([IM_END] + [0] * C)
+            break
+        frames.append([SEM0 + (h + pos) % CB] + [(h + pos + i) % CB for i in range(C)])
+    seq = torch.tensor(frames, dtype=torch.int32)
+    return seq[:-1, 1:].t().contiguous()
+
+
+def req(p, max_new=0, **kw):
+    return GenerateRequest(request=dict(prompt=p, max_new_tokens=max_new, **kw), response_queue=queue.Queue())
+
+
+def drain(q):
+    out = []
+    while not q.empty():
+        out.append(q.get_nowait())
+    return out
+
+
+def test_every_request_gets_its_own_stream_whatever_it_shares_the_batch_with():
+    m = FakeModel(max_rows=3)
+    b = ContinuousBatcher(m, chunk_frames=4)
+    items = [req(prompt(5 + i, i), max_new=(0 if i % 3 else 6)) for i in range(8)]
+    for it in items:
+        b.submit(it)
+    done = b.run_until_idle()
+    assert len(done) == len(items) and b.idle()
+    by_id = {id(it): res for it, res in done}
+    for it in items:
+        want = expected(it.request["prompt"], it.request["max_new_tokens"])
+        got = by_id[id(it)]
+        assert got.dtype == torch.int32 and torch.equal(got, want), (got, want)
+    assert max(len([d for d in c[4] if d == 0]) for c in m._s.calls) == 3       # the rows were used together
+    assert b.frames_kept <= b.frames_run
+
+
+def test_sampling_parameters_group_batches_without_starvation():
+    m = FakeModel(max_rows=3)
+    b = ContinuousBatcher(m, chunk_frames=4)
+    a1, hot, a2 = req(prompt(5, 1), temperature=0.7), req(prompt(6, 2), temperature=1.0), req(prompt(7, 3), temperature=0.7)
+    for it in (a1, hot, a2):
+        b.submit(it)
+    done = b.run_until_idle()
+    assert [id(x[0]) for x in done].index(id(hot)) < [id(x[0]) for x in done].index(id(a2))   # arrival order kept across groups
+    hs = [int(it.request["prompt"][:, :-1].sum()) % 1000 for it in (a1, hot, a2)]
+    assert m.admitted == hs
+    temps = sorted({round(c[1], 3) for c in m._s.calls})
+    assert temps == [round(float(torch.tensor(0.7, dtype=torch.bfloat16)), 3), 1.0]
+    for c in m._s.calls:                                                          # one value per step
+        assert c[1] in (float(torch.tensor(0.7, dtype=torch.bfloat16)), 1.0)
+
+
+def test_bad_requests_fail_alone():
+    m = FakeModel(max_rows=2)
+    b = ContinuousBatcher(m, chunk_frames=3)
+    good, long_, shape = req(prompt(5, 1)), req(prompt(S, 2)), req(torch.zeros((2, 4), dtype=torch.long))
+    for it in (long_, good, shape):
+        b.submit(it)
+    res = {id(it): r for it, r in b.run_until_idle()}
+    assert isinstance(res[id(long_)], ValueError) and "exceeds max_seq_len" in str(res[id(long_)])   # inference.py:262-265
+    assert isinstance(res[id(shape)], ValueError)
+    assert torch.equal(res[id(good)], expected(good.request["prompt"], 0))
+
+
+def test_idle_rows_never_run_past_the_cache():
+    m = FakeModel(max_rows=3)
+    b = ContinuousBatcher(m, chunk_frames=5)
+    p = prompt(4, 9)
+    m.stream = lambda slot, pos: [SEM0 + pos % CB] + [pos % CB] * C          # never ends: runs to the end of the cache
+    b.submit(req(p))
+    (it, codes), = b.run_until_idle()
+    assert codes.shape == (C, S - 4 - 1)
+    with pytest.raises(ValueError):
+        ContinuousBatcher(m, max_rows=4)
+
+
+def test_queue_protocol_of_the_worker_thread():
+    m = FakeModel(max_rows=2)
+    q_in = launch_thread_safe_queue(model=m, max_rows=2, chunk_frames=4)
+    items = [req(prompt(5 + i, 20 + i)) for i in range(5)] + [req(prompt(S + 1, 3))]
+    for it in items:
+        q_in.put(it)
+    for it in items[:-1]:
+        first = it.response_queue.get(timeout=30)
+        second = it.response_queue.get(timeout=30)
+        assert isinstance(first, WrappedGenerateResponse) and first.status == "success"
+        assert isinstance(first.response, GenerateResponse) and first.response.action == "sample"
+        assert torch.equal(first.response.codes, expected(it.request["prompt"], 0))
+        assert second.status == "success" and second.response.action == "next"
+    err = items[-1].response_queue.get(timeout=30)
+    assert err.status == "error" and isinstance(err.response, ValueError)
+    q_in.put(None)

@@ -1,0 +1,78 @@
+"""Continuous batching on the engine (fish_speech_b200/scheduler.py): requests that join and leave a running batch must get
+exactly the frames they get when they run alone through the same many-row kernels (greedy sampling: top_k = 1, RAS off, so the
+draws do not matter), through the reference's queue protocol (inference.py:736-799)."""
+import queue
+
+import pytest
+import torch
+
+from oracle import dual_ar_ref as R
+from tests.util import cfg_from_golden, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(max_rows):
+    from fish_speech_b200 import DualARTransformerB200
+    g = load_golden("dual_ar_tiny_greedy")
+    cfg = cfg_from_golden(g)
+    m = DualARTransformerB200(cfg.__dict__, R.make_state_dict(cfg, seed=g["wseed"]), device="cuda:0", max_rows=max_rows)
+    m.setup_caches(max_rows, cfg.max_seq_len)
+    return cfg, m
+
+
+def _requests(cfg, n):
+    from fish_speech_b200.scheduler import GenerateRequest
+    out = []
+    for i in range(n):
+        T = 6 + 3 * (i % 5)
+        p = R.make_prompt(cfg, T, seed=700 + i, voice_span=3 if i % 2 else 0)
+        out.append(GenerateRequest(request=dict(prompt=p, max_new_tokens=5 + 4 * (i % 4), temperature=0.8, top_p=0.8, top_k=1),
+                                   response_queue=queue.Queue()))
+    return out
+
+
+def test_joining_and_leaving_rows_get_the_frames_they_get_alone():
+    from fish_speech_b200.scheduler import ContinuousBatcher
+    cfg, m = _model(4)
+    b = ContinuousBatcher(m, chunk_frames=4, use_ras=False)
+    b.sess.bias[cfg.im_end_id] = 1.5             # some requests end on <|im_end|> before their budget
+    items = _requests(cfg, 9)
+    for it in items:
+        b.submit(it)
+    got = {id(it): res for it, res in b.run_until_idle()}
+    assert len(got) == len(items)
+    b.sess.check_device()
+    n_eos = 0
+    for it in items:
+        solo = ContinuousBatcher(m, chunk_frames=4, use_ras=False)
+        solo.sess.bias[cfg.im_end_id] = 1.5
+        solo.submit(it)
+        (_, want), = solo.run_until_idle()
+        codes = got[id(it)]
+        assert codes.shape[0] == cfg.num_codebooks and codes.dtype == torch.int32
+        assert torch.equal(codes.cpu(), want.cpu()), (codes, want)
+        assert bool((codes >= 0).all()) and bool((codes < cfg.codebook_size).all())
+        n_eos += int(codes.shape[1] < it.request["max_new_tokens"] - 1)
+    print(f"[sched] 9 requests over 4 rows: {b.steps} steps, {b.frames_kept} frames kept of {b.frames_run} row-frames run, "
+          f"{n_eos} ended on <|im_end|>")
+    assert b.frames_kept <= b.frames_run
+
+
+def test_worker_thread_serves_the_queue_protocol():
+    from fish_speech_b200.scheduler import launch_thread_safe_queue
+    cfg, m = _model(4)
+    q_in = launch_thread_safe_queue(model=m, max_rows=4, chunk_frames=4)
+    items = _requests(cfg, 6)
+    bad = _requests(cfg, 1)[0]
+    bad.request["prompt"] = R.make_prompt(cfg, cfg.max_seq_len, seed=1)
+    for it in items + [bad]:
+        q_in.put(it)
+    for it in items:
+        a, b_ = it.response_queue.get(timeout=120), it.response_queue.get(timeout=120)
+        assert a.status == "success" and a.response.action == "sample" and b_.response.action == "next"
+        n = a.response.codes.shape[1]
+        assert a.response.codes.shape[0] == cfg.num_codebooks and 0 <= n <= it.request["max_new_tokens"] - 1
+    e = bad.response_queue.get(timeout=120)
+    assert e.status == "error" and isinstance(e.response, ValueError)
+    q_in.put(None)
