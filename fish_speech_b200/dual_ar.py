@@ -151,6 +151,14 @@ class DualARTransformerB200:
         self.max_seq_len = -1
         self.max_batch_size = -1
         self._cache_setup_done = False
+        # prefix caching: tokens [C+1, n] whose KV the PROMPT PASS left in slot 0 at positions [0, n).  A
+        # later prompt that starts with the same columns skips them (bit-identical to recomputing: a prompt row's result
+        # does not depend on which rows share its chunk).  "all" also reuses positions written by decode frames (the growing
+        # conversation of generate_long, inference.py:620-688): their KV came through the decode kernels, equal within the
+        # logit tolerance rather than bit for bit.  False switches it off.
+        self.prefix_cache = True
+        self._kv_tokens: Optional[Tensor] = None
+        self.prefix_hits = 0           # prompt columns skipped so far
         self._h = C.c_void_p()
         self._keep: List[Tensor] = []
         with torch.cuda.device(self.device):
@@ -235,6 +243,7 @@ class DualARTransformerB200:
                                                   c.num_codebooks))
         self._cache_setup_done = True
         self._session = None
+        self._kv_tokens = None
 
     def _buffer(self, name: str, dtype=torch.bfloat16) -> Tensor:
         p, n = C.c_void_p(), C.c_size_t()
@@ -244,11 +253,36 @@ class DualARTransformerB200:
     def prefill(self, prompt_cols: Tensor, pos0: int = 0, slot: int = 0):
         """Slow-stack pass over prompt columns [C+1, T] (any int dtype): fills KV, produces no logits."""
         T = prompt_cols.shape[-1]
+        if slot == 0:
+            self._kv_tokens = None   # slot 0 is rewritten by a caller that does not go through prefill_cached
         if T == 0:
             return
         tok = prompt_cols.reshape(self.config.num_codebooks + 1, T).t().to(device=self.device, dtype=torch.int32).contiguous()
         self._keep = [tok]
         self._ck(self.lib.fsb_dual_ar_prefill(self._h, tok.data_ptr(), T, slot, pos0, _stream()), ValueError)
+
+    def prefill_cached(self, prompt_cols: Tensor) -> int:
+        """Prompt pass into slot 0 from position 0 that skips the leading columns whose KV is already there (see
+        `prefix_cache`); returns how many were skipped."""
+        C1 = self.config.num_codebooks + 1
+        cols = prompt_cols.reshape(C1, -1).to(device=self.device, dtype=torch.int32)
+        T = cols.shape[1]
+        have = self._kv_tokens
+        L = 0
+        if self.prefix_cache and have is not None and T > 0:
+            m = min(T, have.shape[1])
+            same = (cols[:, :m] == have[:, :m]).all(0)
+            L = m if bool(same.all()) else int((~same).nonzero()[0])
+        self.prefill(cols[:, L:], L, 0)
+        self._kv_tokens = cols.clone() if self.prefix_cache else None
+        self.prefix_hits += L
+        return L
+
+    def _kv_written_from(self, pos: int):
+        """A decode frame writes slot 0 at `pos` and after: the prompt-pass record ends there (mode "all" keeps what generate()
+        recorded for the frames it fed)."""
+        if self._kv_tokens is not None and self._kv_tokens.shape[1] > pos:
+            self._kv_tokens = self._kv_tokens[:, :pos]
 
     def forward_generate(self, inp: Tensor, input_pos: Optional[Tensor] = None, audio_masks=None, audio_parts=None,
                          return_all: bool = False) -> ForwardResult:
@@ -266,6 +300,7 @@ class DualARTransformerB200:
             if B != 1:
                 raise ValueError("prompt pass supports batch 1 (reference: inference.py:284-288)")
             self.prefill(inp[0, :, :-1], int(input_pos[0]), 0)
+        self._kv_written_from(int(input_pos[-1]))
         tok = inp[:, :, -1].to(device=self.device, dtype=torch.int32).contiguous()
         pos = input_pos[-1:].to(device=self.device, dtype=torch.int32).expand(B).contiguous()
         self._ck(self.lib.fsb_dual_ar_slow_step(self._h, B, tok.data_ptr(), pos.data_ptr(), None, _stream()))
@@ -417,7 +452,11 @@ def decode_one_token_ar(model: DualARTransformerB200, x: Tensor, input_pos: Tens
     if p_last >= model.max_seq_len or p_last - (Tq - 1) < 0:
         raise ValueError(f"input_pos {p_last} is outside the KV cache (max_seq_len {model.max_seq_len})")
     if Tq > 1:
-        model.prefill(x[0, :, :-1], int(input_pos[0]), 0)
+        if int(input_pos[0]) == 0:
+            model.prefill_cached(x[0, :, :-1])
+        else:
+            model.prefill(x[0, :, :-1], int(input_pos[0]), 0)
+    model._kv_written_from(p_last)
     s = model.session(1, getattr(model, "_session_frames", 4096))
     if Tq > 1:  # a new generation starts: frame records (injected uniforms / Philox counters) restart at 0
         s.frame_counter.zero_()
@@ -446,6 +485,7 @@ def decode_n_tokens(model: DualARTransformerB200, cur_token: Tensor, input_pos: 
     if p0 < 0 or p0 + num_new_tokens > model.max_seq_len:  # the reference fails in KVCache.update (llama.py:205-214)
         raise ValueError(f"decoding {num_new_tokens} frames from position {p0} exceeds the KV cache "
                          f"(max_seq_len {model.max_seq_len})")
+    model._kv_written_from(p0)
     s = model.session(1, max(num_new_tokens, getattr(model, "_session_frames", 0)))
     s.cur_tokens.copy_(cur_token.reshape(C1).to(torch.int32).view(1, C1))
     s.pos.fill_(p0)
@@ -512,6 +552,9 @@ def generate(*, model: DualARTransformerB200, prompt: Tensor, max_new_tokens: in
                         top_k, bias, audio_masks, audio_parts, decode_one_token=decode_one_token)
     seq = seq[:, : T + 1 + x.size(1)]
     seq[:, T + 1:] = x.to(seq.dtype)
+    if model.prefix_cache == "all" and decode_one_token is decode_one_token_ar:
+        # every column but the last one produced was fed as an input frame: its KV sits at its position in slot 0
+        model._kv_tokens = seq[:, : seq.shape[1] - 1].to(torch.int32).clone()
     return seq
 
 

@@ -561,3 +561,55 @@ def test_init_model_from_a_checkpoint_directory(tmp_path):
     assert torch.equal(outs[0], outs[1])
     with pytest.raises(ValueError):
         init_model(tmp_path, "cuda:0", torch.float32)
+
+
+def test_prefix_cache_skips_resident_prompt_columns_bit_identically(tiny):
+    """a prompt that starts with the columns whose prompt-pass KV is still in slot 0 skips them.  Same prompt
+    again, and the growing-conversation case (old prompt + new columns), must give the bytes a full prompt pass gives; mode
+    "all" also reuses the positions written by decode frames and stays within the logit tolerance."""
+    from fish_speech_b200 import dual_ar
+    g, cfg, sd, _ = tiny
+    m = _mk(cfg, sd)
+    T = g["prompt"].shape[1]
+    V = cfg.vocab_size
+
+    def first_frame(prompt):
+        bias = dual_ar.make_semantic_logit_bias(m)
+        s = g["sampling"]
+        m._session_frames = 8
+        tok = dual_ar.decode_one_token_ar(m, prompt[None].cuda(), torch.arange(prompt.shape[1]), s["temperature"], s["top_p"],
+                                          s["top_k"], bias)
+        torch.cuda.synchronize()
+        return m._buffer("slow_logits")[:V].clone().cpu(), tok.cpu()
+
+    grown = torch.cat([g["prompt"], R.make_prompt(cfg, 9, seed=77)], dim=1)
+    m.prefix_cache = False
+    ref_same, _ = first_frame(g["prompt"])
+    ref_grown, _ = first_frame(grown)
+    assert m.prefix_hits == 0
+    m.prefix_cache = True
+    a, _ = first_frame(g["prompt"])                       # miss: records the columns
+    assert m.prefix_hits == 0 and torch.equal(a, ref_same)
+    b, _ = first_frame(g["prompt"])                       # hit: T - 1 columns skipped
+    assert m.prefix_hits == T - 1 and torch.equal(b, ref_same)
+    c, _ = first_frame(grown)                             # old prompt + 9 new columns: the decode frame rewrote position T - 1
+    assert m.prefix_hits == 2 * (T - 1) and torch.equal(c, ref_grown)
+    other = R.make_prompt(cfg, T, seed=5)
+    m.prefix_cache = False
+    ref_other, _ = first_frame(other)
+    m.prefix_cache = True
+    first_frame(g["prompt"])
+    hits = m.prefix_hits
+    d, _ = first_frame(other)                             # nothing in common beyond chance: everything recomputed
+    assert torch.equal(d, ref_other) and m.prefix_hits - hits < T - 1
+    # mode "all": the conversation grows by what was generated (inference.py:706-722)
+    m.prefix_cache = "all"
+    seq = _run_generate(m, g, 12)
+    n_fed = seq.shape[1] - 1
+    turn2 = torch.cat([seq, R.make_prompt(cfg, 6, seed=78)], dim=1)
+    hits = m.prefix_hits
+    e, _ = first_frame(turn2)
+    assert m.prefix_hits - hits == n_fed                  # prompt + generated frames skipped, only the new columns computed
+    m.prefix_cache = False
+    ref_turn2, _ = first_frame(turn2)
+    _check_logits("prefix cache 'all' (decode-route KV reused) first-frame logits", e, ref_turn2)
