@@ -13,6 +13,14 @@ response)` out, with `GenerateResponse(action="sample", codes=...)` followed by 
 arguments of `generate()` (inference.py:243-253): `prompt` (encoded [C+1, T] tokens - text encoding is the tokenizer's job,
 outside this path), `max_new_tokens`, `temperature`, `top_p`, `top_k`.
 
+Prefix sharing: the scheduler remembers, per row, which prompt columns the prompt pass left in that KV slot.  A request whose
+prompt starts with `share_min` or more of the columns resident in some row (the same reference voice and system prompt, the
+voice-clone serving case) copies those keys and values into its own slot (`copy_kv_prefix`) and runs the prompt pass over the
+rest only - bit-identical to the full pass, like §5.7 of DESIGN.md.
+
+Sampling draws are keyed by (seed, frame index, row): which row a request lands on and when it joins decide its draws, so
+two runs of the same request agree in distribution, not token for token (exact ties between top candidates included).
+
 Rows of one step share the sampling parameters (one `fsb_frame_args`), so requests are grouped: the batch in flight has one
 (temperature, top_p, top_k); a request with other values waits until the batch has drained, and nothing that arrived after it
 is admitted before it (no starvation).
@@ -57,6 +65,7 @@ class _Row:
     prompt_len: int
     budget: int                    # frames this request may still produce (generate(): max_new_tokens, clipped to the cache)
     frames: List[Tensor] = field(default_factory=list)   # [n, C+1] int32 pieces, on the device
+    produced: int = 0              # frames kept so far: the row's next input position is prompt_len - 1 + produced
 
 
 class ContinuousBatcher:
@@ -64,7 +73,8 @@ class ContinuousBatcher:
     frames for all rows in flight and returns the requests that finished.  `model` is a DualARTransformerB200 built with
     max_rows >= `max_rows` (or anything with the same `prefill` / `session` / `config` surface: the CPU tests use a stand-in)."""
 
-    def __init__(self, model, max_rows: Optional[int] = None, chunk_frames: int = 8, use_ras: bool = True):
+    def __init__(self, model, max_rows: Optional[int] = None, chunk_frames: int = 8, use_ras: bool = True,
+                 share_min: int = 32, ring_frames: int = 1024):
         self.model = model
         self.rows = int(max_rows if max_rows is not None else model.max_rows)
         if self.rows < 1 or self.rows > model.max_rows:
@@ -76,13 +86,24 @@ class ContinuousBatcher:
         c = model.config
         if not getattr(model, "_cache_setup_done", False) or model.max_batch_size < self.rows:
             model.setup_caches(self.rows, c.max_seq_len)
-        self.sess = model.session(self.rows, self.chunk)
+        # the frame counter runs on across chunks (it is part of the sampler's Philox counter: restarting it every chunk would
+        # replay the same draws); the token record is a ring of `ring_frames` frames, and when it wraps the seed moves on
+        self.ring = max(int(ring_frames), self.chunk)
+        self.sess = model.session(self.rows, self.ring)
+        self.sess.seed = int(torch.randint(0, 2 ** 62, (1,)).item())   # like generate(): keyed by torch's CPU generator
+        self.sess.frame_counter.zero_()
+        self.frame0 = 0
         self.sess.bias = make_semantic_logit_bias(model).reshape(-1).to(torch.bfloat16).contiguous()
         self.sess.restrict_scan = True
         self.sess.done.fill_(1)                     # every row idle
         self.waiting: Deque[GenerateRequest] = deque()
         self.active: Dict[int, _Row] = {}
         self.key: Optional[Tuple[float, float, int]] = None
+        self.share_min = int(share_min)             # shortest common prefix worth copying (0 = never share)
+        self.resident: Dict[int, Tensor] = {}       # row -> CPU int32 [C+1, n]: columns whose prompt-pass KV sit in that slot
+        self.park: Dict[int, int] = {}              # idle row -> position it idles at (behind its resident prompt columns)
+        self.prompt_cols = 0                        # prompt columns admitted / of those, taken from another row or kept in place
+        self.shared_cols = 0
         self.steps = 0
         self.frames_run = 0                         # row-frames computed, idle rows included
         self.frames_kept = 0                        # frames delivered to requests
@@ -128,13 +149,35 @@ class ContinuousBatcher:
             self.waiting.popleft()
             row = next(r for r in range(self.rows) if r not in self.active)
             self.key = key
-            self.model.prefill(prompt[:, :-1], 0, row)       # fills KV slot `row` (slot = row)
+            self._fill_slot(row, prompt[:, :-1])              # KV slot `row` (slot = row) <- the prompt but its last column
             s.cur_tokens[row].copy_(prompt[:, -1].to(device=s.cur_tokens.device, dtype=torch.int32))
-            s.pos[row] = T - 1
             s.ras_window[row].zero_()
-            s.done[row] = 0
+            self.park.pop(row, None)
             self.active[row] = _Row(item=item, prompt_len=T, budget=budget)
         return failed
+
+    def _fill_slot(self, row: int, cols: Tensor):
+        """Prompt pass of `cols` into KV slot `row`, minus the longest prefix that is already resident in some slot."""
+        cpu = cols.detach().to(device="cpu", dtype=torch.int32)
+        n = int(cpu.shape[1])
+        best_row, best = -1, 0
+        if self.share_min > 0 and hasattr(self.model, "copy_kv_prefix"):
+            for r, have in self.resident.items():
+                m = min(n, int(have.shape[1]))
+                if m <= best or m < self.share_min or not torch.equal(have[:, :self.share_min], cpu[:, :self.share_min]):
+                    continue
+                same = (have[:, :m] == cpu[:, :m]).all(0)
+                L = m if bool(same.all()) else int((~same).nonzero()[0])
+                if L > best or (L == best and r == row):
+                    best_row, best = r, L
+        if best < self.share_min:
+            best_row, best = -1, 0
+        if best_row >= 0 and best_row != row:
+            self.model.copy_kv_prefix(best_row, row, best)
+        self.model.prefill(cols[:, best:], best, row)
+        self.resident[row] = cpu
+        self.prompt_cols += n
+        self.shared_cols += best
 
     # ------------------------------------------------------------------ one chunk
     def step(self) -> List[Tuple[GenerateRequest, Union[Tensor, Exception]]]:
@@ -146,13 +189,23 @@ class ContinuousBatcher:
         c = self.model.config
         s = self.sess
         n = min(self.chunk, max(r.budget for r in self.active.values()))
-        s.frame_counter.zero_()
+        if self.frame0 + n > self.ring:
+            s.frame_counter.zero_()
+            self.frame0 = 0
+            s.seed = (int(s.seed) + 1) & (2 ** 62 - 1)
+        f0 = self.frame0
+        self.frame0 += n
         T_, P_, K_ = self.key
-        hi = max(r.prompt_len - 1 + sum(int(p.shape[0]) for p in r.frames) for r in self.active.values())
-        s.run(n, T_, P_, K_, self.use_ras, pos_bound=hi)
+        # the host knows every row's position: rows in flight continue where their kept frames end, idle rows (they step along
+        # with the batch, their output is dropped) idle behind their resident prompt columns - one small upload per chunk
+        pos = [self.active[r].prompt_len - 1 + self.active[r].produced if r in self.active else self.park.get(r, 0)
+               for r in range(self.rows)]
+        s.pos.copy_(torch.tensor(pos, dtype=torch.int32))
+        s.done.copy_(torch.tensor([0 if r in self.active else 1 for r in range(self.rows)], dtype=torch.int32))
+        s.run(n, T_, P_, K_, self.use_ras, pos_bound=max(pos))
         self.steps += 1
         self.frames_run += n * self.rows
-        toks = s.out_tokens[:n]                                  # [n][rows][C+1] on the device
+        toks = s.out_tokens[f0: f0 + n]                          # [n][rows][C+1] on the device
         main = toks[:, :, 0].to("cpu")                           # one small synchronising copy per chunk
         if hasattr(s, "check_device"):
             s.check_device()
@@ -165,18 +218,24 @@ class ContinuousBatcher:
                 take = int(hit[0]) + 1                           # the <|im_end|> frame is the last one produced
             r.frames.append(toks[:take, row].clone())
             r.budget -= take
+            r.produced += take
             if ended or r.budget <= 0:
                 seq = torch.cat(r.frames, 0)                     # [n_total, C+1]
                 codes = seq[:-1, 1:].t().contiguous()            # y[1:, prompt_length:-1]
                 self.frames_kept += int(seq.shape[0])
                 out.append((r.item, codes))
                 del self.active[row]
-                s.done[row] = 1
-                s.pos[row] = 0                                   # an idle row keeps stepping: park it at the cache's start
-            # rows still in flight simply continue from the state the kernel left (cur_tokens, pos, RAS window)
-        for row in range(self.rows):                             # idle rows advanced too: keep them parked
-            if row not in self.active:
-                s.pos[row] = 0
+                # the idle row keeps stepping with the batch and writes KV where it stands: let it stand behind its prompt
+                # columns, which stay valid for requests that start the same way; too close to the end of the cache, give
+                # the columns up and idle at the start
+                end = r.prompt_len - 1 + r.produced
+                spot = min(end, c.max_seq_len - self.chunk)
+                if spot >= r.prompt_len - 1:
+                    self.park[row] = spot
+                else:
+                    self.park.pop(row, None)
+                    self.resident.pop(row, None)
+            # rows still in flight continue from the state the kernel left (cur_tokens, RAS window)
         if not self.active:
             self.key = None
         return out

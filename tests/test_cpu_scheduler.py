@@ -29,17 +29,28 @@ class FakeSession:
 
     def run(self, n, temperature, top_p, top_k, use_ras, pos_bound=None):
         m = self.model
-        assert n <= self.max_frames
+        for r in range(self.batch):           # a decode frame writes K/V at its position: model it on the stand-in's slots
+            if r in m.kv:
+                p0 = int(self.pos[r])
+                kv = m.kv[r]
+                for p in range(p0, p0 + n):
+                    if p < len(kv):
+                        kv[p] = -1            # overwritten: no longer the prompt pass's
+                    else:
+                        kv.append(-1)
+        assert int(self.frame_counter) + n <= self.max_frames, "the token record would overflow"
         assert int(self.pos.max()) + n <= m.max_seq_len, "a row would step past the cache"
         self.calls.append((n, temperature, top_p, top_k, [int(d) for d in self.done]))
-        for f in range(n):
+        for _ in range(n):
+            f = int(self.frame_counter)         # the record is indexed by the running frame counter (frame_end_kernel)
             for r in range(self.batch):
                 p = int(self.pos[r])
                 tok = m.stream(r, p + 1)
                 self.cur_tokens[r] = torch.tensor(tok, dtype=torch.int32)
                 if tok[0] == IM_END:
                     self.done[r] = 1
-                self.out_tokens[f, r] = self.cur_tokens[r]
+                if f < self.max_frames:
+                    self.out_tokens[f, r] = self.cur_tokens[r]
                 self.pos[r] = p + 1
             self.frame_counter += 1
 
@@ -57,6 +68,8 @@ class FakeModel:
         self._cache_setup_done = False
         self.max_batch_size = 0
         self.slots = {}
+        self.kv = {}
+        self.computed = self.copied = 0
         self.admitted = []
 
     def setup_caches(self, rows, max_seq_len, dtype=torch.bfloat16):
@@ -67,10 +80,19 @@ class FakeModel:
         return self._s
 
     def prefill(self, cols, pos0, slot):
-        T = cols.shape[-1] + 1
-        h = int(cols.sum()) % 1000
+        kv = self.kv.setdefault(slot, [])
+        assert pos0 <= len(kv), "a prompt pass from pos0 needs the keys before it"
+        del kv[pos0:]
+        kv.extend(int(x) for x in cols.sum(0))          # one number per column stands for its K/V
+        self.computed += cols.shape[-1]
+        T = len(kv) + 1
+        h = sum(kv) % 1000
         self.slots[slot] = (h, T)
         self.admitted.append(h)
+
+    def copy_kv_prefix(self, src, dst, n):
+        self.kv[dst] = list(self.kv[src][:n])
+        self.copied += n
 
     def stream(self, slot, p):
         if slot not in self.slots:
@@ -172,6 +194,34 @@ def test_idle_rows_never_run_past_the_cache():
     assert codes.shape == (C, S - 4 - 1)
     with pytest.raises(ValueError):
         ContinuousBatcher(m, max_rows=4)
+
+
+def test_requests_that_start_alike_share_the_prompt_pass():
+    """Voice-clone serving: many requests start with the same long prefix (system prompt + reference audio).  The first one
+    computes it, later ones copy it from a resident row (or keep it when they land on the same row) and compute only their
+    own columns; outputs are what they are without sharing."""
+    voice = prompt(40, 123)
+    tails = [prompt(3 + i % 4, 200 + i) for i in range(7)]
+    items = [req(torch.cat([voice, t], dim=1), max_new=5) for t in tails] + [req(prompt(12, 999), max_new=5)]
+    m = FakeModel(max_rows=3)
+    b = ContinuousBatcher(m, chunk_frames=4, share_min=16)
+    for it in items:
+        b.submit(it)
+    got = {id(it): res for it, res in b.run_until_idle()}
+    for it in items:
+        assert torch.equal(got[id(it)], expected(it.request["prompt"], 5))
+    total = sum(it.request["prompt"].shape[1] - 1 for it in items)
+    assert b.prompt_cols == total and m.computed == total - b.shared_cols
+    assert b.shared_cols >= 6 * 40 and m.copied > 0        # all but the first took the voice prefix
+    # every resident record still describes what is in the slot: the prompt-pass columns were not overwritten by idle rows
+    for row, cols in b.resident.items():
+        assert m.kv[row][: cols.shape[1]] == [int(x) for x in cols.sum(0)]
+    m2 = FakeModel(max_rows=3)
+    b2 = ContinuousBatcher(m2, chunk_frames=4, share_min=0)
+    for it in items:
+        b2.submit(it)
+    b2.run_until_idle()
+    assert b2.shared_cols == 0 and m2.computed == total
 
 
 def test_queue_protocol_of_the_worker_thread():

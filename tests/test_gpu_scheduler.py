@@ -21,6 +21,14 @@ def _model(max_rows):
     return cfg, m
 
 
+def _same_draws_everywhere(b, cfg):
+    """Exact ties between top candidates are resolved by the draws, which are keyed by frame and row: give every frame and
+    row the same record so that a request's tokens do not depend on where and when it runs."""
+    n = 2 * cfg.vocab_size + (cfg.num_codebooks - 1) * cfg.codebook_size
+    one = (torch.randint(1, 256, (n,), generator=torch.Generator().manual_seed(4)).float() / 256).to(torch.bfloat16)
+    b.sess.uniforms = one.view(1, 1, n).expand(b.ring, b.rows, n).contiguous().cuda()
+
+
 def _requests(cfg, n):
     from fish_speech_b200.scheduler import GenerateRequest
     out = []
@@ -35,7 +43,8 @@ def _requests(cfg, n):
 def test_joining_and_leaving_rows_get_the_frames_they_get_alone():
     from fish_speech_b200.scheduler import ContinuousBatcher
     cfg, m = _model(4)
-    b = ContinuousBatcher(m, chunk_frames=4, use_ras=False)
+    b = ContinuousBatcher(m, chunk_frames=4, use_ras=False, ring_frames=16)   # a short ring: the record wraps during the run
+    _same_draws_everywhere(b, cfg)
     b.sess.bias[cfg.im_end_id] = 1.5             # some requests end on <|im_end|> before their budget
     items = _requests(cfg, 9)
     for it in items:
@@ -45,7 +54,8 @@ def test_joining_and_leaving_rows_get_the_frames_they_get_alone():
     b.sess.check_device()
     n_eos = 0
     for it in items:
-        solo = ContinuousBatcher(m, chunk_frames=4, use_ras=False)
+        solo = ContinuousBatcher(m, chunk_frames=4, use_ras=False, ring_frames=16)
+        _same_draws_everywhere(solo, cfg)
         solo.sess.bias[cfg.im_end_id] = 1.5
         solo.submit(it)
         (_, want), = solo.run_until_idle()
@@ -76,3 +86,31 @@ def test_worker_thread_serves_the_queue_protocol():
     e = bad.response_queue.get(timeout=120)
     assert e.status == "error" and isinstance(e.response, ValueError)
     q_in.put(None)
+
+
+def test_shared_prompt_prefix_is_copied_not_recomputed_and_changes_nothing():
+    """Requests that start with the same 40 columns (a reference voice): the first computes them, the others copy the keys
+    and values from a resident slot and run the prompt pass over their own columns only; every request still gets the frames
+    it gets alone without sharing, bit for bit."""
+    from fish_speech_b200.scheduler import ContinuousBatcher, GenerateRequest
+    cfg, m = _model(4)
+    voice = R.make_prompt(cfg, 40, seed=900, voice_span=30)
+    items = []
+    for i in range(7):
+        p = torch.cat([voice, R.make_prompt(cfg, 4 + i % 3, seed=910 + i)], dim=1)
+        items.append(GenerateRequest(request=dict(prompt=p, max_new_tokens=6 + i % 3, temperature=0.8, top_p=0.8, top_k=1),
+                                     response_queue=queue.Queue()))
+    b = ContinuousBatcher(m, chunk_frames=4, use_ras=False, share_min=16, ring_frames=16)
+    _same_draws_everywhere(b, cfg)
+    for it in items:
+        b.submit(it)
+    got = {id(it): res for it, res in b.run_until_idle()}
+    assert b.shared_cols >= 6 * 40
+    print(f"[sched] shared prefix: {b.shared_cols} of {b.prompt_cols} prompt columns taken from resident slots")
+    for it in items:
+        solo = ContinuousBatcher(m, chunk_frames=4, use_ras=False, share_min=0, ring_frames=16)
+        _same_draws_everywhere(solo, cfg)
+        solo.submit(it)
+        (_, want), = solo.run_until_idle()
+        assert solo.shared_cols == 0
+        assert torch.equal(got[id(it)].cpu(), want.cpu())
