@@ -26,6 +26,7 @@ struct fsb_dac {
     int half = 1;  // operand type of the tcgen05 pipeline: 1 fp16 (11-bit significand, as TF32), 0 bf16; set by the host mirror to
                    //    match the type it packed the ".h" weights in
     int pos_offset = 0;  // position of frame 0 of the next decode calls in the window transformer's RoPE table (pieces of a long clip)
+    int tiled_small = 1;  // window attention and the output conv of the tcgen05 pipeline as shared-memory-tiled kernels (0: per-query / per-sample)
     int force_simt = 0;  // tcgen05 pipeline with every GEMM on the CUDA-core twin kernel (cross-check)
     int n_sm = 148;
     std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, int>, CUtensorMap> maps;
@@ -205,6 +206,7 @@ int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
     else if (n == "tc") h->tc = (int)value;
     else if (n == "half") { h->half = (int)value; h->maps.clear(); }
     else if (n == "force_simt") h->force_simt = (int)value;
+    else if (n == "tiled_small") h->tiled_small = (int)value;
     else if (n == "pos_offset") { if (value < 0) return dfail(h, "pos_offset < 0"); h->pos_offset = (int)value; }
     else return dfail(h, "unknown option " + n);
     return 0;
@@ -394,7 +396,16 @@ int decode_tc_t(fsb_dac* h, void* codes, int B, int T, float* wav, cudaStream_t 
             rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(b2, rope, B, T, H, HD, h->pos_offset);
             dim3 grid((T + 3) / 4, H, B);
             const float scale = 1.f / sqrtf((float)HD);
-            if (HD == 64) window_attn16_kernel<64, F16><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
+            if (h->tiled_small) {  // keys / values of a query tile's windows staged once per CTA (bit-identical to the per-query kernel)
+                dim3 tg((T + WA_QT - 1) / WA_QT, H, B);
+                if (HD == 64) {
+                    DCK(cudaFuncSetAttribute((const void*)window_attn16_tiled_kernel<64, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wa_smem_bytes<64>(128)));
+                    window_attn16_tiled_kernel<64, F16><<<tg, WA_THREADS, wa_smem_bytes<64>(d.tf_window), s>>>(b2, b1, B, T, H, d.tf_window, scale);
+                } else {
+                    DCK(cudaFuncSetAttribute((const void*)window_attn16_tiled_kernel<32, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wa_smem_bytes<32>(128)));
+                    window_attn16_tiled_kernel<32, F16><<<tg, WA_THREADS, wa_smem_bytes<32>(d.tf_window), s>>>(b2, b1, B, T, H, d.tf_window, scale);
+                }
+            } else if (HD == 64) window_attn16_kernel<64, F16><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
             else window_attn16_kernel<32, F16><<<grid, 128, 0, s>>>(b2, b1, B, T, H, d.tf_window, scale);
         }
         r.tc(b1, T, H * HD, D, 1, 1, p + "wo", "", 0, g1, b0, nullptr, 0, TCV_ACT_NONE, nullptr, b3);      // h = x + gamma1 * wo(y)
@@ -453,7 +464,13 @@ int decode_tc_t(fsb_dac* h, void* codes, int B, int T, float* wav, cudaStream_t 
         const float *ow = r.W("dec.out_w"), *ob = r.W("dec.out_b");
         if (r.rc) return r.rc;
         const long long warps = (long long)B * len;
-        conv_out1_16_kernel<F16><<<(int)((warps * 32 + 255) / 256), 256, 0, s>>>(cur16, ow, ob, wav, B, len, ch, 7);
+        const size_t co_bytes = co_smem_bytes(ch, 7);
+        if (h->tiled_small && ch % 8 == 0 && co_bytes <= 200 * 1024) {
+            DCK(cudaFuncSetAttribute((const void*)conv_out1_16_tiled_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            conv_out1_16_tiled_kernel<F16><<<B * ((len + CO_TILE - 1) / CO_TILE), CO_TILE, co_bytes, s>>>(cur16, ow, ob, wav, B, len, ch, 7);
+        } else {
+            conv_out1_16_kernel<F16><<<(int)((warps * 32 + 255) / 256), 256, 0, s>>>(cur16, ow, ob, wav, B, len, ch, 7);
+        }
     }
     DCK(cudaGetLastError());
     return r.rc;

@@ -561,3 +561,140 @@ __global__ void __launch_bounds__(256) conv_out1_16_kernel(const void* A16, cons
     s = warp_sum(s);
     if (lane == 0) out[(size_t)b * T + t] = tanhf(s + (bias ? bias[0] : 0.f));
 }
+
+// ----------------------------------------------------------------------------- tiled forms of the two kernels above
+// window_attn16_kernel reads every key and value row of a query's window from L2 once per query: 128 x 2 x 256 B per (b, h, t),
+// 5.4 GB per layer at 8 clips x 646 frames - 0.8 ms per layer for 63 MB of q/k/v.  Here a CTA owns WA_QT consecutive queries
+// of one (clip, head): the keys and values of their windows (WA_QT + window - 1 rows) are staged in shared memory once, and
+// every warp walks its queries with the SAME arithmetic, in the same order, as window_attn16_kernel (bit-identical output).
+#define WA_QT 64
+#define WA_THREADS 256
+template <int HD>
+__host__ __device__ constexpr size_t wa_smem_bytes(int window) {
+    return (size_t)(WA_QT + window - 1) * ((HD + 4) + HD) * sizeof(float) + (WA_THREADS / 32) * HD * sizeof(float);
+}
+template <int HD, bool F16>
+__global__ void __launch_bounds__(WA_THREADS) window_attn16_tiled_kernel(const float* qkv, void* y16, int B, int T, int H, int window,
+                                                                         float scale) {
+    typedef Tcv16<F16> Hh;
+    constexpr int EPL = HD / 32;
+    constexpr int MAXI = 4;      // window <= 128
+    constexpr int KS = HD + 4;   // key row stride in floats: lanes read different rows with LDS.128, 4 j mod 32 spreads them
+    extern __shared__ __align__(16) float wa_smem[];
+    const int nrows = WA_QT + window - 1;
+    float* ks = wa_smem;
+    float* vs = ks + (size_t)nrows * KS;
+    float* qs = vs + (size_t)nrows * HD;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int t0 = blockIdx.x * WA_QT, h = blockIdx.y, b = blockIdx.z;
+    const size_t rs = (size_t)3 * H * HD;
+    const float* base = qkv + (size_t)b * T * rs;
+    const int first = t0 - window + 1;                       // key position of shared-memory row 0 (may be negative)
+    const int t_end = min(T, t0 + WA_QT);
+    for (int i = threadIdx.x; i < nrows * (HD / 4); i += WA_THREADS) {
+        const int r = i / (HD / 4), c = i % (HD / 4);
+        const int kp = first + r;
+        if (kp >= 0 && kp < t_end) {
+            const float* row = base + (size_t)kp * rs + (size_t)h * HD;
+            *reinterpret_cast<float4*>(ks + (size_t)r * KS + 4 * c) = *reinterpret_cast<const float4*>(row + (size_t)H * HD + 4 * c);
+            *reinterpret_cast<float4*>(vs + (size_t)r * HD + 4 * c) = *reinterpret_cast<const float4*>(row + (size_t)2 * H * HD + 4 * c);
+        }
+    }
+    __syncthreads();
+    float* q = qs + w * HD;
+    for (int t = t0 + w; t < t_end; t += WA_THREADS / 32) {
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) q[lane * EPL + i] = base[(size_t)t * rs + (size_t)h * HD + lane * EPL + i];
+        __syncwarp();
+        const int start = max(0, t - window + 1), n = t - start + 1;
+        const int r0 = start - first;                        // shared-memory row of the window's first key
+        float sc[MAXI], mx = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < MAXI; ++i) {
+            const int j = lane + 32 * i;
+            sc[i] = -INFINITY;
+            if (j < n) {
+                const float4* k = reinterpret_cast<const float4*>(ks + (size_t)(r0 + j) * KS);
+                float d = 0.f;
+#pragma unroll
+                for (int e = 0; e < HD / 4; ++e) {
+                    const float4 kv = k[e];
+                    d = fmaf(q[4 * e], kv.x, d); d = fmaf(q[4 * e + 1], kv.y, d);
+                    d = fmaf(q[4 * e + 2], kv.z, d); d = fmaf(q[4 * e + 3], kv.w, d);
+                }
+                sc[i] = d * scale;
+                mx = fmaxf(mx, sc[i]);
+            }
+        }
+        mx = warp_max(mx);
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXI; ++i) { sc[i] = (sc[i] == -INFINITY) ? 0.f : expf(sc[i] - mx); sum += sc[i]; }
+        sum = warp_sum(sum);
+        const float inv = 1.f / sum;
+        float o[EPL];
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) o[i] = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXI; ++i) {
+            for (int src = 0; src < 32; ++src) {
+                const int j = src + 32 * i;
+                if (j >= n) break;  // uniform across the warp
+                const float p = __shfl_sync(0xffffffffu, sc[i], src);
+                const float* v = vs + (size_t)(r0 + j) * HD + lane * EPL;
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) o[e] = fmaf(p, v[e], o[e]);
+            }
+        }
+        uint16_t* yr = reinterpret_cast<uint16_t*>(y16) + ((size_t)b * T + t) * H * HD + (size_t)h * HD + lane * EPL;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) yr[e] = Hh::pack(o[e] * inv);
+        __syncwarp();
+    }
+}
+
+// Final conv (Cout = 1) + tanh, tiled: conv_out1_16_kernel runs one WARP per output sample and re-reads each input row `taps`
+// times from L2 (6.4 ms per 8 clips for 2 GB of input).  Here a CTA stages CO_TILE + taps - 1 rows once and one THREAD computes
+// one sample; rows are padded to an odd number of 16-byte units so that neighbouring threads' LDS.128 do not collide.
+#define CO_TILE 256
+__host__ __device__ inline int co_row_units(int Cin) { const int u = Cin / 8; return (u & 1) ? u : u + 1; }
+__host__ __device__ inline size_t co_smem_bytes(int Cin, int taps) {
+    return (size_t)(CO_TILE + taps - 1) * co_row_units(Cin) * 16 + (size_t)taps * Cin * sizeof(float);
+}
+template <bool F16>
+__global__ void __launch_bounds__(CO_TILE) conv_out1_16_tiled_kernel(const void* A16, const float* W, const float* bias, float* out,
+                                                                    int B, int T, int Cin, int taps) {
+    typedef Tcv16<F16> H;
+    extern __shared__ __align__(16) unsigned char co_smem[];
+    const int units = Cin / 8, ru = co_row_units(Cin);
+    const int nrows = CO_TILE + taps - 1;
+    uint4* rows = reinterpret_cast<uint4*>(co_smem);
+    float* ws = reinterpret_cast<float*>(co_smem + (size_t)nrows * ru * 16);
+    const int tiles = (T + CO_TILE - 1) / CO_TILE;
+    const int b = blockIdx.x / tiles, t0 = (blockIdx.x % tiles) * CO_TILE;
+    const uint4* A = reinterpret_cast<const uint4*>(A16) + (size_t)b * T * units;
+    for (int i = threadIdx.x; i < nrows * units; i += CO_TILE) {
+        const int r = i / units, c = i % units;
+        const int tt = t0 - (taps - 1) + r;
+        rows[(size_t)r * ru + c] = (tt >= 0 && tt < T) ? A[(size_t)tt * units + c] : make_uint4(0, 0, 0, 0);  // zeros = causal padding
+    }
+    for (int i = threadIdx.x; i < taps * Cin; i += CO_TILE) ws[i] = W[i];
+    __syncthreads();
+    const int t = t0 + threadIdx.x;
+    if (t >= T) return;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int j = 0; j < taps; ++j) {
+        const uint4* row = rows + (size_t)(threadIdx.x + j) * ru;
+        const float* wj = ws + (size_t)j * Cin;
+        for (int c = 0; c < units; ++c) {
+            const uint4 v = row[c];
+            const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                acc[e] = fmaf(H::unpack((uint16_t)(u[e] & 0xffffu)), wj[8 * c + 2 * e], acc[e]);
+                acc[e] = fmaf(H::unpack((uint16_t)(u[e] >> 16)), wj[8 * c + 2 * e + 1], acc[e]);
+            }
+        }
+    }
+    out[(size_t)b * T + t] = tanhf((acc[0] + acc[1]) + (acc[2] + acc[3]) + (bias ? bias[0] : 0.f));
+}

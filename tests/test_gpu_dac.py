@@ -137,6 +137,25 @@ def test_clip_longer_than_the_workspace_decodes_in_pieces_bit_identically():
     assert int(wild[0, 1, 77]) == c.codebook_size - 1
 
 
+def test_tiled_window_attention_and_output_conv_match_the_per_query_kernels():
+    """Option tiled_small: the window attention stages a query tile's keys / values in shared memory (same arithmetic, same
+    order: bit-identical up to the output conv), the output conv sums its taps per thread instead of per warp (fp32 sums in
+    another order: equal to ~1e-6).  Clips longer than one query tile, ragged last tile, both head sizes via the two configs."""
+    for c, T in ((D.small_config(), 150), (D.DACConfig(), 70)):
+        sd = D.make_state_dict(c, seed=7)
+        codes = D.make_codes(c, 2, T)
+        m = _model(c, sd, max_batch=2, max_frames=T)
+        m.set_option("tiled_small", 0)
+        want = m.from_indices(codes.clone().cuda()).cpu()
+        m.set_option("tiled_small", 1)
+        got = m.from_indices(codes.clone().cuda()).cpu()
+        d = float((got - want).abs().max())
+        print(f"[parity] tiled small kernels vs per-query kernels, T={T}: max abs diff {d:.2e}, SNR {snr_db(want, got):.1f} dB")
+        assert d <= 2e-5 and snr_db(want, got) >= 90.0
+        del m
+        torch.cuda.empty_cache()
+
+
 def test_errors():
     c = D.small_config()
     m = _model(c, D.make_state_dict(c, seed=3), max_frames=8)
