@@ -26,6 +26,7 @@ struct fsb_dac {
     int half = 1;  // operand type of the tcgen05 pipeline: 1 fp16 (11-bit significand, as TF32), 0 bf16; set by the host mirror to
                    //    match the type it packed the ".h" weights in
     int pos_offset = 0;  // position of frame 0 of the next decode calls in the window transformer's RoPE table (pieces of a long clip)
+    int staged_epi = 1;   // tcv_kernel: 16-bit-only epilogues (the decoder's convs) through shared memory (coalesced residual loads / stores)
     int tiled_small = 1;  // window attention and the output conv of the tcgen05 pipeline as shared-memory-tiled kernels (0: per-query / per-sample)
     int force_simt = 0;  // tcgen05 pipeline with every GEMM on the CUDA-core twin kernel (cross-check)
     int n_sm = 148;
@@ -116,6 +117,7 @@ struct Runner {
         a.gamma = gamma; a.res32 = res32; a.alpha = alpha; a.act = act;
         a.out16 = out16; a.out32 = out32; a.ld16 = act == TCV_ACT_SWIGLU ? N / 2 : N; a.ld32 = N; a.ldres = N;
         a.res16 = res16; a.out16r = out16r; a.ld16r = N;
+        a.staged_ok = h->staged_epi;
         if (rc) return;
         cudaError_t e;
         if (h->force_simt || !tcv_tc_ok(Cin, N)) {
@@ -207,6 +209,7 @@ int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
     else if (n == "half") { h->half = (int)value; h->maps.clear(); }
     else if (n == "force_simt") h->force_simt = (int)value;
     else if (n == "tiled_small") h->tiled_small = (int)value;
+    else if (n == "staged_epi") h->staged_epi = (int)value;
     else if (n == "pos_offset") { if (value < 0) return dfail(h, "pos_offset < 0"); h->pos_offset = (int)value; }
     else return dfail(h, "unknown option " + n);
     return 0;
@@ -231,6 +234,7 @@ static TcConvArgs tcv_from_abi(const fsb_tc_conv_args& x) {
     a.bias = x.bias; a.gamma = x.gamma; a.res32 = x.res32; a.res16 = x.res16; a.alpha = x.alpha;
     a.bias_mod = x.bias_mod > 0 ? x.bias_mod : x.N; a.alpha_mod = x.alpha_mod > 0 ? x.alpha_mod : x.N; a.ldres = x.ldres;
     a.act = x.act; a.round_lin = x.round_lin;
+    a.staged_ok = x.use_simt >= 0 ? 1 : 0;   // use_simt = -1: the tensor-core kernel with the direct (unstaged) epilogue, for A/B timing
     return a;
 }
 
@@ -240,7 +244,7 @@ int fsb_tc_conv(const fsb_tc_conv_args* x, void* stream) {
     if (x->act == TCV_ACT_SWIGLU && (!x->out16 || (x->N & 1))) return 1;
     TcConvArgs a = tcv_from_abi(*x);
     cudaStream_t s = (cudaStream_t)stream;
-    if (x->use_simt || !tcv_tc_ok(x->Cin, x->N)) return tcv_launch_simt(s, x->f16 != 0, a) == cudaSuccess ? 0 : 4;
+    if (x->use_simt > 0 || !tcv_tc_ok(x->Cin, x->N)) return tcv_launch_simt(s, x->f16 != 0, a) == cudaSuccess ? 0 : 4;
     int dev = 0, n_sm = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 2;
     if (tcv_set_attrs() != cudaSuccess) return 2;

@@ -59,6 +59,8 @@ struct TcConvArgs {
                          // GATE: out16 = rnd(rnd(silu(g)) * rnd(v)) with g read from res16 (the w1 GEMM's output): FeedForward of the
                          // bf16 LLM with a rounding after every op like the reference (llama.py:985-986)
     int vec_ok;          // 1: every row pitch / pointer allows the 16-byte vector paths of the epilogue
+    int staged_ok;       // caller's switch for the staged epilogue (option "staged_epi")
+    int staged;          // 1: the 16-bit-only epilogue through shared memory (set by tcv_launch: see tcv_kernel)
     int round_lin;       // 1: round the reduction to the 16-bit type BEFORE the residual add (the bf16 LLM's rounding points:
                          //    one rounding per Linear, one per add, llama.py:838-843)
 };
@@ -221,7 +223,17 @@ __device__ __forceinline__ void tcv_param(const TcConvArgs& a, int n, float& bia
 // ----------------------------------------------------------------------------- the tensor-core kernel
 __host__ __device__ constexpr uint32_t tcv_stage_bytes(int bn) { return (uint32_t)(TCV_A_BYTES + bn * TCV_BK * 2); }
 __host__ __device__ constexpr int tcv_tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512; }
-inline size_t tcv_smem_bytes(int bn, int nst) { return (size_t)nst * tcv_stage_bytes(bn) + 1024; }
+// Staged epilogue (decoder convs: 16-bit residual in, 16-bit outputs only): a panel of PW columns of the tile at a time.  The
+// residual panel is copied global -> shared with cp.async one panel ahead (coalesced 16-byte pieces, no registers, its
+// latency off the chain), every thread adds its row from there, and the packed outputs go through a staging panel so that the
+// global stores are whole contiguous runs instead of 32 rows x 16 bytes per warp instruction.  (One bulk async store per row
+// from two staging panels was measured too: the same on the 1-tap layers, 24 % slower on the transposed convs - 192-byte bulk
+// copies are too small for the copy engine.)  Rows carry 16 bytes of padding
+// (an odd number of 16-byte units: a thread per row and a thread per piece are both conflict-free).
+__host__ __device__ constexpr int tcv_panel_cols(int bn) { return bn % 96 == 0 ? 96 : (bn % 64 == 0 ? 64 : 32); }
+__host__ __device__ constexpr uint32_t tcv_panel_row_bytes(int bn) { return (uint32_t)tcv_panel_cols(bn) * 2 + 16; }
+__host__ __device__ constexpr uint32_t tcv_epi_bytes(int bn) { return 3u * TCV_BM * tcv_panel_row_bytes(bn); }  // 2 residual + 1 staging
+inline size_t tcv_smem_bytes(int bn, int nst, bool staged) { return (size_t)nst * tcv_stage_bytes(bn) + (staged ? tcv_epi_bytes(bn) : 0) + 1024; }
 
 __device__ __forceinline__ void tcv_epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(32 * TCV_EPI_WARPS) : "memory"); }
 __device__ __forceinline__ void tcv_tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, uint64_t policy) {
@@ -232,6 +244,131 @@ __device__ __forceinline__ void tcv_tma_load_3d(uint32_t dst, const CUtensorMap*
 // instruction descriptor: D fp32, A/B both bf16 (1) or both fp16 (0), K-major, M = 128, N = bn
 __host__ __device__ constexpr uint32_t tcv_idesc(int bn, bool f16) {
     return (1u << 4) | ((f16 ? 0u : 1u) << 7) | ((f16 ? 0u : 1u) << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(TCV_BM >> 4) << 24);
+}
+
+__device__ __forceinline__ void tcv_cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void tcv_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tcv_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <int BN, bool F16>
+__device__ __forceinline__ void tcv_staged_epilogue(const TcConvArgs& a, uint32_t tmem, uint8_t* epi, uint64_t* tfull_bar, uint64_t* tempty_bar,
+                                                    float* ep_bias, float* ep_gamma, float* ep_alpha, float* ep_ainv, int et, int lg,
+                                                    int half, int lane) {
+    typedef Tcv16<F16> H;
+    constexpr int PW = tcv_panel_cols(BN), NP = BN / PW;     // panel width, panels per tile
+    constexpr int HW = PW / 2;                               // columns of one warp of a lane quadrant
+    constexpr int NCB = (HW % 32 == 0) ? 32 : 16, NB = HW / NCB;
+    constexpr int CPR = PW / 8;                              // 16-byte pieces per panel row
+    constexpr uint32_t RB = tcv_panel_row_bytes(BN);
+    constexpr int NT = 32 * TCV_EPI_WARPS;
+    uint8_t* const sbuf = epi + 2 * (size_t)TCV_BM * RB;
+    const uint32_t tlane = (uint32_t)(lg * 32) << 16;
+    const int myrow = lg * 32 + lane;                        // row of the tile this thread reads from TMEM
+    const uint16_t* res = reinterpret_cast<const uint16_t*>(a.res16);
+
+    // residual panel `p` of tile `tile` -> rbuf[slot]: coalesced 16-byte pieces, rows past the end of the clip skipped
+    auto request = [&](int tile, int p, int slot) {
+        if (res == nullptr || tile >= a.n_tiles) return;
+        const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
+        const int col0 = tn * BN + p * PW;
+        for (int i = et; i < TCV_BM * CPR; i += NT) {
+            const int row = i / CPR, c = i % CPR, t = tt * TCV_BM + row;
+            if (t < a.T) tcv_cp_async16(epi + (size_t)slot * TCV_BM * RB + (size_t)row * RB + c * 16, res + ((size_t)b * a.T + t) * a.ldres + col0 + c * 8);
+        }
+    };
+    // staging panel -> global, whole rows of the panel as contiguous runs
+    auto copy_out = [&](uint16_t* base, int ld, int b, int tt, int col0) {
+        for (int i = et; i < TCV_BM * CPR; i += NT) {
+            const int row = i / CPR, c = i % CPR, t = tt * TCV_BM + row;
+            if (t < a.T)
+                *reinterpret_cast<uint4*>(base + ((size_t)b * a.T + t) * ld + col0 + c * 8) = *reinterpret_cast<const uint4*>(sbuf + (size_t)row * RB + c * 16);
+        }
+    };
+    uint32_t iseg = 0, g = 0;   // tiles / panels done by this CTA
+    int tn_loaded = -1;
+    request(blockIdx.x, 0, 0);
+    tcv_cp_async_commit();
+    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
+        const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
+        const int n0 = tn * BN;
+        if (tn != tn_loaded) {  // uniform; everyone is past the previous tile (barriers below)
+            for (int i = et; i < BN; i += NT) tcv_param(a, n0 + i, ep_bias[i], ep_gamma[i], ep_alpha[i], ep_ainv[i]);
+            tn_loaded = tn;
+        }
+        const uint32_t buf = iseg & 1u;
+        mbar_wait(&tfull_bar[buf], (iseg >> 1) & 1u);
+        tc_fence_after();
+        const uint32_t tacc = tmem + tlane + buf * BN;
+#pragma unroll 1
+        for (int p = 0; p < NP; ++p, ++g) {
+            const int slot = (int)(g & 1u);
+            tcv_cp_async_wait_all();         // my pieces of this panel's residual have landed
+            tcv_epi_bar();                   // ... everybody's have; the staging panel and the other residual slot are free
+            if (p + 1 < NP) request(tile, p + 1, slot ^ 1);
+            else request(tile + (int)gridDim.x, 0, slot ^ 1);
+            tcv_cp_async_commit();
+            const int pc = p * PW + half * HW;             // first column (inside the tile) of this thread's share
+            float v[NB][NCB];
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+                if (NCB == 32) tc_ld32(tacc + (uint32_t)(pc + k * NCB), reinterpret_cast<float(&)[32]>(v[k]));
+                else tc_ld16(tacc + (uint32_t)(pc + k * NCB), reinterpret_cast<float(&)[16]>(v[k]));
+            }
+            if (p == NP - 1) {               // the accumulator is in registers: hand it back before the stores
+                tc_fence_before();
+                tcv_epi_bar();
+                if (et == 0) mbar_arrive(&tempty_bar[buf]);
+            }
+            const uint8_t* rrow = epi + (size_t)slot * TCV_BM * RB + (size_t)myrow * RB + (size_t)(half * HW) * 2;
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+#pragma unroll
+                for (int i = 0; i < NCB; ++i) v[k][i] += ep_bias[pc + k * NCB + i];
+                if (res) {
+#pragma unroll
+                    for (int q = 0; q < NCB / 8; ++q) {
+                        const uint4 rr = *reinterpret_cast<const uint4*>(rrow + (k * NCB + 8 * q) * 2);
+                        const uint32_t u[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            v[k][8 * q + 2 * e] += H::unpack((uint16_t)(u[e] & 0xffffu));
+                            v[k][8 * q + 2 * e + 1] += H::unpack((uint16_t)(u[e] >> 16));
+                        }
+                    }
+                }
+            }
+            uint8_t* srow = sbuf + (size_t)myrow * RB + (size_t)(half * HW) * 2;
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {   // 0: raw copy (the residual stream), 1: the consumer's operand (Snake applied)
+                uint16_t* base = reinterpret_cast<uint16_t*>(pass == 0 ? a.out16r : a.out16);
+                if (base == nullptr) continue;       // uniform
+                if (pass == 1 && a.alpha) {
+#pragma unroll
+                    for (int k = 0; k < NB; ++k)
+#pragma unroll
+                        for (int i = 0; i < NCB; ++i) {
+                            const float sn = __sinf(ep_alpha[pc + k * NCB + i] * v[k][i]);
+                            v[k][i] = fmaf(ep_ainv[pc + k * NCB + i] * sn, sn, v[k][i]);
+                        }
+                }
+#pragma unroll
+                for (int k = 0; k < NB; ++k)
+#pragma unroll
+                    for (int q = 0; q < NCB / 8; ++q)
+                        *reinterpret_cast<uint4*>(srow + (k * NCB + 8 * q) * 2) = make_uint4(
+                            (uint32_t)H::pack(v[k][8 * q]) | ((uint32_t)H::pack(v[k][8 * q + 1]) << 16),
+                            (uint32_t)H::pack(v[k][8 * q + 2]) | ((uint32_t)H::pack(v[k][8 * q + 3]) << 16),
+                            (uint32_t)H::pack(v[k][8 * q + 4]) | ((uint32_t)H::pack(v[k][8 * q + 5]) << 16),
+                            (uint32_t)H::pack(v[k][8 * q + 6]) | ((uint32_t)H::pack(v[k][8 * q + 7]) << 16));
+                tcv_epi_bar();
+                copy_out(base, pass == 0 ? a.ld16r : a.ld16, b, tt, n0 + p * PW);
+                tcv_epi_bar();               // the staging panel is free again
+            }
+        }
+    }
+    tcv_cp_async_wait_all();
 }
 
 template <int BN, bool F16>
@@ -318,6 +455,10 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         const uint32_t tlane = (uint32_t)(lg * 32) << 16;
         uint32_t iseg = 0;
         int tn_loaded = -1;
+        if (a.staged) {
+            tcv_staged_epilogue<BN, F16>(a, tmem, tcv_smem_raw + ((sbase - smem_u32(tcv_smem_raw)) + (size_t)a.nst * STAGE), tfull_bar, tempty_bar,
+                                         ep_bias, ep_gamma, ep_alpha, ep_ainv, et, lg, half, lane);
+        } else
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
             const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
             const int t = tt * TCV_BM + lg * 32 + lane, n0 = tn * BN;
@@ -429,8 +570,8 @@ inline tcv_fn tcv_pick(int bn) {
     default: return tcv_kernel<32, F16>;
     }
 }
-inline int tcv_stages_for(int bn) {
-    const int fit = (int)((225 * 1024 - 1024 - 16 * bn - 256) / tcv_stage_bytes(bn));  // static: 4 parameter rows + barriers
+inline int tcv_stages_for(int bn, bool staged) {
+    const int fit = (int)((225 * 1024 - 1024 - 16 * bn - 256 - (staged ? (int)tcv_epi_bytes(bn) : 0)) / tcv_stage_bytes(bn));  // static: 4 parameter rows + barriers
     return fit < TCV_STAGES_MAX ? fit : TCV_STAGES_MAX;
 }
 inline cudaError_t tcv_set_attrs() {
@@ -439,18 +580,19 @@ inline cudaError_t tcv_set_attrs() {
     for (int f = 0; f < 2; ++f)
         for (int i = 0; i < 6; ++i) {
             const void* k = f ? (const void*)tcv_pick<true>(bns[i]) : (const void*)tcv_pick<false>(bns[i]);
-            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcv_smem_bytes(bns[i], tcv_stages_for(bns[i])));
+            const size_t plain = tcv_smem_bytes(bns[i], tcv_stages_for(bns[i], false), false), st = tcv_smem_bytes(bns[i], tcv_stages_for(bns[i], true), true);
+            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(plain > st ? plain : st));
             if (e != cudaSuccess) return e;
         }
     return cudaSuccess;
 }
-// fills the tiling fields of `a` for column-tile width bn
+// fills the tiling fields of `a` for column-tile width bn (a.staged decides how much shared memory the stage ring gets)
 inline void tcv_plan(TcConvArgs& a, int bn) {
     a.tiles_t = (a.T + TCV_BM - 1) / TCV_BM;
     a.tiles_n = (a.N + bn - 1) / bn;
     a.n_tiles = a.B * a.tiles_t * a.tiles_n;
     a.kchunks = (a.Cin + TCV_BK - 1) / TCV_BK;
-    a.nst = tcv_stages_for(bn);
+    a.nst = tcv_stages_for(bn, a.staged != 0);
 }
 inline bool tcv_vec_ok(const TcConvArgs& a) {
     auto al = [](const void* p) { return (((uintptr_t)p) & 15) == 0; };
@@ -459,12 +601,15 @@ inline bool tcv_vec_ok(const TcConvArgs& a) {
 }
 // tensor-core launch (maps built by the caller with box rows 128 for A and `bn` for W); persistent grid of <= n_sm CTAs
 inline cudaError_t tcv_launch(cudaStream_t s, int n_sm, bool f16, int bn, const CUtensorMap& mA, const CUtensorMap& mW, TcConvArgs a) {
-    tcv_plan(a, bn);
     a.vec_ok = tcv_vec_ok(a) ? 1 : 0;
+    // 16-bit-only epilogues (the decoder's convs) go through shared memory: see tcv_staged_epilogue
+    a.staged = (a.staged_ok && a.vec_ok && a.out32 == nullptr && a.res32 == nullptr && a.gamma == nullptr && a.act == TCV_ACT_NONE &&
+                !a.round_lin && a.N % tcv_panel_cols(bn) == 0 && (a.out16 != nullptr || a.out16r != nullptr)) ? 1 : 0;
+    tcv_plan(a, bn);
     if (a.n_tiles <= 0) return cudaSuccess;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(a.n_tiles < n_sm ? a.n_tiles : n_sm); cfg.blockDim = dim3(TCV_THREADS);
-    cfg.dynamicSmemBytes = tcv_smem_bytes(bn, a.nst); cfg.stream = s;
+    cfg.dynamicSmemBytes = tcv_smem_bytes(bn, a.nst, a.staged != 0); cfg.stream = s;
     tcv_fn k = f16 ? tcv_pick<true>(bn) : tcv_pick<false>(bn);
     return cudaLaunchKernelEx(&cfg, k, mA, mW, a);
 }
