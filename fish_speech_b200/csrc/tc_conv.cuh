@@ -403,19 +403,19 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         if (lane == 0) {
             rg_prefetch_map(&tmA);
             rg_prefetch_map(&tmW);
-            uint32_t it = 0;
+            uint32_t s = 0, ph = 1;   // ring slot and the parity its empty barrier is waited with (no divisions on this path)
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
                 const int t0 = tt * TCV_BM, n0 = tn * BN;
                 for (int j = 0; j < a.taps; ++j) {
                     const int trow = t0 - (a.taps - 1 - j) * a.dil;  // negative rows: out of bounds = zeros = causal padding
-                    for (int kc = 0; kc < a.kchunks; ++kc, ++it) {
-                        const uint32_t s = it % (uint32_t)a.nst, use = it / (uint32_t)a.nst;
-                        mbar_wait(&empty_bar[s], (use & 1u) ^ 1u);
+                    for (int kc = 0; kc < a.kchunks; ++kc) {
+                        mbar_wait(&empty_bar[s], ph);
                         const uint32_t st = sbase + s * STAGE, bar = smem_u32(&full_bar[s]);
                         mbar_expect_tx(&full_bar[s], STAGE);
                         tcv_tma_load_3d(st, &tmA, bar, kc * TCV_BK, trow, b, TCV_POLICY_EVICT_NORMAL);  // re-read by the other taps / column tiles: keep in L2
                         tcv_tma_load_3d(st + TCV_A_BYTES, &tmW, bar, kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
+                        if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; }
                     }
                 }
             }
@@ -423,25 +423,30 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
     } else if (warp == 1) {
         // ===== MMA issuer
         constexpr uint32_t IDESC = tcv_idesc(BN, F16);
-        uint32_t it = 0, iseg = 0;
+        // One thread issues every MMA of the CTA: at N = 96 a 16-channel step is ~48 tensor-pipe cycles, so anything this
+        // loop spends per stage beyond that (integer divisions, descriptor rebuilds) shows up 1:1 in the layer time.
+        uint32_t iseg = 0, s = 0, ph = 0;
+        uint64_t adesc = tc_smem_desc(sbase), bdesc = tc_smem_desc(sbase + TCV_A_BYTES);
+        const uint64_t dstep = (uint64_t)(STAGE >> 4);     // descriptor address field counts 16-byte units
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
             const uint32_t buf = iseg & 1u;
             mbar_wait(&tempty_bar[buf], ((iseg >> 1) & 1u) ^ 1u);  // the epilogue has drained this accumulator
             tc_fence_after();
-            for (int i = 0; i < nk; ++i, ++it) {
-                const uint32_t s = it % (uint32_t)a.nst;
-                mbar_wait(&full_bar[s], (it / (uint32_t)a.nst) & 1u);
+            const uint32_t d = tmem + buf * BN;
+            for (int i = 0; i < nk; ++i) {
+                mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
                 if (lane == 0) {
-                    const uint32_t st = sbase + s * STAGE;
-                    const uint64_t adesc = tc_smem_desc(st), bdesc = tc_smem_desc(st + TCV_A_BYTES);
-                    const uint32_t d = tmem + buf * BN;
+                    // (skipping the zero-filled 16-channel steps of a last chunk past Cin - the 96-channel block - was measured:
+                    // no gain, the layer is not bound by the number of MMAs)
 #pragma unroll
                     for (int k = 0; k < TCV_BK / 16; ++k)
                         tc_mma_bf16(d, adesc + 2 * k, bdesc + 2 * k, IDESC, (i > 0 || k > 0) ? 1u : 0u);
                     tc_commit(&empty_bar[s]);
                 }
                 __syncwarp();
+                if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; adesc = tc_smem_desc(sbase); bdesc = tc_smem_desc(sbase + TCV_A_BYTES); }
+                else { adesc += dstep; bdesc += dstep; }
             }
             if (lane == 0) tc_commit(&tfull_bar[buf]);
             __syncwarp();
