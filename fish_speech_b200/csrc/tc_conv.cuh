@@ -78,6 +78,18 @@ template <> struct Tcv16<false> {
     static __device__ __forceinline__ uint16_t pack(float v) { return f_to_bf16_bits(v); }
     static __device__ __forceinline__ float unpack(uint16_t b) { return bf16_bits_to_f(b); }
 };
+// two values -> one 32-bit word (lo = a), same rounding / saturation as pack(): one two-way convert instead of two + shifts
+template <bool F16>
+__device__ __forceinline__ uint32_t tcv_pack2(float a, float b) {
+    if (F16) {
+        a = fminf(fmaxf(a, -65504.f), 65504.f);
+        b = fminf(fmaxf(b, -65504.f), 65504.f);
+        const __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<const uint32_t*>(&h);
+    }
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
 
 __device__ __forceinline__ float tcv_snake(float x, float a) {
     const float s = __sinf(a * x);  // MUFU sine: abs error ~1e-7 on the O(1) arguments here, far below the 16-bit rounding
@@ -232,8 +244,10 @@ __host__ __device__ constexpr int tcv_tmem_cols(int bn) { return 2 * bn <= 32 ? 
 // (an odd number of 16-byte units: a thread per row and a thread per piece are both conflict-free).
 __host__ __device__ constexpr int tcv_panel_cols(int bn) { return bn % 96 == 0 ? 96 : (bn % 64 == 0 ? 64 : 32); }
 __host__ __device__ constexpr uint32_t tcv_panel_row_bytes(int bn) { return (uint32_t)tcv_panel_cols(bn) * 2 + 16; }
-__host__ __device__ constexpr uint32_t tcv_epi_bytes(int bn) { return 3u * TCV_BM * tcv_panel_row_bytes(bn); }  // 2 residual + 1 staging
-inline size_t tcv_smem_bytes(int bn, int nst, bool staged) { return (size_t)nst * tcv_stage_bytes(bn) + (staged ? tcv_epi_bytes(bn) : 0) + 1024; }
+// one staging panel, plus two residual panels when the layer has a 16-bit residual (a layer without one keeps that shared memory
+// for its stage ring: at N = 96 a stage is only ~190 tensor-pipe cycles of work, the ring is what covers the TMA latency)
+__host__ __device__ constexpr uint32_t tcv_epi_bytes(int bn, bool has_res) { return (has_res ? 3u : 1u) * TCV_BM * tcv_panel_row_bytes(bn); }
+inline size_t tcv_smem_bytes(int bn, int nst, bool staged, bool has_res) { return (size_t)nst * tcv_stage_bytes(bn) + (staged ? tcv_epi_bytes(bn, has_res) : 0) + 1024; }
 
 __device__ __forceinline__ void tcv_epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(32 * TCV_EPI_WARPS) : "memory"); }
 __device__ __forceinline__ void tcv_tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, uint64_t policy) {
@@ -263,7 +277,7 @@ __device__ __forceinline__ void tcv_staged_epilogue(const TcConvArgs& a, uint32_
     constexpr int CPR = PW / 8;                              // 16-byte pieces per panel row
     constexpr uint32_t RB = tcv_panel_row_bytes(BN);
     constexpr int NT = 32 * TCV_EPI_WARPS;
-    uint8_t* const sbuf = epi + 2 * (size_t)TCV_BM * RB;
+    uint8_t* const sbuf = epi + (a.res16 != nullptr ? 2 : 0) * (size_t)TCV_BM * RB;   // staging panel behind the residual panels, if any
     const uint32_t tlane = (uint32_t)(lg * 32) << 16;
     const int myrow = lg * 32 + lane;                        // row of the tile this thread reads from TMEM
     const uint16_t* res = reinterpret_cast<const uint16_t*>(a.res16);
@@ -325,7 +339,10 @@ __device__ __forceinline__ void tcv_staged_epilogue(const TcConvArgs& a, uint32_
 #pragma unroll
             for (int k = 0; k < NB; ++k) {
 #pragma unroll
-                for (int i = 0; i < NCB; ++i) v[k][i] += ep_bias[pc + k * NCB + i];
+                for (int q = 0; q < NCB / 4; ++q) {   // per-column parameters as 16-byte broadcast reads
+                    const float4 b4 = *reinterpret_cast<const float4*>(ep_bias + pc + k * NCB + 4 * q);
+                    v[k][4 * q] += b4.x; v[k][4 * q + 1] += b4.y; v[k][4 * q + 2] += b4.z; v[k][4 * q + 3] += b4.w;
+                }
                 if (res) {
 #pragma unroll
                     for (int q = 0; q < NCB / 8; ++q) {
@@ -348,20 +365,24 @@ __device__ __forceinline__ void tcv_staged_epilogue(const TcConvArgs& a, uint32_
 #pragma unroll
                     for (int k = 0; k < NB; ++k)
 #pragma unroll
-                        for (int i = 0; i < NCB; ++i) {
-                            const float sn = __sinf(ep_alpha[pc + k * NCB + i] * v[k][i]);
-                            v[k][i] = fmaf(ep_ainv[pc + k * NCB + i] * sn, sn, v[k][i]);
+                        for (int q = 0; q < NCB / 4; ++q) {
+                            const float4 al = *reinterpret_cast<const float4*>(ep_alpha + pc + k * NCB + 4 * q);
+                            const float4 ai = *reinterpret_cast<const float4*>(ep_ainv + pc + k * NCB + 4 * q);
+                            const float av[4] = {al.x, al.y, al.z, al.w}, iv[4] = {ai.x, ai.y, ai.z, ai.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float sn = __sinf(av[e] * v[k][4 * q + e]);
+                                v[k][4 * q + e] = fmaf(iv[e] * sn, sn, v[k][4 * q + e]);
+                            }
                         }
                 }
 #pragma unroll
                 for (int k = 0; k < NB; ++k)
 #pragma unroll
                     for (int q = 0; q < NCB / 8; ++q)
-                        *reinterpret_cast<uint4*>(srow + (k * NCB + 8 * q) * 2) = make_uint4(
-                            (uint32_t)H::pack(v[k][8 * q]) | ((uint32_t)H::pack(v[k][8 * q + 1]) << 16),
-                            (uint32_t)H::pack(v[k][8 * q + 2]) | ((uint32_t)H::pack(v[k][8 * q + 3]) << 16),
-                            (uint32_t)H::pack(v[k][8 * q + 4]) | ((uint32_t)H::pack(v[k][8 * q + 5]) << 16),
-                            (uint32_t)H::pack(v[k][8 * q + 6]) | ((uint32_t)H::pack(v[k][8 * q + 7]) << 16));
+                        *reinterpret_cast<uint4*>(srow + (k * NCB + 8 * q) * 2) =
+                            make_uint4(tcv_pack2<F16>(v[k][8 * q], v[k][8 * q + 1]), tcv_pack2<F16>(v[k][8 * q + 2], v[k][8 * q + 3]),
+                                       tcv_pack2<F16>(v[k][8 * q + 4], v[k][8 * q + 5]), tcv_pack2<F16>(v[k][8 * q + 6], v[k][8 * q + 7]));
                 tcv_epi_bar();
                 copy_out(base, pass == 0 ? a.ld16r : a.ld16, b, tt, n0 + p * PW);
                 tcv_epi_bar();               // the staging panel is free again
@@ -575,8 +596,8 @@ inline tcv_fn tcv_pick(int bn) {
     default: return tcv_kernel<32, F16>;
     }
 }
-inline int tcv_stages_for(int bn, bool staged) {
-    const int fit = (int)((225 * 1024 - 1024 - 16 * bn - 256 - (staged ? (int)tcv_epi_bytes(bn) : 0)) / tcv_stage_bytes(bn));  // static: 4 parameter rows + barriers
+inline int tcv_stages_for(int bn, bool staged, bool has_res) {
+    const int fit = (int)((225 * 1024 - 1024 - 16 * bn - 256 - (staged ? (int)tcv_epi_bytes(bn, has_res) : 0)) / tcv_stage_bytes(bn));  // static: 4 parameter rows + barriers
     return fit < TCV_STAGES_MAX ? fit : TCV_STAGES_MAX;
 }
 inline cudaError_t tcv_set_attrs() {
@@ -585,8 +606,12 @@ inline cudaError_t tcv_set_attrs() {
     for (int f = 0; f < 2; ++f)
         for (int i = 0; i < 6; ++i) {
             const void* k = f ? (const void*)tcv_pick<true>(bns[i]) : (const void*)tcv_pick<false>(bns[i]);
-            const size_t plain = tcv_smem_bytes(bns[i], tcv_stages_for(bns[i], false), false), st = tcv_smem_bytes(bns[i], tcv_stages_for(bns[i], true), true);
-            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(plain > st ? plain : st));
+            size_t need = tcv_smem_bytes(bns[i], tcv_stages_for(bns[i], false, false), false, false);
+            for (int r = 0; r < 2; ++r) {
+                const size_t st = tcv_smem_bytes(bns[i], tcv_stages_for(bns[i], true, r != 0), true, r != 0);
+                need = st > need ? st : need;
+            }
+            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
             if (e != cudaSuccess) return e;
         }
     return cudaSuccess;
@@ -597,7 +622,7 @@ inline void tcv_plan(TcConvArgs& a, int bn) {
     a.tiles_n = (a.N + bn - 1) / bn;
     a.n_tiles = a.B * a.tiles_t * a.tiles_n;
     a.kchunks = (a.Cin + TCV_BK - 1) / TCV_BK;
-    a.nst = tcv_stages_for(bn, a.staged != 0);
+    a.nst = tcv_stages_for(bn, a.staged != 0, a.res16 != nullptr);
 }
 inline bool tcv_vec_ok(const TcConvArgs& a) {
     auto al = [](const void* p) { return (((uintptr_t)p) & 15) == 0; };
@@ -614,7 +639,7 @@ inline cudaError_t tcv_launch(cudaStream_t s, int n_sm, bool f16, int bn, const 
     if (a.n_tiles <= 0) return cudaSuccess;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(a.n_tiles < n_sm ? a.n_tiles : n_sm); cfg.blockDim = dim3(TCV_THREADS);
-    cfg.dynamicSmemBytes = tcv_smem_bytes(bn, a.nst, a.staged != 0); cfg.stream = s;
+    cfg.dynamicSmemBytes = tcv_smem_bytes(bn, a.nst, a.staged != 0, a.res16 != nullptr); cfg.stream = s;
     tcv_fn k = f16 ? tcv_pick<true>(bn) : tcv_pick<false>(bn);
     return cudaLaunchKernelEx(&cfg, k, mA, mW, a);
 }
