@@ -31,7 +31,8 @@
 #define TCV_BM 128
 #define TCV_BK 64
 #define TCV_EPI_WARPS 8          // two per TMEM lane quadrant: the quadrant's rows, alternate column blocks
-#define TCV_THREADS (64 + 32 * TCV_EPI_WARPS)
+#define TCV_THREADS (64 + 32 * TCV_EPI_WARPS + 32)   // + one warp that issues the weight tiles' TMA loads
+#define TCV_WPROD_WARP (TCV_THREADS / 32 - 1)
 #define TCV_STAGES_MAX 8
 #define TCV_A_BYTES (TCV_BM * TCV_BK * 2)
 #define TCV_POLICY_EVICT_NORMAL 0x1000000000000000ull
@@ -433,12 +434,27 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
                     for (int kc = 0; kc < a.kchunks; ++kc) {
                         mbar_wait(&empty_bar[s], ph);
                         const uint32_t st = sbase + s * STAGE, bar = smem_u32(&full_bar[s]);
-                        mbar_expect_tx(&full_bar[s], STAGE);
+                        mbar_expect_tx(&full_bar[s], STAGE);   // both tiles of the stage; the weight tile is issued by its own warp
                         tcv_tma_load_3d(st, &tmA, bar, kc * TCV_BK, trow, b, TCV_POLICY_EVICT_NORMAL);  // re-read by the other taps / column tiles: keep in L2
-                        tcv_tma_load_3d(st + TCV_A_BYTES, &tmW, bar, kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
                         if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; }
                     }
                 }
+            }
+        }
+    } else if (warp == TCV_WPROD_WARP) {
+        // ===== second TMA producer: the weight tile of every stage.  One thread issuing both tiles of a stage spends ~700-900
+        // cycles per stage whatever the tile width (a tensor copy is issued row by row), more than the stage's MMAs take.
+        if (lane == 0) {
+            rg_prefetch_map(&tmW);
+            uint32_t s = 0, ph = 1;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                const int n0 = (tile % a.tiles_n) * BN;
+                for (int j = 0; j < a.taps; ++j)
+                    for (int kc = 0; kc < a.kchunks; ++kc) {
+                        mbar_wait(&empty_bar[s], ph);
+                        tcv_tma_load_3d(sbase + s * STAGE + TCV_A_BYTES, &tmW, smem_u32(&full_bar[s]), kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
+                        if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; }
+                    }
             }
         }
     } else if (warp == 1) {
