@@ -208,13 +208,16 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             const bool need_mask = kbase + FA_BK - 1 > a.pos0 + q0;  // uniform: the block reaches past the first query of the tile
             float mx = -INFINITY;
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                float v[32];
-                tc_ld32(ts + (uint32_t)(c * 32), v);
+            for (int c = 0; c < 4; c += 2) {   // two 32-column loads in flight per wait (a wait per load put ~12 TMEM round trips
+                uint32_t u0[32], u1[32];       // on every key block's chain)
+                tc_ld32_nowait(ts + (uint32_t)(c * 32), u0);
+                tc_ld32_nowait(ts + (uint32_t)(c * 32 + 32), u1);
+                tc_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    const float sv = (need_mask && kbase + c * 32 + i > q_abs) ? -INFINITY : v[i];
-                    mx = fmaxf(mx, sv);
+                    const float s0 = (need_mask && kbase + c * 32 + i > q_abs) ? -INFINITY : __uint_as_float(u0[i]);
+                    const float s1 = (need_mask && kbase + c * 32 + 32 + i > q_abs) ? -INFINITY : __uint_as_float(u1[i]);
+                    mx = fmaxf(mx, fmaxf(s0, s1));
                 }
             }
             const float m_new = fmaxf(m, mx * a.scale_log2);
@@ -252,11 +255,16 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             mbar_wait(&o_full, (uint32_t)j & 1u);
             tc_fence_after();
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                float v[32];
-                tc_ld32(tmem + tlane + 256 + (uint32_t)(c * 32), v);
+            for (int c = 0; c < 4; c += 2) {
+                uint32_t u0[32], u1[32];
+                tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)(c * 32), u0);
+                tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)(c * 32 + 32), u1);
+                tc_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) O[c * 32 + i] = fmaf(O[c * 32 + i], corr, v[i]);
+                for (int i = 0; i < 32; ++i) {
+                    O[c * 32 + i] = fmaf(O[c * 32 + i], corr, __uint_as_float(u0[i]));
+                    O[c * 32 + 32 + i] = fmaf(O[c * 32 + 32 + i], corr, __uint_as_float(u1[i]));
+                }
             }
             tc_fence_before();
             mbar_arrive(&o_empty);
