@@ -326,10 +326,14 @@ __device__ __forceinline__ void tcv_staged_epilogue(const TcConvArgs& a, uint32_
             tcv_cp_async_commit();
             const int pc = p * PW + half * HW;             // first column (inside the tile) of this thread's share
             float v[NB][NCB];
+            {   // all of this thread's accumulator columns requested before ONE wait
+                uint32_t (&u)[NB][NCB] = reinterpret_cast<uint32_t(&)[NB][NCB]>(v);
 #pragma unroll
-            for (int k = 0; k < NB; ++k) {
-                if (NCB == 32) tc_ld32(tacc + (uint32_t)(pc + k * NCB), reinterpret_cast<float(&)[32]>(v[k]));
-                else tc_ld16(tacc + (uint32_t)(pc + k * NCB), reinterpret_cast<float(&)[16]>(v[k]));
+                for (int k = 0; k < NB; ++k) {
+                    if (NCB == 32) tc_ld32_nowait(tacc + (uint32_t)(pc + k * NCB), reinterpret_cast<uint32_t(&)[32]>(u[k]));
+                    else tc_ld16_nowait(tacc + (uint32_t)(pc + k * NCB), reinterpret_cast<uint32_t(&)[16]>(u[k]));
+                }
+                tc_ld_wait();
             }
             if (p == NP - 1) {               // the accumulator is in registers: hand it back before the stores
                 tc_fence_before();

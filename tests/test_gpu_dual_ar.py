@@ -225,6 +225,7 @@ def test_batched_frames_match_single_requests(tiny):
         return s.out_tokens[:frames].cpu().clone()
 
     mb = _mk(cfg, sd, max_rows=B)
+    mb.set_option("rows_min", 9)                     # the GEMV chain's 8-row pass (2-8 rows take the many-row path by default)
     got = run(mb, prompts, rec)                      # [frames][B][C+1]
     assert bool((got[:, :, 1:] >= 0).all()) and bool((got[:, :, 1:] < cb).all())
     for k in range(B):
@@ -232,6 +233,16 @@ def test_batched_frames_match_single_requests(tiny):
         m1.set_option("mega", 0)                     # same kernel family as the batched path: bit-identical rows
         alone = run(m1, [prompts[k]], rec[:, k: k + 1])
         assert torch.equal(alone[:, 0], got[:, k]), (k, alone[:, 0], got[:, k])
+    # default for 2-8 rows: every Linear once over all rows (tcgen05 kernel).  A request's frames must not depend on what it
+    # shares the step with: each request alone in a step of the same kind (one live row of three) gives the same tokens.
+    mb.set_option("rows_min", 2)
+    rows = run(mb, prompts, rec)
+    assert bool((rows[:, :, 1:] >= 0).all()) and bool((rows[:, :, 1:] < cb).all())
+    for k in range(B):
+        ps = [prompts[k]] * B                        # the same request in every row: identical rows, and equal to the mixed step's row k
+        same = run(mb, ps, rec[:, k: k + 1].expand(-1, B, -1).contiguous())
+        assert torch.equal(same[:, 0], same[:, 1]) and torch.equal(same[:, 0], same[:, 2])
+        assert torch.equal(same[:, 0], rows[:, k]), (k, same[:, 0], rows[:, k])
 
 
 def test_many_row_step_streams_weights_once_and_matches_oracle(tiny):

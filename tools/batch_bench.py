@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--mode", type=int, default=1, help="batch_gemm option: 1 = every Linear once over all rows, 0 = 8-row GEMV passes")
     ap.add_argument("--json", default="")
+    ap.add_argument("--max-rows", type=int, default=0, help="row capacity of the handle (default: the batch)")
     ap.add_argument("--opt", action="append", default=[], help="engine option name=value (e.g. attn_splits=8), repeatable")
     args = ap.parse_args()
     import torch
@@ -47,9 +48,9 @@ def main():
     S = (args.ctx + F + 8 + 7) // 8 * 8
     cfg = s2_pro_config(max_seq_len=S)
     sd = synth_state_dict(cfg, dev, seed=0)
-    model = DualARTransformerB200(cfg, sd, device=dev, max_rows=B)
+    model = DualARTransformerB200(cfg, sd, device=dev, max_rows=max(B, args.max_rows))
     del sd
-    model.setup_caches(B, S)
+    model.setup_caches(max(B, args.max_rows), S)
     model.set_option("batch_gemm", args.mode)
     for kv in args.opt:
         k, v = kv.split("=")
