@@ -423,8 +423,8 @@ int rows_linear(fsb_dual_ar* h, const bf16* W, const bf16* X, bf16* C, int T, in
     return 0;
 }
 
-// the many-row path (its partial-tile buffer is carved for every handle with more than one row)
-bool batch_gemm_active(const fsb_dual_ar* h, int M) { return h->batch_gemm && M >= h->rows_min && h->d.max_rows > 1 && M <= PREFILL_ROWS; }
+// the many-row path
+bool batch_gemm_active(const fsb_dual_ar* h, int M) { return h->batch_gemm && M >= h->rows_min && M <= PREFILL_ROWS; }
 bool rows_tc_active(const fsb_dual_ar* h, int M) { return h->batch_gemm == 1 && h->rg_ok && M <= 128; }
 
 // the whole layer stack runs on the tcgen05 kernel (every Linear's K is a multiple of the 64-column k block)
@@ -1017,7 +1017,7 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
         T(pq, bf16, PR * d.n_head * d.head_dim) T(pvt, bf16, (size_t)d.n_kv_head * d.head_dim * ((size_t)max_seq_len + 8))
         T(cublas_ws, char, CUBLAS_WS_BYTES)
     }
-    if (d.max_rows > 1) {
+    {
         T(rg_partial, float, rg_partial_bytes(RG_GRID_MAX, 128) / sizeof(float))
     }
     T(mega_buf, char, MEGA_BUF_BYTES) T(mega_sync, unsigned, 64) T(mega_prof, unsigned long long, 16)
@@ -1146,7 +1146,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "mega_detail_op") h->mega_detail_op = (int)value;
     else if (n == "mega_skip_dot") h->mega_skip_dot = (int)value;
     else if (n == "mega_long") h->mega_long = (int)value;
-    else if (n == "rows_min") h->rows_min = (int)std::max<int64_t>(2, value);
+    else if (n == "rows_min") h->rows_min = (int)std::max<int64_t>(1, value);
     else if (n == "attn_trace_point") h->attn_trace_point = (int)value;
     else if (n == "spin_ns") {  // poll back-off of tagged-load spins on the current device
         const unsigned ns = (unsigned)value;
