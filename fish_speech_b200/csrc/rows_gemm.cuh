@@ -94,7 +94,7 @@ inline int rg_stages_for(int grid, int n_sm, int bn) {
     if (grid > n_sm) return RG_STAGES_MIN;
     // one CTA per SM: 6 stages (144 KB in flight per SM at 64 rows).  Deeper is slower: every SM requests its whole ring at
     // launch, and the first stage of a CTA only lands when most of that burst has (9 stages: wqkv 11.1 us instead of 9.4)
-    static const int want = getenv("FSB_RG_STAGES") ? atoi(getenv("FSB_RG_STAGES")) : 6;
+    const int want = 6;
     const int fit = (int)((225 * 1024 - 1024) / rg_stage_bytes(bn));
     const int n = want < RG_STAGES_MAX ? want : RG_STAGES_MAX;
     return fit < n ? fit : n;

@@ -58,7 +58,8 @@ int fsb_dual_ar_bind_kv(fsb_dual_ar* h, int32_t is_fast, int32_t layer, void* k,
                         int32_t max_seq);
 /* Options: "pdl" (0/1), "graph" (0/1), "self_prefetch_kb", "attn_splits" (0 = auto), "mega", "masked_head", "batch_gemm",
  * "prefill_gemm", "spin_ns", ... — the full list with defaults is in DESIGN.md §2; every FSB_* environment override of
- * round 1 is an option here (the environment is no longer read, except FSB_OPTIONS="name=value,..." applied at create). */
+ * round 1 is an option here (the environment is no longer read, except FSB_OPTIONS="name=value,..." applied at create
+ * and FSB_RG_TRACE, which makes the stage entry point fsb_rows_gemm record clock stamps for tools/rows_gemm_trace.py). */
 int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value);
 
 /* Prompt pass over the slow stack: fills KV for positions [pos0, pos0+T) of `slot`; no logits.
