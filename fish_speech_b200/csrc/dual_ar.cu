@@ -87,6 +87,7 @@ struct fsb_dual_ar {
                                      // per step) on this library's tcgen05 stream-K kernel (rows_gemm.cuh), 2 = the same through
                                      // cuBLAS, 0 = 8-row passes through the GEMV kernels (weights re-streamed per pass)
     float* rg_partial = nullptr;     // stream-K partial tiles of rows_gemm_kernel
+    float* pks = nullptr;            // split-K partial sums of the prompt pass (PREFILL_KS_ROWS x dim)
     int masked_head = 1;             // fused frames with the constrained-decode bias: compute only the LM-head rows the sampler can
                                      // read (semantic range + <|im_end|>) instead of all `vocab` rows; batch 1 paths
     int rows_narrow = 0;             // many-row Linears with a plain store on narrow weight tiles without a k split
@@ -106,6 +107,7 @@ struct fsb_dual_ar {
     int rows_min = 2;                // fewest rows that take the many-row path (every Linear once over all rows on the tcgen05 kernel).
                                      // Measured at 2k context: 2 rows 5.64 ms per step against 7.59 through the GEMV chain's 8-row
                                      // pass, 4 rows 5.71 / 10.6, 8 rows 6.27 / 22.9 - the chain (rows_min = 9) is kept for comparison
+    int prefill_splitk = 1;          // prompt pass: wo / w2 of a short chunk as split-K pieces + a finish kernel
     int mega_long = 0;               // caches longer than ASP_MAXS x asp_max_keys tokens: 0 = kernel chain (faster as measured: 6.04
                                      // vs 6.29 ms per frame at 8k context), 1 = tiled frame kernel, 2 = tiled kernel at any length (tests)
     int mega_skip_dot = 0;           // experiment (results are garbage): no dot products in the frame kernel
@@ -1016,6 +1018,7 @@ static void carve(const fsb_dual_ar_desc& d, int max_seq_len, int max_splits, ch
         T(py, bf16, PR * d.n_head * d.head_dim) T(ptmp, bf16, PR * d.dim) T(pf1, bf16, PR * d.ffn) T(pf3, bf16, PR * d.ffn)
         T(pq, bf16, PR * d.n_head * d.head_dim) T(pvt, bf16, (size_t)d.n_kv_head * d.head_dim * ((size_t)max_seq_len + 8))
         T(cublas_ws, char, CUBLAS_WS_BYTES)
+        T(pks, float, (size_t)PREFILL_KS_ROWS * d.dim)   // split-K partial sums of the prompt pass's wo / w2 (short chunks)
     }
     {
         T(rg_partial, float, rg_partial_bytes(RG_GRID_MAX, 128) / sizeof(float))
@@ -1146,6 +1149,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "mega_detail_op") h->mega_detail_op = (int)value;
     else if (n == "mega_skip_dot") h->mega_skip_dot = (int)value;
     else if (n == "mega_long") h->mega_long = (int)value;
+    else if (n == "prefill_splitk") h->prefill_splitk = (int)value;
     else if (n == "rows_min") h->rows_min = (int)std::max<int64_t>(1, value);
     else if (n == "attn_trace_point") h->attn_trace_point = (int)value;
     else if (n == "spin_ns") {  // poll back-off of tagged-load spins on the current device
@@ -1258,9 +1262,48 @@ static const CUtensorMap* tcv_map(fsb_dual_ar* h, const void* ptr, int rows, int
     if (!tcv_make_map(&m, ptr, false, (uint64_t)cols, (uint64_t)rows, 1, (uint32_t)box_rows)) return nullptr;
     return &h->tcv_maps.emplace(key, m).first->second;
 }
+// out = bf16(bf16(sum of the split-K partial sums) + res): the rounding points of a Linear followed by the residual add (llama.py:838-843)
+__global__ void __launch_bounds__(256) splitk_finish_kernel(const float* __restrict__ part, int ks, size_t n, const bf16* __restrict__ res,
+                                                            bf16* __restrict__ out) {
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= n) return;
+    float4 acc = *reinterpret_cast<const float4*>(part + i);
+    for (int k = 1; k < ks; ++k) {   // fixed order: deterministic
+        const float4 p = *reinterpret_cast<const float4*>(part + (size_t)k * n + i);
+        acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+    }
+    const uint2 r = *reinterpret_cast<const uint2*>(res + i);
+    const float o0 = rbf(acc.x) + bf16_lo(r.x), o1 = rbf(acc.y) + bf16_hi(r.x), o2 = rbf(acc.z) + bf16_lo(r.y), o3 = rbf(acc.w) + bf16_hi(r.y);
+    *reinterpret_cast<uint2*>(out + i) = make_uint2(pack2(o0, o1), pack2(o2, o3));
+}
+
 static int prefill_linear_tc(fsb_dual_ar* h, cudaStream_t s, const bf16* W, const bf16* X, bf16* C, int T, int N, int K,
                              const bf16* res = nullptr, const bf16* gate = nullptr) {
     if (K % 8) return fail(h, "prompt-pass Linear needs K % 8 == 0");
+    // A Linear with few output columns on a short chunk (wo, w2: 2560 columns) has too few tiles for the chip, and a tile's time
+    // is its number of 64-channel steps (~900 cycles each whatever the tile width): the widest tile, its channel range cut into
+    // pieces that run side by side, fp32 partial sums added by a finish kernel (511 tokens: w2 94 -> ~35 us).
+    if (h->prefill_splitk && res && !gate && N % 4 == 0 && N <= h->d.dim) {
+        const int bnw = tcv_pick_bn(N);
+        const int tiles = ((T + TCV_BM - 1) / TCV_BM) * ((N + bnw - 1) / bnw), kchunks = (K + TCV_BK - 1) / TCV_BK;
+        int ks = std::min(std::min(h->n_sm / std::max(1, tiles), kchunks / 8), 8);
+        ks = std::min(ks, PREFILL_KS_ROWS / std::max(1, T));
+        if (ks >= 2) {
+            const CUtensorMap* mA = tcv_map(h, X, T, K, TCV_BM);
+            const CUtensorMap* mW = tcv_map(h, W, N, K, bnw);
+            if (!mA || !mW) return fail(h, "cuTensorMapEncodeTiled failed");
+            TcConvArgs a{};
+            a.B = 1; a.T = T; a.N = N; a.Cin = K; a.taps = 1; a.dil = 1;
+            a.out32 = h->pks; a.ld32 = N; a.ld16 = N; a.ldres = N; a.bias_mod = N; a.alpha_mod = N;
+            a.ksplit = ks;
+            CK(tcv_launch(s, h->n_sm, false, bnw, *mA, *mW, a));
+            const size_t n = (size_t)T * N;
+            const int ks_used = (kchunks + ((kchunks + ks - 1) / ks) - 1) / ((kchunks + ks - 1) / ks);
+            splitk_finish_kernel<<<(unsigned)((n / 4 + 255) / 256), 256, 0, s>>>(h->pks, ks_used, n, res, C);
+            CK(cudaGetLastError());
+            return 0;
+        }
+    }
     // column-tile width: enough tiles for the 148 SMs when the chunk is short
     int bn = tcv_pick_bn(N);
     const int tiles_t = (T + TCV_BM - 1) / TCV_BM;

@@ -8,6 +8,7 @@
 #pragma once
 #include "common.cuh"
 
+#define PREFILL_KS_ROWS 4096  // rows of fp32 split-K partial sums (pieces x chunk rows) the prompt pass may hold
 #define PREFILL_ROWS 2048  // prompt rows per chunk: bounds the activation scratch (about 100 KB per row at the S2 shape)
 
 // out[t][:] = bf16(bf16(x * rsqrt(mean(x^2) + eps)) * w)      (llama.py:995-1000)

@@ -31,8 +31,7 @@
 #define TCV_BM 128
 #define TCV_BK 64
 #define TCV_EPI_WARPS 8          // two per TMEM lane quadrant: the quadrant's rows, alternate column blocks
-#define TCV_THREADS (64 + 32 * TCV_EPI_WARPS + 32)   // + one warp that issues the weight tiles' TMA loads
-#define TCV_WPROD_WARP (TCV_THREADS / 32 - 1)
+#define TCV_THREADS (64 + 32 * TCV_EPI_WARPS)
 #define TCV_STAGES_MAX 8
 #define TCV_A_BYTES (TCV_BM * TCV_BK * 2)
 #define TCV_POLICY_EVICT_NORMAL 0x1000000000000000ull
@@ -42,6 +41,9 @@ enum { TCV_ACT_NONE = 0, TCV_ACT_GELU = 1, TCV_ACT_TANH = 2, TCV_ACT_SWIGLU = 3,
 struct TcConvArgs {
     int B, T, N, Cin, taps, dil;
     int tiles_t, tiles_n, n_tiles, kchunks, nst;
+    int ksplit, kper;    // split-K: a tile's channel chunks are cut into `ksplit` ranges of `kper` chunks, one work item each (n_tiles
+                         // counts work items); item i = (tile i / ksplit, range i % ksplit) writes its fp32 partial sums to
+                         // out32 + range * B*T rows.  For few-tile Linears of a short prompt chunk (set by the caller, 0/1 = off)
     // ---- operands of the SIMT variant (the tensor-core kernel reads them through its tensor maps)
     const void* A16;     // [B][T][Cin] 16-bit
     const void* W16;     // [taps][N][Cin] 16-bit
@@ -422,7 +424,7 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
-    const int nk = a.taps * a.kchunks;  // reduction steps per tile
+    const int ks = a.ksplit > 1 ? a.ksplit : 1;
 
     if (warp == 0) {
         // ===== TMA producer
@@ -430,35 +432,22 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             rg_prefetch_map(&tmA);
             rg_prefetch_map(&tmW);
             uint32_t s = 0, ph = 1;   // ring slot and the parity its empty barrier is waited with (no divisions on this path)
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            for (int item = blockIdx.x; item < a.n_tiles; item += gridDim.x) {
+                const int sp = item % ks, tile = item / ks;
                 const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
                 const int t0 = tt * TCV_BM, n0 = tn * BN;
+                const int kc_lo = sp * a.kper, kc_hi = min(a.kchunks, kc_lo + a.kper);
                 for (int j = 0; j < a.taps; ++j) {
                     const int trow = t0 - (a.taps - 1 - j) * a.dil;  // negative rows: out of bounds = zeros = causal padding
-                    for (int kc = 0; kc < a.kchunks; ++kc) {
+                    for (int kc = kc_lo; kc < kc_hi; ++kc) {
                         mbar_wait(&empty_bar[s], ph);
                         const uint32_t st = sbase + s * STAGE, bar = smem_u32(&full_bar[s]);
-                        mbar_expect_tx(&full_bar[s], STAGE);   // both tiles of the stage; the weight tile is issued by its own warp
+                        mbar_expect_tx(&full_bar[s], STAGE);
                         tcv_tma_load_3d(st, &tmA, bar, kc * TCV_BK, trow, b, TCV_POLICY_EVICT_NORMAL);  // re-read by the other taps / column tiles: keep in L2
+                        tcv_tma_load_3d(st + TCV_A_BYTES, &tmW, bar, kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
                         if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; }
                     }
                 }
-            }
-        }
-    } else if (warp == TCV_WPROD_WARP) {
-        // ===== second TMA producer: the weight tile of every stage.  One thread issuing both tiles of a stage spends ~700-900
-        // cycles per stage whatever the tile width (a tensor copy is issued row by row), more than the stage's MMAs take.
-        if (lane == 0) {
-            rg_prefetch_map(&tmW);
-            uint32_t s = 0, ph = 1;
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-                const int n0 = (tile % a.tiles_n) * BN;
-                for (int j = 0; j < a.taps; ++j)
-                    for (int kc = 0; kc < a.kchunks; ++kc) {
-                        mbar_wait(&empty_bar[s], ph);
-                        tcv_tma_load_3d(sbase + s * STAGE + TCV_A_BYTES, &tmW, smem_u32(&full_bar[s]), kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
-                        if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; }
-                    }
             }
         }
     } else if (warp == 1) {
@@ -470,6 +459,8 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         uint64_t adesc = tc_smem_desc(sbase), bdesc = tc_smem_desc(sbase + TCV_A_BYTES);
         const uint64_t dstep = (uint64_t)(STAGE >> 4);     // descriptor address field counts 16-byte units
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
+            const int kc_lo = (tile % ks) * a.kper;
+            const int nk = a.taps * (min(a.kchunks, kc_lo + a.kper) - kc_lo);   // reduction steps of this work item
             const uint32_t buf = iseg & 1u;
             mbar_wait(&tempty_bar[buf], ((iseg >> 1) & 1u) ^ 1u);  // the epilogue has drained this accumulator
             tc_fence_after();
@@ -505,7 +496,8 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             tcv_staged_epilogue<BN, F16>(a, tmem, tcv_smem_raw + ((sbase - smem_u32(tcv_smem_raw)) + (size_t)a.nst * STAGE), tfull_bar, tempty_bar,
                                          ep_bias, ep_gamma, ep_alpha, ep_ainv, et, lg, half, lane);
         } else
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++iseg) {
+        for (int item = blockIdx.x; item < a.n_tiles; item += gridDim.x, ++iseg) {
+            const int sp = item % ks, tile = item / ks;
             const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
             const int t = tt * TCV_BM + lg * 32 + lane, n0 = tn * BN;
             if (tn != tn_loaded) {  // uniform over the epilogue threads; everyone is past the previous tile (barrier below)
@@ -517,7 +509,7 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             mbar_wait(&tfull_bar[buf], (iseg >> 1) & 1u);
             tc_fence_after();
             const uint32_t tacc = tmem + tlane + buf * BN;
-            const size_t row = (size_t)b * a.T + t;
+            const size_t row = (size_t)b * a.T + t + (size_t)sp * a.B * a.T;   // split-K: partial sums of range sp go to their own rows
 #pragma unroll 1
             for (int k = half; k < NBLK; k += 2) {
                 const int nc = n0 + k * NCB;
@@ -640,8 +632,15 @@ inline cudaError_t tcv_set_attrs() {
 inline void tcv_plan(TcConvArgs& a, int bn) {
     a.tiles_t = (a.T + TCV_BM - 1) / TCV_BM;
     a.tiles_n = (a.N + bn - 1) / bn;
-    a.n_tiles = a.B * a.tiles_t * a.tiles_n;
     a.kchunks = (a.Cin + TCV_BK - 1) / TCV_BK;
+    if (a.ksplit > 1) {
+        a.kper = (a.kchunks + a.ksplit - 1) / a.ksplit;
+        a.ksplit = (a.kchunks + a.kper - 1) / a.kper;   // no empty ranges
+    } else {
+        a.ksplit = 1;
+        a.kper = a.kchunks;
+    }
+    a.n_tiles = a.B * a.tiles_t * a.tiles_n * a.ksplit;
     a.nst = tcv_stages_for(bn, a.staged != 0, a.res16 != nullptr);
 }
 inline bool tcv_vec_ok(const TcConvArgs& a) {
@@ -654,7 +653,7 @@ inline cudaError_t tcv_launch(cudaStream_t s, int n_sm, bool f16, int bn, const 
     a.vec_ok = tcv_vec_ok(a) ? 1 : 0;
     // 16-bit-only epilogues (the decoder's convs) go through shared memory: see tcv_staged_epilogue
     a.staged = (a.staged_ok && a.vec_ok && a.out32 == nullptr && a.res32 == nullptr && a.gamma == nullptr && a.act == TCV_ACT_NONE &&
-                !a.round_lin && a.N % tcv_panel_cols(bn) == 0 && (a.out16 != nullptr || a.out16r != nullptr)) ? 1 : 0;
+                !a.round_lin && a.ksplit <= 1 && a.N % tcv_panel_cols(bn) == 0 && (a.out16 != nullptr || a.out16r != nullptr)) ? 1 : 0;
     tcv_plan(a, bn);
     if (a.n_tiles <= 0) return cudaSuccess;
     cudaLaunchConfig_t cfg{};
