@@ -1001,11 +1001,17 @@ __device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem
 #pragma unroll
                     for (int g = 0; g < GQ; ++g) sm.sc[g][jl] = d[g] * a.scale;
             }
-            if (t + 1 < ntiles) {  // the key registers are free: request the next tile's keys now
-#pragma unroll
+            uint4 vnext[ASP_KPT];
+            if (t + 1 < ntiles) {  // the key registers are free: request the next tile's keys AND values now, so that both
+#pragma unroll                     // travel under this tile's softmax and P.V (a load that misses L2 waits ~2-4 us behind the weight stream)
                 for (int i = 0; i < ASP_KPT; ++i) {
                     const int j = k0 + tb + MAXK + kslot + KPI * i;
                     kq[i] = (j < kc1) ? ld_stream(kbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int i = 0; i < ASP_KPT; ++i) {
+                    const int j = k0 + tb + MAXK + kslot + KPI * i;
+                    vnext[i] = (j < kc1) ? ld_stream(vbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
                 }
             }
             SY::sync();
@@ -1055,10 +1061,7 @@ __device__ __forceinline__ void attn_split_body(const AttnArgs& a, AttnSplitSmem
             }
             if (t + 1 < ntiles) {
 #pragma unroll
-                for (int i = 0; i < ASP_KPT; ++i) {
-                    const int j = k0 + tb + MAXK + kslot + KPI * i;
-                    vq[i] = (j < kc1) ? ld_stream(vbase + (size_t)j * HD + chunk * 8) : make_uint4(0, 0, 0, 0);
-                }
+                for (int i = 0; i < ASP_KPT; ++i) vq[i] = vnext[i];
                 SY::sync();  // the scores and factors of this tile are overwritten by the next one
             }
         }
