@@ -107,6 +107,7 @@ struct fsb_dual_ar {
     int rows_min = 2;                // fewest rows that take the many-row path (every Linear once over all rows on the tcgen05 kernel).
                                      // Measured at 2k context: 2 rows 5.64 ms per step against 7.59 through the GEMV chain's 8-row
                                      // pass, 4 rows 5.71 / 10.6, 8 rows 6.27 / 22.9 - the chain (rows_min = 9) is kept for comparison
+    int prefill_rows = 1;            // prompt pieces of <= 2 x max_rows rows on handles with >= 16 rows go through the many-row decode kernels
     int prefill_splitk = 1;          // prompt pass: wo / w2 of a short chunk as split-K pieces + a finish kernel
     int mega_long = 0;               // caches longer than ASP_MAXS x asp_max_keys tokens: 0 = kernel chain (faster as measured: 6.04
                                      // vs 6.29 ms per frame at 8k context), 1 = tiled frame kernel, 2 = tiled kernel at any length (tests)
@@ -1150,6 +1151,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "mega_skip_dot") h->mega_skip_dot = (int)value;
     else if (n == "mega_long") h->mega_long = (int)value;
     else if (n == "prefill_splitk") h->prefill_splitk = (int)value;
+    else if (n == "prefill_rows") h->prefill_rows = (int)value;
     else if (n == "rows_min") h->rows_min = (int)std::max<int64_t>(1, value);
     else if (n == "attn_trace_point") h->attn_trace_point = (int)value;
     else if (n == "spin_ns") {  // poll back-off of tagged-load spins on the current device
@@ -1407,6 +1409,28 @@ int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_
     CK(cudaGetLastError());
     const int C1 = h->d.num_codebooks + 1;
     if (h->prefill_gemm == 1 && (rg_get_encode() == nullptr || h->d.dim % 8 || h->d.ffn % 8)) h->prefill_gemm = 0;  // no tensor-map encoder: decode kernels
+    // A short prompt piece on a handle with many rows (the scheduler's: the own columns behind a shared voice prefix): the
+    // many-row decode kernels take it in passes of max_rows rows - rows of one KV slot at consecutive positions; the K / V
+    // append is its own launch before the tensor-core attention, so a row sees the keys of the rows before it.  A pass streams
+    // the weights once over all SMs (~75 us per layer), the 128-row tiles of the prompt-pass GEMM need ~190 us per layer
+    // however few rows there are.
+    if (h->prefill_gemm == 1 && h->prefill_rows && h->d.max_rows >= 16 && T <= 2 * h->d.max_rows) {
+        const int Mr = std::min<int>(T, h->d.max_rows);
+        AttnKernels ak;
+        if (pick_attn(h->d.head_dim, h->d.n_head / h->d.n_kv_head, &ak) && ak.tc && h->attn_tc && rows_tc_layers(h, Mr)) {
+            if (int r = check_bound(h)) return r;
+            for (int t0 = 0; t0 < T; t0 += h->d.max_rows) {
+                const int M = std::min<int>(h->d.max_rows, T - t0);
+                if (int r = run_embed(h, s, M, tokens + (size_t)t0 * C1)) return r;
+                if (rows_tc_layers(h, M)) {
+                    if (int r = run_layers_rows(h, s, false, M, h->x2, h->pf_pos + t0, h->pf_slot + t0, -1, nullptr, nullptr)) return r;
+                } else if (int r = run_layers(h, s, false, M, h->x2, h->pf_pos + t0, h->pf_slot + t0, false, -1)) {  // a last piece of one row
+                    return r;
+                }
+            }
+            return 0;
+        }
+    }
     if (h->prefill_gemm) {
         if (int r = check_bound(h)) return r;
         if (h->prefill_gemm == 1) CK(tcv_set_attrs());

@@ -243,6 +243,48 @@ def test_prompt_pass_on_own_tcgen05_kernel_vs_oracle_and_library(s2w):
             assert mabs <= _abs_tol(ref[0, -1])
 
 
+def test_short_prompt_pieces_through_the_many_row_kernels_vs_prompt_pass_and_oracle():
+    """A handle with 16 rows (a scheduler's) takes prompt pieces of <= 32 columns through the many-row decode kernels in passes of
+    16 rows of ONE KV slot (option prefill_rows): the first frame's logits must agree with the oracle and with the prompt-pass
+    kernels (prefill_rows = 0), for one pass, two passes, a last pass of one row, into slot 0 and slot 5, from position 0 and
+    behind resident columns."""
+    from fish_speech_b200 import DualARTransformerB200
+    import ctypes as C
+    from fish_speech_b200.dual_ar import _stream
+    cfg = s2w_config()
+    sd = R.make_state_dict(cfg, seed=13)
+    m = DualARTransformerB200(cfg.__dict__, sd, device="cuda:0", max_rows=16)
+    m.setup_caches(16, cfg.max_seq_len)
+    om = R.DualARRef(cfg, sd)
+    om.setup_caches(1, cfg.max_seq_len)
+    V = cfg.vocab_size
+
+    def first_logits(seq, slot, rows, split_at=0):
+        m.set_option("prefill_rows", rows)
+        T = seq.shape[1]
+        if split_at:
+            m.prefill(seq[:, :split_at].cuda(), 0, slot)                 # resident columns (prompt-pass kernels: 40 > 2 x 16)
+        m.prefill(seq[:, split_at: T - 1].cuda(), split_at, slot)
+        tok = torch.zeros((16, cfg.num_codebooks + 1), dtype=torch.int32, device="cuda")
+        pos = torch.zeros((16,), dtype=torch.int32, device="cuda")
+        tok[slot] = seq[:, -1].to(torch.int32).cuda()
+        pos[slot] = T - 1
+        m._ck(m.lib.fsb_dual_ar_slow_step(m._h, 16, tok.data_ptr(), pos.data_ptr(), None, _stream()))
+        torch.cuda.synchronize()
+        return m._buffer("slow_logits")[: 16 * V].view(16, V)[slot].float().cpu().clone()
+
+    for T, slot, split_at in ((12, 0, 0), (17, 5, 0), (33, 5, 0), (34, 3, 0), (70, 2, 40)):
+        seq = R.make_prompt(cfg, T, seed=40 + T, voice_span=T // 3)
+        ref, _ = om.forward_generate(seq[None], torch.arange(T))
+        a = first_logits(seq, slot, 1, split_at)
+        b = first_logits(seq, slot, 0, split_at)
+        _check(f"short prompt through the many-row kernels T={T} slot {slot}", a, ref[0, -1])
+        mabs, _, _ = err_stats(a, b)
+        print(f"[parity] many-row route vs prompt-pass kernels T={T}: max-abs {mabs:.4f}")
+        assert mabs <= _abs_tol(ref[0, -1])
+    m.set_option("prefill_rows", 1)
+
+
 def test_flash_attention_prompt_pass_vs_per_row_attention_and_oracle(s2w):
     """fa_prefill_kernel (tcgen05 causal flash attention, option prefill_fa = 1, the default at head_dim 128) against the
     per-row decode attention (prefill_fa = 0) and the oracle: lengths around the 128-row / 128-key block edges, and a prompt
