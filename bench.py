@@ -391,6 +391,49 @@ def cpu_dac_leg(frames=215):
                       "32 x 30 s clips would take 96x as long"}
 
 
+def measure_scheduler(dev, rows=64, n_req=192, voice=384):
+    """Continuous batching (fish_speech_b200/scheduler.py) on one GPU: `n_req` requests through `rows` rows, each a
+    prompt of a shared `voice`-column prefix (a reference voice) + 32-128 own columns and 48-192 frames (<|im_end|> masked so
+    the lengths are the budgets); wall clock from the first submit to the last result, prompts resident on the device."""
+    import queue as _q
+    import torch
+    from fish_speech_b200 import DualARTransformerB200, s2_pro_config
+    from fish_speech_b200.scheduler import ContinuousBatcher, GenerateRequest
+    cfg = s2_pro_config(max_seq_len=1024)
+    model = DualARTransformerB200(cfg, synth_state_dict(cfg, dev, seed=0), device=dev, max_rows=rows)
+    model.setup_caches(rows, cfg.max_seq_len)
+    model.ignore_eos = True
+    g = torch.Generator().manual_seed(0)
+    reqs, vp = [], synth_prompt(cfg, voice, seed=3)
+    for i in range(n_req):
+        T = voice + int(torch.randint(32, 129, (1,), generator=g))
+        p = synth_prompt(cfg, T, seed=10 + i)
+        p[:, :voice] = vp
+        reqs.append(GenerateRequest(request=dict(prompt=p.to(dev), max_new_tokens=int(torch.randint(48, 193, (1,), generator=g)),
+                                                 temperature=0.8, top_p=0.8, top_k=30), response_queue=_q.Queue()))
+    b = ContinuousBatcher(model, chunk_frames=8)
+    for it in reqs[:rows]:      # warm-up: graph capture, tensor maps
+        b.submit(it)
+    b.step()
+    b.active.clear(); b.waiting.clear(); b.resident.clear(); b.park.clear(); b.key = None
+    b.steps = b.frames_run = b.frames_kept = b.prompt_cols = b.shared_cols = 0
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for it in reqs:
+        b.submit(it)
+    done = b.run_until_idle()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    frames = sum(int(c.shape[1]) + 1 for _, c in done)
+    out = {"workload": f"{n_req} requests through {rows} rows (continuous batching behind the reference's queue protocol): a shared {voice}-column "
+                       "voice prefix + 32-128 own prompt columns, 48-192 frames each, S2-Pro shape, one GPU",
+           "value": frames * FRAME_SEC / dt, "unit": "audio-s/s", "wall_s": dt, "frames_delivered": frames, "chunk_steps": b.steps,
+           "row_occupancy": b.frames_kept / max(1, b.frames_run), "prompt_columns": b.prompt_cols, "prompt_columns_shared": b.shared_cols}
+    del b, model
+    torch.cuda.empty_cache()
+    return out
+
+
 def measure_config5(dev, rank, T=8192, F=4096):
     """BASELINE configs[4]: long-form voice clone on one GPU: T-token prompt (pinned host), prompt pass (own tcgen05 GEMM + flash
     attention), F decode frames at max_seq_len 16384 (context 8k -> 12k: kernel chain; the persistent frame kernel's tiled
@@ -581,6 +624,12 @@ def run_ours(args):
             dac_cpu = cpu_dac_leg()
         except Exception as e:
             dac_cpu = {"value": None, "sample": f"failed: {e}"}
+    sched = None
+    if args.sched and world == 1:
+        try:
+            sched = measure_scheduler(dev)
+        except Exception as e:
+            sched = {"error": str(e)}
     c5 = None
     if args.config5:
         try:
@@ -681,6 +730,8 @@ def run_ours(args):
         line["dac"] = {"error": str(dac)}
     if c5 is not None:
         line["config5"] = c5
+    if sched is not None:
+        line["scheduler"] = sched
     if not args.no_cpu and world >= 1:
         try:
             v, cores, sample, _, kind = cpu_leg(args.ref_frames)
@@ -705,6 +756,7 @@ def main():
     ap.add_argument("--no-batched", action="store_true", help="skip the config-3 (bs64) section")
     ap.add_argument("--no-dac", action="store_true", help="skip the config-4 (DAC decode) section")
     ap.add_argument("--no-config5", dest="config5", action="store_false", help="skip the long-form section (8k-token prompt + 4k frames + DAC, BASELINE configs[4], ~30 s)")
+    ap.add_argument("--no-sched", dest="sched", action="store_false", help="skip the continuous-batching section (N = 1 only, ~15 s)")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--batch-ctx", type=int, default=2048)
     ap.add_argument("--batch-frames", type=int, default=48)
