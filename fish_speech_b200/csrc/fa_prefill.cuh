@@ -21,7 +21,8 @@
 #define FA_BQ 128
 #define FA_BK 128
 #define FA_HD 128
-#define FA_THREADS 192
+#define FA_SOFT_WARPS 8                               // two per TMEM lane quadrant: the quadrant's query rows, one half of the columns each
+#define FA_THREADS (64 + 32 * FA_SOFT_WARPS)
 #define FA_TILE_BYTES (128 * 128 * 2)                 // one 128 x 128 bf16 tile = two 16 KB swizzled boxes
 #define FA_SMEM (4 * FA_TILE_BYTES + 2 * FA_TILE_BYTES + 1024)  // K, V^T double-buffered + Q + P
 
@@ -99,7 +100,7 @@ __device__ __forceinline__ void fa_tma_3d(uint32_t dst, const CUtensorMap* map, 
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                  ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
-__device__ __forceinline__ void fa_soft_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void fa_soft_bar() { asm volatile("bar.sync 1, %0;" ::"n"(32 * FA_SOFT_WARPS) : "memory"); }
 
 __global__ void __launch_bounds__(FA_THREADS, 1)
 fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -107,6 +108,8 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     extern __shared__ uint8_t fa_smem_raw[];
     __shared__ uint64_t q_full, kv_full[2], kv_empty[2], s_full[2], s_empty[2], p_full, p_empty, o_full, o_empty;
     __shared__ uint32_t tmem_base_s;
+    __shared__ float ex_max[2][2][FA_BQ];   // [block parity][column half][query row]: the halves' row maxima of a key block
+    __shared__ float ex_sum[FA_BQ];         // the upper half's row sum, handed to the lower half at the end
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t sbase = (smem_u32(fa_smem_raw) + 1023u) & ~1023u;
     const uint32_t sQ = sbase, sP = sbase + FA_TILE_BYTES, sKV = sbase + 2 * FA_TILE_BYTES;  // stage s: K at sKV + s*64K, V^T 32 KB after it
@@ -117,8 +120,8 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
 
     if (tid == 0) {
         mbar_init(&q_full, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 128); }
-        mbar_init(&p_full, 128); mbar_init(&p_empty, 1); mbar_init(&o_full, 1); mbar_init(&o_empty, 128);
+        for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 32 * FA_SOFT_WARPS); }
+        mbar_init(&p_full, 32 * FA_SOFT_WARPS); mbar_init(&p_empty, 1); mbar_init(&o_full, 1); mbar_init(&o_empty, 32 * FA_SOFT_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -191,58 +194,82 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             __syncwarp();
         }
     } else {
-        // ===== softmax + output: thread = query row r of the block (TMEM lane r)
-        const int r = (warp & 3) * 32 + lane;
+        // ===== softmax + output: thread = query row r of the block (TMEM lane r) x one half of the columns.  Four warps (one
+        // per scheduler) could not keep up with the tensor pipe: ~3000 dependent instructions per key block and thread left it
+        // 11 % busy; eight warps halve the chain, the two halves of a row meet once per block (row maximum, through shared
+        // memory) and once at the end (row sum).
+        const int r = (warp & 3) * 32 + lane, hf = (warp - 2) >> 2;
         const uint32_t tlane = (uint32_t)((warp & 3) * 32) << 16;
         const int q_abs = a.pos0 + q0 + r;
-        float m = -INFINITY, l = 0.f;
-        float O[FA_HD];
+        const int c0 = hf * 64;                      // first column (key inside the block / head dim) of this thread's half
+        float m = -INFINITY, l = 0.f, corr_prev = 0.f;
+        float O[64];
 #pragma unroll
-        for (int i = 0; i < FA_HD; ++i) O[i] = 0.f;
+        for (int i = 0; i < 64; ++i) O[i] = 0.f;
         for (int j = 0; j < nblk; ++j) {
             const uint32_t sb = (uint32_t)j & 1u;
             mbar_wait(&s_full[sb], ((uint32_t)j >> 1) & 1u);
             tc_fence_after();
-            const uint32_t ts = tmem + tlane + sb * 128;
-            const int kbase = j * FA_BK;
-            const bool need_mask = kbase + FA_BK - 1 > a.pos0 + q0;  // uniform: the block reaches past the first query of the tile
+            const uint32_t ts = tmem + tlane + sb * 128 + (uint32_t)c0;
+            const int kbase = j * FA_BK + c0;
+            const bool need_mask = j * FA_BK + FA_BK - 1 > a.pos0 + q0;  // uniform: the block reaches past the first query of the tile
+            uint32_t u0[32], u1[32];
+            tc_ld32_nowait(ts, u0);
+            tc_ld32_nowait(ts + 32, u1);
+            tc_ld_wait();
             float mx = -INFINITY;
-#pragma unroll 1
-            for (int c = 0; c < 4; c += 2) {   // two 32-column loads in flight per wait (a wait per load put ~12 TMEM round trips
-                uint32_t u0[32], u1[32];       // on every key block's chain)
-                tc_ld32_nowait(ts + (uint32_t)(c * 32), u0);
-                tc_ld32_nowait(ts + (uint32_t)(c * 32 + 32), u1);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float s0 = (need_mask && kbase + i > q_abs) ? -INFINITY : __uint_as_float(u0[i]);
+                const float s1 = (need_mask && kbase + 32 + i > q_abs) ? -INFINITY : __uint_as_float(u1[i]);
+                mx = fmaxf(mx, fmaxf(s0, s1));
+            }
+            ex_max[sb][hf][r] = mx;
+            fa_soft_bar();
+            mx = fmaxf(mx, ex_max[sb][hf ^ 1][r]);
+            const float m_new = fmaxf(m, mx * a.scale_log2);
+            const float corr = exp2f(m - m_new);  // 0 for the first block (m = -inf)
+            if (j > 0) {
+                // the previous block's P.V ran under this block's maximum pass: fold its result in now (its own factor), which
+                // also means that P.V has read P and the P tile may be overwritten
+                mbar_wait(&o_full, (uint32_t)(j - 1) & 1u);
+                tc_fence_after();
+                uint32_t o0[32], o1[32];
+                tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)c0, o0);
+                tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)c0 + 32, o1);
                 tc_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    const float s0 = (need_mask && kbase + c * 32 + i > q_abs) ? -INFINITY : __uint_as_float(u0[i]);
-                    const float s1 = (need_mask && kbase + c * 32 + 32 + i > q_abs) ? -INFINITY : __uint_as_float(u1[i]);
-                    mx = fmaxf(mx, fmaxf(s0, s1));
+                    O[i] = fmaf(O[i], corr_prev, __uint_as_float(o0[i]));
+                    O[32 + i] = fmaf(O[32 + i], corr_prev, __uint_as_float(o1[i]));
                 }
+                tc_fence_before();
+                mbar_arrive(&o_empty);
+                mbar_wait(&p_empty, ((uint32_t)(j - 1)) & 1u);
             }
-            const float m_new = fmaxf(m, mx * a.scale_log2);
-            const float corr = exp2f(m - m_new);  // 0 for the first block (m = -inf)
-            if (j > 0) mbar_wait(&p_empty, ((uint32_t)(j - 1)) & 1u);  // P.V of the previous block has read P
+            tc_ld32_nowait(ts, u0);      // the scores again (keeping them in registers across the update above would spill)
+            tc_ld32_nowait(ts + 32, u1);
+            tc_ld_wait();
             float lsum = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                float v[32];
-                tc_ld32(ts + (uint32_t)(c * 32), v);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const uint32_t (&v)[32] = c ? u1 : u0;
                 uint32_t w[16];
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
                     const bool k0 = need_mask && kbase + c * 32 + i > q_abs, k1 = need_mask && kbase + c * 32 + i + 1 > q_abs;
-                    const float p0 = k0 ? 0.f : exp2f(fmaf(v[i], a.scale_log2, -m_new));
-                    const float p1 = k1 ? 0.f : exp2f(fmaf(v[i + 1], a.scale_log2, -m_new));
+                    const float p0 = k0 ? 0.f : exp2f(fmaf(__uint_as_float(v[i]), a.scale_log2, -m_new));
+                    const float p1 = k1 ? 0.f : exp2f(fmaf(__uint_as_float(v[i + 1]), a.scale_log2, -m_new));
                     const uint32_t b0 = f_to_bf16_bits(p0), b1 = f_to_bf16_bits(p1);
                     lsum += bf16_bits_to_f((uint16_t)b0) + bf16_bits_to_f((uint16_t)b1);  // the sum of what P.V will use
                     w[i >> 1] = b0 | (b1 << 16);
                 }
-                // swizzled K-major operand layout: 16-byte unit u of row r of a 64-key box sits at unit u ^ (r & 7)
-                const uint32_t box = sP + (uint32_t)(c >> 1) * 16384u + (uint32_t)r * 128u;
+                // swizzled K-major operand layout: 16-byte unit u of row r of a 64-key box sits at unit u ^ (r & 7);
+                // this half's 64 keys are box `hf`
+                const uint32_t box = sP + (uint32_t)hf * 16384u + (uint32_t)r * 128u;
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const uint32_t unit = (uint32_t)((c & 1) * 4 + u) ^ (uint32_t)(r & 7);
+                    const uint32_t unit = (uint32_t)(c * 4 + u) ^ (uint32_t)(r & 7);
                     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(box + (unit << 4)), "r"(w[4 * u]), "r"(w[4 * u + 1]), "r"(w[4 * u + 2]), "r"(w[4 * u + 3]) : "memory");
                 }
             }
@@ -252,28 +279,35 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             mbar_arrive(&p_full);
             l = l * corr + lsum;
             m = m_new;
-            mbar_wait(&o_full, (uint32_t)j & 1u);
+            corr_prev = corr;
+        }
+        {   // the last block's P.V
+            mbar_wait(&o_full, (uint32_t)(nblk - 1) & 1u);
             tc_fence_after();
+            uint32_t o0[32], o1[32];
+            tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)c0, o0);
+            tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)c0 + 32, o1);
+            tc_ld_wait();
 #pragma unroll
-            for (int c = 0; c < 4; c += 2) {
-                uint32_t u0[32], u1[32];
-                tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)(c * 32), u0);
-                tc_ld32_nowait(tmem + tlane + 256 + (uint32_t)(c * 32 + 32), u1);
-                tc_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    O[c * 32 + i] = fmaf(O[c * 32 + i], corr, __uint_as_float(u0[i]));
-                    O[c * 32 + 32 + i] = fmaf(O[c * 32 + 32 + i], corr, __uint_as_float(u1[i]));
-                }
+            for (int i = 0; i < 32; ++i) {
+                O[i] = fmaf(O[i], corr_prev, __uint_as_float(o0[i]));
+                O[32 + i] = fmaf(O[32 + i], corr_prev, __uint_as_float(o1[i]));
             }
             tc_fence_before();
             mbar_arrive(&o_empty);
         }
+        if (hf == 1) ex_sum[r] = l;
+        fa_soft_bar();
+        if (hf == 0) l += ex_sum[r];
+        else l += 0.f;
+        if (hf == 0) ex_sum[r] = l;          // the lower half publishes the full sum for its partner
+        fa_soft_bar();
+        l = ex_sum[r];
         if (q0 + r < a.T) {
             const float inv = 1.f / l;
-            uint4* dst = reinterpret_cast<uint4*>(a.y + ((size_t)(q0 + r) * a.H + h) * FA_HD);
+            uint4* dst = reinterpret_cast<uint4*>(a.y + ((size_t)(q0 + r) * a.H + h) * FA_HD + c0);
 #pragma unroll
-            for (int u = 0; u < 16; ++u)
+            for (int u = 0; u < 8; ++u)
                 dst[u] = make_uint4(pack2(O[8 * u] * inv, O[8 * u + 1] * inv), pack2(O[8 * u + 2] * inv, O[8 * u + 3] * inv),
                                     pack2(O[8 * u + 4] * inv, O[8 * u + 5] * inv), pack2(O[8 * u + 6] * inv, O[8 * u + 7] * inv));
         }
