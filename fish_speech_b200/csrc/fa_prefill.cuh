@@ -100,6 +100,12 @@ __device__ __forceinline__ void fa_tma_3d(uint32_t dst, const CUtensorMap* map, 
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                  ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
+// 2^x on the special-function unit (arguments here are <= 0: scores minus the running maximum, or -inf)
+__device__ __forceinline__ float fa_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ void fa_soft_bar() { asm volatile("bar.sync 1, %0;" ::"n"(32 * FA_SOFT_WARPS) : "memory"); }
 
 __global__ void __launch_bounds__(FA_THREADS, 1)
@@ -218,11 +224,16 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             tc_ld32_nowait(ts + 32, u1);
             tc_ld_wait();
             float mx = -INFINITY;
+            if (need_mask) {   // only the blocks on the diagonal pay for the per-element comparisons
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float s0 = (need_mask && kbase + i > q_abs) ? -INFINITY : __uint_as_float(u0[i]);
-                const float s1 = (need_mask && kbase + 32 + i > q_abs) ? -INFINITY : __uint_as_float(u1[i]);
-                mx = fmaxf(mx, fmaxf(s0, s1));
+                for (int i = 0; i < 32; ++i) {
+                    const float s0 = (kbase + i > q_abs) ? -INFINITY : __uint_as_float(u0[i]);
+                    const float s1 = (kbase + 32 + i > q_abs) ? -INFINITY : __uint_as_float(u1[i]);
+                    mx = fmaxf(mx, fmaxf(s0, s1));
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaxf(__uint_as_float(u0[i]), __uint_as_float(u1[i])));
             }
             ex_max[sb][hf][r] = mx;
             fa_soft_bar();
@@ -257,12 +268,16 @@ fa_prefill_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 uint32_t w[16];
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
-                    const bool k0 = need_mask && kbase + c * 32 + i > q_abs, k1 = need_mask && kbase + c * 32 + i + 1 > q_abs;
-                    const float p0 = k0 ? 0.f : exp2f(fmaf(__uint_as_float(v[i]), a.scale_log2, -m_new));
-                    const float p1 = k1 ? 0.f : exp2f(fmaf(__uint_as_float(v[i + 1]), a.scale_log2, -m_new));
-                    const uint32_t b0 = f_to_bf16_bits(p0), b1 = f_to_bf16_bits(p1);
-                    lsum += bf16_bits_to_f((uint16_t)b0) + bf16_bits_to_f((uint16_t)b1);  // the sum of what P.V will use
-                    w[i >> 1] = b0 | (b1 << 16);
+                    float p0 = fa_ex2(fmaf(__uint_as_float(v[i]), a.scale_log2, -m_new));
+                    float p1 = fa_ex2(fmaf(__uint_as_float(v[i + 1]), a.scale_log2, -m_new));
+                    if (need_mask) {
+                        p0 = (kbase + c * 32 + i > q_abs) ? 0.f : p0;
+                        p1 = (kbase + c * 32 + i + 1 > q_abs) ? 0.f : p1;
+                    }
+                    const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);     // one two-way convert; lo = p0
+                    const float2 pf = __bfloat1622float2(pb);
+                    lsum += pf.x + pf.y;                                         // the sum of what P.V will use
+                    w[i >> 1] = *reinterpret_cast<const uint32_t*>(&pb);
                 }
                 // swizzled K-major operand layout: 16-byte unit u of row r of a 64-key box sits at unit u ^ (r & 7);
                 // this half's 64 keys are box `hf`
