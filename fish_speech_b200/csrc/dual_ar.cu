@@ -107,6 +107,7 @@ struct fsb_dual_ar {
     int rows_min = 2;                // fewest rows that take the many-row path (every Linear once over all rows on the tcgen05 kernel).
                                      // Measured at 2k context: 2 rows 5.64 ms per step against 7.59 through the GEMV chain's 8-row
                                      // pass, 4 rows 5.71 / 10.6, 8 rows 6.27 / 22.9 - the chain (rows_min = 9) is kept for comparison
+    int chain_attn_tc = 2048;        // kernel chain: caches longer than this use the tensor-core decode attention (0 = never)
     int prefill_rows = 1;            // prompt pieces of <= 2 x max_rows rows on handles with >= 16 rows go through the many-row decode kernels
     int prefill_splitk = 1;          // prompt pass: wo / w2 of a short chunk as split-K pieces + a finish kernel
     int mega_long = 0;               // caches longer than ASP_MAXS x asp_max_keys tokens: 0 = kernel chain (faster as measured: 6.04
@@ -657,6 +658,11 @@ int run_layers(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_i
         a.pf_ptr = w.wo; a.pf_bytes = (size_t)D * H * HD * sizeof(bf16);
         if (fast) {
             CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
+        } else if (h->chain_attn_tc && ak.tc && h->attn_tc && h->kv_max_seq > h->chain_attn_tc) {
+            // long caches (a single request past the frame kernel's 2048 tokens): the tensor-core decode attention of the
+            // many-row path (K / V append as its own launch, then attn_tc_kernel) instead of the CUDA-core kernel
+            a.pf_ptr = nullptr; a.pf_bytes = 0;
+            if (int r = rows_attention(h, s, ak, a, splits, KV, M, pdl)) return r;
         } else {
             a.splits = splits;
             a.fused_append = fused_append ? 1 : 0;
@@ -1152,6 +1158,7 @@ int fsb_dual_ar_set_option(fsb_dual_ar* h, const char* name, int64_t value) {
     else if (n == "mega_long") h->mega_long = (int)value;
     else if (n == "prefill_splitk") h->prefill_splitk = (int)value;
     else if (n == "prefill_rows") h->prefill_rows = (int)value;
+    else if (n == "chain_attn_tc") h->chain_attn_tc = (int)value;
     else if (n == "rows_min") h->rows_min = (int)std::max<int64_t>(1, value);
     else if (n == "attn_trace_point") h->attn_trace_point = (int)value;
     else if (n == "spin_ns") {  // poll back-off of tagged-load spins on the current device
@@ -1572,7 +1579,10 @@ int32_t fsb_dual_ar_launches_per_frame(const fsb_dual_ar* h, int32_t batch) {
     const int passes = (batch + 7) / 8;  // GEMV passes of <= 8 rows
     const int per_layer = 4 * passes + 1;
     const int C = d.num_codebooks;
-    return 1 + d.n_layer * per_layer + passes /*head*/ + 1 /*slow sample*/ + C * d.n_fast_layer * per_layer +
+    AttnKernels ak2{};
+    const bool long_tc = h->chain_attn_tc && pick_attn(d.head_dim, d.n_head / d.n_kv_head, &ak2) && ak2.tc && h->attn_tc &&
+                         h->kv_max_seq > h->chain_attn_tc;  // K/V append as its own launch before the tensor-core attention
+    return 1 + d.n_layer * (per_layer + (long_tc ? 1 : 0)) + passes /*head*/ + 1 /*slow sample*/ + C * d.n_fast_layer * per_layer +
            (C - 1) * (passes + 1) + 1 /*frame end*/;
 }
 
