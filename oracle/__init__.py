@@ -11,6 +11,10 @@ Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s `cpu_baseline` /
 the timed CPU baseline.  Nothing under `fish_speech_b200/` imports it; the
 product path has no CPU fallback.
 
+`oracle/make_ref.py` is the recipe for `oracle/_ref/` (git-ignored, travels to the GPU box): the reference's own ten files for
+the path, copied unmodified from the read-only checkout, so that the CPU arm of `bench.py` times the reference itself
+(`kind: "reference"`); `oracle/refshim/` stands in for the absent descript packages those files import.
+
 Pinning status
 --------------
 * Dual-AR: the reference has no tests / golden vectors, so the
