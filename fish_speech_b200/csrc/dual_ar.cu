@@ -501,10 +501,14 @@ int rows_finish_norm(fsb_dual_ar* h, cudaStream_t s, int M, int N, int K_pending
 }
 
 // slow-AR attention of a many-row step: K/V append + tensor-core decode attention (head_dim 128), else the fused kernel
-int rows_attention(fsb_dual_ar* h, cudaStream_t s, const AttnKernels& ak, AttnArgs a, int splits, int KV, int M, bool pdl) {
+// force_splits > 0: exactly that many splits per (row, head) unit (1 = no split workspace is touched: rows beyond the handle's
+// row capacity, as in a prompt piece on a batch-1 handle)
+int rows_attention(fsb_dual_ar* h, cudaStream_t s, const AttnKernels& ak, AttnArgs a, int splits, int KV, int M, bool pdl,
+                   int force_splits = 0) {
+    if (force_splits > 0) splits = force_splits;
     a.splits = splits;
     if (ak.tc && h->attn_tc) {
-        if (h->attn_splits <= 0) {
+        if (h->attn_splits <= 0 && force_splits <= 0) {
             // a (split, kv head, row) item costs ~2 us of q prep / merge besides its stream, and 3 CTAs fit an SM: about two
             // rounds of CTAs measured best (64 rows x 8 kv heads: 2 splits 11.7 ms per step, 4: 12.1, 8: 13.1)
             const int by_len = std::max(1, (h->max_seq_len + 255) / 256);
@@ -520,7 +524,7 @@ int rows_attention(fsb_dual_ar* h, cudaStream_t s, const AttnKernels& ak, AttnAr
         // units cut finer so that the last round is short
         const int units = M * KV, slots = 3 * h->n_sm;
         int u1 = units, s2 = splits;
-        if (h->attn_splits <= 0 && h->attn_tail && units * splits > slots) {
+        if (h->attn_splits <= 0 && force_splits <= 0 && h->attn_tail && units * splits > slots) {
             u1 = std::min(units, (units * splits / slots) * slots / splits);
             if (u1 < units) s2 = std::max(splits, std::min(h->max_splits, std::min((slots + units - u1 - 1) / (units - u1), std::max(1, (h->max_seq_len + 255) / 256))));
         }
@@ -538,8 +542,12 @@ int rows_attention(fsb_dual_ar* h, cudaStream_t s, const AttnKernels& ak, AttnAr
 // transformer layers over 8 < M <= PREFILL_ROWS decode rows (one row per request, each with its own position and KV
 // slot): every Linear runs ONCE over all rows, so a step streams the weights once however many requests are in flight.
 // Same contract as run_layers (result in h->x / h->xf); scratch = the prompt-pass buffers.
+// `rb`: activation buffers for more rows than the handle's row capacity (a prompt piece: the prompt-pass scratch), with
+// `force_splits` = 1 so that the attention needs no per-row split workspace; tensor-core path only.
+struct RowsBufs { bf16 *xa, *xb, *qkv, *y, *ff; };
 int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16* x_in, const int32_t* pos,
-                    const int32_t* slots, int pos_fixed, const bf16* tail_norm_w, bf16* tail_xn) {
+                    const int32_t* slots, int pos_fixed, const bf16* tail_norm_w, bf16* tail_xn, const RowsBufs* rb = nullptr,
+                    int force_splits = 0) {
     const fsb_dual_ar_desc& d = h->d;
     const int D = d.dim, H = d.n_head, KV = d.n_kv_head, HD = d.head_dim, F = d.ffn, QKV = (H + 2 * KV) * HD;
     AttnKernels ak;
@@ -548,10 +556,14 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
     if (!tc)
         if (int r = ensure_blas(h, s)) return r;
     const std::vector<LayerW>& L = fast ? h->fast : h->slow;
-    bf16* xa = fast ? h->xf : h->x;
-    bf16* xb = fast ? h->xf2 : h->x2;
+    if (rb && !tc) return fail(h, "run_layers_rows: external buffers need the tensor-core path");
+    bf16* xa = rb ? rb->xa : (fast ? h->xf : h->x);
+    bf16* xb = rb ? rb->xb : (fast ? h->xf2 : h->x2);
+    bf16* qkv = rb ? rb->qkv : h->qkv;
+    bf16* yb = rb ? rb->y : h->y;
+    bf16* ffb = rb ? rb->ff : h->ff;
     const int ew_blocks = 2 * h->n_sm;
-    const int splits = splits_for(h, M);
+    const int splits = force_splits > 0 ? force_splits : splits_for(h, M);
     const bf16* cur = x_in;
     for (size_t l = 0; l < L.size(); ++l) {
         const LayerW& w = L[l];
@@ -559,6 +571,7 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
             return fail(h, "unbound weights / kv cache in layer " + std::to_string(l));
         if (!tc) rmsnorm_rows_kernel<<<M, 256, 0, s>>>(cur, w.attn_norm, h->pxn, D, d.norm_eps);
         AttnArgs a = make_attn_args(h, w, fast, pos, slots, pos_fixed);
+        a.qkv = qkv; a.y = yb;
         a.splits = splits;
         a.fused_append = 1;
         if (tc) {
@@ -574,19 +587,19 @@ int run_layers_rows(fsb_dual_ar* h, cudaStream_t s, bool fast, int M, const bf16
             const bool qkv_part = (fast || (ak.tc && h->attn_tc)) && h->qkv_fold && qkv_tiles <= RG_CTAS_PER_SM * h->n_sm &&
                                   QKV % RG_BM == 0 && !(h->rows_narrow && rgn_pick_nw(QKV, h->n_sm));
             a.qkv_part = nullptr;
-            if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, h->qkv, nullptr, qkv_part)) return r;
+            if (int r = rows_linear_tc(h, s, w.wqkv, nullptr, h->pxn, M, QKV, D, RG_EPI_STORE, nullptr, qkv, nullptr, qkv_part)) return r;
             if (qkv_part) {
                 a.qkv_part = h->rg_partial;
                 a.qkv_s = rg_grid(qkv_tiles, D / RG_BK, h->n_sm) / qkv_tiles;
                 a.qkv_bn = rg_bn_for(M);
             }
             if (fast) CK(launch(ak.fast, dim3(KV, M), dim3(ak.threads_fast), 0, s, pdl, a));
-            else if (int r = rows_attention(h, s, ak, a, splits, KV, M, pdl)) return r;
+            else if (int r = rows_attention(h, s, ak, a, splits, KV, M, pdl, force_splits)) return r;
             const bool dfr_o = rows_all_partial_ok(h, D, H * HD), dfr_2 = rows_all_partial_ok(h, D, F);
-            if (int r = rows_linear_tc(h, s, w.wo, nullptr, h->y, M, D, H * HD, RG_EPI_RESIDUAL, cur, xb, nullptr, dfr_o)) return r;
+            if (int r = rows_linear_tc(h, s, w.wo, nullptr, yb, M, D, H * HD, RG_EPI_RESIDUAL, cur, xb, nullptr, dfr_o)) return r;
             if (int r = rows_finish_norm(h, s, M, D, dfr_o ? H * HD : 0, cur, xb, xb, w.ffn_norm, h->pxn)) return r;
-            if (int r = rows_linear_tc(h, s, w.w1, w.w3, h->pxn, M, F, D, RG_EPI_SWIGLU, nullptr, h->ff, h->pf1)) return r;
-            if (int r = rows_linear_tc(h, s, w.w2, nullptr, h->ff, M, D, F, RG_EPI_RESIDUAL, xb, xa, nullptr, dfr_2)) return r;
+            if (int r = rows_linear_tc(h, s, w.w1, w.w3, h->pxn, M, F, D, RG_EPI_SWIGLU, nullptr, ffb, h->pf1)) return r;
+            if (int r = rows_linear_tc(h, s, w.w2, nullptr, ffb, M, D, F, RG_EPI_RESIDUAL, xb, xa, nullptr, dfr_2)) return r;
             const bf16* nw = last ? tail_norm_w : L[l + 1].attn_norm;
             bf16* nx = last ? tail_xn : h->pxn;
             if (int r = rows_finish_norm(h, s, M, D, dfr_2 ? F : 0, xb, xa, xa, nw, nx)) return r;
@@ -1416,11 +1429,24 @@ int fsb_dual_ar_prefill(fsb_dual_ar* h, const int32_t* tokens, int32_t T, int32_
     CK(cudaGetLastError());
     const int C1 = h->d.num_codebooks + 1;
     if (h->prefill_gemm == 1 && (rg_get_encode() == nullptr || h->d.dim % 8 || h->d.ffn % 8)) h->prefill_gemm = 0;  // no tensor-map encoder: decode kernels
-    // A short prompt piece on a handle with many rows (the scheduler's: the own columns behind a shared voice prefix): the
-    // many-row decode kernels take it in passes of max_rows rows - rows of one KV slot at consecutive positions; the K / V
-    // append is its own launch before the tensor-core attention, so a row sees the keys of the rows before it.  A pass streams
-    // the weights once over all SMs (~75 us per layer), the 128-row tiles of the prompt-pass GEMM need ~190 us per layer
-    // however few rows there are.
+    // A short prompt piece (<= 128 columns: the own columns behind a resident prefix, a short prompt) goes through the many-row
+    // decode kernels in ONE pass: rows of one KV slot at consecutive positions; the K / V append is its own launch before the
+    // tensor-core attention, so a row sees the keys of the rows before it.  A pass streams the weights once over all SMs (~75 us
+    // per layer), the 128-row tiles of the prompt-pass GEMM need ~190 us per layer however few rows there are.  The rows live in
+    // the prompt-pass scratch (the handle's own activation and split-attention buffers hold max_rows rows only: one attention
+    // item per (row, head), no split workspace).
+    if (h->prefill_gemm == 1 && h->prefill_rows && T >= 2 && T <= 128) {
+        AttnKernels ak;
+        if (pick_attn(h->d.head_dim, h->d.n_head / h->d.n_kv_head, &ak) && ak.tc && h->attn_tc && rows_tc_layers(h, T)) {
+            if (int r = check_bound(h)) return r;
+            EmbedArgs e = make_embed_args(h, tokens);
+            e.x = h->pxa;
+            CK(launch(embed_kernel, dim3(T), dim3(256), 0, s, false, e));
+            const RowsBufs rb{h->ptmp, h->pxb, h->pqkv, h->py, h->pf3};
+            return run_layers_rows(h, s, false, T, h->pxa, h->pf_pos, h->pf_slot, -1, nullptr, nullptr, &rb, 1);
+        }
+    }
+    // ... and a handle with many rows (a scheduler's) takes up to 2 x max_rows columns in passes of max_rows rows on its own buffers
     if (h->prefill_gemm == 1 && h->prefill_rows && h->d.max_rows >= 16 && T <= 2 * h->d.max_rows) {
         const int Mr = std::min<int>(T, h->d.max_rows);
         AttnKernels ak;

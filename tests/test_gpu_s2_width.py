@@ -285,6 +285,36 @@ def test_short_prompt_pieces_through_the_many_row_kernels_vs_prompt_pass_and_ora
     m.set_option("prefill_rows", 1)
 
 
+def test_short_prompt_in_one_many_row_pass_on_a_batch_1_handle(s2w):
+    """A prompt piece of <= 128 columns goes through the many-row decode kernels in one pass on ANY handle (rows in the
+    prompt-pass scratch, one attention item per row and head): first-frame logits against the oracle and against the
+    prompt-pass kernels (prefill_rows = 0) for 2 .. 128 columns from position 0, and for 50 new columns behind 300 resident
+    ones (the prefix-cache case)."""
+    cfg, sd, m, om = s2w
+    try:
+        for T, resident in ((3, 0), (13, 0), (100, 0), (129, 0), (351, 300)):
+            seq = R.make_prompt(cfg, T, seed=60 + T, voice_span=T // 3)
+            ref, _ = om.forward_generate(seq[None], torch.arange(T))
+            outs = {}
+            for rows in (1, 0):
+                m.set_option("prefill_rows", rows)
+                m.prefix_cache = False
+                if resident:
+                    m.prefill(seq[:, :resident].cuda(), 0, 0)
+                    m.prefill(seq[:, resident: T - 1].cuda(), resident, 0)
+                    out = m.forward_generate(seq[None, :, -1:].cuda(), torch.tensor([T - 1]))
+                else:
+                    out = m.forward_generate(seq[None].cuda(), torch.arange(T))
+                outs[rows] = out.logits[0, 0].float().cpu()
+            _check(f"short prompt in one many-row pass T={T} (resident {resident})", outs[1], ref[0, -1])
+            mabs, _, _ = err_stats(outs[1], outs[0])
+            print(f"[parity] one many-row pass vs prompt-pass kernels T={T}: max-abs {mabs:.4f}")
+            assert mabs <= _abs_tol(ref[0, -1])
+    finally:
+        m.set_option("prefill_rows", 1)
+        m.prefix_cache = True
+
+
 def test_flash_attention_prompt_pass_vs_per_row_attention_and_oracle(s2w):
     """fa_prefill_kernel (tcgen05 causal flash attention, option prefill_fa = 1, the default at head_dim 128) against the
     per-row decode attention (prefill_fa = 0) and the oracle: lengths around the 128-row / 128-key block edges, and a prompt
