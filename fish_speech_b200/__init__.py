@@ -7,10 +7,10 @@ CUDA; constructing a model does, and raises if the extension or a B200 is missin
 from .dual_ar import (DualARConfig, DualARTransformerB200, decode_n_tokens, decode_one_token_ar, generate,  # noqa: F401
                       init_model_from_state_dict, make_semantic_logit_bias, s2_pro_config)
 
-from .dac import DACB200, DACConfig  # noqa: F401
+from .dac import DACB200, DACConfig, DACStream  # noqa: F401
 from . import partition  # noqa: F401
 
-__all__ = ["DACB200", "DACConfig", "partition", "DualARConfig", "DualARTransformerB200", "decode_one_token_ar", "decode_n_tokens", "generate",
+__all__ = ["DACB200", "DACConfig", "DACStream", "partition", "DualARConfig", "DualARTransformerB200", "decode_one_token_ar", "decode_n_tokens", "generate",
            "init_model_from_state_dict", "make_semantic_logit_bias", "s2_pro_config"]
 
 from .checkpoint import init_model, load_codec, load_config, load_weights  # noqa: E402,F401

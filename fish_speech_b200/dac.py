@@ -354,6 +354,10 @@ class DACB200:
             ctx = -(-ctx // f)                                 # transposed conv, kernel = stride
         return ctx + c.tf_layers * (c.tf_window - 1)
 
+    def stream(self, batch: int = 1, halo: Optional[int] = None) -> "DACStream":
+        """A DACStream over this engine (audio out while code frames still arrive)."""
+        return DACStream(self, batch, halo)
+
     def _ensure_rope(self, positions: int):
         c = self.config
         if self.weights["tf.rope"].shape[0] >= positions:
@@ -364,3 +368,56 @@ class DACB200:
         self.weights["tf.rope"] = t
         self._ck(self.lib.fsb_dac_bind_weight(self._h, b"tf.rope", t.data_ptr(), t.numel()))
 
+
+
+class DACStream:
+    """Waveform out as code frames arrive: `push(codes[B, 1+n_codebooks, n])` returns the `hop * n` new samples of every clip.
+
+    The reference's engine decodes a whole segment when its last token is there (inference_engine/__init__.py:104-126 feeding
+    vq_manager.py:20-33); its decode side is causal with a finite reach (DACB200.context_frames), so the samples of new frames
+    only need the last `halo` code frames again.  With halo = context_frames() (the default) the stream equals the one-pass
+    decode of the whole clip bit for bit; a shorter halo trades exactness of the first samples of each push for less
+    recomputation (the window transformer's reach, layers x (window - 1) frames, is the long part)."""
+
+    def __init__(self, dac: "DACB200", batch: int = 1, halo: Optional[int] = None):
+        self.dac = dac
+        self.batch = int(batch)
+        if self.batch < 1 or self.batch > dac.max_batch:
+            raise ValueError(f"batch={batch} outside 1..max_batch={dac.max_batch}")
+        self.halo = dac.context_frames() if halo is None else int(halo)
+        if self.halo < 0 or self.halo >= dac.max_frames:
+            raise ValueError(f"halo={self.halo} needs 0 <= halo < max_frames={dac.max_frames}")
+        self.frames = 0                                        # code frames taken so far
+        self._tail = torch.empty((self.batch, dac.config.n_codebooks + 1, 0), dtype=torch.int64, device=dac.device)
+
+    @torch.inference_mode()
+    def push(self, codes: Tensor) -> Tensor:
+        d = self.dac
+        if codes.dim() != 3 or codes.shape[0] != self.batch or codes.shape[1] != d.config.n_codebooks + 1:
+            raise ValueError(f"expected [{self.batch}, {d.config.n_codebooks + 1}, n] codes, got {tuple(codes.shape)}")
+        codes = codes.to(device=d.device, dtype=torch.int64)
+        n, hop = codes.shape[2], d.hop_length
+        wav = torch.empty((self.batch, 1, hop * n), dtype=torch.float32, device=d.device)
+        st = torch.cuda.current_stream().cuda_stream
+        done = 0
+        while done < n:
+            keep = self._tail.shape[2]
+            take = min(n - done, d.max_frames - keep)
+            piece = torch.cat([self._tail, codes[:, :, done: done + take]], dim=2).contiguous()
+            a = self.frames - keep                             # absolute index of the piece's first frame
+            d._ensure_rope(self.frames + take)
+            out = torch.empty((self.batch, 1, hop * (keep + take)), dtype=torch.float32, device=d.device)
+            try:
+                d.set_option("pos_offset", a)
+                d._ck(d.lib.fsb_dac_decode(d._h, piece.data_ptr(), self.batch, keep + take, out.data_ptr(), st))
+            finally:
+                d.set_option("pos_offset", 0)
+            wav[:, :, hop * done: hop * (done + take)] = out[:, :, hop * keep:]
+            self._tail = piece[:, :, max(0, keep + take - self.halo):]
+            self.frames += take
+            done += take
+        return wav
+
+    def reset(self):
+        self.frames = 0
+        self._tail = self._tail[:, :, :0]

@@ -137,6 +137,46 @@ def test_clip_longer_than_the_workspace_decodes_in_pieces_bit_identically():
     assert int(wild[0, 1, 77]) == c.codebook_size - 1
 
 
+def test_stream_of_pushes_equals_the_one_pass_decode():
+    """DACStream: code frames pushed in ragged portions (1 frame, more than the workspace less the halo, ...) give the one-pass
+    waveform bit for bit with the default halo (= context_frames); a zero halo still has the right shape and equals the
+    one-pass decode on the first push only."""
+    c = D.small_config()
+    sd = D.make_state_dict(c, seed=9)
+    codes = D.make_codes(c, 2, 100).cuda()
+    big = _model(c, sd, max_batch=2, max_frames=128)
+    want = big.from_indices(codes.clone())
+    small = _model(c, sd, max_batch=2, max_frames=40)
+    hop = small.hop_length
+    for tc in (1, 0):
+        big.set_option("tc", tc)
+        small.set_option("tc", tc)
+        want = big.from_indices(codes.clone())
+        s = small.stream(batch=2)
+        assert s.halo == 24
+        got, t = [], 0
+        for n in (1, 7, 30, 2, 45, 15):
+            got.append(s.push(codes[:, :, t: t + n].clone()))
+            assert got[-1].shape == (2, 1, hop * n)
+            t += n
+        assert t == 100 and s.frames == 100
+        got = torch.cat(got, dim=2)
+        assert torch.equal(got, want), float((got - want).abs().max())
+    s.reset()
+    assert torch.equal(s.push(codes[:, :, :20].clone()), want[:, :, : hop * 20])
+    z = small.stream(batch=2, halo=0)
+    a = z.push(codes[:, :, :20].clone())
+    b = z.push(codes[:, :, 20:40].clone())
+    assert torch.equal(a, want[:, :, : hop * 20]) and b.shape == a.shape and not torch.equal(b, want[:, :, hop * 20: hop * 40])
+    assert torch.equal(small.from_indices(codes[:, :, :30].clone()), want[:, :, : hop * 30])   # offset left at 0
+    with pytest.raises(ValueError):
+        small.stream(batch=3)
+    with pytest.raises(ValueError):
+        small.stream(halo=40)
+    with pytest.raises(ValueError):
+        s.push(codes[:1, :, :4])
+
+
 def test_tiled_window_attention_and_output_conv_match_the_per_query_kernels():
     """Option tiled_small: the window attention stages a query tile's keys / values in shared memory (same arithmetic, same
     order: bit-identical up to the output conv), the output conv sums its taps per thread instead of per warp (fp32 sums in
