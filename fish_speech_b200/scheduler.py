@@ -32,7 +32,7 @@ import threading
 import traceback
 from collections import deque
 from dataclasses import dataclass, field
-from typing import Any, Deque, Dict, List, Literal, Optional, Tuple, Union
+from typing import Any, Callable, Deque, Dict, List, Literal, Optional, Tuple, Union
 
 import torch
 from torch import Tensor
@@ -42,7 +42,7 @@ from .dual_ar import _as_bf16_float, make_semantic_logit_bias
 
 @dataclass
 class GenerateResponse:            # inference.py:52-56
-    action: Literal["sample", "next"]
+    action: Literal["sample", "next", "partial"]   # "partial" is this scheduler's addition: see ContinuousBatcher.on_partial
     codes: Optional[Tensor] = None
     text: Optional[str] = None
 
@@ -66,6 +66,7 @@ class _Row:
     budget: int                    # frames this request may still produce (generate(): max_new_tokens, clipped to the cache)
     frames: List[Tensor] = field(default_factory=list)   # [n, C+1] int32 pieces, on the device
     produced: int = 0              # frames kept so far: the row's next input position is prompt_len - 1 + produced
+    hold: Optional[Tensor] = None  # streaming: the newest frame, held back until another one follows (the last is dropped)
 
 
 class ContinuousBatcher:
@@ -107,6 +108,10 @@ class ContinuousBatcher:
         self.steps = 0
         self.frames_run = 0                         # row-frames computed, idle rows included
         self.frames_kept = 0                        # frames delivered to requests
+        # streaming: a request with request["stream"] truthy gets its code frames as they are produced, chunk by chunk:
+        # on_partial(request, codes [C, n]) is called from step(); the portions concatenated are exactly the final codes (the
+        # newest frame is held back each time, because the last frame produced is not part of the result, inference.py:708)
+        self.on_partial: Optional[Callable[[GenerateRequest, Tensor], None]] = None
 
     # ------------------------------------------------------------------ queueing
     def submit(self, item: GenerateRequest):
@@ -219,6 +224,11 @@ class ContinuousBatcher:
             r.frames.append(toks[:take, row].clone())
             r.budget -= take
             r.produced += take
+            if self.on_partial is not None and r.item.request.get("stream"):
+                new = r.frames[-1] if r.hold is None else torch.cat([r.hold, r.frames[-1]], 0)
+                r.hold = new[-1:]
+                if new.shape[0] > 1:
+                    self.on_partial(r.item, new[:-1, 1:].t().contiguous())
             if ended or r.budget <= 0:
                 seq = torch.cat(r.frames, 0)                     # [n_total, C+1]
                 codes = seq[:-1, 1:].t().contiguous()            # y[1:, prompt_length:-1]
@@ -255,6 +265,10 @@ def _deliver(item: GenerateRequest, result):
     item.response_queue.put(WrappedGenerateResponse(status="success", response=GenerateResponse(action="next")))
 
 
+def _deliver_partial(item: GenerateRequest, codes: Tensor):
+    item.response_queue.put(WrappedGenerateResponse(status="success", response=GenerateResponse(action="partial", codes=codes)))
+
+
 def launch_thread_safe_queue(checkpoint_path=None, device="cuda", precision=torch.bfloat16, compile: bool = False, *,
                              model=None, max_rows: int = 8, chunk_frames: int = 8, max_length: Optional[int] = None) -> queue.Queue:
     """inference.py:748-799 with continuous batching: returns the input queue; put `GenerateRequest`s on it, `None` to stop
@@ -273,6 +287,7 @@ def launch_thread_safe_queue(checkpoint_path=None, device="cuda", precision=torc
             if dev is not None and torch.device(dev).type == "cuda":
                 torch.cuda.set_device(dev)
             batcher = ContinuousBatcher(m, max_rows=min(max_rows, m.max_rows), chunk_frames=chunk_frames)
+            batcher.on_partial = _deliver_partial
         except BaseException as e:  # noqa: BLE001
             init_error.append(e)
             init_event.set()

@@ -240,3 +240,35 @@ def test_queue_protocol_of_the_worker_thread():
     err = items[-1].response_queue.get(timeout=30)
     assert err.status == "error" and isinstance(err.response, ValueError)
     q_in.put(None)
+
+
+def test_streamed_portions_add_up_to_the_final_codes():
+    """request["stream"]: code frames arrive chunk by chunk as "partial" responses before the usual "sample" / "next" pair; the
+    portions concatenated equal the final codes (the newest frame is held back: the last one produced is not part of the
+    result), requests without the flag see no partial responses."""
+    m = FakeModel(max_rows=2)
+    q_in = launch_thread_safe_queue(model=m, max_rows=2, chunk_frames=3)
+    items = [req(prompt(6, 40), stream=True), req(prompt(7, 41)), req(prompt(5, 42), max_new=5, stream=True),
+             req(prompt(5, 43), max_new=1, stream=True)]
+    for it in items:
+        q_in.put(it)
+    for it in items:
+        got = []
+        while True:
+            r = it.response_queue.get(timeout=30)
+            assert r.status == "success"
+            got.append(r.response)
+            if r.response.action == "next":
+                break
+        want = expected(it.request["prompt"], it.request["max_new_tokens"])
+        assert [g.action for g in got[-2:]] == ["sample", "next"] and torch.equal(got[-2].codes, want)
+        parts = [g.codes for g in got[:-2]]
+        assert all(g.action == "partial" for g in got[:-2])
+        if it.request.get("stream") and want.shape[1] > 0:
+            assert len(parts) >= 1 and all(p.shape[0] == C and p.shape[1] >= 1 for p in parts)
+            assert torch.equal(torch.cat(parts, 1), want)
+            if want.shape[1] > 3:
+                assert len(parts) > 1                         # really chunk by chunk, not once at the end
+        else:
+            assert parts == []
+    q_in.put(None)
