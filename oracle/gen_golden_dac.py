@@ -14,7 +14,7 @@ from oracle import dac_ref as D
 from oracle.gen_golden import GOLD, import_reference
 
 
-def build_reference_dac(c: D.DACConfig, importer=import_reference):
+def build_reference_dac(c: D.DACConfig, importer=import_reference, encode_side: bool = False):
     """Hand-instantiate what configs/modded_dac_vq.yaml describes (hydra is absent).  `importer` puts the reference package on
     the path: the read-only checkout (default) or its vendored copy (oracle.make_ref.import_vendored)."""
     importer()
@@ -26,18 +26,49 @@ def build_reference_dac(c: D.DACConfig, importer=import_reference):
                          rope_base=c.tf_rope_base, norm_eps=c.tf_norm_eps, dropout_rate=0.1,
                          attn_dropout_rate=0.1, channels_first=True)
     post = M.WindowLimitedTransformer(causal=True, window_size=c.tf_window, input_dim=c.latent_dim, config=tf_cfg)
+    pre = None
+    if encode_side:   # the yaml's `pre_module: *transformer_module` is instantiated on its own: same shape, own weights
+        pre = M.WindowLimitedTransformer(causal=True, window_size=c.tf_window, input_dim=c.latent_dim, config=tf_cfg)
     q = rvq.DownsampleResidualVectorQuantize(
         input_dim=c.latent_dim, n_codebooks=c.n_codebooks, codebook_size=c.codebook_size,
         codebook_dim=c.codebook_dim, quantizer_dropout=0.5, downsample_factor=list(c.upsample_factors),
-        post_module=post, pre_module=None, semantic_codebook_size=c.semantic_codebook_size)
+        post_module=post, pre_module=pre, semantic_codebook_size=c.semantic_codebook_size)
     general = partial(M.ModelArgs, block_size=8192, n_local_heads=-1, head_dim=64, rope_base=10000,
                       norm_eps=1e-5, dropout_rate=0.1, attn_dropout_rate=0.1, channels_first=True)
-    # encoder side kept minimal (unused on decode): no transformer layers there
-    dac = M.DAC(sample_rate=c.sample_rate, encoder_dim=c.latent_dim // 16, encoder_rates=[2, 4, 8, 8],
+    if encode_side and c.encoder_tf_window != 512:
+        general.window_size = c.encoder_tf_window    # EncoderBlock reads it with getattr(..., "window_size", 512) (:642)
+    # decode-only fixtures keep the encoder minimal (no transformer layers there); the decoder's transformer slot is unused by
+    # the reference itself (modded_dac.py:741-742), [4, 0, 0, 0] in the yaml or not
+    dac = M.DAC(sample_rate=c.sample_rate, encoder_dim=c.encoder_dim if encode_side else c.latent_dim // 16,
+                encoder_rates=list(c.encoder_rates) if encode_side else [2, 4, 8, 8],
                 decoder_dim=c.decoder_dim, decoder_rates=list(c.decoder_rates),
-                encoder_transformer_layers=[0, 0, 0, 0], decoder_transformer_layers=[0, 0, 0, 0],
+                encoder_transformer_layers=list(c.encoder_tf_layers) if encode_side else [0, 0, 0, 0],
+                decoder_transformer_layers=[0, 0, 0, 0],
                 transformer_general_config=general, quantizer=q)
     return dac.eval()
+
+
+def golden_encode(name: str, c: D.DACConfig, B: int, n_samples: int, seed: int = 0):
+    """DAC.encode of the reference classes on a seeded waveform against oracle.dac_ref.encode: same codes, bit-identical
+    latents in front of the codebooks."""
+    sd = {**D.make_state_dict(c, seed=seed), **D.make_encode_state_dict(c, seed=seed)}
+    audio = D.make_audio(c, B, n_samples)
+    ref = build_reference_dac(c, encode_side=True)
+    missing, unexpected = ref.load_state_dict(sd, strict=False)
+    assert not unexpected and not missing, (missing, unexpected)
+    with torch.inference_mode():
+        codes_ref, lens_ref = ref.encode(audio.clone())
+        z_ref = ref.quantizer.pre_module(ref.quantizer.downsample(ref.encoder(
+            torch.nn.functional.pad(audio, (0, -n_samples % c.hop)))))
+    stages = []
+    codes, lens = D.encode(c, {k: v.clone().requires_grad_(True) for k, v in sd.items()}, audio.clone(), stages)
+    print(f"[golden] {name}: latents max abs diff {float((stages[-1] - z_ref).abs().max()):.2e}, "
+          f"codes equal {float((codes == codes_ref).float().mean()):.4f}")
+    assert torch.equal(codes, codes_ref) and torch.equal(lens, lens_ref), name
+    plain, _ = D.encode(c, sd, audio.clone())
+    print(f"[golden] {name}: oracle(plain tensors) codes equal to reference: {float((plain == codes_ref).float().mean()):.4f}")
+    torch.save({"cfg": c.__dict__, "seed": seed, "audio": audio, "codes": codes_ref.clone(), "lens": lens_ref.clone(),
+                "latent_std": float(z_ref.std())}, GOLD / f"{name}.pt")
 
 
 def golden(name: str, c: D.DACConfig, B: int, T: int, seed: int = 0, oob_codes: bool = False):
@@ -73,6 +104,8 @@ def main():
     torch.manual_seed(0)
     golden("dac_small", D.small_config(), B=2, T=24)
     golden("dac_full_T12", D.DACConfig(), B=2, T=12, oob_codes=True)
+    golden_encode("dac_encode_small", D.small_config(), B=2, n_samples=2048 * 9 - 700)
+    golden_encode("dac_encode_full", D.DACConfig(), B=1, n_samples=2048 * 6 - 100)
 
 
 if __name__ == "__main__":

@@ -1,5 +1,6 @@
-"""Restatement of descript-audio-codec 1.0.0 `dac/nn/quantize.py`, decode side only
-(`from_codes`) — TEST INFRASTRUCTURE, see ../../README.md."""
+"""Restatement of descript-audio-codec 1.0.0 `dac/nn/quantize.py`: `from_codes` (decode side) and the eval-mode `forward`
+(encode side: project, nearest codebook entry by cosine distance, project back, subtract) — TEST INFRASTRUCTURE, see
+../../README.md."""
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -15,6 +16,26 @@ class VectorQuantize(nn.Module):
         self.in_proj = WNConv1d(input_dim, codebook_dim, kernel_size=1)
         self.out_proj = WNConv1d(codebook_dim, input_dim, kernel_size=1)
         self.codebook = nn.Embedding(codebook_size, codebook_dim)
+
+    def forward(self, z):
+        z_e = self.in_proj(z)                                   # [B, codebook_dim, T]
+        z_q, indices = self.decode_latents(z_e)
+        commitment_loss = F.mse_loss(z_e, z_q.detach(), reduction="none").mean([1, 2])
+        codebook_loss = F.mse_loss(z_q, z_e.detach(), reduction="none").mean([1, 2])
+        z_q = z_e + (z_q - z_e).detach()                        # straight-through estimator (kept: it rounds)
+        z_q = self.out_proj(z_q)
+        return z_q, commitment_loss, codebook_loss, indices, z_e
+
+    def decode_latents(self, latents):
+        B, D, T = latents.shape
+        encodings = latents.permute(0, 2, 1).reshape(B * T, D)
+        codebook = self.codebook.weight
+        encodings = F.normalize(encodings)
+        codebook = F.normalize(codebook)
+        dist = (encodings.pow(2).sum(1, keepdim=True) - 2 * encodings @ codebook.t()
+                + codebook.pow(2).sum(1, keepdim=True).t())
+        indices = (-dist).max(1)[1].reshape(B, T)
+        return self.decode_code(indices), indices
 
     def embed_code(self, embed_id):
         return F.embedding(embed_id, self.codebook.weight)
@@ -35,6 +56,29 @@ class ResidualVectorQuantize(nn.Module):
         self.quantizers = nn.ModuleList(
             [VectorQuantize(input_dim, codebook_size, codebook_dim[i]) for i in range(n_codebooks)])
         self.quantizer_dropout = quantizer_dropout
+
+    def forward(self, z, n_quantizers: int = None):
+        assert not self.training, "the shim restates the eval-mode forward only (no quantizer dropout)"
+        z_q = 0
+        residual = z
+        commitment_loss = 0
+        codebook_loss = 0
+        codebook_indices = []
+        latents = []
+        if n_quantizers is None:
+            n_quantizers = self.n_codebooks
+        for i, quantizer in enumerate(self.quantizers):
+            if i >= n_quantizers:
+                break
+            z_q_i, commitment_loss_i, codebook_loss_i, indices_i, z_e_i = quantizer(residual)
+            mask = torch.full((z.shape[0],), fill_value=i, device=z.device) < n_quantizers
+            z_q = z_q + z_q_i * mask[:, None, None]
+            residual = residual - z_q_i
+            commitment_loss = commitment_loss + (commitment_loss_i * mask).mean()
+            codebook_loss = codebook_loss + (codebook_loss_i * mask).mean()
+            codebook_indices.append(indices_i)
+            latents.append(z_e_i)
+        return z_q, torch.stack(codebook_indices, dim=1), torch.cat(latents, dim=1), commitment_loss, codebook_loss
 
     def from_codes(self, codes: torch.Tensor):
         z_q = 0.0

@@ -127,6 +127,58 @@ def test_rvq_from_codes_vs_hf_port():
     assert float((got - want).abs().max()) < 1e-5
 
 
+def test_oracle_dac_encode_golden():
+    """DAC.encode of the reference classes (fixture: oracle/gen_golden_dac.py golden_encode) against the restatement: same
+    codes for every frame and codebook, lengths included; the waveform is ragged (not a whole number of code frames)."""
+    g = load_golden("dac_encode_small")
+    c = D.DACConfig(**g["cfg"])
+    sd = {**D.make_state_dict(c, seed=g["seed"]), **D.make_encode_state_dict(c, seed=g["seed"])}
+    assert g["audio"].shape[-1] % c.hop != 0
+    codes, lens = D.encode(c, sd, g["audio"].clone())
+    assert codes.dtype == torch.int64 and codes.shape == g["codes"].shape and torch.equal(lens, g["lens"])
+    assert float((codes == g["codes"]).float().mean()) >= 0.995      # plain tensors take another fp32 GEMM path (see above)
+    assert int(codes[:, 0].max()) < c.semantic_codebook_size and int(codes[:, 1:].max()) < c.codebook_size
+
+
+def test_vq_encode_step_vs_hf_port():
+    """descript VectorQuantize.forward (absent dependency, restated in oracle/dac_ref.py:vq_step) against the transformers
+    port of the same class: in_proj, nearest entry between L2-normalised vectors, straight-through sum, out_proj; chained
+    over the codebooks on the residual like ResidualVectorQuantize.forward."""
+    try:
+        from transformers.models.dac.configuration_dac import DacConfig
+        from transformers.models.dac.modeling_dac import DacResidualVectorQuantizer
+    except Exception:
+        pytest.skip("transformers DAC port not importable")
+    c = D.small_config()
+    torch.manual_seed(2)
+    q = DacResidualVectorQuantizer(DacConfig(n_codebooks=4, codebook_size=c.codebook_size, codebook_dim=c.codebook_dim,
+                                             hidden_size=c.latent_dim)).eval()
+    for prm in q.parameters():
+        torch.nn.init.normal_(prm, std=0.3)
+    sd = {}
+    for i, vq in enumerate(q.quantizers):
+        p = f"q.{i}."
+        sd[p + "codebook.weight"] = vq.codebook.weight.detach()
+        for proj, m in (("in_proj", vq.in_proj), ("out_proj", vq.out_proj)):
+            w = m.weight.detach()
+            sd[p + proj + ".weight_v"] = w                        # weight_norm(v, g = ||v||) is v itself
+            sd[p + proj + ".weight_g"] = w.flatten(1).norm(dim=1).view(-1, 1, 1)
+            sd[p + proj + ".bias"] = m.bias.detach()
+    z = torch.randn(2, c.latent_dim, 23)
+    with torch.no_grad():
+        out = q(z)
+    want_codes = out[1] if isinstance(out, tuple) else out.audio_codes
+    want_z = out[0] if isinstance(out, tuple) else out.quantized_representation
+    residual, total, codes = z, 0.0, []
+    for i in range(4):
+        z_q, idx = D.vq_step(sd, f"q.{i}.", residual)
+        residual = residual - z_q
+        total = total + z_q
+        codes.append(idx)
+    assert torch.equal(torch.stack(codes, 1), want_codes)
+    assert float((total - want_z).abs().max()) < 1e-4
+
+
 def test_dac_causality_property():
     """rvq.py:374-399 self-check: decoding a prefix equals the prefix of the decode (all convs causal)."""
     c = D.small_config()
