@@ -85,6 +85,7 @@ DAC_EXPORTS = {
     "fsb_dac_last_error": (C.c_char_p, [C.c_void_p]),
     "fsb_dac_bind_weight": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int64]),
     "fsb_dac_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "fsb_dac_encode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
     "fsb_dac_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "fsb_dac_stage": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "fsb_tc_conv": (C.c_int, [C.POINTER(TcConvArgs), C.c_void_p]),

@@ -29,6 +29,9 @@ struct fsb_dac {
     int staged_epi = 1;   // tcv_kernel: 16-bit-only epilogues (the decoder's convs) through shared memory (coalesced residual loads / stores)
     int tiled_small = 1;  // window attention and the output conv of the tcgen05 pipeline as shared-memory-tiled kernels (0: per-query / per-sample)
     int force_simt = 0;  // tcgen05 pipeline with every GEMM on the CUDA-core twin kernel (cross-check)
+    // encode side (DAC.encode): set through fsb_dac_set_option ("enc_dim", "enc_n_rates", "enc_rate0..3", "enc_tf0..3",
+    // "enc_window", "enc_head_dim"); 0 = not configured
+    int enc_dim = 0, enc_n = 0, enc_rate[4] = {0, 0, 0, 0}, enc_tf[4] = {0, 0, 0, 0}, enc_window = 512, enc_hd = 64;
     int n_sm = 148;
     std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, int>, CUtensorMap> maps;
     std::string err;
@@ -72,6 +75,7 @@ struct Runner {
     cudaStream_t s;
     int B;
     int rc = 0;
+    bool exact = false;   // fp32 CUDA-core GEMMs whatever "tf32" says (the encode side: codes are arg-max results)
     const float* W(const std::string& n) {
         auto it = h->w.find(n);
         if (it == h->w.end()) { if (!rc) rc = dfail(h, "weight not bound: " + n); return nullptr; }
@@ -84,7 +88,7 @@ struct Runner {
         a.alpha = alpha; a.res = res; a.gamma = gamma;
         a.B = B; a.T = T; a.Cin = Cin; a.N = N; a.taps = taps; a.dil = dil; a.bias_mod = bias_mod > 0 ? bias_mod : N; a.epi = epi;
         if (rc) return;
-        if (h->tf32 && (taps - 1) * dil <= CM_HALO && Cin % 4 == 0 && N % 4 == 0) {
+        if (h->tf32 && !exact && (taps - 1) * dil <= CM_HALO && Cin % 4 == 0 && N % 4 == 0) {
             if (N % 96 == 0 && N % 128 != 0) {
                 dim3 grid((T + CM_BM - 1) / CM_BM, N / 96, B);
                 conv_mma_kernel<3><<<grid, 256, CM_SMEM, s>>>(a);
@@ -211,6 +215,12 @@ int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
     else if (n == "tiled_small") h->tiled_small = (int)value;
     else if (n == "staged_epi") h->staged_epi = (int)value;
     else if (n == "pos_offset") { if (value < 0) return dfail(h, "pos_offset < 0"); h->pos_offset = (int)value; }
+    else if (n == "enc_dim") h->enc_dim = (int)value;
+    else if (n == "enc_n_rates") { if (value < 1 || value > 4) return dfail(h, "enc_n_rates must be 1..4"); h->enc_n = (int)value; }
+    else if (n.size() == 9 && n.compare(0, 8, "enc_rate") == 0 && n[8] >= '0' && n[8] <= '3') h->enc_rate[n[8] - '0'] = (int)value;
+    else if (n.size() == 7 && n.compare(0, 6, "enc_tf") == 0 && n[6] >= '0' && n[6] <= '3') h->enc_tf[n[6] - '0'] = (int)value;
+    else if (n == "enc_window") h->enc_window = (int)value;
+    else if (n == "enc_head_dim") h->enc_hd = (int)value;
     else return dfail(h, "unknown option " + n);
     return 0;
 }
@@ -485,3 +495,161 @@ int decode_tc(fsb_dac* h, void* codes, int B, int T, float* wav, cudaStream_t s)
 }
 
 }  // namespace
+
+// =============================================================================================== encode side
+// DAC.encode (modded_dac.py:874-923): waveform -> codes, for the reference voice of a cloning request (runs once per voice, in
+// front of the hot path).  Everything in fp32 on the CUDA-core kernels of the decode side's parity anchor: the result is a set of
+// arg-max decisions, and 16-bit or TF32 operands would move the near-ties.  Strided convs (EncoderBlock's kernel 2s / stride s,
+// the quantizer's kernel = stride) need no kernel of their own in a channels-last layout: s consecutive rows of [len][C] ARE one
+// row of [len / s][s * C], so they are 2-tap / 1-tap causal convs over that view with the weights regrouped at pack time.
+namespace {
+
+// x in bx, temporaries ba / bb / bc; the normed output lands in ba (Transformer.forward, modded_dac.py:145-171)
+int window_transformer32(Runner& r, const std::string& pre, int layers, int D, int H, int HD, int F, int window, const float* rope,
+                         int T, float eps, float* bx, float* ba, float* bb, float* bc) {
+    fsb_dac* h = r.h;
+    cudaStream_t s = r.s;
+    const int B = r.B;
+    const long long rows = (long long)B * T;
+    const int nwb = (int)((rows * 32 + 255) / 256);
+    for (int l = 0; l < layers; ++l) {
+        const std::string p = pre + std::to_string(l) + ".";
+        const float *an = r.W(p + "attn_norm"), *fn = r.W(p + "ffn_norm"), *g1 = r.W(p + "gamma1"), *g2 = r.W(p + "gamma2");
+        if (r.rc) return r.rc;
+        rmsnorm_rows_kernel<<<nwb, 256, 0, s>>>(bx, an, ba, rows, D, eps);
+        r.conv(ba, bb, T, D, 3 * H * HD, 1, 1, p + "wqkv", "", 0, nullptr, nullptr, nullptr, DEPI_NONE);
+        {
+            const long long n = rows * 2 * H * (HD / 2);
+            rope_qk_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(bb, rope, B, T, H, HD, 0);
+            dim3 grid((T + 3) / 4, H, B);
+            const float scale = 1.f / sqrtf((float)HD);
+            if (HD == 64 && window <= 128) window_attn_kernel<64, 4><<<grid, 128, 0, s>>>(bb, ba, B, T, H, window, scale);
+            else if (HD == 64) window_attn_kernel<64, 16><<<grid, 128, 0, s>>>(bb, ba, B, T, H, window, scale);
+            else if (window <= 128) window_attn_kernel<32, 4><<<grid, 128, 0, s>>>(bb, ba, B, T, H, window, scale);
+            else window_attn_kernel<32, 16><<<grid, 128, 0, s>>>(bb, ba, B, T, H, window, scale);
+        }
+        r.conv(ba, bc, T, H * HD, D, 1, 1, p + "wo", "", 0, nullptr, bx, g1, DEPI_NONE);      // h = x + gamma1 * wo(y)
+        rmsnorm_rows_kernel<<<nwb, 256, 0, s>>>(bc, fn, ba, rows, D, eps);
+        r.conv(ba, bb, T, D, 2 * F, 1, 1, p + "w13", "", 0, nullptr, nullptr, nullptr, DEPI_NONE);
+        swiglu_kernel<<<(int)((rows * F + 255) / 256), 256, 0, s>>>(bb, ba, rows, F);
+        r.conv(ba, bx, T, F, D, 1, 1, p + "w2", "", 0, nullptr, bc, g2, DEPI_NONE);           // x = h + gamma2 * w2(..)
+    }
+    const float* nw = r.W(pre + "norm");
+    if (r.rc) return r.rc;
+    rmsnorm_rows_kernel<<<nwb, 256, 0, s>>>(bx, nw, ba, rows, D, eps);
+    DCK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int fsb_dac_encode(fsb_dac* h, const void* audio, int32_t B, int64_t n_samples, void* codes, void* stream) {
+    if (!h || !audio || !codes) return 1;
+    const fsb_dac_desc& d = h->d;
+    if (h->enc_dim < 4 || h->enc_dim % 4 || h->enc_n < 1)
+        return dfail(h, "encode side not configured (options enc_dim, enc_n_rates, enc_rate0.., enc_tf0.., enc_window, enc_head_dim)");
+    long long hop = 1;
+    for (int i = 0; i < h->enc_n; ++i) {
+        if (h->enc_rate[i] < 1) return dfail(h, "enc_rate not set");
+        hop *= h->enc_rate[i];
+    }
+    long long down = 1;
+    for (int i = 0; i < d.n_up; ++i) down *= ups(d, i);
+    if (B < 1 || B > d.max_batch || n_samples < hop * down || n_samples % (hop * down))
+        return dfail(h, "encode: B in 1..max_batch and n_samples a positive multiple of the code frame (pad on the host)");
+    const int T = (int)(n_samples / (hop * down));
+    if (T > d.max_frames) return dfail(h, "encode: more code frames than max_frames");
+    if ((h->enc_hd != 64 && h->enc_hd != 32) || h->enc_window > 512 || h->enc_window < 1) return dfail(h, "encode: unsupported encoder transformer shape");
+    const int D = d.latent_dim, NQ = d.n_codebooks + 1;
+    {   // the four scratch slabs were sized for the decode side: check what this plan needs
+        size_t need = 0, len = (size_t)n_samples, ch = h->enc_dim;
+        for (int i = 0; i < h->enc_n; ++i) {
+            need = std::max(need, len * ch);
+            len /= h->enc_rate[i];
+            ch *= 2;
+            if (h->enc_tf[i]) need = std::max(need, len * 6 * ch);
+        }
+        need = std::max(need, len * std::max<size_t>(ch, D));
+        for (int i = 0; i < d.n_up; ++i) {
+            len /= ups(d, i);
+            need = std::max(need, len * (size_t)d.convnext_ratio * D);
+        }
+        need = std::max(need, len * std::max<size_t>(3 * (size_t)d.tf_heads * d.tf_head_dim, 2 * (size_t)d.tf_ffn));
+        if (need * B > h->buf_elems) return dfail(h, "encode: the workspace (sized by max_batch x max_frames for the decode side) is too small for this clip");
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    Runner r{h, s, B};
+    r.exact = true;
+    float *cur = h->buf[0], *t1 = h->buf[1], *t2 = h->buf[2], *t3 = h->buf[3];
+    int len = (int)n_samples, ch = h->enc_dim;
+    {
+        const float *w = r.W("enc.in_w"), *b = r.W("enc.in_b");
+        if (r.rc) return r.rc;
+        const long long n = (long long)B * len * ch;
+        conv_in1_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>((const float*)audio, w, b, cur, B, len, ch, 7);
+    }
+    const int dil[3] = {1, 3, 9};
+    for (int i = 0; i < h->enc_n; ++i) {
+        const int st = h->enc_rate[i];
+        const std::string p = "enc." + std::to_string(i) + ".";
+        float *x = cur, *y = t1, *o = t2, *spare = t3;
+        for (int j = 0; j < 3; ++j) {   // ResidualUnit (modded_dac.py:599-620)
+            const std::string q = p + "r" + std::to_string(j) + ".";
+            r.conv(x, y, len, ch, ch, 7, dil[j], q + "w1", q + "b1", 0, r.W(q + "a1"), nullptr, nullptr, DEPI_NONE);
+            r.conv(y, o, len, ch, ch, 1, 1, q + "w2", q + "b2", 0, r.W(q + "a2"), x, nullptr, DEPI_NONE);
+            float* tmp = x; x = o; o = spare; spare = tmp;
+        }
+        if (len % st) return dfail(h, "encode: length not a multiple of the encoder stride");
+        // Snake + strided conv (kernel 2s, stride s, s zeros on the left) = 2-tap causal conv over the [len/s][s*ch] view
+        r.conv(x, y, len / st, st * ch, 2 * ch, 2, 1, p + "down_w", p + "down_b", 0, r.W(p + "down_alpha"), nullptr, nullptr, DEPI_NONE);
+        len /= st;
+        ch *= 2;
+        if (r.rc) return r.rc;
+        if (h->enc_tf[i]) {
+            const float* rope = r.W("enc.rope");
+            if (r.rc) return r.rc;
+            if ((long long)len * h->enc_hd > h->wn["enc.rope"]) return dfail(h, "encode: enc.rope table shorter than the clip");
+            if (ch % h->enc_hd) return dfail(h, "encode: encoder transformer width not a multiple of the head size");
+            if (window_transformer32(r, p + "tf.", h->enc_tf[i], ch, ch / h->enc_hd, h->enc_hd, 3 * ch, h->enc_window, rope, len, 1e-5f,
+                                     y, x, o, spare)) return 1;
+            cur = x; t1 = y; t2 = o; t3 = spare;
+        } else {
+            cur = y; t1 = x; t2 = o; t3 = spare;
+        }
+    }
+    // Snake + 3-tap conv to the latent width (modded_dac.py:699-702)
+    r.conv(cur, t1, len, ch, D, 3, 1, "enc.out_w", "enc.out_b", 0, r.W("enc.out_alpha"), nullptr, nullptr, DEPI_NONE);
+    // quantizer.downsample (rvq.py:249-261): conv kernel = stride = f over the [len/f][f*D] view, ConvNeXt block
+    for (int i = 0; i < d.n_up; ++i) {
+        const int f = ups(d, i);
+        const std::string p = "down." + std::to_string(i) + ".";
+        if (len % f) return dfail(h, "encode: length not a multiple of the downsample factor");
+        r.conv(t1, t2, len / f, f * D, D, 1, 1, p + "w", p + "b", 0, nullptr, nullptr, nullptr, DEPI_NONE);
+        len /= f;
+        const float *dww = r.W(p + "dw_w"), *dwb = r.W(p + "dw_b"), *lw = r.W(p + "ln_w"), *lb = r.W(p + "ln_b");
+        const float* gm = r.W(p + "gamma");
+        if (r.rc) return r.rc;
+        dwconv_ln_kernel<<<dim3(len, B), 256, D * sizeof(float), s>>>(t2, dww, dwb, lw, lb, t3, len, D);
+        r.conv(t3, cur, len, D, d.convnext_ratio * D, 1, 1, p + "pw1_w", p + "pw1_b", 0, nullptr, nullptr, nullptr, DEPI_GELU);
+        r.conv(cur, t1, len, d.convnext_ratio * D, D, 1, 1, p + "pw2_w", p + "pw2_b", 0, nullptr, t2, gm, DEPI_NONE);
+    }
+    if (len != T) return dfail(h, "encode: internal length mismatch");
+    // pre_module (the post_module's twin) then the codebooks
+    {
+        const float* rope = r.W("tf.rope");
+        if (r.rc) return r.rc;
+        if ((long long)T * d.tf_head_dim > h->wn["tf.rope"]) return dfail(h, "encode: tf.rope table shorter than the clip");
+        if (window_transformer32(r, "pre.", d.tf_layers, D, d.tf_heads, d.tf_head_dim, d.tf_ffn, d.tf_window, rope, T, d.tf_norm_eps,
+                                 t1, t2, t3, cur)) return 1;
+    }
+    {
+        VqEncArgs a{};
+        a.z = t2; a.in_w = r.W("vq.in_w"); a.in_b = r.W("vq.in_b"); a.cb = r.W("rvq.codebooks"); a.cbn = r.W("vq.cbn");
+        a.cbsq = r.W("vq.cbsq"); a.out_w = r.W("rvq.proj_w"); a.out_b = r.W("rvq.proj_b"); a.codes = (long long*)codes;
+        a.B = B; a.T = T; a.NQ = NQ; a.D = D; a.CD = d.codebook_dim; a.size0 = d.semantic_codebook_size; a.size_rest = d.codebook_size;
+        if (r.rc) return r.rc;
+        vq_encode_kernel<<<dim3(T, B), 256, D * sizeof(float), s>>>(a);
+    }
+    DCK(cudaGetLastError());
+    return r.rc;
+}

@@ -366,11 +366,11 @@ __global__ void rope_qk_kernel(float* qkv, const float* table, int B, int T, int
 
 // causal attention limited to the last `window` keys (WindowLimitedTransformer mask, modded_dac.py:380-398);
 // one warp per (b, h, t); lane scores keys start+lane+32i, then owns output dims lane*EPL..
-template <int HD>
+// MAXI: rounds of 32 keys a lane scores, window <= 32 * MAXI (4 for the quantizer's transformers, 16 for the encoder's 512)
+template <int HD, int MAXI = 4>
 __global__ void __launch_bounds__(128) window_attn_kernel(const float* qkv, float* y, int B, int T, int H, int window,
                                                          float scale) {
     constexpr int EPL = HD / 32;
-    constexpr int MAXI = 4;  // window <= 128
     __shared__ float qs[4][HD];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int t = blockIdx.x * 4 + w, h = blockIdx.y, b = blockIdx.z;
@@ -417,6 +417,110 @@ __global__ void __launch_bounds__(128) window_attn_kernel(const float* qkv, floa
     }
 #pragma unroll
     for (int e = 0; e < EPL; ++e) y[((size_t)b * T + t) * H * HD + (size_t)h * HD + lane * EPL + e] = o[e] * inv;
+}
+
+// ============================================================================= encode side (DAC.encode, modded_dac.py:874-923)
+// The encoder's first conv (modded_dac.py:683): 1 -> N channels, `taps` taps, causal.  One thread per output element.
+__global__ void __launch_bounds__(256) conv_in1_kernel(const float* x, const float* W, const float* bias, float* out, int B,
+                                                      long long T, int N, int taps) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= (long long)B * T * N) return;
+    const int n = (int)(i % N);
+    const long long bt = i / N, t = bt % T, b = bt / T;
+    float acc = 0.f;
+    for (int j = 0; j < taps; ++j) {
+        const long long tt = t - (taps - 1 - j);
+        if (tt >= 0) acc = fmaf(x[b * T + tt], W[j * N + n], acc);
+    }
+    out[i] = acc + bias[n];
+}
+
+// The codebooks (rvq.py:300-312 over descript VectorQuantize.forward / decode_latents): for one latent row, codebook after
+// codebook on what the previous ones left: e = in_proj(r); nearest entry between L2-normalised vectors (distance written as
+// the reference writes it: |e|^2 - 2 e.c + |c|^2, first index on ties); u = e + (entry - e) (the straight-through sum, it
+// rounds); r -= out_proj(u).  One CTA per (frame, clip); the row never leaves shared memory.
+struct VqEncArgs {
+    const float* z;       // [B][T][D]
+    const float* in_w;    // [NQ][CD][D]   weight-normed
+    const float* in_b;    // [NQ][CD]
+    const float* cb;      // [size0 + (NQ-1)*size_rest][CD]   entries as stored
+    const float* cbn;     // same shape, rows L2-normalised (F.normalize)
+    const float* cbsq;    // [..]  |normalised row|^2 (fp32: not exactly 1)
+    const float* out_w;   // [NQ][D][CD]   weight-normed
+    const float* out_b;   // [NQ][D]
+    long long* codes;     // [B][NQ][T]
+    int B, T, NQ, D, CD, size0, size_rest;
+};
+
+__global__ void __launch_bounds__(256) vq_encode_kernel(VqEncArgs a) {
+    extern __shared__ float vq_r[];            // [D] residual
+    __shared__ float e_s[16], en_s[16], u_s[16];
+    __shared__ float best_v[8];
+    __shared__ int best_i[8];
+    const int t = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float* zr = a.z + ((size_t)b * a.T + t) * a.D;
+    for (int c = tid; c < a.D; c += 256) vq_r[c] = zr[c];
+    __syncthreads();
+    int off = 0;
+    for (int q = 0; q < a.NQ; ++q) {
+        const int size = q == 0 ? a.size0 : a.size_rest;
+        // ---- e = in_proj(r): one warp per codebook dimension
+        for (int k = warp; k < a.CD; k += 8) {
+            const float* w = a.in_w + ((size_t)q * a.CD + k) * a.D;
+            float acc = 0.f;
+            for (int c = lane; c < a.D; c += 32) acc = fmaf(w[c], vq_r[c], acc);
+            acc = warp_sum(acc);
+            if (lane == 0) e_s[k] = acc + a.in_b[q * a.CD + k];
+        }
+        __syncthreads();
+        if (tid == 0) {                        // F.normalize: e / max(|e|, 1e-12)
+            float ss = 0.f;
+            for (int k = 0; k < a.CD; ++k) ss += e_s[k] * e_s[k];
+            const float nrm = fmaxf(sqrtf(ss), 1e-12f);
+            for (int k = 0; k < a.CD; ++k) en_s[k] = e_s[k] / nrm;
+        }
+        __syncthreads();
+        float en[16], esq = 0.f;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { en[k] = k < a.CD ? en_s[k] : 0.f; if (k < a.CD) esq += en[k] * en[k]; }
+        // ---- nearest entry: the largest -dist, the smallest index among equals
+        float bv = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int j = tid; j < size; j += 256) {
+            const float* c = a.cbn + (size_t)(off + j) * a.CD;
+            float m = 0.f;
+            for (int k = 0; k < a.CD; ++k) m = fmaf(en[k], c[k], m);
+            const float v = -((esq - 2.f * m) + a.cbsq[off + j]);
+            if (v > bv) { bv = v; bi = j; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) { best_v[warp] = bv; best_i[warp] = bi; }
+        __syncthreads();
+        if (tid == 0) {
+            float v = best_v[0];
+            int i = best_i[0];
+            for (int w = 1; w < 8; ++w)
+                if (best_v[w] > v || (best_v[w] == v && best_i[w] < i)) { v = best_v[w]; i = best_i[w]; }
+            a.codes[((size_t)b * a.NQ + q) * a.T + t] = i;
+            const float* c = a.cb + (size_t)(off + i) * a.CD;
+            for (int k = 0; k < a.CD; ++k) u_s[k] = e_s[k] + (c[k] - e_s[k]);
+        }
+        __syncthreads();
+        // ---- r -= out_proj(u)
+        for (int c = tid; c < a.D; c += 256) {
+            const float* w = a.out_w + ((size_t)q * a.D + c) * a.CD;
+            float acc = 0.f;
+            for (int k = 0; k < a.CD; ++k) acc = fmaf(w[k], u_s[k], acc);
+            vq_r[c] -= acc + a.out_b[q * a.D + c];
+        }
+        __syncthreads();
+        off += size;
+    }
 }
 
 // ============================================================================= tcgen05 pipeline: the non-GEMM pieces

@@ -41,6 +41,13 @@ class DACConfig:
     tf_norm_eps: float = 1e-5
     tf_window: int = 128
     convnext_ratio: int = 4
+    # encode side (DAC.encode): Encoder(encoder_dim, encoder_rates), window transformer after the blocks named in
+    # encoder_tf_layers (heads = dim // 64, ffn = 3 * dim, window 512: modded_dac.py:636-650)
+    encoder_dim: int = 64
+    encoder_rates: Tuple[int, ...] = (2, 4, 8, 8)
+    encoder_tf_layers: Tuple[int, ...] = (0, 0, 0, 4)
+    encoder_tf_window: int = 512
+    encoder_tf_head_dim: int = 64
 
     @property
     def hop(self) -> int:
@@ -53,7 +60,7 @@ class DACConfig:
         names = [f.name for f in fields(cls)]
         get = (lambda k: cfg.get(k)) if isinstance(cfg, dict) else (lambda k: getattr(cfg, k, None))
         kw = {k: get(k) for k in names if get(k) is not None}
-        for k in ("decoder_rates", "upsample_factors"):
+        for k in ("decoder_rates", "upsample_factors", "encoder_rates", "encoder_tf_layers"):
             if k in kw:
                 kw[k] = tuple(kw[k])
         return cls(**kw)
@@ -134,6 +141,76 @@ def pack_weights(c: DACConfig, sd: Dict[str, Tensor], max_frames: int) -> Dict[s
     n = len(c.decoder_rates)
     out["dec.out_alpha"] = f32(sd[f"decoder.model.{n + 1}.alpha"]).flatten()
     out["dec.out_w"], out["dec.out_b"] = conv_pack(wn_new(f"decoder.model.{n + 2}.")), f32(sd[f"decoder.model.{n + 2}.conv.bias"])
+    return out
+
+
+def has_encode_side(sd: Dict[str, Tensor]) -> bool:
+    return "encoder.block.0.conv.bias" in sd and "quantizer.semantic_quantizer.quantizers.0.in_proj.bias" in sd
+
+
+def pack_encode_weights(c: DACConfig, sd: Dict[str, Tensor], max_positions: int) -> Dict[str, Tensor]:
+    """Encode-side tensors of the reference state dict (Encoder, quantizer.downsample, quantizer.pre_module, the codebooks'
+    in_proj) -> engine tensors, fp32.  Convs as [taps][Cin][N]; a strided conv (kernel k = m * s, stride s) is regrouped for
+    the [len / s][s * Cin] view of its channels-last input: tap j of m, row r * Cin + c  <-  w[n][c][j * s + r]."""
+    f32 = lambda t: t.detach().float()
+    out: Dict[str, Tensor] = {}
+
+    def wn_new(p):
+        return _weight_norm(f32(sd[p + "conv.parametrizations.weight.original1"]),
+                            f32(sd[p + "conv.parametrizations.weight.original0"]))
+
+    conv_pack = lambda w: w.permute(2, 1, 0).contiguous()           # [Cout,Cin,k] -> [k][Cin][Cout]
+
+    def strided_pack(w, s):                                         # [Cout,Cin,m*s] -> [m][s*Cin][Cout]
+        cout, cin, k = w.shape
+        return w.view(cout, cin, k // s, s).permute(2, 3, 1, 0).reshape(k // s, s * cin, cout).contiguous()
+
+    def transformer(p, q, layers):
+        for i in range(layers):
+            u, v = f"{p}layers.{i}.", f"{q}{i}."
+            out[v + "attn_norm"] = f32(sd[u + "attention_norm.weight"])
+            out[v + "ffn_norm"] = f32(sd[u + "ffn_norm.weight"])
+            out[v + "gamma1"] = f32(sd[u + "attention_layer_scale.gamma"])
+            out[v + "gamma2"] = f32(sd[u + "ffn_layer_scale.gamma"])
+            out[v + "wqkv"] = f32(sd[u + "attention.wqkv.weight"]).t().contiguous()
+            out[v + "wo"] = f32(sd[u + "attention.wo.weight"]).t().contiguous()
+            out[v + "w13"] = torch.cat([f32(sd[u + "feed_forward.w1.weight"]), f32(sd[u + "feed_forward.w3.weight"])], 0).t().contiguous()
+            out[v + "w2"] = f32(sd[u + "feed_forward.w2.weight"]).t().contiguous()
+        out[q + "norm"] = f32(sd[p + "norm.weight"])
+
+    out["enc.in_w"], out["enc.in_b"] = conv_pack(wn_new("encoder.block.0.")), f32(sd["encoder.block.0.conv.bias"])
+    for i, (s, nl) in enumerate(zip(c.encoder_rates, c.encoder_tf_layers)):
+        p, q = f"encoder.block.{i + 1}.block.", f"enc.{i}."
+        for j in range(3):
+            u, v = p + f"{j}.block.", q + f"r{j}."
+            out[v + "a1"], out[v + "a2"] = f32(sd[u + "0.alpha"]).flatten(), f32(sd[u + "2.alpha"]).flatten()
+            out[v + "w1"], out[v + "b1"] = conv_pack(wn_new(u + "1.")), f32(sd[u + "1.conv.bias"])
+            out[v + "w2"], out[v + "b2"] = conv_pack(wn_new(u + "3.")), f32(sd[u + "3.conv.bias"])
+        out[q + "down_alpha"] = f32(sd[p + "3.alpha"]).flatten().repeat(s)
+        out[q + "down_w"], out[q + "down_b"] = strided_pack(wn_new(p + "4."), s), f32(sd[p + "4.conv.bias"])
+        if nl:
+            transformer(p + "5.", q + "tf.", nl)
+    n = len(c.encoder_rates)
+    out["enc.out_alpha"] = f32(sd[f"encoder.block.{n + 1}.alpha"]).flatten()
+    out["enc.out_w"], out["enc.out_b"] = conv_pack(wn_new(f"encoder.block.{n + 2}.")), f32(sd[f"encoder.block.{n + 2}.conv.bias"])
+    out["enc.rope"] = _rope_table(max_positions, c.encoder_tf_head_dim, 10000.0).contiguous()
+    for i, f in enumerate(c.upsample_factors):
+        p, q = f"quantizer.downsample.{i}.", f"down.{i}."
+        out[q + "w"], out[q + "b"] = strided_pack(f32(sd[p + "0.conv.weight"]), f), f32(sd[p + "0.conv.bias"])
+        out[q + "dw_w"] = f32(sd[p + "1.dwconv.conv.weight"])[:, 0, :].contiguous()
+        out[q + "dw_b"] = f32(sd[p + "1.dwconv.conv.bias"])
+        out[q + "ln_w"], out[q + "ln_b"] = f32(sd[p + "1.norm.weight"]), f32(sd[p + "1.norm.bias"])
+        out[q + "pw1_w"], out[q + "pw1_b"] = f32(sd[p + "1.pwconv1.weight"]).t().contiguous(), f32(sd[p + "1.pwconv1.bias"])
+        out[q + "pw2_w"], out[q + "pw2_b"] = f32(sd[p + "1.pwconv2.weight"]).t().contiguous(), f32(sd[p + "1.pwconv2.bias"])
+        out[q + "gamma"] = f32(sd[p + "1.gamma"])
+    transformer("quantizer.pre_module.", "pre.", c.tf_layers)
+    prefixes = ["quantizer.semantic_quantizer.quantizers.0."] + [f"quantizer.quantizer.quantizers.{i}." for i in range(c.n_codebooks)]
+    out["vq.in_w"] = torch.stack([_weight_norm(f32(sd[p + "in_proj.weight_v"]), f32(sd[p + "in_proj.weight_g"]))[:, :, 0]
+                                  for p in prefixes]).contiguous()                      # [NQ][CD][D]
+    out["vq.in_b"] = torch.stack([f32(sd[p + "in_proj.bias"]) for p in prefixes]).contiguous()
+    cbn = torch.cat([torch.nn.functional.normalize(f32(sd[p + "codebook.weight"])) for p in prefixes], 0).contiguous()
+    out["vq.cbn"] = cbn
+    out["vq.cbsq"] = cbn.pow(2).sum(1).contiguous()
     return out
 
 
@@ -223,7 +300,8 @@ def synthetic_state_dict(c: "DACConfig", seed: int = 0, device="cpu") -> Dict[st
 
 
 class DACB200:
-    """Engine-backed stand-in for modded_dac.DAC on the decode side."""
+    """Engine-backed stand-in for modded_dac.DAC: from_indices (decode side, the hot path) and, when the state dict has the
+    encode side's weights, encode (reference voice -> codes)."""
 
     def __init__(self, config, state_dict: Dict[str, Tensor], device="cuda:0", max_batch: int = 4, max_frames: int = 1024,
                  operand: str = "f16"):
@@ -257,6 +335,7 @@ class DACB200:
             # box reads); the transformer's gate/up matrix with its columns interleaved (SwiGLU in the GEMM epilogue)
             self.operand = operand
             hdt = torch.float16 if operand == "f16" else torch.bfloat16
+            self.can_encode = has_encode_side(dev_sd)
             for k in [k for k, v in self.weights.items() if v.dim() == 3 and k != "dec.out_w"] + \
                      [k for k in self.weights if k.startswith("tf.") and k.split(".")[-1] in ("wqkv", "wo", "w13", "w2")] + \
                      [k for k in self.weights if k.endswith(("pw1_w", "pw2_w"))]:
@@ -267,9 +346,23 @@ class DACB200:
                     F_ = w.shape[1] // 2
                     w = torch.stack([w[:, :F_], w[:, F_:]], dim=2).reshape(w.shape[0], 2 * F_, w.shape[2])
                 self.weights[k + ".h"] = w.to(hdt).contiguous()
+            if self.can_encode:        # fp32 only: the encode side's result is a set of arg-max decisions
+                down = int(math.prod(c.upsample_factors))
+                for k, v in pack_encode_weights(c, dev_sd, self.max_frames * down).items():
+                    self.weights[k] = v.to(self.device, torch.float32).contiguous()
             for k, v in self.weights.items():
                 self._ck(self.lib.fsb_dac_bind_weight(self._h, k.encode(), v.data_ptr(), v.numel()))
             self.set_option("half", 1 if operand == "f16" else 0)
+            if self.can_encode:
+                if len(c.encoder_rates) != len(c.encoder_tf_layers) or not 1 <= len(c.encoder_rates) <= 4:
+                    raise ValueError("encoder_rates / encoder_tf_layers: 1..4 entries each, same length")
+                self.set_option("enc_dim", c.encoder_dim)
+                self.set_option("enc_n_rates", len(c.encoder_rates))
+                for i, (r_, n_) in enumerate(zip(c.encoder_rates, c.encoder_tf_layers)):
+                    self.set_option(f"enc_rate{i}", r_)
+                    self.set_option(f"enc_tf{i}", n_)
+                self.set_option("enc_window", c.encoder_tf_window)
+                self.set_option("enc_head_dim", c.encoder_tf_head_dim)
 
     def _ck(self, rc: int):
         if rc != 0:
@@ -338,6 +431,38 @@ class DACB200:
         finally:
             self.set_option("pos_offset", 0)
         return wav
+
+    @torch.inference_mode()
+    def encode(self, audio_data: Tensor, audio_lengths: Optional[Tensor] = None, n_quantizers: Optional[int] = None, **kwargs):
+        """DAC.encode (modded_dac.py:874-923): [B, 1, n] or [B, n] waveform -> (indices [B, 1+n_codebooks, ceil(n / frame)] int64,
+        indices_lens).  fp32 throughout.  Needs the encode side's weights in the state dict the engine was built from."""
+        if not self.can_encode:
+            raise RuntimeError("fish_b200 dac: built from a state dict without the encode side (encoder.*, quantizer.downsample.*, "
+                               "quantizer.pre_module.*, in_proj.*)")
+        if n_quantizers is not None and n_quantizers != self.config.n_codebooks:
+            # rvq.py:309-311 passes it to the residual codebooks only; fewer codebooks is a training-time feature
+            raise NotImplementedError("n_quantizers other than all of them")
+        if audio_data.dim() == 2:
+            audio_data = audio_data.unsqueeze(1)
+        if audio_data.dim() != 3 or audio_data.shape[1] != 1:
+            raise ValueError(f"expected [B, 1, n] or [B, n] audio, got {tuple(audio_data.shape)}")
+        B, _, length = audio_data.shape
+        frame = self.frame_length
+        right_pad = -length % frame
+        T = (length + right_pad) // frame
+        if T < 1 or T > self.max_frames:
+            raise ValueError(f"{length} samples = {T} code frames, outside 1..max_frames={self.max_frames}")
+        x = torch.zeros((B, length + right_pad), dtype=torch.float32, device=self.device)
+        x[:, :length] = audio_data[:, 0].to(device=self.device, dtype=torch.float32)
+        if audio_lengths is None:
+            audio_lengths = torch.LongTensor([length + right_pad]).to(self.device)
+        codes = torch.empty((B, self.config.n_codebooks + 1, T), dtype=torch.int64, device=self.device)
+        st = torch.cuda.current_stream().cuda_stream
+        for b0 in range(0, B, self.max_batch):
+            nb = min(self.max_batch, B - b0)
+            self._ck(self.lib.fsb_dac_encode(self._h, x[b0: b0 + nb].data_ptr(), nb, length + right_pad,
+                                             codes[b0: b0 + nb].data_ptr(), st))
+        return codes, torch.ceil(audio_lengths / frame).long()
 
     def context_frames(self) -> int:
         """How many earlier code frames an output sample can depend on: the causal convs' taps walked back from the waveform

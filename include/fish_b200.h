@@ -172,6 +172,12 @@ const char* fsb_dac_last_error(const fsb_dac* h);
 int fsb_dac_bind_weight(fsb_dac* h, const char* name, const void* dptr, int64_t numel);
 /* DAC.from_indices: codes int64 [B][1+n_codebooks][T] (clamped IN PLACE like rvq.py:354-359) -> wav fp32 [B][hop*T]. */
 int fsb_dac_decode(fsb_dac* h, void* codes, int32_t B, int32_t T, void* wav, void* stream);
+/* DAC.encode (modded_dac.py:874-923: Encoder :670-709, DownsampleResidualVectorQuantize.forward rvq.py:293-318 up to the codes):
+ * audio fp32 [B][n_samples], n_samples a positive multiple of the code frame (the caller pads with zeros on the right like
+ * :909-911) -> codes int64 [B][1+n_codebooks][n_samples / hop].  fp32 throughout.  The encode side's shape is set with
+ * fsb_dac_set_option first: "enc_dim", "enc_n_rates", "enc_rate0".."enc_rate3", "enc_tf0".."enc_tf3" (transformer layers after
+ * each block), "enc_window", "enc_head_dim"; its weights are bound under the names fish_speech_b200/dac.py lists. */
+int fsb_dac_encode(fsb_dac* h, const void* audio, int32_t B, int64_t n_samples, void* codes, void* stream);
 /* Options: "tf32" (1 = GEMM-shaped layers on the tensor cores with TF32 operands and fp32 accumulation, the default;
  * 0 = fp32 CUDA-core path, the parity anchor). */
 int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value);
