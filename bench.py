@@ -360,6 +360,62 @@ def measure_dac(dev, B=32, T=646, iters=2):
     return out
 
 
+def measure_dac_encode(dev, seconds=30.0, iters=3):
+    """The codec's encode side (the reference voice of a cloning request -> codes): one clip of `seconds` seconds
+    from pinned host memory -> codes on the device; fp32 CUDA-core path.  -> {"ms", "audio_s_per_s", ...}"""
+    import torch
+    from fish_speech_b200.dac import DACB200, DACConfig, synthetic_state_dict
+    cfg = DACConfig()
+    n = int(seconds * cfg.sample_rate)
+    m = DACB200(cfg, synthetic_state_dict(cfg, 0, encode_side=True), device=dev, max_batch=1, max_frames=-(-n // cfg.hop))
+    g = torch.Generator().manual_seed(3)
+    audio = (0.3 * torch.randn((1, 1, n), generator=g)).pin_memory()
+    codes, _ = m.encode(audio.to(dev, non_blocking=True))
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        again, _ = m.encode(audio.to(dev, non_blocking=True))
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    out = {"workload": f"DAC.encode, 1 clip x {seconds:.0f} s at 44.1 kHz -> {codes.shape[2]} code frames x {codes.shape[1]} codebooks",
+           "ms": ms, "value": seconds / (ms * 1e-3), "unit": "audio-s/s", "dtype": "f32",
+           "deterministic": bool(torch.equal(again, codes))}
+    del m
+    torch.cuda.empty_cache()
+    return out
+
+
+def cpu_dac_encode_leg(seconds=2.0):
+    """The reference's CPU encode path on a bounded sample: `seconds` of audio, fp32, all host threads: `DAC.encode`
+    (modded_dac.py:874-923) of the vendored classes when oracle/_ref is present, else the oracle port pinned to them."""
+    import torch
+    from oracle import dac_ref as D
+    from oracle import make_ref
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    c = D.DACConfig()
+    sd = {**D.make_state_dict(c, seed=0), **D.make_encode_state_dict(c, seed=0)}
+    audio = D.make_audio(c, 1, int(seconds * c.sample_rate))
+    kind, fn = "port", (lambda: D.encode(c, sd, audio))
+    if make_ref.available() and (make_ref.DEST / "fish_speech/models/dac/modded_dac.py").exists():
+        try:
+            from oracle.gen_golden_dac import build_reference_dac
+            ref = build_reference_dac(c, importer=make_ref.import_vendored, encode_side=True)
+            ref.load_state_dict(sd, strict=False)
+            kind, fn = "reference", (lambda: ref.encode(audio))
+        except Exception as e:
+            sys.stderr.write(f"[bench] vendored reference codec (encode) failed ({e}); timing the oracle port instead\n")
+    with torch.inference_mode():
+        t0 = time.perf_counter()
+        fn()
+        dt = time.perf_counter() - t0
+    what = "reference DAC.encode (oracle/_ref, unmodified)" if kind == "reference" else "oracle port of DAC.encode"
+    return {"value": seconds / dt, "unit": "audio-s/s", "cores": cores, "kind": kind,
+            "sample": f"1 clip x {seconds:.0f} s of audio, fp32, {what}"}
+
+
 def cpu_dac_leg(frames=215):
     """The reference's CPU codec path on a bounded sample: ONE clip of `frames` code frames (10 s of audio), fp32, all host
     threads; audio-s/s.  With oracle/_ref present it is the reference's own `DAC.from_indices` (modded_dac.py:925-927, classes
@@ -624,6 +680,14 @@ def run_ours(args):
             dac_cpu = cpu_dac_leg()
         except Exception as e:
             dac_cpu = {"value": None, "sample": f"failed: {e}"}
+    dac_enc = None
+    if not args.no_dac and world == 1:
+        try:
+            dac_enc = measure_dac_encode(dev)
+            if not args.no_cpu:
+                dac_enc["cpu_baseline"] = cpu_dac_encode_leg()
+        except Exception as e:
+            dac_enc = {"error": str(e)}
     sched = None
     if args.sched and world == 1:
         try:
@@ -726,6 +790,8 @@ def run_ours(args):
                                             "against the measured sustained bf16/fp16 tensor peak"}}
         if dac_cpu is not None:
             line["dac"]["cpu_baseline"] = dac_cpu
+        if dac_enc is not None:
+            line["dac"]["encode"] = dac_enc
     elif dac is not None:
         line["dac"] = {"error": str(dac)}
     if c5 is not None:

@@ -279,11 +279,68 @@ def state_dict_shapes(c: "DACConfig") -> Dict[str, tuple]:
     return out
 
 
-def synthetic_state_dict(c: "DACConfig", seed: int = 0, device="cpu") -> Dict[str, Tensor]:
-    """Random decode-path weights of the right shapes (benchmarks only: bounded activations, no claim of audio)."""
+def encode_state_dict_shapes(c: "DACConfig") -> Dict[str, tuple]:
+    """Reference state-dict keys of the encode side (Encoder modded_dac.py:670-709, quantizer.downsample / pre_module
+    rvq.py:249-283, the codebooks' in_proj) and their shapes: what `pack_encode_weights` needs."""
+    D = c.latent_dim
+    out: Dict[str, tuple] = {}
+
+    def wnconv(p, cout, cin, k):
+        out[p + "conv.parametrizations.weight.original0"] = (cout, 1, 1)
+        out[p + "conv.parametrizations.weight.original1"] = (cout, cin, k)
+        out[p + "conv.bias"] = (cout,)
+
+    def transformer(p, layers, dim, heads, hd, ffn):
+        for i in range(layers):
+            q = f"{p}layers.{i}."
+            out[q + "attention.wqkv.weight"] = (3 * heads * hd, dim)
+            out[q + "attention.wo.weight"] = (dim, heads * hd)
+            for w_, shp in (("w1", (ffn, dim)), ("w3", (ffn, dim)), ("w2", (dim, ffn))):
+                out[q + f"feed_forward.{w_}.weight"] = shp
+            for n_ in ("ffn_norm.weight", "attention_norm.weight", "attention_layer_scale.gamma", "ffn_layer_scale.gamma"):
+                out[q + n_] = (dim,)
+        out[p + "norm.weight"] = (dim,)
+
+    wnconv("encoder.block.0.", c.encoder_dim, 1, 7)
+    ch = c.encoder_dim
+    for i, (s, nl) in enumerate(zip(c.encoder_rates, c.encoder_tf_layers)):
+        p = f"encoder.block.{i + 1}.block."
+        for j in range(3):
+            out[p + f"{j}.block.0.alpha"] = (1, ch, 1)
+            wnconv(p + f"{j}.block.1.", ch, ch, 7)
+            out[p + f"{j}.block.2.alpha"] = (1, ch, 1)
+            wnconv(p + f"{j}.block.3.", ch, ch, 1)
+        out[p + "3.alpha"] = (1, ch, 1)
+        wnconv(p + "4.", 2 * ch, ch, 2 * s)
+        ch *= 2
+        if nl:
+            transformer(p + "5.", nl, ch, ch // c.encoder_tf_head_dim, c.encoder_tf_head_dim, 3 * ch)
+    n = len(c.encoder_rates)
+    out[f"encoder.block.{n + 1}.alpha"] = (1, ch, 1)
+    wnconv(f"encoder.block.{n + 2}.", D, ch, 3)
+    for i, f in enumerate(c.upsample_factors):
+        p = f"quantizer.downsample.{i}."
+        out[p + "0.conv.weight"], out[p + "0.conv.bias"] = (D, D, f), (D,)
+        out[p + "1.dwconv.conv.weight"], out[p + "1.dwconv.conv.bias"] = (D, 1, 7), (D,)
+        out[p + "1.norm.weight"], out[p + "1.norm.bias"] = (D,), (D,)
+        out[p + "1.pwconv1.weight"], out[p + "1.pwconv1.bias"] = (c.convnext_ratio * D, D), (c.convnext_ratio * D,)
+        out[p + "1.pwconv2.weight"], out[p + "1.pwconv2.bias"] = (D, c.convnext_ratio * D), (D,)
+        out[p + "1.gamma"] = (D,)
+    transformer("quantizer.pre_module.", c.tf_layers, c.tf_dim, c.tf_heads, c.tf_head_dim, c.tf_ffn)
+    for p in ["quantizer.semantic_quantizer.quantizers.0."] + [f"quantizer.quantizer.quantizers.{i}." for i in range(c.n_codebooks)]:
+        out[p + "in_proj.weight_g"], out[p + "in_proj.weight_v"], out[p + "in_proj.bias"] = (c.codebook_dim, 1, 1), (c.codebook_dim, D, 1), (c.codebook_dim,)
+    return out
+
+
+def synthetic_state_dict(c: "DACConfig", seed: int = 0, device="cpu", encode_side: bool = False) -> Dict[str, Tensor]:
+    """Random weights of the right shapes (benchmarks only: bounded activations, no claim of audio); `encode_side` adds the
+    encoder, the quantizer's downsample / pre_module and the codebooks' in_proj."""
     g = torch.Generator().manual_seed(seed)
     sd: Dict[str, Tensor] = {}
-    for name, shape in state_dict_shapes(c).items():
+    shapes = dict(state_dict_shapes(c))
+    if encode_side:
+        shapes.update(encode_state_dict_shapes(c))
+    for name, shape in shapes.items():
         if name.endswith("alpha"):
             w = 0.5 + torch.rand(shape, generator=g)
         elif name.endswith(("gamma", "original0", "weight_g")):
