@@ -32,6 +32,7 @@ struct fsb_dac {
     // encode side (DAC.encode): set through fsb_dac_set_option ("enc_dim", "enc_n_rates", "enc_rate0..3", "enc_tf0..3",
     // "enc_window", "enc_head_dim"); 0 = not configured
     int enc_dim = 0, enc_n = 0, enc_rate[4] = {0, 0, 0, 0}, enc_tf[4] = {0, 0, 0, 0}, enc_window = 512, enc_hd = 64;
+    int enc_exact = 1;   // 1: fp32 CUDA-core GEMMs on the encode side; 0: they follow "tf32" (measurement of how many codes move)
     int n_sm = 148;
     std::map<std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, int>, CUtensorMap> maps;
     std::string err;
@@ -221,6 +222,7 @@ int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
     else if (n.size() == 7 && n.compare(0, 6, "enc_tf") == 0 && n[6] >= '0' && n[6] <= '3') h->enc_tf[n[6] - '0'] = (int)value;
     else if (n == "enc_window") h->enc_window = (int)value;
     else if (n == "enc_head_dim") h->enc_hd = (int)value;
+    else if (n == "enc_exact") h->enc_exact = (int)value;
     else return dfail(h, "unknown option " + n);
     return 0;
 }
@@ -579,7 +581,7 @@ extern "C" int fsb_dac_encode(fsb_dac* h, const void* audio, int32_t B, int64_t 
     }
     cudaStream_t s = (cudaStream_t)stream;
     Runner r{h, s, B};
-    r.exact = true;
+    r.exact = h->enc_exact != 0;
     float *cur = h->buf[0], *t1 = h->buf[1], *t2 = h->buf[2], *t3 = h->buf[3];
     int len = (int)n_samples, ch = h->enc_dim;
     {

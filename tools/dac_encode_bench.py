@@ -30,6 +30,20 @@ for _ in range(reps):
     ts.append(e0.elapsed_time(e1))
 assert torch.equal(again, codes)
 ms = sorted(ts)[len(ts) // 2]
+m.set_option("enc_exact", 0)                     # GEMM-shaped layers on the TF32 mma.sync kernels: how many codes move, how fast
+m.set_option("tf32", 1)
+tf, _ = m.encode(audio)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+tf, _ = m.encode(audio)
+e1.record()
+e1.synchronize()
+tf32 = {"ms": round(e0.elapsed_time(e1), 2), "codes_equal": round(float((tf == codes).float().mean()), 4),
+        "semantic_codes_equal": round(float((tf[:, 0] == codes[:, 0]).float().mean()), 4),
+        "frames_fully_equal": round(float((tf == codes).all(dim=1).float().mean()), 4)}
+m.set_option("enc_exact", 1)
+print(json.dumps({"tf32_variant": tf32}))
 print(json.dumps({"seconds_per_clip": seconds, "clips": batch, "frames": frames, "ms": round(ms, 2),
                   "audio_s_per_s": round(batch * seconds / (ms * 1e-3), 1),
                   "codes_used": [int(torch.unique(codes[:, i]).numel()) for i in range(codes.shape[1])]}))
