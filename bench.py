@@ -504,12 +504,22 @@ def measure_config5(dev, rank, T=8192, F=4096):
     model.setup_caches(1, cfg.max_seq_len)
     model.ignore_eos = True
     dcfg = DACConfig()
-    dac = DACB200(dcfg, synthetic_state_dict(dcfg, 0), device=dev, max_batch=1, max_frames=F)
-    prompt = synth_prompt(cfg, T, seed=11 + rank)
-    # voice-clone prompt: the last 7/8 are reference-audio frames (semantic tokens + codes, content_sequence.py:206-209)
-    g = torch.Generator().manual_seed(5 + rank)
     span = T - T // 8
-    codes = torch.randint(0, cfg.codebook_size, (cfg.num_codebooks, span), generator=g)
+    dac = DACB200(dcfg, synthetic_state_dict(dcfg, 0, encode_side=True), device=dev, max_batch=1, max_frames=max(F, span))
+    prompt = synth_prompt(cfg, T, seed=11 + rank)
+    # voice-clone prompt: the last 7/8 are reference-audio frames (semantic tokens + codes, content_sequence.py:206-209), and the
+    # codes are what the codec's encode side makes of a (synthetic) reference waveform of that length (vq_manager.py:24-52);
+    # timed on its own: the reference voice is encoded once, not per request
+    g = torch.Generator().manual_seed(5 + rank)
+    ref_wav = (0.3 * torch.randn((1, 1, span * dcfg.hop), generator=g)).pin_memory()
+    dac.encode(ref_wav[:, :, : 8 * dcfg.hop].to(dev))
+    torch.cuda.synchronize()
+    ee = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ee[0].record()
+    codes = dac.encode(ref_wav.to(dev, non_blocking=True))[0][0].cpu()          # [10, span]
+    ee[1].record()
+    torch.cuda.synchronize()
+    enc_ms = ee[0].elapsed_time(ee[1])
     prompt[1:, T - span:] = codes
     prompt[0, T - span:] = cfg.semantic_begin_id + codes[0]
     hp = prompt.pin_memory()
@@ -561,6 +571,9 @@ def measure_config5(dev, rank, T=8192, F=4096):
                             if model.launches_per_frame(1) == 1 else
                             "context 8k -> 12k: kernel chain (PDL-chained launches per frame in a CUDA graph)") + ", restricted LM head"},
         "dac": {"ms": dac_ms, "tflops": dac.flops(1, n_new) / dac_ms / 1e9, "frac_of_tensor_peak": dac.flops(1, n_new) / dac_ms / 1e9 / tpeak},
+        "reference_encode": {"ms": enc_ms, "frames": span, "audio_s": span * FRAME_SEC,
+                             "note": "DAC.encode of the reference waveform whose codes fill the prompt's audio span (fp32; once per voice, "
+                                     "outside wall_s; H2D of the waveform and D2H of the codes inside ms)"},
     }
     del model, dac
     torch.cuda.empty_cache()
