@@ -26,6 +26,7 @@ class FrameArgs(C.Structure):
         ("logit_bias", C.c_void_p), ("restrict_scan", C.c_int32),
         ("temperature", C.c_float), ("top_p", C.c_float), ("top_k", C.c_int32),
         ("uniforms", C.c_void_p), ("seed", C.c_uint64),
+        ("row_temperature", C.c_void_p), ("row_top_p", C.c_void_p), ("row_top_k", C.c_void_p),
     ]
 
 

@@ -366,6 +366,7 @@ SampleArgs make_slow_sample(const fsb_dual_ar* h, const fsb_frame_args& fa) {
     sa.top_k = fa.top_k;
     sa.n_variants = 2;
     sa.temp[0] = fa.temperature; sa.top_p[0] = fa.top_p;
+    sa.row_temp = fa.row_temperature; sa.row_top_p = fa.row_top_p; sa.row_top_k = fa.row_top_k;
     sa.temp[1] = 1.0f;         // RAS_HIGH_TEMP  (inference.py:50)
     sa.top_p[1] = 0.8984375f;  // RAS_HIGH_TOP_P 0.9 as bf16 (inference.py:51, tensor built in the model dtype)
     sa.uniforms = (const bf16*)fa.uniforms;
@@ -390,6 +391,7 @@ SampleArgs make_fast_sample(const fsb_dual_ar* h, const fsb_frame_args& fa, int 
     fs.seg_lo[0] = 0; fs.seg_hi[0] = cb; fs.seg_lo[1] = fs.seg_hi[1] = 0;
     fs.top_k = fa.top_k; fs.n_variants = 1;
     fs.temp[0] = fa.temperature; fs.top_p[0] = fa.top_p; fs.temp[1] = 1.f; fs.top_p[1] = 1.f;
+    fs.row_temp = fa.row_temperature; fs.row_top_p = fa.row_top_p; fs.row_top_k = fa.row_top_k;
     fs.uniforms = (const bf16*)fa.uniforms;
     fs.u_stride = 2LL * V + (long long)(C - 1) * cb; fs.u_offset = 2LL * V + (long long)(i - 1) * cb;
     fs.seed = fa.seed; fs.frame_counter = fa.frame_counter; fs.draw_id = i;

@@ -28,6 +28,9 @@ struct SampleArgs {
     int top_k;
     int n_variants;            // 1, or 2 = (normal, RAS high-temperature) for the slow token
     float temp[2], top_p[2];   // bf16-representable values (generate() builds them in the model dtype)
+    const float* row_temp;     // [B] per-request values for variant 0 (batches that mix requests), or nullptr
+    const float* row_top_p;
+    const int32_t* row_top_k;
     const bf16* uniforms;      // injected draws [frames][B][u_stride]; nullptr -> Philox
     long long u_stride;        // elements per (frame, request)
     long long u_offset;        // offset of this call's first draw inside a (frame, request) record
@@ -169,7 +172,7 @@ __device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, 
     kmax = __reduce_max_sync(0xffffffffu, kmax);
     int nfin_total;
     block_excl_scan<SY>(nfin, wsum, &nfin_total, tid);
-    const int k_eff = min(min(a.top_k, SAMPLE_MAXK), nfin_total);
+    const int k_eff = min(min(a.row_top_k ? a.row_top_k[b] : a.top_k, SAMPLE_MAXK), nfin_total);
     // no finite logit at all: the reference's softmax is NaN everywhere and its argmax returns index 0; the token is
     // still written through the common output section (code, EOS flag, the next fast-AR input row and its tag — a
     // consumer of the persistent frame kernel waits for that row)
@@ -301,8 +304,8 @@ __device__ __forceinline__ void sample_body(const SampleArgs& a, int b, int nB, 
 
     const float tmin = rbf(1e-5f);
     for (int v = 0; v < a.n_variants; ++v) {
-        const float T = fmaxf(a.temp[v], tmin);
-        const float P = a.top_p[v];
+        const float T = fmaxf((v == 0 && a.row_temp) ? a.row_temp[b] : a.temp[v], tmin);
+        const float P = (v == 0 && a.row_top_p) ? a.row_top_p[b] : a.top_p[v];
         bool keep[2];
         float l2[2];
         float m2 = -INFINITY;

@@ -376,6 +376,18 @@ class DecodeSession:
         self.bias: Optional[Tensor] = None
         self.seed = 0
         self.restrict_scan = True
+        # per-request sampling parameters (fsb_frame_args.row_*): float32 / float32 / int32 device tensors [batch] that replace
+        # the scalars of run() for each request's normal draw, or None.  Values as generate() would round them (bf16).
+        self.row_temperature: Optional[Tensor] = None
+        self.row_top_p: Optional[Tensor] = None
+        self.row_top_k: Optional[Tensor] = None
+
+    def use_row_parameters(self):
+        """Allocates the per-request parameter arrays (filled with generate()'s defaults); the caller writes rows."""
+        dev = self.model.device
+        self.row_temperature = torch.full((self.batch,), _as_bf16_float(1.0), dtype=torch.float32, device=dev)
+        self.row_top_p = torch.full((self.batch,), _as_bf16_float(0.9), dtype=torch.float32, device=dev)
+        self.row_top_k = torch.full((self.batch,), 30, dtype=torch.int32, device=dev)
 
     def args(self, temperature: float, top_p: float, top_k: int, use_ras: bool) -> _lib.FrameArgs:
         return _lib.FrameArgs(
@@ -383,7 +395,8 @@ class DecodeSession:
             ras_window=self.ras_window.data_ptr() if use_ras else None, out_tokens=self.out_tokens.data_ptr(),
             max_frames=self.max_frames, frame_counter=self.frame_counter.data_ptr(), done=self.done.data_ptr(),
             logit_bias=_ptr(self.bias), restrict_scan=int(self.restrict_scan and self.bias is not None),
-            temperature=temperature, top_p=top_p, top_k=top_k, uniforms=_ptr(self.uniforms), seed=self.seed)
+            temperature=temperature, top_p=top_p, top_k=top_k, uniforms=_ptr(self.uniforms), seed=self.seed,
+            row_temperature=_ptr(self.row_temperature), row_top_p=_ptr(self.row_top_p), row_top_k=_ptr(self.row_top_k))
 
     def run(self, n_frames: int, temperature: float, top_p: float, top_k: int, use_ras: bool,
             pos_bound: Optional[int] = None):

@@ -21,9 +21,10 @@ rest only - bit-identical to the full pass, like §5.7 of DESIGN.md.
 Sampling draws are keyed by (seed, frame index, row): which row a request lands on and when it joins decide its draws, so
 two runs of the same request agree in distribution, not token for token (exact ties between top candidates included).
 
-Rows of one step share the sampling parameters (one `fsb_frame_args`), so requests are grouped: the batch in flight has one
-(temperature, top_p, top_k); a request with other values waits until the batch has drained, and nothing that arrived after it
-is admitted before it (no starvation).
+Sampling parameters are per request: `fsb_frame_args.row_temperature / row_top_p / row_top_k` carry one entry per row, so
+requests with different values decode side by side.  (With a session that has no such arrays - the CPU stand-in of the tests -
+requests are grouped instead: the batch in flight has one (temperature, top_p, top_k), a request with other values waits until
+the batch has drained, and nothing that arrived after it is admitted before it.)
 """
 from __future__ import annotations
 
@@ -97,6 +98,13 @@ class ContinuousBatcher:
         self.sess.bias = make_semantic_logit_bias(model).reshape(-1).to(torch.bfloat16).contiguous()
         self.sess.restrict_scan = True
         self.sess.done.fill_(1)                     # every row idle
+        # per-request (temperature, top_p, top_k): fsb_frame_args.row_* arrays, one entry per row, so requests with different
+        # values share a batch; a session without them (older engine, the CPU stand-in) groups requests by their values instead
+        self.per_row = hasattr(self.sess, "use_row_parameters")
+        if self.per_row:
+            self.sess.use_row_parameters()
+            self.row_params: List[Tuple[float, float, int]] = [(_as_bf16_float(1.0), _as_bf16_float(0.9), 30)] * self.rows
+            self.row_params_dirty = True
         self.waiting: Deque[GenerateRequest] = deque()
         self.active: Dict[int, _Row] = {}
         self.key: Optional[Tuple[float, float, int]] = None
@@ -143,7 +151,9 @@ class ContinuousBatcher:
                 if T >= c.max_seq_len:   # inference.py:262-265
                     raise ValueError(f"Input sequence length {T} exceeds max_seq_len {c.max_seq_len}")
                 key = self._key(req)
-                if self.active and key != self.key:
+                if not 1 <= key[2] <= 64:
+                    raise ValueError(f"top_k must be in [1, 64], got {key[2]}")
+                if not self.per_row and self.active and key != self.key:
                     break                # other sampling parameters: wait for the batch to drain, keep the order
                 max_new = int(req.get("max_new_tokens", 0) or 0)
                 budget = min(max_new, c.max_seq_len - T) if max_new else c.max_seq_len - T   # inference.py:267-274
@@ -154,6 +164,9 @@ class ContinuousBatcher:
             self.waiting.popleft()
             row = next(r for r in range(self.rows) if r not in self.active)
             self.key = key
+            if self.per_row:
+                self.row_params[row] = key
+                self.row_params_dirty = True
             self._fill_slot(row, prompt[:, :-1])              # KV slot `row` (slot = row) <- the prompt but its last column
             s.cur_tokens[row].copy_(prompt[:, -1].to(device=s.cur_tokens.device, dtype=torch.int32))
             s.ras_window[row].zero_()
@@ -207,6 +220,11 @@ class ContinuousBatcher:
                for r in range(self.rows)]
         s.pos.copy_(torch.tensor(pos, dtype=torch.int32))
         s.done.copy_(torch.tensor([0 if r in self.active else 1 for r in range(self.rows)], dtype=torch.int32))
+        if self.per_row and self.row_params_dirty:
+            s.row_temperature.copy_(torch.tensor([p[0] for p in self.row_params], dtype=torch.float32))
+            s.row_top_p.copy_(torch.tensor([p[1] for p in self.row_params], dtype=torch.float32))
+            s.row_top_k.copy_(torch.tensor([p[2] for p in self.row_params], dtype=torch.int32))
+            self.row_params_dirty = False
         s.run(n, T_, P_, K_, self.use_ras, pos_bound=max(pos))
         self.steps += 1
         self.frames_run += n * self.rows

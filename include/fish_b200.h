@@ -99,6 +99,11 @@ typedef struct {
     int32_t top_k;
     const void* uniforms;    /* optional injected bf16 draws [max_frames][B][2*vocab + (C-1)*codebook_size] */
     uint64_t seed;           /* Philox seed when uniforms == NULL */
+    /* per-request sampling parameters (a batch that mixes requests, scheduler.py): device arrays [B] that take the place
+     * of temperature / top_p / top_k for the request's normal draw (the RAS variant keeps its constants), or NULL */
+    const float* row_temperature;
+    const float* row_top_p;
+    const int32_t* row_top_k;
 } fsb_frame_args;
 
 /* n_frames back-to-back frames, no host synchronisation in between (CUDA graph replay when enabled). */

@@ -55,12 +55,28 @@ class FakeSession:
             self.frame_counter += 1
 
 
+class RowParamSession(FakeSession):
+    """A session with per-request sampling parameters (fsb_frame_args.row_*): records the arrays of every step."""
+
+    def use_row_parameters(self):
+        self.row_temperature = torch.ones((self.batch,), dtype=torch.float32)
+        self.row_top_p = torch.full((self.batch,), 0.9, dtype=torch.float32)
+        self.row_top_k = torch.full((self.batch,), 30, dtype=torch.int32)
+        self.row_calls = []
+
+    def run(self, n, temperature, top_p, top_k, use_ras, pos_bound=None):
+        self.row_calls.append((self.row_temperature.clone(), self.row_top_p.clone(), self.row_top_k.clone(),
+                               [int(d) for d in self.done]))
+        super().run(n, temperature, top_p, top_k, use_ras, pos_bound)
+
+
 class FakeModel:
     """Token at position p of the request whose prompt sums to h: main = SEM0 + (h + p) % CB, codes = (h + p + i) % CB;
     <|im_end|> at position eos_at(h) = prompt_len + 3 + h % 9."""
 
-    def __init__(self, max_rows=3):
+    def __init__(self, max_rows=3, row_params=False):
         self.max_rows = max_rows
+        self.row_params = row_params
         self.config = types.SimpleNamespace(num_codebooks=C, max_seq_len=S, im_end_id=IM_END, vocab_size=SEM0 + CB,
                                             semantic_begin_id=SEM0, semantic_end_id=SEM0 + CB - 1, codebook_size=CB)
         self.device = torch.device("cpu")
@@ -76,7 +92,7 @@ class FakeModel:
         self.max_batch_size, self.max_seq_len, self._cache_setup_done = rows, max_seq_len, True
 
     def session(self, batch, max_frames):
-        self._s = FakeSession(self, batch, max_frames)
+        self._s = (RowParamSession if self.row_params else FakeSession)(self, batch, max_frames)
         return self._s
 
     def prefill(self, cols, pos0, slot):
@@ -170,6 +186,30 @@ def test_sampling_parameters_group_batches_without_starvation():
     assert temps == [round(float(torch.tensor(0.7, dtype=torch.bfloat16)), 3), 1.0]
     for c in m._s.calls:                                                          # one value per step
         assert c[1] in (float(torch.tensor(0.7, dtype=torch.bfloat16)), 1.0)
+
+
+def test_requests_with_different_sampling_parameters_share_a_batch():
+    """With per-request parameter arrays nothing waits for the batch to drain: the three requests run together from the first
+    step, each row carrying its own (temperature, top_p, top_k) as generate() would round them; an out-of-range top_k fails
+    its request alone; every request still gets its own stream."""
+    m = FakeModel(max_rows=3, row_params=True)
+    b = ContinuousBatcher(m, chunk_frames=4)
+    assert b.per_row
+    items = [req(prompt(5, 1), temperature=0.7, top_p=0.8, top_k=20), req(prompt(6, 2), temperature=1.0),
+             req(prompt(7, 3), temperature=0.3, top_k=64), req(prompt(5, 4), top_k=65), req(prompt(5, 5), top_k=0)]
+    for it in items:
+        b.submit(it)
+    done = b.run_until_idle()
+    by_id = {id(it): res for it, res in done}
+    assert isinstance(by_id[id(items[3])], ValueError) and isinstance(by_id[id(items[4])], ValueError)
+    for it in items[:3]:
+        assert torch.equal(by_id[id(it)], expected(it.request["prompt"], 0))
+    t, p, k, idle = m._s.row_calls[0]
+    assert idle == [0, 0, 0]                                   # all three in flight in the very first step
+    bf = lambda v: float(torch.tensor(v, dtype=torch.bfloat16))
+    assert [float(x) for x in t] == [bf(0.7), 1.0, bf(0.3)]
+    assert [float(x) for x in p] == [bf(0.8), bf(0.9), bf(0.9)]
+    assert [int(x) for x in k] == [20, 30, 64]
 
 
 def test_bad_requests_fail_alone():

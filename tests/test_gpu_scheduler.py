@@ -114,3 +114,36 @@ def test_shared_prompt_prefix_is_copied_not_recomputed_and_changes_nothing():
         (_, want), = solo.run_until_idle()
         assert solo.shared_cols == 0
         assert torch.equal(got[id(it)].cpu(), want.cpu())
+
+
+def test_requests_with_their_own_sampling_parameters_share_a_batch():
+    """fsb_frame_args.row_temperature / row_top_p / row_top_k: three requests with different (temperature, top_p, top_k) decode
+    side by side and each gets, bit for bit, the frames it gets alone through the scalar parameters of the same call (real
+    sampling: top_k > 1, RAS on; the draws are the same record for every frame and row, so placement does not matter)."""
+    from fish_speech_b200.scheduler import ContinuousBatcher, GenerateRequest
+    cfg, m = _model(4)
+    params = [(0.7, 0.8, 20), (1.0, 0.9, 30), (0.3, 0.5, 3), (1.2, 0.95, 64)]
+    items = []
+    for i, (t, p, k) in enumerate(params):
+        pr = R.make_prompt(cfg, 7 + 2 * i, seed=800 + i, voice_span=3 if i % 2 else 0)
+        items.append(GenerateRequest(request=dict(prompt=pr, max_new_tokens=14, temperature=t, top_p=p, top_k=k),
+                                     response_queue=queue.Queue()))
+    b = ContinuousBatcher(m, chunk_frames=4, use_ras=True, ring_frames=32)
+    assert b.per_row
+    _same_draws_everywhere(b, cfg)
+    for it in items:
+        b.submit(it)
+    got = {id(it): res for it, res in b.run_until_idle()}
+    assert b.steps <= 5                                        # together, not one after the other
+    b.sess.check_device()
+    outs = []
+    for it in items:
+        solo = ContinuousBatcher(m, chunk_frames=4, use_ras=True, ring_frames=32)
+        solo.per_row = False                                   # the scalar parameters of fsb_frame_args
+        solo.sess.row_temperature = solo.sess.row_top_p = solo.sess.row_top_k = None
+        _same_draws_everywhere(solo, cfg)
+        solo.submit(it)
+        (_, want), = solo.run_until_idle()
+        assert torch.equal(got[id(it)].cpu(), want.cpu()), (it.request["temperature"], got[id(it)], want)
+        outs.append(want.cpu())
+    assert not torch.equal(outs[0][:, :8], outs[2][:, :8]) or not torch.equal(outs[1][:, :8], outs[3][:, :8])
