@@ -70,13 +70,24 @@ class _Row:
     hold: Optional[Tensor] = None  # streaming: the newest frame, held back until another one follows (the last is dropped)
 
 
+@dataclass
+class _Fill:
+    """A request whose prompt pass is under way (chunked prefill): columns [0, at) of `cols` are in its KV slot."""
+    item: GenerateRequest
+    prompt: Tensor
+    cols: Tensor                   # prompt[:, :-1]
+    cpu: Tensor                    # the same on the host, int32 (the record for prefix sharing)
+    at: int
+    budget: int
+
+
 class ContinuousBatcher:
     """The scheduling core, free of threads: `submit()` queues a request, `step()` admits what fits, runs one chunk of
     frames for all rows in flight and returns the requests that finished.  `model` is a DualARTransformerB200 built with
     max_rows >= `max_rows` (or anything with the same `prefill` / `session` / `config` surface: the CPU tests use a stand-in)."""
 
     def __init__(self, model, max_rows: Optional[int] = None, chunk_frames: int = 8, use_ras: bool = True,
-                 share_min: int = 32, ring_frames: int = 1024):
+                 share_min: int = 32, ring_frames: int = 1024, prefill_budget: Optional[int] = None):
         self.model = model
         self.rows = int(max_rows if max_rows is not None else model.max_rows)
         if self.rows < 1 or self.rows > model.max_rows:
@@ -105,6 +116,10 @@ class ContinuousBatcher:
             self.sess.use_row_parameters()
             self.row_params: List[Tuple[float, float, int]] = [(_as_bf16_float(1.0), _as_bf16_float(0.9), 30)] * self.rows
             self.row_params_dirty = True
+        # chunked prefill: at most `prefill_budget` prompt columns are computed between two chunks of frames while rows are
+        # decoding (None: a prompt pass always runs in one piece), so a long prompt does not stall the requests in flight
+        self.prefill_budget = None if prefill_budget is None else max(1, int(prefill_budget))
+        self.filling: Dict[int, _Fill] = {}
         self.waiting: Deque[GenerateRequest] = deque()
         self.active: Dict[int, _Row] = {}
         self.key: Optional[Tuple[float, float, int]] = None
@@ -126,7 +141,7 @@ class ContinuousBatcher:
         self.waiting.append(item)
 
     def idle(self) -> bool:
-        return not self.waiting and not self.active
+        return not self.waiting and not self.active and not self.filling
 
     @staticmethod
     def _key(req: dict) -> Tuple[float, float, int]:
@@ -138,7 +153,7 @@ class ContinuousBatcher:
         C1 = c.num_codebooks + 1
         failed = []
         s = self.sess
-        while self.waiting and len(self.active) < self.rows:
+        while self.waiting and len(self.active) + len(self.filling) < self.rows:
             item = self.waiting[0]
             try:
                 req = item.request
@@ -153,7 +168,7 @@ class ContinuousBatcher:
                 key = self._key(req)
                 if not 1 <= key[2] <= 64:
                     raise ValueError(f"top_k must be in [1, 64], got {key[2]}")
-                if not self.per_row and self.active and key != self.key:
+                if not self.per_row and (self.active or self.filling) and key != self.key:
                     break                # other sampling parameters: wait for the batch to drain, keep the order
                 max_new = int(req.get("max_new_tokens", 0) or 0)
                 budget = min(max_new, c.max_seq_len - T) if max_new else c.max_seq_len - T   # inference.py:267-274
@@ -162,21 +177,52 @@ class ContinuousBatcher:
                 failed.append((item, e))
                 continue
             self.waiting.popleft()
-            row = next(r for r in range(self.rows) if r not in self.active)
+            row = next(r for r in range(self.rows) if r not in self.active and r not in self.filling)
             self.key = key
             if self.per_row:
                 self.row_params[row] = key
                 self.row_params_dirty = True
-            self._fill_slot(row, prompt[:, :-1])              # KV slot `row` (slot = row) <- the prompt but its last column
-            s.cur_tokens[row].copy_(prompt[:, -1].to(device=s.cur_tokens.device, dtype=torch.int32))
-            s.ras_window[row].zero_()
-            self.park.pop(row, None)
-            self.active[row] = _Row(item=item, prompt_len=T, budget=budget)
+            cols = prompt[:, :-1]                             # KV slot `row` (slot = row) <- the prompt but its last column
+            cpu = cols.detach().to(device="cpu", dtype=torch.int32)
+            at = self._share_prefix(row, cpu)
+            self.resident.pop(row, None)                      # the slot is being rewritten: nobody copies from it meanwhile
+            # until its prompt is in, the row idles with the batch and writes K/V where it stands: behind the prompt columns
+            self.park[row] = T - 1
+            self.filling[row] = _Fill(item=item, prompt=prompt, cols=cols, cpu=cpu, at=at, budget=budget)
+            if self.prefill_budget is None or T - 1 + self.chunk > c.max_seq_len:
+                self._advance_fill(row, None)                 # in one piece (always, when there is no room to idle behind it)
+        self._advance_fills()
         return failed
 
-    def _fill_slot(self, row: int, cols: Tensor):
-        """Prompt pass of `cols` into KV slot `row`, minus the longest prefix that is already resident in some slot."""
-        cpu = cols.detach().to(device="cpu", dtype=torch.int32)
+    def _advance_fills(self):
+        """Spends the prompt-column budget of this chunk boundary on the requests being filled, oldest first; with nothing
+        decoding there is nobody to stall, so everything is computed."""
+        left = self.prefill_budget if (self.prefill_budget is not None and self.active) else None
+        for row in list(self.filling):
+            if left is not None and left <= 0:
+                break
+            left = self._advance_fill(row, left)
+
+    def _advance_fill(self, row: int, left: Optional[int]) -> Optional[int]:
+        f = self.filling[row]
+        s = self.sess
+        total = int(f.cols.shape[1])
+        n = total - f.at if left is None else min(total - f.at, left)
+        if n > 0 or total == 0:
+            self.model.prefill(f.cols[:, f.at: f.at + n], f.at, row)
+        f.at += n
+        if f.at >= total:                                     # the prompt is in: the row joins the batch
+            s.cur_tokens[row].copy_(f.prompt[:, -1].to(device=s.cur_tokens.device, dtype=torch.int32))
+            s.ras_window[row].zero_()
+            self.park.pop(row, None)
+            self.resident[row] = f.cpu
+            self.active[row] = _Row(item=f.item, prompt_len=total + 1, budget=f.budget)
+            del self.filling[row]
+        return None if left is None else left - n
+
+    def _share_prefix(self, row: int, cpu: Tensor) -> int:
+        """Copies into KV slot `row` the longest prefix of the prompt columns `cpu` that is already resident in some slot;
+        returns its length (the prompt pass starts there)."""
         n = int(cpu.shape[1])
         best_row, best = -1, 0
         if self.share_min > 0 and hasattr(self.model, "copy_kv_prefix"):
@@ -192,10 +238,9 @@ class ContinuousBatcher:
             best_row, best = -1, 0
         if best_row >= 0 and best_row != row:
             self.model.copy_kv_prefix(best_row, row, best)
-        self.model.prefill(cols[:, best:], best, row)
-        self.resident[row] = cpu
         self.prompt_cols += n
         self.shared_cols += best
+        return best
 
     # ------------------------------------------------------------------ one chunk
     def step(self) -> List[Tuple[GenerateRequest, Union[Tensor, Exception]]]:
@@ -264,7 +309,7 @@ class ContinuousBatcher:
                     self.park.pop(row, None)
                     self.resident.pop(row, None)
             # rows still in flight continue from the state the kernel left (cur_tokens, RAS window)
-        if not self.active:
+        if not self.active and not self.filling:
             self.key = None
         return out
 
@@ -288,7 +333,8 @@ def _deliver_partial(item: GenerateRequest, codes: Tensor):
 
 
 def launch_thread_safe_queue(checkpoint_path=None, device="cuda", precision=torch.bfloat16, compile: bool = False, *,
-                             model=None, max_rows: int = 8, chunk_frames: int = 8, max_length: Optional[int] = None) -> queue.Queue:
+                             model=None, max_rows: int = 8, chunk_frames: int = 8, max_length: Optional[int] = None,
+                             prefill_budget: Optional[int] = None) -> queue.Queue:
     """inference.py:748-799 with continuous batching: returns the input queue; put `GenerateRequest`s on it, `None` to stop
     the worker.  Either `checkpoint_path` (loaded with checkpoint.init_model, rows = max_rows) or a ready `model`."""
     input_queue: queue.Queue = queue.Queue()
@@ -304,7 +350,8 @@ def launch_thread_safe_queue(checkpoint_path=None, device="cuda", precision=torc
             dev = getattr(m, "device", None)
             if dev is not None and torch.device(dev).type == "cuda":
                 torch.cuda.set_device(dev)
-            batcher = ContinuousBatcher(m, max_rows=min(max_rows, m.max_rows), chunk_frames=chunk_frames)
+            batcher = ContinuousBatcher(m, max_rows=min(max_rows, m.max_rows), chunk_frames=chunk_frames,
+                                        prefill_budget=prefill_budget)
             batcher.on_partial = _deliver_partial
         except BaseException as e:  # noqa: BLE001
             init_error.append(e)
@@ -329,9 +376,10 @@ def launch_thread_safe_queue(checkpoint_path=None, device="cuda", precision=torc
                     _deliver(it, res)
             except Exception as e:  # noqa: BLE001 - a failed step fails every request in flight, the worker lives on
                 traceback.print_exc()
-                for r in list(batcher.active.values()):
+                for r in list(batcher.active.values()) + list(batcher.filling.values()):
                     _deliver(r.item, e)
                 batcher.active.clear()
+                batcher.filling.clear()
                 batcher.sess.done.fill_(1)
                 batcher.key = None
 

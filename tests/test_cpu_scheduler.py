@@ -212,6 +212,41 @@ def test_requests_with_different_sampling_parameters_share_a_batch():
     assert [int(x) for x in k] == [20, 30, 64]
 
 
+def test_long_prompts_are_filled_in_pieces_between_chunks():
+    """prefill_budget: while rows are decoding, at most that many prompt columns are computed per chunk boundary, so the
+    request in flight keeps producing frames while a long prompt comes in; every request still gets its own stream, and
+    with nothing in flight the prompt pass runs in one piece."""
+    m = FakeModel(max_rows=3)
+    sizes = []
+    real = m.prefill
+
+    def spy(cols, pos0, slot):
+        sizes.append((int(cols.shape[-1]), pos0, slot, decoding[0]))
+        real(cols, pos0, slot)
+    m.prefill = spy
+    decoding = [0]                                             # rows in flight when the chunk boundary began
+    b = ContinuousBatcher(m, chunk_frames=2, prefill_budget=5, share_min=0)
+    first = req(prompt(9, 50))
+    b.submit(first)
+    assert b.step() == [] and sizes == [(8, 0, 0, 0)]          # nobody to stall: one piece
+    long1, long2 = req(prompt(23, 51)), req(prompt(14, 52))
+    b.submit(long1)
+    b.submit(long2)
+    done, steps_while_filling = [], 0
+    while not b.idle():
+        filling_before = bool(b.filling) or bool(b.waiting)
+        decoding[0] = len(b.active)
+        done.extend(b.step())
+        steps_while_filling += int(filling_before and bool(b.filling))
+    assert steps_while_filling >= 2                            # decode chunks ran while prompts were still coming in
+    with_rows = [n for n, _, _, act in sizes[1:] if act > 0]
+    assert with_rows and max(with_rows) <= 5                   # the budget held whenever somebody was decoding
+    assert sum(n for n, _, slot, _ in sizes if slot == 1) == 22 and sum(n for n, _, slot, _ in sizes if slot == 2) == 13
+    by_id = {id(it): res for it, res in done}
+    for it in (first, long1, long2):
+        assert torch.equal(by_id[id(it)], expected(it.request["prompt"], 0))
+
+
 def test_bad_requests_fail_alone():
     m = FakeModel(max_rows=2)
     b = ContinuousBatcher(m, chunk_frames=3)

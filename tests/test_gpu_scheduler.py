@@ -147,3 +147,23 @@ def test_requests_with_their_own_sampling_parameters_share_a_batch():
         assert torch.equal(got[id(it)].cpu(), want.cpu()), (it.request["temperature"], got[id(it)], want)
         outs.append(want.cpu())
     assert not torch.equal(outs[0][:, :8], outs[2][:, :8]) or not torch.equal(outs[1][:, :8], outs[3][:, :8])
+
+
+def test_prompts_filled_in_pieces_give_the_same_frames():
+    """prefill_budget: prompt passes cut into pieces of at most 5 columns between chunks of frames, idle-while-filling rows
+    parked behind their prompt: every request gets bit for bit the frames of the one-piece prompt pass."""
+    from fish_speech_b200.scheduler import ContinuousBatcher
+    cfg, m = _model(4)
+    items = _requests(cfg, 8)
+    outs = []
+    for budget in (None, 5):
+        b = ContinuousBatcher(m, chunk_frames=4, use_ras=False, ring_frames=16, prefill_budget=budget, share_min=0)
+        _same_draws_everywhere(b, cfg)
+        for it in items:
+            b.submit(it)
+        outs.append({id(it): res.cpu() for it, res in b.run_until_idle()})
+        b.sess.check_device()
+        steps = b.steps
+    assert steps >= 1
+    for it in items:
+        assert torch.equal(outs[0][id(it)], outs[1][id(it)]), (outs[0][id(it)], outs[1][id(it)])

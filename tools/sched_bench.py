@@ -1,6 +1,6 @@
 """Continuous batching at the S2-Pro shape: N requests (prompts of 64-512 tokens, 48-192 frames each, <|im_end|> masked so the
 lengths are the budgets) through ContinuousBatcher with `rows` rows; delivered audio-s/s against the static many-row step.
-usage: python tools/sched_bench.py [rows] [requests] [chunk] [voice]     voice > 0: every prompt starts with the same `voice`
+usage: python tools/sched_bench.py [rows] [requests] [chunk] [voice] [share_min] [prefill_budget]     voice > 0: every prompt starts with the same `voice`
 columns (a reference voice), followed by its own 32-128 columns: the prefix is computed once and copied afterwards"""
 import json
 import queue
@@ -34,11 +34,12 @@ for i in range(n_req):
     reqs.append(GenerateRequest(request=dict(prompt=p.to(dev), max_new_tokens=F, temperature=0.8,
                                              top_p=0.8, top_k=30), response_queue=queue.Queue()))
 share = int(sys.argv[5]) if len(sys.argv) > 5 else 32
-b = ContinuousBatcher(model, chunk_frames=chunk, share_min=share)
+budget = int(sys.argv[6]) if len(sys.argv) > 6 and int(sys.argv[6]) > 0 else None     # prompt columns per chunk boundary
+b = ContinuousBatcher(model, chunk_frames=chunk, share_min=share, prefill_budget=budget)
 for it in reqs[:rows]:       # warm-up: graph capture, tensor maps
     b.submit(it)
 b.step()
-b.active.clear(); b.waiting.clear(); b.resident.clear(); b.park.clear(); b.key = None
+b.active.clear(); b.waiting.clear(); b.filling.clear(); b.resident.clear(); b.park.clear(); b.key = None
 b.steps = b.frames_run = b.frames_kept = b.prompt_cols = b.shared_cols = 0
 torch.cuda.synchronize()
 t0 = time.perf_counter()
@@ -48,7 +49,7 @@ done = b.run_until_idle()
 torch.cuda.synchronize()
 dt = time.perf_counter() - t0
 frames = sum(int(c.shape[1]) + 1 for _, c in done)
-print(json.dumps({"rows": rows, "requests": n_req, "chunk_frames": chunk, "wall_s": round(dt, 3), "frames_delivered": frames,
+print(json.dumps({"rows": rows, "requests": n_req, "chunk_frames": chunk, "prefill_budget": budget, "wall_s": round(dt, 3), "frames_delivered": frames,
                   "audio_s_per_s": round(frames * FRAME_SEC / dt, 1), "steps": b.steps,
                   "row_occupancy": round(b.frames_kept / max(1, b.frames_run), 3),
                   "ms_per_chunk_step": round(dt / max(1, b.steps) * 1e3, 2),
