@@ -185,7 +185,7 @@ def init_model(checkpoint_path, device, precision=torch.bfloat16, compile: bool 
 
 # ----------------------------------------------------------------------------------------------- codec
 def normalise_codec_state_dict(sd: Dict[str, Tensor]) -> Dict[str, Tensor]:
-    """dac/inference.py:29-42 ("state_dict" wrapper, "generator." prefix) plus both weight-norm spellings: the decoder's convs
+    """dac/inference.py:29-42 ("state_dict" wrapper, "generator." prefix) plus both weight-norm spellings: the decoder's and the encoder's convs
     are read as `...conv.parametrizations.weight.original0/1`, the descript quantizers' projections as `...weight_g/weight_v`
     (fish_speech_b200/dac.py: pack_weights); a checkpoint saved in the other spelling is renamed, never re-computed."""
     if "state_dict" in sd:
@@ -194,21 +194,23 @@ def normalise_codec_state_dict(sd: Dict[str, Tensor]) -> Dict[str, Tensor]:
         sd = {k.replace("generator.", ""): v for k, v in sd.items() if "generator." in k}
     out: Dict[str, Tensor] = {}
     for k, v in sd.items():
-        if k.startswith("decoder.") and k.endswith(".weight_g"):
+        if k.startswith(("decoder.", "encoder.")) and k.endswith(".weight_g"):
             k = k[: -len("weight_g")] + "parametrizations.weight.original0"
-        elif k.startswith("decoder.") and k.endswith(".weight_v"):
+        elif k.startswith(("decoder.", "encoder.")) and k.endswith(".weight_v"):
             k = k[: -len("weight_v")] + "parametrizations.weight.original1"
-        elif "out_proj.parametrizations.weight.original0" in k:
+        elif "_proj.parametrizations.weight.original0" in k:       # the quantizers' in_proj / out_proj
             k = k.replace("parametrizations.weight.original0", "weight_g")
-        elif "out_proj.parametrizations.weight.original1" in k:
+        elif "_proj.parametrizations.weight.original1" in k:
             k = k.replace("parametrizations.weight.original1", "weight_v")
         out[k] = v
     return out
 
 
 def load_codec(checkpoint_path, device="cuda", config=None, **kw):
-    """dac/inference.py:23-48 on the engine (decode side): codec.pth -> DACB200 with `from_indices`, `sample_rate`, `device`.
-    `config`: the modded_dac_vq.yaml values (default: fish_speech_b200.dac.DACConfig, which restates that file)."""
+    """dac/inference.py:23-48 on the engine: codec.pth -> DACB200 with `from_indices`, `sample_rate`, `device`, and `encode`
+    when the file carries the encode side (encoder.*, quantizer.downsample.*, quantizer.pre_module.*, in_proj.*: the released
+    codec.pth does; `can_encode` says).  `config`: the modded_dac_vq.yaml values (default: fish_speech_b200.dac.DACConfig,
+    which restates that file)."""
     from .dac import DACB200, DACConfig
     sd = torch.load(checkpoint_path, map_location="cpu", mmap=True, weights_only=True)
     return DACB200(config or DACConfig(), normalise_codec_state_dict(sd), device=device, **kw)

@@ -124,6 +124,19 @@ def test_codec_state_dict_normalisation():
     out = CK.normalise_codec_state_dict(sd)
     assert set(out) == {"decoder.model.0.conv.parametrizations.weight.original0", "decoder.model.0.conv.parametrizations.weight.original1",
                         "quantizer.quantizer.quantizers.0.out_proj.weight_g"}
+    # the encode side's keys take the same two spellings, and a whole encode-side state dict is recognised as one
+    enc = {"generator.encoder.block.0.conv.weight_g": g, "generator.encoder.block.0.conv.weight_v": v,
+           "generator.quantizer.semantic_quantizer.quantizers.0.in_proj.parametrizations.weight.original1": v}
+    out = CK.normalise_codec_state_dict(enc)
+    assert set(out) == {"encoder.block.0.conv.parametrizations.weight.original0", "encoder.block.0.conv.parametrizations.weight.original1",
+                        "quantizer.semantic_quantizer.quantizers.0.in_proj.weight_v"}
+    from fish_speech_b200.dac import DACConfig, encode_state_dict_shapes, has_encode_side, state_dict_shapes
+    c = DACConfig()
+    full = {**state_dict_shapes(c), **encode_state_dict_shapes(c)}
+    assert has_encode_side(full) and not has_encode_side(state_dict_shapes(c))
+    assert full["encoder.block.4.block.4.conv.parametrizations.weight.original1"] == (1024, 512, 16)       # modded_dac.py:655-663
+    assert full["encoder.block.4.block.5.layers.3.attention.wqkv.weight"] == (3072, 1024)                    # :636-650
+    assert full["quantizer.downsample.1.0.conv.weight"] == (1024, 1024, 2)                                    # rvq.py:249-261
 
 
 @pytest.mark.skipif(not REF.exists(), reason="the reference tree is only in the build container")
