@@ -361,7 +361,9 @@ class DACB200:
     encode side's weights, encode (reference voice -> codes)."""
 
     def __init__(self, config, state_dict: Dict[str, Tensor], device="cuda:0", max_batch: int = 4, max_frames: int = 1024,
-                 operand: str = "f16"):
+                 operand: str = "f16", encode_side: Optional[bool] = None):
+        """`encode_side`: None = bind the encode side when the state dict has it (~0.8 GB of fp32 weights at the full config),
+        False = decode only, True = required (KeyError when it is missing)."""
         _lib.require_cuda()
         self.lib = _lib.load()
         self.config = c = DACConfig.from_any(config)
@@ -392,7 +394,7 @@ class DACB200:
             # box reads); the transformer's gate/up matrix with its columns interleaved (SwiGLU in the GEMM epilogue)
             self.operand = operand
             hdt = torch.float16 if operand == "f16" else torch.bfloat16
-            self.can_encode = has_encode_side(dev_sd)
+            self.can_encode = has_encode_side(dev_sd) if encode_side is None else bool(encode_side)
             for k in [k for k, v in self.weights.items() if v.dim() == 3 and k != "dec.out_w"] + \
                      [k for k in self.weights if k.startswith("tf.") and k.split(".")[-1] in ("wqkv", "wo", "w13", "w2")] + \
                      [k for k in self.weights if k.endswith(("pw1_w", "pw2_w"))]:
