@@ -77,7 +77,7 @@ class _Fill:
     prompt: Tensor
     cols: Tensor                   # prompt[:, :-1]
     cpu: Tensor                    # the same on the host, int32 (the record for prefix sharing)
-    at: int
+    at: int                        # -1: not started (the shared prefix is looked up when the first piece runs)
     budget: int
 
 
@@ -184,38 +184,44 @@ class ContinuousBatcher:
                 self.row_params_dirty = True
             cols = prompt[:, :-1]                             # KV slot `row` (slot = row) <- the prompt but its last column
             cpu = cols.detach().to(device="cpu", dtype=torch.int32)
-            at = self._share_prefix(row, cpu)
-            self.resident.pop(row, None)                      # the slot is being rewritten: nobody copies from it meanwhile
             # until its prompt is in, the row idles with the batch and writes K/V where it stands: behind the prompt columns
+            # (what the slot held before survives in front of that spot only)
             self.park[row] = T - 1
-            self.filling[row] = _Fill(item=item, prompt=prompt, cols=cols, cpu=cpu, at=at, budget=budget)
+            if row in self.resident:
+                self.resident[row] = self.resident[row][:, : T - 1]
+            self.filling[row] = _Fill(item=item, prompt=prompt, cols=cols, cpu=cpu, at=-1, budget=budget)
             if self.prefill_budget is None or T - 1 + self.chunk > c.max_seq_len:
                 self._advance_fill(row, None)                 # in one piece (always, when there is no room to idle behind it)
         self._advance_fills()
         return failed
 
     def _advance_fills(self):
-        """Spends the prompt-column budget of this chunk boundary on the requests being filled, oldest first; with nothing
-        decoding there is nobody to stall, so everything is computed."""
-        left = self.prefill_budget if (self.prefill_budget is not None and self.active) else None
+        """Spends the prompt-column budget of this chunk boundary on the requests being filled, oldest first; while nothing
+        is decoding there is nobody to stall, so the oldest prompt is computed in one piece."""
+        spent = 0
         for row in list(self.filling):
-            if left is not None and left <= 0:
+            if self.prefill_budget is None or not self.active:
+                self._advance_fill(row, None)                 # (the request it lets in is decoding from here on: budget next)
+                continue
+            if spent >= self.prefill_budget:
                 break
-            left = self._advance_fill(row, left)
+            spent = self.prefill_budget - self._advance_fill(row, self.prefill_budget - spent)
 
     def _advance_fill(self, row: int, left: Optional[int]) -> Optional[int]:
         f = self.filling[row]
         s = self.sess
         total = int(f.cols.shape[1])
+        if f.at < 0:                                          # first piece: start behind what some slot already holds
+            f.at = self._share_prefix(row, f.cpu)
         n = total - f.at if left is None else min(total - f.at, left)
         if n > 0 or total == 0:
             self.model.prefill(f.cols[:, f.at: f.at + n], f.at, row)
         f.at += n
+        self.resident[row] = f.cpu[:, : f.at]                 # what is in the slot so far can already be shared
         if f.at >= total:                                     # the prompt is in: the row joins the batch
             s.cur_tokens[row].copy_(f.prompt[:, -1].to(device=s.cur_tokens.device, dtype=torch.int32))
             s.ras_window[row].zero_()
             self.park.pop(row, None)
-            self.resident[row] = f.cpu
             self.active[row] = _Row(item=f.item, prompt_len=total + 1, budget=f.budget)
             del self.filling[row]
         return None if left is None else left - n

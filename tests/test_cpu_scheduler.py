@@ -288,6 +288,18 @@ def test_requests_that_start_alike_share_the_prompt_pass():
     total = sum(it.request["prompt"].shape[1] - 1 for it in items)
     assert b.prompt_cols == total and m.computed == total - b.shared_cols
     assert b.shared_cols >= 6 * 40 and m.copied > 0        # all but the first took the voice prefix
+    # the same with the prompt passes cut into pieces: requests that arrive together still share (the prefix is looked up when
+    # a request's first piece runs, and what a slot holds so far can already be copied)
+    m2 = FakeModel(max_rows=3)
+    b2 = ContinuousBatcher(m2, chunk_frames=4, share_min=16, prefill_budget=16)
+    items2 = [req(it.request["prompt"], max_new=5) for it in items]
+    for it in items2:
+        b2.submit(it)
+    got2 = {id(it): res for it, res in b2.run_until_idle()}
+    for it in items2:
+        assert torch.equal(got2[id(it)], expected(it.request["prompt"], 5))
+    assert b2.prompt_cols == total and m2.computed == total - b2.shared_cols
+    assert b2.shared_cols >= 6 * 16 and m2.copied > 0
     # every resident record still describes what is in the slot: the prompt-pass columns were not overwritten by idle rows
     for row, cols in b.resident.items():
         assert m.kv[row][: cols.shape[1]] == [int(x) for x in cols.sum(0)]

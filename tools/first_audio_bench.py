@@ -1,6 +1,6 @@
 """Time to first audio at the S2-Pro shape: one request (a 384-column reference voice + 64 own columns) through the scheduler
 with request["stream"], its code portions through DACStream; prints the time from submit to the first waveform samples on the
-host, and the delivered rate after that.  usage: python tools/first_audio_bench.py [rows] [chunk_frames] [frames]
+host, and the delivered rate after that.  usage: python tools/first_audio_bench.py [rows] [chunk_frames] [frames] [prefill_budget]
 (rows > 1: the other rows run requests of their own at the same time)"""
 import json
 import queue
@@ -18,6 +18,7 @@ from fish_speech_b200.scheduler import ContinuousBatcher, GenerateRequest  # noq
 rows = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 chunk = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 frames = int(sys.argv[3]) if len(sys.argv) > 3 else 128
+budget = int(sys.argv[4]) if len(sys.argv) > 4 and int(sys.argv[4]) > 0 else None      # prompt columns per chunk boundary
 dev = torch.device("cuda", 0)
 cfg = s2_pro_config(max_seq_len=1024)
 model = DualARTransformerB200(cfg, synth_state_dict(cfg, dev, seed=0), device=dev, max_rows=rows)
@@ -36,7 +37,7 @@ def make(i, stream=False):
 
 
 def run(reqs):
-    b = ContinuousBatcher(model, chunk_frames=chunk)
+    b = ContinuousBatcher(model, chunk_frames=chunk, prefill_budget=budget)
     stream = dac.stream(batch=1)
     marks = []                                     # (host time, frames of audio on the host so far)
     got = [0]
@@ -62,7 +63,7 @@ def run(reqs):
 run([make(i, i == 0) for i in range(rows)])                # warm-up: graph capture, tensor maps, rope tables
 t0, marks, t1 = run([make(100 + i, i == 0) for i in range(rows)])
 first = marks[0]
-print(json.dumps({"rows": rows, "chunk_frames": chunk, "prompt_columns": 448, "frames": frames,
+print(json.dumps({"rows": rows, "chunk_frames": chunk, "prefill_budget": budget, "prompt_columns": 448, "frames": frames,
                   "first_audio_ms": round((first[0] - t0) * 1e3, 2), "first_audio_frames": first[1],
                   "first_audio_seconds_of_audio": round(first[1] * FRAME_SEC, 3),
                   "portions": len(marks), "wall_ms": round((t1 - t0) * 1e3, 1),
