@@ -29,6 +29,7 @@ struct fsb_dac {
     int staged_epi = 1;   // tcv_kernel: 16-bit-only epilogues (the decoder's convs) through shared memory (coalesced residual loads / stores)
     int tiled_small = 1;  // window attention and the output conv of the tcgen05 pipeline as shared-memory-tiled kernels (0: per-query / per-sample)
     int force_simt = 0;  // tcgen05 pipeline with every GEMM on the CUDA-core twin kernel (cross-check)
+    int conv_group = 0;  // tcv_kernel: ring slots per barrier round (0: automatic = 2 for convs with taps, 1: one slot per round)
     // encode side (DAC.encode): set through fsb_dac_set_option ("enc_dim", "enc_n_rates", "enc_rate0..3", "enc_tf0..3",
     // "enc_window", "enc_head_dim"); 0 = not configured
     int enc_dim = 0, enc_n = 0, enc_rate[4] = {0, 0, 0, 0}, enc_tf[4] = {0, 0, 0, 0}, enc_window = 512, enc_hd = 64;
@@ -123,6 +124,7 @@ struct Runner {
         a.out16 = out16; a.out32 = out32; a.ld16 = act == TCV_ACT_SWIGLU ? N / 2 : N; a.ld32 = N; a.ldres = N;
         a.res16 = res16; a.out16r = out16r; a.ld16r = N;
         a.staged_ok = h->staged_epi;
+        a.kgroup = h->conv_group;
         if (rc) return;
         cudaError_t e;
         if (h->force_simt || !tcv_tc_ok(Cin, N)) {
@@ -215,6 +217,7 @@ int fsb_dac_set_option(fsb_dac* h, const char* name, int64_t value) {
     else if (n == "force_simt") h->force_simt = (int)value;
     else if (n == "tiled_small") h->tiled_small = (int)value;
     else if (n == "staged_epi") h->staged_epi = (int)value;
+    else if (n == "conv_group") { if (value < 0 || value > 3) return dfail(h, "conv_group must be 0..3"); h->conv_group = (int)value; }
     else if (n == "pos_offset") { if (value < 0) return dfail(h, "pos_offset < 0"); h->pos_offset = (int)value; }
     else if (n == "enc_dim") h->enc_dim = (int)value;
     else if (n == "enc_n_rates") { if (value < 1 || value > 4) return dfail(h, "enc_n_rates must be 1..4"); h->enc_n = (int)value; }

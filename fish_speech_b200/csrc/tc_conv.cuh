@@ -64,6 +64,7 @@ struct TcConvArgs {
     int vec_ok;          // 1: every row pitch / pointer allows the 16-byte vector paths of the epilogue
     int staged_ok;       // caller's switch for the staged epilogue (option "staged_epi")
     int staged;          // 1: the 16-bit-only epilogue through shared memory (set by tcv_launch: see tcv_kernel)
+    int kgroup;          // ring slots filled / consumed per barrier round (set by tcv_plan; nst is a multiple of it)
     int round_lin;       // 1: round the reduction to the 16-bit type BEFORE the residual add (the bf16 LLM's rounding points:
                          //    one rounding per Linear, one per add, llama.py:838-843)
 };
@@ -437,6 +438,7 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
                 const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
                 const int t0 = tt * TCV_BM, n0 = tn * BN;
                 const int kc_lo = sp * a.kper, kc_hi = min(a.kchunks, kc_lo + a.kper);
+                if (a.kgroup == 1) {
                 for (int j = 0; j < a.taps; ++j) {
                     const int trow = t0 - (a.taps - 1 - j) * a.dil;  // negative rows: out of bounds = zeros = causal padding
                     for (int kc = kc_lo; kc < kc_hi; ++kc) {
@@ -447,6 +449,29 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
                         tcv_tma_load_3d(st + TCV_A_BYTES, &tmW, bar, kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
                         if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; }
                     }
+                }
+                } else {
+                // reduction steps (tap j, channel chunk kc) in groups of a.kgroup ring slots behind ONE barrier pair: what a
+                // narrow 7-tap layer costs is this thread's (and the issuer's) latency per barrier round, not bytes or MMAs
+                // (measured by switching loads / MMAs / the epilogue off: DESIGN.md 5.4).  The per-slot loop above is kept
+                // as it was for kgroup = 1: anything added to it shows 1:1 in the plain GEMMs' time.
+                const int nk = a.taps * (kc_hi - kc_lo);
+                int j = 0, kc = kc_lo;
+                for (int i = 0; i < nk; i += a.kgroup) {
+                    const int cnt = min(a.kgroup, nk - i);
+                    mbar_wait(&empty_bar[s], ph);
+                    const uint32_t bar = smem_u32(&full_bar[s]);
+                    mbar_expect_tx(&full_bar[s], (uint32_t)cnt * STAGE);
+                    for (int c = 0; c < cnt; ++c) {
+                        const uint32_t st = sbase + (s + c) * STAGE;
+                        const int trow = t0 - (a.taps - 1 - j) * a.dil;  // negative rows: out of bounds = zeros = causal padding
+                        tcv_tma_load_3d(st, &tmA, bar, kc * TCV_BK, trow, b, TCV_POLICY_EVICT_NORMAL);  // re-read by the other taps / column tiles: keep in L2
+                        tcv_tma_load_3d(st + TCV_A_BYTES, &tmW, bar, kc * TCV_BK, n0, j, RG_POLICY_EVICT_LAST);
+                        if (++kc == kc_hi) { kc = kc_lo; ++j; }
+                    }
+                    s += (uint32_t)a.kgroup;
+                    if (s >= (uint32_t)a.nst) { s = 0; ph ^= 1u; }
+                }
                 }
             }
         }
@@ -465,6 +490,7 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             mbar_wait(&tempty_bar[buf], ((iseg >> 1) & 1u) ^ 1u);  // the epilogue has drained this accumulator
             tc_fence_after();
             const uint32_t d = tmem + buf * BN;
+            if (a.kgroup == 1) {
             for (int i = 0; i < nk; ++i) {
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
@@ -479,6 +505,32 @@ tcv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
                 __syncwarp();
                 if (++s == (uint32_t)a.nst) { s = 0; ph ^= 1u; adesc = tc_smem_desc(sbase); bdesc = tc_smem_desc(sbase + TCV_A_BYTES); }
                 else { adesc += dstep; bdesc += dstep; }
+            }
+            } else {
+            for (int i = 0; i < nk; i += a.kgroup) {
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                if (lane == 0) {
+                    // (skipping the zero-filled 16-channel steps of a last chunk past Cin - the 96-channel block - was measured:
+                    // no gain, the layer is not bound by the number of MMAs)
+#pragma unroll
+                    for (int k = 0; k < TCV_BK / 16; ++k)
+                        tc_mma_bf16(d, adesc + 2 * k, bdesc + 2 * k, IDESC, (i > 0 || k > 0) ? 1u : 0u);
+                    const int cnt = min(a.kgroup, nk - i);
+                    uint64_t ad = adesc, bd = bdesc;
+                    for (int c = 1; c < cnt; ++c) {      // the group's other ring slots
+                        ad += dstep; bd += dstep;
+#pragma unroll
+                        for (int k = 0; k < TCV_BK / 16; ++k)
+                            tc_mma_bf16(d, ad + 2 * k, bd + 2 * k, IDESC, 1u);
+                    }
+                    tc_commit(&empty_bar[s]);
+                }
+                __syncwarp();
+                s += (uint32_t)a.kgroup;
+                if (s >= (uint32_t)a.nst) { s = 0; ph ^= 1u; adesc = tc_smem_desc(sbase); bdesc = tc_smem_desc(sbase + TCV_A_BYTES); }
+                else { adesc += dstep * (uint64_t)a.kgroup; bdesc += dstep * (uint64_t)a.kgroup; }
+            }
             }
             if (lane == 0) tc_commit(&tfull_bar[buf]);
             __syncwarp();
@@ -642,6 +694,11 @@ inline void tcv_plan(TcConvArgs& a, int bn) {
     }
     a.n_tiles = a.B * a.tiles_t * a.tiles_n * a.ksplit;
     a.nst = tcv_stages_for(bn, a.staged != 0, a.res16 != nullptr);
+    // a.kgroup on entry: the caller's wish (0 = automatic: 2 for convs with more than one tap, 1 for plain GEMMs)
+    static const int kg_all = getenv("FSB_TCV_KGROUP_ALL") ? atoi(getenv("FSB_TCV_KGROUP_ALL")) : 0;   // measurement switch
+    const int want = a.kgroup > 0 ? a.kgroup : ((a.taps > 1 || kg_all) ? 2 : 1);
+    a.kgroup = 1;
+    if (want >= 2 && a.nst >= 2 * want) { a.kgroup = want; a.nst -= a.nst % want; }
 }
 inline bool tcv_vec_ok(const TcConvArgs& a) {
     auto al = [](const void* p) { return (((uintptr_t)p) & 15) == 0; };
