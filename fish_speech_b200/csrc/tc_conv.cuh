@@ -695,8 +695,7 @@ inline void tcv_plan(TcConvArgs& a, int bn) {
     a.n_tiles = a.B * a.tiles_t * a.tiles_n * a.ksplit;
     a.nst = tcv_stages_for(bn, a.staged != 0, a.res16 != nullptr);
     // a.kgroup on entry: the caller's wish (0 = automatic: 2 for convs with more than one tap, 1 for plain GEMMs)
-    static const int kg_all = getenv("FSB_TCV_KGROUP_ALL") ? atoi(getenv("FSB_TCV_KGROUP_ALL")) : 0;   // measurement switch
-    const int want = a.kgroup > 0 ? a.kgroup : ((a.taps > 1 || kg_all) ? 2 : 1);
+    const int want = a.kgroup > 0 ? a.kgroup : (a.taps > 1 ? 2 : 1);
     a.kgroup = 1;
     if (want >= 2 && a.nst >= 2 * want) { a.kgroup = want; a.nst -= a.nst % want; }
 }
