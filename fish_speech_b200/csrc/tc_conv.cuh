@@ -85,11 +85,10 @@ template <> struct Tcv16<false> {
 // two values -> one 32-bit word (lo = a), same rounding / saturation as pack(): one two-way convert instead of two + shifts
 template <bool F16>
 __device__ __forceinline__ uint32_t tcv_pack2(float a, float b) {
-    if (F16) {
-        a = fminf(fmaxf(a, -65504.f), 65504.f);
-        b = fminf(fmaxf(b, -65504.f), 65504.f);
-        const __half2 h = __floats2half2_rn(a, b);
-        return *reinterpret_cast<const uint32_t*>(&h);
+    if (F16) {   // one instruction: round to nearest even, +-65504 past the range (F2FP.SATFINITE.F16.F32.PACK_AB)
+        uint32_t r;
+        asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+        return r;
     }
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<const uint32_t*>(&h);
@@ -285,23 +284,30 @@ __device__ __forceinline__ void tcv_staged_epilogue(const TcConvArgs& a, uint32_
     const uint32_t tlane = (uint32_t)(lg * 32) << 16;
     const int myrow = lg * 32 + lane;                        // row of the tile this thread reads from TMEM
     const uint16_t* res = reinterpret_cast<const uint16_t*>(a.res16);
+    const int row0 = et / CPR, c0 = et % CPR;                // this thread's first 16-byte piece of a panel (then + NT pieces)
 
     // residual panel `p` of tile `tile` -> rbuf[slot]: coalesced 16-byte pieces, rows past the end of the clip skipped
     auto request = [&](int tile, int p, int slot) {
         if (res == nullptr || tile >= a.n_tiles) return;
         const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
         const int col0 = tn * BN + p * PW;
+        int row = row0, c = c0;
         for (int i = et; i < TCV_BM * CPR; i += NT) {
-            const int row = i / CPR, c = i % CPR, t = tt * TCV_BM + row;
+            const int t = tt * TCV_BM + row;
             if (t < a.T) tcv_cp_async16(epi + (size_t)slot * TCV_BM * RB + (size_t)row * RB + c * 16, res + ((size_t)b * a.T + t) * a.ldres + col0 + c * 8);
+            row += NT / CPR; c += NT % CPR;
+            if (c >= CPR) { c -= CPR; ++row; }
         }
     };
     // staging panel -> global, whole rows of the panel as contiguous runs
     auto copy_out = [&](uint16_t* base, int ld, int b, int tt, int col0) {
+        int row = row0, c = c0;
         for (int i = et; i < TCV_BM * CPR; i += NT) {
-            const int row = i / CPR, c = i % CPR, t = tt * TCV_BM + row;
+            const int t = tt * TCV_BM + row;
             if (t < a.T)
                 *reinterpret_cast<uint4*>(base + ((size_t)b * a.T + t) * ld + col0 + c * 8) = *reinterpret_cast<const uint4*>(sbuf + (size_t)row * RB + c * 16);
+            row += NT / CPR; c += NT % CPR;
+            if (c >= CPR) { c -= CPR; ++row; }
         }
     };
     uint32_t iseg = 0, g = 0;   // tiles / panels done by this CTA
