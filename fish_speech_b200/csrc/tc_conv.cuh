@@ -286,29 +286,40 @@ __device__ __forceinline__ void tcv_staged_epilogue(const TcConvArgs& a, uint32_
     const uint16_t* res = reinterpret_cast<const uint16_t*>(a.res16);
     const int row0 = et / CPR, c0 = et % CPR;                // this thread's first 16-byte piece of a panel (then + NT pieces)
 
+    // The cooperative copies (residual panel in, staging panel out) move 16-byte pieces, NT at a time; which pieces a thread
+    // takes is the same for every panel, so their (row, offset) pairs are worked out once: the loops below were a third of
+    // the kernel's instructions when they derived them per piece (ncu source page, 1-tap layers: issue-bound epilogue).
+    constexpr int ITER = TCV_BM * CPR / NT;
+    static_assert(ITER * NT == TCV_BM * CPR, "whole rounds of pieces");
+    int prow[ITER], pcol8[ITER], soff[ITER];
+    {
+        int row = row0, c = c0;
+#pragma unroll
+        for (int k = 0; k < ITER; ++k) {
+            prow[k] = row; pcol8[k] = c * 8; soff[k] = row * (int)RB + c * 16;
+            row += NT / CPR; c += NT % CPR;
+            if (c >= CPR) { c -= CPR; ++row; }
+        }
+    }
     // residual panel `p` of tile `tile` -> rbuf[slot]: coalesced 16-byte pieces, rows past the end of the clip skipped
     auto request = [&](int tile, int p, int slot) {
         if (res == nullptr || tile >= a.n_tiles) return;
         const int tn = tile % a.tiles_n, r = tile / a.tiles_n, tt = r % a.tiles_t, b = r / a.tiles_t;
-        const int col0 = tn * BN + p * PW;
-        int row = row0, c = c0;
-        for (int i = et; i < TCV_BM * CPR; i += NT) {
-            const int t = tt * TCV_BM + row;
-            if (t < a.T) tcv_cp_async16(epi + (size_t)slot * TCV_BM * RB + (size_t)row * RB + c * 16, res + ((size_t)b * a.T + t) * a.ldres + col0 + c * 8);
-            row += NT / CPR; c += NT % CPR;
-            if (c >= CPR) { c -= CPR; ++row; }
-        }
+        const uint16_t* gb = res + ((size_t)b * a.T + (size_t)tt * TCV_BM) * a.ldres + tn * BN + p * PW;
+        uint8_t* sb = epi + (size_t)slot * TCV_BM * RB;
+        const int left = a.T - tt * TCV_BM;
+#pragma unroll
+        for (int k = 0; k < ITER; ++k)
+            if (prow[k] < left) tcv_cp_async16(sb + soff[k], gb + (size_t)prow[k] * a.ldres + pcol8[k]);
     };
     // staging panel -> global, whole rows of the panel as contiguous runs
     auto copy_out = [&](uint16_t* base, int ld, int b, int tt, int col0) {
-        int row = row0, c = c0;
-        for (int i = et; i < TCV_BM * CPR; i += NT) {
-            const int t = tt * TCV_BM + row;
-            if (t < a.T)
-                *reinterpret_cast<uint4*>(base + ((size_t)b * a.T + t) * ld + col0 + c * 8) = *reinterpret_cast<const uint4*>(sbuf + (size_t)row * RB + c * 16);
-            row += NT / CPR; c += NT % CPR;
-            if (c >= CPR) { c -= CPR; ++row; }
-        }
+        uint16_t* gb = base + ((size_t)b * a.T + (size_t)tt * TCV_BM) * ld + col0;
+        const int left = a.T - tt * TCV_BM;
+#pragma unroll
+        for (int k = 0; k < ITER; ++k)
+            if (prow[k] < left)
+                *reinterpret_cast<uint4*>(gb + (size_t)prow[k] * ld + pcol8[k]) = *reinterpret_cast<const uint4*>(sbuf + soff[k]);
     };
     uint32_t iseg = 0, g = 0;   // tiles / panels done by this CTA
     int tn_loaded = -1;
