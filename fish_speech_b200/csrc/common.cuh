@@ -5,18 +5,43 @@
 #include <stdint.h>
 
 #include <mutex>
+#include <condition_variable>
+#include <map>
 #include <set>
 #include <utility>
 // Function attributes (dynamic shared memory opt-in) are per device: one-time setup is keyed by (current device, key) so
-// that a thread-per-GPU host sets them on every device it uses.  true = first call for this key on the current device.
-inline bool fsb_first_on_device(int key) {
-    static std::mutex mu;
-    static std::set<std::pair<int, int>> seen;
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return true;
-    std::lock_guard<std::mutex> lock(mu);
-    return seen.insert(std::make_pair(dev, key)).second;
-}
+// that a thread-per-GPU host sets them on every device it uses.  `first` is true for the first thread that asks for this
+// key on the current device; it does the setup while the object lives.  Any other thread that asks meanwhile WAITS until
+// that setup is finished (two host threads starting on a cold device: the second must not launch before the first has set
+// the attribute).
+struct FsbOnce {
+    bool first = true;
+    FsbOnce(int key) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return;          // no device: the caller's own CUDA call reports it
+        id_ = std::make_pair(dev, key);
+        tracked_ = true;
+        std::unique_lock<std::mutex> lock(mu());
+        auto it = state().find(id_);
+        if (it == state().end()) { state()[id_] = 1; return; }  // 1: being set up by this thread
+        first = false;
+        cv().wait(lock, [&] { return state()[id_] == 2; });
+    }
+    ~FsbOnce() {
+        if (!tracked_ || !first) return;
+        { std::lock_guard<std::mutex> lock(mu()); state()[id_] = 2; }
+        cv().notify_all();
+    }
+    FsbOnce(const FsbOnce&) = delete;
+    FsbOnce& operator=(const FsbOnce&) = delete;
+
+private:
+    std::pair<int, int> id_{0, 0};
+    bool tracked_ = false;
+    static std::mutex& mu() { static std::mutex m; return m; }
+    static std::condition_variable& cv() { static std::condition_variable c; return c; }
+    static std::map<std::pair<int, int>, int>& state() { static std::map<std::pair<int, int>, int> s; return s; }
+};
 
 #ifndef __CUDA_ARCH__
 #define FSB_ARCH_OK 1

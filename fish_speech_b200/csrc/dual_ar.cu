@@ -180,7 +180,8 @@ gemv_fn pick_gemv(int M, int pro, int epi) {
 int m_bucket(int M) { return M <= 1 ? 1 : M <= 2 ? 2 : M <= 4 ? 4 : 8; }
 
 cudaError_t set_gemv_attrs() {
-    if (!fsb_first_on_device(0)) return cudaSuccess;
+    FsbOnce once(0);
+    if (!once.first) return cudaSuccess;
     const int ms[4] = {1, 2, 4, 8};
     for (int pro = 0; pro < 2; ++pro)
         for (int epi = 0; epi < 3; ++epi)
@@ -211,7 +212,8 @@ gemv_tma_fn pick_gemv_tma(int M, int pro, int epi) {
     return pick_gemv_tma<PRO_NONE, EPI_SWIGLU>(M);
 }
 cudaError_t set_gemv_tma_attrs() {
-    if (!fsb_first_on_device(1)) return cudaSuccess;
+    FsbOnce once(1);
+    if (!once.first) return cudaSuccess;
     const int ms[4] = {1, 2, 4, 8};
     for (int pro = 0; pro < 2; ++pro)
         for (int epi = 0; epi < 3; ++epi)
@@ -1357,7 +1359,10 @@ static const CUtensorMap* fa_map(fsb_dual_ar* h, const void* ptr, uint64_t d0, u
 static int prefill_attention_fa(fsb_dual_ar* h, cudaStream_t s, const LayerW& w, int T, const int32_t* pos, int pos0, int slot) {
     const fsb_dual_ar_desc& d = h->d;
     const int H = d.n_head, KV = d.n_kv_head, S = h->kv_max_seq;
-    if (fsb_first_on_device(5)) CK(cudaFuncSetAttribute((const void*)fa_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
+    {
+        FsbOnce once(5);
+        if (once.first) CK(cudaFuncSetAttribute((const void*)fa_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
+    }
     QkPrepArgs qa{};
     qa.qkv = h->pqkv; qa.q_out = h->pq; qa.kcache = w.kc; qa.vcache = w.vc; qa.q_norm = w.q_norm; qa.k_norm = w.k_norm; qa.rope = h->rope;
     qa.pos = pos; qa.T = T; qa.H = H; qa.KV = KV; qa.S = S; qa.slot = slot; qa.qk_norm = d.qk_norm; qa.eps = d.norm_eps;

@@ -371,9 +371,12 @@ inline int rgn_pick_nw(int N, int n_sm) {
     return 0;
 }
 inline cudaError_t rgn_launch(cudaStream_t s, bool pdl, const CUtensorMap& mW, const CUtensorMap& mX, int M, int N, int K, int nw, bf16* out) {
-    if (fsb_first_on_device(3)) {
-        cudaError_t e = cudaFuncSetAttribute((const void*)rows_gemm_narrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rgn_smem_bytes());
-        if (e != cudaSuccess) return e;
+    {
+        FsbOnce once(3);
+        if (once.first) {
+            cudaError_t e = cudaFuncSetAttribute((const void*)rows_gemm_narrow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rgn_smem_bytes());
+            if (e != cudaSuccess) return e;
+        }
     }
     RowsGemmNArgs a{};
     a.out = out; a.M = M; a.N = N; a.K = K; a.nw = nw; a.kb = K / RG_BK;
@@ -598,7 +601,8 @@ typedef void (*rows_gemm_fn)(const CUtensorMap, const CUtensorMap, const CUtenso
 inline rows_gemm_fn rg_pick(int bn) { return bn == 32 ? rows_gemm_kernel<32> : bn == 64 ? rows_gemm_kernel<64> : rows_gemm_kernel<128>; }
 inline int rg_bn_for(int M) { return M <= 32 ? 32 : M <= 64 ? 64 : 128; }
 inline cudaError_t rg_set_attrs() {
-    if (!fsb_first_on_device(2)) return cudaSuccess;
+    FsbOnce once(2);
+    if (!once.first) return cudaSuccess;
     const int bns[3] = {32, 64, 128};
     for (int i = 0; i < 3; ++i) {
         cudaError_t e = cudaFuncSetAttribute((const void*)rg_pick(bns[i]), cudaFuncAttributeMaxDynamicSharedMemorySize,

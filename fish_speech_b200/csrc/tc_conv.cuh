@@ -682,7 +682,8 @@ inline int tcv_stages_for(int bn, bool staged, bool has_res) {
     return fit < TCV_STAGES_MAX ? fit : TCV_STAGES_MAX;
 }
 inline cudaError_t tcv_set_attrs() {
-    if (!fsb_first_on_device(4)) return cudaSuccess;
+    FsbOnce once(4);
+    if (!once.first) return cudaSuccess;
     const int bns[6] = {256, 192, 128, 96, 64, 32};
     for (int f = 0; f < 2; ++f)
         for (int i = 0; i < 6; ++i) {
